@@ -1,0 +1,88 @@
+/*
+ * oracle/ctrsampler.cpp — TEST INFRASTRUCTURE.
+ *
+ * A Mitsuba *sampler plugin* ("ctr") written for this repository and built against the unmodified
+ * reference by oracle/Makefile.ref.  It implements the reference's Sampler interface
+ * (include/mitsuba/render/sampler.h:77-173; the stock implementation it stands in for is
+ * src/samplers/independent.cpp:51-106) with the SAME counter-based stream the CUDA path uses:
+ *
+ *     word(x, y, sampleIndex, dim) = Philox4x32-10(ctr = {x, y, sampleIndex, dim/4},
+ *                                                   key = {seed, 0x6d747362})[dim % 4]
+ *     float = bitcast((word >> 9) | 0x3f800000) - 1      (same 23-bit trick as Random::nextFloat,
+ *                                                        src/libcore/random.cpp:626-635)
+ *
+ * `dim` counts next1D()/next2D() draws since generate()/advance().  With it the reference's own `path`
+ * plugin consumes exactly the random numbers of the CUDA wavefront, so per-sample radiance can be
+ * compared directly (classic block renderer: SamplingIntegrator::renderBlock,
+ * src/librender/integrator.cpp:141-189 — generate(offset) per pixel, advance() per sample).
+ */
+#include <mitsuba/render/sampler.h>
+
+MTS_NAMESPACE_BEGIN
+
+static inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+		uint32_t k0, uint32_t k1, uint32_t out[4]) {
+	for (int r = 0; r < 10; ++r) {
+		uint64_t p0 = (uint64_t) 0xD2511F53u * c0, p1 = (uint64_t) 0xCD9E8D57u * c2;
+		uint32_t n0 = (uint32_t) (p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t) p1,
+		         n2 = (uint32_t) (p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t) p0;
+		c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+		k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+	}
+	out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+class CounterSampler : public Sampler {
+public:
+	CounterSampler() : Sampler(Properties()) { }
+	CounterSampler(const Properties &props) : Sampler(props) {
+		m_sampleCount = props.getSize("sampleCount", 4);
+		m_seed = (uint32_t) props.getInteger("seed", 0);
+		m_px = m_py = 0; m_dim = 0; m_block = 0xFFFFFFFFu;
+	}
+	CounterSampler(Stream *stream, InstanceManager *manager) : Sampler(stream, manager) {
+		m_seed = stream->readUInt();
+		m_px = m_py = 0; m_dim = 0; m_block = 0xFFFFFFFFu;
+	}
+	void serialize(Stream *stream, InstanceManager *manager) const {
+		Sampler::serialize(stream, manager);
+		stream->writeUInt(m_seed);
+	}
+	ref<Sampler> clone() {
+		ref<CounterSampler> s = new CounterSampler();
+		s->m_sampleCount = m_sampleCount; s->m_seed = m_seed;
+		s->m_px = m_px; s->m_py = m_py; s->m_dim = 0; s->m_block = 0xFFFFFFFFu;
+		for (size_t i=0; i<m_req1D.size(); ++i) s->request1DArray(m_req1D[i]);
+		for (size_t i=0; i<m_req2D.size(); ++i) s->request2DArray(m_req2D[i]);
+		return s.get();
+	}
+	void generate(const Point2i &offset, size_t nextSampleIdx) {
+		m_px = (uint32_t) offset.x; m_py = (uint32_t) offset.y;
+		if (nextSampleIdx != (size_t) ~0) m_sampleIndex = nextSampleIdx;
+		m_dim = 0; m_block = 0xFFFFFFFFu;
+		m_dimension1DArray = m_dimension2DArray = 0;
+	}
+	void advance() { Sampler::advance(); m_dim = 0; m_block = 0xFFFFFFFFu; }
+	void setSampleIndex(size_t idx) { Sampler::setSampleIndex(idx); m_dim = 0; m_block = 0xFFFFFFFFu; }
+	Float next1D() {
+		uint32_t blk = m_dim >> 2;
+		if (blk != m_block) {
+			philox4x32_10(m_px, m_py, (uint32_t) m_sampleIndex, blk, m_seed, 0x6d747362u, m_words);
+			m_block = blk;
+		}
+		uint32_t w = m_words[m_dim & 3];
+		++m_dim;
+		union { uint32_t u; float f; } x;
+		x.u = (w >> 9) | 0x3f800000u;
+		return x.f - 1.0f;
+	}
+	Point2 next2D() { Float a = next1D(); Float b = next1D(); return Point2(a, b); }
+	std::string toString() const { return "CounterSampler[]"; }
+	MTS_DECLARE_CLASS()
+private:
+	uint32_t m_seed, m_px, m_py, m_dim, m_block, m_words[4];
+};
+
+MTS_IMPLEMENT_CLASS_S(CounterSampler, false, Sampler)
+MTS_EXPORT_PLUGIN(CounterSampler, "Counter-based (Philox4x32-10) sampler shared with the CUDA path");
+MTS_NAMESPACE_END

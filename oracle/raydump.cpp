@@ -1,0 +1,243 @@
+/*
+ * oracle/raydump.cpp — TEST INFRASTRUCTURE (golden-vector generator + CPU reference timing).
+ *
+ * A Mitsuba *utility plugin* (loaded by the reference's own `mtsutil`, src/mitsuba/mtsutil.cpp:300-345)
+ * written for this repository and compiled against the UNMODIFIED reference headers/libraries built by
+ * oracle/Makefile.ref.  It calls the reference's public API only:
+ *
+ *   trace   : ShapeKDTree::rayIntersect(ray, its)  (src/librender/skdtree.cpp:112-142)  closest hit
+ *             ShapeKDTree::rayIntersect(ray)       (src/librender/skdtree.cpp:207-226)  any hit
+ *   bsdf    : BSDF::eval / pdf / sample            (include/mitsuba/render/bsdf.h:215-445)
+ *   emitter : Scene::sampleEmitterDirect / pdfEmitterDirect (src/librender/scene.cpp:860-884,981-984)
+ *
+ * Usage (all files raw little-endian float32/int32, no header):
+ *   mtsutil raydump trace   <scene.xml|mesh.ply> <rays.bin> <out.bin> [threads] [repeats]
+ *       rays : N x 8  {o.xyz, mint, d.xyz, maxt}
+ *       out  : N x 16 {t, u, v, shape(i32), prim(i32), p.xyz, ng.xyz, ns.xyz, any(i32), 0}
+ *   mtsutil raydump bsdf    <scene.xml> <in.bin> <out.bin>
+ *       in   : N x 12 {shape, wi.xyz, wo.xyz, s1, s2, 0,0,0}
+ *       out  : N x 16 {eval.rgb, pdf, weight.rgb, wo'.xyz, pdf', eta, sampledType, 0,0,0}
+ *   mtsutil raydump emitter <scene.xml> <in.bin> <out.bin>
+ *       in   : N x 8  {p.xyz, n.xyz, s1, s2}
+ *       out  : N x 12 {value.rgb, pdf, d.xyz, dist, measure, pdfEmitterDirect, n_emitter.z?0, 0}
+ * Timing for `trace` is printed as one JSON line on stdout (prefix "RAYDUMP ").
+ */
+#include <mitsuba/render/util.h>
+#include <mitsuba/render/scene.h>
+#include <mitsuba/render/skdtree.h>
+#include <mitsuba/render/trimesh.h>
+#include <mitsuba/render/bsdf.h>
+#include <mitsuba/render/emitter.h>
+#include <mitsuba/core/plugin.h>
+#include <mitsuba/core/fresolver.h>
+#include <mitsuba/core/timer.h>
+#include <mitsuba/core/filesystem.h>
+#include <thread>
+#include <vector>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+
+MTS_NAMESPACE_BEGIN
+
+static std::vector<float> readFloats(const char *fn) {
+	FILE *f = fopen(fn, "rb");
+	if (!f) SLog(EError, "raydump: cannot open \"%s\"", fn);
+	fseek(f, 0, SEEK_END);
+	size_t sz = (size_t) ftell(f);
+	fseek(f, 0, SEEK_SET);
+	std::vector<float> v(sz / 4);
+	if (fread(v.data(), 4, v.size(), f) != v.size()) SLog(EError, "raydump: short read");
+	fclose(f);
+	return v;
+}
+
+static void writeFloats(const char *fn, const std::vector<float> &v) {
+	FILE *f = fopen(fn, "wb");
+	if (!f) SLog(EError, "raydump: cannot write \"%s\"", fn);
+	fwrite(v.data(), 4, v.size(), f);
+	fclose(f);
+}
+
+static inline float i2f(int32_t i) { float f; memcpy(&f, &i, 4); return f; }
+
+class RayDump : public Utility {
+public:
+	ref<Scene> m_scene;
+	ref<ShapeKDTree> m_kdtree;
+	std::vector<const Shape *> m_shapes;
+
+	void load(const char *fn) {
+		ref<FileResolver> fileResolver = Thread::getThread()->getFileResolver();
+		std::string lower(fn);
+		for (auto &c : lower) c = (char) tolower(c);
+		bool isPly = lower.size() > 4 && lower.substr(lower.size()-4) == ".ply";
+		if (!isPly) {
+			fs::path filename = fs::decode_pathstr(fileResolver->resolve(fs::pathstr(fn)));
+			ref<FileResolver> frClone = fileResolver->clone();
+			frClone->prependPath(fs::encode_pathstr(fs::absolute(filename).parent_path()));
+			Thread::getThread()->setFileResolver(frClone);
+			m_scene = loadScene(fs::pathstr(fn));
+			m_scene->initialize();
+			m_kdtree = m_scene->getKDTree();
+			/* kd-tree shape order == order of addShape() calls == Scene::m_shapes order */
+			const ref_vector<Shape> &shapes = m_scene->getShapes();
+			for (size_t i=0; i<shapes.size(); ++i)
+				m_shapes.push_back(shapes[i].get());
+		} else {
+			Properties props("ply");
+			props.setString("filename", fn);
+			ref<TriMesh> mesh = static_cast<TriMesh *>(PluginManager::getInstance()->
+				createObject(MTS_CLASS(TriMesh), props));
+			mesh->configure();
+			mesh->incRef();
+			m_kdtree = new ShapeKDTree();
+			m_kdtree->addShape(mesh);
+			m_kdtree->build();
+			m_shapes.push_back(mesh.get());
+		}
+	}
+
+	int shapeIndex(const Shape *s) const {
+		for (size_t i=0; i<m_shapes.size(); ++i)
+			if (m_shapes[i] == s) return (int) i;
+		return -1;
+	}
+
+	int trace(int argc, char **argv) {
+		if (argc < 5) { cout << "trace <scene> <rays> <out> [threads] [repeats]" << endl; return 1; }
+		ref<Timer> buildTimer = new Timer();
+		load(argv[2]);
+		unsigned buildMs = buildTimer->getMilliseconds();
+		std::vector<float> rays = readFloats(argv[3]);
+		size_t n = rays.size() / 8;
+		int nThreads = argc > 5 ? atoi(argv[5]) : 1;
+		int repeats = argc > 6 ? atoi(argv[6]) : 1;
+		if (nThreads < 1) nThreads = (int) std::thread::hardware_concurrency();
+		std::vector<float> out(n * 16, 0.0f);
+		const ShapeKDTree *kd = m_kdtree.get();
+		Thread *parent = Thread::getThread();
+		double bestClosest = 1e30, bestAny = 1e30;
+
+		for (int rep = 0; rep < repeats; ++rep) {
+			for (int pass = 0; pass < 2; ++pass) {
+				auto t0 = std::chrono::steady_clock::now();
+				std::vector<std::thread> threads;
+				for (int tid = 0; tid < nThreads; ++tid) {
+					threads.emplace_back([&, tid]() {
+						Thread *thr = Thread::registerUnmanagedThread("raydump");
+						thr->setLogger(parent->getLogger());
+						thr->setFileResolver(parent->getFileResolver());
+						size_t begin = n * tid / nThreads, end = n * (tid + 1) / nThreads;
+						for (size_t i = begin; i < end; ++i) {
+							const float *r = &rays[i*8];
+							float *o = &out[i*16];
+							Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7], 0.0f);
+							if (pass == 0) {
+								Intersection its;
+								if (kd->rayIntersect(ray, its)) {
+									o[0] = its.t; o[1] = its.uv.x; o[2] = its.uv.y;
+									o[3] = i2f(shapeIndex(its.shape)); o[4] = i2f((int32_t) its.primIndex);
+									o[5] = its.p.x; o[6] = its.p.y; o[7] = its.p.z;
+									o[8] = its.geoFrame.n.x; o[9] = its.geoFrame.n.y; o[10] = its.geoFrame.n.z;
+									o[11] = its.shFrame.n.x; o[12] = its.shFrame.n.y; o[13] = its.shFrame.n.z;
+								} else {
+									o[0] = std::numeric_limits<float>::infinity();
+									o[3] = i2f(-1); o[4] = i2f(-1);
+								}
+							} else {
+								o[14] = i2f(kd->rayIntersect(ray) ? 1 : 0);
+							}
+						}
+					});
+				}
+				for (auto &t : threads) t.join();
+				double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+				if (pass == 0) bestClosest = std::min(bestClosest, ms); else bestAny = std::min(bestAny, ms);
+			}
+		}
+		writeFloats(argv[4], out);
+		printf("RAYDUMP {\"rays\": %zu, \"threads\": %d, \"repeats\": %d, \"build_ms\": %u, \"closest_ms\": %.3f, "
+			"\"any_ms\": %.3f, \"closest_mrays\": %.4f, \"any_mrays\": %.4f, \"prims\": %u}\n",
+			n, nThreads, repeats, buildMs, bestClosest, bestAny, n / bestClosest / 1e3, n / bestAny / 1e3,
+			(unsigned) kd->getPrimitiveCount());
+		fflush(stdout);
+		return 0;
+	}
+
+	int bsdf(int argc, char **argv) {
+		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
+		load(argv[2]);
+		std::vector<float> in = readFloats(argv[3]);
+		size_t n = in.size() / 12;
+		std::vector<float> out(n * 16, 0.0f);
+		for (size_t i = 0; i < n; ++i) {
+			const float *r = &in[i*12];
+			float *o = &out[i*16];
+			const Shape *shape = m_shapes.at((size_t) r[0]);
+			const BSDF *bsdf = shape->getBSDF();
+			Intersection its;
+			its.p = Point(0.0f); its.t = 1.0f; its.shape = shape;
+			its.geoFrame = Frame(Normal(0, 0, 1)); its.shFrame = its.geoFrame;
+			its.uv = Point2(0.5f); its.hasUVPartials = false; its.time = 0; its.instance = NULL;
+			its.dpdu = Vector(1, 0, 0); its.dpdv = Vector(0, 1, 0);
+			Vector wi(r[1], r[2], r[3]), wo(r[4], r[5], r[6]);
+			its.wi = wi;
+			{
+				BSDFSamplingRecord bRec(its, wi, wo, ERadiance);
+				Spectrum f = bsdf->eval(bRec);
+				Float pdf = bsdf->pdf(bRec);
+				Float rr, gg, bb; f.toLinearRGB(rr, gg, bb);
+				o[0] = rr; o[1] = gg; o[2] = bb; o[3] = pdf;
+			}
+			{
+				BSDFSamplingRecord bRec(its, NULL, ERadiance);
+				bRec.wi = wi;
+				Float pdf = 0;
+				Spectrum w = bsdf->sample(bRec, pdf, Point2(r[7], r[8]));
+				Float rr, gg, bb; w.toLinearRGB(rr, gg, bb);
+				o[4] = rr; o[5] = gg; o[6] = bb;
+				o[7] = bRec.wo.x; o[8] = bRec.wo.y; o[9] = bRec.wo.z;
+				o[10] = pdf; o[11] = bRec.eta; o[12] = (float) bRec.sampledType;
+			}
+		}
+		writeFloats(argv[4], out);
+		return 0;
+	}
+
+	int emitter(int argc, char **argv) {
+		if (argc < 5) { cout << "emitter <scene> <in> <out>" << endl; return 1; }
+		load(argv[2]);
+		std::vector<float> in = readFloats(argv[3]);
+		size_t n = in.size() / 8;
+		std::vector<float> out(n * 12, 0.0f);
+		for (size_t i = 0; i < n; ++i) {
+			const float *r = &in[i*8];
+			float *o = &out[i*12];
+			DirectSamplingRecord dRec(Point(r[0], r[1], r[2]), 0.0f);
+			dRec.refN = Normal(r[3], r[4], r[5]);
+			Spectrum value = m_scene->sampleEmitterDirect(dRec, Point2(r[6], r[7]), false);
+			Float rr, gg, bb; value.toLinearRGB(rr, gg, bb);
+			o[0] = rr; o[1] = gg; o[2] = bb; o[3] = dRec.pdf;
+			o[4] = dRec.d.x; o[5] = dRec.d.y; o[6] = dRec.d.z; o[7] = dRec.dist;
+			o[8] = (float) dRec.measure;
+			o[9] = (dRec.pdf > 0 && !value.isZero()) ? m_scene->pdfEmitterDirect(dRec) : 0.0f;
+		}
+		writeFloats(argv[4], out);
+		return 0;
+	}
+
+	int run(int argc, char **argv) {
+		if (argc < 2) { cout << "raydump trace|bsdf|emitter ..." << endl; return 1; }
+		if (!strcmp(argv[1], "trace")) return trace(argc, argv);
+		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
+		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
+		cout << "unknown mode" << endl;
+		return 1;
+	}
+
+	MTS_DECLARE_UTILITY()
+};
+
+MTS_EXPORT_UTILITY(RayDump, "Dump hit records / BSDF / emitter values through the reference API")
+MTS_NAMESPACE_END
