@@ -1,0 +1,251 @@
+/*
+ * mtsb200.h — flat C ABI of libmtsb200.so, the B200-native (sm_100a CUDA) implementation of Mitsuba's
+ * ray-intersection + path-tracing hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, opaque handles, no C++/torch/Mitsuba types.
+ * Every entry point cites the reference interface it stands in for (paths relative to the reference
+ * tree, li779/mitsuba-im).  The Mitsuba-side adapter (an Integrator / ResponsiveIntegrator plugin) lives
+ * in mitsuba-im_b200/plugin/ and is described in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returning int returns 0 on success and a negative MTSB_E* code on failure;
+ *     mtsb_last_error() returns a thread-local description of the last failure.
+ *   - the caller owns every host buffer passed in; the library copies what it needs before returning
+ *     (mtsb_scene_* calls) or before mtsb_*_sync() returns (trace / film calls).
+ *   - a handle may be used from one host thread at a time; different handles are independent.
+ *   - there is NO CPU fallback: without a CUDA device every call fails with MTSB_ENODEVICE.
+ *   - Float = float32, Spectrum = 3 x float32 linear RGB (reference build: SINGLE_PRECISION,
+ *     SPECTRUM_SAMPLES=3).
+ */
+#ifndef MTSB200_H
+#define MTSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#  define MTSB_API
+#else
+#  define MTSB_API __attribute__((visibility("default")))
+#endif
+
+#define MTSB_ABI_VERSION 1
+
+enum {
+	MTSB_OK          =  0,
+	MTSB_EINVAL      = -1,   /* bad argument / call order */
+	MTSB_ENODEVICE   = -2,   /* no CUDA device / wrong architecture */
+	MTSB_ECUDA       = -3,   /* CUDA runtime error (message in mtsb_last_error) */
+	MTSB_EUNSUPPORTED= -4,   /* plugin outside the supported subset */
+	MTSB_ENOMEM      = -5
+};
+
+typedef struct mtsb_ctx    mtsb_ctx;
+typedef struct mtsb_scene  mtsb_scene;
+typedef struct mtsb_render mtsb_render;
+
+/* ---------------------------------------------------------------- records ------------------------ */
+
+/* A ray, the fields of TRay that intersection queries read (include/mitsuba/core/ray.h:36-134):
+ * o, mint, d, maxt.  dRcp is recomputed on the device; time is unused on this path. 32 bytes. */
+typedef struct mtsb_ray {
+	float o[3]; float mint;
+	float d[3]; float maxt;
+} mtsb_ray;
+
+/* Closest-hit record: what ShapeKDTree's IntersectionCache holds after rayIntersectHavran
+ * (include/mitsuba/render/skdtree.h:237-241) plus t.  `prim` is the kd-tree's GLOBAL primitive index
+ * (shape prefix sum + index inside the shape, ShapeKDTree::build, src/librender/skdtree.cpp:68-70);
+ * 0xFFFFFFFF and t = +inf on a miss.  For an analytic rectangle u,v are the object-space x,y of the
+ * hit (Rectangle::rayIntersect temp record, src/shapes/rectangle.cpp:125-147).  16 bytes. */
+typedef struct mtsb_hit {
+	float t, u, v;
+	uint32_t prim;
+} mtsb_hit;
+#define MTSB_NO_HIT 0xFFFFFFFFu
+
+/* Full surface record = the fields of Intersection that MIPathTracer reads after
+ * ShapeKDTree::fillIntersectionRecord<true> (include/mitsuba/render/skdtree.h:343-428). */
+typedef struct mtsb_surface {
+	float t, u, v; uint32_t prim;      /* as mtsb_hit                                        */
+	uint32_t shape, prim_local;         /* shape index (addShape order) and index in the shape */
+	float p[3];                         /* barycentric hit point                               */
+	float ng[3];                        /* geoFrame.n                                          */
+	float ns[3], s[3], tt[3];           /* shFrame.n / .s / .t                                 */
+	float uv[2];                        /* its.uv                                              */
+} mtsb_surface;
+
+/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor}.cpp), constant textures only. */
+enum {
+	MTSB_BSDF_DIFFUSE        = 0,  /* p[0..2] reflectance                                                    */
+	MTSB_BSDF_DIELECTRIC     = 1,  /* p[0] eta=intIOR/extIOR, p[1..3] specularReflectance, p[4..6] specularTransmittance */
+	MTSB_BSDF_PLASTIC        = 2,  /* p[0] eta, p[1..3] diffuseReflectance, p[4..6] specularReflectance,
+	                                  p[7] fdrInt, p[8] fdrExt, p[9] specularSamplingWeight, p[10] nonlinear(0/1) */
+	MTSB_BSDF_ROUGHCONDUCTOR = 3,  /* p[0] alphaU, p[1] alphaV, p[2..4] eta, p[5..7] k, p[8..10] specularReflectance,
+	                                  p[11] distribution (0 beckmann, 1 ggx), p[12] sampleVisible(0/1)           */
+	MTSB_BSDF_NULL           = 4,  /* black diffuse given to BSDF-less emitter shapes (src/librender/shape.cpp:48-58) */
+	MTSB_BSDF_TWOSIDED_FLAG  = 0x100 /* OR-ed in: wrapped by `twosided` (src/bsdfs/twosided.cpp), same BSDF both sides */
+};
+typedef struct mtsb_bsdf_desc {
+	int32_t type;
+	float   p[15];
+} mtsb_bsdf_desc;
+
+/* Emitter subset (src/emitters/{area,point,constant}.cpp). */
+enum {
+	MTSB_EMITTER_AREA     = 0,  /* radiance; attached to shape `shape`            */
+	MTSB_EMITTER_POINT    = 1,  /* intensity; position pos                        */
+	MTSB_EMITTER_CONSTANT = 2   /* radiance; bounding sphere filled in at commit  */
+};
+typedef struct mtsb_emitter_desc {
+	int32_t  type;
+	uint32_t shape;              /* AREA: shape index                                   */
+	float    radiance[3];        /* radiance / intensity, linear RGB                    */
+	float    pos[3];             /* POINT: world position                               */
+	float    sampling_weight;    /* Emitter::m_samplingWeight (default 1)               */
+} mtsb_emitter_desc;
+
+/* Perspective sensor: the matrices PerspectiveCameraImpl::configure builds
+ * (src/sensors/perspective.cpp:126-180), row-major 4x4. */
+typedef struct mtsb_camera {
+	float sample_to_camera[16];  /* m_sampleToCamera (maps [0,1]^2 x near plane to camera space) */
+	float camera_to_world[16];   /* m_worldTransform->eval(t) — assumed static                    */
+	float near_clip, far_clip;
+	float inv_resolution[2];     /* 1/film size (m_invResolution)                                 */
+} mtsb_camera;
+
+/* Film: the float bitmap of an ImageBlock (src/librender/imageblock.cpp:22-37) + its filter table. */
+typedef struct mtsb_film_desc {
+	int32_t width, height;       /* ImageBlock size (without border)                           */
+	int32_t offset[2];           /* ImageBlock::getOffset()                                    */
+	int32_t border;              /* ImageBlock::getBorderSize() = ceil(radius - 0.5)           */
+	int32_t channels;            /* 4 = ESpectrumAlpha/ERGBA, 5 = ESpectrumAlphaWeight         */
+	float   filter_radius;       /* ReconstructionFilter::getRadius()                          */
+	float   filter_table[32];    /* m_values[0..31] (include/mitsuba/core/rfilter.h:76-77)     */
+	int32_t crop_offset[2];      /* film crop window in sensor pixels                          */
+	int32_t crop_size[2];
+} mtsb_film_desc;
+
+enum { MTSB_INTEGRATOR_PATH = 0, MTSB_INTEGRATOR_DIRECT = 1 };
+typedef struct mtsb_integrator_desc {
+	int32_t type;
+	int32_t max_depth;           /* MonteCarloIntegrator maxDepth (-1 = unbounded)  (src/librender/integrator.cpp:191-226) */
+	int32_t rr_depth;            /* rrDepth (default 5)                              */
+	int32_t strict_normals;
+	int32_t hide_emitters;
+	int32_t emitter_samples;     /* direct only (src/integrators/direct/direct.cpp)  */
+	int32_t bsdf_samples;        /* direct only                                      */
+} mtsb_integrator_desc;
+
+enum { MTSB_BUILDER_LBVH = 0, MTSB_BUILDER_PLOC = 1 };
+
+/* ---------------------------------------------------------------- context ------------------------ */
+
+MTSB_API int         mtsb_abi_version(void);
+MTSB_API const char *mtsb_last_error(void);
+MTSB_API int         mtsb_device_count(void);
+/* One context per GPU (one CUDA stream + scratch allocator). */
+MTSB_API int  mtsb_ctx_create(int device, mtsb_ctx **out);
+MTSB_API void mtsb_ctx_destroy(mtsb_ctx *ctx);
+MTSB_API int  mtsb_ctx_sync(mtsb_ctx *ctx);
+/* cudaStream_t of the context, for callers that time with their own events. */
+MTSB_API void *mtsb_ctx_stream(mtsb_ctx *ctx);
+
+/* ---------------------------------------------------------------- scene -------------------------- */
+/* Replaces ShapeKDTree::addShape/build (src/librender/skdtree.cpp:49-110) and the emitter/BSDF lookups
+ * Scene::initialize performs (src/librender/scene.cpp:330-392).  Shapes must be added in the order of
+ * Scene::getShapes(); that order defines shape indices and the global primitive index. */
+MTSB_API int  mtsb_scene_create(mtsb_ctx *ctx, mtsb_scene **out);
+MTSB_API void mtsb_scene_destroy(mtsb_scene *scene);
+MTSB_API int  mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc);          /* returns id >= 0 */
+MTSB_API int  mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc);    /* returns id >= 0 */
+/* TriMesh (include/mitsuba/render/trimesh.h): positions 3V, normals 3V or NULL, texcoords 2V or NULL,
+ * triangles 3T uint32.  emitter = -1 if none.  Returns the shape index. */
+MTSB_API int  mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *normals,
+                                  const float *texcoords, const uint32_t *triangles,
+                                  size_t vertex_count, size_t triangle_count, int bsdf, int emitter);
+/* Analytic rectangle (src/shapes/rectangle.cpp): object-to-world 4x4 row-major, flipNormals. */
+MTSB_API int  mtsb_scene_add_rectangle(mtsb_scene *scene, const float object_to_world[16],
+                                       int flip_normals, int bsdf, int emitter);
+/* Builds TriAccel records, the BVH and the emitter tables on the device. */
+MTSB_API int  mtsb_scene_commit(mtsb_scene *scene, int builder);
+/* Scene AABB as ShapeKDTree::getAABB() returns it (enlarged, include/mitsuba/render/gkdtree.h:1217-1220). */
+MTSB_API int  mtsb_scene_aabb(const mtsb_scene *scene, float min_out[3], float max_out[3]);
+MTSB_API size_t mtsb_scene_primitive_count(const mtsb_scene *scene);
+MTSB_API size_t mtsb_scene_shape_count(const mtsb_scene *scene);
+/* shape_offsets[i] = global primitive index of shape i's first primitive; n+1 entries. */
+MTSB_API int  mtsb_scene_shape_offsets(const mtsb_scene *scene, uint32_t *offsets_out);
+/* Build statistics: out[0]=build ms (device), out[1]=wide nodes, out[2]=bytes of nodes, out[3]=bytes of
+ * triangle records, out[4]=SAH cost of the wide tree, out[5]=leaf count, out[6]=max depth. */
+MTSB_API int  mtsb_scene_build_stats(const mtsb_scene *scene, double out[8]);
+
+/* ---------------------------------------------------------------- ray queries -------------------- */
+/* Batched ShapeKDTree::rayIntersect(ray, its) (src/librender/skdtree.cpp:112-142) without the record
+ * fill: scene-AABB clip, adaptive epsilon (mint == Epsilon is scaled by max(|o|, Epsilon)), closest
+ * primitive, inclusive t range.  rays/hits are HOST pointers unless on_device != 0.  Asynchronous on
+ * the context stream when on_device != 0; synchronous (returns with hits filled) otherwise. */
+MTSB_API int  mtsb_trace_closest(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device);
+/* Batched ShapeKDTree::rayIntersect(ray) (src/librender/skdtree.cpp:207-226): any hit; out[i] = 0/1.
+ * The epsilon scale has no Epsilon floor in this overload. */
+MTSB_API int  mtsb_trace_any(mtsb_scene *scene, const mtsb_ray *rays, size_t n, uint8_t *out, int on_device);
+/* Batched closest hit + ShapeKDTree::fillIntersectionRecord<true> (include/mitsuba/render/skdtree.h:343-428). */
+MTSB_API int  mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_surface *out, int on_device);
+/* Traversal counters of the last trace call when built with counters enabled, else zeros:
+ * out[0]=nodes visited, out[1]=primitive tests, out[2]=rays. */
+MTSB_API int  mtsb_trace_counters(mtsb_scene *scene, uint64_t out[4]);
+/* Re-traces a batch with the counters enabled (closest or any hit) and returns them; the analogue of the
+ * "Expected traversals/query" / "Expected prim. visits/query" figures the kd-tree build logs
+ * (include/mitsuba/render/gkdtree.h:1252-1255), measured rather than estimated. */
+MTSB_API int  mtsb_trace_count(mtsb_scene *scene, const mtsb_ray *rays, size_t n, int any_hit, int on_device, uint64_t out[4]);
+/* Page-locked host memory so that host-pointer calls copy at PCIe speed (plain malloc memory also works). */
+MTSB_API void *mtsb_host_alloc(size_t bytes);
+MTSB_API void  mtsb_host_free(void *p);
+
+/* Pointwise plugin math, for parity tests against BSDF::eval/pdf/sample
+ * (include/mitsuba/render/bsdf.h:215-445) and Scene::sampleEmitterDirect / pdfEmitterDirect
+ * (src/librender/scene.cpp:860-884,981-984) *without* the visibility test.  Host pointers.
+ *   bsdf_in  : n x 8  {wi.xyz, wo.xyz, s1, s2}   local frame
+ *   bsdf_out : n x 16 {eval.rgb, pdf, weight.rgb, wo'.xyz, pdf', eta, sampledType, 0,0,0}
+ *   em_in    : n x 8  {p.xyz, refN.xyz, s1, s2}
+ *   em_out   : n x 12 {value.rgb, pdf, d.xyz, dist, measure, pdfEmitterDirect, emitter id, 0} */
+MTSB_API int  mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *bsdf_in, size_t n, float *bsdf_out);
+MTSB_API int  mtsb_eval_emitter(mtsb_scene *scene, const float *em_in, size_t n, float *em_out);
+
+/* ---------------------------------------------------------------- rendering ---------------------- */
+/* Replaces the per-sample loop SamplingIntegrator::renderBlock / ImageOrderIntegrator::render
+ * (src/librender/integrator.cpp:141-189,336-402) + MIPathTracer::Li (src/integrators/path/path.cpp:119-294)
+ * / MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309) + ImageBlock::put
+ * (include/mitsuba/render/imageblock.h:161-221) with a wavefront pipeline.  The film lives on the
+ * device as un-normalised sums in ImageBlock layout: (H+2b) x (W+2b) x channels float32. */
+MTSB_API int  mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_film_desc *film,
+                                 const mtsb_integrator_desc *integrator, uint64_t seed, mtsb_render **out);
+MTSB_API void mtsb_render_destroy(mtsb_render *r);
+MTSB_API int  mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera);
+MTSB_API int  mtsb_render_clear(mtsb_render *r);
+/* Render sample indices [spp_begin, spp_begin + spp_count) of every pixel in `rect` = {x0,y0,x1,y1}
+ * (NULL = whole crop window); spp_total = the sampler's sampleCount (sets diffScaleFactor).
+ * sample_stride/sample_phase select indices s with s % stride == phase (multi-GPU sample-pass split;
+ * pass 1,0 for all).  Asynchronous on the context stream. */
+MTSB_API int  mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
+                               const int32_t rect[4], uint32_t sample_stride, uint32_t sample_phase);
+MTSB_API int  mtsb_render_sync(mtsb_render *r);
+/* Device pointer + float count of the film accumulation buffer (for NCCL reduce by the caller). */
+MTSB_API int  mtsb_film_device_ptr(mtsb_render *r, void **ptr_out, size_t *float_count_out);
+/* dst[i] += film[i] (accumulate != 0) or dst[i] = film[i]; dst is ImageBlock::getBitmap()->getFloatData(). */
+MTSB_API int  mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumulate);
+/* Statistics of the passes since the last clear: out[0]=camera paths, out[1]=closest-hit rays,
+ * out[2]=shadow rays, out[3]=sum of path depths (avgPathLength numerator, path.cpp:290-291),
+ * out[4]=kernel launches. */
+MTSB_API int  mtsb_render_stats(mtsb_render *r, uint64_t out[8]);
+/* Radiance of single camera samples, for parity tests against MIPathTracer::Li with the `ctr`
+ * sampler: samples n x 4 uint32 {px, py, sampleIndex, 0}; out n x 4 float {L.rgb, alpha}; host ptrs. */
+MTSB_API int  mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTSB200_H */

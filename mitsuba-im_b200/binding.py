@@ -1,0 +1,358 @@
+"""ctypes binding of libmtsb200.so (include/mtsb200.h) — the Python host side used by tests and bench.py.
+
+This is plumbing only: every call forwards to the C ABI; there is no Python or CPU implementation of any
+query behind it.  If the shared library is missing the import fails loudly (RuntimeError), and without a
+CUDA device every entry point raises MtsbError(MTSB_ENODEVICE).
+
+Names mirror the reference's operators: Scene.ray_intersect  ~ ShapeKDTree::rayIntersect(ray, its)
+(src/librender/skdtree.cpp:112-142), Scene.ray_intersect_any ~ ShapeKDTree::rayIntersect(ray) (:207-226),
+Render.render_pass ~ SamplingIntegrator::renderBlock (src/librender/integrator.cpp:141-189).
+"""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmtsb200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
+
+MTSB_NO_HIT = 0xFFFFFFFF
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL = 0, 1, 2, 3, 4
+BSDF_TWOSIDED_FLAG = 0x100
+EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
+INTEGRATOR_PATH, INTEGRATOR_DIRECT = 0, 1
+BUILDER_LBVH, BUILDER_PLOC = 0, 1
+
+ray_dtype = np.dtype([("o", "<f4", 3), ("mint", "<f4"), ("d", "<f4", 3), ("maxt", "<f4")])
+hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")])
+surface_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4"), ("shape", "<u4"),
+                          ("prim_local", "<u4"), ("p", "<f4", 3), ("ng", "<f4", 3), ("ns", "<f4", 3),
+                          ("s", "<f4", 3), ("tt", "<f4", 3), ("uv", "<f4", 2)])
+assert ray_dtype.itemsize == 32 and hit_dtype.itemsize == 16 and surface_dtype.itemsize == 92
+
+
+class MtsbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libmtsb200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class BsdfDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("p", C.c_float * 15)]
+
+
+class EmitterDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("shape", C.c_uint32), ("radiance", C.c_float * 3), ("pos", C.c_float * 3),
+                ("sampling_weight", C.c_float)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("sample_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
+                ("near_clip", C.c_float), ("far_clip", C.c_float), ("inv_resolution", C.c_float * 2)]
+
+
+class FilmDesc(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("offset", C.c_int32 * 2), ("border", C.c_int32),
+                ("channels", C.c_int32), ("filter_radius", C.c_float), ("filter_table", C.c_float * 32),
+                ("crop_offset", C.c_int32 * 2), ("crop_size", C.c_int32 * 2)]
+
+
+class IntegratorDesc(C.Structure):
+    _fields_ = [("type", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("strict_normals", C.c_int32),
+                ("hide_emitters", C.c_int32), ("emitter_samples", C.c_int32), ("bsdf_samples", C.c_int32)]
+
+
+def header_symbols():
+    """Every function name the C header declares with MTSB_API."""
+    text = open(HEADER_PATH).read()
+    return sorted(set(re.findall(r"MTSB_API\s+[A-Za-z_ ]+?\*?\s*\*?(mtsb_[a-z0-9_]+)\s*\(", text)))
+
+
+_lib = None
+
+
+def lib():
+    """Loads libmtsb200.so; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libmtsb200.so not found at %s — run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, sz, i32, u32, u64 = C.c_void_p, C.c_size_t, C.c_int, C.c_uint32, C.c_uint64
+    sig = {
+        "mtsb_abi_version": (i32, []), "mtsb_last_error": (C.c_char_p, []), "mtsb_device_count": (i32, []),
+        "mtsb_ctx_create": (i32, [i32, C.POINTER(vp)]), "mtsb_ctx_destroy": (None, [vp]), "mtsb_ctx_sync": (i32, [vp]),
+        "mtsb_ctx_stream": (vp, [vp]),
+        "mtsb_scene_create": (i32, [vp, C.POINTER(vp)]), "mtsb_scene_destroy": (None, [vp]),
+        "mtsb_scene_add_bsdf": (i32, [vp, C.POINTER(BsdfDesc)]), "mtsb_scene_add_emitter": (i32, [vp, C.POINTER(EmitterDesc)]),
+        "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
+        "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]),
+        "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
+        "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
+        "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
+        "mtsb_trace_closest": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_any": (i32, [vp, vp, sz, vp, i32]),
+        "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
+        "mtsb_trace_count": (i32, [vp, vp, sz, i32, i32, vp]),
+        "mtsb_host_alloc": (vp, [sz]), "mtsb_host_free": (None, [vp]),
+        "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
+        "mtsb_render_create": (i32, [vp, C.POINTER(Camera), C.POINTER(FilmDesc), C.POINTER(IntegratorDesc), u64, C.POINTER(vp)]),
+        "mtsb_render_destroy": (None, [vp]), "mtsb_render_set_camera": (i32, [vp, C.POINTER(Camera)]),
+        "mtsb_render_clear": (i32, [vp]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
+        "mtsb_render_sync": (i32, [vp]), "mtsb_film_device_ptr": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]),
+        "mtsb_film_to_host": (i32, [vp, vp, sz, i32]), "mtsb_render_stats": (i32, [vp, vp]),
+        "mtsb_render_samples": (i32, [vp, vp, sz, u32, vp]),
+    }
+    for name, (res, args) in sig.items():
+        if not hasattr(L, name):
+            continue      # symbol table completeness is asserted by tests/test_abi.py
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc < 0:
+        raise MtsbError(rc, lib().mtsb_last_error().decode("utf-8", "replace"))
+    return rc
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def device_count():
+    return lib().mtsb_device_count()
+
+
+class Context:
+    """One per GPU (mtsb_ctx)."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _check(lib().mtsb_ctx_create(device, C.byref(self.h)))
+        self.device = device
+
+    def sync(self):
+        _check(lib().mtsb_ctx_sync(self.h))
+
+    @property
+    def stream(self):
+        return lib().mtsb_ctx_stream(self.h)
+
+    def close(self):
+        if self.h:
+            lib().mtsb_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class PinnedArray:
+    """numpy view over page-locked memory from mtsb_host_alloc."""
+
+    def __init__(self, shape, dtype):
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        self.ptr = lib().mtsb_host_alloc(max(n, 1))
+        if not self.ptr:
+            raise MtsbError(-5, "mtsb_host_alloc failed")
+        buf = (C.c_uint8 * max(n, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().mtsb_host_free(self.ptr)
+            self.ptr = None
+
+
+class Scene:
+    """Device scene (mtsb_scene): shapes are added in Scene::getShapes() order, then commit() builds the BVH."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        _check(lib().mtsb_scene_create(ctx.h, C.byref(self.h)))
+
+    def add_bsdf(self, type_, params=()):
+        d = BsdfDesc()
+        d.type = type_
+        for i, v in enumerate(params):
+            d.p[i] = float(v)
+        return _check(lib().mtsb_scene_add_bsdf(self.h, C.byref(d)))
+
+    def add_emitter(self, type_, radiance=(1, 1, 1), pos=(0, 0, 0), sampling_weight=1.0):
+        d = EmitterDesc()
+        d.type = type_
+        d.shape = 0
+        d.radiance[:] = [float(x) for x in radiance]
+        d.pos[:] = [float(x) for x in pos]
+        d.sampling_weight = float(sampling_weight)
+        return _check(lib().mtsb_scene_add_emitter(self.h, C.byref(d)))
+
+    def add_mesh(self, positions, triangles, normals=None, texcoords=None, bsdf=0, emitter=-1):
+        P = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        T = np.ascontiguousarray(triangles, dtype=np.uint32).reshape(-1, 3)
+        N = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 3)
+        UV = None if texcoords is None else np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1, 2)
+        return _check(lib().mtsb_scene_add_mesh(self.h, _ptr(P), _ptr(N), _ptr(UV), _ptr(T), P.shape[0], T.shape[0], bsdf, emitter))
+
+    def add_rectangle(self, to_world, flip_normals=False, bsdf=0, emitter=-1):
+        M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
+        return _check(lib().mtsb_scene_add_rectangle(self.h, _ptr(M), int(flip_normals), bsdf, emitter))
+
+    def commit(self, builder=BUILDER_LBVH):
+        _check(lib().mtsb_scene_commit(self.h, builder))
+
+    def aabb(self):
+        mn = np.zeros(3, np.float32)
+        mx = np.zeros(3, np.float32)
+        _check(lib().mtsb_scene_aabb(self.h, _ptr(mn), _ptr(mx)))
+        return mn, mx
+
+    @property
+    def primitive_count(self):
+        return lib().mtsb_scene_primitive_count(self.h)
+
+    def shape_offsets(self):
+        n = lib().mtsb_scene_shape_count(self.h)
+        out = np.zeros(n + 1, np.uint32)
+        _check(lib().mtsb_scene_shape_offsets(self.h, _ptr(out)))
+        return out
+
+    def build_stats(self):
+        out = np.zeros(8, np.float64)
+        _check(lib().mtsb_scene_build_stats(self.h, _ptr(out)))
+        return dict(build_ms=out[0], nodes=int(out[1]), node_bytes=int(out[2]), tri_bytes=int(out[3]),
+                    sah_cost=out[4], leaves=int(out[5]), depth=int(out[6]))
+
+    # --- ray queries -------------------------------------------------------------------------
+    @staticmethod
+    def _rays(rays):
+        r = np.ascontiguousarray(rays)
+        if r.dtype != ray_dtype:
+            r = np.ascontiguousarray(r, dtype=np.float32).reshape(-1, 8).view(ray_dtype).reshape(-1)
+        return r
+
+    def ray_intersect(self, rays, out=None):
+        """Closest hit of each ray; returns a hit_dtype array (host buffers in, host buffers out)."""
+        r = self._rays(rays)
+        if out is None:
+            out = np.empty(r.shape[0], hit_dtype)
+        _check(lib().mtsb_trace_closest(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def ray_intersect_any(self, rays, out=None):
+        r = self._rays(rays)
+        if out is None:
+            out = np.empty(r.shape[0], np.uint8)
+        _check(lib().mtsb_trace_any(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def ray_intersect_surface(self, rays):
+        r = self._rays(rays)
+        out = np.empty(r.shape[0], surface_dtype)
+        _check(lib().mtsb_trace_surface(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def trace_device(self, mode, d_rays, n, d_out):
+        """Asynchronous query on device pointers (ints); mode in {'closest','any','surface'}."""
+        fn = {"closest": lib().mtsb_trace_closest, "any": lib().mtsb_trace_any, "surface": lib().mtsb_trace_surface}[mode]
+        _check(fn(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_out), 1))
+
+    def trace_count(self, rays, any_hit=False):
+        r = self._rays(rays)
+        out = np.zeros(4, np.uint64)
+        _check(lib().mtsb_trace_count(self.h, _ptr(r), r.shape[0], int(any_hit), 0, _ptr(out)))
+        return dict(nodes=int(out[0]), prims=int(out[1]), rays=int(out[2]))
+
+    def trace_count_device(self, d_rays, n, any_hit=False):
+        out = np.zeros(4, np.uint64)
+        _check(lib().mtsb_trace_count(self.h, C.c_void_p(d_rays), n, int(any_hit), 1, _ptr(out)))
+        return dict(nodes=int(out[0]), prims=int(out[1]), rays=int(out[2]))
+
+    # --- pointwise plugin math ------------------------------------------------------------------
+    def eval_bsdf(self, bsdf, wi, wo, samples):
+        n = len(wi)
+        inp = np.zeros((n, 8), np.float32)
+        inp[:, 0:3] = wi
+        inp[:, 3:6] = wo
+        inp[:, 6:8] = samples
+        out = np.zeros((n, 16), np.float32)
+        _check(lib().mtsb_eval_bsdf(self.h, bsdf, _ptr(inp), n, _ptr(out)))
+        return out
+
+    def eval_emitter(self, p, n_ref, samples):
+        n = len(p)
+        inp = np.zeros((n, 8), np.float32)
+        inp[:, 0:3] = p
+        inp[:, 3:6] = n_ref
+        inp[:, 6:8] = samples
+        out = np.zeros((n, 12), np.float32)
+        _check(lib().mtsb_eval_emitter(self.h, _ptr(inp), n, _ptr(out)))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().mtsb_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class Render:
+    """Wavefront renderer state (mtsb_render): device film in ImageBlock layout + path queues."""
+
+    def __init__(self, scene, camera, film, integrator, seed=0):
+        self.scene = scene
+        self.film = film
+        self.h = C.c_void_p()
+        _check(lib().mtsb_render_create(scene.h, C.byref(camera), C.byref(film), C.byref(integrator), seed, C.byref(self.h)))
+
+    def set_camera(self, camera):
+        _check(lib().mtsb_render_set_camera(self.h, C.byref(camera)))
+
+    def clear(self):
+        _check(lib().mtsb_render_clear(self.h))
+
+    def render_pass(self, spp_begin, spp_count, spp_total, rect=None, stride=1, phase=0):
+        r = None if rect is None else np.ascontiguousarray(rect, dtype=np.int32)
+        _check(lib().mtsb_render_pass(self.h, spp_begin, spp_count, spp_total, _ptr(r), stride, phase))
+
+    def sync(self):
+        _check(lib().mtsb_render_sync(self.h))
+
+    def film_shape(self):
+        f = self.film
+        return (f.height + 2 * f.border, f.width + 2 * f.border, f.channels)
+
+    def film_device_ptr(self):
+        p = C.c_void_p()
+        n = C.c_size_t()
+        _check(lib().mtsb_film_device_ptr(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def film_to_host(self, out=None, accumulate=False):
+        if out is None:
+            out = np.zeros(self.film_shape(), np.float32)
+        _check(lib().mtsb_film_to_host(self.h, _ptr(out), out.size, int(accumulate)))
+        return out
+
+    def stats(self):
+        out = np.zeros(8, np.uint64)
+        _check(lib().mtsb_render_stats(self.h, _ptr(out)))
+        return dict(paths=int(out[0]), closest_rays=int(out[1]), shadow_rays=int(out[2]), depth_sum=int(out[3]),
+                    launches=int(out[4]))
+
+    def render_samples(self, samples, spp_total):
+        s = np.ascontiguousarray(samples, dtype=np.uint32).reshape(-1, 4)
+        out = np.zeros((s.shape[0], 4), np.float32)
+        _check(lib().mtsb_render_samples(self.h, _ptr(s), s.shape[0], spp_total, _ptr(out)))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().mtsb_render_destroy(self.h)
+            self.h = C.c_void_p()

@@ -1,0 +1,20 @@
+// bvh.cuh — host interface of the GPU BVH builder (bvh.cu).
+#pragma once
+#include "common.cuh"
+
+namespace mtsb {
+
+struct BvhResult {
+	DevBuf<uint4>  nodes;   // 5 x uint4 per wide node
+	DevBuf<float4> tris;    // 3 x float4 per leaf slot (TriAccel record)
+	uint32_t nodeCount = 0, slotCount = 0, leafCount = 0;
+	int depth = 0;
+	float buildMs = 0, sahCost = 0;
+	float tightMin[3] = {0,0,0}, tightMax[3] = {0,0,0};   // GenericKDTree::m_tightAABB
+};
+
+// Builds the BVH over the primitives described by S (shapes/rects/positions/indices must be valid device
+// pointers; S.nodes/S.tris are filled in by the caller from `out`).
+int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhResult &out);
+
+} // namespace mtsb

@@ -1,0 +1,340 @@
+// scene.cu — context + scene assembly half of the C ABI (include/mtsb200.h).
+//
+// Stands in for ShapeKDTree::addShape/build (src/librender/skdtree.cpp:49-110) and for the emitter
+// distribution Scene::initialize builds (src/librender/scene.cpp:370-389).  Geometry is staged on the host
+// in the order shapes are added (that order defines shape indices and the global primitive index, as
+// m_shapeMap does), uploaded once, and every derived structure is built on the device.
+#include "scene.cuh"
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+
+namespace mtsb {
+
+static thread_local char g_error[1024] = "";
+void set_error(const char *fmt, ...) {
+	va_list ap; va_start(ap, fmt);
+	vsnprintf(g_error, sizeof(g_error), fmt, ap);
+	va_end(ap);
+}
+
+static void invert_affine(const float m[16], float inv[12]) {
+	// inverse of the upper 3x4 affine part (general 3x3 inverse)
+	double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+	double A = e*i - f*h, B = -(d*i - f*g), C = d*h - e*g;
+	double det = a*A + b*B + c*C;
+	double id = 1.0 / det;
+	double r[9] = { A*id, -(b*i - c*h)*id, (b*f - c*e)*id,
+	                B*id, (a*i - c*g)*id, -(a*f - c*d)*id,
+	                C*id, -(a*h - b*g)*id, (a*e - b*d)*id };
+	double tx = m[3], ty = m[7], tz = m[11];
+	for (int k = 0; k < 3; ++k) {
+		inv[k*4+0] = (float) r[k*3+0]; inv[k*4+1] = (float) r[k*3+1]; inv[k*4+2] = (float) r[k*3+2];
+		inv[k*4+3] = (float) -(r[k*3+0]*tx + r[k*3+1]*ty + r[k*3+2]*tz);
+	}
+}
+
+} // namespace mtsb
+
+using namespace mtsb;
+void mtsb_release_pipe(mtsb_scene *scene);   // trace.cu
+
+extern "C" {
+
+int mtsb_abi_version(void) { return MTSB_ABI_VERSION; }
+const char *mtsb_last_error(void) { return mtsb::g_error; }
+
+int mtsb_device_count(void) {
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return n;
+}
+
+int mtsb_ctx_create(int device, mtsb_ctx **out) {
+	if (!out) MTSB_FAIL(MTSB_EINVAL, "mtsb_ctx_create: out is NULL");
+	*out = nullptr;
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+		cudaGetLastError();
+		MTSB_FAIL(MTSB_ENODEVICE, "mtsb_ctx_create: no CUDA device available (this library has no CPU fallback)");
+	}
+	if (device < 0 || device >= n) MTSB_FAIL(MTSB_EINVAL, "mtsb_ctx_create: device %d out of range [0,%d)", device, n);
+	MTSB_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	MTSB_CUDA(cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10)
+		MTSB_FAIL(MTSB_ENODEVICE, "mtsb_ctx_create: device %d is sm_%d%d; this build targets sm_100a (B200) only", device, prop.major, prop.minor);
+	mtsb_ctx *ctx = new mtsb_ctx();
+	ctx->device = device; ctx->smCount = prop.multiProcessorCount;
+	cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+	if (e != cudaSuccess) { delete ctx; MTSB_FAIL(MTSB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+	*out = ctx;
+	return 0;
+}
+
+void mtsb_ctx_destroy(mtsb_ctx *ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+int mtsb_ctx_sync(mtsb_ctx *ctx) {
+	if (!ctx) MTSB_FAIL(MTSB_EINVAL, "mtsb_ctx_sync: NULL context");
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	MTSB_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+void *mtsb_ctx_stream(mtsb_ctx *ctx) { return ctx ? (void *) ctx->stream : nullptr; }
+
+int mtsb_scene_create(mtsb_ctx *ctx, mtsb_scene **out) {
+	if (!ctx || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_create: NULL argument");
+	mtsb_scene *s = new mtsb_scene();
+	s->ctx = ctx;
+	s->shapeOffsets.push_back(0);
+	memset(&s->dev, 0, sizeof(s->dev));
+	*out = s;
+	return 0;
+}
+
+void mtsb_scene_destroy(mtsb_scene *scene) {
+	if (!scene) return;
+	cudaSetDevice(scene->ctx->device);
+	mtsb_release_pipe(scene);
+	delete scene;
+}
+
+int mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc) {
+	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: scene already committed");
+	int base = desc->type & 0xff;
+	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_NULL)
+		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_bsdf: BSDF type %d is outside the GPU subset", desc->type);
+	BsdfRec r; r.type = desc->type; memcpy(r.p, desc->p, sizeof(r.p));
+	scene->bsdfs.push_back(r);
+	return (int) scene->bsdfs.size() - 1;
+}
+
+int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
+	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_emitter: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_emitter: scene already committed");
+	if (desc->type < MTSB_EMITTER_AREA || desc->type > MTSB_EMITTER_CONSTANT)
+		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_emitter: emitter type %d is outside the GPU subset", desc->type);
+	EmitterRec r; memset(&r, 0, sizeof(r));
+	r.type = desc->type; r.shape = desc->shape;
+	r.radiance = v3(desc->radiance[0], desc->radiance[1], desc->radiance[2]);
+	r.pos = v3(desc->pos[0], desc->pos[1], desc->pos[2]);
+	scene->emitters.push_back(r);
+	scene->emitterWeights.push_back(desc->sampling_weight);
+	return (int) scene->emitters.size() - 1;
+}
+
+static int check_refs(mtsb_scene *scene, int bsdf, int emitter, const char *who) {
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "%s: scene already committed", who);
+	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size()) MTSB_FAIL(MTSB_EINVAL, "%s: bsdf id %d unknown", who, bsdf);
+	if (emitter < -1 || emitter >= (int) scene->emitters.size()) MTSB_FAIL(MTSB_EINVAL, "%s: emitter id %d unknown", who, emitter);
+	return 0;
+}
+
+int mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *normals, const float *texcoords,
+		const uint32_t *triangles, size_t vertex_count, size_t triangle_count, int bsdf, int emitter) {
+	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_mesh: NULL scene");
+	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_mesh"));
+	if (triangle_count == 0 || vertex_count == 0 || !positions || !triangles)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_mesh: empty triangle mesh");   // TriMesh::prepareSamplingTable logs the same error
+	if ((uint64_t) scene->primCount + triangle_count > 0x7fffffffull)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_mesh: more than 2^31 primitives");
+	for (size_t i = 0; i < triangle_count * 3; ++i)
+		if (triangles[i] >= vertex_count)
+			MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_mesh: triangle %zu references vertex %u >= %zu", i / 3, triangles[i], vertex_count);
+	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	sh.type = SHAPE_MESH;
+	sh.primOffset = scene->primCount; sh.primCount = (uint32_t) triangle_count;
+	sh.vtxBase = (uint32_t) (scene->positions.size() / 3);
+	sh.triBase = (uint32_t) (scene->indices.size() / 3);
+	sh.flags = (normals ? SHAPE_HAS_NORMALS : 0) | (texcoords ? SHAPE_HAS_UV : 0);
+	sh.bsdf = bsdf; sh.emitter = emitter;
+	scene->positions.insert(scene->positions.end(), positions, positions + vertex_count * 3);
+	if (normals) scene->normals.insert(scene->normals.end(), normals, normals + vertex_count * 3);
+	else scene->normals.resize(scene->normals.size() + vertex_count * 3, 0.0f);
+	if (texcoords) scene->texcoords.insert(scene->texcoords.end(), texcoords, texcoords + vertex_count * 2);
+	else scene->texcoords.resize(scene->texcoords.size() + vertex_count * 2, 0.0f);
+	scene->indices.insert(scene->indices.end(), triangles, triangles + triangle_count * 3);
+	scene->shapes.push_back(sh);
+	scene->primCount += (uint32_t) triangle_count;
+	scene->shapeOffsets.push_back(scene->primCount);
+	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
+	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_normals, int bsdf, int emitter) {
+	if (!scene || !m) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_rectangle: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_rectangle"));
+	float ow[16]; memcpy(ow, m, sizeof(ow));
+	if (flip_normals)   // m_objectToWorld * scale(1,1,-1)  (rectangle.cpp:81-83)
+		for (int r = 0; r < 4; ++r) ow[r*4+2] = -ow[r*4+2];
+	RectRec rr; memset(&rr, 0, sizeof(rr));
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) rr.toWorld[r*4+c] = ow[r*4+c];
+	invert_affine(ow, rr.toObject);
+	// configure(): dpdu = toWorld(Vector(2,0,0)), dpdv = toWorld(Vector(0,2,0)), n = normalize(toWorld(Normal(0,0,1)))
+	rr.dpdu = v3(2*ow[0], 2*ow[4], 2*ow[8]);
+	rr.dpdv = v3(2*ow[1], 2*ow[5], 2*ow[9]);
+	// normals transform with the inverse transpose: n_i = sum_j inv[j][i] * (0,0,1)_j = inv[2][i]
+	V3 n = v3(rr.toObject[8], rr.toObject[9], rr.toObject[10]);
+	float len = sqrtf(n.x*n.x + n.y*n.y + n.z*n.z);
+	rr.n = v3(n.x/len, n.y/len, n.z/len);
+	float lu = sqrtf(dot(rr.dpdu, rr.dpdu)), lv = sqrtf(dot(rr.dpdv, rr.dpdv));
+	if (fabsf(dot(rr.dpdu, rr.dpdv) / (lu * lv)) > MTS_EPSILON)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_rectangle: 'toWorld' transformation contains shear!");   // rectangle.cpp:106-107
+	rr.invSurfaceArea = 1.0f / (lu * lv);
+	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	sh.type = SHAPE_RECT; sh.primOffset = scene->primCount; sh.primCount = 1;
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.invArea = rr.invSurfaceArea;
+	scene->rects.push_back(rr);
+	scene->shapes.push_back(sh);
+	scene->primCount += 1;
+	scene->shapeOffsets.push_back(scene->primCount);
+	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
+	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_commit(mtsb_scene *scene, int builder) {
+	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: NULL scene");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: already committed");
+	if (scene->primCount == 0) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: scene has no primitives");
+	if (builder != MTSB_BUILDER_LBVH && builder != MTSB_BUILDER_PLOC) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: unknown builder %d", builder);
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t st = ctx->stream;
+
+	// area-light tables: TriMesh::prepareSamplingTable (src/librender/trimesh.cpp:389-404) in float, like the reference
+	std::vector<float> triAreaCdf;
+	std::vector<uint32_t> triAreaCdfOffset(scene->shapes.size(), 0xffffffffu);
+	for (size_t s = 0; s < scene->shapes.size(); ++s) {
+		ShapeRec &sh = scene->shapes[s];
+		if (sh.type != SHAPE_MESH) continue;
+		const bool needTable = sh.emitter >= 0;
+		if (!needTable) continue;
+		triAreaCdfOffset[s] = (uint32_t) triAreaCdf.size();
+		size_t base = triAreaCdf.size();
+		triAreaCdf.push_back(0.0f);
+		for (uint32_t t = 0; t < sh.primCount; ++t) {
+			const uint32_t *ix = &scene->indices[(size_t) (sh.triBase + t) * 3];
+			const float *p0 = &scene->positions[(size_t) (sh.vtxBase + ix[0]) * 3];
+			const float *p1 = &scene->positions[(size_t) (sh.vtxBase + ix[1]) * 3];
+			const float *p2 = &scene->positions[(size_t) (sh.vtxBase + ix[2]) * 3];
+			V3 a = v3(p1[0]-p0[0], p1[1]-p0[1], p1[2]-p0[2]), b = v3(p2[0]-p0[0], p2[1]-p0[1], p2[2]-p0[2]);
+			V3 c = cross(a, b);
+			float area = 0.5f * sqrtf(dot(c, c));
+			triAreaCdf.push_back(triAreaCdf.back() + area);
+		}
+		float sum = triAreaCdf.back();
+		if (sum > 0) {
+			float norm = 1.0f / sum;
+			for (size_t i = base + 1; i < triAreaCdf.size(); ++i) triAreaCdf[i] *= norm;
+			triAreaCdf.back() = 1.0f;
+			sh.invArea = 1.0f / sum;
+		}
+	}
+
+	// emitter selection distribution (DiscreteDistribution, include/mitsuba/core/pmf.h)
+	std::vector<float> emitterCdf(1, 0.0f);
+	for (size_t i = 0; i < scene->emitters.size(); ++i) emitterCdf.push_back(emitterCdf.back() + scene->emitterWeights[i]);
+	float emitterNorm = 0;
+	if (emitterCdf.back() > 0) {
+		emitterNorm = 1.0f / emitterCdf.back();
+		for (size_t i = 1; i < emitterCdf.size(); ++i) emitterCdf[i] *= emitterNorm;
+		emitterCdf.back() = 1.0f;
+	}
+	int envEmitter = -1;
+	for (size_t i = 0; i < scene->emitters.size(); ++i) {
+		EmitterRec &e = scene->emitters[i];
+		if (e.type == MTSB_EMITTER_CONSTANT) envEmitter = (int) i;
+		if (e.type == MTSB_EMITTER_AREA) {
+			if (e.shape >= scene->shapes.size() || scene->shapes[e.shape].emitter != (int) i)
+				MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: area emitter %zu is not attached to a shape", i);
+			e.invSurfaceArea = scene->shapes[e.shape].invArea;
+		}
+	}
+
+	MTSB_CHECK(scene->dShapes.upload(scene->shapes, st));
+	MTSB_CHECK(scene->dRects.upload(scene->rects, st));
+	MTSB_CHECK(scene->dBsdfs.upload(scene->bsdfs, st));
+	MTSB_CHECK(scene->dPositions.upload(scene->positions, st));
+	MTSB_CHECK(scene->dNormals.upload(scene->normals, st));
+	MTSB_CHECK(scene->dTexcoords.upload(scene->texcoords, st));
+	MTSB_CHECK(scene->dIndices.upload(scene->indices, st));
+	MTSB_CHECK(scene->dEmitterCdf.upload(emitterCdf, st));
+	MTSB_CHECK(scene->dTriAreaCdf.upload(triAreaCdf, st));
+	MTSB_CHECK(scene->dTriAreaCdfOffset.upload(triAreaCdfOffset, st));
+	MTSB_CHECK(scene->dCounters.alloc(4));
+	MTSB_CUDA(cudaMemsetAsync(scene->dCounters.ptr, 0, 4 * sizeof(unsigned long long), st));
+
+	SceneDev &D = scene->dev;
+	memset(&D, 0, sizeof(D));
+	D.shapes = scene->dShapes.ptr; D.rects = scene->dRects.ptr; D.bsdfs = scene->dBsdfs.ptr;
+	D.positions = scene->dPositions.ptr; D.normals = scene->dNormals.ptr; D.texcoords = scene->dTexcoords.ptr;
+	D.indices = scene->dIndices.ptr;
+	D.emitterCdf = scene->dEmitterCdf.ptr; D.triAreaCdf = scene->dTriAreaCdf.ptr; D.triAreaCdfOffset = scene->dTriAreaCdfOffset.ptr;
+	D.shapeCount = (uint32_t) scene->shapes.size(); D.emitterCount = (uint32_t) scene->emitters.size();
+	D.envEmitter = envEmitter; D.emitterNorm = emitterNorm;
+	D.counters = nullptr;
+
+	MTSB_CHECK(build_bvh(ctx, D, scene->primCount, builder, scene->bvh));
+	D.nodes = scene->bvh.nodes.ptr; D.tris = scene->bvh.tris.ptr;
+	D.nodeCount = scene->bvh.nodeCount; D.slotCount = scene->bvh.slotCount;
+
+	// "Slightly enlarge the bounding box" — include/mitsuba/render/gkdtree.h:1213-1220 (max uses the already moved min)
+	for (int a = 0; a < 3; ++a) {
+		float mn = scene->bvh.tightMin[a], mx = scene->bvh.tightMax[a];
+		const float eps = MTS_KD_AABB_EPS;
+		mn -= (mx - mn) * eps + eps;
+		mx += (mx - mn) * eps + eps;
+		scene->aabbMin[a] = mn; scene->aabbMax[a] = mx;
+	}
+	D.aabbMin = v3(scene->aabbMin[0], scene->aabbMin[1], scene->aabbMin[2]);
+	D.aabbMax = v3(scene->aabbMax[0], scene->aabbMax[1], scene->aabbMax[2]);
+
+	// constant environment: bounding sphere of the (kd-tree) AABB, radius x1.5 (src/emitters/constant.cpp:69-80;
+	// AABB::getBSphere = centre + distance to max corner)
+	for (size_t i = 0; i < scene->emitters.size(); ++i) {
+		EmitterRec &e = scene->emitters[i];
+		if (e.type != MTSB_EMITTER_CONSTANT) continue;
+		V3 c = 0.5f * (D.aabbMin + D.aabbMax);
+		V3 h = D.aabbMax - c;
+		e.sphereCenter = c;
+		e.sphereRadius = fmaxf(MTS_EPSILON, sqrtf(dot(h, h)) * 1.5f);
+	}
+	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
+	D.emitters = scene->dEmitters.ptr;
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	scene->committed = true;
+	return 0;
+}
+
+int mtsb_scene_aabb(const mtsb_scene *scene, float mn[3], float mx[3]) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_aabb: scene not committed");
+	for (int a = 0; a < 3; ++a) { mn[a] = scene->aabbMin[a]; mx[a] = scene->aabbMax[a]; }
+	return 0;
+}
+
+size_t mtsb_scene_primitive_count(const mtsb_scene *scene) { return scene ? scene->primCount : 0; }
+size_t mtsb_scene_shape_count(const mtsb_scene *scene) { return scene ? scene->shapes.size() : 0; }
+
+int mtsb_scene_shape_offsets(const mtsb_scene *scene, uint32_t *out) {
+	if (!scene || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_shape_offsets: NULL argument");
+	memcpy(out, scene->shapeOffsets.data(), scene->shapeOffsets.size() * sizeof(uint32_t));
+	return 0;
+}
+
+int mtsb_scene_build_stats(const mtsb_scene *scene, double out[8]) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_build_stats: scene not committed");
+	out[0] = scene->bvh.buildMs; out[1] = scene->bvh.nodeCount; out[2] = (double) scene->bvh.nodes.bytes();
+	out[3] = (double) scene->bvh.tris.bytes(); out[4] = scene->bvh.sahCost; out[5] = scene->bvh.leafCount;
+	out[6] = scene->bvh.depth; out[7] = 0;
+	return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,238 @@
+// trace.cu — batched ray queries of the C ABI: mtsb_trace_closest / mtsb_trace_any / mtsb_trace_surface.
+//
+// Batched equivalents of the three ShapeKDTree::rayIntersect overloads (src/librender/skdtree.cpp:112-226).
+// Kernels are persistent: one grid sized to the SM count, each warp pulls batches of 32 rays from a global
+// counter (one atomic per warp, broadcast by shuffle), rays and hits move as 16-byte vectors.
+// Host-pointer calls are pipelined in chunks over three streams so that PCIe traffic overlaps traversal.
+#include "scene.cuh"
+#include "trace.cuh"
+#include "surface.cuh"
+#include <algorithm>
+
+namespace mtsb {
+
+enum { MODE_CLOSEST = 0, MODE_ANY = 1, MODE_SURFACE = 2 };
+
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, void *__restrict__ out,
+		unsigned long long *__restrict__ workCounter) {
+	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
+	const unsigned lane = threadIdx.x & 31;
+	while (true) {
+		unsigned long long base = 0;
+		if (lane == 0) base = atomicAdd(workCounter, 32ull);
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if (base >= n) break;
+		const unsigned long long i = base + lane;
+		if (i < n) {
+			const float4 r0 = __ldg(rays + 2 * i), r1 = __ldg(rays + 2 * i + 1);
+			const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
+			float mint, maxt;
+			HitRec hit; hit.t = INFINITY; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
+			bool found = false;
+			if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, mint, maxt))
+				found = traverse<MODE == MODE_ANY, COUNT>(S, o, d, mint, maxt, hit, shStack + threadIdx.x, S.counters);
+			if (MODE == MODE_ANY) {
+				((uint8_t *) out)[i] = found ? 1 : 0;
+			} else if (MODE == MODE_CLOSEST) {
+				uint32_t prim = MTSB_NO_HIT;
+				if (found) {
+					const float4 c = __ldg(S.tris + (size_t) hit.slot * 3 + 2);
+					prim = S.shapes[__float_as_uint(c.z)].primOffset + __float_as_uint(c.w);
+				} else { hit.t = INFINITY; hit.u = hit.v = 0; }
+				((float4 *) out)[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim));
+			} else {
+				mtsb_surface rec;
+				memset(&rec, 0, sizeof(rec));
+				rec.t = INFINITY; rec.prim = MTSB_NO_HIT; rec.shape = MTSB_NO_HIT;
+				if (found) {
+					Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
+					rec.t = hit.t; rec.u = hit.u; rec.v = hit.v;
+					rec.shape = sf.shape; rec.prim_local = sf.prim; rec.prim = S.shapes[sf.shape].primOffset + sf.prim;
+					rec.p[0] = sf.p.x; rec.p[1] = sf.p.y; rec.p[2] = sf.p.z;
+					rec.ng[0] = sf.ng.x; rec.ng[1] = sf.ng.y; rec.ng[2] = sf.ng.z;
+					rec.ns[0] = sf.ns.x; rec.ns[1] = sf.ns.y; rec.ns[2] = sf.ns.z;
+					rec.s[0] = sf.s.x; rec.s[1] = sf.s.y; rec.s[2] = sf.s.z;
+					rec.tt[0] = sf.t.x; rec.tt[1] = sf.t.y; rec.tt[2] = sf.t.z;
+					rec.uv[0] = sf.u; rec.uv[1] = sf.v;
+				}
+				((mtsb_surface *) out)[i] = rec;
+			}
+		}
+	}
+	if (COUNT && threadIdx.x == 0 && blockIdx.x == 0 && S.counters) atomicAdd(S.counters + 2, n);
+}
+
+static size_t out_stride(int mode) {
+	return mode == MODE_ANY ? 1 : (mode == MODE_CLOSEST ? sizeof(mtsb_hit) : sizeof(mtsb_surface));
+}
+
+// launches one persistent grid over n rays that already live on the device
+int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, void *dOut, unsigned long long *dWork,
+		cudaStream_t st, bool count) {
+	if (n == 0) return 0;
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaMemsetAsync(dWork, 0, sizeof(unsigned long long), st));
+	const int blocksPerSm = 8;
+	unsigned grid = (unsigned) std::min<size_t>((size_t) ctx->smCount * blocksPerSm, (n + MTSB_TRACE_BLOCK - 1) / MTSB_TRACE_BLOCK);
+	SceneDev S = scene->dev;
+	S.counters = count ? scene->dCounters.ptr : nullptr;
+	const float4 *r = (const float4 *) dRays;
+	#define LAUNCH(M) do { if (count) trace_kernel<M, true><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, n, dOut, dWork); \
+		else trace_kernel<M, false><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, n, dOut, dWork); } while (0)
+	if (mode == MODE_CLOSEST) LAUNCH(MODE_CLOSEST);
+	else if (mode == MODE_ANY) LAUNCH(MODE_ANY);
+	else LAUNCH(MODE_SURFACE);
+	#undef LAUNCH
+	MTSB_CUDA(cudaGetLastError());
+	return 0;
+}
+
+struct TracePipe {
+	// double-buffered device staging + streams for host-pointer calls
+	cudaStream_t sIn = nullptr, sOut = nullptr;
+	cudaEvent_t inDone[2] = { nullptr, nullptr }, kDone[2] = { nullptr, nullptr }, outDone[2] = { nullptr, nullptr };
+	DevBuf<mtsb_ray> rays[2];
+	DevBuf<uint8_t> out[2];
+	DevBuf<unsigned long long> work;
+	size_t chunk = 0, outBytes = 0;
+	bool ready = false;
+};
+
+} // namespace mtsb
+
+using namespace mtsb;
+
+// one pipe per scene, created lazily (kept in a side table to keep scene.cuh free of it)
+#include <map>
+#include <mutex>
+static std::mutex g_pipeMutex;
+static std::map<mtsb_scene *, TracePipe *> g_pipes;
+
+static int get_pipe(mtsb_scene *scene, size_t chunk, size_t outBytesPerRay, TracePipe **outPipe) {
+	std::lock_guard<std::mutex> lock(g_pipeMutex);
+	TracePipe *&p = g_pipes[scene];
+	if (!p) p = new TracePipe();
+	if (!p->ready) {
+		MTSB_CUDA(cudaStreamCreateWithFlags(&p->sIn, cudaStreamNonBlocking));
+		MTSB_CUDA(cudaStreamCreateWithFlags(&p->sOut, cudaStreamNonBlocking));
+		for (int i = 0; i < 2; ++i) {
+			MTSB_CUDA(cudaEventCreateWithFlags(&p->inDone[i], cudaEventDisableTiming));
+			MTSB_CUDA(cudaEventCreateWithFlags(&p->kDone[i], cudaEventDisableTiming));
+			MTSB_CUDA(cudaEventCreateWithFlags(&p->outDone[i], cudaEventDisableTiming));
+		}
+		MTSB_CHECK(p->work.alloc(4));
+		p->ready = true;
+	}
+	if (p->chunk < chunk) {
+		for (int i = 0; i < 2; ++i) MTSB_CHECK(p->rays[i].alloc(chunk));
+		p->chunk = chunk;
+	}
+	if (p->outBytes < chunk * outBytesPerRay) {
+		for (int i = 0; i < 2; ++i) MTSB_CHECK(p->out[i].alloc(chunk * outBytesPerRay));
+		p->outBytes = chunk * outBytesPerRay;
+	}
+	*outPipe = p;
+	return 0;
+}
+
+void mtsb_release_pipe(mtsb_scene *scene) {
+	std::lock_guard<std::mutex> lock(g_pipeMutex);
+	auto it = g_pipes.find(scene);
+	if (it == g_pipes.end()) return;
+	TracePipe *p = it->second;
+	if (p->ready) {
+		cudaStreamDestroy(p->sIn); cudaStreamDestroy(p->sOut);
+		for (int i = 0; i < 2; ++i) { cudaEventDestroy(p->inDone[i]); cudaEventDestroy(p->kDone[i]); cudaEventDestroy(p->outDone[i]); }
+	}
+	delete p;
+	g_pipes.erase(it);
+}
+
+static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_t n, void *out, int onDevice, const char *who) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "%s: scene not committed", who);
+	if (n == 0) return 0;
+	if (!rays || !out) MTSB_FAIL(MTSB_EINVAL, "%s: NULL buffer", who);
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	const size_t ob = out_stride(mode);
+	TracePipe *p = nullptr;
+	if (onDevice) {
+		MTSB_CHECK(get_pipe(scene, 1, ob, &p));
+		return launch_trace(scene, mode, rays, n, out, p->work.ptr, ctx->stream, false);
+	}
+	// host path: chunks of up to 2M rays, H2D on sIn, kernel on ctx->stream, D2H on sOut
+	const size_t chunk = std::min<size_t>(n, (size_t) 1 << 21);
+	MTSB_CHECK(get_pipe(scene, chunk, ob, &p));
+	const size_t nChunks = (n + chunk - 1) / chunk;
+	for (size_t c = 0; c < nChunks; ++c) {
+		const int b = (int) (c & 1);
+		const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+		// buffer b is free once the D2H of chunk c-2 is done
+		if (c >= 2) MTSB_CUDA(cudaStreamWaitEvent(p->sIn, p->outDone[b], 0));
+		MTSB_CUDA(cudaMemcpyAsync(p->rays[b].ptr, rays + off, cnt * sizeof(mtsb_ray), cudaMemcpyHostToDevice, p->sIn));
+		MTSB_CUDA(cudaEventRecord(p->inDone[b], p->sIn));
+		MTSB_CUDA(cudaStreamWaitEvent(ctx->stream, p->inDone[b], 0));
+		if (c >= 2) MTSB_CUDA(cudaStreamWaitEvent(ctx->stream, p->outDone[b], 0));
+		MTSB_CHECK(launch_trace(scene, mode, p->rays[b].ptr, cnt, p->out[b].ptr, p->work.ptr + b, ctx->stream, false));
+		MTSB_CUDA(cudaEventRecord(p->kDone[b], ctx->stream));
+		MTSB_CUDA(cudaStreamWaitEvent(p->sOut, p->kDone[b], 0));
+		MTSB_CUDA(cudaMemcpyAsync((uint8_t *) out + off * ob, p->out[b].ptr, cnt * ob, cudaMemcpyDeviceToHost, p->sOut));
+		MTSB_CUDA(cudaEventRecord(p->outDone[b], p->sOut));
+	}
+	MTSB_CUDA(cudaStreamSynchronize(p->sOut));
+	MTSB_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+extern "C" {
+
+int mtsb_trace_closest(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device) {
+	return trace_common(scene, MODE_CLOSEST, rays, n, hits, on_device, "mtsb_trace_closest");
+}
+int mtsb_trace_any(mtsb_scene *scene, const mtsb_ray *rays, size_t n, uint8_t *out, int on_device) {
+	return trace_common(scene, MODE_ANY, rays, n, out, on_device, "mtsb_trace_any");
+}
+int mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_surface *out, int on_device) {
+	return trace_common(scene, MODE_SURFACE, rays, n, out, on_device, "mtsb_trace_surface");
+}
+
+// counting variant: re-traces a device or host batch with node / primitive-test counters enabled
+int mtsb_trace_count(mtsb_scene *scene, const mtsb_ray *rays, size_t n, int any_hit, int on_device, uint64_t out[4]) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_count: scene not committed");
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t st = ctx->stream;
+	DevBuf<mtsb_ray> dRays; DevBuf<uint8_t> dOut; DevBuf<unsigned long long> work;
+	const int mode = any_hit ? MODE_ANY : MODE_CLOSEST;
+	MTSB_CHECK(dOut.alloc(n * out_stride(mode))); MTSB_CHECK(work.alloc(1));
+	const mtsb_ray *src = rays;
+	if (!on_device) { MTSB_CHECK(dRays.upload(rays, n, st)); src = dRays.ptr; }
+	MTSB_CUDA(cudaMemsetAsync(scene->dCounters.ptr, 0, 4 * sizeof(unsigned long long), st));
+	MTSB_CHECK(launch_trace(scene, mode, src, n, dOut.ptr, work.ptr, st, true));
+	unsigned long long h[4];
+	MTSB_CUDA(cudaMemcpyAsync(h, scene->dCounters.ptr, sizeof(h), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	for (int i = 0; i < 4; ++i) out[i] = h[i];
+	return 0;
+}
+
+int mtsb_trace_counters(mtsb_scene *scene, uint64_t out[4]) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_counters: scene not committed");
+	unsigned long long h[4];
+	MTSB_CUDA(cudaSetDevice(scene->ctx->device));
+	MTSB_CUDA(cudaMemcpy(h, scene->dCounters.ptr, sizeof(h), cudaMemcpyDeviceToHost));
+	for (int i = 0; i < 4; ++i) out[i] = h[i];
+	return 0;
+}
+
+// pinned host memory for callers that want the pipelined copies to run at PCIe speed
+void *mtsb_host_alloc(size_t bytes) {
+	void *p = nullptr;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); mtsb::set_error("cudaHostAlloc(%zu) failed", bytes); return nullptr; }
+	return p;
+}
+void mtsb_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+} // extern "C"

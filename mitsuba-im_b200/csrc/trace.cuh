@@ -1,0 +1,229 @@
+// trace.cuh — device-side BVH8 traversal + primitive tests (closest hit and any hit).
+//
+// Replaces SAHKDTree3D::rayIntersectHavran<shadowRay> (include/mitsuba/render/sahkdtree3.h:178-308) and
+// TriAccel::rayIntersect (include/mitsuba/render/triaccel.h:96-158).  The acceleration structure is a
+// GPU-built 8-wide BVH with quantised child boxes (80-byte nodes read as five 16-byte vector loads);
+// the primitive test is the reference's own Wald projection test on 48-byte records so that accepted
+// hits, t and barycentrics agree with the CPU path to rounding.
+//
+// Node layout (5 x uint4):
+//   n0 = { p.x, p.y, p.z (float bits), ex | ey<<8 | ez<<16 | imask<<24 }     quantisation frame + internal mask
+//   n1 = { childBase, triBase, meta[0..3], meta[4..7] }
+//   n2 = { qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7] }
+//   n3 = { qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7] }
+//   n4 = { qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7] }
+// meta[i]: 0 = empty; internal child = (1<<5) | (24 + slot); leaf = (unary triangle count << 5) | triangle
+// offset (0..23).  Children sit in octant-ordered slots (slot bit set = child lies towards +axis), so the
+// traversal order for a ray is "slot XOR (7 - octant)", highest first — no per-node distance sort.
+#pragma once
+#include "common.cuh"
+
+namespace mtsb {
+
+#define MTSB_STACK_SHARED 8      // stack entries per thread kept in shared memory
+#define MTSB_STACK_LOCAL  56     // overflow entries in local memory
+#define MTSB_TRACE_BLOCK  128    // threads per block of every traversal kernel
+
+struct HitRec { float t, u, v; uint32_t slot; };
+
+__device__ __forceinline__ float byte_to_float(uint32_t word, int j) {
+	// PRMT picks byte j into the low byte of 0x4B000000 -> 2^23 + byte, exact subtraction afterwards
+	return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | (uint32_t) j)) - 8388608.0f;
+}
+
+// Reference Wald test, evaluated without FMA contraction in source order (triaccel.h:96-158).
+__device__ __forceinline__ bool tri_test(const float4 a, const float4 b, const float4 c,
+		const V3 &o, const V3 &d, float mint, float maxt, float &t, float &u, float &v) {
+	uint32_t k = __float_as_uint(a.x);
+	float o_u, o_v, o_k, d_u, d_v, d_k;
+	if (k == 0)      { o_u = o.y; o_v = o.z; o_k = o.x; d_u = d.y; d_v = d.z; d_k = d.x; }
+	else if (k == 1) { o_u = o.z; o_v = o.x; o_k = o.y; d_u = d.z; d_v = d.x; d_k = d.y; }
+	else if (k == 2) { o_u = o.x; o_v = o.y; o_k = o.z; d_u = d.x; d_v = d.y; d_k = d.z; }
+	else return false;
+	const float n_u = a.y, n_v = a.z, n_d = a.w;
+	float num = __fsub_rn(__fsub_rn(__fsub_rn(n_d, __fmul_rn(o_u, n_u)), __fmul_rn(o_v, n_v)), o_k);
+	float den = __fadd_rn(__fadd_rn(__fmul_rn(d_u, n_u), __fmul_rn(d_v, n_v)), d_k);
+	t = __fdiv_rn(num, den);
+	if (t < mint || t > maxt) return false;   // NaN passes, exactly as on the CPU; u/v test below rejects it
+	const float hu = __fsub_rn(__fadd_rn(o_u, __fmul_rn(t, d_u)), b.x);
+	const float hv = __fsub_rn(__fadd_rn(o_v, __fmul_rn(t, d_v)), b.y);
+	u = __fadd_rn(__fmul_rn(hv, b.z), __fmul_rn(hu, b.w));
+	v = __fadd_rn(__fmul_rn(hu, c.x), __fmul_rn(hv, c.y));
+	return u >= 0 && v >= 0 && __fadd_rn(u, v) <= 1.0f;
+}
+
+// Rectangle::rayIntersect (src/shapes/rectangle.cpp:125-147): object-space plane z=0, |x|,|y| <= 1.
+__device__ __forceinline__ bool rect_test(const RectRec &r, const V3 &o, const V3 &d,
+		float mint, float maxt, float &t, float &u, float &v) {
+	const float *m = r.toObject;
+	float ox = m[0]*o.x + m[1]*o.y + m[2]*o.z + m[3];
+	float oy = m[4]*o.x + m[5]*o.y + m[6]*o.z + m[7];
+	float oz = m[8]*o.x + m[9]*o.y + m[10]*o.z + m[11];
+	float dx = m[0]*d.x + m[1]*d.y + m[2]*d.z;
+	float dy = m[4]*d.x + m[5]*d.y + m[6]*d.z;
+	float dz = m[8]*d.x + m[9]*d.y + m[10]*d.z;
+	float hit = -oz / dz;
+	if (!(hit >= mint && hit <= maxt)) return false;
+	float lx = ox + dx * hit, ly = oy + dy * hit;
+	if (fabsf(lx) <= 1 && fabsf(ly) <= 1) { t = hit; u = lx; v = ly; return true; }
+	return false;
+}
+
+// Tests the 8 quantised child boxes of a node; returns the hit mask (bits 24..31 internal children in
+// traversal priority order, bits 0..23 triangles).
+__device__ __forceinline__ uint32_t node_test(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
+		const uint4 n4, const V3 &o, const V3 &idir, uint32_t octinv4, float tmin, float tmax) {
+	const uint32_t e = n0.w;
+	const float sx = __uint_as_float((e & 0xffu) << 23) * idir.x;
+	const float sy = __uint_as_float(((e >> 8) & 0xffu) << 23) * idir.y;
+	const float sz = __uint_as_float(((e >> 16) & 0xffu) << 23) * idir.z;
+	const float bx = (__uint_as_float(n0.x) - o.x) * idir.x;
+	const float by = (__uint_as_float(n0.y) - o.y) * idir.y;
+	const float bz = (__uint_as_float(n0.z) - o.z) * idir.z;
+	uint32_t hitmask = 0;
+	#pragma unroll
+	for (int g = 0; g < 2; ++g) {
+		const uint32_t meta4 = g ? n1.w : n1.z;
+		const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+		const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
+		const uint32_t bitIndex4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1f1f1f1fu;
+		const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+		const uint32_t qlox = g ? n2.y : n2.x, qloy = g ? n2.w : n2.z, qloz = g ? n3.y : n3.x;
+		const uint32_t qhix = g ? n3.w : n3.z, qhiy = g ? n4.y : n4.x, qhiz = g ? n4.w : n4.z;
+		const uint32_t xn = idir.x < 0 ? qhix : qlox, xf = idir.x < 0 ? qlox : qhix;
+		const uint32_t yn = idir.y < 0 ? qhiy : qloy, yf = idir.y < 0 ? qloy : qhiy;
+		const uint32_t zn = idir.z < 0 ? qhiz : qloz, zf = idir.z < 0 ? qloz : qhiz;
+		#pragma unroll
+		for (int j = 0; j < 4; ++j) {
+			const float tnx = fmaf(byte_to_float(xn, j), sx, bx), tfx = fmaf(byte_to_float(xf, j), sx, bx);
+			const float tny = fmaf(byte_to_float(yn, j), sy, by), tfy = fmaf(byte_to_float(yf, j), sy, by);
+			const float tnz = fmaf(byte_to_float(zn, j), sz, bz), tfz = fmaf(byte_to_float(zf, j), sz, bz);
+			const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+			const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax)) * 1.0000005f;  // conservative (Ize 2013)
+			if (cmin <= cmax) {
+				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu;
+				const uint32_t idx = (bitIndex4 >> (8 * j)) & 0xffu;
+				hitmask |= bits << idx;
+			}
+		}
+	}
+	return hitmask;
+}
+
+// Per-thread traversal stack: first MTSB_STACK_SHARED entries in shared memory (interleaved by thread),
+// the rest in local memory.
+struct TravStack {
+	uint2 *sh;            // &shared[threadIdx.x], stride blockDim.x
+	uint2 loc[MTSB_STACK_LOCAL];
+	int n;
+	__device__ __forceinline__ void push(uint2 v) {
+		if (n < MTSB_STACK_SHARED) sh[n * MTSB_TRACE_BLOCK] = v;
+		else if (n < MTSB_STACK_SHARED + MTSB_STACK_LOCAL) loc[n - MTSB_STACK_SHARED] = v;
+		else return;  // cannot happen for trees built by bvh.cu (depth bounded well below)
+		++n;
+	}
+	__device__ __forceinline__ uint2 pop() {
+		--n;
+		return n < MTSB_STACK_SHARED ? sh[n * MTSB_TRACE_BLOCK] : loc[n - MTSB_STACK_SHARED];
+	}
+};
+
+// Closest (ANY=false) or any (ANY=true) hit of the segment [tmin, tmax] (inclusive, as the reference).
+// Returns true on a hit; for closest hits `hit` holds t,u,v and the TriAccel slot.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool traverse(const SceneDev &S, const V3 &o, const V3 &d, float tmin, float tmax,
+		HitRec &hit, uint2 *shStack, unsigned long long *cnt) {
+	const float tiny = 1e-18f;
+	V3 idir;
+	idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+	idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+	idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+	const uint32_t octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
+	const uint32_t octinv4 = octinv * 0x01010101u;
+
+	TravStack st; st.sh = shStack; st.n = 0;
+	uint2 ng = make_uint2(0u, 0x80000000u), tg = make_uint2(0u, 0u);
+	bool found = false;
+	hit.t = tmax; hit.slot = 0xffffffffu; hit.u = hit.v = 0;
+	unsigned nNodes = 0, nTris = 0;
+
+	while (true) {
+		if (ng.y > 0x00ffffffu) {
+			const uint32_t bit = 31u - __clz(ng.y);
+			const uint32_t imask = ng.y & 0xffu;
+			ng.y &= ~(1u << bit);
+			if (ng.y > 0x00ffffffu) st.push(ng);
+			const uint32_t slot = (bit - 24u) ^ octinv;
+			const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+			const uint4 *np = S.nodes + (size_t) (ng.x + rel) * 5;
+			const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+			if (COUNT) ++nNodes;
+			const uint32_t hm = node_test(n0, n1, n2, n3, n4, o, idir, octinv4, tmin, hit.t);
+			ng = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+			tg = make_uint2(n1.y, hm & 0x00ffffffu);
+		} else {
+			tg = ng; ng = make_uint2(0u, 0u);
+		}
+
+		while (tg.y) {
+			const uint32_t bit = __ffs(tg.y) - 1;
+			tg.y &= tg.y - 1;
+			const uint32_t slot = tg.x + bit;
+			const float4 *tp = S.tris + (size_t) slot * 3;
+			const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+			if (COUNT) ++nTris;
+			float t, u, v; bool h;
+			if (__float_as_uint(a.x) != K_NO_TRIANGLE)
+				h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
+			else
+				h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
+			if (h) {
+				if (ANY) { if (COUNT && cnt) { atomicAdd(cnt, nNodes); atomicAdd(cnt + 1, nTris); } return true; }
+				hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
+			}
+		}
+
+		if (ng.y <= 0x00ffffffu) {
+			if (st.n == 0) break;
+			ng = st.pop();
+		}
+	}
+	if (COUNT && cnt) { atomicAdd(cnt, (unsigned long long) nNodes); atomicAdd(cnt + 1, (unsigned long long) nTris); }
+	return found;
+}
+
+// The scene-AABB clip and adaptive epsilon that precede traversal in the three ShapeKDTree::rayIntersect
+// overloads (src/librender/skdtree.cpp:112-142, 207-226; AABB::rayIntersect include/mitsuba/core/aabb.h:308-338).
+// floorEps: the closest-hit overload floors the epsilon scale at Epsilon, the other two do not.
+__device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V3 &d, float rayMint, float rayMaxt,
+		bool floorEps, float &mint, float &maxt) {
+	float nearT = -INFINITY, farT = INFINITY;
+	#pragma unroll
+	for (int i = 0; i < 3; ++i) {
+		const float origin = comp(o, i), dir = comp(d, i);
+		const float minVal = comp(S.aabbMin, i), maxVal = comp(S.aabbMax, i);
+		if (dir == 0) {
+			if (origin < minVal || origin > maxVal) return false;
+		} else {
+			const float rcp = __fdiv_rn(1.0f, dir);
+			float t1 = __fmul_rn(__fsub_rn(minVal, origin), rcp);
+			float t2 = __fmul_rn(__fsub_rn(maxVal, origin), rcp);
+			if (t1 > t2) { float tmp = t1; t1 = t2; t2 = tmp; }
+			nearT = fmaxf(t1, nearT);
+			farT = fminf(t2, farT);
+			if (!(nearT <= farT)) return false;
+		}
+	}
+	float rayMinT = rayMint;
+	if (rayMinT == MTS_EPSILON) {
+		float m = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+		if (floorEps) m = fmaxf(m, MTS_EPSILON);
+		rayMinT = __fmul_rn(rayMinT, m);
+	}
+	mint = nearT; maxt = farT;
+	if (rayMinT > mint) mint = rayMinT;
+	if (rayMaxt < maxt) maxt = rayMaxt;
+	return maxt > mint;
+}
+
+} // namespace mtsb

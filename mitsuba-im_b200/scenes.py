@@ -1,0 +1,529 @@
+"""Procedural scenes and ray batches for the five BASELINE.json configs, described ONCE and emitted twice:
+as Mitsuba XML + binary PLY for the reference (oracle/_ref) and as flat arrays for the C ABI (binding.Scene).
+
+Host-side helpers only (numpy); nothing here traces a ray.  The camera / film / filter set-up restates
+PerspectiveCameraImpl::configure (src/sensors/perspective.cpp:126-180), Transform::lookAt / perspective
+(src/libcore/transform.cpp:99-123,191-214) and ReconstructionFilter::configure (src/libcore/rfilter.cpp:37-55)
+so that both back ends see the same sensor.
+"""
+import math
+import os
+
+import numpy as np
+
+from . import binding as B
+
+EPSILON = 1e-4
+SHADOW_EPSILON = 1e-3
+
+
+# ------------------------------------------------------------------------------------------------ meshes
+def icosphere(subdiv):
+    """Unit icosphere: 20 * 4**subdiv triangles, shared vertices."""
+    t = (1.0 + math.sqrt(5.0)) / 2.0
+    V = np.array([[-1, t, 0], [1, t, 0], [-1, -t, 0], [1, -t, 0], [0, -1, t], [0, 1, t], [0, -1, -t], [0, 1, -t],
+                  [t, 0, -1], [t, 0, 1], [-t, 0, -1], [-t, 0, 1]], dtype=np.float64)
+    V /= np.linalg.norm(V, axis=1, keepdims=True)
+    F = np.array([[0, 11, 5], [0, 5, 1], [0, 1, 7], [0, 7, 10], [0, 10, 11], [1, 5, 9], [5, 11, 4], [11, 10, 2],
+                  [10, 7, 6], [7, 1, 8], [3, 9, 4], [3, 4, 2], [3, 2, 6], [3, 6, 8], [3, 8, 9], [4, 9, 5], [2, 4, 11],
+                  [6, 2, 10], [8, 6, 7], [9, 8, 1]], dtype=np.int64)
+    for _ in range(subdiv):
+        e = np.concatenate([F[:, [0, 1]], F[:, [1, 2]], F[:, [2, 0]]], axis=0)
+        es = np.sort(e, axis=1)
+        key = es[:, 0] * (V.shape[0] + 1) + es[:, 1]
+        uniq, inv = np.unique(key, return_inverse=True)
+        a = uniq // (V.shape[0] + 1)
+        b = uniq % (V.shape[0] + 1)
+        mid = V[a] + V[b]
+        mid /= np.linalg.norm(mid, axis=1, keepdims=True)
+        base = V.shape[0]
+        V = np.concatenate([V, mid], axis=0)
+        n = F.shape[0]
+        m01, m12, m20 = base + inv[:n], base + inv[n:2 * n], base + inv[2 * n:]
+        F = np.concatenate([np.stack([F[:, 0], m01, m20], 1), np.stack([F[:, 1], m12, m01], 1),
+                            np.stack([F[:, 2], m20, m12], 1), np.stack([m01, m12, m20], 1)], axis=0)
+    return V, F
+
+
+def fbm(P, seed, octaves=4):
+    """Deterministic smooth pseudo-noise in [-1,1]: octaves of randomly oriented sinusoids (seeded)."""
+    rng = np.random.Generator(np.random.Philox(seed))
+    out = np.zeros(P.shape[0])
+    amp, freq, norm = 1.0, 2.0, 0.0
+    for _ in range(octaves):
+        acc = np.zeros(P.shape[0])
+        for _ in range(3):
+            d = rng.normal(size=3)
+            d /= np.linalg.norm(d)
+            acc += np.sin(freq * (P @ d) + rng.uniform(0, 2 * math.pi))
+        out += amp * acc / 3.0
+        norm += amp
+        amp *= 0.5
+        freq *= 2.0
+    return out / norm
+
+
+def vertex_normals(V, F):
+    fn = np.cross(V[F[:, 1]] - V[F[:, 0]], V[F[:, 2]] - V[F[:, 0]])
+    N = np.zeros_like(V)
+    for k in range(3):
+        np.add.at(N, F[:, k], fn)
+    N /= np.maximum(np.linalg.norm(N, axis=1, keepdims=True), 1e-30)
+    return N
+
+
+def displaced_sphere(subdiv, seed=1, radius=1.0, center=(0, 0, 0), amplitude=0.05):
+    """Config 2/3 geometry: icosphere displaced radially by amplitude * fbm(seed); returns float32 V, N and uint32 F."""
+    V, F = icosphere(subdiv)
+    V = V * (1.0 + amplitude * fbm(V, seed))[:, None]
+    N = vertex_normals(V, F)
+    V = V * radius + np.asarray(center, dtype=np.float64)
+    return V.astype(np.float32), N.astype(np.float32), F.astype(np.uint32)
+
+
+def write_ply(path, V, N, F):
+    """Binary little-endian PLY with per-vertex normals (so TriMesh::computeNormals keeps them as-is)."""
+    V = np.asarray(V, np.float32)
+    F = np.asarray(F, np.int32)
+    hdr = "ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n" % V.shape[0]
+    if N is not None:
+        hdr += "property float nx\nproperty float ny\nproperty float nz\n"
+    hdr += "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % F.shape[0]
+    with open(path, "wb") as f:
+        f.write(hdr.encode("ascii"))
+        vd = V if N is None else np.concatenate([V, np.asarray(N, np.float32)], axis=1)
+        f.write(np.ascontiguousarray(vd, "<f4").tobytes())
+        fd = np.empty(F.shape[0], dtype=[("n", "u1"), ("i", "<i4", 3)])
+        fd["n"] = 3
+        fd["i"] = F
+        f.write(fd.tobytes())
+
+
+# ------------------------------------------------------------------------------------------------ transforms
+def translate(x, y, z):
+    M = np.eye(4)
+    M[:3, 3] = [x, y, z]
+    return M
+
+
+def scale(x, y=None, z=None):
+    y = x if y is None else y
+    z = x if z is None else z
+    return np.diag([x, y, z, 1.0])
+
+
+def rotate(axis, angle_deg):
+    a = np.asarray(axis, dtype=np.float64)
+    a /= np.linalg.norm(a)
+    s, c = math.sin(math.radians(angle_deg)), math.cos(math.radians(angle_deg))
+    x, y, z = a
+    R = np.array([[x * x + (1 - x * x) * c, x * y * (1 - c) - z * s, x * z * (1 - c) + y * s, 0],
+                  [x * y * (1 - c) + z * s, y * y + (1 - y * y) * c, y * z * (1 - c) - x * s, 0],
+                  [x * z * (1 - c) - y * s, y * z * (1 - c) + x * s, z * z + (1 - z * z) * c, 0],
+                  [0, 0, 0, 1]])
+    return R
+
+
+def look_at(origin, target, up):
+    p, t, up = (np.asarray(v, dtype=np.float64) for v in (origin, target, up))
+    d = (t - p) / np.linalg.norm(t - p)
+    left = np.cross(up, d)
+    left /= np.linalg.norm(left)
+    new_up = np.cross(d, left)
+    M = np.eye(4)
+    M[:3, 0], M[:3, 1], M[:3, 2], M[:3, 3] = left, new_up, d, p
+    return M
+
+
+def _mat_xml(M):
+    return '<matrix value="%s"/>' % " ".join(repr(float(np.float32(v))) for v in np.asarray(M).reshape(-1))
+
+
+# ------------------------------------------------------------------------------------------------ sensor / film
+def filter_table(kind, radius=None, stddev=0.5):
+    """(radius, 32-entry table, border) as ReconstructionFilter::configure computes them (float32)."""
+    if kind == "box":
+        r = np.float32((0.5 if radius is None else radius)) + np.float32(1e-5)
+        ev = lambda x: np.float32(1.0) if abs(x) <= r else np.float32(0.0)
+    elif kind == "gaussian":
+        r = np.float32(4 * stddev)
+        alpha = -1.0 / (2.0 * stddev * stddev)
+        ev = lambda x: np.float32(max(0.0, math.exp(alpha * x * x) - math.exp(alpha * float(r) * float(r))))
+    else:
+        raise ValueError(kind)
+    vals = np.zeros(32, np.float32)
+    s = np.float32(0)
+    for i in range(31):
+        vals[i] = ev(float(r) * i / 31.0)
+        s += vals[i]
+    s = s * np.float32(2) * r / np.float32(31)
+    vals[:31] *= np.float32(1.0) / s
+    return float(r), vals, int(math.ceil(float(r) - 0.5))
+
+
+def make_camera(to_world, fov_deg, width, height, near=1e-2, far=1e4, fov_axis="x", crop=None):
+    aspect = width / float(height)
+    if fov_axis == "y":
+        fov_deg = math.degrees(2 * math.atan(math.tan(0.5 * math.radians(fov_deg)) * aspect))
+    cx, cy, cw, ch = (0, 0, width, height) if crop is None else crop
+    rel_size = (cw / width, ch / height)
+    rel_off = (cx / width, cy / height)
+    recip = 1.0 / (far - near)
+    cot = 1.0 / math.tan(math.radians(fov_deg / 2.0))
+    persp = np.array([[cot, 0, 0, 0], [0, cot, 0, 0], [0, 0, far * recip, -near * far * recip], [0, 0, 1, 0]], dtype=np.float64)
+    cam_to_sample = (scale(1.0 / rel_size[0], 1.0 / rel_size[1], 1.0) @ translate(-rel_off[0], -rel_off[1], 0.0) @
+                     scale(-0.5, -0.5 * aspect, 1.0) @ translate(-1.0, -1.0 / aspect, 0.0) @ persp)
+    sample_to_cam = np.linalg.inv(cam_to_sample)
+    cam = B.Camera()
+    cam.sample_to_camera[:] = [float(v) for v in sample_to_cam.reshape(-1)]
+    cam.camera_to_world[:] = [float(v) for v in np.asarray(to_world, dtype=np.float64).reshape(-1)]
+    cam.near_clip, cam.far_clip = near, far
+    cam.inv_resolution[:] = [1.0 / cw, 1.0 / ch]
+    return cam
+
+
+def make_film(width, height, rfilter="box", channels=5, stddev=0.5):
+    r, table, border = filter_table(rfilter, stddev=stddev)
+    f = B.FilmDesc()
+    f.width, f.height = width, height
+    f.offset[:] = [0, 0]
+    f.border, f.channels, f.filter_radius = border, channels, r
+    f.filter_table[:] = [float(v) for v in table]
+    f.crop_offset[:] = [0, 0]
+    f.crop_size[:] = [width, height]
+    return f
+
+
+def make_integrator(kind="path", max_depth=-1, rr_depth=5, strict_normals=False, hide_emitters=False,
+                    emitter_samples=1, bsdf_samples=1):
+    d = B.IntegratorDesc()
+    d.type = B.INTEGRATOR_PATH if kind == "path" else B.INTEGRATOR_DIRECT
+    d.max_depth, d.rr_depth = max_depth, rr_depth
+    d.strict_normals, d.hide_emitters = int(strict_normals), int(hide_emitters)
+    d.emitter_samples, d.bsdf_samples = emitter_samples, bsdf_samples
+    return d
+
+
+# ------------------------------------------------------------------------------------------------ scene description
+class SceneDesc:
+    """Back-end neutral scene: shapes (mesh | rectangle) with a BSDF dict and an optional area-emitter radiance,
+    plus free emitters (point, constant), a perspective sensor and an integrator."""
+
+    def __init__(self):
+        self.shapes = []
+        self.emitters = []          # free emitters: dict(type='point'|'constant', ...)
+        self.sensor = None
+        self.integrator = dict(kind="path", max_depth=-1, rr_depth=5)
+        self.sampler = dict(kind="independent", spp=4, seed=0)
+
+    # -- building --------------------------------------------------------------------------------
+    def add_mesh(self, V, N, F, bsdf=None, emitter=None, name=None):
+        self.shapes.append(dict(type="mesh", V=np.asarray(V, np.float32), N=None if N is None else np.asarray(N, np.float32),
+                                F=np.asarray(F, np.uint32), bsdf=bsdf or dict(type="diffuse"), emitter=emitter, name=name))
+        return len(self.shapes) - 1
+
+    def add_rectangle(self, to_world, bsdf=None, emitter=None, flip_normals=False):
+        self.shapes.append(dict(type="rectangle", to_world=np.asarray(to_world, np.float64), bsdf=bsdf or dict(type="diffuse"),
+                                emitter=emitter, flip_normals=flip_normals))
+        return len(self.shapes) - 1
+
+    def add_point_light(self, pos, intensity):
+        self.emitters.append(dict(type="point", pos=tuple(pos), intensity=tuple(intensity)))
+
+    def add_constant_env(self, radiance):
+        self.emitters.append(dict(type="constant", radiance=tuple(radiance)))
+
+    def set_sensor(self, to_world, fov, width, height, rfilter="box", spp=4, seed=0, sampler="independent", fov_axis="x"):
+        self.sensor = dict(to_world=np.asarray(to_world, np.float64), fov=fov, width=width, height=height, rfilter=rfilter,
+                           fov_axis=fov_axis)
+        self.sampler = dict(kind=sampler, spp=spp, seed=seed)
+
+    def set_integrator(self, kind="path", **kw):
+        self.integrator = dict(kind=kind, **kw)
+
+    # -- GPU back end ----------------------------------------------------------------------------
+    @staticmethod
+    def _bsdf_params(b):
+        """dict -> (type id, parameter vector) in the layout include/mtsb200.h documents."""
+        t = b["type"]
+        two = B.BSDF_TWOSIDED_FLAG if b.get("twosided") else 0
+        if t == "diffuse":
+            return B.BSDF_DIFFUSE | two, list(b.get("reflectance", (0.5, 0.5, 0.5)))
+        if t == "null":
+            return B.BSDF_NULL, [0, 0, 0]
+        if t == "dielectric":
+            eta = b.get("int_ior", 1.5046) / b.get("ext_ior", 1.000277)
+            return B.BSDF_DIELECTRIC, [eta] + list(b.get("specular_reflectance", (1, 1, 1))) + list(b.get("specular_transmittance", (1, 1, 1)))
+        if t == "plastic":
+            eta = b.get("int_ior", 1.49) / b.get("ext_ior", 1.000277)
+            from .hostmath import fresnel_diffuse_reflectance
+            fdr_int = fresnel_diffuse_reflectance(1.0 / eta)
+            fdr_ext = fresnel_diffuse_reflectance(eta)
+            dr = list(b.get("diffuse_reflectance", (0.5, 0.5, 0.5)))
+            sr = list(b.get("specular_reflectance", (1, 1, 1)))
+            d_avg = sum(dr) / 3.0          # Spectrum::average over 3 RGB samples
+            s_avg = sum(sr) / 3.0
+            ssw = s_avg / (d_avg + s_avg)
+            return B.BSDF_PLASTIC | two, [eta] + dr + sr + [fdr_int, fdr_ext, ssw, 1.0 if b.get("nonlinear") else 0.0]
+        if t == "roughconductor":
+            a = b.get("alpha", 0.1)
+            au, av = b.get("alpha_u", a), b.get("alpha_v", a)
+            eta = list(b.get("eta", (0.2004, 0.9240, 1.1022)))     # Cu @ RGB, see hostmath.CU_ETA_K
+            k = list(b.get("k", (3.9129, 2.4528, 2.1421)))
+            ext = b.get("ext_eta", 1.000277)
+            eta = [e / ext for e in eta]
+            k = [e / ext for e in k]
+            dist = dict(beckmann=0, ggx=1)[b.get("distribution", "beckmann")]
+            return B.BSDF_ROUGHCONDUCTOR | two, [au, av] + eta + k + list(b.get("specular_reflectance", (1, 1, 1))) + [dist, 1.0 if b.get("sample_visible", True) else 0.0]
+        raise ValueError("BSDF outside the GPU subset: %s" % t)
+
+    def upload(self, ctx, builder=B.BUILDER_LBVH):
+        """Creates and commits a binding.Scene.  Emitter order = Mitsuba's: Scene::addChild registers a shape's area
+        emitter when the shape is added, free emitters in XML order — free emitters are emitted first in to_xml()."""
+        sc = B.Scene(ctx)
+        for e in self.emitters:
+            if e["type"] == "point":
+                sc.add_emitter(B.EMITTER_POINT, radiance=e["intensity"], pos=e["pos"])
+            else:
+                sc.add_emitter(B.EMITTER_CONSTANT, radiance=e["radiance"])
+        for s in self.shapes:
+            bd = s["bsdf"]
+            if s["emitter"] is not None and bd is None:
+                bd = dict(type="null")
+            tid, params = self._bsdf_params(bd)
+            bid = sc.add_bsdf(tid, params)
+            eid = -1
+            if s["emitter"] is not None:
+                eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
+            if s["type"] == "mesh":
+                sc.add_mesh(s["V"], s["F"], normals=s["N"], bsdf=bid, emitter=eid)
+            else:
+                sc.add_rectangle(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
+        sc.commit(builder)
+        return sc
+
+    def camera(self):
+        s = self.sensor
+        return make_camera(s["to_world"], s["fov"], s["width"], s["height"], fov_axis=s["fov_axis"])
+
+    def film(self, channels=5):
+        s = self.sensor
+        return make_film(s["width"], s["height"], s["rfilter"], channels=channels)
+
+    def integrator_desc(self):
+        return make_integrator(**self.integrator)
+
+    # -- reference back end ----------------------------------------------------------------------
+    @staticmethod
+    def _bsdf_xml(b):
+        t = b["type"]
+        rgb = lambda name, v: '<rgb name="%s" value="%s"/>' % (name, ", ".join(repr(float(x)) for x in v))
+        if t == "null":
+            return ""
+        inner = ""
+        if t == "diffuse":
+            inner = '<bsdf type="diffuse">%s</bsdf>' % rgb("reflectance", b.get("reflectance", (0.5, 0.5, 0.5)))
+        elif t == "dielectric":
+            inner = '<bsdf type="dielectric"><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/></bsdf>' % (
+                b.get("int_ior", 1.5046), b.get("ext_ior", 1.000277))
+        elif t == "plastic":
+            inner = '<bsdf type="plastic"><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/>%s%s<boolean name="nonlinear" value="%s"/></bsdf>' % (
+                b.get("int_ior", 1.49), b.get("ext_ior", 1.000277), rgb("diffuseReflectance", b.get("diffuse_reflectance", (0.5, 0.5, 0.5))),
+                rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), "true" if b.get("nonlinear") else "false")
+        elif t == "roughconductor":
+            a = b.get("alpha", 0.1)
+            inner = ('<bsdf type="roughconductor"><string name="distribution" value="%s"/><float name="alphaU" value="%r"/>'
+                     '<float name="alphaV" value="%r"/>%s%s<float name="extEta" value="%r"/><boolean name="sampleVisible" value="%s"/></bsdf>') % (
+                b.get("distribution", "beckmann"), b.get("alpha_u", a), b.get("alpha_v", a),
+                rgb("eta", b.get("eta", (0.2004, 0.9240, 1.1022))), rgb("k", b.get("k", (3.9129, 2.4528, 2.1421))),
+                b.get("ext_eta", 1.000277), "true" if b.get("sample_visible", True) else "false")
+        else:
+            raise ValueError(t)
+        if b.get("twosided"):
+            inner = '<bsdf type="twosided">%s</bsdf>' % inner
+        return inner
+
+    def to_xml(self, directory, name="scene", film_format="pfm"):
+        """Writes <directory>/<name>.xml (+ one PLY per mesh) and returns the XML path."""
+        os.makedirs(directory, exist_ok=True)
+        out = ['<?xml version="1.0" encoding="utf-8"?>', '<scene version="0.5.0">']
+        ig = self.integrator
+        out.append('<integrator type="%s">' % ig["kind"])
+        for k, xmlk in (("max_depth", "maxDepth"), ("rr_depth", "rrDepth"), ("emitter_samples", "emitterSamples"), ("bsdf_samples", "bsdfSamples")):
+            if k in ig:
+                out.append('<integer name="%s" value="%d"/>' % (xmlk, ig[k]))
+        for k, xmlk in (("strict_normals", "strictNormals"), ("hide_emitters", "hideEmitters")):
+            if k in ig:
+                out.append('<boolean name="%s" value="%s"/>' % (xmlk, "true" if ig[k] else "false"))
+        out.append('</integrator>')
+        if self.sensor is not None:
+            s, sm = self.sensor, self.sampler
+            out.append('<sensor type="perspective"><float name="fov" value="%r"/><string name="fovAxis" value="%s"/>' % (s["fov"], s["fov_axis"]))
+            out.append('<transform name="toWorld">%s</transform>' % _mat_xml(s["to_world"]))
+            if sm["kind"] == "ctr":
+                out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/></sampler>' % (sm["spp"], sm["seed"]))
+            else:
+                out.append('<sampler type="independent"><integer name="sampleCount" value="%d"/></sampler>' % sm["spp"])
+            out.append('<film type="hdrfilm"><integer name="width" value="%d"/><integer name="height" value="%d"/>'
+                       '<rfilter type="%s"/><string name="fileFormat" value="%s"/><string name="pixelFormat" value="rgb"/>'
+                       '<boolean name="banner" value="false"/></film>' % (s["width"], s["height"], s["rfilter"], film_format))
+            out.append('</sensor>')
+        for e in self.emitters:
+            if e["type"] == "point":
+                out.append('<emitter type="point"><point name="position" x="%r" y="%r" z="%r"/><rgb name="intensity" value="%s"/></emitter>' % (
+                    e["pos"][0], e["pos"][1], e["pos"][2], ", ".join(repr(float(x)) for x in e["intensity"])))
+            else:
+                out.append('<emitter type="constant"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in e["radiance"]))
+        for i, s in enumerate(self.shapes):
+            em = ""
+            if s["emitter"] is not None:
+                em = '<emitter type="area"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in s["emitter"])
+            bs = self._bsdf_xml(s["bsdf"]) if s["bsdf"] is not None else ""
+            if s["type"] == "mesh":
+                fn = "%s_mesh%d.ply" % (name, i)
+                write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"])
+                face = "" if s["N"] is not None else '<boolean name="faceNormals" value="true"/>'
+                out.append('<shape type="ply"><string name="filename" value="%s"/>%s%s%s</shape>' % (fn, face, bs, em))
+            else:
+                flip = '<boolean name="flipNormals" value="true"/>' if s["flip_normals"] else ""
+                out.append('<shape type="rectangle"><transform name="toWorld">%s</transform>%s%s%s</shape>' % (_mat_xml(s["to_world"]), flip, bs, em))
+        out.append('</scene>')
+        path = os.path.join(directory, name + ".xml")
+        with open(path, "w") as f:
+            f.write("\n".join(out))
+        return path
+
+
+# ------------------------------------------------------------------------------------------------ the configs
+def cube_mesh(to_world):
+    """A 12-triangle, 24-vertex box [-1,1]^3 with per-face normals (used instead of the `cube` plugin when the scene
+    is driven through the C ABI; the Mitsuba plugin path reads the real `cube` TriMesh)."""
+    V, N, F = [], [], []
+    for axis in range(3):
+        for sgn in (-1.0, 1.0):
+            n = np.zeros(3)
+            n[axis] = sgn
+            u = np.zeros(3)
+            u[(axis + 1) % 3] = 1.0
+            v = np.cross(n, u)
+            base = len(V)
+            for a, b in ((-1, -1), (1, -1), (1, 1), (-1, 1)):
+                V.append(n + a * u + b * v)
+                N.append(n)
+            F += [[base, base + 1, base + 2], [base + 2, base + 3, base]]
+    V = np.asarray(V)
+    N = np.asarray(N)
+    M = np.asarray(to_world, dtype=np.float64)
+    Vw = V @ M[:3, :3].T + M[:3, 3]
+    Nw = N @ np.linalg.inv(M[:3, :3])
+    Nw /= np.linalg.norm(Nw, axis=1, keepdims=True)
+    return Vw.astype(np.float32), Nw.astype(np.float32), np.asarray(F, np.uint32)
+
+
+def cornell_box(width=512, height=512, spp=64, max_depth=5, rfilter="box", sampler="independent", seed=0):
+    """Config 1: 5 diffuse rectangles + a cube + a rectangular area light."""
+    sd = SceneDesc()
+    white = dict(type="diffuse", reflectance=(0.5, 0.5, 0.5))
+    sd.add_rectangle(translate(0, 0, 0) @ rotate((1, 0, 0), -90), bsdf=white)
+    sd.add_rectangle(translate(0, 2, 0) @ rotate((1, 0, 0), 90), bsdf=white)
+    sd.add_rectangle(translate(0, 1, -1), bsdf=white)
+    sd.add_rectangle(translate(-1, 1, 0) @ rotate((0, 1, 0), 90), bsdf=dict(type="diffuse", reflectance=(0.63, 0.065, 0.05)))
+    sd.add_rectangle(translate(1, 1, 0) @ rotate((0, 1, 0), -90), bsdf=dict(type="diffuse", reflectance=(0.14, 0.45, 0.091)))
+    V, N, F = cube_mesh(translate(0.3, 0.3, 0.2) @ rotate((0, 1, 0), 20) @ scale(0.3))
+    sd.add_mesh(V, N, F, bsdf=white)
+    sd.add_rectangle(translate(0, 1.98, 0) @ rotate((1, 0, 0), 90) @ scale(0.25), bsdf=None, emitter=(17, 12, 4))
+    sd.set_sensor(look_at((0, 1, 3.9), (0, 1, 0), (0, 1, 0)), 39.3077, width, height, rfilter=rfilter, spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator("path", max_depth=max_depth, rr_depth=5)
+    return sd
+
+
+def sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian",
+                 sampler="independent", seed=0):
+    """Config 3/4/5: nx*ny displaced icospheres (20*4**subdiv triangles each) alternating GGX rough copper and bk7
+    glass on a diffuse ground quad, one area light quad + constant environment.  subdiv=6, 16x8 -> 10 485 762 triangles."""
+    sd = SceneDesc()
+    base_V, base_F = icosphere(subdiv)
+    metal_V, metal_N, metal_F, glass_V, glass_N, glass_F = [], [], [], [], [], []
+    mo = go = 0
+    for j in range(ny):
+        for i in range(nx):
+            idx = j * nx + i
+            V = base_V * (1.0 + 0.05 * fbm(base_V, idx + 1))[:, None]
+            N = vertex_normals(V, base_F)
+            V = V * 0.45 + np.array([i - (nx - 1) / 2.0, 0.5, j - (ny - 1) / 2.0])
+            if (i + j) % 2 == 0:
+                metal_V.append(V); metal_N.append(N); metal_F.append(base_F + mo); mo += V.shape[0]
+            else:
+                glass_V.append(V); glass_N.append(N); glass_F.append(base_F + go); go += V.shape[0]
+    sd.add_mesh(np.concatenate(metal_V), np.concatenate(metal_N), np.concatenate(metal_F),
+                bsdf=dict(type="roughconductor", distribution="ggx", alpha=0.1))
+    if glass_V:
+        sd.add_mesh(np.concatenate(glass_V), np.concatenate(glass_N), np.concatenate(glass_F), bsdf=dict(type="dielectric"))
+    g = max(nx, ny) * 0.75
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
+    sd.add_rectangle(translate(0, 6, 0) @ rotate((1, 0, 0), 90) @ scale(2.0), bsdf=None, emitter=(30, 30, 30))
+    sd.add_constant_env((0.5, 0.5, 0.5))
+    sd.set_sensor(look_at((0, 5.5, -ny * 1.1 - 2), (0, 0.3, 0), (0, 1, 0)), 45.0, width, height, rfilter=rfilter, spp=spp,
+                  sampler=sampler, seed=seed)
+    sd.set_integrator("path", max_depth=max_depth, rr_depth=5)
+    return sd
+
+
+# ------------------------------------------------------------------------------------------------ ray batches (config 2)
+def _uniform_sphere(u):
+    z = 1.0 - 2.0 * u[:, 1]
+    r = np.sqrt(np.maximum(0.0, 1.0 - z * z))
+    phi = 2.0 * math.pi * u[:, 0]
+    return np.stack([r * np.cos(phi), r * np.sin(phi), z], axis=1)
+
+
+def chord_rays(n, center=(0, 0, 0), radius=1.1, seed=42, mint=0.0):
+    """Incoherent rays between two uniform points on a bounding sphere — the distribution of `mtsutil kdbench`
+    (src/utils/kdbench.cpp:226-230).  mint=EPSILON reproduces kdbench's Ray(o,d,time) constructor default."""
+    rng = np.random.Generator(np.random.Philox(seed))
+    u = rng.random((n, 4), dtype=np.float32).astype(np.float64)
+    c = np.asarray(center, dtype=np.float64)
+    p1 = c + radius * _uniform_sphere(u[:, 0:2])
+    p2 = c + radius * _uniform_sphere(u[:, 2:4])
+    d = p2 - p1
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-20)
+    rays = np.zeros(n, B.ray_dtype)
+    rays["o"], rays["d"] = p1.astype(np.float32), d.astype(np.float32)
+    rays["mint"], rays["maxt"] = np.float32(mint), np.float32(np.inf)
+    return rays
+
+
+def pinhole_rays(res, origin=(0, 0, -3.0), target=(0, 0, 0), fov_deg=45.0):
+    """Coherent primary rays of a res x res pinhole camera, row-major."""
+    M = look_at(origin, target, (0, 1, 0))
+    t = math.tan(math.radians(fov_deg) / 2.0)
+    xs = (np.arange(res) + 0.5) / res * 2.0 - 1.0
+    px, py = np.meshgrid(xs, -xs)
+    d = np.stack([px.ravel() * t, py.ravel() * t, np.ones(res * res)], axis=1)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d @ M[:3, :3].T
+    rays = np.zeros(res * res, B.ray_dtype)
+    rays["o"] = np.asarray(origin, np.float32)
+    rays["d"] = d.astype(np.float32)
+    rays["mint"], rays["maxt"] = np.float32(EPSILON), np.float32(np.inf)
+    return rays
+
+
+def shadow_rays(points, light_center=(0, 3.0, 0), light_half=0.2, seed=43):
+    """Shadow segments from surface points to uniform points on a light quad, with the reference's conventions:
+    mint = Epsilon (scaled adaptively on the device) and maxt = dist * (1 - ShadowEpsilon)  (src/librender/scene.cpp:871-873)."""
+    n = points.shape[0]
+    rng = np.random.Generator(np.random.Philox(seed))
+    u = rng.random((n, 2), dtype=np.float32).astype(np.float64)
+    lc = np.asarray(light_center, dtype=np.float64)
+    lp = lc + np.stack([(u[:, 0] * 2 - 1) * light_half, np.zeros(n), (u[:, 1] * 2 - 1) * light_half], axis=1)
+    d = lp - points.astype(np.float64)
+    dist = np.linalg.norm(d, axis=1)
+    d /= np.maximum(dist[:, None], 1e-20)
+    rays = np.zeros(n, B.ray_dtype)
+    rays["o"], rays["d"] = points.astype(np.float32), d.astype(np.float32)
+    rays["mint"] = np.float32(EPSILON)
+    rays["maxt"] = (dist.astype(np.float32) * np.float32(1 - SHADOW_EPSILON)).astype(np.float32)
+    return rays
