@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark: BASELINE.json config 2, closest-hit Mrays/s on a 1.3 M-triangle synthetic mesh.
+
+One "step" = one closest-hit pass of libmtsb200 over a batch of 16 777 216 incoherent chord rays (the distribution of
+the reference's own `mtsutil kdbench`, src/utils/kdbench.cpp:226-230).  `value` is timed on the device with the rays
+already resident in HBM; `e2e` is the same query through the host-pointer C-ABI call (pinned host buffers, H2D of the
+rays and D2H of the hit records inside the timed region).  Coherent primary rays, shadow (any-hit) rays and the
+wavefront path tracer are reported in `detail` on the same JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+N > 1 is launched under torchrun (one rank per GPU); rays are sharded across ranks with no data-path collective
+(weak scaling: every rank traces its own 16 M-ray batch against a replicated scene).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as graft  # noqa: E402
+
+SUBDIV = 8                      # 20 * 4^8 = 1 310 720 triangles
+N_RAYS = 1 << 24                # 16 777 216
+BYTES_PER_RAY_CLOSEST = 48      # 32 B ray in + 16 B hit out
+BYTES_PER_RAY_ANY = 33          # 32 B in + 1 B out
+CPU_SAMPLE_RAYS = 1 << 21       # bounded sample for the CPU legs
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.rows, self.proc, self.device = [], None, device
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def build_mesh(S):
+    V, N, F = S.displaced_sphere(SUBDIV, seed=1)
+    sd = S.SceneDesc()
+    sd.add_mesh(V, N, F)
+    sd.add_point_light((0, 5, 0), (1, 1, 1))
+    return sd
+
+
+def reference_arm(args, rank, world):
+    """The reference's own CPU implementation (oracle/_ref: unmodified ShapeKDTree::rayIntersect via oracle/raydump.cpp)
+    on all host threads, on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    pkg = graft.load_package()
+    S = pkg.scenes
+    import tempfile
+    cores = os.cpu_count() or 1
+    sd = build_mesh(S)
+    rays = S.chord_rays(CPU_SAMPLE_RAYS, radius=1.1, seed=42)
+    with tempfile.TemporaryDirectory() as td:
+        xml = sd.to_xml(td, "bench")
+        if O.have_reference():
+            _, tm = O.ref_trace(xml, rays, threads=cores, repeats=args.warmup + args.steps)
+            times = tm.get("closest_ms_all", [tm["closest_ms"]])[args.warmup:] or [tm["closest_ms"]]
+            ms = float(np.mean(times))
+            kind, build_ms = "reference", tm.get("build_ms")
+        else:
+            osc = O.OracleScene(sd)
+            sub = rays[:4096]
+            t0 = time.perf_counter()
+            osc.closest(sub)
+            ms = (time.perf_counter() - t0) * 1e3 * (rays.shape[0] / sub.shape[0])
+            kind, build_ms, cores = "port", None, 1
+    value = rays.shape[0] / ms / 1e3
+    sample = "%d of the %d chord rays per step, %d threads, kd-tree build (%s ms) excluded" % (rays.shape[0], N_RAYS, cores, build_ms)
+    line = {"impl": "reference", "metric": "closest-hit Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "config2: closest-hit, 1310720-triangle displaced icosphere, incoherent chord rays"},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(S, sd, cores):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    import tempfile
+    rays = S.chord_rays(CPU_SAMPLE_RAYS, radius=1.1, seed=42)
+    if not O.have_reference():
+        osc = O.OracleScene(sd)
+        sub = rays[:2048]
+        t0 = time.perf_counter()
+        osc.closest(sub)
+        dt = time.perf_counter() - t0
+        return {"value": sub.shape[0] / dt / 1e6, "unit": "Mrays/s", "cores": 1, "kind": "port",
+                "sample": "2048 rays, brute-force C restatement (no kd-tree)"}
+    with tempfile.TemporaryDirectory() as td:
+        xml = sd.to_xml(td, "bench")
+        _, tm = O.ref_trace(xml, rays, threads=cores, repeats=2)
+    return {"value": tm["closest_mrays"], "unit": "Mrays/s", "cores": cores, "kind": "reference",
+            "sample": "%d of the %d chord rays, best of 2, kd-tree build %s ms excluded; any-hit %.2f Mrays/s" % (
+                rays.shape[0], N_RAYS, tm.get("build_ms"), tm.get("any_mrays", 0.0)),
+            "kd_build_ms": tm.get("build_ms")}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--builder", default="ploc", choices=["lbvh", "ploc"])
+    ap.add_argument("--rays", type=int, default=N_RAYS)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    pkg = graft.load_package()
+    S, B = pkg.scenes, pkg.binding
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = B.Context(local)
+    torch.cuda.set_device(local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
+
+    sd = build_mesh(S)
+    builder = B.BUILDER_PLOC if args.builder == "ploc" else B.BUILDER_LBVH
+    sc = sd.upload(ctx, builder)
+    bstats = sc.build_stats()
+    n = args.rays
+    rays_h = S.chord_rays(n, radius=1.1, seed=42 + rank)
+    rays_d = torch.from_numpy(rays_h.view(np.float32).reshape(-1, 8)).cuda()
+    hits_d = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+
+    def step():
+        sc.trace_device("closest", rays_d.data_ptr(), n, hits_d.data_ptr())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kern_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for k in range(args.steps):
+            kern_ev[k][0].record(stream)
+            step()
+            kern_ev[k][1].record(stream)
+        e1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms_total = e0.elapsed_time(e1)
+    if world > 1:
+        tt = torch.tensor([ms_total], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in kern_ev]))
+    value = world * n / ms_step / 1e3
+
+    # hit rate / traversal statistics (outside the timed region)
+    hits_h = hits_d.cpu().numpy()
+    hit_rate = float(np.isfinite(hits_h[:, 0]).mean())
+    cnt = sc.trace_count_device(rays_d.data_ptr(), min(n, 1 << 22))
+    nodes_per_ray, prims_per_ray = cnt["nodes"] / max(cnt["rays"], 1), cnt["prims"] / max(cnt["rays"], 1)
+
+    # --- end-to-end through the host-pointer C ABI (pinned buffers; H2D + D2H inside the timed region) ---
+    pin_r = B.PinnedArray((n,), B.ray_dtype)
+    pin_h = B.PinnedArray((n,), B.hit_dtype)
+    pin_r.array[:] = rays_h
+    for _ in range(2):
+        sc.ray_intersect(pin_r.array, out=pin_h.array)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, args.steps // 2)
+    for _ in range(e2e_steps):
+        sc.ray_intersect(pin_r.array, out=pin_h.array)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if world > 1:
+        tt = torch.tensor([e2e_ms], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
+    assert np.array_equal(pin_h.array.view(np.uint32).reshape(-1, 4), hits_h.view(np.uint32)), "host-path hits differ from device-path hits"
+    e2e_value = world * n / e2e_ms / 1e3
+
+    # --- other ray sets of config 2 (detail only) ---
+    detail = {}
+    if rank == 0:
+        res = 4096 if n >= (1 << 24) else int(np.sqrt(n))
+        coh = S.pinhole_rays(res, origin=(0, 0.3, -3.0))
+        coh_d = torch.from_numpy(coh.view(np.float32).reshape(-1, 8)).cuda()
+        surf = sc.ray_intersect_surface(coh[:: max(1, coh.shape[0] // (1 << 20))])
+        pts = surf["p"][np.isfinite(surf["t"])]
+        sh = S.shadow_rays(np.tile(pts, (int(np.ceil(coh.shape[0] / max(len(pts), 1))), 1))[: coh.shape[0]], light_center=(0, 3.0, 0.5))
+        sh_d = torch.from_numpy(sh.view(np.float32).reshape(-1, 8)).cuda()
+        out_any = torch.empty(sh.shape[0], dtype=torch.uint8, device="cuda")
+        for name, mode, buf, out in (("coherent_closest", "closest", coh_d, hits_d), ("shadow_any", "any", sh_d, out_any),
+                                     ("random_any", "any", rays_d, out_any)):
+            m = min(buf.shape[0], out.shape[0])
+            for _ in range(2):
+                sc.trace_device(mode, buf.data_ptr(), m, out.data_ptr())
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                a.record(stream)
+                for _ in range(5):
+                    sc.trace_device(mode, buf.data_ptr(), m, out.data_ptr())
+                b.record(stream)
+            torch.cuda.synchronize()
+            detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
+        try:
+            import bench_render
+            detail["path"] = bench_render.run(pkg, ctx, stream)
+        except ImportError:
+            pass
+
+    if rank == 0:
+        peak, peak_kind = measured_peaks()
+        scene_bytes = bstats["node_bytes"] + bstats["tri_bytes"]
+        algo_bytes = n * BYTES_PER_RAY_CLOSEST + scene_bytes
+        achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("trace_closest_bytes_per_launch")
+            except Exception:
+                traffic = None
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            cpu = cpu_baseline(S, sd, os.cpu_count() or 1)
+        line = {
+            "metric": "closest-hit Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "config2: closest-hit, 1310720-triangle displaced icosphere (BVH8, %s), %d incoherent chord rays per GPU per step" % (args.builder, n),
+                       "l2": "inputs larger than L2 (%.0f MB of rays + %.0f MB of hits per step)" % (n * 32 / 1e6, n * 16 / 1e6),
+                       "parallelism": "rays sharded across %d GPU(s), scene replicated, no collective" % world},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
+                    "ms_per_step": e2e_ms, "api": "mtsb_trace_closest(host pointers), pinned buffers, 2M-ray chunks pipelined over 3 streams"},
+            "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>", "kernel_ms": kern_ms,
+                         "algorithmic_bytes": algo_bytes, "nodes_per_ray": nodes_per_ray, "prim_tests_per_ray": prims_per_ray,
+                         "traversal_bytes_per_ray": nodes_per_ray * 80 + prims_per_ray * 48 + 48},
+            "cpu_baseline": cpu,
+            "detail": dict(detail, hit_rate=hit_rate, build=bstats),
+        }
+        print(json.dumps(line), flush=True)
+    pin_r.free()
+    pin_h.free()
+    sc.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

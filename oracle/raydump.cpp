@@ -118,6 +118,7 @@ public:
 		const ShapeKDTree *kd = m_kdtree.get();
 		Thread *parent = Thread::getThread();
 		double bestClosest = 1e30, bestAny = 1e30;
+		std::vector<double> allClosest, allAny;
 
 		for (int rep = 0; rep < repeats; ++rep) {
 			for (int pass = 0; pass < 2; ++pass) {
@@ -153,14 +154,19 @@ public:
 				}
 				for (auto &t : threads) t.join();
 				double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-				if (pass == 0) bestClosest = std::min(bestClosest, ms); else bestAny = std::min(bestAny, ms);
+				if (pass == 0) { bestClosest = std::min(bestClosest, ms); allClosest.push_back(ms); }
+				else { bestAny = std::min(bestAny, ms); allAny.push_back(ms); }
 			}
 		}
 		writeFloats(argv[4], out);
 		printf("RAYDUMP {\"rays\": %zu, \"threads\": %d, \"repeats\": %d, \"build_ms\": %u, \"closest_ms\": %.3f, "
-			"\"any_ms\": %.3f, \"closest_mrays\": %.4f, \"any_mrays\": %.4f, \"prims\": %u}\n",
+			"\"any_ms\": %.3f, \"closest_mrays\": %.4f, \"any_mrays\": %.4f, \"prims\": %u, \"closest_ms_all\": [",
 			n, nThreads, repeats, buildMs, bestClosest, bestAny, n / bestClosest / 1e3, n / bestAny / 1e3,
 			(unsigned) kd->getPrimitiveCount());
+		for (size_t i = 0; i < allClosest.size(); ++i) printf("%s%.3f", i ? ", " : "", allClosest[i]);
+		printf("], \"any_ms_all\": [");
+		for (size_t i = 0; i < allAny.size(); ++i) printf("%s%.3f", i ? ", " : "", allAny[i]);
+		printf("]}\n");
 		fflush(stdout);
 		return 0;
 	}

@@ -1,0 +1,190 @@
+"""GPU parity tests for the intersection half of the hot path, through the C ABI (binding.Scene):
+CUDA BVH8 closest-hit / any-hit vs (1) golden hit records of the unmodified reference, (2) the C restatement on
+seeded inputs, (3) the live reference (oracle/_ref) at a larger size, and (4) size-independent properties at
+BASELINE config-2 scale."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _global_ref_prim(sd, gold):
+    offs = np.cumsum([0] + [s["F"].shape[0] if s["type"] == "mesh" else 1 for s in sd.shapes])
+    is_rect = np.array([s["type"] != "mesh" for s in sd.shapes])
+    sh = np.maximum(gold["ref_shape"], 0)
+    prim = np.where(is_rect[sh], 0, np.maximum(gold["ref_prim"], 0))
+    return np.where(gold["ref_shape"] >= 0, offs[sh] + prim, -1)
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+@pytest.mark.parametrize("kind", ["sphere", "cornell"])
+def test_hits_match_reference_golden(pkg, ctx, golden, kind, builder):
+    gold = golden("hits_%s.npz" % kind)
+    sd = helpers.desc_from_golden(pkg.scenes, gold, kind)
+    sc = sd.upload(ctx, builder)
+    try:
+        hits = sc.ray_intersect(gold["rays"])
+        surf = sc.ray_intersect_surface(gold["rays"])
+        bound = 0.9999 if kind == "sphere" else 0.995   # see tests/test_oracle.py for the grazing self-hit rays
+        cos = np.abs((gold["rays"][:, 4:7] * gold["ref_ng"]).sum(axis=1))
+        st = helpers.compare_hits(gold["rays"], hits["t"], hits["prim"].view(np.int32), gold["ref_t"], _global_ref_prim(sd, gold),
+                                  p=surf["p"], ref_p=gold["ref_p"], min_agree=bound, cos=cos)
+        assert st["miss_agree"] >= bound
+        # record fill: normals as fillIntersectionRecord computes them
+        m = np.isfinite(gold["ref_t"]) & (surf["prim"].view(np.int32) == _global_ref_prim(sd, gold))
+        assert np.abs(surf["ng"][m] - gold["ref_ng"][m]).max() < 2e-4
+        assert np.abs(surf["ns"][m] - gold["ref_ns"][m]).max() < 2e-4
+        assert (surf["t"] == hits["t"]).all() or np.allclose(surf["t"], hits["t"], equal_nan=True)
+        a = sc.ray_intersect_any(gold["rays"])
+        assert (a == gold["ref_any"]).mean() >= bound
+    finally:
+        sc.close()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_hits_match_restatement_on_seeded_scenes(pkg, ctx, seed):
+    S = pkg.scenes
+    rng = np.random.default_rng(seed)
+    sd = S.SceneDesc()
+    for k in range(3):
+        V, N, F = S.displaced_sphere(2, seed=seed * 10 + k, radius=0.3 + 0.2 * k, center=rng.uniform(-1, 1, 3))
+        sd.add_mesh(V, N if k != 1 else None, F)
+    sd.add_rectangle(S.translate(0, -1.2, 0) @ S.rotate((1, 0, 0), -90) @ S.scale(3.0))
+    rays = np.concatenate([S.chord_rays(20000, radius=2.5, seed=seed, mint=0.0), S.chord_rays(20000, radius=1.0, seed=seed + 5, mint=S.EPSILON)])
+    osc = O.OracleScene(sd)
+    t, u, v, prim = osc.closest(rays)
+    sc = sd.upload(ctx, seed % 2)
+    try:
+        hits = sc.ray_intersect(rays)
+        surf = sc.ray_intersect_surface(rays)
+        cos = np.abs((rays["d"] * surf["ng"]).sum(axis=1))
+        helpers.compare_hits(rays, hits["t"], hits["prim"].view(np.int32), t, np.where(np.isfinite(t), prim.view(np.int32), -1), cos=cos)
+        m = np.isfinite(t) & (hits["prim"] == prim)
+        # barycentrics directly: |du| ~ |dp| / edge length (edge ~ 0.1 here), same conditioning as t
+        c = np.maximum(cos[m], 1e-4)
+        assert (np.abs(hits["u"][m] - u[m]) * c).max() < 1e-4 and (np.abs(hits["v"][m] - v[m]) * c).max() < 1e-4
+        assert (sc.ray_intersect_any(rays) == osc.any(rays)).mean() >= 0.9999
+        mn, mx = sc.aabb()
+        omn, omx = osc.aabb()
+        assert np.allclose(mn, omn, atol=1e-6) and np.allclose(mx, omx, atol=1e-6)
+    finally:
+        sc.close()
+
+
+def test_edge_cases(pkg, ctx):
+    S, B = pkg.scenes, pkg.binding
+    # single triangle, degenerate triangle, axis-parallel rays, rays outside the AABB, t windows, empty batches
+    sd = S.SceneDesc()
+    V = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [2, 2, 2], [2, 2, 2], [2, 2, 2]], np.float32)
+    F = np.array([[0, 1, 2], [3, 4, 5]], np.uint32)
+    sd.add_mesh(V, None, F)
+    sc = sd.upload(ctx)
+    try:
+        assert sc.primitive_count == 2
+        assert sc.ray_intersect(np.zeros(0, B.ray_dtype)).shape == (0,)
+        rays = np.zeros(8, B.ray_dtype)
+        rays["o"] = [[0.25, 0.25, 1], [0.25, 0.25, 1], [0.25, 0.25, 1], [0.25, 0.25, -1], [5, 5, 5], [0.25, 0.25, 1], [0, 0, 1], [0.25, 0.25, 1]]
+        rays["d"] = [[0, 0, -1], [0, 0, -1], [0, 0, -1], [0, 0, 1], [1, 0, 0], [0, 0, 1], [0, 0, -1], [0, 0, -1]]
+        rays["mint"] = [0, 0, 1.5, 0, 0, 0, 0, 1.0]
+        rays["maxt"] = [np.inf, 0.5, np.inf, np.inf, np.inf, np.inf, np.inf, 1.0]
+        h = sc.ray_intersect(rays)
+        osc = O.OracleScene(sd)
+        t, u, v, prim = osc.closest(rays)
+        assert np.array_equal(np.isfinite(h["t"]), np.isfinite(t))
+        assert list(np.isfinite(h["t"])) == [True, False, False, True, False, False, True, False]
+        assert np.allclose(h["t"][np.isfinite(t)], t[np.isfinite(t)], rtol=1e-6)
+        assert (h["prim"][~np.isfinite(t)] == B.MTSB_NO_HIT).all()
+        assert np.array_equal(sc.ray_intersect_any(rays), osc.any(rays))
+    finally:
+        sc.close()
+    # error behaviour of the boundary
+    bad = B.Scene(ctx)
+    with pytest.raises(B.MtsbError):
+        bad.commit()            # no primitives
+    with pytest.raises(B.MtsbError):
+        bad.add_bsdf(99, [])    # outside the subset
+    bid = bad.add_bsdf(B.BSDF_DIFFUSE, [0.5, 0.5, 0.5])
+    with pytest.raises(B.MtsbError):
+        bad.add_mesh(V, np.array([[0, 1, 9]], np.uint32), bsdf=bid)   # index out of range
+    with pytest.raises(B.MtsbError):
+        bad.ray_intersect(np.zeros(1, B.ray_dtype))                   # not committed
+    bad.close()
+
+
+def test_large_mesh_properties(pkg, ctx):
+    """BASELINE config-2 scale (1.3 M triangles, 4 M rays): properties that need no oracle."""
+    S, B = pkg.scenes, pkg.binding
+    V, N, F = S.displaced_sphere(8, seed=1)
+    assert F.shape[0] == 1310720
+    sd = S.SceneDesc()
+    sd.add_mesh(V, N, F)
+    sc = sd.upload(ctx, B.BUILDER_LBVH)
+    sc2 = sd.upload(ctx, B.BUILDER_PLOC)
+    try:
+        rays = S.chord_rays(1 << 22, radius=1.1, seed=42)
+        h = sc.ray_intersect(rays)
+        hit = np.isfinite(h["t"])
+        assert 0.5 < hit.mean() < 1.0
+        # 1. the reported hit lies on the reported triangle: p = o + t d equals the barycentric point
+        f = F[h["prim"][hit]]
+        w = 1 - h["u"][hit] - h["v"][hit]
+        pb = V[f[:, 0]] * w[:, None] + V[f[:, 1]] * h["u"][hit][:, None] + V[f[:, 2]] * h["v"][hit][:, None]
+        pr = rays["o"][hit] + rays["d"][hit] * h["t"][hit][:, None]
+        assert np.abs(pb - pr).max() < 2e-5
+        assert (h["u"][hit] >= 0).all() and (h["v"][hit] >= 0).all() and (h["u"][hit] + h["v"][hit] <= 1 + 1e-6).all()
+        # 2. any-hit agrees with closest-hit existence
+        assert np.array_equal(sc.ray_intersect_any(rays).astype(bool), hit)
+        # 3. order independence: a permuted batch gives the permuted answers bit for bit
+        perm = np.random.default_rng(0).permutation(rays.shape[0])[:1 << 20]
+        hp = sc.ray_intersect(rays[perm])
+        assert np.array_equal(hp.view(np.uint32), h[perm].view(np.uint32))
+        # 4. two different trees (LBVH / PLOC) return the same hits (ties excepted)
+        h2 = sc2.ray_intersect(rays)
+        same = (h2["prim"] == h["prim"]) | (np.abs(h2["t"] - h["t"]) <= 1e-5 * np.maximum(h["t"], 1.1))
+        assert same.mean() >= 0.9999
+        # 5. shrinking maxt just below the hit turns it into a miss of that primitive; just above keeps it
+        sub = np.where(hit)[0][:1 << 18]
+        r2 = rays[sub].copy()
+        r2["maxt"] = h["t"][sub] * np.float32(1 + 1e-4)
+        assert np.array_equal(sc.ray_intersect(r2)["prim"], h["prim"][sub])
+        r2["maxt"] = h["t"][sub] * np.float32(1 - 1e-3)
+        assert (sc.ray_intersect(r2)["t"] < h["t"][sub]).sum() == 0
+    finally:
+        sc.close()
+        sc2.close()
+
+
+def test_against_live_reference(pkg, ctx, tmp_path):
+    """81 920-triangle displaced sphere, 262 144 rays per set, traced by the unmodified reference on this box's CPU
+    (oracle/_ref travels with the repo) and by the CUDA path."""
+    if not O.have_reference():
+        pytest.fail("oracle/_ref is missing: build it with `make -f oracle/Makefile.ref` before shipping to the GPU box")
+    S = pkg.scenes
+    V, N, F = S.displaced_sphere(6, seed=1)
+    sd = S.SceneDesc()
+    sd.add_mesh(V, N, F)
+    sd.add_point_light((0, 5, 0), (1, 1, 1))
+    xml = sd.to_xml(str(tmp_path), "s6")
+    n = 1 << 18
+    r0 = S.chord_rays(n, radius=1.1, seed=42, mint=0.0)
+    r1 = S.pinhole_rays(512, origin=(0, 0.3, -3.0))
+    sc = sd.upload(ctx)
+    try:
+        h1 = sc.ray_intersect_surface(r1)
+        r2 = S.shadow_rays(h1["p"][np.isfinite(h1["t"])], light_center=(0, 3.0, 0.5))
+        rays = np.concatenate([r0, r1, r2])
+        ref, timing = O.ref_trace(xml, rays, threads=os.cpu_count() or 1)
+        h = sc.ray_intersect_surface(rays)
+        ref_prim = ref[:, 4].copy().view(np.int32)
+        cos = np.abs((rays["d"] * ref[:, 8:11]).sum(axis=1))
+        st = helpers.compare_hits(rays, h["t"], h["prim"].view(np.int32), ref[:, 0], ref_prim, p=h["p"], ref_p=ref[:, 5:8], cos=cos)
+        print("live reference parity:", st, timing)
+        a = sc.ray_intersect_any(rays)
+        assert (a == ref[:, 14].copy().view(np.int32)).mean() >= 0.9999
+    finally:
+        sc.close()
