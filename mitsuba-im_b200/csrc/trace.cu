@@ -13,54 +13,60 @@ namespace mtsb {
 
 enum { MODE_CLOSEST = 0, MODE_ANY = 1, MODE_SURFACE = 2 };
 
+// Ray source / record sink of the batched C-ABI queries: AoS mtsb_ray in, mtsb_hit / byte / mtsb_surface out.
+template <int MODE>
+struct BatchIO {
+	SceneDev S;
+	const float4 *__restrict__ rays;
+	void *__restrict__ out;
+
+	__device__ __forceinline__ void write_miss(unsigned long long i) const {
+		if (MODE == MODE_ANY) ((uint8_t *) out)[i] = 0;
+		else if (MODE == MODE_CLOSEST) ((float4 *) out)[i] = make_float4(INFINITY, 0.0f, 0.0f, __uint_as_float(MTSB_NO_HIT));
+		else {
+			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
+			rec.t = INFINITY; rec.prim = MTSB_NO_HIT; rec.shape = MTSB_NO_HIT;
+			((mtsb_surface *) out)[i] = rec;
+		}
+	}
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+		const float4 r0 = __ldg(rays + 2 * i), r1 = __ldg(rays + 2 * i + 1);
+		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
+		if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, tmin, tmax)) return true;
+		write_miss(i);
+		return false;
+	}
+	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &hit, const V3 &o, const V3 &d) const {
+		if (!found) { write_miss(i); return; }
+		if (MODE == MODE_ANY) {
+			((uint8_t *) out)[i] = 1;
+		} else if (MODE == MODE_CLOSEST) {
+			const float4 c = __ldg(S.tris + (size_t) hit.slot * 3 + 2);
+			const uint32_t prim = S.shapes[__float_as_uint(c.z)].primOffset + __float_as_uint(c.w);
+			((float4 *) out)[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim));
+		} else {
+			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
+			Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
+			rec.t = hit.t; rec.u = hit.u; rec.v = hit.v;
+			rec.shape = sf.shape; rec.prim_local = sf.prim; rec.prim = S.shapes[sf.shape].primOffset + sf.prim;
+			rec.p[0] = sf.p.x; rec.p[1] = sf.p.y; rec.p[2] = sf.p.z;
+			rec.ng[0] = sf.ng.x; rec.ng[1] = sf.ng.y; rec.ng[2] = sf.ng.z;
+			rec.ns[0] = sf.ns.x; rec.ns[1] = sf.ns.y; rec.ns[2] = sf.ns.z;
+			rec.s[0] = sf.s.x; rec.s[1] = sf.s.y; rec.s[2] = sf.s.z;
+			rec.tt[0] = sf.t.x; rec.tt[1] = sf.t.y; rec.tt[2] = sf.t.z;
+			rec.uv[0] = sf.u; rec.uv[1] = sf.v;
+			((mtsb_surface *) out)[i] = rec;
+		}
+	}
+};
+
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
 trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, void *__restrict__ out,
 		unsigned long long *__restrict__ workCounter) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
-	const unsigned lane = threadIdx.x & 31;
-	while (true) {
-		unsigned long long base = 0;
-		if (lane == 0) base = atomicAdd(workCounter, 32ull);
-		base = __shfl_sync(0xffffffffu, base, 0);
-		if (base >= n) break;
-		const unsigned long long i = base + lane;
-		if (i < n) {
-			const float4 r0 = __ldg(rays + 2 * i), r1 = __ldg(rays + 2 * i + 1);
-			const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
-			float mint, maxt;
-			HitRec hit; hit.t = INFINITY; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
-			bool found = false;
-			if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, mint, maxt))
-				found = traverse<MODE == MODE_ANY, COUNT>(S, o, d, mint, maxt, hit, shStack + threadIdx.x, S.counters);
-			if (MODE == MODE_ANY) {
-				((uint8_t *) out)[i] = found ? 1 : 0;
-			} else if (MODE == MODE_CLOSEST) {
-				uint32_t prim = MTSB_NO_HIT;
-				if (found) {
-					const float4 c = __ldg(S.tris + (size_t) hit.slot * 3 + 2);
-					prim = S.shapes[__float_as_uint(c.z)].primOffset + __float_as_uint(c.w);
-				} else { hit.t = INFINITY; hit.u = hit.v = 0; }
-				((float4 *) out)[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim));
-			} else {
-				mtsb_surface rec;
-				memset(&rec, 0, sizeof(rec));
-				rec.t = INFINITY; rec.prim = MTSB_NO_HIT; rec.shape = MTSB_NO_HIT;
-				if (found) {
-					Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
-					rec.t = hit.t; rec.u = hit.u; rec.v = hit.v;
-					rec.shape = sf.shape; rec.prim_local = sf.prim; rec.prim = S.shapes[sf.shape].primOffset + sf.prim;
-					rec.p[0] = sf.p.x; rec.p[1] = sf.p.y; rec.p[2] = sf.p.z;
-					rec.ng[0] = sf.ng.x; rec.ng[1] = sf.ng.y; rec.ng[2] = sf.ng.z;
-					rec.ns[0] = sf.ns.x; rec.ns[1] = sf.ns.y; rec.ns[2] = sf.ns.z;
-					rec.s[0] = sf.s.x; rec.s[1] = sf.s.y; rec.s[2] = sf.s.z;
-					rec.tt[0] = sf.t.x; rec.tt[1] = sf.t.y; rec.tt[2] = sf.t.z;
-					rec.uv[0] = sf.u; rec.uv[1] = sf.v;
-				}
-				((mtsb_surface *) out)[i] = rec;
-			}
-		}
-	}
+	BatchIO<MODE> io; io.S = S; io.rays = rays; io.out = out;
+	trace_persistent<MODE == MODE_ANY, COUNT>(S, io, n, workCounter, shStack + threadIdx.x);
 	if (COUNT && threadIdx.x == 0 && blockIdx.x == 0 && S.counters) atomicAdd(S.counters + 2, n);
 }
 

@@ -128,70 +128,6 @@ struct TravStack {
 	}
 };
 
-// Closest (ANY=false) or any (ANY=true) hit of the segment [tmin, tmax] (inclusive, as the reference).
-// Returns true on a hit; for closest hits `hit` holds t,u,v and the TriAccel slot.
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ bool traverse(const SceneDev &S, const V3 &o, const V3 &d, float tmin, float tmax,
-		HitRec &hit, uint2 *shStack, unsigned long long *cnt) {
-	const float tiny = 1e-18f;
-	V3 idir;
-	idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-	idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-	idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
-	const uint32_t octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
-	const uint32_t octinv4 = octinv * 0x01010101u;
-
-	TravStack st; st.sh = shStack; st.n = 0;
-	uint2 ng = make_uint2(0u, 0x80000000u), tg = make_uint2(0u, 0u);
-	bool found = false;
-	hit.t = tmax; hit.slot = 0xffffffffu; hit.u = hit.v = 0;
-	unsigned nNodes = 0, nTris = 0;
-
-	while (true) {
-		if (ng.y > 0x00ffffffu) {
-			const uint32_t bit = 31u - __clz(ng.y);
-			const uint32_t imask = ng.y & 0xffu;
-			ng.y &= ~(1u << bit);
-			if (ng.y > 0x00ffffffu) st.push(ng);
-			const uint32_t slot = (bit - 24u) ^ octinv;
-			const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
-			const uint4 *np = S.nodes + (size_t) (ng.x + rel) * 5;
-			const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-			if (COUNT) ++nNodes;
-			const uint32_t hm = node_test(n0, n1, n2, n3, n4, o, idir, octinv4, tmin, hit.t);
-			ng = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
-			tg = make_uint2(n1.y, hm & 0x00ffffffu);
-		} else {
-			tg = ng; ng = make_uint2(0u, 0u);
-		}
-
-		while (tg.y) {
-			const uint32_t bit = __ffs(tg.y) - 1;
-			tg.y &= tg.y - 1;
-			const uint32_t slot = tg.x + bit;
-			const float4 *tp = S.tris + (size_t) slot * 3;
-			const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-			if (COUNT) ++nTris;
-			float t, u, v; bool h;
-			if (__float_as_uint(a.x) != K_NO_TRIANGLE)
-				h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
-			else
-				h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
-			if (h) {
-				if (ANY) { if (COUNT && cnt) { atomicAdd(cnt, nNodes); atomicAdd(cnt + 1, nTris); } return true; }
-				hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
-			}
-		}
-
-		if (ng.y <= 0x00ffffffu) {
-			if (st.n == 0) break;
-			ng = st.pop();
-		}
-	}
-	if (COUNT && cnt) { atomicAdd(cnt, (unsigned long long) nNodes); atomicAdd(cnt + 1, (unsigned long long) nTris); }
-	return found;
-}
-
 // The scene-AABB clip and adaptive epsilon that precede traversal in the three ShapeKDTree::rayIntersect
 // overloads (src/librender/skdtree.cpp:112-142, 207-226; AABB::rayIntersect include/mitsuba/core/aabb.h:308-338).
 // floorEps: the closest-hit overload floors the epsilon scale at Epsilon, the other two do not.
@@ -224,6 +160,117 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 	if (rayMinT > mint) mint = rayMinT;
 	if (rayMaxt < maxt) maxt = rayMaxt;
 	return maxt > mint;
+}
+
+// Persistent, warp-synchronous traversal of a whole ray batch.
+//
+// Every warp keeps 32 rays in flight.  Each loop iteration is warp-convergent (it starts with a full-mask
+// ballot): (1) lanes whose ray has finished have written their record; once MTSB_FETCH_MIN_IDLE lanes are idle the
+// warp pulls that many new rays from the global work counter with ONE atomic (lane 0) broadcast by shuffle, each
+// idle lane taking the slot given by its rank in the ballot; (2) every lane with a pending node group pops its
+// nearest child and tests the 8 quantised boxes; (3) lanes with leaf triangles test them; (4) lanes whose group is
+// exhausted pop the stack or finish.  ANY=false: closest hit (shrinks hit.t); ANY=true: first accepted hit ends the ray.
+//
+// IO supplies the rays and consumes the records:
+//   bool IO::load(i, o, d, tmin, tmax)   -> false if the ray needs no traversal (IO has already written a miss)
+//   void IO::store(i, found, hit, o, d)
+#ifndef MTSB_FETCH_MIN_IDLE
+#define MTSB_FETCH_MIN_IDLE 4
+#endif
+
+template <bool ANY, bool COUNT, class IO>
+__device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsigned long long n,
+		unsigned long long *__restrict__ workCounter, uint2 *shStack) {
+	const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+	const unsigned FULL = 0xffffffffu;
+	bool active = false, exhausted = false, found = false;
+	V3 o = v3(0.0f), d = v3(0.0f), idir = v3(0.0f);
+	float tmin = 0;
+	HitRec hit; hit.t = 0; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
+	uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+	uint32_t octinv = 0, octinv4 = 0;
+	unsigned long long idx = 0;
+	TravStack st; st.sh = shStack; st.n = 0;
+	unsigned nNodes = 0, nTris = 0;
+
+	for (;;) {
+		// ---- (1) refill idle lanes
+		const unsigned idleMask = __ballot_sync(FULL, !active);
+		const unsigned nIdle = __popc(idleMask);
+		if (!exhausted && nIdle >= MTSB_FETCH_MIN_IDLE) {
+			unsigned long long base = 0;
+			if (lane == 0) base = atomicAdd(workCounter, (unsigned long long) nIdle);
+			base = __shfl_sync(FULL, base, 0);
+			if (!active) {
+				idx = base + __popc(idleMask & ltMask);
+				if (idx < n) {
+					float tmax;
+					if (io.load(idx, o, d, tmin, tmax)) {
+						const float tiny = 1e-18f;
+						idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+						idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+						idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+						octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
+						octinv4 = octinv * 0x01010101u;
+						ng = make_uint2(0u, 0x80000000u); tg = make_uint2(0u, 0u);
+						hit.t = tmax; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
+						found = false; st.n = 0; active = true;
+					}
+				}
+			}
+			if (base + nIdle >= n) exhausted = true;
+		}
+		if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
+
+		// ---- (2) node phase
+		if (active) {
+			if (ng.y > 0x00ffffffu) {
+				const uint32_t bit = 31u - __clz(ng.y);
+				const uint32_t imask = ng.y & 0xffu;
+				ng.y &= ~(1u << bit);
+				if (ng.y > 0x00ffffffu) st.push(ng);
+				const uint32_t slot = (bit - 24u) ^ octinv;
+				const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+				const uint4 *np = S.nodes + (size_t) (ng.x + rel) * 5;
+				const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+				if (COUNT) ++nNodes;
+				const uint32_t hm = node_test(n0, n1, n2, n3, n4, o, idir, octinv4, tmin, hit.t);
+				ng = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
+				tg = make_uint2(n1.y, hm & 0x00ffffffu);
+			} else {
+				tg = ng; ng = make_uint2(0u, 0u);
+			}
+		}
+
+		// ---- (3) triangle phase
+		while (active && tg.y) {
+			const uint32_t bit = __ffs(tg.y) - 1;
+			tg.y &= tg.y - 1;
+			const uint32_t slot = tg.x + bit;
+			const float4 *tp = S.tris + (size_t) slot * 3;
+			const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+			if (COUNT) ++nTris;
+			float t, u, v; bool h;
+			if (__float_as_uint(a.x) != K_NO_TRIANGLE)
+				h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
+			else
+				h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
+			if (h) {
+				hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
+				if (ANY) { tg.y = 0; ng = make_uint2(0u, 0u); st.n = 0; }
+			}
+		}
+
+		// ---- (4) pop or finish
+		if (active && ng.y <= 0x00ffffffu) {
+			if (st.n == 0) { io.store(idx, found, hit, o, d); active = false; }
+			else ng = st.pop();
+		}
+	}
+	if (COUNT && S.counters) {
+		atomicAdd(S.counters, (unsigned long long) nNodes);
+		atomicAdd(S.counters + 1, (unsigned long long) nTris);
+	}
 }
 
 } // namespace mtsb
