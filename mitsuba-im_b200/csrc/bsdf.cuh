@@ -1,0 +1,166 @@
+// bsdf.cuh — the closed BSDF set, dispatched by tag.  Semantics of BSDF::eval / pdf / sample with the default
+// arguments MIPathTracer uses (measure = ESolidAngle, typeMask = EAll, component = -1, mode = ERadiance;
+// include/mitsuba/render/bsdf.h:215-445):
+//   eval   -> f * cos(theta_o)          pdf -> solid-angle density          sample -> f * cos / pdf, sets wo, eta, type
+//   diffuse        src/bsdfs/diffuse.cpp:112-153
+//   dielectric     src/bsdfs/dielectric.cpp:231-343
+//   plastic        src/bsdfs/plastic.cpp:248-455
+//   roughconductor src/bsdfs/roughconductor.cpp:260-413
+//   twosided       src/bsdfs/twosided.cpp:106-170 (same nested BRDF on both sides)
+//   null           the black diffuse BSDF Shape::configure gives emitters without one (src/librender/shape.cpp:48-58)
+#pragma once
+
+namespace mtsb {
+
+struct BsdfSample { V3 wo; float pdf, eta; uint32_t type; };
+
+__device__ inline uint32_t bsdf_type(const BsdfRec &b) {   // m_combinedType of each plugin
+	uint32_t t;
+	switch (b.type & 0xff) {
+		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: t = B_DIFFUSE_REFL | B_FRONT; break;
+		case MTSB_BSDF_DIELECTRIC: t = B_DELTA_REFL | B_DELTA_TRANS | B_FRONT | B_BACK; break;
+		case MTSB_BSDF_PLASTIC: t = B_DELTA_REFL | B_DIFFUSE_REFL | B_FRONT; break;
+		default: t = B_GLOSSY_REFL | B_FRONT; break;
+	}
+	if (b.type & MTSB_BSDF_TWOSIDED_FLAG) t |= B_BACK;
+	return t;
+}
+
+__device__ inline V3 plastic_diffuse(const BsdfRec &b) {
+	V3 diff = v3(b.p[1], b.p[2], b.p[3]);
+	const float fdrInt = b.p[7];
+	if (b.p[10] != 0) diff = diff / (v3(1.0f) - diff * fdrInt); else diff = diff / (1 - fdrInt);
+	return diff;
+}
+__device__ inline float plastic_prob_specular(const BsdfRec &b, float Fi) {
+	const float w = b.p[9];
+	return (Fi * w) / (Fi * w + (1 - Fi) * (1 - w));
+}
+
+// --- one-sided evaluation (wi, wo in the local shading frame) ---
+__device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
+	switch (b.type & 0xff) {
+		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: {
+			if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
+			return v3(b.p[0], b.p[1], b.p[2]) * (MTS_INV_PI * wo.z);
+		}
+		case MTSB_BSDF_DIELECTRIC: return v3(0.0f);     // discrete measure only
+		case MTSB_BSDF_PLASTIC: {
+			if (wo.z <= 0 || wi.z <= 0) return v3(0.0f);
+			const float eta = b.p[0];
+			const float Fi = fresnel_dielectric_ext(wi.z, eta), Fo = fresnel_dielectric_ext(wo.z, eta);
+			return plastic_diffuse(b) * ((MTS_INV_PI * wo.z) * (1 / (eta * eta)) * (1 - Fi) * (1 - Fo));
+		}
+		default: {
+			if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
+			const V3 H = normalize(wo + wi);
+			Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+			const float D = distr.eval(H);
+			if (D == 0) return v3(0.0f);
+			const V3 F = fresnel_conductor_exact(dot(wi, H), v3(b.p[2], b.p[3], b.p[4]), v3(b.p[5], b.p[6], b.p[7])) * v3(b.p[8], b.p[9], b.p[10]);
+			const float G = distr.G(wi, wo, H);
+			return F * (D * G / (4.0f * wi.z));
+		}
+	}
+}
+
+__device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
+	switch (b.type & 0xff) {
+		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL:
+			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+			return MTS_INV_PI * wo.z;
+		case MTSB_BSDF_DIELECTRIC: return 0.0f;
+		case MTSB_BSDF_PLASTIC: {
+			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
+			const float Fi = fresnel_dielectric_ext(wi.z, b.p[0]);
+			return MTS_INV_PI * wo.z * (1 - plastic_prob_specular(b, Fi));
+		}
+		default: {
+			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+			const V3 H = normalize(wo + wi);
+			Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+			if (distr.sampleVisible) return distr.eval(H) * distr.smithG1(wi, H) / (4.0f * wi.z);
+			return distr.pdf(wi, H) / (4 * fabsf(dot(wo, H)));
+		}
+	}
+}
+
+// returns the importance weight (f cos / pdf); zero weight = failed sample
+__device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, float sy, BsdfSample &out) {
+	out.pdf = 0; out.eta = 1.0f; out.type = 0; out.wo = v3(0.0f);
+	switch (b.type & 0xff) {
+		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: {
+			if (wi.z <= 0) return v3(0.0f);
+			out.wo = square_to_cosine_hemisphere(sx, sy);
+			out.type = B_DIFFUSE_REFL;
+			out.pdf = MTS_INV_PI * out.wo.z;
+			return v3(b.p[0], b.p[1], b.p[2]);
+		}
+		case MTSB_BSDF_DIELECTRIC: {
+			const float eta = b.p[0], invEta = 1 / eta;
+			float cosThetaT;
+			const float F = fresnel_dielectric_ext(wi.z, cosThetaT, eta);
+			if (sx <= F) {
+				out.type = B_DELTA_REFL; out.wo = v3(-wi.x, -wi.y, wi.z); out.pdf = F;
+				return v3(b.p[1], b.p[2], b.p[3]);
+			}
+			out.type = B_DELTA_TRANS;
+			const float scale = -(cosThetaT < 0 ? invEta : eta);
+			out.wo = v3(scale * wi.x, scale * wi.y, cosThetaT);
+			out.eta = cosThetaT < 0 ? eta : invEta;
+			out.pdf = 1 - F;
+			const float factor = cosThetaT < 0 ? invEta : eta;
+			return v3(b.p[4], b.p[5], b.p[6]) * (factor * factor);
+		}
+		case MTSB_BSDF_PLASTIC: {
+			if (wi.z <= 0) return v3(0.0f);
+			const float eta = b.p[0];
+			const float Fi = fresnel_dielectric_ext(wi.z, eta);
+			const float probSpecular = plastic_prob_specular(b, Fi);
+			if (sx < probSpecular) {
+				out.type = B_DELTA_REFL; out.wo = v3(-wi.x, -wi.y, wi.z); out.pdf = probSpecular;
+				return v3(b.p[4], b.p[5], b.p[6]) * Fi / probSpecular;
+			}
+			out.type = B_DIFFUSE_REFL;
+			out.wo = square_to_cosine_hemisphere((sx - probSpecular) / (1 - probSpecular), sy);
+			const float Fo = fresnel_dielectric_ext(out.wo.z, eta);
+			out.pdf = (1 - probSpecular) * (MTS_INV_PI * out.wo.z);
+			return plastic_diffuse(b) * ((1 / (eta * eta)) * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
+		}
+		default: {
+			if (wi.z < 0) return v3(0.0f);
+			Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+			float pdf;
+			const V3 m = distr.sample(wi, sx, sy, pdf);
+			if (pdf == 0) return v3(0.0f);
+			out.wo = 2 * dot(wi, m) * m - wi;
+			out.type = B_GLOSSY_REFL;
+			if (out.wo.z <= 0) return v3(0.0f);
+			const V3 F = fresnel_conductor_exact(dot(wi, m), v3(b.p[2], b.p[3], b.p[4]), v3(b.p[5], b.p[6], b.p[7])) * v3(b.p[8], b.p[9], b.p[10]);
+			float weight;
+			if (distr.sampleVisible) weight = distr.smithG1(out.wo, m);
+			else weight = distr.eval(m) * distr.G(wi, out.wo, m) * dot(wi, m) / (pdf * wi.z);
+			out.pdf = pdf / (4.0f * dot(out.wo, m));
+			return F * weight;
+		}
+	}
+}
+
+// --- public entry points: add the twosided adapter ---
+__device__ inline V3 bsdf_eval(const BsdfRec &b, V3 wi, V3 wo) {
+	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && !(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; }
+	return bsdf_eval_1(b, wi, wo);
+}
+__device__ inline float bsdf_pdf(const BsdfRec &b, V3 wi, V3 wo) {
+	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && !(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; }
+	return bsdf_pdf_1(b, wi, wo);
+}
+__device__ inline V3 bsdf_sample(const BsdfRec &b, V3 wi, float sx, float sy, BsdfSample &out) {
+	bool flipped = false;
+	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && wi.z < 0) { wi.z = -wi.z; flipped = true; }
+	const V3 w = bsdf_sample_1(b, wi, sx, sy, out);
+	if (flipped && !is_zero(w) && out.pdf != 0) out.wo.z = -out.wo.z;
+	return w;
+}
+
+} // namespace mtsb

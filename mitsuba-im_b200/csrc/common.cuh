@@ -83,7 +83,7 @@ struct EmitterRec {
 	V3 radiance; V3 pos;
 	V3 sphereCenter; float sphereRadius;   // constant env: scene bounding sphere (constant.cpp:69-94)
 	float invSurfaceArea;                  // area
-	uint32_t pad;
+	float samplingWeight;                  // Emitter::m_samplingWeight
 };
 
 struct BsdfRec { int32_t type; float p[15]; };

@@ -1,0 +1,165 @@
+// emitter.cuh — direct-illumination sampling for the emitter subset.
+//   Scene::sampleEmitterDirect / pdfEmitterDirect   src/librender/scene.cpp:860-884, 981-984 (without the shadow ray)
+//   DiscreteDistribution::sampleReuse                 include/mitsuba/core/pmf.h:124-188
+//   AreaLight::{eval,sampleDirect,pdfDirect}          src/emitters/area.cpp:106-111,160-184
+//   Shape::sampleDirect / pdfDirect                   src/librender/shape.cpp:102-126
+//   TriMesh::samplePosition, Triangle::sample         src/librender/trimesh.cpp:413-425, src/libcore/triangle.cpp:24-60
+//   Rectangle::samplePosition                         src/shapes/rectangle.cpp:210-216
+//   PointEmitter::{sampleDirect,pdfDirect}            src/emitters/point.cpp:133-153
+//   ConstantBackgroundEmitter::{sampleDirect,pdfDirect,fillDirectSamplingRecord}  src/emitters/constant.cpp:175-256
+#pragma once
+
+namespace mtsb {
+
+struct DirectSample {
+	V3 value;        // radiance / pdf (already divided by the emitter selection probability)
+	V3 d, n;         // direction ref -> emitter, emitter normal
+	float dist, pdf;
+	int measure, emitter;
+};
+
+// DiscreteDistribution::sample on a normalised cdf with count+1 entries (pmf.h:124-136)
+__device__ inline uint32_t cdf_sample(const float *cdf, uint32_t count, float value) {
+	uint32_t lo = 0, hi = count + 1;            // std::lower_bound over [0, count+1)
+	while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (cdf[mid] < value) lo = mid + 1; else hi = mid; }
+	long idx = (long) lo - 1;
+	if (idx < 0) idx = 0;
+	if (idx > (long) count - 1) idx = (long) count - 1;
+	uint32_t index = (uint32_t) idx;
+	while (cdf[index + 1] - cdf[index] == 0 && index < count) ++index;
+	return index;
+}
+__device__ inline uint32_t cdf_sample_reuse(const float *cdf, uint32_t count, float &value, float &pdf) {
+	const uint32_t index = cdf_sample(cdf, count, value);
+	pdf = cdf[index + 1] - cdf[index];
+	value = (value - cdf[index]) / (cdf[index + 1] - cdf[index]);
+	return index;
+}
+
+__device__ inline bool sphere_intersect(const V3 &center, float radius, const V3 &ro, const V3 &rd, float &nearT, float &farT) {
+	const V3 o = ro - center;                     // BSphere::rayIntersect + solveQuadratic (util.cpp:449-487)
+	const float A = dot(rd, rd), Bq = 2 * dot(o, rd), C = dot(o, o) - radius * radius;
+	if (A == 0) { if (Bq != 0) { nearT = farT = -C / Bq; return true; } return false; }
+	const float discrim = Bq * Bq - 4.0f * A * C;
+	if (discrim < 0) return false;
+	const float sq = sqrtf(discrim);
+	const float temp = Bq < 0 ? -0.5f * (Bq - sq) : -0.5f * (Bq + sq);
+	float x0 = temp / A, x1 = C / temp;
+	if (x0 > x1) { const float t = x0; x0 = x1; x1 = t; }
+	nearT = x0; farT = x1;
+	return true;
+}
+
+// Shape::samplePosition for the shape an area light is attached to
+__device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeIdx, float sx, float sy, V3 &p, V3 &n, float &pdf) {
+	const ShapeRec sh = S.shapes[shapeIdx];
+	if (sh.type == SHAPE_RECT) {
+		const RectRec &r = S.rects[sh.rect];
+		const float x = sx * 2 - 1, y = sy * 2 - 1;
+		const float *m = r.toWorld;
+		p = v3(m[0] * x + m[1] * y + m[3], m[4] * x + m[5] * y + m[7], m[8] * x + m[9] * y + m[11]);
+		n = r.n; pdf = r.invSurfaceArea;
+		return;
+	}
+	const float *cdf = S.triAreaCdf + S.triAreaCdfOffset[shapeIdx];
+	float dummy;
+	const uint32_t tri = cdf_sample_reuse(cdf, sh.primCount, sy, dummy);
+	const uint32_t *ix = S.indices + (size_t) (sh.triBase + tri) * 3;
+	const uint32_t i0 = sh.vtxBase + ix[0], i1 = sh.vtxBase + ix[1], i2 = sh.vtxBase + ix[2];
+	const float *P = S.positions;
+	const V3 p0 = v3(P[i0*3], P[i0*3+1], P[i0*3+2]), p1 = v3(P[i1*3], P[i1*3+1], P[i1*3+2]), p2 = v3(P[i2*3], P[i2*3+1], P[i2*3+2]);
+	float bx, by; square_to_uniform_triangle(sx, sy, bx, by);
+	const V3 sideA = p1 - p0, sideB = p2 - p0;
+	p = p0 + sideA * bx + sideB * by;
+	if (sh.flags & SHAPE_HAS_NORMALS) {
+		const float *N = S.normals;
+		const V3 n0 = v3(N[i0*3], N[i0*3+1], N[i0*3+2]), n1 = v3(N[i1*3], N[i1*3+1], N[i1*3+2]), n2 = v3(N[i2*3], N[i2*3+1], N[i2*3+2]);
+		n = normalize(n0 * (1.0f - bx - by) + n1 * bx + n2 * by);
+	} else {
+		n = normalize(cross(sideA, sideB));
+	}
+	pdf = sh.invArea;
+}
+
+// Emitter::sampleDirect for emitter `e`
+__device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
+	const EmitterRec &em = S.emitters[e];
+	out.emitter = (int) e; out.pdf = 0; out.n = v3(0.0f); out.d = v3(0.0f); out.dist = 0; out.measure = M_SOLID_ANGLE;
+	if (em.type == MTSB_EMITTER_AREA) {
+		V3 p; float pdf;
+		shape_sample_position(S, em.shape, sx, sy, p, out.n, pdf);
+		V3 d = p - ref;
+		const float distSquared = dot(d, d);
+		out.dist = sqrtf(distSquared);
+		d /= out.dist;
+		const float dp = fabsf(dot(d, out.n));
+		pdf *= dp != 0 ? (distSquared / dp) : 0.0f;
+		out.d = d; out.pdf = pdf;
+		if (dot(d, refN) >= 0 && dot(d, out.n) < 0 && pdf != 0) return em.radiance / pdf;
+		out.pdf = 0.0f;
+		return v3(0.0f);
+	} else if (em.type == MTSB_EMITTER_POINT) {
+		V3 d = em.pos - ref;
+		out.dist = length(d);
+		const float invDist = 1.0f / out.dist;
+		out.d = d * invDist; out.pdf = 1; out.measure = M_DISCRETE;
+		return em.radiance * (invDist * invDist);
+	} else {
+		V3 d; float pdf;
+		if (!is_zero(refN)) {
+			const V3 l = square_to_cosine_hemisphere(sx, sy);
+			pdf = MTS_INV_PI * l.z;
+			V3 s, t; coordinate_system(refN, s, t);
+			d = s * l.x + t * l.y + refN * l.z;
+		} else {
+			d = square_to_uniform_sphere(sx, sy);
+			pdf = 1.0f / (4.0f * MTS_PI);
+		}
+		float nearT, farT;
+		if (!sphere_intersect(em.sphereCenter, em.sphereRadius, ref, d, nearT, farT)) return v3(0.0f);
+		if (!(nearT < 0 && farT > 0)) return v3(0.0f);
+		const V3 p = ref + d * farT;
+		out.n = normalize(em.sphereCenter - p);
+		out.d = d; out.dist = farT; out.pdf = pdf;
+		if (!is_zero(refN) && dot(d, refN) <= 0) return v3(0.0f);
+		return em.radiance / pdf;
+	}
+}
+
+// Emitter::pdfDirect for a direction that hit emitter `e` (d, dist, n of the hit; measure = solid angle)
+__device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const V3 &refN, const V3 &d, float dist, const V3 &n, int measure) {
+	const EmitterRec &em = S.emitters[e];
+	if (em.type == MTSB_EMITTER_AREA) {
+		if (dot(d, refN) >= 0 && dot(d, n) < 0) {
+			if (measure == M_SOLID_ANGLE) return em.invSurfaceArea * (dist * dist) / fabsf(dot(d, n));
+			if (measure == M_AREA) return em.invSurfaceArea;
+		}
+		return 0.0f;
+	} else if (em.type == MTSB_EMITTER_POINT) {
+		return measure == M_DISCRETE ? 1.0f : 0.0f;
+	} else {
+		const float pdfSA = !is_zero(refN) ? MTS_INV_PI * fmaxf(0.0f, dot(d, refN)) : 1.0f / (4.0f * MTS_PI);
+		if (measure == M_SOLID_ANGLE) return pdfSA;
+		if (measure == M_AREA) return pdfSA * fabsf(dot(d, n)) / (dist * dist);
+		return 0.0f;
+	}
+}
+
+// Scene::pdfEmitterDiscrete (include/mitsuba/render/scene.h): samplingWeight * m_emitterPDF.getNormalization()
+__device__ inline float emitter_pdf_discrete(const SceneDev &S, uint32_t e) { return S.emitters[e].samplingWeight * S.emitterNorm; }
+
+// Scene::sampleEmitterDirect(dRec, sample, testVisibility = false)
+__device__ inline V3 scene_sample_emitter_direct(const SceneDev &S, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
+	float emPdf;
+	const uint32_t index = cdf_sample_reuse(S.emitterCdf, S.emitterCount, sx, emPdf);
+	V3 value = emitter_sample_direct(S, index, ref, refN, sx, sy, out);
+	if (out.pdf != 0) { out.pdf *= emPdf; return value / emPdf; }
+	return v3(0.0f);
+}
+
+// Emitter::eval(its, d) for an area light hit from direction -d (area.cpp:106-111)
+__device__ inline V3 area_emitter_eval(const SceneDev &S, uint32_t e, const V3 &ns, const V3 &d) {
+	return dot(ns, d) <= 0 ? v3(0.0f) : S.emitters[e].radiance;
+}
+
+} // namespace mtsb

@@ -1,0 +1,156 @@
+// render.cu — wavefront path tracer: generate -> (extend -> shade -> connect)* -> splat.
+//
+// Replaces, for the GPU plugin subset, the per-sample loop of SamplingIntegrator::renderBlock
+// (src/librender/integrator.cpp:141-189), PerspectiveCameraImpl::sampleRayDifferential
+// (src/sensors/perspective.cpp:271-298), MIPathTracer::Li (src/integrators/path/path.cpp:119-294),
+// MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309, via the same kernels with maxDepth = 2) and
+// ImageBlock::put (include/mitsuba/render/imageblock.h:161-221).
+//
+// One loop iteration of Li is split at its ray cast: `shade` runs the tail of iteration k-1 (emitter hit by the BSDF
+// sample + MIS, Russian roulette) followed by the head of iteration k (emitted radiance, emitter sampling, BSDF
+// sampling).  Random numbers are consumed in the reference's order from a counter-based stream, so a path sees the
+// same numbers as MIPathTracer does under oracle/ctrsampler.cpp.
+#include "render.cuh"
+#include "shading.cuh"
+#include <algorithm>
+#include <string.h>
+
+namespace mtsb {
+
+#define RENDER_BLOCK 128
+#define INVALID_SLOT 0xffffffffu
+
+// warp-aggregated append: one atomic per warp, ranks from the active mask
+__device__ __forceinline__ uint32_t warp_append(uint32_t *counter) {
+	const unsigned m = __activemask();
+	const unsigned lane = threadIdx.x & 31u;
+	const int leader = __ffs(m) - 1;
+	uint32_t base = 0;
+	if ((int) lane == leader) base = atomicAdd(counter, (uint32_t) __popc(m));
+	base = __shfl_sync(m, base, leader);
+	return base + __popc(m & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ V3 xform_affine_point(const float *m, const V3 &p) {
+	return v3(m[0]*p.x + m[1]*p.y + m[2]*p.z + m[3], m[4]*p.x + m[5]*p.y + m[6]*p.z + m[7], m[8]*p.x + m[9]*p.y + m[10]*p.z + m[11]);
+}
+__device__ __forceinline__ V3 xform_vector(const float *m, const V3 &v) {
+	return v3(m[0]*v.x + m[1]*v.y + m[2]*v.z, m[4]*v.x + m[5]*v.y + m[6]*v.z, m[8]*v.x + m[9]*v.y + m[10]*v.z);
+}
+__device__ __forceinline__ V3 xform_projective_point(const float *m, const V3 &p) {   // Transform::operator()(Point)
+	const float x = m[0]*p.x + m[1]*p.y + m[2]*p.z + m[3], y = m[4]*p.x + m[5]*p.y + m[6]*p.z + m[7];
+	const float z = m[8]*p.x + m[9]*p.y + m[10]*p.z + m[11], w = m[12]*p.x + m[13]*p.y + m[14]*p.z + m[15];
+	if (w == 1.0f) return v3(x, y, z);
+	return v3(x, y, z) / w;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// generate: sample position + sensor ray for every path of the chunk
+// ---------------------------------------------------------------------------------------------------
+struct GenParams {
+	uint32_t count;            // path slots in this chunk (padded to whole 8x4 pixel tiles)
+	unsigned long long first;  // index of the chunk's first path within the pass
+	int x0, y0, w, h;          // pixel rectangle, relative to the crop window
+	uint32_t tilesX, pixPadded;
+	uint32_t sppBegin, sppStride, sppPhase, seed;
+	const uint32_t *samples;   // explicit {px,py,sampleIndex,0} list (mtsb_render_samples) or NULL
+};
+
+__global__ void __launch_bounds__(RENDER_BLOCK)
+generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= g.count) return;
+	uint32_t px, py, sidx;
+	bool valid = true;
+	if (g.samples) {
+		px = g.samples[4 * j]; py = g.samples[4 * j + 1]; sidx = g.samples[4 * j + 2];
+	} else {
+		const unsigned long long gi = g.first + j;
+		const uint32_t k = (uint32_t) (gi / g.pixPadded), q = (uint32_t) (gi % g.pixPadded);
+		const uint32_t tile = q >> 5, within = q & 31u;
+		const uint32_t lx = (tile % g.tilesX) * 8 + (within & 7u), ly = (tile / g.tilesX) * 4 + (within >> 3);
+		valid = lx < (uint32_t) g.w && ly < (uint32_t) g.h;
+		px = g.x0 + lx; py = g.y0 + ly;
+		sidx = g.sppBegin + g.sppPhase + k * g.sppStride;
+	}
+	if (!valid) { ps.rng[j] = make_uint4(INVALID_SLOT, 0, 0, 0); return; }
+	SamplerState rs; rs.px = px; rs.py = py; rs.sample = sidx; rs.dim = 0; rs.seed = g.seed;
+	float u1, u2; next2D(rs, u1, u2);
+	const float sx = (float) px + u1, sy = (float) py + u2;            // samplePos (integrator.cpp:172)
+	const V3 nearP = xform_projective_point(cam.s2c, v3(sx * cam.invResX, sy * cam.invResY, 0.0f));
+	const V3 d = normalize(nearP);
+	const float invZ = 1.0f / d.z;
+	const V3 o = v3(cam.c2w[3], cam.c2w[7], cam.c2w[11]);
+	const V3 dw = xform_vector(cam.c2w, d);
+	ps.rayO[j] = make_float4(o.x, o.y, o.z, cam.nearClip * invZ);
+	ps.rayD[j] = make_float4(dw.x, dw.y, dw.z, cam.farClip * invZ);
+	ps.thr[j] = make_float4(1, 1, 1, 1);
+	ps.L[j] = make_float4(0, 0, 0, 0);
+	ps.prev[j] = make_float4(0, 0, 0, 0);
+	ps.misc[j] = make_float4(sx, sy, __uint_as_float(0u), __uint_as_float(1u));   // flags = 0, depth = 1
+	ps.rng[j] = make_uint4(px, py, sidx, rs.dim);
+	queue[warp_append(ps.counters + 0)] = j;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// extend / connect: persistent traversal over the queues
+// ---------------------------------------------------------------------------------------------------
+struct ExtendIO {
+	SceneDev S; PathState ps; const uint32_t *queue;
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+		const uint32_t slot = queue[i];
+		const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot];
+		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
+		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax)) return true;
+		ps.hit[slot] = make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
+		return false;
+	}
+	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &hit, const V3 &, const V3 &) const {
+		const uint32_t slot = queue[i];
+		ps.hit[slot] = found ? make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot))
+		                     : make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
+	}
+};
+
+struct ConnectIO {
+	SceneDev S; PathState ps;
+	__device__ __forceinline__ void add(unsigned long long i) const {
+		const float4 c = ps.shL[i];
+		const uint32_t slot = __float_as_uint(c.w);
+		float4 L = ps.L[slot];
+		L.x += c.x; L.y += c.y; L.z += c.z;
+		ps.L[slot] = L;
+	}
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+		const float4 r0 = ps.shO[i], r1 = ps.shD[i];
+		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
+		if (clip_ray(S, o, d, r0.w, r1.w, false, tmin, tmax)) return true;
+		add(i);                 // nothing can occlude a segment outside the scene box
+		return false;
+	}
+	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &, const V3 &, const V3 &) const {
+		if (!found) add(i);
+	}
+};
+
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *count) {
+	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
+	ExtendIO io; io.S = S; io.ps = ps; io.queue = queue;
+	const unsigned long long n = *count;
+	trace_persistent<false, false>(S, io, n, ps.work + 0, shStack + threadIdx.x);
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
+}
+
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+connect_kernel(SceneDev S, PathState ps, const uint32_t *count) {
+	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
+	ConnectIO io; io.S = S; io.ps = ps;
+	const unsigned long long n = *count;
+	trace_persistent<true, false>(S, io, n, ps.work + 1, shStack + threadIdx.x);
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 2, n);
+}
+
+} // namespace mtsb
+#include "render_shade.cuh"
+#include "render_host.cuh"

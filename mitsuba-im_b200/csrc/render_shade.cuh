@@ -1,0 +1,222 @@
+// render_shade.cuh — the shade and splat kernels (included by render.cu).
+#pragma once
+
+namespace mtsb {
+
+__device__ __forceinline__ float mi_weight(float pdfA, float pdfB) {   // path.cpp:296-300 (power heuristic)
+	pdfA *= pdfA; pdfB *= pdfB;
+	return pdfA / (pdfA + pdfB);
+}
+
+// One thread per live path.  Line references are to src/integrators/path/path.cpp.
+__global__ void __launch_bounds__(RENDER_BLOCK)
+shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const uint32_t *queueIn, uint32_t *queueOut,
+		const uint32_t *countIn, uint32_t *countOut, uint32_t *countShadow) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= *countIn) return;
+	const uint32_t slot = queueIn[i];
+	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
+	float4 thr4 = ps.thr[slot], L4 = ps.L[slot], prev = ps.prev[slot], misc = ps.misc[slot];
+	const uint4 rg = ps.rng[slot];
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = rg.w; rs.seed = seed;
+	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
+	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(L4.x, L4.y, L4.z);
+	float eta = thr4.w;
+	uint32_t flags = __float_as_uint(misc.z), depth = __float_as_uint(misc.w);
+	const uint32_t hitSlot = __float_as_uint(h.w);
+	const bool valid = hitSlot != INVALID_SLOT;
+	bool alive = true;
+
+	Surf sf;
+	int emitterId = -1, bsdfId = 0;
+	if (valid) {
+		fill_surface(S, hitSlot, h.x, h.y, h.z, o, d, sf);
+		emitterId = S.shapes[sf.shape].emitter; bsdfId = S.shapes[sf.shape].bsdf;
+	}
+
+	if (flags & PF_FROM_BSDF) {
+		// ---- tail of the previous iteration (:224-286): the BSDF sample's ray has been traced
+		const V3 refN = v3(prev.x, prev.y, prev.z);
+		const float bsdfPdf = prev.w;
+		bool hitEmitter = false; V3 value = v3(0.0f); float lumPdf = 0;
+		if (valid) {
+			if (emitterId >= 0) {
+				value = area_emitter_eval(S, emitterId, sf.ns, -d);
+				hitEmitter = true;
+				if (!(flags & PF_DELTA))
+					lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, emitterId);
+			}
+		} else if (S.envEmitter >= 0) {
+			if (integ.hideEmitters && !(flags & PF_SCATTERED)) alive = false;
+			else {
+				const EmitterRec &env = S.emitters[S.envEmitter];
+				value = env.radiance;
+				float nearT, farT;       // fillDirectSamplingRecord (constant.cpp:238-256)
+				if (!sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) || nearT > 0 || farT < 0) alive = false;
+				else {
+					hitEmitter = true;
+					if (!(flags & PF_DELTA)) {
+						const V3 n = normalize(env.sphereCenter - (o + d * farT));
+						lumPdf = emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
+					}
+				}
+			}
+		} else alive = false;
+		if (alive && hitEmitter) Li += thr * value * mi_weight(bsdfPdf, lumPdf);
+		if (!valid) alive = false;                      // :262 "if (!its.isValid() ...) break"
+		if (alive) {
+			if (depth++ >= (uint32_t) integ.rrDepth) {     // :266-286 Russian roulette
+				const float q = fminf(vmax(thr) * eta * eta, 0.95f);
+				if (next1D(rs) >= q) alive = false;
+				else thr /= q;
+			}
+		}
+		if (alive && !((int) depth <= integ.maxDepth || integ.maxDepth < 0)) alive = false;   // while condition (:135)
+	} else {
+		// ---- first iteration: the sensor ray (:129-150)
+		L4.w = valid ? 1.0f : 0.0f;                     // RadianceQueryRecord::rayIntersect sets alpha
+		if (!valid) {
+			if (!integ.hideEmitters && S.envEmitter >= 0) Li += thr * S.emitters[S.envEmitter].radiance;
+			alive = false;
+		} else if (emitterId >= 0 && !integ.hideEmitters) {
+			Li += thr * area_emitter_eval(S, emitterId, sf.ns, -d);
+		}
+	}
+
+	bool shadow = false;
+	float4 shO = make_float4(0, 0, 0, 0), shD = shO, shL = shO;
+	if (alive) {
+		const V3 wi = to_local(sf, -d);
+		// :155-164
+		if (((int) depth >= integ.maxDepth && integ.maxDepth > 0) || (integ.strictNormals && dot(d, sf.ng) * wi.z >= 0)) alive = false;
+		if (alive) {
+			const BsdfRec bsdf = S.bsdfs[bsdfId];
+			const uint32_t btype = bsdf_type(bsdf);
+			const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);   // DirectSamplingRecord(its), records.inl:160-164
+			// ---- emitter sampling (:171-199)
+			if ((btype & B_SMOOTH) && S.emitterCount > 0) {
+				float sx, sy; next2D(rs, sx, sy);
+				DirectSample ds;
+				const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
+				if (!is_zero(value)) {
+					const V3 wo = to_local(sf, ds.d);
+					const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
+					if (!is_zero(bsdfVal) && (!integ.strictNormals || dot(sf.ng, ds.d) * wo.z > 0)) {
+						// Emitter::isOnSurface(): area (area.cpp:72) and constant environment (constant.cpp:50) set EOnSurface, point does not
+						const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
+						const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf(bsdf, wi, wo) : 0;
+						const V3 c = thr * value * bsdfVal * mi_weight(ds.pdf, bp);
+						shadow = true;      // visibility test of Scene::sampleEmitterDirect (scene.cpp:871-876), deferred to `connect`
+						shO = make_float4(sf.p.x, sf.p.y, sf.p.z, MTS_EPSILON);
+						shD = make_float4(ds.d.x, ds.d.y, ds.d.z, ds.dist * (1 - MTS_SHADOW_EPSILON));
+						shL = make_float4(c.x, c.y, c.z, __uint_as_float(slot));
+					}
+				}
+			}
+			// ---- BSDF sampling (:205-222)
+			float sx, sy; next2D(rs, sx, sy);
+			BsdfSample bs;
+			const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, bs);
+			if (is_zero(bsdfWeight)) alive = false;
+			else {
+				flags |= PF_SCATTERED;
+				const V3 wo = to_world(sf, bs.wo);
+				if (integ.strictNormals && dot(sf.ng, wo) * bs.wo.z <= 0) alive = false;
+				else {
+					ps.rayO[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, MTS_EPSILON);
+					ps.rayD[slot] = make_float4(wo.x, wo.y, wo.z, INFINITY);
+					thr *= bsdfWeight; eta *= bs.eta;           // :252-253 (applied before the trace; unused if the path ends)
+					flags |= PF_FROM_BSDF;
+					if (bs.type & B_DELTA) flags |= PF_DELTA; else flags &= ~PF_DELTA;
+					ps.prev[slot] = make_float4(refN.x, refN.y, refN.z, bs.pdf);
+				}
+			}
+		}
+	}
+
+	ps.L[slot] = make_float4(Li.x, Li.y, Li.z, L4.w);
+	ps.misc[slot] = make_float4(misc.x, misc.y, __uint_as_float(flags), __uint_as_float(depth));
+	if (alive) {
+		ps.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
+		ps.rng[slot] = make_uint4(rg.x, rg.y, rg.z, rs.dim);
+		queueOut[warp_append(countOut)] = slot;
+	}
+	if (shadow) {
+		const uint32_t k = warp_append(countShadow);
+		ps.shO[k] = shO; ps.shD[k] = shD; ps.shL[k] = shL;
+	}
+}
+
+// ImageBlock::put (imageblock.h:161-221) with atomics (the Integrator2 path uses putAtomic, :223-318).
+__global__ void __launch_bounds__(RENDER_BLOCK)
+splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned depth = 0, one = 0;
+	if (j < count && ps.rng[j].x != INVALID_SLOT) {
+		one = 1;
+		const float4 L = ps.L[j], misc = ps.misc[j];
+		depth = __float_as_uint(misc.w);
+		if (samplesOut) {
+			((float4 *) samplesOut)[j] = L;
+		} else {
+			const float value[5] = { L.x, L.y, L.z, L.w, 1.0f };
+			bool ok = true;
+			for (int c = 0; c < film.channels; ++c) if (!isfinite(value[c]) || value[c] < 0) ok = false;
+			if (ok) {
+				const int sizeX = film.width + 2 * film.border, sizeY = film.height + 2 * film.border;
+				const float px = misc.x - 0.5f - (float) (film.offX - film.border), py = misc.y - 0.5f - (float) (film.offY - film.border);
+				const int x0 = max((int) ceilf(px - film.radius), 0), y0 = max((int) ceilf(py - film.radius), 0);
+				const int x1 = min((int) floorf(px + film.radius), sizeX - 1), y1 = min((int) floorf(py + film.radius), sizeY - 1);
+				for (int y = y0; y <= y1; ++y) {
+					const float wy = film.table[min((int) fabsf((y - py) * film.scale), 31)];
+					for (int x = x0; x <= x1; ++x) {
+						const float w = film.table[min((int) fabsf((x - px) * film.scale), 31)] * wy;
+						float *dest = film.data + ((size_t) y * sizeX + x) * film.channels;
+						for (int c = 0; c < film.channels; ++c) atomicAdd(dest + c, w * value[c]);
+					}
+				}
+			}
+		}
+	}
+	// avgPathLength += rRec.depth (path.cpp:290-291)
+	unsigned sum = depth;
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); one += __shfl_xor_sync(0xffffffffu, one, o); }
+	if ((threadIdx.x & 31) == 0 && one) { atomicAdd(ps.stats + 3, (unsigned long long) sum); atomicAdd(ps.stats + 0, (unsigned long long) one); }
+}
+
+__global__ void prep_kernel(PathState ps, uint32_t *countOut, uint32_t *countShadow) {
+	ps.work[0] = 0; ps.work[1] = 0;
+	if (countOut) *countOut = 0;
+	if (countShadow) *countShadow = 0;
+}
+
+// ---- pointwise plugin math for parity tests (mtsb_eval_bsdf / mtsb_eval_emitter) ----
+__global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, size_t n, float *out) {
+	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const BsdfRec b = S.bsdfs[bsdfId];
+	const float *r = in + i * 8; float *o = out + i * 16;
+	const V3 wi = v3(r[0], r[1], r[2]), wo = v3(r[3], r[4], r[5]);
+	const V3 f = bsdf_eval(b, wi, wo);
+	o[0] = f.x; o[1] = f.y; o[2] = f.z; o[3] = bsdf_pdf(b, wi, wo);
+	BsdfSample bs;
+	const V3 w = bsdf_sample(b, wi, r[6], r[7], bs);
+	o[4] = w.x; o[5] = w.y; o[6] = w.z; o[7] = bs.wo.x; o[8] = bs.wo.y; o[9] = bs.wo.z;
+	o[10] = bs.pdf; o[11] = bs.eta; o[12] = (float) bs.type; o[13] = o[14] = o[15] = 0;
+}
+
+__global__ void eval_emitter_kernel(SceneDev S, const float *in, size_t n, float *out) {
+	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float *r = in + i * 8; float *o = out + i * 12;
+	const V3 p = v3(r[0], r[1], r[2]), refN = v3(r[3], r[4], r[5]);
+	DirectSample ds;
+	const V3 value = scene_sample_emitter_direct(S, p, refN, r[6], r[7], ds);
+	o[0] = value.x; o[1] = value.y; o[2] = value.z; o[3] = ds.pdf;
+	o[4] = ds.d.x; o[5] = ds.d.y; o[6] = ds.d.z; o[7] = ds.dist; o[8] = (float) ds.measure;
+	o[9] = (ds.pdf > 0 && !is_zero(value)) ? emitter_pdf_direct(S, ds.emitter, refN, ds.d, ds.dist, ds.n, ds.measure) * emitter_pdf_discrete(S, ds.emitter) : 0.0f;
+	o[10] = (float) ds.emitter; o[11] = 0;
+}
+
+} // namespace mtsb

@@ -125,6 +125,7 @@ int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
 	r.type = desc->type; r.shape = desc->shape;
 	r.radiance = v3(desc->radiance[0], desc->radiance[1], desc->radiance[2]);
 	r.pos = v3(desc->pos[0], desc->pos[1], desc->pos[2]);
+	r.samplingWeight = desc->sampling_weight;
 	scene->emitters.push_back(r);
 	scene->emitterWeights.push_back(desc->sampling_weight);
 	return (int) scene->emitters.size() - 1;

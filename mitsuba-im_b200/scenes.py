@@ -81,17 +81,22 @@ def displaced_sphere(subdiv, seed=1, radius=1.0, center=(0, 0, 0), amplitude=0.0
     return V.astype(np.float32), N.astype(np.float32), F.astype(np.uint32)
 
 
-def write_ply(path, V, N, F):
-    """Binary little-endian PLY with per-vertex normals (so TriMesh::computeNormals keeps them as-is)."""
+def write_ply(path, V, N, F, UV=None):
+    """Binary little-endian PLY with per-vertex normals (so TriMesh::computeNormals keeps them as-is) and optional
+    texture coordinates (properties u, v)."""
     V = np.asarray(V, np.float32)
     F = np.asarray(F, np.int32)
     hdr = "ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n" % V.shape[0]
     if N is not None:
         hdr += "property float nx\nproperty float ny\nproperty float nz\n"
+    if UV is not None:
+        hdr += "property float u\nproperty float v\n"
     hdr += "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % F.shape[0]
     with open(path, "wb") as f:
         f.write(hdr.encode("ascii"))
         vd = V if N is None else np.concatenate([V, np.asarray(N, np.float32)], axis=1)
+        if UV is not None:
+            vd = np.concatenate([vd, np.asarray(UV, np.float32)], axis=1)
         f.write(np.ascontiguousarray(vd, "<f4").tobytes())
         fd = np.empty(F.shape[0], dtype=[("n", "u1"), ("i", "<i4", 3)])
         fd["n"] = 3
@@ -217,9 +222,9 @@ class SceneDesc:
         self.sampler = dict(kind="independent", spp=4, seed=0)
 
     # -- building --------------------------------------------------------------------------------
-    def add_mesh(self, V, N, F, bsdf=None, emitter=None, name=None):
+    def add_mesh(self, V, N, F, bsdf=None, emitter=None, name=None, UV=None):
         self.shapes.append(dict(type="mesh", V=np.asarray(V, np.float32), N=None if N is None else np.asarray(N, np.float32),
-                                F=np.asarray(F, np.uint32), bsdf=bsdf or dict(type="diffuse"), emitter=emitter, name=name))
+                                F=np.asarray(F, np.uint32), UV=None if UV is None else np.asarray(UV, np.float32), bsdf=bsdf or dict(type="diffuse"), emitter=emitter, name=name))
         return len(self.shapes) - 1
 
     def add_rectangle(self, to_world, bsdf=None, emitter=None, flip_normals=False):
@@ -261,8 +266,8 @@ class SceneDesc:
             fdr_ext = fresnel_diffuse_reflectance(eta)
             dr = list(b.get("diffuse_reflectance", (0.5, 0.5, 0.5)))
             sr = list(b.get("specular_reflectance", (1, 1, 1)))
-            d_avg = sum(dr) / 3.0          # Spectrum::average over 3 RGB samples
-            s_avg = sum(sr) / 3.0
+            lum = lambda c: 0.212671 * c[0] + 0.715160 * c[1] + 0.072169 * c[2]   # Spectrum::getLuminance (RGB build)
+            d_avg, s_avg = lum(dr), lum(sr)
             ssw = s_avg / (d_avg + s_avg)
             return B.BSDF_PLASTIC | two, [eta] + dr + sr + [fdr_int, fdr_ext, ssw, 1.0 if b.get("nonlinear") else 0.0]
         if t == "roughconductor":
@@ -296,7 +301,7 @@ class SceneDesc:
             if s["emitter"] is not None:
                 eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
             if s["type"] == "mesh":
-                sc.add_mesh(s["V"], s["F"], normals=s["N"], bsdf=bid, emitter=eid)
+                sc.add_mesh(s["V"], s["F"], normals=s["N"], texcoords=s.get("UV"), bsdf=bid, emitter=eid)
             else:
                 sc.add_rectangle(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
         sc.commit(builder)
@@ -381,7 +386,7 @@ class SceneDesc:
             bs = self._bsdf_xml(s["bsdf"]) if s["bsdf"] is not None else ""
             if s["type"] == "mesh":
                 fn = "%s_mesh%d.ply" % (name, i)
-                write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"])
+                write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"], s.get("UV"))
                 face = "" if s["N"] is not None else '<boolean name="faceNormals" value="true"/>'
                 out.append('<shape type="ply"><string name="filename" value="%s"/>%s%s%s</shape>' % (fn, face, bs, em))
             else:
@@ -527,3 +532,41 @@ def shadow_rays(points, light_center=(0, 3.0, 0), light_half=0.2, seed=43):
     rays["mint"] = np.float32(EPSILON)
     rays["maxt"] = (dist.astype(np.float32) * np.float32(1 - SHADOW_EPSILON)).astype(np.float32)
     return rays
+
+
+# ------------------------------------------------------------------------------------------------ small test scenes
+MATERIALS = [
+    dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)),
+    dict(type="dielectric"),
+    dict(type="plastic", diffuse_reflectance=(0.2, 0.3, 0.6)),
+    dict(type="plastic", diffuse_reflectance=(0.7, 0.6, 0.1), nonlinear=True, int_ior=1.9),
+    dict(type="roughconductor", distribution="ggx", alpha=0.1),
+    dict(type="roughconductor", distribution="beckmann", alpha=0.3),
+    dict(type="roughconductor", distribution="ggx", alpha_u=0.05, alpha_v=0.3, sample_visible=False),
+    dict(type="diffuse", reflectance=(0.4, 0.7, 0.4), twosided=True),
+]
+
+
+def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, subdiv=2, env=True, point=True):
+    """Eight displaced spheres, one per entry of MATERIALS, on a diffuse floor; area light (mesh), point light and a
+    constant environment — exercises every BSDF and emitter of the GPU subset."""
+    sd = SceneDesc()
+    if point:
+        sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
+    if env:
+        sd.add_constant_env((0.3, 0.35, 0.5))
+    for i, m in enumerate(MATERIALS):
+        V, N, F = displaced_sphere(subdiv, seed=20 + i, radius=0.45, center=((i % 4) - 1.5, 0.5, (i // 4) * 1.2 - 0.6))
+        c = np.array(((i % 4) - 1.5, 0.5, (i // 4) * 1.2 - 0.6))
+        dn = (V - c) / np.linalg.norm(V - c, axis=1, keepdims=True)          # spherical (u,v); required by anisotropic BSDFs
+        UV = np.stack([np.arctan2(dn[:, 2], dn[:, 0]) / (2 * math.pi) + 0.5, np.arccos(np.clip(dn[:, 1], -1, 1)) / math.pi], axis=1)
+        sd.add_mesh(V, N, F, bsdf=m, UV=UV if i % 2 == 0 else None)
+    g = 4.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
+    lV, lN, lF = displaced_sphere(1, seed=99, radius=0.4, center=(0.5, 2.6, 0.3), amplitude=0.0)
+    sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
+    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd

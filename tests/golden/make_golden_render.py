@@ -1,0 +1,97 @@
+"""Golden vectors for the shading half of the hot path, produced by the UNMODIFIED reference (oracle/_ref):
+
+  bsdf.npz     BSDF::eval / pdf / sample of every BSDF in scenes.MATERIALS on random directions (oracle/raydump.cpp `bsdf`)
+  emitter.npz  Scene::sampleEmitterDirect / pdfEmitterDirect on random reference points (`emitter`)
+  li_*.npz     images rendered by the reference's own `path` plugin through `mitsuba -C` with the counter-based `ctr`
+               sampler (oracle/ctrsampler.cpp) and a box filter: each pixel is the mean of MIPathTracer::Li over the
+               pixel's samples, which the CUDA path must reproduce sample by sample.
+
+Run here:  python tests/golden/make_golden_render.py
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import __graft_entry__ as g  # noqa: E402
+import oracle as O  # noqa: E402
+
+pkg = g.load_package()
+S = pkg.scenes
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def run_util(mode, xml, inp, ncols_out):
+    with tempfile.TemporaryDirectory() as td:
+        ip, op = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+        np.ascontiguousarray(inp, np.float32).tofile(ip)
+        r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", mode, xml, ip, op], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0 or not os.path.exists(op):
+            raise RuntimeError(r.stdout[-3000:])
+        return np.fromfile(op, np.float32).reshape(-1, ncols_out)
+
+
+def rand_dirs(rng, n, upper_frac=0.8):
+    v = rng.normal(size=(n, 3))
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    flip = rng.random(n) < upper_frac
+    v[:, 2] = np.where(flip, np.abs(v[:, 2]), v[:, 2])
+    return v.astype(np.float32)
+
+
+def bsdf_case(td):
+    sd = S.materials_scene()
+    xml = sd.to_xml(td, "mats")
+    rng = np.random.default_rng(5)
+    n = 384
+    rows = []
+    for shape in range(len(S.MATERIALS)):
+        inp = np.zeros((n, 12), np.float32)
+        inp[:, 0] = shape
+        inp[:, 1:4] = rand_dirs(rng, n)
+        inp[:, 4:7] = rand_dirs(rng, n, 0.7)
+        inp[:, 7:9] = rng.random((n, 2), dtype=np.float32)
+        rows.append(inp)
+    inp = np.concatenate(rows)
+    out = run_util("bsdf", xml, inp, 16)
+    np.savez_compressed(os.path.join(GOLD, "bsdf.npz"), inp=inp, out=out)
+    print("bsdf:", inp.shape, "nonzero eval frac", (out[:, 0:3].sum(1) > 0).mean(), "nonzero sample frac", (out[:, 4:7].sum(1) > 0).mean())
+
+
+def emitter_case(td):
+    sd = S.materials_scene()
+    xml = sd.to_xml(td, "mats_e")
+    rng = np.random.default_rng(6)
+    n = 1536
+    inp = np.zeros((n, 8), np.float32)
+    inp[:, 0:3] = rng.uniform([-2, 0, -1.5], [2, 1.5, 1.5], (n, 3))
+    nrm = rand_dirs(rng, n, 0.5)
+    nrm[: n // 4] = 0          # refN = 0: transmissive reference surface
+    inp[:, 3:6] = nrm
+    inp[:, 6:8] = rng.random((n, 2), dtype=np.float32)
+    out = run_util("emitter", xml, inp, 12)
+    np.savez_compressed(os.path.join(GOLD, "emitter.npz"), inp=inp, out=out)
+    print("emitter:", inp.shape, "nonzero frac", (out[:, 0:3].sum(1) > 0).mean(), "measures", np.unique(out[:, 8]))
+
+
+def li_case(td, name, sd):
+    xml = sd.to_xml(td, name)
+    pfm = os.path.join(td, name + ".pfm")
+    O.ref_render(xml, pfm, threads=4, classic=True)
+    img = O.read_pfm(pfm)
+    np.savez_compressed(os.path.join(GOLD, "li_%s.npz" % name), image=img, spp=sd.sampler["spp"], seed=sd.sampler["seed"])
+    print(name, img.shape, "mean", img.mean(axis=(0, 1)))
+
+
+if __name__ == "__main__":
+    with tempfile.TemporaryDirectory() as td:
+        bsdf_case(td)
+        emitter_case(td)
+        li_case(td, "cornell", S.cornell_box(32, 32, spp=4, max_depth=5, sampler="ctr", seed=7))
+        li_case(td, "materials", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=11))
+        li_case(td, "materials_deep", S.materials_scene(24, 16, spp=2, max_depth=-1, sampler="ctr", seed=3))
