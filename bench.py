@@ -274,7 +274,7 @@ def main():
             detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
         try:
             import bench_render
-            detail["path"] = bench_render.run(pkg, ctx, stream)
+            detail["path"] = bench_render.run(pkg, ctx, stream, cpu=not args.no_cpu_baseline and world == 1)
         except ImportError:
             pass
 

@@ -1,0 +1,133 @@
+// extract.h — loaded Mitsuba Scene -> flat arrays of the C ABI (include/mtsb200.h).
+//
+// Host side of the drop-in: reads the reference's own object graph through its public accessors
+// (include/mitsuba/render/scene.h:1065-1100, trimesh.h, ConfigurableObject::getProperties) and re-derives plugin
+// parameters the way the plugin constructors do (file:line cited per item).  Anything outside the GPU subset is
+// rejected with Log(EError) — there is no CPU fallback.
+#pragma once
+#include <mitsuba/render/scene.h>
+#include <mitsuba/render/trimesh.h>
+#include <mitsuba/render/bsdf.h>
+#include <mitsuba/render/emitter.h>
+#include <mitsuba/render/sensor.h>
+#include <mitsuba/render/film.h>
+#include <mitsuba/render/sampler.h>
+#include <mitsuba/core/fresolver.h>
+#include <mitsuba/core/plugin.h>
+#include "ior.h"                 /* src/bsdfs/ior.h: lookupIOR(), header-only, as the BSDF plugins include it */
+#include "../../include/mtsb200.h"
+#include <map>
+
+MTS_NAMESPACE_BEGIN
+
+#define MTSB_CALL(expr) do { int rc__ = (expr); if (rc__ < 0) SLog(EError, "libmtsb200: %s failed (%d): %s", #expr, rc__, mtsb_last_error()); } while (0)
+
+static inline void toRGB(const Spectrum &s, float out[3]) {
+	Float r, g, b; s.toLinearRGB(r, g, b);
+	out[0] = (float) r; out[1] = (float) g; out[2] = (float) b;
+}
+
+static inline void matrixToArray(const Matrix4x4 &m, float out[16]) {
+	for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) out[r*4+c] = (float) m(r, c);
+}
+
+static inline Intersection dummyIntersection() {
+	Intersection its;
+	its.p = Point(0.0f); its.t = 1.0f; its.shape = NULL;
+	its.geoFrame = Frame(Normal(0, 0, 1)); its.shFrame = its.geoFrame;
+	its.uv = Point2(0.5f); its.hasUVPartials = false; its.time = 0; its.instance = NULL;
+	its.dpdu = Vector(1, 0, 0); its.dpdv = Vector(0, 1, 0); its.wi = Vector(0, 0, 1);
+	return its;
+}
+
+/// BSDF plugin -> mtsb_bsdf_desc.  Class names are the reference's RTTI names.
+static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
+	memset(&d, 0, sizeof(d));
+	const std::string cls = bsdf->getClass()->getName();
+	const Properties &props = bsdf->getProperties();
+	if (bsdf->usesRayDifferentials())
+		SLog(EError, "gpupath: BSDF \"%s\" uses textures that need ray differentials — outside the GPU subset", cls.c_str());
+	Intersection its = dummyIntersection();
+	if (cls == "SmoothDiffuse") {                                   // src/bsdfs/diffuse.cpp:80-100
+		d.type = MTSB_BSDF_DIFFUSE;
+		toRGB(bsdf->getDiffuseReflectance(its), d.p);
+	} else if (cls == "SmoothDielectric") {                         // src/bsdfs/dielectric.cpp:150-165
+		d.type = MTSB_BSDF_DIELECTRIC;
+		d.p[0] = (float) bsdf->getEta();
+		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 1);
+		toRGB(props.getSpectrum("specularTransmittance", Spectrum(1.0f)), d.p + 4);
+	} else if (cls == "SmoothPlastic") {                            // src/bsdfs/plastic.cpp:148-215
+		d.type = MTSB_BSDF_PLASTIC;
+		const Float intIOR = lookupIOR(props, "intIOR", "polypropylene"), extIOR = lookupIOR(props, "extIOR", "air");
+		const Float eta = intIOR / extIOR;
+		const Spectrum diff = props.getSpectrum("diffuseReflectance", Spectrum(0.5f));
+		const Spectrum spec = props.getSpectrum("specularReflectance", Spectrum(1.0f));
+		d.p[0] = (float) eta;
+		toRGB(diff, d.p + 1); toRGB(spec, d.p + 4);
+		d.p[7] = (float) fresnelDiffuseReflectance(1 / eta, false);
+		d.p[8] = (float) fresnelDiffuseReflectance(eta, false);
+		const Float dAvg = diff.getLuminance(), sAvg = spec.getLuminance();
+		d.p[9] = (float) (sAvg / (dAvg + sAvg));
+		d.p[10] = props.getBoolean("nonlinear", false) ? 1.0f : 0.0f;
+	} else if (cls == "RoughConductor") {                           // src/bsdfs/roughconductor.cpp:171-203
+		d.type = MTSB_BSDF_ROUGHCONDUCTOR;
+		ref<FileResolver> fResolver = Thread::getThread()->getFileResolver();
+		const std::string materialName = props.getString("material", "Cu");
+		Spectrum intEta, intK;
+		if (to_lower_copy(materialName) == "none") { intEta = Spectrum(0.0f); intK = Spectrum(1.0f); }
+		else {
+			intEta.fromContinuousSpectrum(InterpolatedSpectrum(fResolver->resolve(fs::pathstr("data/ior/" + materialName + ".eta.spd"))));
+			intK.fromContinuousSpectrum(InterpolatedSpectrum(fResolver->resolve(fs::pathstr("data/ior/" + materialName + ".k.spd"))));
+		}
+		const Float extEta = lookupIOR(props, "extEta", "air");
+		Float alphaU = 0.1f, alphaV = 0.1f;                         // MicrofacetDistribution(props), src/bsdfs/microfacet.h:84-128
+		if (props.hasProperty("alpha")) alphaU = alphaV = props.getFloat("alpha");
+		else if (props.hasProperty("alphaU") || props.hasProperty("alphaV")) { alphaU = props.getFloat("alphaU"); alphaV = props.getFloat("alphaV"); }
+		const std::string distr = to_lower_copy(props.getString("distribution", "beckmann"));
+		if (distr != "beckmann" && distr != "ggx")
+			SLog(EError, "gpupath: roughconductor distribution \"%s\" is outside the GPU subset (beckmann, ggx)", distr.c_str());
+		d.p[0] = (float) alphaU; d.p[1] = (float) alphaV;
+		toRGB(props.getSpectrum("eta", intEta) / extEta, d.p + 2);
+		toRGB(props.getSpectrum("k", intK) / extEta, d.p + 5);
+		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 8);
+		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
+		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
+	} else if (cls == "TwoSidedBRDF") {                             // src/bsdfs/twosided.cpp — nested diffuse only
+		const std::string desc = bsdf->toString();
+		if (desc.find("nestedBRDF[0] = SmoothDiffuse[") == std::string::npos || desc.find("nestedBRDF[1] = SmoothDiffuse[") == std::string::npos)
+			SLog(EError, "gpupath: twosided is supported around `diffuse` only — got %s", desc.c_str());
+		d.type = MTSB_BSDF_DIFFUSE | MTSB_BSDF_TWOSIDED_FLAG;
+		toRGB(bsdf->getDiffuseReflectance(its), d.p);
+	} else {
+		return false;
+	}
+	return true;
+}
+
+/// Cross-checks the device BSDF against the CPU plugin on a few fixed directions (SURVEY.md §7 "self-check at load").
+static void selfCheckBSDF(mtsb_scene *scene, int id, const BSDF *bsdf) {
+	static const float dirs[4][6] = {
+		{ 0.3f, 0.2f, 0.93273791f, -0.4f, 0.1f, 0.91104336f }, { 0.0f, 0.0f, 1.0f, 0.6f, 0.0f, 0.8f },
+		{ -0.5f, 0.5f, 0.70710678f, 0.5f, -0.5f, 0.70710678f }, { 0.8f, 0.1f, 0.59160798f, -0.7f, -0.2f, 0.68556546f } };
+	float in[4][8], out[4][16];
+	for (int i = 0; i < 4; ++i) { memcpy(in[i], dirs[i], 6 * sizeof(float)); in[i][6] = 0.35f + 0.1f * i; in[i][7] = 0.6f - 0.1f * i; }
+	MTSB_CALL(mtsb_eval_bsdf(scene, id, &in[0][0], 4, &out[0][0]));
+	Intersection its = dummyIntersection();
+	for (int i = 0; i < 4; ++i) {
+		Vector wi(in[i][0], in[i][1], in[i][2]), wo(in[i][3], in[i][4], in[i][5]);
+		its.wi = wi;
+		BSDFSamplingRecord bRec(its, wi, wo, ERadiance);
+		float ref[3]; toRGB(bsdf->eval(bRec), ref);
+		const Float pdf = bsdf->pdf(bRec);
+		for (int c = 0; c < 3; ++c)
+			if (std::abs(ref[c] - out[i][c]) > 2e-3f * (std::abs(ref[c]) + 1e-3f))
+				SLog(EError, "gpupath: device BSDF %d (%s) disagrees with the CPU plugin: eval[%d] = %g vs %g", id,
+					bsdf->getClass()->getName().c_str(), c, out[i][c], ref[c]);
+		if (std::abs(pdf - out[i][3]) > 2e-3f * (std::abs(pdf) + 1e-3f))
+			SLog(EError, "gpupath: device BSDF %d (%s) disagrees with the CPU plugin: pdf = %g vs %g", id,
+				bsdf->getClass()->getName().c_str(), out[i][3], (float) pdf);
+	}
+}
+
+MTS_NAMESPACE_END
+#include "extract_scene.h"

@@ -1,0 +1,122 @@
+// extract_scene.h — geometry, emitters, sensor and film of a loaded Scene -> C ABI calls (included by extract.h).
+#pragma once
+
+MTS_NAMESPACE_BEGIN
+
+/// Uploads shapes / BSDFs / emitters in Scene order and commits (BVH build on the device).
+static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
+	mtsb_scene *out = NULL;
+	MTSB_CALL(mtsb_scene_create(ctx, &out));
+	// emitters first, in Scene::getEmitters() order (that order defines the selection CDF, scene.cpp:381-386)
+	const ref_vector<Emitter> &emitters = scene->getEmitters();
+	std::map<const Emitter *, int> emitterIds;
+	for (size_t i = 0; i < emitters.size(); ++i) {
+		const Emitter *e = emitters[i].get();
+		const std::string cls = e->getClass()->getName();
+		const Properties &props = e->getProperties();
+		mtsb_emitter_desc d; memset(&d, 0, sizeof(d));
+		d.sampling_weight = (float) e->getSamplingWeight();
+		if (cls == "AreaLight") {                                   // src/emitters/area.cpp:64-73
+			d.type = MTSB_EMITTER_AREA;
+			toRGB(props.getSpectrum("radiance", Spectrum::getD65()), d.radiance);
+		} else if (cls == "PointEmitter") {                         // src/emitters/point.cpp:52-61
+			d.type = MTSB_EMITTER_POINT;
+			toRGB(props.getSpectrum("intensity", Spectrum::getD65()), d.radiance);
+			const Point p = e->getWorldTransform()->eval(0).transformAffine(Point(0.0f));
+			d.pos[0] = (float) p.x; d.pos[1] = (float) p.y; d.pos[2] = (float) p.z;
+		} else if (cls == "ConstantBackgroundEmitter") {            // src/emitters/constant.cpp:44-52
+			d.type = MTSB_EMITTER_CONSTANT;
+			toRGB(props.getSpectrum("radiance", Spectrum::getD65()), d.radiance);
+		} else {
+			SLog(EError, "gpupath: emitter \"%s\" is outside the GPU subset (area, point, constant)", cls.c_str());
+		}
+		int id = mtsb_scene_add_emitter(out, &d);
+		if (id < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+		emitterIds[e] = id;
+	}
+	const ref_vector<Shape> &shapes = scene->getShapes();
+	std::map<const BSDF *, int> bsdfIds;
+	for (size_t i = 0; i < shapes.size(); ++i) {
+		const Shape *shape = shapes[i].get();
+		const BSDF *bsdf = shape->getBSDF();
+		if (!bsdf) SLog(EError, "gpupath: shape %d has no BSDF", (int) i);
+		if (shape->isMediumTransition() || shape->hasSubsurface())
+			SLog(EError, "gpupath: participating media / subsurface scattering are outside the GPU subset");
+		int bid;
+		if (bsdfIds.count(bsdf)) bid = bsdfIds[bsdf];
+		else {
+			mtsb_bsdf_desc bd;
+			if (!describeBSDF(bsdf, bd))
+				SLog(EError, "gpupath: BSDF \"%s\" is outside the GPU subset (diffuse, dielectric, plastic, roughconductor, twosided(diffuse))",
+					bsdf->getClass()->getName().c_str());
+			bid = mtsb_scene_add_bsdf(out, &bd);
+			if (bid < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+			bsdfIds[bsdf] = bid;
+		}
+		int eid = -1;
+		if (shape->isEmitter()) {
+			std::map<const Emitter *, int>::const_iterator it = emitterIds.find(shape->getEmitter());
+			if (it == emitterIds.end()) SLog(EError, "gpupath: shape %d carries an emitter the scene does not list", (int) i);
+			eid = it->second;
+		}
+		int rc;
+		if (shape->getClass()->derivesFrom(MTS_CLASS(TriMesh))) {
+			const TriMesh *mesh = static_cast<const TriMesh *>(shape);
+			// Point / Normal are 3 packed floats, Point2 2 floats, Triangle 3 uint32 (include/mitsuba/core/triangle.h)
+			rc = mtsb_scene_add_mesh(out, (const float *) mesh->getVertexPositions(), (const float *) mesh->getVertexNormals(),
+				(const float *) mesh->getVertexTexcoords(), (const uint32_t *) mesh->getTriangles(),
+				mesh->getVertexCount(), mesh->getTriangleCount(), bid, eid);
+		} else if (shape->getClass()->getName() == "Rectangle") {   // src/shapes/rectangle.cpp:79-84
+			const Properties &props = shape->getProperties();
+			float m[16]; matrixToArray(props.getTransform("toWorld", Transform()).getMatrix(), m);
+			rc = mtsb_scene_add_rectangle(out, m, props.getBoolean("flipNormals", false) ? 1 : 0, bid, eid);
+		} else {
+			SLog(EError, "gpupath: shape \"%s\" is outside the GPU subset (triangle meshes, rectangle)", shape->getClass()->getName().c_str());
+			rc = -1;
+		}
+		if (rc < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+	}
+	MTSB_CALL(mtsb_scene_commit(out, builder));
+	for (std::map<const BSDF *, int>::const_iterator it = bsdfIds.begin(); it != bsdfIds.end(); ++it)
+		selfCheckBSDF(out, it->second, it->first);
+	return out;
+}
+
+/// PerspectiveCameraImpl::configure (src/sensors/perspective.cpp:126-180) restated with the reference's own Transform class.
+static void describeCamera(const Sensor *sensor, mtsb_camera &cam) {
+	if (!sensor->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)) || sensor->needsApertureSample() || sensor->needsTimeSample())
+		SLog(EError, "gpupath: sensor \"%s\" is outside the GPU subset (perspective)", sensor->getClass()->getName().c_str());
+	const PerspectiveCamera *pc = static_cast<const PerspectiveCamera *>(sensor);
+	const Film *film = sensor->getFilm();
+	const Vector2i filmSize = film->getSize(), cropSize = film->getCropSize();
+	const Point2i cropOffset = film->getCropOffset();
+	const Float aspect = pc->getAspect();
+	Vector2 relSize((Float) cropSize.x / (Float) filmSize.x, (Float) cropSize.y / (Float) filmSize.y);
+	Point2 relOffset((Float) cropOffset.x / (Float) filmSize.x, (Float) cropOffset.y / (Float) filmSize.y);
+	Transform cameraToSample =
+		  Transform::scale(Vector(1.0f / relSize.x, 1.0f / relSize.y, 1.0f))
+		* Transform::translate(Vector(-relOffset.x, -relOffset.y, 0.0f))
+		* Transform::scale(Vector(-0.5f, -0.5f * aspect, 1.0f))
+		* Transform::translate(Vector(-1.0f, -1.0f / aspect, 0.0f))
+		* Transform::perspective(pc->getXFov(), pc->getNearClip(), pc->getFarClip());
+	matrixToArray(cameraToSample.inverse().getMatrix(), cam.sample_to_camera);
+	matrixToArray(sensor->getWorldTransform()->eval(0).getMatrix(), cam.camera_to_world);
+	cam.near_clip = (float) pc->getNearClip(); cam.far_clip = (float) pc->getFarClip();
+	cam.inv_resolution[0] = 1.0f / cropSize.x; cam.inv_resolution[1] = 1.0f / cropSize.y;
+}
+
+/// The float layout of an ImageBlock + its filter table (include/mitsuba/core/rfilter.h:76-77).
+static void describeFilm(const ImageBlock &block, const ReconstructionFilter *rf, const Film *film, mtsb_film_desc &fd) {
+	memset(&fd, 0, sizeof(fd));
+	fd.width = block.getSize().x; fd.height = block.getSize().y;
+	fd.offset[0] = block.getOffset().x; fd.offset[1] = block.getOffset().y;
+	fd.border = block.getBorderSize();
+	fd.channels = block.getChannelCount();
+	fd.filter_radius = (float) rf->getRadius();
+	for (int i = 0; i < 32; ++i)     // evalDiscretized(x) = m_values[min(int(|x| * 31 / r), 31)]
+		fd.filter_table[i] = (float) rf->evalDiscretized((i + 0.5f) * rf->getRadius() / 31.0f);
+	fd.crop_offset[0] = film->getCropOffset().x; fd.crop_offset[1] = film->getCropOffset().y;
+	fd.crop_size[0] = film->getCropSize().x; fd.crop_size[1] = film->getCropSize().y;
+}
+
+MTS_NAMESPACE_END

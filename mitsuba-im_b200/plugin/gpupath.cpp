@@ -1,0 +1,182 @@
+// gpupath.cpp — Mitsuba integrator plugin that routes the `path` / `direct` hot path through libmtsb200 (B200 CUDA).
+//
+// Drop-in at the reference's plugin boundary: exports CreateInstance / GetDescription
+// (include/mitsuba/core/cobject.h:102-110) and the `mitsuba_integrator_plugin` marker
+// (src/integrators/mark_integrator.cpp), derives from MonteCarloIntegrator (src/librender/integrator.cpp:191-226, same
+// XML properties: maxDepth, rrDepth, strictNormals, hideEmitters) and serves both schedulers:
+//   classic     Integrator::render   (include/mitsuba/render/integrator.h:61-120; caller RenderJob::run, renderjob.cpp:86-117)
+//   responsive  ResponsiveIntegrator (include/mitsuba/render/integrator2.h:49-100; callers src/mitsuba/im_render.cpp, src/im-mts/scene.cpp)
+// Built as gpupath.so; installed under the name path.so / direct.so in an overlay plugin directory it replaces the stock
+// integrators for unmodified scene files.  Extra properties: gpus, builder (lbvh|ploc), sppPerPass, seed.
+#include <mitsuba/render/integrator.h>
+#include <mitsuba/render/integrator2.h>
+#include <mitsuba/render/renderjob.h>
+#include <mitsuba/render/imageblock.h>
+#include <mitsuba/core/statistics.h>
+#include <mitsuba/core/lock.h>
+#include "extract.h"
+
+MTS_NAMESPACE_BEGIN
+
+/// Per-GPU state shared by both scheduler paths; cached on scene identity so that Integrator2's per-frame preprocess
+/// (src/im-mts/shell.cpp:240-242) does not rebuild the BVH.
+struct GPUDevice {
+	mtsb_ctx *ctx; mtsb_scene *scene; const Scene *owner;
+	GPUDevice() : ctx(NULL), scene(NULL), owner(NULL) { }
+	void ensure(int device, const Scene *s, int builder) {
+		if (!ctx) MTSB_CALL(mtsb_ctx_create(device, &ctx));
+		if (scene && owner == s) return;
+		if (scene) mtsb_scene_destroy(scene);
+		scene = uploadScene(ctx, s, builder);
+		owner = s;
+		double st[8]; mtsb_scene_build_stats(scene, st);
+		SLog(EInfo, "gpupath: device %d: BVH8 over %u primitives built in %.1f ms (%d nodes, SAH cost %.1f)", device,
+			(unsigned) mtsb_scene_primitive_count(scene), st[0], (int) st[1], st[4]);
+	}
+	~GPUDevice() { if (scene) mtsb_scene_destroy(scene); if (ctx) mtsb_ctx_destroy(ctx); }
+};
+
+class GPUPathTracer;
+
+/// Responsive (Integrator2) adapter: thread t renders the sample indices s = t (mod threadCount) of every pixel on GPU
+/// t % gpus, accumulates un-normalised sums into the caller's ImageBlock and reports its own spp share, which is what
+/// InteractiveSceneProcess::develop sums up (src/mitsuba/im_render.cpp:225-247).
+class GPUResponsiveIntegrator : public ResponsiveIntegrator {
+public:
+	GPUResponsiveIntegrator(GPUPathTracer *parent);
+	bool preprocess(const Scene *scene, const Sensor *sensor, const Sampler *sampler);
+	bool allocate(const Scene &scene, Sampler *const *samplers, ImageBlock *const *targets, int threadCount);
+	int render(const Scene &scene, const Sensor &sensor, Sampler &sampler, ImageBlock &target, Controls controls, int threadIdx, int threadCount);
+	const char *getRealtimeStatistics() { return m_stats.c_str(); }
+	MTS_DECLARE_CLASS()
+protected:
+	virtual ~GPUResponsiveIntegrator();
+	ref<GPUPathTracer> m_parent;
+	std::vector<mtsb_render *> m_renders;      // one per thread
+	std::string m_stats;
+};
+
+class GPUPathTracer : public MonteCarloIntegrator {
+public:
+	GPUPathTracer(const Properties &props) : MonteCarloIntegrator(props), m_cancel(false) {
+		m_gpus = props.getInteger("gpus", 1);
+		m_sppPerPass = props.getInteger("sppPerPass", 0);
+		m_seed = props.getInteger("seed", 0);
+		const std::string b = to_lower_copy(props.getString("builder", "ploc"));
+		if (b != "ploc" && b != "lbvh") Log(EError, "gpupath: builder must be \"lbvh\" or \"ploc\"");
+		m_builder = b == "ploc" ? MTSB_BUILDER_PLOC : MTSB_BUILDER_LBVH;
+		// `direct` semantics when installed as direct.so or asked for explicitly
+		m_direct = props.getPluginName() == "direct" || props.getBoolean("direct", false);
+		m_emitterSamples = props.getInteger("emitterSamples", props.getInteger("shadingSamples", 1));
+		m_bsdfSamples = props.getInteger("bsdfSamples", props.getInteger("shadingSamples", 1));
+		const int n = mtsb_device_count();
+		if (n == 0) Log(EError, "gpupath: no CUDA device — this integrator has no CPU fallback");
+		if (m_gpus < 1 || m_gpus > n) Log(EError, "gpupath: gpus=%d but %d device(s) are visible", m_gpus, n);
+		m_mutex = new Mutex();
+		m_devices.resize(m_gpus);
+	}
+	GPUPathTracer(Stream *stream, InstanceManager *manager) : MonteCarloIntegrator(stream, manager) {
+		Log(EError, "gpupath: network rendering is not supported (the GPU path replaces the use of remote workers)");
+	}
+
+	/// Per-ray entry point other integrators (adaptive, irrcache) call; the batch pipeline has no per-ray mode.
+	Spectrum Li(const RayDifferential &, RadianceQueryRecord &) const {
+		Log(EError, "gpupath: Li() per ray is not available — use the stock `path` plugin for integrators that call it");
+		return Spectrum(0.0f);
+	}
+
+	void describeIntegrator(mtsb_integrator_desc &d) const {
+		memset(&d, 0, sizeof(d));
+		d.type = m_direct ? MTSB_INTEGRATOR_DIRECT : MTSB_INTEGRATOR_PATH;
+		d.max_depth = m_maxDepth; d.rr_depth = m_rrDepth;
+		d.strict_normals = m_strictNormals ? 1 : 0; d.hide_emitters = m_hideEmitters ? 1 : 0;
+		d.emitter_samples = m_emitterSamples; d.bsdf_samples = m_bsdfSamples;
+	}
+
+	uint64_t seedFor(const Sampler *sampler) const {
+		// share the stream of oracle/ctrsampler.cpp when the scene uses it, so renders are comparable sample by sample
+		if (sampler && sampler->getProperties().hasProperty("seed")) return (uint64_t) sampler->getProperties().getInteger("seed");
+		return (uint64_t) m_seed;
+	}
+
+	GPUDevice &device(int i, const Scene *scene) {
+		LockGuard lock(m_mutex);
+		m_devices[i].ensure(i, scene, m_builder);
+		return m_devices[i];
+	}
+
+	bool preprocess(const Scene *scene, RenderQueue *, const RenderJob *, int, int, int) {
+		for (int i = 0; i < m_gpus; ++i) device(i, scene);
+		return true;
+	}
+
+	/// Classic scheduler path: the whole image in this thread, sample passes split over the GPUs.
+	bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int, int, int) {
+		ref<Sensor> sensor = scene->getSensor();
+		ref<Film> film = sensor->getFilm();
+		const Sampler *sampler = scene->getSampler();
+		const uint32_t sampleCount = (uint32_t) sampler->getSampleCount();
+		m_cancel = false;
+		Log(EInfo, "Starting render job (%ix%i, %u %s, %d GPU%s) ..", film->getCropSize().x, film->getCropSize().y,
+			sampleCount, sampleCount == 1 ? "sample" : "samples", m_gpus, m_gpus == 1 ? "" : "s");
+		ref<ImageBlock> block = new ImageBlock(Bitmap::ESpectrumAlphaWeight, film->getCropSize(), film->getReconstructionFilter());
+		block->setOffset(Point2i(0, 0));
+		block->clear();
+		mtsb_camera cam; describeCamera(sensor, cam);
+		mtsb_film_desc fd; describeFilm(*block, film->getReconstructionFilter(), film, fd);
+		mtsb_integrator_desc id; describeIntegrator(id);
+		std::vector<mtsb_render *> renders(m_gpus, (mtsb_render *) NULL);
+		for (int g = 0; g < m_gpus; ++g)
+			MTSB_CALL(mtsb_render_create(device(g, scene).scene, &cam, &fd, &id, seedFor(sampler), &renders[g]));
+		ref<Timer> timer = new Timer();
+		// GPU g renders sample indices s = g (mod gpus); passes are asynchronous, one stream per GPU
+		const uint32_t perGpu = (sampleCount + m_gpus - 1) / m_gpus;
+		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : perGpu;
+		for (uint32_t done = 0; done < perGpu && !m_cancel; done += pass) {
+			for (int g = 0; g < m_gpus; ++g) {
+				const uint32_t first = done, last = std::min(perGpu, done + pass);
+				// the k-th local sample of GPU g has index g + k * gpus; drop indices beyond sampleCount
+				uint32_t cnt = 0;
+				for (uint32_t k = first; k < last; ++k) if ((uint32_t) g + k * m_gpus < sampleCount) ++cnt;
+				if (cnt) MTSB_CALL(mtsb_render_pass(renders[g], first * m_gpus, cnt, sampleCount, NULL, m_gpus, g));
+			}
+			for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_sync(renders[g]));
+		}
+		float *dst = block->getBitmap()->getFloatData();
+		const size_t n = (size_t) block->getBitmap()->getSize().x * block->getBitmap()->getSize().y * block->getChannelCount();
+		uint64_t st[8] = { 0 }, tot[8] = { 0 };
+		for (int g = 0; g < m_gpus; ++g) {
+			MTSB_CALL(mtsb_film_to_host(renders[g], dst, n, g > 0));
+			mtsb_render_stats(renders[g], st);
+			for (int i = 0; i < 8; ++i) tot[i] += st[i];
+			mtsb_render_destroy(renders[g]);
+		}
+		film->put(block);
+		if (queue && job) queue->signalRefresh(job);
+		const double s = timer->getMilliseconds() * 1e-3;
+		Log(EInfo, "gpupath: %llu paths, %llu closest-hit + %llu shadow rays, average path length %.2f, %.1f M samples/s",
+			(unsigned long long) tot[0], (unsigned long long) tot[1], (unsigned long long) tot[2],
+			tot[0] ? (double) tot[3] / tot[0] : 0.0, tot[0] / std::max(s, 1e-9) / 1e6);
+		return !m_cancel;
+	}
+
+	void cancel() { m_cancel = true; }
+	ref<ResponsiveIntegrator> makeResponsiveIntegrator() { return new GPUResponsiveIntegrator(this); }
+	void serialize(Stream *stream, InstanceManager *manager) const { MonteCarloIntegrator::serialize(stream, manager); }
+	std::string toString() const {
+		std::ostringstream oss;
+		oss << "GPUPathTracer[maxDepth = " << m_maxDepth << ", rrDepth = " << m_rrDepth << ", strictNormals = " << m_strictNormals
+			<< ", gpus = " << m_gpus << ", direct = " << m_direct << "]";
+		return oss.str();
+	}
+	MTS_DECLARE_CLASS()
+
+	int m_gpus, m_sppPerPass, m_seed, m_builder, m_emitterSamples, m_bsdfSamples;
+	bool m_direct;
+	volatile bool m_cancel;
+	ref<Mutex> m_mutex;
+	std::vector<GPUDevice> m_devices;
+};
+
+MTS_NAMESPACE_END
+#include "gpupath_responsive.h"
