@@ -154,6 +154,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-path", action="store_true", help="skip the path-tracer detail runs (short runs under ncu)")
     ap.add_argument("--builder", default="ploc", choices=["lbvh", "ploc"])
     ap.add_argument("--rays", type=int, default=N_RAYS)
     args = ap.parse_args()
@@ -273,6 +274,8 @@ def main():
             torch.cuda.synchronize()
             detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
         try:
+            if args.no_path:
+                raise ImportError
             import bench_render
             detail["path"] = bench_render.run(pkg, ctx, stream, cpu=not args.no_cpu_baseline and world == 1)
         except ImportError:
