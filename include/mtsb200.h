@@ -245,6 +245,30 @@ MTSB_API int  mtsb_render_stats(mtsb_render *r, uint64_t out[8]);
  * sampler: samples n x 4 uint32 {px, py, sampleIndex, 0}; out n x 4 float {L.rgb, alpha}; host ptrs. */
 MTSB_API int  mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out);
 
+/* ---------------------------------------------------------------- multi-GPU film reduction ------- */
+/* The path shards by SAMPLE INDEX: every GPU holds the scene + BVH and renders the indices s = phase (mod stride) of
+ * every pixel into its own full-size film (mtsb_render_pass); nothing is exchanged while tracing.  The one exchange
+ * step is the sum of the per-GPU films, the device-side form of Film::put(block) -> ImageBlock::put(const ImageBlock*)
+ * -> Bitmap::accumulate (src/films/hdrfilm.cpp:391-393, include/mitsuba/render/imageblock.h:140-143) and of the
+ * responsive caller summing its per-thread targets (src/mitsuba/im_render.cpp:225-247).  It runs as ONE NCCL
+ * reduce over NVLink on the context streams.  NCCL is bound at run time (libnccl.so.2); without it these calls fail
+ * with MTSB_EUNSUPPORTED — there is no host-side substitute. */
+typedef struct mtsb_comm mtsb_comm;
+#define MTSB_COMM_ID_BYTES 128
+/* NCCL version code (e.g. 22809) or a negative error. */
+MTSB_API int  mtsb_comm_version(void);
+/* One process per GPU (torchrun): rank 0 makes an id, ships it to the others by any side channel, everyone joins. */
+MTSB_API int  mtsb_comm_unique_id(uint8_t id[MTSB_COMM_ID_BYTES]);
+MTSB_API int  mtsb_comm_create(mtsb_ctx *ctx, int nranks, int rank, const uint8_t id[MTSB_COMM_ID_BYTES], mtsb_comm **out);
+/* One process driving n GPUs (the Mitsuba plugin with gpus=n): out receives n communicators, rank i on ctxs[i]. */
+MTSB_API int  mtsb_comm_create_all(mtsb_ctx *const *ctxs, int n, mtsb_comm **out);
+MTSB_API void mtsb_comm_destroy(mtsb_comm *comm);
+/* film(root) = sum over ranks of film(rank); root < 0 = every rank receives the sum.  Asynchronous on the context
+ * stream, ordered after the passes already queued there; mtsb_render_sync / mtsb_film_to_host wait for it. */
+MTSB_API int  mtsb_film_reduce(mtsb_render *r, mtsb_comm *comm, int root);
+/* Single-process form: the n per-GPU reduces issued as one NCCL group. */
+MTSB_API int  mtsb_film_reduce_all(mtsb_render *const *renders, mtsb_comm *const *comms, int n, int root);
+
 #ifdef __cplusplus
 }
 #endif

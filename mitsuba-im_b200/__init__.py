@@ -7,3 +7,4 @@ The directory name contains a hyphen, so import it through __graft_entry__.load_
 """
 from . import binding  # noqa: F401
 from . import scenes   # noqa: F401
+from . import multigpu  # noqa: F401

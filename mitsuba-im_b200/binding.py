@@ -105,6 +105,10 @@ def lib():
         "mtsb_render_sync": (i32, [vp]), "mtsb_film_device_ptr": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]),
         "mtsb_film_to_host": (i32, [vp, vp, sz, i32]), "mtsb_render_stats": (i32, [vp, vp]),
         "mtsb_render_samples": (i32, [vp, vp, sz, u32, vp]),
+        "mtsb_comm_version": (i32, []), "mtsb_comm_unique_id": (i32, [vp]),
+        "mtsb_comm_create": (i32, [vp, i32, i32, vp, C.POINTER(vp)]), "mtsb_comm_create_all": (i32, [C.POINTER(vp), i32, C.POINTER(vp)]),
+        "mtsb_comm_destroy": (None, [vp]), "mtsb_film_reduce": (i32, [vp, vp, i32]),
+        "mtsb_film_reduce_all": (i32, [C.POINTER(vp), C.POINTER(vp), i32, i32]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(L, name):
@@ -356,3 +360,53 @@ class Render:
         if self.h:
             lib().mtsb_render_destroy(self.h)
             self.h = C.c_void_p()
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id():
+    """ncclUniqueId bytes made by rank 0 and shipped to the other ranks by the launcher's side channel."""
+    buf = (C.c_uint8 * COMM_ID_BYTES)()
+    _check(lib().mtsb_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Comm:
+    """NCCL communicator of one rank (mtsb_comm), used only for the film reduction at the end of a render."""
+
+    def __init__(self, ctx, nranks, rank, unique_id):
+        self.h = C.c_void_p()
+        self.nranks, self.rank = nranks, rank
+        buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(unique_id)
+        _check(lib().mtsb_comm_create(ctx.h, nranks, rank, buf, C.byref(self.h)))
+
+    def film_reduce(self, render, root=0):
+        """film(root) += films of every other rank; asynchronous on the context stream."""
+        _check(lib().mtsb_film_reduce(render.h, self.h, root))
+
+    def close(self):
+        if self.h:
+            lib().mtsb_comm_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+def comm_create_all(contexts):
+    """Single process, one context per GPU: list of Comm objects (rank i on contexts[i])."""
+    n = len(contexts)
+    ctxs = (C.c_void_p * n)(*[c.h for c in contexts])
+    out = (C.c_void_p * n)()
+    _check(lib().mtsb_comm_create_all(ctxs, n, out))
+    comms = []
+    for i in range(n):
+        c = Comm.__new__(Comm)
+        c.h, c.nranks, c.rank = C.c_void_p(out[i]), n, i
+        comms.append(c)
+    return comms
+
+
+def film_reduce_all(renders, comms, root=0):
+    n = len(renders)
+    r = (C.c_void_p * n)(*[x.h for x in renders])
+    c = (C.c_void_p * n)(*[x.h for x in comms])
+    _check(lib().mtsb_film_reduce_all(r, c, n, root))
