@@ -88,6 +88,13 @@ def li_case(td, name, sd):
     print(name, img.shape, "mean", img.mean(axis=(0, 1)))
 
 
+def direct_case(td):
+    """MIDirectIntegrator (src/integrators/direct/direct.cpp) with its default emitterSamples = bsdfSamples = 1."""
+    sd = S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=13)
+    sd.set_integrator("direct")
+    li_case(td, "direct", sd)
+
+
 if __name__ == "__main__":
     with tempfile.TemporaryDirectory() as td:
         bsdf_case(td)
@@ -95,3 +102,4 @@ if __name__ == "__main__":
         li_case(td, "cornell", S.cornell_box(32, 32, spp=4, max_depth=5, sampler="ctr", seed=7))
         li_case(td, "materials", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=11))
         li_case(td, "materials_deep", S.materials_scene(24, 16, spp=2, max_depth=-1, sampler="ctr", seed=3))
+        direct_case(td)

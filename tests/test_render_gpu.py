@@ -88,7 +88,7 @@ def _li_image(pkg, ctx, sd):
     return L, film, stats
 
 
-@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep"])
+@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer)."""
@@ -100,6 +100,10 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
         sd = S.cornell_box(32, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)
     elif name == "materials":
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+    elif name == "direct":
+        # MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309) with emitterSamples = bsdfSamples = 1
+        sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+        sd.set_integrator("direct")
     else:
         sd = S.materials_scene(24, 16, spp=spp, max_depth=-1, sampler="ctr", seed=seed)
     L, film, stats = _li_image(pkg, ctx, sd)
