@@ -10,7 +10,8 @@ wavefront path tracer are reported in `detail` on the same JSON line.
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 N > 1 is launched under torchrun (one rank per GPU); rays are sharded across ranks with no data-path collective
-(weak scaling: every rank traces its own 16 M-ray batch against a replicated scene).
+(weak scaling: every rank traces its own 16 M-ray batch against a replicated scene).  detail.path also carries config 4
+(3840x2160, 1024 spp) split by sample index over the N ranks with one NCCL film reduce at the end (strong scaling).
 """
 import argparse
 import json
@@ -155,6 +156,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-path", action="store_true", help="skip the path-tracer detail runs (short runs under ncu)")
+    ap.add_argument("--no-config4", action="store_true", help="skip the 3840x2160 multi-GPU render (config 4)")
+    ap.add_argument("--spp4", type=int, default=1024, help="samples per pixel of config 4 (BASELINE: 1024)")
     ap.add_argument("--builder", default="ploc", choices=["lbvh", "ploc"])
     ap.add_argument("--rays", type=int, default=N_RAYS)
     args = ap.parse_args()
@@ -273,13 +276,34 @@ def main():
                 b.record(stream)
             torch.cuda.synchronize()
             detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
-        try:
-            if args.no_path:
-                raise ImportError
+        if not args.no_path:
             import bench_render
-            detail["path"] = bench_render.run(pkg, ctx, stream, cpu=not args.no_cpu_baseline and world == 1)
-        except ImportError:
-            pass
+            detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5), cpu=not args.no_cpu_baseline and world == 1)
+
+    # --- config 4: 3840x2160, 1024 spp split by sample index over the ranks (strong scaling), one NCCL film reduce ---
+    if not args.no_path and not args.no_config4:
+        import bench_render
+        comm = None
+        if world > 1:
+            uid = pkg.multigpu.exchange_unique_id(dist, B.comm_unique_id, rank)
+            comm = B.Comm(ctx, world, rank, uid)
+        c4 = bench_render.run(pkg, ctx, stream, configs=(4,), cpu=False, rank=rank, world=world, comm=comm, spp4=args.spp4)
+        c4 = list(c4.values())[0]
+        barrier()
+        tt = torch.tensor([c4["total_ms"], c4["render_ms"], c4["reduce_ms"]], device="cuda", dtype=torch.float64)
+        ss = torch.tensor([float(c4["paths"]), float(c4["rays"]), float(c4["launches"])], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            total_ms = float(tt[0].item())
+            c4.update(total_ms_max_over_ranks=total_ms, render_ms_max_over_ranks=float(tt[1].item()), reduce_ms_max_over_ranks=float(tt[2].item()),
+                      samples_per_s=c4["width"] * c4["height"] * c4["spp"] / (total_ms * 1e-3), paths_all_ranks=int(ss[0].item()),
+                      mrays_per_s=float(ss[1].item()) / (total_ms * 1e-3) / 1e6, launches_all_ranks=int(ss[2].item()), scaling="strong",
+                      split="sample index s mod %d, scene replicated, ncclReduce(sum) of the %d-byte film into rank 0" % (world, c4["film_bytes"]))
+            detail.setdefault("path", {})["config4_3840x2160_%dspp_%dgpu" % (args.spp4, world)] = c4
+        if comm is not None:
+            comm.close()
 
     if rank == 0:
         peak, peak_kind = measured_peaks()

@@ -67,6 +67,92 @@ def render_config(pkg, ctx, stream, sd, spp, warmup=1, builder=None):
     return out
 
 
+def render_config4(pkg, ctx, stream, sd, spp, rank=0, world=1, comm=None, spp_per_pass=32):
+    """Config 4: the config-3 scene at 3840x2160, `spp` samples per pixel split by sample index over `world` ranks
+    (strong scaling), the per-rank films summed into rank 0 by ONE NCCL reduce (mtsb_film_reduce).  Times the render
+    and the reduce on the device (context stream); the caller takes the max over ranks."""
+    import torch
+    B, M = pkg.binding, pkg.multigpu
+    sc = sd.upload(ctx, B.BUILDER_PLOC)
+    rd = B.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=1)
+    w, h = sd.sensor["width"], sd.sensor["height"]
+    rd.render_pass(0, 1, spp, stride=world, phase=rank)
+    if comm is not None and world > 1:
+        comm.film_reduce(rd, 0)          # warm-up of the collective (NCCL channel setup) outside the timed region
+    rd.sync()
+    rd.clear()
+    rd.sync()
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for begin, count in M.passes(spp, world, rank, spp_per_pass):
+            rd.render_pass(begin, count, spp, stride=world, phase=rank)
+        e1.record(stream)
+        if comm is not None and world > 1:
+            comm.film_reduce(rd, 0)
+        e2.record(stream)
+    rd.sync()
+    st = rd.stats()
+    t0 = time.perf_counter()
+    film = rd.film_to_host() if rank == 0 else None
+    d2h_ms = (time.perf_counter() - t0) * 1e3
+    out = {"render_ms": e0.elapsed_time(e1), "reduce_ms": e1.elapsed_time(e2), "total_ms": e0.elapsed_time(e2), "d2h_ms": d2h_ms,
+           "width": w, "height": h, "spp": spp, "world": world, "rank_spp": M.sample_share(spp, world, rank),
+           "avg_path_length": st["depth_sum"] / max(st["paths"], 1), "paths": st["paths"],
+           "rays": st["closest_rays"] + st["shadow_rays"], "launches": st["launches"],
+           "film_bytes": int(rd.film_device_ptr()[1]) * 4}
+    if film is not None:
+        b = sd.film().border
+        img = film[b:film.shape[0] - b, b:film.shape[1] - b]
+        out["film_weight_per_pixel"] = float(img[..., 4].mean())          # ~= spp (Gaussian table normalisation) once reduced
+        out["mean_radiance"] = float(np.nanmean(img[..., 0:3] / np.maximum(img[..., 4:5], 1e-9)))
+    rd.close()
+    sc.close()
+    return out
+
+
+def orbit(sd, deg):
+    """Camera of config 5: the scene's sensor rotated `deg` degrees about the world Y axis through the look-at target."""
+    S = graft.load_package().scenes
+    return S.make_camera(S.rotate((0, 1, 0), deg) @ sd.sensor["to_world"], sd.sensor["fov"], sd.sensor["width"], sd.sensor["height"],
+                         fov_axis=sd.sensor["fov_axis"])
+
+
+def render_config5(pkg, ctx, stream, sd, frames=600, warmup=5):
+    """Config 5: Integrator2-style progressive preview driven through the C ABI exactly as GPUResponsiveIntegrator::render
+    does per frame: new camera -> mtsb_render_set_camera -> clear -> one 1-spp pass -> film into (pinned) host memory.
+    frames/s over `frames` frames with the camera moving 1 degree every frame; time-to-first-frame = latency from the
+    camera change to the complete 1-spp film in host memory (every frame here is a first frame)."""
+    B = pkg.binding
+    sc = sd.upload(ctx, B.BUILDER_PLOC)
+    rd = B.Render(sc, sd.camera(), sd.film(channels=4), sd.integrator_desc(), seed=1)    # ERGBA target of im-mts
+    shape = rd.film_shape()
+    pin = B.PinnedArray(shape, np.float32)
+    cams = [orbit(sd, float(k % 360)) for k in range(frames + warmup)]
+    lat = []
+    for k in range(frames + warmup):
+        if k == warmup:
+            t_start = time.perf_counter()
+        t0 = time.perf_counter()
+        rd.set_camera(cams[k])
+        rd.clear()
+        rd.render_pass(k, 1, 1)
+        rd.film_to_host(out=pin.array)
+        if k >= warmup:
+            lat.append((time.perf_counter() - t0) * 1e3)
+    total = time.perf_counter() - t_start
+    st = rd.stats()
+    lat = np.array(lat)
+    out = {"frames": frames, "fps": frames / total, "time_to_first_frame_ms": float(np.median(lat)), "latency_ms_p99": float(np.percentile(lat, 99)),
+           "latency_ms_max": float(lat.max()), "width": sd.sensor["width"], "height": sd.sensor["height"], "spp_per_frame": 1,
+           "samples_per_s": sd.sensor["width"] * sd.sensor["height"] * frames / total, "d2h_bytes_per_frame": int(pin.array.nbytes),
+           "launches_last_frame": st["launches"], "camera": "orbit 1 degree per frame about Y; BVH never rebuilt (camera = kernel parameters)"}
+    pin.free()
+    rd.close()
+    sc.close()
+    return out
+
+
 def cpu_reference(pkg, sd_small, threads):
     """The reference's own renderer (oracle/_ref/mitsuba -C) on the host cores, bounded sample of config 1."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -83,26 +169,35 @@ def cpu_reference(pkg, sd_small, threads):
             "sample": "config 1 at %d spp (of 64), mitsuba -C, 'Render time' %.3f s" % (sd_small.sampler["spp"], t)}
 
 
-def run(pkg, ctx, stream, configs=(1, 3), cpu=True):
+def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024):
     S = pkg.scenes
     out = {}
-    if 1 in configs:
+    if 1 in configs and rank == 0:
         out["config1_cornell_512x512_64spp"] = render_config(pkg, ctx, stream, S.cornell_box(512, 512, spp=64, max_depth=5), 64)
         if cpu:
             out["config1_cpu_reference"] = cpu_reference(pkg, S.cornell_box(512, 512, spp=16, max_depth=5), os.cpu_count() or 1)
-    if 3 in configs:
+    sd = None
+    if {3, 4, 5} & set(configs):
         t0 = time.perf_counter()
         sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian")
         gen_s = time.perf_counter() - t0
+    if 3 in configs and rank == 0:
         r = render_config(pkg, ctx, stream, sd, 256, warmup=1)
         r["scene_generation_s"] = gen_s
         out["config3_spherefield_10Mtri_1920x1080_256spp"] = r
+    if 5 in configs and rank == 0:
+        sd.sensor["width"], sd.sensor["height"] = 1280, 720
+        out["config5_interactive_1280x720_1spp"] = render_config5(pkg, ctx, stream, sd)
+    if 4 in configs:
+        sd.sensor["width"], sd.sensor["height"] = 3840, 2160
+        out["config4_spherefield_3840x2160_%dspp" % spp4] = render_config4(pkg, ctx, stream, sd, spp4, rank, world, comm)
     return out
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, nargs="*", default=[1, 3])
+    ap.add_argument("--config", type=int, nargs="*", default=[1, 3, 5])
+    ap.add_argument("--spp4", type=int, default=1024)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     import torch
@@ -110,4 +205,4 @@ if __name__ == "__main__":
     ctx = pkg.binding.Context(0)
     torch.cuda.set_device(0)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", 0))
-    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu)))
+    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4)))

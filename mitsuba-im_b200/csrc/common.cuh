@@ -111,6 +111,7 @@ struct SceneDev {
 	float    emitterNorm;        // DiscreteDistribution normalisation (1/sum of weights)
 	V3 aabbMin, aabbMax;         // enlarged kd-tree AABB (gkdtree.h:1217-1220)
 	unsigned long long *counters; // optional traversal counters (nodes, tris, rays) or NULL
+	int triMinLanes;             // triangle phase: lanes needed for a second/third round in one iteration (trace.cuh)
 };
 
 // ----------------------------------------------------------------------------- RAII device buffer

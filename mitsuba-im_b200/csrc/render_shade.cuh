@@ -94,8 +94,12 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 			const uint32_t btype = bsdf_type(bsdf);
 			const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);   // DirectSamplingRecord(its), records.inl:160-164
 			// ---- emitter sampling (:171-199)
-			if ((btype & B_SMOOTH) && S.emitterCount > 0) {
-				float sx, sy; next2D(rs, sx, sy);
+			// MIDirectIntegrator draws the emitter sample before it looks at the BSDF type (direct.cpp:211-215); MIPathTracer
+			// only inside the smooth branch (path.cpp:171-176) — the stream position must follow the integrator in use
+			float sx = 0, sy = 0;
+			const bool smooth = (btype & B_SMOOTH) && S.emitterCount > 0;
+			if (smooth || integ.type == MTSB_INTEGRATOR_DIRECT) next2D(rs, sx, sy);
+			if (smooth) {
 				DirectSample ds;
 				const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
 				if (!is_zero(value)) {
@@ -114,7 +118,7 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 				}
 			}
 			// ---- BSDF sampling (:205-222)
-			float sx, sy; next2D(rs, sx, sy);
+			next2D(rs, sx, sy);
 			BsdfSample bs;
 			const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, bs);
 			if (is_zero(bsdfWeight)) alive = false;

@@ -5,6 +5,7 @@
 // in the order shapes are added (that order defines shape indices and the global primitive index, as
 // m_shapeMap does), uploaded once, and every derived structure is built on the device.
 #include "scene.cuh"
+#include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
 #include <math.h>
@@ -282,6 +283,9 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	D.shapeCount = (uint32_t) scene->shapes.size(); D.emitterCount = (uint32_t) scene->emitters.size();
 	D.envEmitter = envEmitter; D.emitterNorm = emitterNorm;
 	D.counters = nullptr;
+	// tuning knob of the triangle phase (trace.cuh); MTSB_TRI_MIN_LANES overrides for experiments
+	D.triMinLanes = 8;
+	if (const char *e = getenv("MTSB_TRI_MIN_LANES")) { const int v = atoi(e); if (v >= 1 && v <= 33) D.triMinLanes = v; }
 
 	MTSB_CHECK(build_bvh(ctx, D, scene->primCount, builder, scene->bvh));
 	D.nodes = scene->bvh.nodes.ptr; D.tris = scene->bvh.tris.ptr;

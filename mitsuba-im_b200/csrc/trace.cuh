@@ -222,8 +222,8 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 		}
 		if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
 
-		// ---- (2) node phase
-		if (active) {
+		// ---- (2) node phase (lanes still holding untested triangles sit this one out: they drain one per iteration)
+		if (active && tg.y == 0) {
 			if (ng.y > 0x00ffffffu) {
 				const uint32_t bit = 31u - __clz(ng.y);
 				const uint32_t imask = ng.y & 0xffu;
@@ -242,27 +242,35 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 			}
 		}
 
-		// ---- (3) triangle phase
-		while (active && tg.y) {
-			const uint32_t bit = __ffs(tg.y) - 1;
-			tg.y &= tg.y - 1;
-			const uint32_t slot = tg.x + bit;
-			const float4 *tp = S.tris + (size_t) slot * 3;
-			const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-			if (COUNT) ++nTris;
-			float t, u, v; bool h;
-			if (__float_as_uint(a.x) != K_NO_TRIANGLE)
-				h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
-			else
-				h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
-			if (h) {
-				hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
-				if (ANY) { tg.y = 0; ng = make_uint2(0u, 0u); st.n = 0; }
+		// ---- (3) triangle phase: ONE triangle per lane per round.  The first round runs whenever any lane has a triangle;
+		// further rounds only while at least triMinLanes lanes still have one — draining a long leaf with two or three
+		// lanes active (the old while-loop: 2.5 of 32 threads, profiles/r01) costs more issue slots than letting those
+		// lanes skip a node step.  Round count is warp-uniform, so the loop stays convergent.
+		for (bool first = true; ; first = false) {
+			const bool want = active && tg.y;
+			const unsigned wm = __ballot_sync(FULL, want);
+			if (wm == 0 || (!first && __popc(wm) < S.triMinLanes)) break;
+			if (want) {
+				const uint32_t bit = __ffs(tg.y) - 1;
+				tg.y &= tg.y - 1;
+				const uint32_t slot = tg.x + bit;
+				const float4 *tp = S.tris + (size_t) slot * 3;
+				const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+				if (COUNT) ++nTris;
+				float t, u, v; bool h;
+				if (__float_as_uint(a.x) != K_NO_TRIANGLE)
+					h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
+				else
+					h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
+				if (h) {
+					hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
+					if (ANY) { tg.y = 0; ng = make_uint2(0u, 0u); st.n = 0; }
+				}
 			}
 		}
 
 		// ---- (4) pop or finish
-		if (active && ng.y <= 0x00ffffffu) {
+		if (active && tg.y == 0 && ng.y <= 0x00ffffffu) {
 			if (st.n == 0) { io.store(idx, found, hit, o, d); active = false; }
 			else ng = st.pop();
 		}

@@ -145,8 +145,18 @@ public:
 		float *dst = block->getBitmap()->getFloatData();
 		const size_t n = (size_t) block->getBitmap()->getSize().x * block->getBitmap()->getSize().y * block->getChannelCount();
 		uint64_t st[8] = { 0 }, tot[8] = { 0 };
+		// the per-GPU films meet on the device: one NCCL reduce into GPU 0's film, then a single D2H into the ImageBlock
+		if (m_gpus > 1) {
+			if (m_comms.empty()) {
+				std::vector<mtsb_ctx *> ctxs(m_gpus);
+				for (int g = 0; g < m_gpus; ++g) ctxs[g] = m_devices[g].ctx;
+				m_comms.assign(m_gpus, (mtsb_comm *) NULL);
+				MTSB_CALL(mtsb_comm_create_all(ctxs.data(), m_gpus, m_comms.data()));
+			}
+			MTSB_CALL(mtsb_film_reduce_all(renders.data(), m_comms.data(), m_gpus, 0));
+		}
+		MTSB_CALL(mtsb_film_to_host(renders[0], dst, n, 0));
 		for (int g = 0; g < m_gpus; ++g) {
-			MTSB_CALL(mtsb_film_to_host(renders[g], dst, n, g > 0));
 			mtsb_render_stats(renders[g], st);
 			for (int i = 0; i < 8; ++i) tot[i] += st[i];
 			mtsb_render_destroy(renders[g]);
@@ -176,6 +186,8 @@ public:
 	volatile bool m_cancel;
 	ref<Mutex> m_mutex;
 	std::vector<GPUDevice> m_devices;
+	std::vector<mtsb_comm *> m_comms;
+	virtual ~GPUPathTracer() { for (size_t i = 0; i < m_comms.size(); ++i) mtsb_comm_destroy(m_comms[i]); }
 };
 
 MTS_NAMESPACE_END
