@@ -169,7 +169,7 @@ def cpu_reference(pkg, sd_small, threads):
             "sample": "config 1 at %d spp (of 64), mitsuba -C, 'Render time' %.3f s" % (sd_small.sampler["spp"], t)}
 
 
-def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024):
+def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024, spp3=256):
     S = pkg.scenes
     out = {}
     if 1 in configs and rank == 0:
@@ -182,9 +182,9 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian")
         gen_s = time.perf_counter() - t0
     if 3 in configs and rank == 0:
-        r = render_config(pkg, ctx, stream, sd, 256, warmup=1)
+        r = render_config(pkg, ctx, stream, sd, spp3, warmup=1)
         r["scene_generation_s"] = gen_s
-        out["config3_spherefield_10Mtri_1920x1080_256spp"] = r
+        out["config3_spherefield_10Mtri_1920x1080_%dspp" % spp3] = r
     if 5 in configs and rank == 0:
         sd.sensor["width"], sd.sensor["height"] = 1280, 720
         out["config5_interactive_1280x720_1spp"] = render_config5(pkg, ctx, stream, sd)
@@ -198,6 +198,7 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", type=int, nargs="*", default=[1, 3, 5])
     ap.add_argument("--spp4", type=int, default=1024)
+    ap.add_argument("--spp3", type=int, default=256, help="samples per pixel of config 3 (BASELINE: 256; smaller only for ncu runs)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     import torch
@@ -205,4 +206,4 @@ if __name__ == "__main__":
     ctx = pkg.binding.Context(0)
     torch.cuda.set_device(0)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", 0))
-    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4)))
+    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4, spp3=args.spp3)))

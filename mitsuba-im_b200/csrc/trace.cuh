@@ -69,25 +69,37 @@ __device__ __forceinline__ bool rect_test(const RectRec &r, const V3 &o, const V
 	return false;
 }
 
+// Byte j of `word` placed in bits 8..15 of the mantissa of 1.0f: 1 + q * 2^-15, exact, ONE PRMT and no arithmetic.
+// The slab distance q * step * idir + (p - o) * idir is then a single FMA with the 2^15 folded into the scale and
+// the "1 +" folded into the offset (node_test).  `one` = 0x3F800000 comes from the kernel parameter bank: PRMT has a single immediate slot, and with both the
+// selector and the pattern constant ptxas re-materialises one of them before every PRMT (48 extra moves per node).
+__device__ __forceinline__ float q_to_unit(uint32_t word, uint32_t one, int j) {
+	return __uint_as_float(__byte_perm(word, one, 0x7604u | ((uint32_t) j << 4)));
+}
+
 // Tests the 8 quantised child boxes of a node; returns the hit mask (bits 24..31 internal children in
-// traversal priority order, bits 0..23 triangles).
+// traversal priority order, bits 0..23 triangles).  Conservative by construction: every near distance is lowered and
+// every far distance raised by a bound on the rounding error of the offset (a few ulps of |scale| + |offset|).
 __device__ __forceinline__ uint32_t node_test(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
-		const uint4 n4, const V3 &o, const V3 &idir, uint32_t octinv4, float tmin, float tmax) {
+		const uint4 n4, const V3 &o, const V3 &idir, uint32_t octinv4, float tmin, float tmax, uint32_t one) {
 	const uint32_t e = n0.w;
-	const float sx = __uint_as_float((e & 0xffu) << 23) * idir.x;
-	const float sy = __uint_as_float(((e >> 8) & 0xffu) << 23) * idir.y;
-	const float sz = __uint_as_float(((e >> 16) & 0xffu) << 23) * idir.z;
-	const float bx = (__uint_as_float(n0.x) - o.x) * idir.x;
-	const float by = (__uint_as_float(n0.y) - o.y) * idir.y;
-	const float bz = (__uint_as_float(n0.z) - o.z) * idir.z;
+	// 2^(e + 15) * idir: the scale per unit of q_to_unit's mantissa step
+	const float sx = __uint_as_float(((e & 0xffu) << 23) + (15u << 23)) * idir.x;
+	const float sy = __uint_as_float((((e >> 8) & 0xffu) << 23) + (15u << 23)) * idir.y;
+	const float sz = __uint_as_float((((e >> 16) & 0xffu) << 23) + (15u << 23)) * idir.z;
+	const float px = (__uint_as_float(n0.x) - o.x) * idir.x, py = (__uint_as_float(n0.y) - o.y) * idir.y,
+	            pz = (__uint_as_float(n0.z) - o.z) * idir.z;
+	const float mx = (fabsf(sx) + fabsf(px)) * 4.8e-7f, my = (fabsf(sy) + fabsf(py)) * 4.8e-7f, mz = (fabsf(sz) + fabsf(pz)) * 4.8e-7f;
+	const float bnx = (px - sx) - mx, bny = (py - sy) - my, bnz = (pz - sz) - mz;
+	const float bfx = (px - sx) + mx, bfy = (py - sy) + my, bfz = (pz - sz) + mz;
 	uint32_t hitmask = 0;
 	#pragma unroll
 	for (int g = 0; g < 2; ++g) {
 		const uint32_t meta4 = g ? n1.w : n1.z;
 		const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
 		const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
-		const uint32_t bitIndex4 = (meta4 ^ (octinv4 & innerMask4)) & 0x1f1f1f1fu;
-		const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+		// per child byte: [unary triangle count : 3 | bit index : 5]; SHF.L.W uses the low 5 bits of the shift amount
+		const uint32_t m4 = meta4 ^ (octinv4 & innerMask4 & 0x07070707u);
 		const uint32_t qlox = g ? n2.y : n2.x, qloy = g ? n2.w : n2.z, qloz = g ? n3.y : n3.x;
 		const uint32_t qhix = g ? n3.w : n3.z, qhiy = g ? n4.y : n4.x, qhiz = g ? n4.w : n4.z;
 		const uint32_t xn = idir.x < 0 ? qhix : qlox, xf = idir.x < 0 ? qlox : qhix;
@@ -95,15 +107,14 @@ __device__ __forceinline__ uint32_t node_test(const uint4 n0, const uint4 n1, co
 		const uint32_t zn = idir.z < 0 ? qhiz : qloz, zf = idir.z < 0 ? qloz : qhiz;
 		#pragma unroll
 		for (int j = 0; j < 4; ++j) {
-			const float tnx = fmaf(byte_to_float(xn, j), sx, bx), tfx = fmaf(byte_to_float(xf, j), sx, bx);
-			const float tny = fmaf(byte_to_float(yn, j), sy, by), tfy = fmaf(byte_to_float(yf, j), sy, by);
-			const float tnz = fmaf(byte_to_float(zn, j), sz, bz), tfz = fmaf(byte_to_float(zf, j), sz, bz);
+			const float tnx = fmaf(q_to_unit(xn, one, j), sx, bnx), tfx = fmaf(q_to_unit(xf, one, j), sx, bfx);
+			const float tny = fmaf(q_to_unit(yn, one, j), sy, bny), tfy = fmaf(q_to_unit(yf, one, j), sy, bfy);
+			const float tnz = fmaf(q_to_unit(zn, one, j), sz, bnz), tfz = fmaf(q_to_unit(zf, one, j), sz, bfz);
 			const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-			const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax)) * 1.0000005f;  // conservative (Ize 2013)
+			const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
 			if (cmin <= cmax) {
-				const uint32_t bits = (childBits4 >> (8 * j)) & 0xffu;
-				const uint32_t idx = (bitIndex4 >> (8 * j)) & 0xffu;
-				hitmask |= bits << idx;
+				const uint32_t m = (m4 >> (8 * j)) & 0xffu;
+				hitmask |= (m >> 5) << (m & 31u);
 			}
 		}
 	}
@@ -192,6 +203,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 	unsigned long long idx = 0;
 	TravStack st; st.sh = shStack; st.n = 0;
 	unsigned nNodes = 0, nTris = 0;
+	const uint32_t one = S.oneBits;                 // 1.0f bit pattern from the parameter bank (see q_to_unit)
 
 	for (;;) {
 		// ---- (1) refill idle lanes
@@ -234,7 +246,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 				const uint4 *np = S.nodes + (size_t) (ng.x + rel) * 5;
 				const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
 				if (COUNT) ++nNodes;
-				const uint32_t hm = node_test(n0, n1, n2, n3, n4, o, idir, octinv4, tmin, hit.t);
+				const uint32_t hm = node_test(n0, n1, n2, n3, n4, o, idir, octinv4, tmin, hit.t, one);
 				ng = make_uint2(n1.x, (hm & 0xff000000u) | (n0.w >> 24));
 				tg = make_uint2(n1.y, hm & 0x00ffffffu);
 			} else {
