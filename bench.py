@@ -123,7 +123,7 @@ def reference_arm(args, rank, world):
             "config": {"workload": "config2: closest-hit, 1310720-triangle displaced icosphere, incoherent chord rays"},
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def cpu_baseline(S, sd, cores):
@@ -148,7 +148,29 @@ def cpu_baseline(S, sd, cores):
             "kd_build_ms": tm.get("build_ms")}
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Routes fd 1 to stderr for the rest of the run so that library chatter (NCCL prints its version banner to stdout
+    when NCCL_DEBUG=VERSION) cannot land beside the ONE JSON line, which emit() writes to the original stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -338,7 +360,7 @@ def main():
             "cpu_baseline": cpu,
             "detail": dict(detail, hit_rate=hit_rate, build=bstats),
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     pin_r.free()
     pin_h.free()
     sc.close()
