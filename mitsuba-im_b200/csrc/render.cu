@@ -97,11 +97,11 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 // ---------------------------------------------------------------------------------------------------
 struct ExtendIO {
 	SceneDev S; PathState ps; const uint32_t *queue;
-	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
 		const uint32_t slot = queue[i];
 		const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot];
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
-		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax)) return true;
+		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax, rcp)) return true;
 		ps.hit[slot] = make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
 		return false;
 	}
@@ -121,10 +121,10 @@ struct ConnectIO {
 		L.x += c.x; L.y += c.y; L.z += c.z;
 		ps.L[slot] = L;
 	}
-	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
 		const float4 r0 = ps.shO[i], r1 = ps.shD[i];
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
-		if (clip_ray(S, o, d, r0.w, r1.w, false, tmin, tmax)) return true;
+		if (clip_ray(S, o, d, r0.w, r1.w, false, tmin, tmax, rcp)) return true;
 		add(i);                 // nothing can occlude a segment outside the scene box
 		return false;
 	}
@@ -133,7 +133,7 @@ struct ConnectIO {
 	}
 };
 
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
 extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *count) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	ExtendIO io; io.S = S; io.ps = ps; io.queue = queue;
@@ -142,7 +142,7 @@ extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *c
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
 }
 
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
 connect_kernel(SceneDev S, PathState ps, const uint32_t *count) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	ConnectIO io; io.S = S; io.ps = ps;

@@ -29,10 +29,10 @@ struct BatchIO {
 			((mtsb_surface *) out)[i] = rec;
 		}
 	}
-	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax) const {
+	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
 		const float4 r0 = __ldg(rays + 2 * i), r1 = __ldg(rays + 2 * i + 1);
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
-		if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, tmin, tmax)) return true;
+		if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, tmin, tmax, rcp)) return true;
 		write_miss(i);
 		return false;
 	}
@@ -61,7 +61,7 @@ struct BatchIO {
 };
 
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
 trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, void *__restrict__ out,
 		unsigned long long *__restrict__ workCounter) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];

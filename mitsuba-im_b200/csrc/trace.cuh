@@ -34,12 +34,12 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, int j) {
 // Reference Wald test, evaluated without FMA contraction in source order (triaccel.h:96-158).
 __device__ __forceinline__ bool tri_test(const float4 a, const float4 b, const float4 c,
 		const V3 &o, const V3 &d, float mint, float maxt, float &t, float &u, float &v) {
-	uint32_t k = __float_as_uint(a.x);
-	float o_u, o_v, o_k, d_u, d_v, d_k;
-	if (k == 0)      { o_u = o.y; o_v = o.z; o_k = o.x; d_u = d.y; d_v = d.z; d_k = d.x; }
-	else if (k == 1) { o_u = o.z; o_v = o.x; o_k = o.y; d_u = d.z; d_v = d.x; d_k = d.y; }
-	else if (k == 2) { o_u = o.x; o_v = o.y; o_k = o.z; d_u = d.x; d_v = d.y; d_k = d.z; }
-	else return false;
+	const uint32_t k = __float_as_uint(a.x);
+	if (k > 2u) return false;                       // degenerate triangle (k = 3, triaccel.h:77-80)
+	// axis permutation as selects, not as three divergent branches (each ran with ~3 lanes, profiles/r01b)
+	const bool k0 = k == 0, k1 = k == 1;
+	const float o_u = k0 ? o.y : (k1 ? o.z : o.x), o_v = k0 ? o.z : (k1 ? o.x : o.y), o_k = k0 ? o.x : (k1 ? o.y : o.z);
+	const float d_u = k0 ? d.y : (k1 ? d.z : d.x), d_v = k0 ? d.z : (k1 ? d.x : d.y), d_k = k0 ? d.x : (k1 ? d.y : d.z);
 	const float n_u = a.y, n_v = a.z, n_d = a.w;
 	float num = __fsub_rn(__fsub_rn(__fsub_rn(n_d, __fmul_rn(o_u, n_u)), __fmul_rn(o_v, n_v)), o_k);
 	float den = __fadd_rn(__fadd_rn(__fmul_rn(d_u, n_u), __fmul_rn(d_v, n_v)), d_k);
@@ -143,8 +143,9 @@ struct TravStack {
 // overloads (src/librender/skdtree.cpp:112-142, 207-226; AABB::rayIntersect include/mitsuba/core/aabb.h:308-338).
 // floorEps: the closest-hit overload floors the epsilon scale at Epsilon, the other two do not.
 __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V3 &d, float rayMint, float rayMaxt,
-		bool floorEps, float &mint, float &maxt) {
+		bool floorEps, float &mint, float &maxt, V3 &rcpOut) {
 	float nearT = -INFINITY, farT = INFINITY;
+	float rcps[3] = { 0.0f, 0.0f, 0.0f };
 	#pragma unroll
 	for (int i = 0; i < 3; ++i) {
 		const float origin = comp(o, i), dir = comp(d, i);
@@ -153,6 +154,7 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 			if (origin < minVal || origin > maxVal) return false;
 		} else {
 			const float rcp = __fdiv_rn(1.0f, dir);
+			rcps[i] = rcp;
 			float t1 = __fmul_rn(__fsub_rn(minVal, origin), rcp);
 			float t2 = __fmul_rn(__fsub_rn(maxVal, origin), rcp);
 			if (t1 > t2) { float tmp = t1; t1 = t2; t2 = tmp; }
@@ -167,6 +169,7 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 		if (floorEps) m = fmaxf(m, MTS_EPSILON);
 		rayMinT = __fmul_rn(rayMinT, m);
 	}
+	rcpOut = v3(rcps[0], rcps[1], rcps[2]);
 	mint = nearT; maxt = farT;
 	if (rayMinT > mint) mint = rayMinT;
 	if (rayMaxt < maxt) maxt = rayMaxt;
@@ -183,7 +186,7 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 // exhausted pop the stack or finish.  ANY=false: closest hit (shrinks hit.t); ANY=true: first accepted hit ends the ray.
 //
 // IO supplies the rays and consumes the records:
-//   bool IO::load(i, o, d, tmin, tmax)   -> false if the ray needs no traversal (IO has already written a miss)
+//   bool IO::load(i, o, d, tmin, tmax, rcp) -> rcp = 1/d from clip_ray; false if the ray needs no traversal (IO has already written a miss)
 //   void IO::store(i, found, hit, o, d)
 #ifndef MTSB_FETCH_MIN_IDLE
 #define MTSB_FETCH_MIN_IDLE 4
@@ -217,11 +220,12 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 				idx = base + __popc(idleMask & ltMask);
 				if (idx < n) {
 					float tmax;
-					if (io.load(idx, o, d, tmin, tmax)) {
-						const float tiny = 1e-18f;
-						idir.x = 1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-						idir.y = 1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-						idir.z = 1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+					if (io.load(idx, o, d, tmin, tmax, idir)) {
+						// idir = the exact reciprocals clip_ray already computed; axis-parallel components are clamped
+						const float tiny = 1e-18f, big = 1e18f;
+						if (!(fabsf(d.x) > tiny)) idir.x = copysignf(big, d.x);
+						if (!(fabsf(d.y) > tiny)) idir.y = copysignf(big, d.y);
+						if (!(fabsf(d.z) > tiny)) idir.z = copysignf(big, d.z);
 						octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
 						octinv4 = octinv * 0x01010101u;
 						ng = make_uint2(0u, 0x80000000u); tg = make_uint2(0u, 0u);
