@@ -332,13 +332,22 @@ def main():
         scene_bytes = bstats["node_bytes"] + bstats["tri_bytes"]
         algo_bytes = n * BYTES_PER_RAY_CLOSEST + scene_bytes
         achieved = algo_bytes / (kern_ms * 1e-3) / 1e9
-        traffic = None
+        traffic, issue = None, None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
+        if os.path.exists(tp) and n == N_RAYS:
             try:
-                traffic = json.load(open(tp)).get("trace_closest_bytes_per_launch")
+                tj = json.load(open(tp))
+                traffic = tj.get("trace_closest_bytes_per_launch")
+                # the bound that actually binds this kernel: warp instructions issued (ncu smsp__inst_executed.sum of the
+                # same launch on the same rays) against SMs x 4 schedulers x max SM clock
+                props = torch.cuda.get_device_properties(local)
+                issue_peak = props.multi_processor_count * 4 * (clocks.get("sm_max_mhz") or 1965.0) * 1e6
+                inst = tj.get("trace_closest_warp_inst_per_launch")
+                if inst:
+                    issue = {"warp_inst_per_launch": inst, "achieved_per_s": inst / (kern_ms * 1e-3), "peak_per_s": issue_peak,
+                             "frac": inst / (kern_ms * 1e-3) / issue_peak, "source": tj.get("source")}
             except Exception:
-                traffic = None
+                traffic, issue = None, None
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             cpu = cpu_baseline(S, sd, os.cpu_count() or 1)
@@ -356,7 +365,7 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>", "kernel_ms": kern_ms,
                          "algorithmic_bytes": algo_bytes, "nodes_per_ray": nodes_per_ray, "prim_tests_per_ray": prims_per_ray,
-                         "traversal_bytes_per_ray": nodes_per_ray * 80 + prims_per_ray * 48 + 48},
+                         "traversal_bytes_per_ray": nodes_per_ray * 80 + prims_per_ray * 48 + 48, "issue": issue},
             "cpu_baseline": cpu,
             "detail": dict(detail, hit_rate=hit_rate, build=bstats),
         }

@@ -28,9 +28,12 @@ def render_config(pkg, ctx, stream, sd, spp, warmup=1, builder=None):
     upload_s = time.perf_counter() - t0
     rd = B.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=1)
     w, h = sd.sensor["width"], sd.sensor["height"]
-    for _ in range(warmup):
+    # warm-up: at least `warmup` short passes and at least 0.3 s of rendering, so that clocks and caches are in steady state
+    t_w, n_w = time.perf_counter(), 0
+    while n_w < max(warmup, 3) or time.perf_counter() - t_w < 0.3:
         rd.render_pass(0, min(spp, 4), spp)
-    rd.sync()
+        rd.sync()
+        n_w += 1
     rd.clear()
     rd.sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

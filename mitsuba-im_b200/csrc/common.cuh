@@ -112,6 +112,7 @@ struct SceneDev {
 	V3 aabbMin, aabbMax;         // enlarged kd-tree AABB (gkdtree.h:1217-1220)
 	unsigned long long *counters; // optional traversal counters (nodes, tris, rays) or NULL
 	uint32_t oneBits;            // 0x3F800000, read as a constant-bank operand by the box test (trace.cuh: q_to_unit)
+	int fetchMinIdle;            // idle lanes a warp waits for before it pulls new rays from the work counter
 	int triMinLanes;             // triangle phase: lanes needed for a second/third round in one iteration (trace.cuh)
 };
 

@@ -286,6 +286,8 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	// tuning knob of the triangle phase (trace.cuh); MTSB_TRI_MIN_LANES overrides for experiments
 	D.triMinLanes = 8;
 	D.oneBits = 0x3F800000u;
+	D.fetchMinIdle = 8;
+	if (const char *e = getenv("MTSB_FETCH_MIN_IDLE")) { const int v = atoi(e); if (v >= 1 && v <= 32) D.fetchMinIdle = v; }
 	if (const char *e = getenv("MTSB_TRI_MIN_LANES")) { const int v = atoi(e); if (v >= 1 && v <= 33) D.triMinLanes = v; }
 
 	MTSB_CHECK(build_bvh(ctx, D, scene->primCount, builder, scene->bvh));

@@ -212,7 +212,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 		// ---- (1) refill idle lanes
 		const unsigned idleMask = __ballot_sync(FULL, !active);
 		const unsigned nIdle = __popc(idleMask);
-		if (!exhausted && nIdle >= MTSB_FETCH_MIN_IDLE) {
+		if (!exhausted && nIdle >= (unsigned) S.fetchMinIdle) {
 			unsigned long long base = 0;
 			if (lane == 0) base = atomicAdd(workCounter, (unsigned long long) nIdle);
 			base = __shfl_sync(FULL, base, 0);

@@ -70,6 +70,7 @@ if __name__ == "__main__":
     os.makedirs(PROF, exist_ok=True)
     launches("launches_trace.csv", tag)
     launches("launches_render.csv", tag)
+    launches("launches_c3.csv", tag)
     t = full("prof_trace.ncu-rep", tag, "trace")
     full("prof_render.ncu-rep", tag, "render")
     if t:
