@@ -133,7 +133,7 @@ struct ConnectIO {
 	}
 };
 
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *count) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	ExtendIO io; io.S = S; io.ps = ps; io.queue = queue;
@@ -142,7 +142,7 @@ extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *c
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
 }
 
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 connect_kernel(SceneDev S, PathState ps, const uint32_t *count) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	ConnectIO io; io.S = S; io.ps = ps;

@@ -30,7 +30,7 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut) {
 	cudaStream_t st = ctx->stream;
 	PathState &ps = r->ps;
 	uint32_t *cnt = ps.counters;       // [0] queue A count, [1] queue B count, [2] shadow count
-	const unsigned traceGrid = (unsigned) ctx->smCount * 8;
+	const unsigned traceGrid = (unsigned) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM;
 	SceneDev S = scene->dev; S.counters = nullptr;
 
 	MTSB_CUDA(cudaMemsetAsync(cnt, 0, 4 * sizeof(uint32_t), st));

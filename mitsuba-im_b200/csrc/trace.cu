@@ -61,7 +61,7 @@ struct BatchIO {
 };
 
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, 8)
+__global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, void *__restrict__ out,
 		unsigned long long *__restrict__ workCounter) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
@@ -80,7 +80,7 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 	if (n == 0) return 0;
 	mtsb_ctx *ctx = scene->ctx;
 	MTSB_CUDA(cudaMemsetAsync(dWork, 0, sizeof(unsigned long long), st));
-	const int blocksPerSm = 8;
+	const int blocksPerSm = MTSB_TRACE_BLOCKS_PER_SM;
 	unsigned grid = (unsigned) std::min<size_t>((size_t) ctx->smCount * blocksPerSm, (n + MTSB_TRACE_BLOCK - 1) / MTSB_TRACE_BLOCK);
 	SceneDev S = scene->dev;
 	S.counters = count ? scene->dCounters.ptr : nullptr;

@@ -23,6 +23,9 @@ namespace mtsb {
 #define MTSB_STACK_SHARED 8      // stack entries per thread kept in shared memory
 #define MTSB_STACK_LOCAL  56     // overflow entries in local memory
 #define MTSB_TRACE_BLOCK  128    // threads per block of every traversal kernel
+#ifndef MTSB_TRACE_BLOCKS_PER_SM
+#define MTSB_TRACE_BLOCKS_PER_SM 8   // resident CTAs per SM of the persistent traversal grids (bounds the register budget)
+#endif
 
 struct HitRec { float t, u, v; uint32_t slot; };
 
