@@ -29,9 +29,11 @@ def render_config(pkg, ctx, stream, sd, spp, warmup=1, builder=None):
     rd = B.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=1)
     w, h = sd.sensor["width"], sd.sensor["height"]
     # warm-up: at least `warmup` short passes and at least 0.3 s of rendering, so that clocks and caches are in steady state
+    # (warm-up passes are large enough to reach the full path-state capacity, so no allocation lands in the timed pass)
+    spp_w = min(spp, max(4, -(-(1 << 23) // (w * h)) + 1))
     t_w, n_w = time.perf_counter(), 0
     while n_w < max(warmup, 3) or time.perf_counter() - t_w < 0.3:
-        rd.render_pass(0, min(spp, 4), spp)
+        rd.render_pass(0, spp_w, spp)
         rd.sync()
         n_w += 1
     rd.clear()

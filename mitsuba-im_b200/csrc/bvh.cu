@@ -449,6 +449,36 @@ __global__ void triaccel_kernel(SceneDev S, uint32_t slotCount, const uint32_t *
 }
 
 // ---------------------------------------------------------------------------------------------------
+// 6. de-indexed shading records in slot order (layout in common.cuh: SceneDev::verts)
+// ---------------------------------------------------------------------------------------------------
+__global__ void shading_record_kernel(SceneDev S, uint32_t slotCount, const uint32_t *slotPrim, float4 *verts) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= slotCount) return;
+	const uint32_t prim = slotPrim[i];
+	const uint32_t s = find_shape(S.shapes, S.shapeCount, prim);
+	const ShapeRec sh = S.shapes[s];
+	float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0, r3 = r0, r4 = r0;
+	uint32_t local = 0;
+	if (sh.type == SHAPE_MESH) {
+		local = prim - sh.primOffset;
+		const uint32_t *ix = S.indices + (size_t) (sh.triBase + local) * 3;
+		const uint32_t i0 = sh.vtxBase + ix[0], i1 = sh.vtxBase + ix[1], i2 = sh.vtxBase + ix[2];
+		const float *P = S.positions, *N = S.normals;
+		r0 = make_float4(P[i0*3], P[i0*3+1], P[i0*3+2], P[i1*3]);
+		r1 = make_float4(P[i1*3+1], P[i1*3+2], P[i2*3], P[i2*3+1]);
+		r2.x = P[i2*3+2];
+		if (sh.flags & SHAPE_HAS_NORMALS) {
+			r2.y = N[i0*3]; r2.z = N[i0*3+1]; r2.w = N[i0*3+2];
+			r3 = make_float4(N[i1*3], N[i1*3+1], N[i1*3+2], N[i2*3]);
+			r4.x = N[i2*3+1]; r4.y = N[i2*3+2];
+		}
+	}
+	r4.z = __uint_as_float(s); r4.w = __uint_as_float(local);
+	float4 *o = verts + (size_t) i * 5;
+	o[0] = r0; o[1] = r1; o[2] = r2; o[3] = r3; o[4] = r4;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // host driver
 // ---------------------------------------------------------------------------------------------------
 static inline unsigned div_up(size_t a, unsigned b) { return (unsigned) ((a + b - 1) / b); }
@@ -550,6 +580,8 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 	MTSB_CUDA(cudaMemcpyAsync(out.nodes.ptr, nodesTmp.ptr, (size_t) nodeCount * 5 * sizeof(uint4), cudaMemcpyDeviceToDevice, st));
 	MTSB_CHECK(out.tris.alloc((size_t) slotCount * 3));
 	triaccel_kernel<<<div_up(slotCount, 256), 256, 0, st>>>(S, slotCount, slotPrim.ptr, out.tris.ptr);
+	MTSB_CHECK(out.verts.alloc((size_t) slotCount * 5));
+	shading_record_kernel<<<div_up(slotCount, 256), 256, 0, st>>>(S, slotCount, slotPrim.ptr, out.verts.ptr);
 	MTSB_CUDA(cudaGetLastError());
 
 	uint32_t box[6];

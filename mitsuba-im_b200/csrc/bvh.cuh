@@ -7,6 +7,7 @@ namespace mtsb {
 struct BvhResult {
 	DevBuf<uint4>  nodes;   // 5 x uint4 per wide node
 	DevBuf<float4> tris;    // 3 x float4 per leaf slot (TriAccel record)
+	DevBuf<float4> verts;   // 5 x float4 per leaf slot: the triangle's de-indexed vertices + normals + (shape, prim), see surface.cuh
 	uint32_t nodeCount = 0, slotCount = 0, leafCount = 0;
 	int depth = 0;
 	float buildMs = 0, sahCost = 0;

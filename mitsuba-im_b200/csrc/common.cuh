@@ -95,6 +95,10 @@ struct SceneDev {
 	// TriAccel slots in BVH leaf order: 3 x float4 per slot
 	//   [0] = {k (bits), n_u, n_v, n_d}  [1] = {a_u, a_v, b_nu, b_nv}  [2] = {c_nu, c_nv, shapeIndex(bits), primIndex(bits)}
 	const float4 *tris;
+	// de-indexed shading record per slot (leaf order), 5 x float4 = 80 B:
+	//   {p0.xyz p1.x} {p1.yz p2.xy} {p2.z n0.xyz} {n1.xyz n2.x} {n2.yz shape(bits) prim(bits)}
+	// one 80-byte gather instead of the TriAccel tail -> shape -> indices -> 3 positions + 3 normals chain
+	const float4 *verts;
 	const ShapeRec *shapes;
 	const RectRec  *rects;
 	const float    *positions;   // 3 floats per vertex, all meshes

@@ -291,7 +291,7 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	if (const char *e = getenv("MTSB_TRI_MIN_LANES")) { const int v = atoi(e); if (v >= 1 && v <= 33) D.triMinLanes = v; }
 
 	MTSB_CHECK(build_bvh(ctx, D, scene->primCount, builder, scene->bvh));
-	D.nodes = scene->bvh.nodes.ptr; D.tris = scene->bvh.tris.ptr;
+	D.nodes = scene->bvh.nodes.ptr; D.tris = scene->bvh.tris.ptr; D.verts = scene->bvh.verts.ptr;
 	D.nodeCount = scene->bvh.nodeCount; D.slotCount = scene->bvh.slotCount;
 
 	// "Slightly enlarge the bounding box" — include/mitsuba/render/gkdtree.h:1213-1220 (max uses the already moved min)

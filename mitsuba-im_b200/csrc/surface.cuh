@@ -30,16 +30,15 @@ __host__ __device__ inline V3 to_world(const Surf &s, const V3 &v) { return s.s 
 // `slot` indexes the TriAccel array; o,d are the ray (needed for the rectangle's p = ray(t)).
 __device__ inline void fill_surface(const SceneDev &S, uint32_t slot, float t, float bu, float bv,
 		const V3 &o, const V3 &d, Surf &out) {
-	const float4 c = __ldg(S.tris + (size_t) slot * 3 + 2);
-	const uint32_t shapeIdx = __float_as_uint(c.z), prim = __float_as_uint(c.w);
+	// one 80-byte record per slot (SceneDev::verts) instead of TriAccel tail -> shape -> indices -> 6 vertex gathers
+	const float4 *vr = S.verts + (size_t) slot * 5;
+	const float4 q0 = __ldg(vr), q1 = __ldg(vr + 1), q2 = __ldg(vr + 2), q3 = __ldg(vr + 3), q4 = __ldg(vr + 4);
+	const uint32_t shapeIdx = __float_as_uint(q4.z), prim = __float_as_uint(q4.w);
 	const ShapeRec sh = S.shapes[shapeIdx];
 	out.shape = shapeIdx; out.prim = prim;
 	V3 dpdu;
 	if (sh.type == SHAPE_MESH) {
-		const uint32_t *ix = S.indices + (size_t) (sh.triBase + prim) * 3;
-		const uint32_t i0 = sh.vtxBase + ix[0], i1 = sh.vtxBase + ix[1], i2 = sh.vtxBase + ix[2];
-		const float *P = S.positions;
-		const V3 p0 = v3(P[i0*3], P[i0*3+1], P[i0*3+2]), p1 = v3(P[i1*3], P[i1*3+1], P[i1*3+2]), p2 = v3(P[i2*3], P[i2*3+1], P[i2*3+2]);
+		const V3 p0 = v3(q0.x, q0.y, q0.z), p1 = v3(q0.w, q1.x, q1.y), p2 = v3(q1.z, q1.w, q2.x);
 		const float b0 = 1 - bu - bv, b1 = bu, b2 = bv;
 		out.p = p0 * b0 + p1 * b1 + p2 * b2;
 		const V3 side1 = p1 - p0, side2 = p2 - p0;
@@ -48,6 +47,8 @@ __device__ inline void fill_surface(const SceneDev &S, uint32_t slot, float t, f
 		if (!is_zero(faceNormal)) faceNormal /= len;
 		dpdu = side1;
 		if (sh.flags & SHAPE_HAS_UV) {
+			const uint32_t *ix = S.indices + (size_t) (sh.triBase + prim) * 3;
+			const uint32_t i0 = sh.vtxBase + ix[0], i1 = sh.vtxBase + ix[1], i2 = sh.vtxBase + ix[2];
 			const float *T = S.texcoords;
 			const float u0 = T[i0*2], v0 = T[i0*2+1], u1 = T[i1*2], v1 = T[i1*2+1], u2 = T[i2*2], v2 = T[i2*2+1];
 			out.u = u0 * b0 + u1 * b1 + u2 * b2; out.v = v0 * b0 + v1 * b1 + v2 * b2;
@@ -61,8 +62,7 @@ __device__ inline void fill_surface(const SceneDev &S, uint32_t slot, float t, f
 			out.u = b1; out.v = b2;
 		}
 		if (sh.flags & SHAPE_HAS_NORMALS) {
-			const float *N = S.normals;
-			const V3 n0 = v3(N[i0*3], N[i0*3+1], N[i0*3+2]), n1 = v3(N[i1*3], N[i1*3+1], N[i1*3+2]), n2 = v3(N[i2*3], N[i2*3+1], N[i2*3+2]);
+			const V3 n0 = v3(q2.y, q2.z, q2.w), n1 = v3(q3.x, q3.y, q3.z), n2 = v3(q3.w, q4.x, q4.y);
 			out.ns = normalize(n0 * b0 + n1 * b1 + n2 * b2);
 			if (dot(faceNormal, out.ns) < 0) faceNormal = -faceNormal;
 		} else {
