@@ -222,11 +222,19 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
+    # the clock sampler starts before the warm-up (nvidia-smi needs a few hundred ms to deliver its first row, longer on
+    # an 8-GPU box) and the warm-up keeps the same kernel running until the first rows are in, so that the rows recorded
+    # up to the end of the timed region are all taken under this load
     sampler = ClockSampler(local)
     sampler.start()
+    for _ in range(args.warmup):
+        step()
+    t_w = time.perf_counter()
+    while len(sampler.rows) < 2 and time.perf_counter() - t_w < 3.0 and sampler.proc is not None:
+        step()
+        torch.cuda.synchronize()
+    barrier()
+    rows_before = len(sampler.rows)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kern_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     with torch.cuda.stream(stream):
@@ -237,6 +245,11 @@ def main():
             kern_ev[k][1].record(stream)
         e1.record(stream)
     barrier()
+    # keep the load on until at least two rows fall inside/after the timed region (short runs finish between two samples)
+    t_w = time.perf_counter()
+    while len(sampler.rows) < rows_before + 2 and time.perf_counter() - t_w < 1.0 and sampler.proc is not None:
+        step()
+        torch.cuda.synchronize()
     clocks = sampler.stop()
     ms_total = e0.elapsed_time(e1)
     if world > 1:

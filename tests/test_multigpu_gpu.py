@@ -58,3 +58,38 @@ def test_two_gpu_nccl_film_reduce(pkg):
     finally:
         for x in rds + comms + scs + ctxs:
             x.close()
+
+
+def test_config3_scale_properties(pkg, ctx):
+    """BASELINE config-3 scale (10 485 762 triangles, GGX copper + bk7 glass + diffuse ground, area light + constant
+    environment, Gaussian film) at a reduced image size: properties that need no oracle."""
+    S, B, M = pkg.scenes, pkg.binding, pkg.multigpu
+    sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=240, height=136, spp=4, max_depth=8, rfilter="gaussian")
+    sc = sd.upload(ctx, B.BUILDER_PLOC)
+    try:
+        assert sc.primitive_count == 10485763          # 128 x 81 920 + 2 ground triangles + the light rectangle
+        st = sc.build_stats()
+        assert st["nodes"] > 1000000 and st["depth"] < 32
+        rd = B.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=5)
+        rd.render_pass(0, 4, 4)
+        full = rd.film_to_host().astype(np.float64)
+        stats = rd.stats()
+        rd.clear()
+        for r in range(2):
+            M.render_distributed(rd, None, 4, 2, r, 1)
+        split = rd.film_to_host().astype(np.float64)
+        rd.close()
+        assert stats["paths"] == 240 * 136 * 4
+        assert stats["closest_rays"] >= stats["paths"] and 1.0 <= stats["depth_sum"] / stats["paths"] <= 8.0
+        assert np.isfinite(full).all() and (full >= 0).all()
+        # every sample deposits filter weights that sum to ~1 (32-bin Gaussian table, normalised as in rfilter.cpp:37-55)
+        assert abs(full[..., 4].sum() / (240 * 136 * 4) - 1.0) < 2e-2
+        # alpha <= weight everywhere, = weight where every contributing sample hit geometry
+        assert (full[..., 3] <= full[..., 4] * (1 + 1e-5) + 1e-6).all()
+        assert np.allclose(split, full, rtol=5e-5, atol=1e-5)
+        # the ground / spheres / sky all show up: radiance varies, nothing is black overall
+        b = sd.film().border
+        img = full[b:-b, b:-b, 0:3] / np.maximum(full[b:-b, b:-b, 4:5], 1e-9)
+        assert img.mean() > 0.05 and img.std() > 0.01
+    finally:
+        sc.close()
