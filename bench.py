@@ -373,7 +373,7 @@ def main():
                        "parallelism": "rays sharded across %d GPU(s), scene replicated, no collective" % world},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
-                    "ms_per_step": e2e_ms, "api": "mtsb_trace_closest(host pointers), pinned buffers, 2M-ray chunks pipelined over 3 streams"},
+                    "ms_per_step": e2e_ms, "api": "mtsb_trace_closest(host pointers), pinned buffers, 2M-ray chunks pipelined over 3 streams and a 4-buffer ring"},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>", "kernel_ms": kern_ms,

@@ -3,11 +3,13 @@
 // Batched equivalents of the three ShapeKDTree::rayIntersect overloads (src/librender/skdtree.cpp:112-226).
 // Kernels are persistent: one grid sized to the SM count, each warp pulls batches of 32 rays from a global
 // counter (one atomic per warp, broadcast by shuffle), rays and hits move as 16-byte vectors.
-// Host-pointer calls are pipelined in chunks over three streams so that PCIe traffic overlaps traversal.
+// Host-pointer calls are pipelined in 2M-ray chunks over three streams and a four-buffer ring so that PCIe traffic
+// in both directions overlaps traversal.
 #include "scene.cuh"
 #include "trace.cuh"
 #include "surface.cuh"
 #include <algorithm>
+#include <stdlib.h>
 
 namespace mtsb {
 
@@ -95,12 +97,14 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 	return 0;
 }
 
+#define MTSB_PIPE_BUFS 4
 struct TracePipe {
-	// double-buffered device staging + streams for host-pointer calls
+	// device staging ring + streams for host-pointer calls: with four buffers the H2D of chunk c+3 never waits for the
+	// D2H of chunk c, so the steady-state period is max(H2D, kernel, D2H) of one chunk, not their sum over two
 	cudaStream_t sIn = nullptr, sOut = nullptr;
-	cudaEvent_t inDone[2] = { nullptr, nullptr }, kDone[2] = { nullptr, nullptr }, outDone[2] = { nullptr, nullptr };
-	DevBuf<mtsb_ray> rays[2];
-	DevBuf<uint8_t> out[2];
+	cudaEvent_t inDone[MTSB_PIPE_BUFS] = {}, kDone[MTSB_PIPE_BUFS] = {}, outDone[MTSB_PIPE_BUFS] = {};
+	DevBuf<mtsb_ray> rays[MTSB_PIPE_BUFS];
+	DevBuf<uint8_t> out[MTSB_PIPE_BUFS];
 	DevBuf<unsigned long long> work;
 	size_t chunk = 0, outBytes = 0;
 	bool ready = false;
@@ -123,20 +127,20 @@ static int get_pipe(mtsb_scene *scene, size_t chunk, size_t outBytesPerRay, Trac
 	if (!p->ready) {
 		MTSB_CUDA(cudaStreamCreateWithFlags(&p->sIn, cudaStreamNonBlocking));
 		MTSB_CUDA(cudaStreamCreateWithFlags(&p->sOut, cudaStreamNonBlocking));
-		for (int i = 0; i < 2; ++i) {
+		for (int i = 0; i < MTSB_PIPE_BUFS; ++i) {
 			MTSB_CUDA(cudaEventCreateWithFlags(&p->inDone[i], cudaEventDisableTiming));
 			MTSB_CUDA(cudaEventCreateWithFlags(&p->kDone[i], cudaEventDisableTiming));
 			MTSB_CUDA(cudaEventCreateWithFlags(&p->outDone[i], cudaEventDisableTiming));
 		}
-		MTSB_CHECK(p->work.alloc(4));
+		MTSB_CHECK(p->work.alloc(MTSB_PIPE_BUFS + 1));
 		p->ready = true;
 	}
 	if (p->chunk < chunk) {
-		for (int i = 0; i < 2; ++i) MTSB_CHECK(p->rays[i].alloc(chunk));
+		for (int i = 0; i < MTSB_PIPE_BUFS; ++i) MTSB_CHECK(p->rays[i].alloc(chunk));
 		p->chunk = chunk;
 	}
 	if (p->outBytes < chunk * outBytesPerRay) {
-		for (int i = 0; i < 2; ++i) MTSB_CHECK(p->out[i].alloc(chunk * outBytesPerRay));
+		for (int i = 0; i < MTSB_PIPE_BUFS; ++i) MTSB_CHECK(p->out[i].alloc(chunk * outBytesPerRay));
 		p->outBytes = chunk * outBytesPerRay;
 	}
 	*outPipe = p;
@@ -150,7 +154,7 @@ void mtsb_release_pipe(mtsb_scene *scene) {
 	TracePipe *p = it->second;
 	if (p->ready) {
 		cudaStreamDestroy(p->sIn); cudaStreamDestroy(p->sOut);
-		for (int i = 0; i < 2; ++i) { cudaEventDestroy(p->inDone[i]); cudaEventDestroy(p->kDone[i]); cudaEventDestroy(p->outDone[i]); }
+		for (int i = 0; i < MTSB_PIPE_BUFS; ++i) { cudaEventDestroy(p->inDone[i]); cudaEventDestroy(p->kDone[i]); cudaEventDestroy(p->outDone[i]); }
 	}
 	delete p;
 	g_pipes.erase(it);
@@ -168,19 +172,21 @@ static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_
 		MTSB_CHECK(get_pipe(scene, 1, ob, &p));
 		return launch_trace(scene, mode, rays, n, out, p->work.ptr, ctx->stream, false);
 	}
-	// host path: chunks of up to 2M rays, H2D on sIn, kernel on ctx->stream, D2H on sOut
-	const size_t chunk = std::min<size_t>(n, (size_t) 1 << 21);
+	// host path: chunks of 2M rays (64 MB in, 32 MB out; 1M and smaller measured slower), H2D on sIn, kernel on ctx->stream, D2H on sOut
+	static size_t hostChunk = 0;
+	if (!hostChunk) { const char *e = getenv("MTSB_HOST_CHUNK"); hostChunk = e && atol(e) >= 1024 ? (size_t) atol(e) : (size_t) 1 << 21; }
+	const size_t chunk = std::min<size_t>(n, hostChunk);
 	MTSB_CHECK(get_pipe(scene, chunk, ob, &p));
 	const size_t nChunks = (n + chunk - 1) / chunk;
 	for (size_t c = 0; c < nChunks; ++c) {
-		const int b = (int) (c & 1);
+		const int b = (int) (c % MTSB_PIPE_BUFS);
 		const size_t off = c * chunk, cnt = std::min(chunk, n - off);
-		// buffer b is free once the D2H of chunk c-2 is done
-		if (c >= 2) MTSB_CUDA(cudaStreamWaitEvent(p->sIn, p->outDone[b], 0));
+		// buffer b is free once the D2H of chunk c - MTSB_PIPE_BUFS is done
+		if (c >= MTSB_PIPE_BUFS) MTSB_CUDA(cudaStreamWaitEvent(p->sIn, p->outDone[b], 0));
 		MTSB_CUDA(cudaMemcpyAsync(p->rays[b].ptr, rays + off, cnt * sizeof(mtsb_ray), cudaMemcpyHostToDevice, p->sIn));
 		MTSB_CUDA(cudaEventRecord(p->inDone[b], p->sIn));
 		MTSB_CUDA(cudaStreamWaitEvent(ctx->stream, p->inDone[b], 0));
-		if (c >= 2) MTSB_CUDA(cudaStreamWaitEvent(ctx->stream, p->outDone[b], 0));
+		if (c >= MTSB_PIPE_BUFS) MTSB_CUDA(cudaStreamWaitEvent(ctx->stream, p->outDone[b], 0));
 		MTSB_CHECK(launch_trace(scene, mode, p->rays[b].ptr, cnt, p->out[b].ptr, p->work.ptr + b, ctx->stream, false));
 		MTSB_CUDA(cudaEventRecord(p->kDone[b], ctx->stream));
 		MTSB_CUDA(cudaStreamWaitEvent(p->sOut, p->kDone[b], 0));
