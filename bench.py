@@ -180,7 +180,8 @@ def main():
     ap.add_argument("--no-path", action="store_true", help="skip the path-tracer detail runs (short runs under ncu)")
     ap.add_argument("--no-config4", action="store_true", help="skip the 3840x2160 multi-GPU render (config 4)")
     ap.add_argument("--spp4", type=int, default=1024, help="samples per pixel of config 4 (BASELINE: 1024)")
-    ap.add_argument("--builder", default="ploc", choices=["lbvh", "ploc"])
+    ap.add_argument("--builder", default="lbvh", choices=["lbvh", "ploc"],
+                    help="BVH builder of the config-2 mesh (measured: LBVH 2.44, PLOC 2.08 Grays/s on the chord rays; PLOC wins on configs 1/3)")
     ap.add_argument("--rays", type=int, default=N_RAYS)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -289,6 +290,24 @@ def main():
     # --- other ray sets of config 2 (detail only) ---
     detail = {}
     if rank == 0:
+        # the other builder on the same rays (both are first-class in the C ABI: mtsb_scene_commit(scene, builder))
+        other = B.BUILDER_LBVH if builder == B.BUILDER_PLOC else B.BUILDER_PLOC
+        sc2 = sd.upload(ctx, other)
+        for _ in range(2):
+            sc2.trace_device("closest", rays_d.data_ptr(), n, hits_d.data_ptr())
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            a.record(stream)
+            for _ in range(3):
+                sc2.trace_device("closest", rays_d.data_ptr(), n, hits_d.data_ptr())
+            b.record(stream)
+        torch.cuda.synchronize()
+        detail["closest_mrays_%s" % ("lbvh" if other == B.BUILDER_LBVH else "ploc")] = n / (a.elapsed_time(b) / 3) / 1e3
+        detail["build_other"] = sc2.build_stats()
+        sc2.close()
+        sc.trace_device("closest", rays_d.data_ptr(), n, hits_d.data_ptr())      # hits_d back to the headline tree's answers
+        torch.cuda.synchronize()
         res = 4096 if n >= (1 << 24) else int(np.sqrt(n))
         coh = S.pinhole_rays(res, origin=(0, 0.3, -3.0))
         coh_d = torch.from_numpy(coh.view(np.float32).reshape(-1, 8)).cuda()

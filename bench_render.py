@@ -174,11 +174,11 @@ def cpu_reference(pkg, sd_small, threads):
             "sample": "config 1 at %d spp (of 64), mitsuba -C, 'Render time' %.3f s" % (sd_small.sampler["spp"], t)}
 
 
-def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024, spp3=256):
+def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024, spp3=256, builder=None):
     S = pkg.scenes
     out = {}
     if 1 in configs and rank == 0:
-        out["config1_cornell_512x512_64spp"] = render_config(pkg, ctx, stream, S.cornell_box(512, 512, spp=64, max_depth=5), 64)
+        out["config1_cornell_512x512_64spp"] = render_config(pkg, ctx, stream, S.cornell_box(512, 512, spp=64, max_depth=5), 64, builder=builder)
         if cpu:
             out["config1_cpu_reference"] = cpu_reference(pkg, S.cornell_box(512, 512, spp=16, max_depth=5), os.cpu_count() or 1)
     sd = None
@@ -187,7 +187,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian")
         gen_s = time.perf_counter() - t0
     if 3 in configs and rank == 0:
-        r = render_config(pkg, ctx, stream, sd, spp3, warmup=1)
+        r = render_config(pkg, ctx, stream, sd, spp3, warmup=1, builder=builder)
         r["scene_generation_s"] = gen_s
         out["config3_spherefield_10Mtri_1920x1080_%dspp" % spp3] = r
     if 5 in configs and rank == 0:
@@ -203,6 +203,7 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", type=int, nargs="*", default=[1, 3, 5])
     ap.add_argument("--spp4", type=int, default=1024)
+    ap.add_argument("--builder", default=None, choices=["lbvh", "ploc"])
     ap.add_argument("--spp3", type=int, default=256, help="samples per pixel of config 3 (BASELINE: 256; smaller only for ncu runs)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -211,4 +212,5 @@ if __name__ == "__main__":
     ctx = pkg.binding.Context(0)
     torch.cuda.set_device(0)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", 0))
-    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4, spp3=args.spp3)))
+    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4, spp3=args.spp3,
+                         builder=None if args.builder is None else dict(lbvh=0, ploc=1)[args.builder])))

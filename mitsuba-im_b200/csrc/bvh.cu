@@ -182,7 +182,9 @@ __global__ void refit_kernel(int n, const uint32_t *sortedPrim, const float4 *pr
 // 3b. PLOC (Meister & Bittner 2018): iterative merging of mutually-nearest clusters within a window of
 // the Morton-sorted order.  Produces the same binary representation as LBVH (ids 0..N-2 internal).
 // ---------------------------------------------------------------------------------------------------
+#ifndef PLOC_RADIUS
 #define PLOC_RADIUS 16
+#endif
 __device__ __forceinline__ float box_area(float4 l, float4 h) {
 	float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
 	return 2.0f * (dx * dy + dy * dz + dz * dx);
