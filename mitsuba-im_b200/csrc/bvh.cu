@@ -295,6 +295,21 @@ __global__ void collapse_kernel(int n, int rootIsLeaf, const CollapseItem *inQ, 
 			int2 cc = children[kids[bi]];
 			kids[bi] = cc.x; kids[nk++] = cc.y;
 		}
+#ifndef MTSB_NO_LEAF_SPLIT
+		// free slots left: open multi-triangle leaves (largest box first) — tighter leaf boxes at no extra node
+		while (nk < 8) {
+			float best = -1; int bi = -1;
+			for (int i = 0; i < nk; ++i) {
+				int k = kids[i];
+				if (k >= n - 1) continue;
+				float a = box_area(blo[k], bhi[k]);
+				if (a > best) { best = a; bi = i; }
+			}
+			if (bi < 0) break;
+			int2 cc = children[kids[bi]];
+			kids[bi] = cc.x; kids[nk++] = cc.y;
+		}
+#endif
 	}
 
 	// node frame
