@@ -59,3 +59,25 @@ def test_gaussian_filter_and_independent_sampler_statistics(tmp_path):
     rel = np.mean((gpu - ref) ** 2 / (ref ** 2 + 1e-3))
     assert rel < 0.02, rel
     assert abs(gpu.mean() - ref.mean()) < 0.01 * ref.mean()
+
+
+def test_plugin_two_gpus_film_reduce(tmp_path):
+    """`<integer name="gpus" value="2"/>`: the plugin splits the sample indices over two devices inside the reference's own
+    process and sums the films with mtsb_comm_create_all + mtsb_film_reduce_all (system NCCL, bound by dlopen) before the
+    single D2H into the ImageBlock.  Same counter sampler => the image equals the 1-GPU one up to float summation order."""
+    import __graft_entry__ as graft
+    if graft.load_package().binding.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    global XML
+    src = open(XML).read()
+    xml2 = str(tmp_path / "cbox_2gpu.xml")
+    open(xml2, "w").write(src.replace('<integer name="maxDepth" value="5"/>', '<integer name="maxDepth" value="5"/><integer name="gpus" value="2"/>'))
+    d = dict(sampler="ctr", spp=16, res=64, rfilter="gaussian")
+    one, _ = run_mitsuba(str(tmp_path / "one.pfm"), True, True, d)
+    keep, XML = XML, xml2
+    try:
+        two, log = run_mitsuba(str(tmp_path / "two.pfm"), True, True, d)
+    finally:
+        XML = keep
+    assert "2 GPUs" in log, "the plugin did not run on two devices"
+    assert np.allclose(two, one, rtol=2e-4, atol=1e-5), float(np.abs(two - one).max())
