@@ -53,8 +53,11 @@ def test_reference_cli_with_gpu_plugin(tmp_path):
 
 def test_gaussian_filter_and_independent_sampler_statistics(tmp_path):
     """Gaussian film + the stock independent sampler: images agree statistically (relMSE well below the 1-vs-1 noise)."""
-    d = dict(sampler="independent", spp=64, res=64, rfilter="gaussian")
-    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, dict(d, spp=256), threads=os.cpu_count() or 4)
+    # the reference seeds its independent sampler from the clock (src/libcore/random.cpp:479-483), so this comparison is
+    # statistical: sample counts are chosen so that the noise of the image means (~0.25 % + ~0.12 %, filter-correlated
+    # pixels) sits well inside the 1 % bound — at 64 / 256 spp a 1.1 % deviation (2 sigma) was seen once in ten runs
+    d = dict(sampler="independent", spp=400, res=64, rfilter="gaussian")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, dict(d, spp=1600), threads=os.cpu_count() or 4)
     gpu, _ = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d)
     rel = np.mean((gpu - ref) ** 2 / (ref ** 2 + 1e-3))
     assert rel < 0.02, rel
