@@ -79,7 +79,7 @@ typedef struct mtsb_surface {
 	float uv[2];                        /* its.uv                                              */
 } mtsb_surface;
 
-/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor}.cpp), constant textures only. */
+/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor,conductor}.cpp), constant textures only. */
 enum {
 	MTSB_BSDF_DIFFUSE        = 0,  /* p[0..2] reflectance                                                    */
 	MTSB_BSDF_DIELECTRIC     = 1,  /* p[0] eta=intIOR/extIOR, p[1..3] specularReflectance, p[4..6] specularTransmittance */
@@ -88,6 +88,8 @@ enum {
 	MTSB_BSDF_ROUGHCONDUCTOR = 3,  /* p[0] alphaU, p[1] alphaV, p[2..4] eta, p[5..7] k, p[8..10] specularReflectance,
 	                                  p[11] distribution (0 beckmann, 1 ggx), p[12] sampleVisible(0/1)           */
 	MTSB_BSDF_NULL           = 4,  /* black diffuse given to BSDF-less emitter shapes (src/librender/shape.cpp:48-58) */
+	MTSB_BSDF_CONDUCTOR      = 5,  /* p[0..2] eta, p[3..5] k (both already divided by extEta), p[6..8] specularReflectance
+	                                  (src/bsdfs/conductor.cpp:167-199)                                       */
 	MTSB_BSDF_TWOSIDED_FLAG  = 0x100 /* OR-ed in: wrapped by `twosided` (src/bsdfs/twosided.cpp), same BSDF both sides */
 };
 typedef struct mtsb_bsdf_desc {

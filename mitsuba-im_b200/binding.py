@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmtsb200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
-BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL = 0, 1, 2, 3, 4
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR = 0, 1, 2, 3, 4, 5
 BSDF_TWOSIDED_FLAG = 0x100
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
 INTEGRATOR_PATH, INTEGRATOR_DIRECT = 0, 1

@@ -20,6 +20,7 @@ __device__ inline uint32_t bsdf_type(const BsdfRec &b) {   // m_combinedType of 
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: t = B_DIFFUSE_REFL | B_FRONT; break;
 		case MTSB_BSDF_DIELECTRIC: t = B_DELTA_REFL | B_DELTA_TRANS | B_FRONT | B_BACK; break;
 		case MTSB_BSDF_PLASTIC: t = B_DELTA_REFL | B_DIFFUSE_REFL | B_FRONT; break;
+		case MTSB_BSDF_CONDUCTOR: t = B_DELTA_REFL | B_FRONT; break;
 		default: t = B_GLOSSY_REFL | B_FRONT; break;
 	}
 	if (b.type & MTSB_BSDF_TWOSIDED_FLAG) t |= B_BACK;
@@ -44,7 +45,7 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 			if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
 			return v3(b.p[0], b.p[1], b.p[2]) * (MTS_INV_PI * wo.z);
 		}
-		case MTSB_BSDF_DIELECTRIC: return v3(0.0f);     // discrete measure only
+		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return v3(0.0f);     // discrete measure only
 		case MTSB_BSDF_PLASTIC: {
 			if (wo.z <= 0 || wi.z <= 0) return v3(0.0f);
 			const float eta = b.p[0];
@@ -69,7 +70,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL:
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return MTS_INV_PI * wo.z;
-		case MTSB_BSDF_DIELECTRIC: return 0.0f;
+		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return 0.0f;
 		case MTSB_BSDF_PLASTIC: {
 			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
 			const float Fi = fresnel_dielectric_ext(wi.z, b.p[0]);
@@ -126,6 +127,11 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			const float Fo = fresnel_dielectric_ext(out.wo.z, eta);
 			out.pdf = (1 - probSpecular) * (MTS_INV_PI * out.wo.z);
 			return plastic_diffuse(b) * ((1 / (eta * eta)) * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
+		}
+		case MTSB_BSDF_CONDUCTOR: {                                // conductor.cpp:214-235
+			if (wi.z <= 0) return v3(0.0f);
+			out.type = B_DELTA_REFL; out.wo = v3(-wi.x, -wi.y, wi.z); out.pdf = 1.0f;
+			return v3(b.p[6], b.p[7], b.p[8]) * fresnel_conductor_exact(wi.z, v3(b.p[0], b.p[1], b.p[2]), v3(b.p[3], b.p[4], b.p[5]));
 		}
 		default: {
 			if (wi.z < 0) return v3(0.0f);

@@ -92,6 +92,20 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 8);
 		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
 		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
+	} else if (cls == "SmoothConductor") {                          // src/bsdfs/conductor.cpp:155-177
+		d.type = MTSB_BSDF_CONDUCTOR;
+		ref<FileResolver> fResolver = Thread::getThread()->getFileResolver();
+		const std::string materialName = props.getString("material", "Cu");
+		Spectrum intEta, intK;
+		if (to_lower_copy(materialName) == "none") { intEta = Spectrum(0.0f); intK = Spectrum(1.0f); }
+		else {
+			intEta.fromContinuousSpectrum(InterpolatedSpectrum(fResolver->resolve(fs::pathstr("data/ior/" + materialName + ".eta.spd"))));
+			intK.fromContinuousSpectrum(InterpolatedSpectrum(fResolver->resolve(fs::pathstr("data/ior/" + materialName + ".k.spd"))));
+		}
+		const Float extEta = lookupIOR(props, "extEta", "air");
+		toRGB(props.getSpectrum("eta", intEta) / extEta, d.p + 0);
+		toRGB(props.getSpectrum("k", intK) / extEta, d.p + 3);
+		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 6);
 	} else if (cls == "TwoSidedBRDF") {                             // src/bsdfs/twosided.cpp — nested diffuse only
 		const std::string desc = bsdf->toString();
 		if (desc.find("nestedBRDF[0] = SmoothDiffuse[") == std::string::npos || desc.find("nestedBRDF[1] = SmoothDiffuse[") == std::string::npos)

@@ -280,6 +280,11 @@ class SceneDesc:
             k = [e / ext for e in k]
             dist = dict(beckmann=0, ggx=1)[b.get("distribution", "beckmann")]
             return B.BSDF_ROUGHCONDUCTOR | two, [au, av] + eta + k + list(b.get("specular_reflectance", (1, 1, 1))) + [dist, 1.0 if b.get("sample_visible", True) else 0.0]
+        if t == "conductor":
+            ext = b.get("ext_eta", 1.000277)
+            eta = [e / ext for e in b.get("eta", (0.2004, 0.9240, 1.1022))]
+            k = [e / ext for e in b.get("k", (3.9129, 2.4528, 2.1421))]
+            return B.BSDF_CONDUCTOR | two, eta + k + list(b.get("specular_reflectance", (1, 1, 1)))
         raise ValueError("BSDF outside the GPU subset: %s" % t)
 
     def upload(self, ctx, builder=B.BUILDER_LBVH):
@@ -342,6 +347,10 @@ class SceneDesc:
                 b.get("distribution", "beckmann"), b.get("alpha_u", a), b.get("alpha_v", a),
                 rgb("eta", b.get("eta", (0.2004, 0.9240, 1.1022))), rgb("k", b.get("k", (3.9129, 2.4528, 2.1421))),
                 b.get("ext_eta", 1.000277), "true" if b.get("sample_visible", True) else "false")
+        elif t == "conductor":
+            inner = '<bsdf type="conductor">%s%s%s<float name="extEta" value="%r"/></bsdf>' % (
+                rgb("eta", b.get("eta", (0.2004, 0.9240, 1.1022))), rgb("k", b.get("k", (3.9129, 2.4528, 2.1421))),
+                rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), b.get("ext_eta", 1.000277))
         else:
             raise ValueError(t)
         if b.get("twosided"):
@@ -544,11 +553,12 @@ MATERIALS = [
     dict(type="roughconductor", distribution="beckmann", alpha=0.3),
     dict(type="roughconductor", distribution="ggx", alpha_u=0.05, alpha_v=0.3, sample_visible=False),
     dict(type="diffuse", reflectance=(0.4, 0.7, 0.4), twosided=True),
+    dict(type="conductor", eta=(0.143, 0.375, 1.442), k=(3.983, 2.386, 1.603), specular_reflectance=(0.9, 0.95, 1.0)),
 ]
 
 
 def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, subdiv=2, env=True, point=True):
-    """Eight displaced spheres, one per entry of MATERIALS, on a diffuse floor; area light (mesh), point light and a
+    """Displaced spheres, one per entry of MATERIALS, on a diffuse floor; area light (mesh), point light and a
     constant environment — exercises every BSDF and emitter of the GPU subset."""
     sd = SceneDesc()
     if point:
