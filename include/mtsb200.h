@@ -79,7 +79,7 @@ typedef struct mtsb_surface {
 	float uv[2];                        /* its.uv                                              */
 } mtsb_surface;
 
-/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor,conductor}.cpp), constant textures only. */
+/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor,conductor,roughdielectric}.cpp), constant textures only. */
 enum {
 	MTSB_BSDF_DIFFUSE        = 0,  /* p[0..2] reflectance                                                    */
 	MTSB_BSDF_DIELECTRIC     = 1,  /* p[0] eta=intIOR/extIOR, p[1..3] specularReflectance, p[4..6] specularTransmittance */
@@ -90,6 +90,9 @@ enum {
 	MTSB_BSDF_NULL           = 4,  /* black diffuse given to BSDF-less emitter shapes (src/librender/shape.cpp:48-58) */
 	MTSB_BSDF_CONDUCTOR      = 5,  /* p[0..2] eta, p[3..5] k (both already divided by extEta), p[6..8] specularReflectance
 	                                  (src/bsdfs/conductor.cpp:167-199)                                       */
+	MTSB_BSDF_ROUGHDIELECTRIC = 6, /* p[0] alphaU, p[1] alphaV, p[2] eta=intIOR/extIOR, p[3..5] specularReflectance,
+	                                  p[6..8] specularTransmittance, p[11] distribution, p[12] sampleVisible
+	                                  (src/bsdfs/roughdielectric.cpp:186-214)                                 */
 	MTSB_BSDF_TWOSIDED_FLAG  = 0x100 /* OR-ed in: wrapped by `twosided` (src/bsdfs/twosided.cpp), same BSDF both sides */
 };
 typedef struct mtsb_bsdf_desc {
@@ -215,6 +218,9 @@ MTSB_API void  mtsb_host_free(void *p);
  *   em_in    : n x 8  {p.xyz, refN.xyz, s1, s2}
  *   em_out   : n x 12 {value.rgb, pdf, d.xyz, dist, measure, pdfEmitterDirect, emitter id, 0} */
 MTSB_API int  mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *bsdf_in, size_t n, float *bsdf_out);
+/* Same, with the extra draw that EUsesSampler plugins take from bRec.sampler inside sample() (roughdielectric's
+ * lobe selection, src/bsdfs/roughdielectric.cpp:562): s3 = n floats, NULL = 0.5 for every row. */
+MTSB_API int  mtsb_eval_bsdf_s3(mtsb_scene *scene, int bsdf, const float *bsdf_in, const float *s3, size_t n, float *bsdf_out);
 MTSB_API int  mtsb_eval_emitter(mtsb_scene *scene, const float *em_in, size_t n, float *em_out);
 
 /* ---------------------------------------------------------------- rendering ---------------------- */

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmtsb200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
-BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR = 0, 1, 2, 3, 4, 5
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
 BSDF_TWOSIDED_FLAG = 0x100
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
 INTEGRATOR_PATH, INTEGRATOR_DIRECT = 0, 1
@@ -98,7 +98,7 @@ def lib():
         "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
         "mtsb_trace_count": (i32, [vp, vp, sz, i32, i32, vp]),
         "mtsb_host_alloc": (vp, [sz]), "mtsb_host_free": (None, [vp]),
-        "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
+        "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
         "mtsb_render_create": (i32, [vp, C.POINTER(Camera), C.POINTER(FilmDesc), C.POINTER(IntegratorDesc), u64, C.POINTER(vp)]),
         "mtsb_render_destroy": (None, [vp]), "mtsb_render_set_camera": (i32, [vp, C.POINTER(Camera)]),
         "mtsb_render_clear": (i32, [vp]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
@@ -280,14 +280,18 @@ class Scene:
         return dict(nodes=int(out[0]), prims=int(out[1]), rays=int(out[2]))
 
     # --- pointwise plugin math ------------------------------------------------------------------
-    def eval_bsdf(self, bsdf, wi, wo, samples):
+    def eval_bsdf(self, bsdf, wi, wo, samples, s3=None):
         n = len(wi)
         inp = np.zeros((n, 8), np.float32)
         inp[:, 0:3] = wi
         inp[:, 3:6] = wo
         inp[:, 6:8] = samples
         out = np.zeros((n, 16), np.float32)
-        _check(lib().mtsb_eval_bsdf(self.h, bsdf, _ptr(inp), n, _ptr(out)))
+        if s3 is not None:
+            s3 = np.ascontiguousarray(s3, np.float32)
+            _check(lib().mtsb_eval_bsdf_s3(self.h, bsdf, _ptr(inp), _ptr(s3), n, _ptr(out)))
+        else:
+            _check(lib().mtsb_eval_bsdf(self.h, bsdf, _ptr(inp), n, _ptr(out)))
         return out
 
     def eval_emitter(self, p, n_ref, samples):

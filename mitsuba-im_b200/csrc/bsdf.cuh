@@ -21,6 +21,7 @@ __device__ inline uint32_t bsdf_type(const BsdfRec &b) {   // m_combinedType of 
 		case MTSB_BSDF_DIELECTRIC: t = B_DELTA_REFL | B_DELTA_TRANS | B_FRONT | B_BACK; break;
 		case MTSB_BSDF_PLASTIC: t = B_DELTA_REFL | B_DIFFUSE_REFL | B_FRONT; break;
 		case MTSB_BSDF_CONDUCTOR: t = B_DELTA_REFL | B_FRONT; break;
+		case MTSB_BSDF_ROUGHDIELECTRIC: t = B_GLOSSY_REFL | B_GLOSSY_TRANS | B_FRONT | B_BACK; break;
 		default: t = B_GLOSSY_REFL | B_FRONT; break;
 	}
 	if (b.type & MTSB_BSDF_TWOSIDED_FLAG) t |= B_BACK;
@@ -39,6 +40,100 @@ __device__ inline float plastic_prob_specular(const BsdfRec &b, float Fi) {
 }
 
 // --- one-sided evaluation (wi, wo in the local shading frame) ---
+// --- roughdielectric (src/bsdfs/roughdielectric.cpp): p[0] alphaU, p[1] alphaV, p[2] eta, p[3..5] specularReflectance,
+// p[6..8] specularTransmittance, p[11] distribution, p[12] sampleVisible.  ERadiance transport mode.
+__device__ inline float signum1(float v) { return copysignf(1.0f, v); }          // math::signum (core/math.h:269-280)
+
+__device__ inline V3 roughdielectric_eval(const BsdfRec &b, const V3 &wi, const V3 &wo) {          // :282-351
+	if (wi.z == 0) return v3(0.0f);
+	const float etaI = b.p[2], invEta = 1 / etaI;
+	const bool reflect = wi.z * wo.z > 0;
+	const float eta = wi.z > 0 ? etaI : invEta;
+	V3 H = reflect ? normalize(wo + wi) : normalize(wi + wo * eta);
+	H = H * signum1(H.z);
+	Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+	const float D = distr.eval(H);
+	if (D == 0) return v3(0.0f);
+	const float F = fresnel_dielectric_ext(dot(wi, H), etaI);
+	const float G = distr.G(wi, wo, H);
+	if (reflect) {
+		const float value = F * D * G / (4.0f * fabsf(wi.z));
+		return v3(b.p[3], b.p[4], b.p[5]) * value;
+	}
+	const float sqrtDenom = dot(wi, H) + eta * dot(wo, H);
+	const float value = ((1 - F) * D * G * eta * eta * dot(wi, H) * dot(wo, H)) / (wi.z * sqrtDenom * sqrtDenom);
+	const float factor = wi.z > 0 ? invEta : etaI;
+	return v3(b.p[6], b.p[7], b.p[8]) * fabsf(value * factor * factor);
+}
+
+__device__ inline float roughdielectric_pdf(const BsdfRec &b, const V3 &wi, const V3 &wo) {         // :353-424
+	const float etaI = b.p[2], invEta = 1 / etaI;
+	const bool reflect = wi.z * wo.z > 0;
+	V3 H; float dwh_dwo;
+	if (reflect) {
+		H = normalize(wo + wi);
+		dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+	} else {
+		const float eta = wi.z > 0 ? etaI : invEta;
+		H = normalize(wi + wo * eta);
+		const float sqrtDenom = dot(wi, H) + eta * dot(wo, H);
+		dwh_dwo = (eta * eta * dot(wo, H)) / (sqrtDenom * sqrtDenom);
+	}
+	H = H * signum1(H.z);
+	Microfacet sampleDistr; sampleDistr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+	if (!sampleDistr.sampleVisible) {
+		const float sc = 1.2f - 0.2f * sqrtf(fabsf(wi.z));
+		sampleDistr.alphaU *= sc; sampleDistr.alphaV *= sc;
+	}
+	float prob = sampleDistr.pdf(wi * signum1(wi.z), H);
+	const float F = fresnel_dielectric_ext(dot(wi, H), etaI);
+	prob *= reflect ? F : (1 - F);
+	return fabsf(prob * dwh_dwo);
+}
+
+// `sz` is the lobe-selection draw the plugin takes from bRec.sampler->next1D() (:562)
+__device__ inline V3 roughdielectric_sample(const BsdfRec &b, const V3 &wi, float sx, float sy, float sz, BsdfSample &out) {   // :529-620
+	const float etaI = b.p[2], invEta = 1 / etaI;
+	Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+	Microfacet sampleDistr = distr;
+	if (!distr.sampleVisible) {
+		const float sc = 1.2f - 0.2f * sqrtf(fabsf(wi.z));
+		sampleDistr.alphaU *= sc; sampleDistr.alphaV *= sc;
+	}
+	float microfacetPDF;
+	const V3 m = sampleDistr.sample(wi * signum1(wi.z), sx, sy, microfacetPDF);
+	if (microfacetPDF == 0) return v3(0.0f);
+	float pdf = microfacetPDF;
+	float cosThetaT;
+	const float F = fresnel_dielectric_ext(dot(wi, m), cosThetaT, etaI);
+	V3 weight = v3(1.0f);
+	bool sampleReflection = true;
+	if (sz > F) { sampleReflection = false; pdf *= 1 - F; } else pdf *= F;
+	float dwh_dwo;
+	if (sampleReflection) {
+		out.wo = 2 * dot(wi, m) * m - wi;
+		out.eta = 1.0f; out.type = B_GLOSSY_REFL;
+		if (wi.z * out.wo.z <= 0) return v3(0.0f);
+		weight = v3(b.p[3], b.p[4], b.p[5]);
+		dwh_dwo = 1.0f / (4.0f * dot(out.wo, m));
+	} else {
+		if (cosThetaT == 0) return v3(0.0f);
+		const float e = cosThetaT < 0 ? invEta : etaI;                     // refract(wi, m, eta, cosThetaT), util.cpp:769-774
+		out.wo = m * (dot(wi, m) * e + cosThetaT) - wi * e;
+		out.eta = cosThetaT < 0 ? etaI : invEta; out.type = B_GLOSSY_TRANS;
+		if (wi.z * out.wo.z >= 0) return v3(0.0f);
+		const float factor = cosThetaT < 0 ? invEta : etaI;
+		weight = v3(b.p[6], b.p[7], b.p[8]) * (factor * factor);
+		const float sqrtDenom = dot(wi, m) + out.eta * dot(out.wo, m);
+		dwh_dwo = (out.eta * out.eta * dot(out.wo, m)) / (sqrtDenom * sqrtDenom);
+	}
+	if (distr.sampleVisible) weight = weight * distr.smithG1(out.wo, m);
+	else weight = weight * fabsf(distr.eval(m) * distr.G(wi, out.wo, m) * dot(wi, m) / (microfacetPDF * wi.z));
+	out.pdf = pdf * fabsf(dwh_dwo);
+	return weight;
+}
+
+
 __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 	switch (b.type & 0xff) {
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: {
@@ -46,6 +141,7 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 			return v3(b.p[0], b.p[1], b.p[2]) * (MTS_INV_PI * wo.z);
 		}
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return v3(0.0f);     // discrete measure only
+		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_eval(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (wo.z <= 0 || wi.z <= 0) return v3(0.0f);
 			const float eta = b.p[0];
@@ -71,6 +167,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return MTS_INV_PI * wo.z;
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return 0.0f;
+		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_pdf(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
 			const float Fi = fresnel_dielectric_ext(wi.z, b.p[0]);
@@ -87,7 +184,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 }
 
 // returns the importance weight (f cos / pdf); zero weight = failed sample
-__device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, float sy, BsdfSample &out) {
+__device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, float sy, float sz, BsdfSample &out) {
 	out.pdf = 0; out.eta = 1.0f; out.type = 0; out.wo = v3(0.0f);
 	switch (b.type & 0xff) {
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: {
@@ -128,6 +225,7 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			out.pdf = (1 - probSpecular) * (MTS_INV_PI * out.wo.z);
 			return plastic_diffuse(b) * ((1 / (eta * eta)) * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
 		}
+		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(b, wi, sx, sy, sz, out);
 		case MTSB_BSDF_CONDUCTOR: {                                // conductor.cpp:214-235
 			if (wi.z <= 0) return v3(0.0f);
 			out.type = B_DELTA_REFL; out.wo = v3(-wi.x, -wi.y, wi.z); out.pdf = 1.0f;
@@ -161,10 +259,14 @@ __device__ inline float bsdf_pdf(const BsdfRec &b, V3 wi, V3 wo) {
 	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && !(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; }
 	return bsdf_pdf_1(b, wi, wo);
 }
-__device__ inline V3 bsdf_sample(const BsdfRec &b, V3 wi, float sx, float sy, BsdfSample &out) {
+// true for the plugins whose sample() takes one more draw from bRec.sampler (EUsesSampler); the caller draws it
+// right after the 2D sample, which is where the plugin's next1D() lands in the stream
+__device__ inline bool bsdf_uses_sampler(const BsdfRec &b) { return (b.type & 0xff) == MTSB_BSDF_ROUGHDIELECTRIC; }
+
+__device__ inline V3 bsdf_sample(const BsdfRec &b, V3 wi, float sx, float sy, float sz, BsdfSample &out) {
 	bool flipped = false;
 	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && wi.z < 0) { wi.z = -wi.z; flipped = true; }
-	const V3 w = bsdf_sample_1(b, wi, sx, sy, out);
+	const V3 w = bsdf_sample_1(b, wi, sx, sy, sz, out);
 	if (flipped && !is_zero(w) && out.pdf != 0) out.wo.z = -out.wo.z;
 	return w;
 }

@@ -224,18 +224,23 @@ int mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint3
 	return 0;
 }
 
-int mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *in, size_t n, float *out) {
+int mtsb_eval_bsdf_s3(mtsb_scene *scene, int bsdf, const float *in, const float *s3, size_t n, float *out) {
 	if (!scene || !scene->committed || !in || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_eval_bsdf: NULL argument or scene not committed");
 	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_eval_bsdf: bsdf id %d unknown", bsdf);
 	if (n == 0) return 0;
 	MTSB_CUDA(cudaSetDevice(scene->ctx->device));
 	cudaStream_t st = scene->ctx->stream;
-	DevBuf<float> dI, dO;
+	DevBuf<float> dI, dO, dS;
 	MTSB_CHECK(dI.upload(in, n * 8, st)); MTSB_CHECK(dO.alloc(n * 16));
-	eval_bsdf_kernel<<<blocks_for(n, 128), 128, 0, st>>>(scene->dev, bsdf, dI.ptr, n, dO.ptr);
+	if (s3) MTSB_CHECK(dS.upload(s3, n, st));
+	eval_bsdf_kernel<<<blocks_for(n, 128), 128, 0, st>>>(scene->dev, bsdf, dI.ptr, s3 ? dS.ptr : nullptr, n, dO.ptr);
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 16 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	return 0;
+}
+
+int mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *in, size_t n, float *out) {
+	return mtsb_eval_bsdf_s3(scene, bsdf, in, nullptr, n, out);
 }
 
 int mtsb_eval_emitter(mtsb_scene *scene, const float *in, size_t n, float *out) {

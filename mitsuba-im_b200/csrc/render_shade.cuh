@@ -122,8 +122,9 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 			}
 			// ---- BSDF sampling (:205-222)
 			next2D(rs, sx, sy);
+			const float sz = bsdf_uses_sampler(bsdf) ? next1D(rs) : 0.0f;
 			BsdfSample bs;
-			const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, bs);
+			const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, sz, bs);
 			if (is_zero(bsdfWeight)) alive = false;
 			else {
 				flags |= PF_SCATTERED;
@@ -253,7 +254,7 @@ __global__ void prep_kernel(PathState ps, uint32_t *countOut, uint32_t *countSha
 }
 
 // ---- pointwise plugin math for parity tests (mtsb_eval_bsdf / mtsb_eval_emitter) ----
-__global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, size_t n, float *out) {
+__global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, const float *s3, size_t n, float *out) {
 	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	const BsdfRec b = S.bsdfs[bsdfId];
@@ -262,7 +263,7 @@ __global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, size_t
 	const V3 f = bsdf_eval(b, wi, wo);
 	o[0] = f.x; o[1] = f.y; o[2] = f.z; o[3] = bsdf_pdf(b, wi, wo);
 	BsdfSample bs;
-	const V3 w = bsdf_sample(b, wi, r[6], r[7], bs);
+	const V3 w = bsdf_sample(b, wi, r[6], r[7], s3 ? s3[i] : 0.5f, bs);
 	o[4] = w.x; o[5] = w.y; o[6] = w.z; o[7] = bs.wo.x; o[8] = bs.wo.y; o[9] = bs.wo.z;
 	o[10] = bs.pdf; o[11] = bs.eta; o[12] = (float) bs.type; o[13] = o[14] = o[15] = 0;
 }

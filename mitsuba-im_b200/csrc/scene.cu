@@ -110,7 +110,7 @@ int mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc) {
 	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: NULL argument");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: scene already committed");
 	int base = desc->type & 0xff;
-	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_CONDUCTOR)
+	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_ROUGHDIELECTRIC)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_bsdf: BSDF type %d is outside the GPU subset", desc->type);
 	BsdfRec r; r.type = desc->type; memcpy(r.p, desc->p, sizeof(r.p));
 	scene->bsdfs.push_back(r);

@@ -92,6 +92,20 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 8);
 		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
 		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
+	} else if (cls == "RoughDielectric") {                          // src/bsdfs/roughdielectric.cpp:186-214
+		d.type = MTSB_BSDF_ROUGHDIELECTRIC;
+		Float alphaU = 0.1f, alphaV = 0.1f;                         // MicrofacetDistribution(props), src/bsdfs/microfacet.h:84-128
+		if (props.hasProperty("alpha")) alphaU = alphaV = props.getFloat("alpha");
+		else if (props.hasProperty("alphaU") || props.hasProperty("alphaV")) { alphaU = props.getFloat("alphaU"); alphaV = props.getFloat("alphaV"); }
+		const std::string distr = to_lower_copy(props.getString("distribution", "beckmann"));
+		if (distr != "beckmann" && distr != "ggx")
+			SLog(EError, "gpupath: roughdielectric distribution \"%s\" is outside the GPU subset (beckmann, ggx)", distr.c_str());
+		d.p[0] = (float) alphaU; d.p[1] = (float) alphaV;
+		d.p[2] = (float) bsdf->getEta();
+		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 3);
+		toRGB(props.getSpectrum("specularTransmittance", Spectrum(1.0f)), d.p + 6);
+		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
+		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
 	} else if (cls == "SmoothConductor") {                          // src/bsdfs/conductor.cpp:155-177
 		d.type = MTSB_BSDF_CONDUCTOR;
 		ref<FileResolver> fResolver = Thread::getThread()->getFileResolver();

@@ -285,6 +285,13 @@ class SceneDesc:
             eta = [e / ext for e in b.get("eta", (0.2004, 0.9240, 1.1022))]
             k = [e / ext for e in b.get("k", (3.9129, 2.4528, 2.1421))]
             return B.BSDF_CONDUCTOR | two, eta + k + list(b.get("specular_reflectance", (1, 1, 1)))
+        if t == "roughdielectric":
+            a = b.get("alpha", 0.1)
+            au, av = b.get("alpha_u", a), b.get("alpha_v", a)
+            eta = b.get("int_ior", 1.5046) / b.get("ext_ior", 1.000277)
+            dist = dict(beckmann=0, ggx=1)[b.get("distribution", "beckmann")]
+            return B.BSDF_ROUGHDIELECTRIC, ([au, av, eta] + list(b.get("specular_reflectance", (1, 1, 1))) + list(b.get("specular_transmittance", (1, 1, 1)))
+                                            + [0, 0, dist, 1.0 if b.get("sample_visible", True) else 0.0])
         raise ValueError("BSDF outside the GPU subset: %s" % t)
 
     def upload(self, ctx, builder=B.BUILDER_LBVH):
@@ -351,6 +358,14 @@ class SceneDesc:
             inner = '<bsdf type="conductor">%s%s%s<float name="extEta" value="%r"/></bsdf>' % (
                 rgb("eta", b.get("eta", (0.2004, 0.9240, 1.1022))), rgb("k", b.get("k", (3.9129, 2.4528, 2.1421))),
                 rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), b.get("ext_eta", 1.000277))
+        elif t == "roughdielectric":
+            a = b.get("alpha", 0.1)
+            inner = ('<bsdf type="roughdielectric"><string name="distribution" value="%s"/><float name="alphaU" value="%r"/>'
+                     '<float name="alphaV" value="%r"/><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/>%s%s'
+                     '<boolean name="sampleVisible" value="%s"/></bsdf>') % (
+                b.get("distribution", "beckmann"), b.get("alpha_u", a), b.get("alpha_v", a), b.get("int_ior", 1.5046), b.get("ext_ior", 1.000277),
+                rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), rgb("specularTransmittance", b.get("specular_transmittance", (1, 1, 1))),
+                "true" if b.get("sample_visible", True) else "false")
         else:
             raise ValueError(t)
         if b.get("twosided"):
@@ -554,6 +569,8 @@ MATERIALS = [
     dict(type="roughconductor", distribution="ggx", alpha_u=0.05, alpha_v=0.3, sample_visible=False),
     dict(type="diffuse", reflectance=(0.4, 0.7, 0.4), twosided=True),
     dict(type="conductor", eta=(0.143, 0.375, 1.442), k=(3.983, 2.386, 1.603), specular_reflectance=(0.9, 0.95, 1.0)),
+    dict(type="roughdielectric", distribution="ggx", alpha=0.15, specular_transmittance=(0.9, 1.0, 0.9)),
+    dict(type="roughdielectric", distribution="beckmann", alpha_u=0.1, alpha_v=0.25, int_ior=1.33, sample_visible=False),
 ]
 
 

@@ -15,7 +15,7 @@
  *       rays : N x 8  {o.xyz, mint, d.xyz, maxt}
  *       out  : N x 16 {t, u, v, shape(i32), prim(i32), p.xyz, ng.xyz, ns.xyz, any(i32), 0}
  *   mtsutil raydump bsdf    <scene.xml> <in.bin> <out.bin>
- *       in   : N x 12 {shape, wi.xyz, wo.xyz, s1, s2, 0,0,0}
+ *       in   : N x 12 {shape, wi.xyz, wo.xyz, s1, s2, s3 (the draw from bRec.sampler), 0,0}
  *       out  : N x 16 {eval.rgb, pdf, weight.rgb, wo'.xyz, pdf', eta, sampledType, 0,0,0}
  *   mtsutil raydump emitter <scene.xml> <in.bin> <out.bin>
  *       in   : N x 8  {p.xyz, n.xyz, s1, s2}
@@ -51,6 +51,18 @@ static std::vector<float> readFloats(const char *fn) {
 	fclose(f);
 	return v;
 }
+
+/// Hands the `bsdf` mode's third input sample to plugins that draw from bRec.sampler inside sample() (EUsesSampler:
+/// roughdielectric's lobe selection) — so that draw is an input of the golden vector like the other two.
+class FixedSampler : public Sampler {
+public:
+	FixedSampler() : Sampler(Properties()), m_value(0.5f) { }
+	void set(Float v) { m_value = v; }
+	Float next1D() { return m_value; }
+	Point2 next2D() { return Point2(m_value, m_value); }
+private:
+	Float m_value;
+};
 
 static void writeFloats(const char *fn, const std::vector<float> &v) {
 	FILE *f = fopen(fn, "wb");
@@ -177,6 +189,7 @@ public:
 		std::vector<float> in = readFloats(argv[3]);
 		size_t n = in.size() / 12;
 		std::vector<float> out(n * 16, 0.0f);
+		ref<FixedSampler> fixedSampler = new FixedSampler();
 		for (size_t i = 0; i < n; ++i) {
 			const float *r = &in[i*12];
 			float *o = &out[i*16];
@@ -197,7 +210,8 @@ public:
 				o[0] = rr; o[1] = gg; o[2] = bb; o[3] = pdf;
 			}
 			{
-				BSDFSamplingRecord bRec(its, NULL, ERadiance);
+				fixedSampler->set(r[9]);
+				BSDFSamplingRecord bRec(its, fixedSampler.get(), ERadiance);
 				bRec.wi = wi;
 				Float pdf = 0;
 				Spectrum w = bsdf->sample(bRec, pdf, Point2(r[7], r[8]));

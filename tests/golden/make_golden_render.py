@@ -56,6 +56,7 @@ def bsdf_case(td):
         inp[:, 1:4] = rand_dirs(rng, n)
         inp[:, 4:7] = rand_dirs(rng, n, 0.7)
         inp[:, 7:9] = rng.random((n, 2), dtype=np.float32)
+        inp[:, 9] = rng.random(n, dtype=np.float32)     # the draw EUsesSampler plugins take inside sample()
         rows.append(inp)
     inp = np.concatenate(rows)
     out = run_util("bsdf", xml, inp, 16)

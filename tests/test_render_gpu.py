@@ -17,7 +17,8 @@ def _close(a, b, rtol, atol):
 
 def test_bsdf_pointwise_matches_reference_plugins(pkg, ctx, golden):
     """mtsb_eval_bsdf vs BSDF::eval / pdf / sample of diffuse, dielectric, plastic (linear, nonlinear), roughconductor
-    (GGX visible, Beckmann visible, anisotropic GGX sampleAll) and twosided — tests/golden/bsdf.npz."""
+    (GGX visible, Beckmann visible, anisotropic GGX sampleAll), twosided, conductor and roughdielectric (GGX visible,
+    anisotropic Beckmann sampleAll) — tests/golden/bsdf.npz."""
     S = pkg.scenes
     g = golden("bsdf.npz")
     inp, ref = g["inp"], g["out"]
@@ -27,7 +28,7 @@ def test_bsdf_pointwise_matches_reference_plugins(pkg, ctx, golden):
         for shape in range(len(S.MATERIALS)):
             rows = inp[:, 0] == shape
             bsdf_id = shape            # materials_scene adds one BSDF per shape in order
-            out = sc.eval_bsdf(bsdf_id, inp[rows, 1:4], inp[rows, 4:7], inp[rows, 7:9])
+            out = sc.eval_bsdf(bsdf_id, inp[rows, 1:4], inp[rows, 4:7], inp[rows, 7:9], s3=inp[rows, 9])
             r = ref[rows]
             name = S.MATERIALS[shape]
             rtol = 2e-3 if name.get("distribution") == "beckmann" else 5e-4      # reference uses math::fastexp / erf fits
