@@ -114,13 +114,16 @@ typedef struct mtsb_emitter_desc {
 	float    sampling_weight;    /* Emitter::m_samplingWeight (default 1)               */
 } mtsb_emitter_desc;
 
-/* Perspective sensor: the matrices PerspectiveCameraImpl::configure builds
+/* Perspective / thin-lens sensor: the matrices PerspectiveCameraImpl::configure builds
  * (src/sensors/perspective.cpp:126-180), row-major 4x4. */
 typedef struct mtsb_camera {
 	float sample_to_camera[16];  /* m_sampleToCamera (maps [0,1]^2 x near plane to camera space) */
 	float camera_to_world[16];   /* m_worldTransform->eval(t) — assumed static                    */
 	float near_clip, far_clip;
 	float inv_resolution[2];     /* 1/film size (m_invResolution)                                 */
+	float aperture_radius;       /* `thinlens` (src/sensors/thinlens.cpp:293-322): world-space lens radius;
+	                                0 = pinhole `perspective`, no aperture sample is drawn         */
+	float focus_distance;        /* ProjectiveCamera::getFocusDistance(), used when aperture_radius > 0 */
 } mtsb_camera;
 
 /* Film: the float bitmap of an ImageBlock (src/librender/imageblock.cpp:22-37) + its filter table. */

@@ -50,7 +50,8 @@ class EmitterDesc(C.Structure):
 
 class Camera(C.Structure):
     _fields_ = [("sample_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
-                ("near_clip", C.c_float), ("far_clip", C.c_float), ("inv_resolution", C.c_float * 2)]
+                ("near_clip", C.c_float), ("far_clip", C.c_float), ("inv_resolution", C.c_float * 2),
+                ("aperture_radius", C.c_float), ("focus_distance", C.c_float)]
 
 
 class FilmDesc(C.Structure):

@@ -78,9 +78,21 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	float u1, u2; next2D(rs, u1, u2);
 	const float sx = (float) px + u1, sy = (float) py + u2;            // samplePos (integrator.cpp:172)
 	const V3 nearP = xform_projective_point(cam.s2c, v3(sx * cam.invResX, sy * cam.invResY, 0.0f));
-	const V3 d = normalize(nearP);
+	V3 d, o;
+	if (cam.apertureRadius > 0) {                                      // ThinLens::sampleRay (thinlens.cpp:293-322)
+		float a1, a2; next2D(rs, a1, a2);                              // apertureSample (integrator.cpp:174-175)
+		float ax, ay; square_to_disk_concentric(a1, a2, ax, ay);
+		const V3 apertureP = v3(ax * cam.apertureRadius, ay * cam.apertureRadius, 0.0f);
+		const V3 focusP = nearP * (cam.focusDistance / nearP.z);
+		d = normalize(focusP - apertureP);
+		o = v3(cam.c2w[0] * apertureP.x + cam.c2w[1] * apertureP.y + cam.c2w[3],
+		       cam.c2w[4] * apertureP.x + cam.c2w[5] * apertureP.y + cam.c2w[7],
+		       cam.c2w[8] * apertureP.x + cam.c2w[9] * apertureP.y + cam.c2w[11]);
+	} else {                                                           // PerspectiveCameraImpl::sampleRay (perspective.cpp:208-231)
+		d = normalize(nearP);
+		o = v3(cam.c2w[3], cam.c2w[7], cam.c2w[11]);
+	}
 	const float invZ = 1.0f / d.z;
-	const V3 o = v3(cam.c2w[3], cam.c2w[7], cam.c2w[11]);
 	const V3 dw = xform_vector(cam.c2w, d);
 	ps.rayO[j] = make_float4(o.x, o.y, o.z, cam.nearClip * invZ);
 	ps.rayD[j] = make_float4(dw.x, dw.y, dw.z, cam.farClip * invZ);

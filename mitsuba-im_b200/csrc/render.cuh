@@ -28,6 +28,7 @@ enum { PF_FROM_BSDF = 1, PF_SCATTERED = 2, PF_DELTA = 4 };
 struct CameraDev {
 	float s2c[16], c2w[16];
 	float nearClip, farClip, invResX, invResY;
+	float apertureRadius, focusDistance;   // thinlens; apertureRadius == 0: pinhole
 };
 
 struct FilmDev {

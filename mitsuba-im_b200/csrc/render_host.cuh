@@ -66,6 +66,7 @@ static void fill_camera(CameraDev &c, const mtsb_camera *cam) {
 	memcpy(c.c2w, cam->camera_to_world, sizeof(c.c2w));
 	c.nearClip = cam->near_clip; c.farClip = cam->far_clip;
 	c.invResX = cam->inv_resolution[0]; c.invResY = cam->inv_resolution[1];
+	c.apertureRadius = cam->aperture_radius; c.focusDistance = cam->focus_distance;
 }
 
 extern "C" {

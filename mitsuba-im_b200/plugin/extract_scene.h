@@ -84,8 +84,10 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 
 /// PerspectiveCameraImpl::configure (src/sensors/perspective.cpp:126-180) restated with the reference's own Transform class.
 static void describeCamera(const Sensor *sensor, mtsb_camera &cam) {
-	if (!sensor->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)) || sensor->needsApertureSample() || sensor->needsTimeSample())
-		SLog(EError, "gpupath: sensor \"%s\" is outside the GPU subset (perspective)", sensor->getClass()->getName().c_str());
+	const std::string sensorCls = sensor->getClass()->getName();
+	const bool thinlens = sensorCls == "ThinLens";
+	if (!sensor->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)) || (sensor->needsApertureSample() && !thinlens) || sensor->needsTimeSample())
+		SLog(EError, "gpupath: sensor \"%s\" is outside the GPU subset (perspective, thinlens)", sensorCls.c_str());
 	const PerspectiveCamera *pc = static_cast<const PerspectiveCamera *>(sensor);
 	const Film *film = sensor->getFilm();
 	const Vector2i filmSize = film->getSize(), cropSize = film->getCropSize();
@@ -103,6 +105,11 @@ static void describeCamera(const Sensor *sensor, mtsb_camera &cam) {
 	matrixToArray(sensor->getWorldTransform()->eval(0).getMatrix(), cam.camera_to_world);
 	cam.near_clip = (float) pc->getNearClip(); cam.far_clip = (float) pc->getFarClip();
 	cam.inv_resolution[0] = 1.0f / cropSize.x; cam.inv_resolution[1] = 1.0f / cropSize.y;
+	cam.aperture_radius = 0.0f; cam.focus_distance = (float) pc->getFocusDistance();
+	if (thinlens) {                                                 // src/sensors/thinlens.cpp:124-138
+		Float r = sensor->getProperties().getFloat("apertureRadius");
+		cam.aperture_radius = (float) (r == 0 ? Epsilon : r);
+	}
 }
 
 /// The float layout of an ImageBlock + its filter table (include/mitsuba/core/rfilter.h:76-77).

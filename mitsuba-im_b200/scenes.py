@@ -238,9 +238,11 @@ class SceneDesc:
     def add_constant_env(self, radiance):
         self.emitters.append(dict(type="constant", radiance=tuple(radiance)))
 
-    def set_sensor(self, to_world, fov, width, height, rfilter="box", spp=4, seed=0, sampler="independent", fov_axis="x"):
+    def set_sensor(self, to_world, fov, width, height, rfilter="box", spp=4, seed=0, sampler="independent", fov_axis="x",
+                   aperture_radius=0.0, focus_distance=1.0):
+        """aperture_radius > 0 selects the `thinlens` sensor (src/sensors/thinlens.cpp), else `perspective`."""
         self.sensor = dict(to_world=np.asarray(to_world, np.float64), fov=fov, width=width, height=height, rfilter=rfilter,
-                           fov_axis=fov_axis)
+                           fov_axis=fov_axis, aperture_radius=float(aperture_radius), focus_distance=float(focus_distance))
         self.sampler = dict(kind=sampler, spp=spp, seed=seed)
 
     def set_integrator(self, kind="path", **kw):
@@ -321,7 +323,9 @@ class SceneDesc:
 
     def camera(self):
         s = self.sensor
-        return make_camera(s["to_world"], s["fov"], s["width"], s["height"], fov_axis=s["fov_axis"])
+        cam = make_camera(s["to_world"], s["fov"], s["width"], s["height"], fov_axis=s["fov_axis"])
+        cam.aperture_radius, cam.focus_distance = s.get("aperture_radius", 0.0), s.get("focus_distance", 1.0)
+        return cam
 
     def film(self, channels=5):
         s = self.sensor
@@ -387,7 +391,11 @@ class SceneDesc:
         out.append('</integrator>')
         if self.sensor is not None:
             s, sm = self.sensor, self.sampler
-            out.append('<sensor type="perspective"><float name="fov" value="%r"/><string name="fovAxis" value="%s"/>' % (s["fov"], s["fov_axis"]))
+            if s.get("aperture_radius", 0.0) > 0:
+                out.append('<sensor type="thinlens"><float name="apertureRadius" value="%r"/><float name="focusDistance" value="%r"/>'
+                           '<float name="fov" value="%r"/><string name="fovAxis" value="%s"/>' % (s["aperture_radius"], s["focus_distance"], s["fov"], s["fov_axis"]))
+            else:
+                out.append('<sensor type="perspective"><float name="fov" value="%r"/><string name="fovAxis" value="%s"/>' % (s["fov"], s["fov_axis"]))
             out.append('<transform name="toWorld">%s</transform>' % _mat_xml(s["to_world"]))
             if sm["kind"] == "ctr":
                 out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/></sampler>' % (sm["spp"], sm["seed"]))

@@ -96,6 +96,15 @@ def direct_case(td):
     li_case(td, "direct", sd)
 
 
+def thinlens_case(td):
+    """ThinLens::sampleRay (src/sensors/thinlens.cpp:293-322): the aperture sample is drawn right after the pixel sample."""
+    sd = S.materials_scene(48, 32, spp=4, max_depth=4, sampler="ctr", seed=17)
+    s = sd.sensor
+    sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=4, seed=17, sampler="ctr",
+                  aperture_radius=0.12, focus_distance=5.2)
+    li_case(td, "thinlens", sd)
+
+
 if __name__ == "__main__":
     with tempfile.TemporaryDirectory() as td:
         bsdf_case(td)
@@ -104,3 +113,4 @@ if __name__ == "__main__":
         li_case(td, "materials", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=11))
         li_case(td, "materials_deep", S.materials_scene(24, 16, spp=2, max_depth=-1, sampler="ctr", seed=3))
         direct_case(td)
+        thinlens_case(td)

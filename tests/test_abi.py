@@ -29,7 +29,7 @@ def test_struct_sizes_match_binding(pkg):
     B = pkg.binding
     assert ctypes.sizeof(B.BsdfDesc) == 64
     assert ctypes.sizeof(B.EmitterDesc) == 36
-    assert ctypes.sizeof(B.Camera) == 144
+    assert ctypes.sizeof(B.Camera) == 152      # + aperture_radius, focus_distance (thinlens)
     assert ctypes.sizeof(B.FilmDesc) == 172
     assert ctypes.sizeof(B.IntegratorDesc) == 28
 

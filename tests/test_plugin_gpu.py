@@ -16,7 +16,10 @@ OVERLAY = os.path.join(ROOT, "mitsuba-im_b200", "plugin", "overlay")
 XML = os.path.join(ROOT, "tests", "golden", "cbox_config1.xml")
 
 
-def run_mitsuba(out, classic, overlay, defines, threads=4):
+XML_GLOSSY = os.path.join(ROOT, "tests", "golden", "cbox_glossy.xml")
+
+
+def run_mitsuba(out, classic, overlay, defines, threads=4, xml=XML):
     cmd = [os.path.join(O.REF_DIR, "mitsuba"), "-p", str(threads)]
     if classic:
         cmd.append("-C")
@@ -24,7 +27,7 @@ def run_mitsuba(out, classic, overlay, defines, threads=4):
         cmd += ["-a", OVERLAY]
     for k, v in defines.items():
         cmd += ["-D", "%s=%s" % (k, v)]
-    cmd += ["-o", out, XML]
+    cmd += ["-o", out, xml]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     return O.read_pfm(out), r.stdout
@@ -49,6 +52,18 @@ def test_reference_cli_with_gpu_plugin(tmp_path):
     assert 0.9999 < ratio < 1.00001, ratio
     close = np.abs(gpu_r - gpu_c * ratio) <= 1e-4 + 1e-3 * gpu_c
     assert close.mean() >= 0.999, (float(close.mean()), float(np.abs(gpu_r - gpu_c * ratio).max()))
+
+
+def test_thinlens_conductor_roughdielectric_through_the_loader(tmp_path):
+    """plugin/extract.h for the SURVEY 8f item-2 plugins: `thinlens`, `conductor` (measured gold from data/ior) and
+    `roughdielectric` instantiated by the stock XML loader; same samples (ctr), classic scheduler, per-pixel match."""
+    d = dict(sampler="ctr", spp=8, res=64, rfilter="box")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, d, xml=XML_GLOSSY)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d, xml=XML_GLOSSY)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
 def test_gaussian_filter_and_independent_sampler_statistics(tmp_path):

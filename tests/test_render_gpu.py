@@ -89,7 +89,7 @@ def _li_image(pkg, ctx, sd):
     return L, film, stats
 
 
-@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct"])
+@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer)."""
@@ -105,6 +105,12 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
         # MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309) with emitterSamples = bsdfSamples = 1
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
         sd.set_integrator("direct")
+    elif name == "thinlens":
+        # ThinLens::sampleRay (src/sensors/thinlens.cpp:293-322); the parameters are those of make_golden_render.thinlens_case
+        sd = S.materials_scene(48, 32, spp=spp, max_depth=4, sampler="ctr", seed=seed)
+        s = sd.sensor
+        sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=spp, seed=seed, sampler="ctr",
+                      aperture_radius=0.12, focus_distance=5.2)
     else:
         sd = S.materials_scene(24, 16, spp=spp, max_depth=-1, sampler="ctr", seed=seed)
     L, film, stats = _li_image(pkg, ctx, sd)
