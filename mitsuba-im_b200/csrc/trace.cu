@@ -172,15 +172,22 @@ static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_
 		MTSB_CHECK(get_pipe(scene, 1, ob, &p));
 		return launch_trace(scene, mode, rays, n, out, p->work.ptr, ctx->stream, false);
 	}
-	// host path: chunks of 2M rays (64 MB in, 32 MB out; 1M and smaller measured slower), H2D on sIn, kernel on ctx->stream, D2H on sOut
+	// host path: chunks of 2M rays (64 MB in, 32 MB out; uniform 1M and smaller measured slower), H2D on sIn, kernel on ctx->stream, D2H on sOut
 	static size_t hostChunk = 0;
 	if (!hostChunk) { const char *e = getenv("MTSB_HOST_CHUNK"); hostChunk = e && atol(e) >= 1024 ? (size_t) atol(e) : (size_t) 1 << 21; }
 	const size_t chunk = std::min<size_t>(n, hostChunk);
 	MTSB_CHECK(get_pipe(scene, chunk, ob, &p));
-	const size_t nChunks = (n + chunk - 1) / chunk;
-	for (size_t c = 0; c < nChunks; ++c) {
+	// The H2D engine is the bottleneck and is busy from the first byte on; what the pipeline adds to the bare copy time is
+	// the tail — kernel + D2H of the LAST chunk.  So the last `chunk` rays go in halving pieces (1M, 512K, 512K; measured +12 % end to end,
+	// pieces below 256K lose it again to launch overheads).
+	static size_t minChunk = 0;
+	if (!minChunk) { const char *e = getenv("MTSB_HOST_TAPER"); minChunk = e ? (size_t) std::max(0L, atol(e)) : (size_t) 1 << 19; if (!minChunk) minChunk = hostChunk; }
+	size_t off = 0;
+	for (size_t c = 0; off < n; ++c) {
 		const int b = (int) (c % MTSB_PIPE_BUFS);
-		const size_t off = c * chunk, cnt = std::min(chunk, n - off);
+		const size_t remaining = n - off;
+		size_t cnt = std::min(chunk, remaining);
+		if (remaining <= chunk && remaining > minChunk) cnt = std::max(remaining / 2, minChunk);
 		// buffer b is free once the D2H of chunk c - MTSB_PIPE_BUFS is done
 		if (c >= MTSB_PIPE_BUFS) MTSB_CUDA(cudaStreamWaitEvent(p->sIn, p->outDone[b], 0));
 		MTSB_CUDA(cudaMemcpyAsync(p->rays[b].ptr, rays + off, cnt * sizeof(mtsb_ray), cudaMemcpyHostToDevice, p->sIn));
@@ -192,6 +199,7 @@ static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_
 		MTSB_CUDA(cudaStreamWaitEvent(p->sOut, p->kDone[b], 0));
 		MTSB_CUDA(cudaMemcpyAsync((uint8_t *) out + off * ob, p->out[b].ptr, cnt * ob, cudaMemcpyDeviceToHost, p->sOut));
 		MTSB_CUDA(cudaEventRecord(p->outDone[b], p->sOut));
+		off += cnt;
 	}
 	MTSB_CUDA(cudaStreamSynchronize(p->sOut));
 	MTSB_CUDA(cudaStreamSynchronize(ctx->stream));
