@@ -57,4 +57,5 @@ struct mtsb_render {
 	mtsb::DevBuf<uint32_t> bufQueue, bufCounters;
 	mtsb::DevBuf<unsigned long long> bufWork;
 	unsigned long long launches = 0;
+	float *hostStage = nullptr;    // page-locked staging for mtsb_film_to_host(accumulate = 1), allocated on first use
 };

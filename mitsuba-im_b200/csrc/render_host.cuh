@@ -118,6 +118,7 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 void mtsb_render_destroy(mtsb_render *r) {
 	if (!r) return;
 	cudaSetDevice(r->scene->ctx->device);
+	if (r->hostStage) cudaFreeHost(r->hostStage);
 	delete r;
 }
 
@@ -189,10 +190,14 @@ int mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumu
 		MTSB_CUDA(cudaStreamSynchronize(st));
 		return 0;
 	}
-	std::vector<float> tmp(float_count);
-	MTSB_CUDA(cudaMemcpyAsync(tmp.data(), r->dFilm.ptr, float_count * sizeof(float), cudaMemcpyDeviceToHost, st));
+	// accumulate (ResponsiveIntegrator contract: the caller's target holds un-normalised sums of earlier passes): the film
+	// lands in a page-locked staging buffer kept with the render — a fresh pageable vector per frame costs more in page
+	// faults than the copy itself
+	if (!r->hostStage) MTSB_CUDA(cudaMallocHost((void **) &r->hostStage, float_count * sizeof(float)));
+	MTSB_CUDA(cudaMemcpyAsync(r->hostStage, r->dFilm.ptr, float_count * sizeof(float), cudaMemcpyDeviceToHost, st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
-	for (size_t i = 0; i < float_count; ++i) dst[i] += tmp[i];
+	const float *src = r->hostStage;
+	for (size_t i = 0; i < float_count; ++i) dst[i] += src[i];
 	return 0;
 }
 
