@@ -96,6 +96,14 @@ def direct_case(td):
     li_case(td, "direct", sd)
 
 
+def strict_case(td):
+    """MonteCarloIntegrator's strictNormals and hideEmitters switches (src/librender/integrator.cpp:191-226,
+    src/integrators/path/path.cpp:136-165,196-199,218-222) on meshes with interpolated normals."""
+    sd = S.materials_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=23)
+    sd.set_integrator("path", max_depth=5, rr_depth=3, strict_normals=True, hide_emitters=True)
+    li_case(td, "strict", sd)
+
+
 def thinlens_case(td):
     """ThinLens::sampleRay (src/sensors/thinlens.cpp:293-322): the aperture sample is drawn right after the pixel sample."""
     sd = S.materials_scene(48, 32, spp=4, max_depth=4, sampler="ctr", seed=17)
@@ -114,3 +122,4 @@ if __name__ == "__main__":
         li_case(td, "materials_deep", S.materials_scene(24, 16, spp=2, max_depth=-1, sampler="ctr", seed=3))
         direct_case(td)
         thinlens_case(td)
+        strict_case(td)

@@ -89,7 +89,7 @@ def _li_image(pkg, ctx, sd):
     return L, film, stats
 
 
-@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens"])
+@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer)."""
@@ -105,6 +105,10 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
         # MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309) with emitterSamples = bsdfSamples = 1
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
         sd.set_integrator("direct")
+    elif name == "strict":
+        # strictNormals + hideEmitters (path.cpp:136-165,196-199,218-222); parameters of make_golden_render.strict_case
+        sd = S.materials_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)
+        sd.set_integrator("path", max_depth=5, rr_depth=3, strict_normals=True, hide_emitters=True)
     elif name == "thinlens":
         # ThinLens::sampleRay (src/sensors/thinlens.cpp:293-322); the parameters are those of make_golden_render.thinlens_case
         sd = S.materials_scene(48, 32, spp=spp, max_depth=4, sampler="ctr", seed=seed)
