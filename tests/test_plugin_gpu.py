@@ -66,6 +66,29 @@ def test_thinlens_conductor_roughdielectric_through_the_loader(tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_crop_window(tmp_path):
+    """Film crop window (hdrfilm cropOffsetX/Y, cropWidth/Height): the sensor's sample-to-camera matrix and the
+    ImageBlock size follow the crop (src/sensors/perspective.cpp:126-180, src/librender/film.cpp), per-pixel match."""
+    xml = open(XML).read().replace('<rfilter type="$rfilter"/>',
+        '<rfilter type="$rfilter"/><integer name="cropOffsetX" value="20"/><integer name="cropOffsetY" value="9"/>'
+        '<integer name="cropWidth" value="37"/><integer name="cropHeight" value="30"/>')
+    path = str(tmp_path / "cbox_crop.xml")
+    open(path, "w").write(xml)
+    d = dict(sampler="ctr", spp=8, res=64, rfilter="box")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, d, xml=path)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d, xml=path)
+    assert ref.shape == (30, 37, 3) and gpu.shape == ref.shape
+    assert "gpupath:" in log
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.97, "%.4f of the pixels match the reference's own render" % ok.mean()
+    # and the crop shows the same part of the scene as that window of the full frame (other random numbers: the sampler
+    # is keyed on crop-relative pixel coordinates, in the reference as well)
+    full, _ = run_mitsuba(str(tmp_path / "full.pfm"), True, True, d)
+    win = full[9:39, 20:57]
+    assert abs(gpu.mean() - win.mean()) <= 0.1 * win.mean()
+    assert np.corrcoef(gpu.mean(axis=2).ravel(), win.mean(axis=2).ravel())[0, 1] > 0.8
+
+
 def test_gaussian_filter_and_independent_sampler_statistics(tmp_path):
     """Gaussian film + the stock independent sampler: images agree statistically (relMSE well below the 1-vs-1 noise)."""
     # the reference seeds its independent sampler from the clock (src/libcore/random.cpp:479-483), so this comparison is
