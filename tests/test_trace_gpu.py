@@ -116,6 +116,30 @@ def test_edge_cases(pkg, ctx):
     bad.close()
 
 
+def test_host_batches_of_ragged_sizes(pkg, ctx):
+    """Host-pointer batches are cut into 2M-ray chunks with smaller pieces at the end, traversed on alternating streams
+    (csrc/trace.cu): every batch size around the chunk and taper boundaries must give, ray for ray and bit for bit, what
+    the same rays give inside one large batch — closest-hit records and any-hit flags."""
+    S, B = pkg.scenes, pkg.binding
+    V, N, F = S.displaced_sphere(5, seed=3)
+    sd = S.SceneDesc()
+    sd.add_mesh(V, N, F)
+    sc = sd.upload(ctx, B.BUILDER_LBVH)
+    try:
+        total = (1 << 22) + 12345
+        rays = S.chord_rays(total, radius=1.1, seed=7)
+        full = sc.ray_intersect(rays)
+        full_any = sc.ray_intersect_any(rays)
+        assert 0.3 < np.isfinite(full["t"]).mean() < 1.0
+        for n in (1, 31, 33, (1 << 18) + 1, (1 << 19) - 1, 1 << 19, (1 << 19) + 1, (1 << 20) + 3, (1 << 21) - 5, 1 << 21, (1 << 21) + 1,
+                  3 * (1 << 20) + 17, (1 << 22) - 1):
+            h = sc.ray_intersect(rays[:n])
+            assert h.tobytes() == full[:n].tobytes(), n
+            assert np.array_equal(sc.ray_intersect_any(rays[:n]), full_any[:n]), n
+    finally:
+        sc.close()
+
+
 def test_large_mesh_properties(pkg, ctx):
     """BASELINE config-2 scale (1.3 M triangles, 4 M rays): properties that need no oracle."""
     S, B = pkg.scenes, pkg.binding
