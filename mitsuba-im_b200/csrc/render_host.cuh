@@ -102,14 +102,14 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 	const size_t filmFloats = (size_t) (f.width + 2 * f.border) * (f.height + 2 * f.border) * f.channels;
 	int rc = r->dFilm.alloc(filmFloats);
 	if (rc == 0) rc = r->bufCounters.alloc(16);
-	if (rc == 0) rc = r->bufWork.alloc(16);
+	if (rc == 0) rc = r->bufWork.alloc(16 + 2 * SPLAT_STAT_STRIPES);
 	if (rc < 0) { delete r; return rc; }
 	f.data = r->dFilm.ptr;
 	r->ps.counters = r->bufCounters.ptr;
-	r->ps.work = r->bufWork.ptr; r->ps.stats = r->bufWork.ptr + 4;
+	r->ps.work = r->bufWork.ptr; r->ps.stats = r->bufWork.ptr + 4;     // stats[12 ..): striped path / depth counters of splat_kernel
 	cudaStream_t st = scene->ctx->stream;
 	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, filmFloats * sizeof(float), st));
-	MTSB_CUDA(cudaMemsetAsync(r->bufWork.ptr, 0, 16 * sizeof(unsigned long long), st));
+	MTSB_CUDA(cudaMemsetAsync(r->bufWork.ptr, 0, (16 + 2 * SPLAT_STAT_STRIPES) * sizeof(unsigned long long), st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	*out = r;
 	return 0;
@@ -133,7 +133,7 @@ int mtsb_render_clear(mtsb_render *r) {
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
 	cudaStream_t st = r->scene->ctx->stream;
 	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, r->dFilm.bytes(), st));
-	MTSB_CUDA(cudaMemsetAsync(r->ps.stats, 0, 8 * sizeof(unsigned long long), st));
+	MTSB_CUDA(cudaMemsetAsync(r->ps.stats, 0, (12 + 2 * SPLAT_STAT_STRIPES) * sizeof(unsigned long long), st));
 	r->launches = 0;
 	return 0;
 }
@@ -204,9 +204,10 @@ int mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumu
 int mtsb_render_stats(mtsb_render *r, uint64_t out[8]) {
 	if (!r || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_stats: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	unsigned long long h[4];
+	unsigned long long h[12 + 2 * SPLAT_STAT_STRIPES];
 	MTSB_CUDA(cudaMemcpyAsync(h, r->ps.stats, sizeof(h), cudaMemcpyDeviceToHost, r->scene->ctx->stream));
 	MTSB_CUDA(cudaStreamSynchronize(r->scene->ctx->stream));
+	for (int i = 0; i < SPLAT_STAT_STRIPES; ++i) { h[0] += h[12 + 2 * i]; h[3] += h[12 + 2 * i + 1]; }
 	for (int i = 0; i < 8; ++i) out[i] = 0;
 	out[0] = h[0]; out[1] = h[1]; out[2] = h[2]; out[3] = h[3]; out[4] = r->launches;
 	return 0;

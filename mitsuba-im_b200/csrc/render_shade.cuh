@@ -165,6 +165,7 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 #define SPLAT_TILE_W 16
 #define SPLAT_TILE_H 12
 #define SPLAT_MAX_CH 5
+#define SPLAT_STAT_STRIPES 64     // striped path-count / depth-sum counters behind ps.stats[12]
 
 __global__ void __launch_bounds__(RENDER_BLOCK)
 splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
@@ -244,7 +245,12 @@ splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
 	unsigned sum = depth;
 	#pragma unroll
 	for (int o = 16; o > 0; o >>= 1) { sum += __shfl_xor_sync(FULL, sum, o); one += __shfl_xor_sync(FULL, one, o); }
-	if (lane == 0 && one) { atomicAdd(ps.stats + 3, (unsigned long long) sum); atomicAdd(ps.stats + 0, (unsigned long long) one); }
+	// one pair of counters per 64 blocks' worth of stripes: half a million warps adding to ONE address cost more than the
+	// film atomics (the same-address adds serialise in L2: 1 ms of the 12 ms Cornell frame); mtsb_render_stats sums the stripes
+	if (lane == 0 && one) {
+		unsigned long long *stripe = ps.stats + 12 + 2 * (blockIdx.x & (SPLAT_STAT_STRIPES - 1));
+		atomicAdd(stripe + 1, (unsigned long long) sum); atomicAdd(stripe, (unsigned long long) one);
+	}
 }
 
 __global__ void prep_kernel(PathState ps, uint32_t *countOut, uint32_t *countShadow) {
