@@ -237,10 +237,17 @@ MTSB_API int  mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, c
 MTSB_API void mtsb_render_destroy(mtsb_render *r);
 MTSB_API int  mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera);
 MTSB_API int  mtsb_render_clear(mtsb_render *r);
+/* Live-path count below which one persistent kernel carries the surviving paths through all their remaining bounces
+ * instead of one wavefront round per bounce (csrc/render_tail.cuh).  0 = wavefront stages only, < 0 = the context's
+ * default (131072).  Results do not depend on it (same estimator, same random numbers); it exists so that tests can
+ * drive every path through either route. */
+MTSB_API int  mtsb_render_set_tail(mtsb_render *r, int paths);
 /* Render sample indices [spp_begin, spp_begin + spp_count) of every pixel in `rect` = {x0,y0,x1,y1}
  * (NULL = whole crop window); spp_total = the sampler's sampleCount (sets diffScaleFactor).
  * sample_stride/sample_phase select indices s with s % stride == phase (multi-GPU sample-pass split;
- * pass 1,0 for all).  Asynchronous on the context stream. */
+ * pass 1,0 for all).  Asynchronous on the context stream: the call queues its kernels and returns without waiting for
+ * the device (no host polling of queue counts, whatever maxDepth is); mtsb_render_sync / mtsb_film_to_host /
+ * mtsb_render_stats wait. */
 MTSB_API int  mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
                                const int32_t rect[4], uint32_t sample_stride, uint32_t sample_phase);
 MTSB_API int  mtsb_render_sync(mtsb_render *r);
@@ -248,6 +255,11 @@ MTSB_API int  mtsb_render_sync(mtsb_render *r);
 MTSB_API int  mtsb_film_device_ptr(mtsb_render *r, void **ptr_out, size_t *float_count_out);
 /* dst[i] += film[i] (accumulate != 0) or dst[i] = film[i]; dst is ImageBlock::getBitmap()->getFloatData(). */
 MTSB_API int  mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumulate);
+/* Copies the film into a page-locked staging buffer owned by the render (allocated on first use), waits for it and
+ * returns the pointer: for callers that merge the film into memory they share with other threads under their own lock
+ * (the ResponsiveIntegrator adapter; the reference's counterpart is ImageBlock::putAtomic, imageblock.h:223-318).
+ * The pointer stays valid until the next mtsb_film_stage / mtsb_film_to_host(accumulate) / mtsb_render_destroy. */
+MTSB_API int  mtsb_film_stage(mtsb_render *r, const float **stage_out, size_t *float_count_out);
 /* Statistics of the passes since the last clear: out[0]=camera paths, out[1]=closest-hit rays,
  * out[2]=shadow rays, out[3]=sum of path depths (avgPathLength numerator, path.cpp:290-291),
  * out[4]=kernel launches. */
@@ -255,6 +267,9 @@ MTSB_API int  mtsb_render_stats(mtsb_render *r, uint64_t out[8]);
 /* Radiance of single camera samples, for parity tests against MIPathTracer::Li with the `ctr`
  * sampler: samples n x 4 uint32 {px, py, sampleIndex, 0}; out n x 4 float {L.rgb, alpha}; host ptrs. */
 MTSB_API int  mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out);
+/* Same, and pos_out (n x 2 float, may be NULL) receives each sample's film position px + u (integrator.cpp:172), the
+ * argument ImageBlock::put sees — so that a test can restate the splat on the host. */
+MTSB_API int  mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out, float *pos_out);
 
 /* ---------------------------------------------------------------- multi-GPU film reduction ------- */
 /* The path shards by SAMPLE INDEX: every GPU holds the scene + BVH and renders the indices s = phase (mod stride) of

@@ -102,10 +102,10 @@ def lib():
         "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
         "mtsb_render_create": (i32, [vp, C.POINTER(Camera), C.POINTER(FilmDesc), C.POINTER(IntegratorDesc), u64, C.POINTER(vp)]),
         "mtsb_render_destroy": (None, [vp]), "mtsb_render_set_camera": (i32, [vp, C.POINTER(Camera)]),
-        "mtsb_render_clear": (i32, [vp]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
+        "mtsb_render_clear": (i32, [vp]), "mtsb_render_set_tail": (i32, [vp, i32]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
         "mtsb_render_sync": (i32, [vp]), "mtsb_film_device_ptr": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]),
-        "mtsb_film_to_host": (i32, [vp, vp, sz, i32]), "mtsb_render_stats": (i32, [vp, vp]),
-        "mtsb_render_samples": (i32, [vp, vp, sz, u32, vp]),
+        "mtsb_film_to_host": (i32, [vp, vp, sz, i32]), "mtsb_film_stage": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]), "mtsb_render_stats": (i32, [vp, vp]),
+        "mtsb_render_samples": (i32, [vp, vp, sz, u32, vp]), "mtsb_render_samples_ex": (i32, [vp, vp, sz, u32, vp, vp]),
         "mtsb_comm_version": (i32, []), "mtsb_comm_unique_id": (i32, [vp]),
         "mtsb_comm_create": (i32, [vp, i32, i32, vp, C.POINTER(vp)]), "mtsb_comm_create_all": (i32, [C.POINTER(vp), i32, C.POINTER(vp)]),
         "mtsb_comm_destroy": (None, [vp]), "mtsb_film_reduce": (i32, [vp, vp, i32]),
@@ -326,6 +326,10 @@ class Render:
     def clear(self):
         _check(lib().mtsb_render_clear(self.h))
 
+    def set_tail(self, paths):
+        """Live-path count below which the late-bounce kernel takes over (0 = wavefront stages only, -1 = default)."""
+        _check(lib().mtsb_render_set_tail(self.h, int(paths)))
+
     def render_pass(self, spp_begin, spp_count, spp_total, rect=None, stride=1, phase=0):
         r = None if rect is None else np.ascontiguousarray(rect, dtype=np.int32)
         _check(lib().mtsb_render_pass(self.h, spp_begin, spp_count, spp_total, _ptr(r), stride, phase))
@@ -355,11 +359,15 @@ class Render:
         return dict(paths=int(out[0]), closest_rays=int(out[1]), shadow_rays=int(out[2]), depth_sum=int(out[3]),
                     launches=int(out[4]))
 
-    def render_samples(self, samples, spp_total):
+    def render_samples(self, samples, spp_total, positions=False):
         s = np.ascontiguousarray(samples, dtype=np.uint32).reshape(-1, 4)
         out = np.zeros((s.shape[0], 4), np.float32)
-        _check(lib().mtsb_render_samples(self.h, _ptr(s), s.shape[0], spp_total, _ptr(out)))
-        return out
+        if not positions:
+            _check(lib().mtsb_render_samples(self.h, _ptr(s), s.shape[0], spp_total, _ptr(out)))
+            return out
+        pos = np.zeros((s.shape[0], 2), np.float32)
+        _check(lib().mtsb_render_samples_ex(self.h, _ptr(s), s.shape[0], spp_total, _ptr(out), _ptr(pos)))
+        return out, pos
 
     def close(self):
         if self.h:

@@ -651,10 +651,8 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 	DevBuf<float> dpCost; DevBuf<uint8_t> dpSplit; DevBuf<uint32_t> dpFlags;
 	const uint8_t *dpSplitPtr = nullptr;
 	{
-		const char *e = getenv("MTSB_COLLAPSE_DP");
-		if ((!e || atoi(e) != 0) && n > LEAF_MAX) {
-			const char *a = getenv("MTSB_DP_CNODE"), *b = getenv("MTSB_DP_CPRIM");
-			const float cNode = a ? (float) atof(a) : 1.0f, cPrim = b ? (float) atof(b) : 0.7f;
+		if (ctx->collapseDp && n > LEAF_MAX) {
+			const float cNode = ctx->dpCNode, cPrim = ctx->dpCPrim;
 			MTSB_CHECK(dpCost.alloc((size_t) (2 * n) * 7)); MTSB_CHECK(dpSplit.alloc((size_t) (2 * n) * 8)); MTSB_CHECK(dpFlags.alloc(n));
 			MTSB_CUDA(cudaMemsetAsync(dpFlags.ptr, 0, (size_t) n * sizeof(uint32_t), st));
 			const int minusOne = -1;     // PLOC never writes the root's parent
@@ -682,10 +680,14 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 	const uint32_t nodeCount = fin[0], slotCount = fin[1];
 	if (slotCount != primCount) MTSB_FAIL(MTSB_EINVAL, "build_bvh: %u primitives but %u leaf slots", primCount, slotCount);
 
-	MTSB_CHECK(out.nodes.alloc((size_t) nodeCount * 5));
-	MTSB_CUDA(cudaMemcpyAsync(out.nodes.ptr, nodesTmp.ptr, (size_t) nodeCount * 5 * sizeof(uint4), cudaMemcpyDeviceToDevice, st));
-	MTSB_CHECK(out.tris.alloc((size_t) slotCount * 3));
-	triaccel_kernel<<<div_up(slotCount, 256), 256, 0, st>>>(S, slotCount, slotPrim.ptr, out.tris.ptr);
+	// the traversal stack holds one entry per level (MTSB_STACK_SHARED + MTSB_STACK_LOCAL); a deeper tree (thousands of
+	// coincident centroids under duplicate Morton keys) would silently drop entries, so it is refused here instead
+	if (depth > 64) MTSB_FAIL(MTSB_EINVAL, "build_bvh: wide tree is %d levels deep, the traversal stack holds 64 (degenerate geometry: many coincident primitives?)", depth);
+	MTSB_CHECK(out.accel.alloc((size_t) nodeCount * 5 + (size_t) slotCount * 3));
+	out.nodes = out.accel.ptr; out.tris = (float4 *) (out.accel.ptr + (size_t) nodeCount * 5);
+	out.nodeBytes = (size_t) nodeCount * 5 * sizeof(uint4); out.triBytes = (size_t) slotCount * 3 * sizeof(float4);
+	MTSB_CUDA(cudaMemcpyAsync(out.nodes, nodesTmp.ptr, out.nodeBytes, cudaMemcpyDeviceToDevice, st));
+	triaccel_kernel<<<div_up(slotCount, 256), 256, 0, st>>>(S, slotCount, slotPrim.ptr, out.tris);
 	MTSB_CHECK(out.verts.alloc((size_t) slotCount * 5));
 	shading_record_kernel<<<div_up(slotCount, 256), 256, 0, st>>>(S, slotCount, slotPrim.ptr, out.verts.ptr);
 	MTSB_CUDA(cudaGetLastError());

@@ -5,8 +5,12 @@
 namespace mtsb {
 
 struct BvhResult {
-	DevBuf<uint4>  nodes;   // 5 x uint4 per wide node
-	DevBuf<float4> tris;    // 3 x float4 per leaf slot (TriAccel record)
+	// nodes and TriAccel records share ONE allocation (nodes first) so that a single cudaAccessPolicyWindow can keep the
+	// hot part of the acceleration structure resident in L2 while rays and hit records stream past it
+	DevBuf<uint4>  accel;
+	uint4  *nodes = nullptr;   // 5 x uint4 per wide node
+	float4 *tris = nullptr;    // 3 x float4 per leaf slot (TriAccel record)
+	size_t nodeBytes = 0, triBytes = 0;
 	DevBuf<float4> verts;   // 5 x float4 per leaf slot: the triangle's de-indexed vertices + normals + (shape, prim), see surface.cuh
 	uint32_t nodeCount = 0, slotCount = 0, leafCount = 0;
 	int depth = 0;

@@ -149,4 +149,16 @@ struct mtsb_ctx {
 	int device = 0;
 	int smCount = 0;
 	cudaStream_t stream = nullptr;
+	// Experiment knobs, read ONCE from the environment in mtsb_ctx_create (never from a kernel-launch path: the plugin
+	// calls the library from several mitsuba::Threads) and immutable afterwards.
+	size_t hostChunk = (size_t) 1 << 21;   // MTSB_HOST_CHUNK: rays per pipelined chunk of the host-pointer queries
+	size_t hostTaper = (size_t) 1 << 19;   // MTSB_HOST_TAPER: smallest piece at the end of a host batch (0 = no taper)
+	int fetchMinIdle = 8;                  // MTSB_FETCH_MIN_IDLE (trace.cuh)
+	int triMinLanes = 8;                   // MTSB_TRI_MIN_LANES (trace.cuh)
+	int collapseDp = 1;                    // MTSB_COLLAPSE_DP: cost-driven BVH8 collapse (0 = greedy)
+	float dpCNode = 1.0f, dpCPrim = 0.7f;  // MTSB_DP_CNODE / MTSB_DP_CPRIM
+	int tailPaths = 0;                     // MTSB_TAIL_PATHS: live-path count below which the late-bounce kernel takes over (render)
+	// L2 residency of the acceleration structure (cudaAccessPolicyWindow, see l2_window in scene.cuh)
+	size_t l2Persist = 0;                  // bytes of persisting L2 set aside for this device (0 = off, MTSB_L2_PERSIST=0)
+	size_t l2WindowMax = 0;                // cudaDevAttrMaxAccessPolicyWindowSize
 };

@@ -165,4 +165,5 @@ connect_kernel(SceneDev S, PathState ps, const uint32_t *count) {
 
 } // namespace mtsb
 #include "render_shade.cuh"
+#include "render_tail.cuh"
 #include "render_host.cuh"

@@ -18,8 +18,9 @@ struct PathState {
 	uint4  *rng;
 	float4 *shO, *shD, *shL;
 	uint32_t *queueA, *queueB;     // live path slots (ping-pong)
-	uint32_t *counters;            // [0] live in, [1] live out, [2] shadow count, [3..] statistics
-	unsigned long long *work;      // work counters of the persistent trace kernels [0] extend, [1] connect
+	uint32_t *counters;            // [0] queue A count, [1] queue B count, [2] shadow count, [4..7] hand-over to the tail kernel (render_tail.cuh)
+	unsigned long long *work;      // work counters of the persistent kernels [0] extend, [1] connect, [2] tail
+	volatile uint32_t *feedback;   // pinned host word (mapped): bounce at which the last chunk went to the tail kernel
 	unsigned long long *stats;     // [0] camera paths, [1] closest rays, [2] shadow rays, [3] depth sum
 };
 
@@ -57,5 +58,8 @@ struct mtsb_render {
 	mtsb::DevBuf<uint32_t> bufQueue, bufCounters;
 	mtsb::DevBuf<unsigned long long> bufWork;
 	unsigned long long launches = 0;
+	uint32_t *hostFeedback = nullptr;   // pinned + mapped, see PathState::feedback
+	int tailPaths = 0;                  // live-path count below which the tail kernel takes over (0 = never; mtsb_render_set_tail)
+	int waveBounces = 0;                // wavefront bounces enqueued per chunk before the tail kernel (adapted from hostFeedback)
 	float *hostStage = nullptr;    // page-locked staging for mtsb_film_to_host(accumulate = 1), allocated on first use
 };

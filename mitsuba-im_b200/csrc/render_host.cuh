@@ -23,39 +23,76 @@ static int ensure_capacity(mtsb_render *r, size_t paths) {
 
 static inline unsigned blocks_for(size_t n, unsigned b) { return (unsigned) std::max<size_t>(1, (n + b - 1) / b); }
 
-// Runs generate -> bounces -> splat for one chunk of `count` path slots.
-static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut) {
+// cudaLaunchKernelEx with the scene's L2 access-policy window attached (traversal kernels only)
+template <typename... KArgs, typename... Args>
+static int launch_trav(mtsb_scene *scene, void (*kernel)(KArgs...), unsigned grid, cudaStream_t st, Args... args) {
+	cudaLaunchAttribute attr[1];
+	cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof(cfg));
+	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(MTSB_TRACE_BLOCK); cfg.stream = st;
+	cfg.attrs = attr; cfg.numAttrs = l2_window(scene, attr);
+	MTSB_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+	return 0;
+}
+
+// Runs generate -> bounces -> splat for one chunk of `count` path slots.  Nothing here waits for the device: every
+// kernel reads its counts from device memory, the wavefront stages run for a number of bounces chosen from the
+// previous chunks' feedback word, and the tail kernel (render_tail.cuh) finishes whatever is alive after them — so the
+// call returns as soon as the launches are queued (mtsb_render_pass is asynchronous, as include/mtsb200.h says).
+static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, float *posOut = nullptr) {
 	mtsb_scene *scene = r->scene;
 	mtsb_ctx *ctx = scene->ctx;
 	cudaStream_t st = ctx->stream;
 	PathState &ps = r->ps;
-	uint32_t *cnt = ps.counters;       // [0] queue A count, [1] queue B count, [2] shadow count
+	uint32_t *cnt = ps.counters;       // [0] queue A count, [1] queue B count, [2] shadow count, [4..7] tail hand-over
 	const unsigned traceGrid = (unsigned) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM;
+	const unsigned shadeGrid = std::min(blocks_for(g.count, RENDER_BLOCK), (unsigned) ctx->smCount * MTSB_SHADE_MIN_BLOCKS * 2u);
 	SceneDev S = scene->dev; S.counters = nullptr;
 
-	MTSB_CUDA(cudaMemsetAsync(cnt, 0, 4 * sizeof(uint32_t), st));
+	MTSB_CUDA(cudaMemsetAsync(cnt, 0, 8 * sizeof(uint32_t), st));
 	generate_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(g, r->cam, ps, ps.queueA);
 	r->launches += 1;
 	uint32_t *qIn = ps.queueA, *qOut = ps.queueB, *cIn = cnt + 0, *cOut = cnt + 1;
 	const int maxDepth = r->integ.maxDepth;
 	const int bounded = maxDepth > 0 ? maxDepth : 1 << 30;
-	for (int bounce = 0; bounce < bounded; ++bounce) {
-		prep_kernel<<<1, 1, 0, st>>>(ps, cOut, cnt + 2);
-		extend_kernel<<<traceGrid, MTSB_TRACE_BLOCK, 0, st>>>(S, ps, qIn, cIn);
-		shade_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, qIn, qOut, cIn, cOut, cnt + 2);
-		connect_kernel<<<traceGrid, MTSB_TRACE_BLOCK, 0, st>>>(S, ps, cnt + 2);
+	const uint32_t tailBelow = (uint32_t) std::max(0, r->tailPaths);
+	// wavefront bounces to enqueue: all of them without the tail kernel, else what the feedback of earlier chunks suggests
+	if (tailBelow && r->hostFeedback) {
+		const uint32_t fb = r->hostFeedback[0], live = r->hostFeedback[1];
+		if (fb != 0xffffffffu) {
+			const bool forced = (fb & 0x80000000u) != 0;
+			const int at = (int) (fb & 0x7fffffffu);
+			if (!forced) r->waveBounces = at;
+			else if (live > 8u * tailBelow) r->waveBounces = at + 2;
+			else if (live > 2u * tailBelow) r->waveBounces = at + 1;
+			r->hostFeedback[0] = 0xffffffffu;
+		}
+	}
+	const int waves = tailBelow ? std::min(bounded, std::max(0, r->waveBounces)) : bounded;
+	uint32_t parity = 0;
+	int bounce = 0;
+	for (; bounce < waves; ++bounce) {
+		prep_kernel<<<1, 1, 0, st>>>(ps, cIn, cOut, cnt + 2, parity, (uint32_t) bounce, tailBelow, 0u);
+		MTSB_CHECK(launch_trav(scene, extend_kernel, traceGrid, st, S, ps, (const uint32_t *) qIn, (const uint32_t *) cIn));
+		shade_kernel<<<shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, qIn, qOut, cIn, cOut, cnt + 2);
+		MTSB_CHECK(launch_trav(scene, connect_kernel, traceGrid, st, S, ps, (const uint32_t *) (cnt + 2)));
 		r->launches += 4;
-		std::swap(qIn, qOut); std::swap(cIn, cOut);
-		// unbounded depth (or long chains): poll the live count every 4 bounces and stop when the queue is empty
-		if (maxDepth < 0 || (bounce & 3) == 3) {
+		std::swap(qIn, qOut); std::swap(cIn, cOut); parity ^= 1u;
+		// debugging configuration only (tail kernel switched off AND unbounded depth): the host has to look at the count
+		if (!tailBelow && maxDepth < 0 && (bounce & 7) == 7) {
 			uint32_t live = 0;
 			MTSB_CUDA(cudaMemcpyAsync(&live, cIn, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 			MTSB_CUDA(cudaStreamSynchronize(st));
 			if (live == 0) break;
+			if (bounce > 100000) MTSB_FAIL(MTSB_EINVAL, "render: path depth exceeded 100000 bounces");
 		}
-		if (bounce > 100000) MTSB_FAIL(MTSB_EINVAL, "render: path depth exceeded 100000 bounces");
 	}
-	splat_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(ps, r->film, g.count, samplesOut);
+	if (tailBelow && bounce < bounded) {
+		// hand whatever is alive to the tail kernel (a no-op if the hand-over already happened or nothing is left)
+		prep_kernel<<<1, 1, 0, st>>>(ps, cIn, nullptr, cnt + 2, parity, (uint32_t) bounce, tailBelow, 1u);
+		MTSB_CHECK(launch_trav(scene, tail_kernel, (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS, st, S, ps, r->integ, r->seed));
+		r->launches += 2;
+	}
+	splat_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(ps, r->film, g.count, samplesOut, posOut);
 	r->launches += 1;
 	MTSB_CUDA(cudaGetLastError());
 	return 0;
@@ -106,7 +143,14 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 	if (rc < 0) { delete r; return rc; }
 	f.data = r->dFilm.ptr;
 	r->ps.counters = r->bufCounters.ptr;
-	r->ps.work = r->bufWork.ptr; r->ps.stats = r->bufWork.ptr + 4;     // stats[12 ..): striped path / depth counters of splat_kernel
+	r->ps.work = r->bufWork.ptr; r->ps.stats = r->bufWork.ptr + 4;
+	r->tailPaths = scene->ctx->tailPaths; r->waveBounces = 3;
+	r->ps.feedback = nullptr;
+	if (cudaHostAlloc((void **) &r->hostFeedback, 2 * sizeof(uint32_t), cudaHostAllocMapped) == cudaSuccess) {
+		r->hostFeedback[0] = 0xffffffffu; r->hostFeedback[1] = 0;
+		uint32_t *dp = nullptr;
+		if (cudaHostGetDevicePointer((void **) &dp, r->hostFeedback, 0) == cudaSuccess) r->ps.feedback = dp;
+	} else { cudaGetLastError(); r->hostFeedback = nullptr; }     // stats[12 ..): striped path / depth counters of splat_kernel
 	cudaStream_t st = scene->ctx->stream;
 	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, filmFloats * sizeof(float), st));
 	MTSB_CUDA(cudaMemsetAsync(r->bufWork.ptr, 0, (16 + 2 * SPLAT_STAT_STRIPES) * sizeof(unsigned long long), st));
@@ -118,13 +162,23 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 void mtsb_render_destroy(mtsb_render *r) {
 	if (!r) return;
 	cudaSetDevice(r->scene->ctx->device);
+	cudaStreamSynchronize(r->scene->ctx->stream);     // passes are asynchronous: nothing of this render may still be queued
 	if (r->hostStage) cudaFreeHost(r->hostStage);
+	if (r->hostFeedback) cudaFreeHost(r->hostFeedback);
 	delete r;
 }
 
 int mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera) {
 	if (!r || !camera) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera: NULL argument");
 	fill_camera(r->cam, camera);       // kernel parameter only: no device traffic, no rebuild
+	return 0;
+}
+
+int mtsb_render_set_tail(mtsb_render *r, int paths) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_tail: NULL argument");
+	r->tailPaths = paths < 0 ? r->scene->ctx->tailPaths : paths;
+	r->waveBounces = 3;
+	if (r->hostFeedback) r->hostFeedback[0] = 0xffffffffu;
 	return 0;
 }
 
@@ -201,6 +255,19 @@ int mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumu
 	return 0;
 }
 
+int mtsb_film_stage(mtsb_render *r, const float **stage_out, size_t *float_count_out) {
+	if (!r || !stage_out) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_stage: NULL argument");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	cudaStream_t st = r->scene->ctx->stream;
+	const size_t n = r->dFilm.count;
+	if (!r->hostStage) MTSB_CUDA(cudaMallocHost((void **) &r->hostStage, n * sizeof(float)));
+	MTSB_CUDA(cudaMemcpyAsync(r->hostStage, r->dFilm.ptr, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	*stage_out = r->hostStage;
+	if (float_count_out) *float_count_out = n;
+	return 0;
+}
+
 int mtsb_render_stats(mtsb_render *r, uint64_t out[8]) {
 	if (!r || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_stats: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
@@ -214,6 +281,10 @@ int mtsb_render_stats(mtsb_render *r, uint64_t out[8]) {
 }
 
 int mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out) {
+	return mtsb_render_samples_ex(r, samples, n, spp_total, out, nullptr);
+}
+
+int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out, float *pos_out) {
 	(void) spp_total;
 	if (!r || !samples || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_samples: NULL argument");
 	if (n == 0) return 0;
@@ -221,12 +292,14 @@ int mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint3
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
 	cudaStream_t st = r->scene->ctx->stream;
 	MTSB_CHECK(ensure_capacity(r, n));
-	DevBuf<uint32_t> dS; DevBuf<float> dO;
+	DevBuf<uint32_t> dS; DevBuf<float> dO, dP;
 	MTSB_CHECK(dS.upload(samples, n * 4, st)); MTSB_CHECK(dO.alloc(n * 4));
+	if (pos_out) MTSB_CHECK(dP.alloc(n * 2));
 	GenParams g; memset(&g, 0, sizeof(g));
 	g.count = (uint32_t) n; g.samples = dS.ptr; g.seed = r->seed; g.pixPadded = 1; g.tilesX = 1; g.sppStride = 1;
-	MTSB_CHECK(run_chunk(r, g, dO.ptr));
+	MTSB_CHECK(run_chunk(r, g, dO.ptr, pos_out ? dP.ptr : nullptr));
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
+	if (pos_out) MTSB_CUDA(cudaMemcpyAsync(pos_out, dP.ptr, n * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	return 0;
 }

@@ -8,16 +8,14 @@ __device__ __forceinline__ float mi_weight(float pdfA, float pdfB) {   // path.c
 	return pdfA / (pdfA + pdfB);
 }
 
-// One thread per live path.  Line references are to src/integrators/path/path.cpp.
-#ifndef MTSB_SHADE_MIN_BLOCKS
-#define MTSB_SHADE_MIN_BLOCKS 5
-#endif
-__global__ void __launch_bounds__(RENDER_BLOCK, MTSB_SHADE_MIN_BLOCKS)
-shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const uint32_t *queueIn, uint32_t *queueOut,
-		const uint32_t *countIn, uint32_t *countOut, uint32_t *countShadow) {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= *countIn) return;
-	const uint32_t slot = queueIn[i];
+// What one shading step hands back to its caller: whether the path continues (its next ray is in ps.rayO/rayD[slot]) and
+// the shadow-ray entry of the emitter sample, if any.  The wavefront kernel appends both to queues, the late-bounce
+// kernel (render_tail.cuh) keeps them in registers.
+struct ShadeOut { bool alive, shadow; float4 shO, shD, shL; };
+
+// One shading step of one path; state lives in ps.*[slot].  Line references are to src/integrators/path/path.cpp.
+__device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
+		uint32_t slot, ShadeOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
 	float4 thr4 = ps.thr[slot], L4 = ps.L[slot], prev = ps.prev[slot], misc = ps.misc[slot];
 	const uint4 rg = ps.rng[slot];
@@ -147,11 +145,28 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 	if (alive) {
 		ps.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
 		ps.rng[slot] = make_uint4(rg.x, rg.y, rg.z, rs.dim);
-		queueOut[warp_append(countOut)] = slot;
 	}
-	if (shadow) {
-		const uint32_t k = warp_append(countShadow);
-		ps.shO[k] = shO; ps.shD[k] = shD; ps.shL[k] = shL;
+	out.alive = alive; out.shadow = shadow; out.shO = shO; out.shD = shD; out.shL = shL;
+}
+
+// One thread per live path, grid-stride: the grid is sized to the machine (render_host.cuh), not to the chunk, so a late
+// bounce with a few thousand survivors does not launch 65 K blocks that exit on the count.
+#ifndef MTSB_SHADE_MIN_BLOCKS
+#define MTSB_SHADE_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(RENDER_BLOCK, MTSB_SHADE_MIN_BLOCKS)
+shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const uint32_t *queueIn, uint32_t *queueOut,
+		const uint32_t *countIn, uint32_t *countOut, uint32_t *countShadow) {
+	const uint32_t n = *countIn;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const uint32_t slot = queueIn[i];
+		ShadeOut so;
+		shade_path(S, ps, integ, seed, slot, so);
+		if (so.alive) queueOut[warp_append(countOut)] = slot;
+		if (so.shadow) {
+			const uint32_t k = warp_append(countShadow);
+			ps.shO[k] = so.shO; ps.shD[k] = so.shD; ps.shL[k] = so.shL;
+		}
 	}
 }
 
@@ -168,7 +183,7 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const
 #define SPLAT_STAT_STRIPES 64     // striped path-count / depth-sum counters behind ps.stats[12]
 
 __global__ void __launch_bounds__(RENDER_BLOCK)
-splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
+splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut, float *posOut) {
 	__shared__ float shTile[RENDER_BLOCK / 32][SPLAT_TILE_W * SPLAT_TILE_H * SPLAT_MAX_CH];
 	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
 	const unsigned lane = threadIdx.x & 31u, FULL = 0xffffffffu;
@@ -185,6 +200,7 @@ splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
 		depth = __float_as_uint(misc.w);
 		if (samplesOut) {
 			((float4 *) samplesOut)[j] = L;
+			if (posOut) { posOut[2 * j] = misc.x; posOut[2 * j + 1] = misc.y; }
 		} else {
 			value[0] = L.x; value[1] = L.y; value[2] = L.z; value[3] = L.w;
 			ok = true;
@@ -251,12 +267,6 @@ splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut) {
 		unsigned long long *stripe = ps.stats + 12 + 2 * (blockIdx.x & (SPLAT_STAT_STRIPES - 1));
 		atomicAdd(stripe + 1, (unsigned long long) sum); atomicAdd(stripe, (unsigned long long) one);
 	}
-}
-
-__global__ void prep_kernel(PathState ps, uint32_t *countOut, uint32_t *countShadow) {
-	ps.work[0] = 0; ps.work[1] = 0;
-	if (countOut) *countOut = 0;
-	if (countShadow) *countShadow = 0;
 }
 
 // ---- pointwise plugin math for parity tests (mtsb_eval_bsdf / mtsb_eval_emitter) ----

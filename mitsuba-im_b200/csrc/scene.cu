@@ -9,6 +9,7 @@
 #include <stdarg.h>
 #include <string.h>
 #include <math.h>
+#include <algorithm>
 
 namespace mtsb {
 
@@ -67,6 +68,27 @@ int mtsb_ctx_create(int device, mtsb_ctx **out) {
 		MTSB_FAIL(MTSB_ENODEVICE, "mtsb_ctx_create: device %d is sm_%d%d; this build targets sm_100a (B200) only", device, prop.major, prop.minor);
 	mtsb_ctx *ctx = new mtsb_ctx();
 	ctx->device = device; ctx->smCount = prop.multiProcessorCount;
+	// experiment knobs: the environment is read here, once per context, and nowhere else in the library
+	if (const char *e = getenv("MTSB_HOST_CHUNK")) { if (atol(e) >= 1024) ctx->hostChunk = (size_t) atol(e); }
+	if (const char *e = getenv("MTSB_HOST_TAPER")) ctx->hostTaper = (size_t) std::max(0L, atol(e));
+	if (ctx->hostTaper == 0) ctx->hostTaper = ctx->hostChunk;
+	if (const char *e = getenv("MTSB_FETCH_MIN_IDLE")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctx->fetchMinIdle = v; }
+	if (const char *e = getenv("MTSB_TRI_MIN_LANES")) { const int v = atoi(e); if (v >= 1 && v <= 33) ctx->triMinLanes = v; }
+	if (const char *e = getenv("MTSB_COLLAPSE_DP")) ctx->collapseDp = atoi(e) != 0;
+	if (const char *e = getenv("MTSB_DP_CNODE")) ctx->dpCNode = (float) atof(e);
+	if (const char *e = getenv("MTSB_DP_CPRIM")) ctx->dpCPrim = (float) atof(e);
+	ctx->tailPaths = 1 << 17;
+	if (const char *e = getenv("MTSB_TAIL_PATHS")) ctx->tailPaths = std::max(0, atoi(e));
+	// L2 residency: set aside as much persisting L2 as the device grants (B200: 126 MB of L2); the traversal launches
+	// attach an access-policy window over the acceleration structure (scene.cuh: l2_window)
+	{
+		size_t want = (size_t) prop.persistingL2CacheMaxSize;
+		if (const char *e = getenv("MTSB_L2_PERSIST")) want = std::min<size_t>(want, (size_t) std::max(0L, atol(e)) << 20);
+		if (want > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+			size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitPersistingL2CacheSize);
+			ctx->l2Persist = got; ctx->l2WindowMax = (size_t) prop.accessPolicyMaxWindowSize;
+		} else cudaGetLastError();
+	}
 	cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
 	if (e != cudaSuccess) { delete ctx; MTSB_FAIL(MTSB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
 	*out = ctx;
@@ -284,14 +306,12 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	D.envEmitter = envEmitter; D.emitterNorm = emitterNorm;
 	D.counters = nullptr;
 	// tuning knob of the triangle phase (trace.cuh); MTSB_TRI_MIN_LANES overrides for experiments
-	D.triMinLanes = 8;
+	D.triMinLanes = ctx->triMinLanes;
 	D.oneBits = 0x3F800000u;
-	D.fetchMinIdle = 8;
-	if (const char *e = getenv("MTSB_FETCH_MIN_IDLE")) { const int v = atoi(e); if (v >= 1 && v <= 32) D.fetchMinIdle = v; }
-	if (const char *e = getenv("MTSB_TRI_MIN_LANES")) { const int v = atoi(e); if (v >= 1 && v <= 33) D.triMinLanes = v; }
+	D.fetchMinIdle = ctx->fetchMinIdle;
 
 	MTSB_CHECK(build_bvh(ctx, D, scene->primCount, builder, scene->bvh));
-	D.nodes = scene->bvh.nodes.ptr; D.tris = scene->bvh.tris.ptr; D.verts = scene->bvh.verts.ptr;
+	D.nodes = scene->bvh.nodes; D.tris = scene->bvh.tris; D.verts = scene->bvh.verts.ptr;
 	D.nodeCount = scene->bvh.nodeCount; D.slotCount = scene->bvh.slotCount;
 
 	// "Slightly enlarge the bounding box" — include/mitsuba/render/gkdtree.h:1213-1220 (max uses the already moved min)
@@ -339,8 +359,8 @@ int mtsb_scene_shape_offsets(const mtsb_scene *scene, uint32_t *out) {
 
 int mtsb_scene_build_stats(const mtsb_scene *scene, double out[8]) {
 	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_build_stats: scene not committed");
-	out[0] = scene->bvh.buildMs; out[1] = scene->bvh.nodeCount; out[2] = (double) scene->bvh.nodes.bytes();
-	out[3] = (double) scene->bvh.tris.bytes(); out[4] = scene->bvh.sahCost; out[5] = scene->bvh.leafCount;
+	out[0] = scene->bvh.buildMs; out[1] = scene->bvh.nodeCount; out[2] = (double) scene->bvh.nodeBytes;
+	out[3] = (double) scene->bvh.triBytes; out[4] = scene->bvh.sahCost; out[5] = scene->bvh.leafCount;
 	out[6] = scene->bvh.depth; out[7] = 0;
 	return 0;
 }

@@ -10,6 +10,7 @@
 #include "surface.cuh"
 #include <algorithm>
 #include <stdlib.h>
+#include <string.h>
 
 namespace mtsb {
 
@@ -24,7 +25,7 @@ struct BatchIO {
 
 	__device__ __forceinline__ void write_miss(unsigned long long i) const {
 		if (MODE == MODE_ANY) ((uint8_t *) out)[i] = 0;
-		else if (MODE == MODE_CLOSEST) ((float4 *) out)[i] = make_float4(INFINITY, 0.0f, 0.0f, __uint_as_float(MTSB_NO_HIT));
+		else if (MODE == MODE_CLOSEST) __stcs((float4 *) out + i, make_float4(INFINITY, 0.0f, 0.0f, __uint_as_float(MTSB_NO_HIT)));
 		else {
 			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
 			rec.t = INFINITY; rec.prim = MTSB_NO_HIT; rec.shape = MTSB_NO_HIT;
@@ -32,7 +33,9 @@ struct BatchIO {
 		}
 	}
 	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
-		const float4 r0 = __ldg(rays + 2 * i), r1 = __ldg(rays + 2 * i + 1);
+		// rays are read once and records written once: evict-first (ld/st.global.cs) so that the stream does not push the
+		// acceleration structure out of L2
+		const float4 r0 = __ldcs(rays + 2 * i), r1 = __ldcs(rays + 2 * i + 1);
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
 		if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, tmin, tmax, rcp)) return true;
 		write_miss(i);
@@ -45,7 +48,7 @@ struct BatchIO {
 		} else if (MODE == MODE_CLOSEST) {
 			const float4 c = __ldg(S.tris + (size_t) hit.slot * 3 + 2);
 			const uint32_t prim = S.shapes[__float_as_uint(c.z)].primOffset + __float_as_uint(c.w);
-			((float4 *) out)[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim));
+			__stcs((float4 *) out + i, make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim)));
 		} else {
 			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
 			Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
@@ -87,13 +90,17 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 	SceneDev S = scene->dev;
 	S.counters = count ? scene->dCounters.ptr : nullptr;
 	const float4 *r = (const float4 *) dRays;
-	#define LAUNCH(M) do { if (count) trace_kernel<M, true><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, n, dOut, dWork); \
-		else trace_kernel<M, false><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, n, dOut, dWork); } while (0)
+	const unsigned long long nn = n;
+	cudaLaunchAttribute attr[1];
+	cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof(cfg));
+	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(MTSB_TRACE_BLOCK); cfg.stream = st;
+	cfg.attrs = attr; cfg.numAttrs = l2_window(scene, attr);
+	#define LAUNCH(M) do { if (count) MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, true>, S, r, nn, dOut, dWork)); \
+		else MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, false>, S, r, nn, dOut, dWork)); } while (0)
 	if (mode == MODE_CLOSEST) LAUNCH(MODE_CLOSEST);
 	else if (mode == MODE_ANY) LAUNCH(MODE_ANY);
 	else LAUNCH(MODE_SURFACE);
 	#undef LAUNCH
-	MTSB_CUDA(cudaGetLastError());
 	return 0;
 }
 
@@ -115,15 +122,10 @@ struct TracePipe {
 
 using namespace mtsb;
 
-// one pipe per scene, created lazily (kept in a side table to keep scene.cuh free of it)
-#include <map>
-#include <mutex>
-static std::mutex g_pipeMutex;
-static std::map<mtsb_scene *, TracePipe *> g_pipes;
-
+// one pipe per scene, created on first use and owned by the scene
 static int get_pipe(mtsb_scene *scene, size_t chunk, size_t outBytesPerRay, TracePipe **outPipe) {
-	std::lock_guard<std::mutex> lock(g_pipeMutex);
-	TracePipe *&p = g_pipes[scene];
+	std::lock_guard<std::mutex> lock(scene->pipeMutex);
+	TracePipe *&p = scene->pipe;
 	if (!p) p = new TracePipe();
 	if (!p->ready) {
 		MTSB_CUDA(cudaStreamCreateWithFlags(&p->sIn, cudaStreamNonBlocking));
@@ -150,16 +152,15 @@ static int get_pipe(mtsb_scene *scene, size_t chunk, size_t outBytesPerRay, Trac
 }
 
 void mtsb_release_pipe(mtsb_scene *scene) {
-	std::lock_guard<std::mutex> lock(g_pipeMutex);
-	auto it = g_pipes.find(scene);
-	if (it == g_pipes.end()) return;
-	TracePipe *p = it->second;
+	std::lock_guard<std::mutex> lock(scene->pipeMutex);
+	TracePipe *p = scene->pipe;
+	if (!p) return;
 	if (p->ready) {
 		cudaStreamDestroy(p->sIn); cudaStreamDestroy(p->sOut); cudaStreamDestroy(p->sK2);
 		for (int i = 0; i < MTSB_PIPE_BUFS; ++i) { cudaEventDestroy(p->inDone[i]); cudaEventDestroy(p->kDone[i]); cudaEventDestroy(p->outDone[i]); }
 	}
 	delete p;
-	g_pipes.erase(it);
+	scene->pipe = nullptr;
 }
 
 static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_t n, void *out, int onDevice, const char *who) {
@@ -175,15 +176,13 @@ static int trace_common(mtsb_scene *scene, int mode, const mtsb_ray *rays, size_
 		return launch_trace(scene, mode, rays, n, out, p->work.ptr, ctx->stream, false);
 	}
 	// host path: chunks of 2M rays (64 MB in, 32 MB out; uniform 1M and smaller measured slower), H2D on sIn, kernel on ctx->stream, D2H on sOut
-	static size_t hostChunk = 0;
-	if (!hostChunk) { const char *e = getenv("MTSB_HOST_CHUNK"); hostChunk = e && atol(e) >= 1024 ? (size_t) atol(e) : (size_t) 1 << 21; }
+	const size_t hostChunk = ctx->hostChunk;
 	const size_t chunk = std::min<size_t>(n, hostChunk);
 	MTSB_CHECK(get_pipe(scene, chunk, ob, &p));
 	// The H2D engine is the bottleneck and is busy from the first byte on; what the pipeline adds to the bare copy time is
 	// the tail — kernel + D2H of the LAST chunk.  So the last two chunks' worth of rays goes in smaller pieces (1M, 1M,
 	// 1M, 512K, 512K; measured +12 % end to end, pieces below 256K lose it again to launch overheads).
-	static size_t minChunk = 0;
-	if (!minChunk) { const char *e = getenv("MTSB_HOST_TAPER"); minChunk = e ? (size_t) std::max(0L, atol(e)) : (size_t) 1 << 19; if (!minChunk) minChunk = hostChunk; }
+	const size_t minChunk = ctx->hostTaper;
 	size_t off = 0;
 	// Even and odd chunks traverse on two streams: a persistent grid ends with a tail in which the last warps finish
 	// their longest rays on a mostly idle GPU (≈ 0.17 ms per launch, measured: 2M rays 1.0 ms, 512K rays 0.36 ms); with

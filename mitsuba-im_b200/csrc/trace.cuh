@@ -128,7 +128,8 @@ __device__ __forceinline__ uint32_t node_test(const uint4 n0, const uint4 n1, co
 // the rest in local memory.
 struct TravStack {
 	uint2 *sh;            // &shared[threadIdx.x], stride blockDim.x
-	uint2 loc[MTSB_STACK_LOCAL];
+	uint2 *loc;           // MTSB_STACK_LOCAL entries of local memory, declared by the kernel (kept out of this struct so
+	                      // that the scalar members stay in registers)
 	int n;
 	__device__ __forceinline__ void push(uint2 v) {
 		if (n < MTSB_STACK_SHARED) sh[n * MTSB_TRACE_BLOCK] = v;
@@ -156,7 +157,7 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 		if (dir == 0) {
 			if (origin < minVal || origin > maxVal) return false;
 		} else {
-			const float rcp = __fdiv_rn(1.0f, dir);
+			const float rcp = __frcp_rn(dir);          // correctly rounded, bit-identical to 1.0f / dir without the division's slow path
 			rcps[i] = rcp;
 			float t1 = __fmul_rn(__fsub_rn(minVal, origin), rcp);
 			float t2 = __fmul_rn(__fsub_rn(maxVal, origin), rcp);
@@ -179,69 +180,44 @@ __device__ __forceinline__ bool clip_ray(const SceneDev &S, const V3 &o, const V
 	return maxt > mint;
 }
 
-// Persistent, warp-synchronous traversal of a whole ray batch.
-//
-// Every warp keeps 32 rays in flight.  Each loop iteration is warp-convergent (it starts with a full-mask
-// ballot): (1) lanes whose ray has finished have written their record; once MTSB_FETCH_MIN_IDLE lanes are idle the
-// warp pulls that many new rays from the global work counter with ONE atomic (lane 0) broadcast by shuffle, each
-// idle lane taking the slot given by its rank in the ballot; (2) every lane with a pending node group pops its
-// nearest child and tests the 8 quantised boxes; (3) lanes with leaf triangles test them; (4) lanes whose group is
-// exhausted pop the stack or finish.  ANY=false: closest hit (shrinks hit.t); ANY=true: first accepted hit ends the ray.
-//
-// IO supplies the rays and consumes the records:
-//   bool IO::load(i, o, d, tmin, tmax, rcp) -> rcp = 1/d from clip_ray; false if the ray needs no traversal (IO has already written a miss)
-//   void IO::store(i, found, hit, o, d)
-#ifndef MTSB_FETCH_MIN_IDLE
-#define MTSB_FETCH_MIN_IDLE 4
-#endif
+// Per-lane traversal state + one warp-convergent traversal iteration, shared by the persistent batch kernels
+// (trace_persistent) and by the late-bounce kernel of the path tracer (render_tail.cuh: trace_warp).
+struct Trav {
+	V3 o, d, idir;
+	float tmin;
+	HitRec hit;
+	uint2 ng, tg;                 // pending node group {child base, hit mask | imask} / triangle group {slot base, mask}
+	uint32_t octinv, octinv4;
+	bool active, found;
+	TravStack st;
 
-template <bool ANY, bool COUNT, class IO>
-__device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsigned long long n,
-		unsigned long long *__restrict__ workCounter, uint2 *shStack) {
-	const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
-	const unsigned FULL = 0xffffffffu;
-	bool active = false, exhausted = false, found = false;
-	V3 o = v3(0.0f), d = v3(0.0f), idir = v3(0.0f);
-	float tmin = 0;
-	HitRec hit; hit.t = 0; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
-	uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
-	uint32_t octinv = 0, octinv4 = 0;
-	unsigned long long idx = 0;
-	TravStack st; st.sh = shStack; st.n = 0;
-	unsigned nNodes = 0, nTris = 0;
-	const uint32_t one = S.oneBits;                 // 1.0f bit pattern from the parameter bank (see q_to_unit)
+	__device__ __forceinline__ void init(uint2 *shStack, uint2 *locStack) {
+		active = false; found = false;
+		o = v3(0.0f); d = v3(0.0f); idir = v3(0.0f); tmin = 0;
+		hit.t = 0; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
+		ng = make_uint2(0u, 0u); tg = make_uint2(0u, 0u); octinv = 0; octinv4 = 0;
+		st.sh = shStack; st.loc = locStack; st.n = 0;
+	}
+	// o, d, tmin already set; rcp = the exact reciprocals clip_ray computed; axis-parallel components are clamped
+	__device__ __forceinline__ void begin(float tmax, const V3 &rcp) {
+		idir = rcp;
+		const float tiny = 1e-18f, big = 1e18f;
+		if (!(fabsf(d.x) > tiny)) idir.x = copysignf(big, d.x);
+		if (!(fabsf(d.y) > tiny)) idir.y = copysignf(big, d.y);
+		if (!(fabsf(d.z) > tiny)) idir.z = copysignf(big, d.z);
+		octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
+		octinv4 = octinv * 0x01010101u;
+		ng = make_uint2(0u, 0x80000000u); tg = make_uint2(0u, 0u);
+		hit.t = tmax; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
+		found = false; st.n = 0; active = true;
+	}
 
-	for (;;) {
-		// ---- (1) refill idle lanes
-		const unsigned idleMask = __ballot_sync(FULL, !active);
-		const unsigned nIdle = __popc(idleMask);
-		if (!exhausted && nIdle >= (unsigned) S.fetchMinIdle) {
-			unsigned long long base = 0;
-			if (lane == 0) base = atomicAdd(workCounter, (unsigned long long) nIdle);
-			base = __shfl_sync(FULL, base, 0);
-			if (!active) {
-				idx = base + __popc(idleMask & ltMask);
-				if (idx < n) {
-					float tmax;
-					if (io.load(idx, o, d, tmin, tmax, idir)) {
-						// idir = the exact reciprocals clip_ray already computed; axis-parallel components are clamped
-						const float tiny = 1e-18f, big = 1e18f;
-						if (!(fabsf(d.x) > tiny)) idir.x = copysignf(big, d.x);
-						if (!(fabsf(d.y) > tiny)) idir.y = copysignf(big, d.y);
-						if (!(fabsf(d.z) > tiny)) idir.z = copysignf(big, d.z);
-						octinv = ((idir.x < 0 ? 1u : 0u) | (idir.y < 0 ? 2u : 0u) | (idir.z < 0 ? 4u : 0u)) ^ 7u;
-						octinv4 = octinv * 0x01010101u;
-						ng = make_uint2(0u, 0x80000000u); tg = make_uint2(0u, 0u);
-						hit.t = tmax; hit.u = hit.v = 0; hit.slot = 0xffffffffu;
-						found = false; st.n = 0; active = true;
-					}
-				}
-			}
-			if (base + nIdle >= n) exhausted = true;
-		}
-		if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
-
-		// ---- (2) node phase (lanes still holding untested triangles sit this one out: they drain one per iteration)
+	// One iteration: node phase, triangle phase, pop-or-finish.  Must be called by all 32 lanes of the warp (it ballots).
+	// Returns true for the lanes whose ray finished in this iteration (`active` is already false for them).
+	template <bool ANY, bool COUNT>
+	__device__ __forceinline__ bool step(const SceneDev &S, uint32_t one, unsigned &nNodes, unsigned &nTris) {
+		const unsigned FULL = 0xffffffffu;
+		// ---- node phase (lanes still holding untested triangles sit this one out: they drain one per iteration)
 		if (active && tg.y == 0) {
 			if (ng.y > 0x00ffffffu) {
 				const uint32_t bit = 31u - __clz(ng.y);
@@ -261,7 +237,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 			}
 		}
 
-		// ---- (3) triangle phase: ONE triangle per lane per round.  The first round runs whenever any lane has a triangle;
+		// ---- triangle phase: ONE triangle per lane per round.  The first round runs whenever any lane has a triangle;
 		// further rounds only while at least triMinLanes lanes still have one — draining a long leaf with two or three
 		// lanes active (the old while-loop: 2.5 of 32 threads, profiles/r01) costs more issue slots than letting those
 		// lanes skip a node step.  Round count is warp-uniform, so the loop stays convergent.
@@ -288,16 +264,73 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 			}
 		}
 
-		// ---- (4) pop or finish
+		// ---- pop or finish
 		if (active && tg.y == 0 && ng.y <= 0x00ffffffu) {
-			if (st.n == 0) { io.store(idx, found, hit, o, d); active = false; }
-			else ng = st.pop();
+			if (st.n == 0) { active = false; return true; }
+			ng = st.pop();
 		}
+		return false;
+	}
+};
+
+// Persistent, warp-synchronous traversal of a whole ray batch.
+//
+// Every warp keeps 32 rays in flight.  Each loop iteration is warp-convergent (it starts with a full-mask
+// ballot): (1) lanes whose ray has finished have written their record; once fetchMinIdle lanes are idle the
+// warp pulls that many new rays from the global work counter with ONE atomic (lane 0) broadcast by shuffle, each
+// idle lane taking the slot given by its rank in the ballot; (2) every lane with a pending node group pops its
+// nearest child and tests the 8 quantised boxes; (3) lanes with leaf triangles test them; (4) lanes whose group is
+// exhausted pop the stack or finish.  ANY=false: closest hit (shrinks hit.t); ANY=true: first accepted hit ends the ray.
+//
+// IO supplies the rays and consumes the records:
+//   bool IO::load(i, o, d, tmin, tmax, rcp) -> rcp = 1/d from clip_ray; false if the ray needs no traversal (IO has already written a miss)
+//   void IO::store(i, found, hit, o, d)
+template <bool ANY, bool COUNT, class IO>
+__device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsigned long long n,
+		unsigned long long *__restrict__ workCounter, uint2 *shStack) {
+	const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+	const unsigned FULL = 0xffffffffu;
+	bool exhausted = false;
+	uint2 locStack[MTSB_STACK_LOCAL];
+	Trav tv; tv.init(shStack, locStack);
+	unsigned long long idx = 0;
+	unsigned nNodes = 0, nTris = 0;
+	const uint32_t one = S.oneBits;                 // 1.0f bit pattern from the parameter bank (see q_to_unit)
+
+	for (;;) {
+		// ---- (1) refill idle lanes
+		const unsigned idleMask = __ballot_sync(FULL, !tv.active);
+		const unsigned nIdle = __popc(idleMask);
+		if (!exhausted && nIdle >= (unsigned) S.fetchMinIdle) {
+			unsigned long long base = 0;
+			if (lane == 0) base = atomicAdd(workCounter, (unsigned long long) nIdle);
+			base = __shfl_sync(FULL, base, 0);
+			if (!tv.active) {
+				idx = base + __popc(idleMask & ltMask);
+				if (idx < n) {
+					float tmax; V3 rcp;
+					if (io.load(idx, tv.o, tv.d, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
+				}
+			}
+			if (base + nIdle >= n) exhausted = true;
+		}
+		if (!__any_sync(FULL, tv.active)) { if (exhausted) break; else continue; }
+		// ---- (2)-(4)
+		if (tv.template step<ANY, COUNT>(S, one, nNodes, nTris)) io.store(idx, tv.found, tv.hit, tv.o, tv.d);
 	}
 	if (COUNT && S.counters) {
 		atomicAdd(S.counters, (unsigned long long) nNodes);
 		atomicAdd(S.counters + 1, (unsigned long long) nTris);
 	}
+}
+
+// Traces the ONE ray each lane holds in `tv` (tv.begin called by the lanes that have one) until every lane of the warp
+// is done; no refill.  Used where a warp owns 32 paths and alternates traversal with shading (render_tail.cuh).
+template <bool ANY>
+__device__ __forceinline__ void trace_warp(const SceneDev &S, Trav &tv) {
+	const uint32_t one = S.oneBits;
+	unsigned nNodes = 0, nTris = 0;
+	while (__any_sync(0xffffffffu, tv.active)) tv.template step<ANY, false>(S, one, nNodes, nTris);
 }
 
 } // namespace mtsb

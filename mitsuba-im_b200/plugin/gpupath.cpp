@@ -15,6 +15,7 @@
 #include <mitsuba/core/statistics.h>
 #include <mitsuba/core/lock.h>
 #include "extract.h"
+#include <map>
 
 MTS_NAMESPACE_BEGIN
 
@@ -22,7 +23,8 @@ MTS_NAMESPACE_BEGIN
 /// (src/im-mts/shell.cpp:240-242) does not rebuild the BVH.
 struct GPUDevice {
 	mtsb_ctx *ctx; mtsb_scene *scene; const Scene *owner;
-	GPUDevice() : ctx(NULL), scene(NULL), owner(NULL) { }
+	ref<Mutex> submit;     // held while one pass is being QUEUED on this GPU (the responsive path, several host threads per GPU)
+	GPUDevice() : ctx(NULL), scene(NULL), owner(NULL) { submit = new Mutex(); }
 	void ensure(int device, const Scene *s, int builder) {
 		if (!ctx) MTSB_CALL(mtsb_ctx_create(device, &ctx));
 		if (scene && owner == s) return;
@@ -51,8 +53,10 @@ public:
 	MTS_DECLARE_CLASS()
 protected:
 	virtual ~GPUResponsiveIntegrator();
+	Mutex *targetLock(const ImageBlock *target);
 	ref<GPUPathTracer> m_parent;
 	std::vector<mtsb_render *> m_renders;      // one per thread
+	std::map<const ImageBlock *, ref<Mutex> > m_targetLocks;
 	std::string m_stats;
 };
 
@@ -129,10 +133,15 @@ public:
 		for (int g = 0; g < m_gpus; ++g)
 			MTSB_CALL(mtsb_render_create(device(g, scene).scene, &cam, &fd, &id, seedFor(sampler), &renders[g]));
 		ref<Timer> timer = new Timer();
-		// GPU g renders sample indices s = g (mod gpus); passes are asynchronous, one stream per GPU
+		// GPU g renders sample indices s = g (mod gpus).  mtsb_render_pass only QUEUES work (no host wait inside), so this one
+		// thread keeps all devices busy: pass k goes to every GPU before anything is waited for.  A pass covers about one
+		// chunk of paths in flight (8 M) so that cancel() is looked at every few tens of milliseconds; the host waits for
+		// the devices only every fourth pass.
 		const uint32_t perGpu = (sampleCount + m_gpus - 1) / m_gpus;
-		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : perGpu;
-		for (uint32_t done = 0; done < perGpu && !m_cancel; done += pass) {
+		const size_t pixels = (size_t) film->getCropSize().x * film->getCropSize().y;
+		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixels, 1));
+		uint32_t passIdx = 0;
+		for (uint32_t done = 0; done < perGpu && !m_cancel; done += pass, ++passIdx) {
 			for (int g = 0; g < m_gpus; ++g) {
 				const uint32_t first = done, last = std::min(perGpu, done + pass);
 				// the k-th local sample of GPU g has index g + k * gpus; drop indices beyond sampleCount
@@ -140,8 +149,9 @@ public:
 				for (uint32_t k = first; k < last; ++k) if ((uint32_t) g + k * m_gpus < sampleCount) ++cnt;
 				if (cnt) MTSB_CALL(mtsb_render_pass(renders[g], first * m_gpus, cnt, sampleCount, NULL, m_gpus, g));
 			}
-			for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_sync(renders[g]));
+			if ((passIdx & 3) == 3) for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_sync(renders[g]));
 		}
+		for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_sync(renders[g]));
 		float *dst = block->getBitmap()->getFloatData();
 		const size_t n = (size_t) block->getBitmap()->getSize().x * block->getBitmap()->getSize().y * block->getChannelCount();
 		uint64_t st[8] = { 0 }, tot[8] = { 0 };

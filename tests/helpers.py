@@ -13,8 +13,13 @@ T_REL = 1e-5
 PRIM_AGREE = 0.9999
 
 
-def compare_hits(rays, t, prim, ref_t, ref_prim, p=None, ref_p=None, min_agree=PRIM_AGREE, cos=None):
+def compare_hits(rays, t, prim, ref_t, ref_prim, p=None, ref_p=None, min_agree=PRIM_AGREE, cos=None, exclude=None):
+    """exclude: boolean mask of rays left out of every figure (callers say in a comment which rays and why)."""
     rays = np.asarray(rays).view(np.float32).reshape(-1, 8)
+    if exclude is not None and exclude.any():
+        keep = ~exclude
+        return compare_hits(rays[keep], t[keep], prim[keep], ref_t[keep], ref_prim[keep], None if p is None else p[keep],
+                            None if ref_p is None else ref_p[keep], min_agree, None if cos is None else cos[keep])
     ref_hit = np.isfinite(ref_t)
     hit = np.isfinite(t)
     miss_agree = (hit == ref_hit).mean()
@@ -30,12 +35,29 @@ def compare_hits(rays, t, prim, ref_t, ref_prim, p=None, ref_p=None, min_agree=P
     m = ref_hit & hit & (prim.astype(np.int64) == ref_prim.astype(np.int64))
     scale = np.maximum(np.maximum(np.abs(ref_t[m]), np.abs(rays[m, 0:3]).max(axis=1)), 1.0)
     cond = np.ones(int(m.sum()), np.float32) if cos is None else np.maximum(np.abs(cos[m]), 1e-4)
-    dt = np.abs(t[m] - ref_t[m]) * cond / scale
+    raw = np.abs(t[m] - ref_t[m]) / scale          # the UNWEIGHTED relative error, reported beside the weighted one
+    dt = raw * cond
     assert dt.max() <= T_REL, "t differs by %.3g (scaled) > %.1g" % (dt.max(), T_REL)
     if p is not None:
         dp = np.abs(p[m] - ref_p[m]).max(axis=1) * cond / scale
         assert dp.max() <= T_REL * 2, "hit point differs by %.3g (scaled)" % dp.max()
-    return dict(agree=float(agree), strict=float(strict), miss_agree=float(miss_agree), max_dt=float(dt.max()) if m.any() else 0.0)
+    return dict(agree=float(agree), strict=float(strict), miss_agree=float(miss_agree), n=int(rays.shape[0]),
+                max_dt=float(dt.max()) if m.any() else 0.0, max_dt_unweighted=float(raw.max()) if m.any() else 0.0,
+                p9999_dt_unweighted=float(np.quantile(raw, 0.9999)) if m.any() else 0.0,
+                frac_dt_unweighted_over_tol=float((raw > T_REL).mean()) if m.any() else 0.0)
+
+
+def compare_barycentrics(rays, u, v, ref_u, ref_v, e1, e2, ref_t, cos=None):
+    """Barycentrics of rays on which both sides report the same primitive.  du is a displacement of the hit point along the
+    triangle edge e1 (dv: e2), so |du| * |e1| is held to the same 1e-5 * scale as t (perpendicular to the surface the
+    displacement is |dt| * cos; along it |dt| * sin / ... — callers pass cos = |d . ng| as for t).  Returns the raw figures."""
+    rays = np.asarray(rays).view(np.float32).reshape(-1, 8)
+    scale = np.maximum(np.maximum(np.abs(ref_t), np.abs(rays[:, 0:3]).max(axis=1)), 1.0)
+    cond = np.ones(len(u), np.float32) if cos is None else np.maximum(np.abs(cos), 1e-4)
+    du, dv = np.abs(u - ref_u), np.abs(v - ref_v)
+    eu, ev = du * np.linalg.norm(e1, axis=1) * cond / scale, dv * np.linalg.norm(e2, axis=1) * cond / scale
+    assert eu.max() <= 2 * T_REL and ev.max() <= 2 * T_REL, "barycentrics differ by %.3g / %.3g (edge-scaled)" % (eu.max(), ev.max())
+    return dict(max_du=float(du.max()), max_dv=float(dv.max()), max_du_scaled=float(eu.max()), max_dv_scaled=float(ev.max()))
 
 
 def desc_from_golden(S, gold, kind):

@@ -20,13 +20,22 @@ def test_restatement_matches_reference_hits(pkg, golden, kind):
     # Rectangle::fillIntersectionRecord leaves primIndex unset; compare by shape there
     rect_hit = (gold["ref_shape"] >= 0) & is_rect[np.maximum(gold["ref_shape"], 0)]
     ref_prim = np.where(rect_hit, offs[np.maximum(gold["ref_shape"], 0)], ref_prim)
-    # the Cornell set contains shadow rays that start ON the light rectangle and graze it (|d.n| ~ 1e-7): their
-    # self-intersection is decided by rounding in Rectangle::rayIntersect, hence the looser bound there
-    bound = 0.9995 if kind == "sphere" else 0.995
-    st = helpers.compare_hits(gold["rays"], t, prim.view(np.int32), gold["ref_t"], ref_prim, min_agree=bound)
-    assert st["miss_agree"] >= bound
-    a = osc.any(gold["rays"])
-    assert (a == gold["ref_any"]).mean() >= bound
+    # the Cornell set contains 14 shadow rays that start ON the light rectangle and run inside its plane (|d.n| < 1e-5):
+    # their self-intersection is decided by the last bit of -o.z / d.z in Rectangle::rayIntersect.  They are tagged by
+    # that geometric criterion and left out; every other ray is held to the north-star bound (99.99 %)
+    rays = gold["rays"]
+    graze = (np.abs(rays[:, 1] - 1.98) < 1e-4) & (np.abs(rays[:, 5]) < 1e-5) if kind == "cornell" else np.zeros(len(rays), bool)
+    st = helpers.compare_hits(rays, t, prim.view(np.int32), gold["ref_t"], ref_prim, min_agree=helpers.PRIM_AGREE, exclude=graze)
+    assert st["miss_agree"] >= helpers.PRIM_AGREE and st["max_dt_unweighted"] <= helpers.T_REL
+    a = osc.any(rays)
+    assert (a == gold["ref_any"])[~graze].mean() >= helpers.PRIM_AGREE
+    # barycentrics of the reference (its.uv = (b1, b2) on a mesh without texture coordinates) on the sphere set
+    if kind == "sphere":
+        m = np.isfinite(t) & (prim.view(np.int32) == ref_prim)
+        f = gold["F"][np.maximum(gold["ref_prim"], 0)]
+        e1, e2 = gold["V"][f[:, 1]] - gold["V"][f[:, 0]], gold["V"][f[:, 2]] - gold["V"][f[:, 0]]
+        cos = np.abs((rays[:, 4:7] * gold["ref_ng"]).sum(axis=1))
+        helpers.compare_barycentrics(rays[m], u[m], v[m], gold["ref_u"][m], gold["ref_v"][m], e1[m], e2[m], gold["ref_t"][m], cos=cos[m])
 
 
 def test_restatement_aabb_is_enlarged_like_the_kdtree(pkg):

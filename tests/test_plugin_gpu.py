@@ -102,23 +102,35 @@ def test_gaussian_filter_and_independent_sampler_statistics(tmp_path):
     assert abs(gpu.mean() - ref.mean()) < 0.01 * ref.mean()
 
 
+def _gpupath_rate(log):
+    """`gpupath: ... %.1f M samples/s` of the classic path's summary line."""
+    import re
+    m = re.search(r"gpupath: .* ([0-9.]+) M samples/s", log)
+    assert m, log[-2000:]
+    return float(m.group(1))
+
+
 def test_plugin_two_gpus_film_reduce(tmp_path):
     """`<integer name="gpus" value="2"/>`: the plugin splits the sample indices over two devices inside the reference's own
     process and sums the films with mtsb_comm_create_all + mtsb_film_reduce_all (system NCCL, bound by dlopen) before the
-    single D2H into the ImageBlock.  Same counter sampler => the image equals the 1-GPU one up to float summation order."""
+    single D2H into the ImageBlock.  Same counter sampler => the image equals the 1-GPU one up to float summation order;
+    and because mtsb_render_pass only queues work, the one host thread keeps both devices busy: a render long enough to
+    time (1024^2, 256 spp) runs at >= 1.6x the one-GPU rate."""
     import __graft_entry__ as graft
     if graft.load_package().binding.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
-    global XML
     src = open(XML).read()
     xml2 = str(tmp_path / "cbox_2gpu.xml")
     open(xml2, "w").write(src.replace('<integer name="maxDepth" value="5"/>', '<integer name="maxDepth" value="5"/><integer name="gpus" value="2"/>'))
+    assert 'name="gpus"' in open(xml2).read()
     d = dict(sampler="ctr", spp=16, res=64, rfilter="gaussian")
     one, _ = run_mitsuba(str(tmp_path / "one.pfm"), True, True, d)
-    keep, XML = XML, xml2
-    try:
-        two, log = run_mitsuba(str(tmp_path / "two.pfm"), True, True, d)
-    finally:
-        XML = keep
+    two, log = run_mitsuba(str(tmp_path / "two.pfm"), True, True, d, xml=xml2)
     assert "2 GPUs" in log, "the plugin did not run on two devices"
     assert np.allclose(two, one, rtol=2e-4, atol=1e-5), float(np.abs(two - one).max())
+    big = dict(sampler="ctr", spp=256, res=1024, rfilter="gaussian")
+    _, log1 = run_mitsuba(str(tmp_path / "big1.pfm"), True, True, big)
+    _, log2 = run_mitsuba(str(tmp_path / "big2.pfm"), True, True, big, xml=xml2)
+    r1, r2 = _gpupath_rate(log1), _gpupath_rate(log2)
+    print("plugin, classic scheduler: 1 GPU %.1f, 2 GPUs %.1f M samples/s (x%.2f)" % (r1, r2, r2 / r1))
+    assert r2 >= 1.6 * r1, (r1, r2)

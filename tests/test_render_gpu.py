@@ -73,13 +73,21 @@ def test_emitter_sampling_matches_reference(pkg, ctx, golden):
         sc.close()
 
 
-def _li_image(pkg, ctx, sd):
+TAIL_ALL, TAIL_OFF = 1 << 30, 0     # every path through the late-bounce kernel / wavefront stages only (csrc/render_tail.cuh)
+
+
+def _li_image(pkg, ctx, sd, tail=-1, positions=False):
     sc = sd.upload(ctx)
     w, h, spp = sd.sensor["width"], sd.sensor["height"], sd.sampler["spp"]
     rd = pkg.binding.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=sd.sampler["seed"])
+    rd.set_tail(tail)
     ys, xs, ss = np.meshgrid(np.arange(h), np.arange(w), np.arange(spp), indexing="ij")
     samples = np.stack([xs.ravel(), ys.ravel(), ss.ravel(), np.zeros(xs.size)], axis=1).astype(np.uint32)
-    L = rd.render_samples(samples, spp).reshape(h, w, spp, 4)
+    if positions:
+        L, pos = rd.render_samples(samples, spp, positions=True)
+        L = np.concatenate([L, pos], axis=1).reshape(h, w, spp, 6)
+    else:
+        L = rd.render_samples(samples, spp).reshape(h, w, spp, 4)
     # the same samples through the film (ImageBlock layout, un-normalised sums)
     rd.render_pass(0, spp, spp)
     film = rd.film_to_host()
@@ -89,10 +97,12 @@ def _li_image(pkg, ctx, sd):
     return L, film, stats
 
 
+@pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict"])
-def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
+def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
-    the same random numbers (ctr sampler, box filter, classic block renderer)."""
+    the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
+    stages and once with every path carried by the late-bounce kernel."""
     S = pkg.scenes
     g = golden("li_%s.npz" % name)
     ref = g["image"]
@@ -117,7 +127,7 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
                       aperture_radius=0.12, focus_distance=5.2)
     else:
         sd = S.materials_scene(24, 16, spp=spp, max_depth=-1, sampler="ctr", seed=seed)
-    L, film, stats = _li_image(pkg, ctx, sd)
+    L, film, stats = _li_image(pkg, ctx, sd, tail=tail)
     img = L[..., 0:3].mean(axis=2)
     ok = _close(img, ref, 2e-3, 2e-4).all(axis=2)
     # a path whose hit flips across a triangle edge (rounding) takes a different course: bounded fraction of pixels
@@ -136,25 +146,52 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name):
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
 
 
-def test_gaussian_film_splat_matches_imageblock_put(pkg, ctx):
-    """Gaussian reconstruction filter: the device film equals ImageBlock::put applied (on the host, numpy) to the very
-    samples the device rendered."""
+def _imageblock_put(shape, border, radius, table, pos, values):
+    """ImageBlock::put(pos, value) restated in numpy (include/mitsuba/render/imageblock.h:161-221): offset 0, the filter's
+    32-entry table through evalDiscretized (rfilter.h:76-77), float64 accumulation."""
+    out = np.zeros(shape, np.float64)
+    size_y, size_x = shape[0], shape[1]
+    scale = np.float32(31.0) / np.float32(radius)
+    px = pos[:, 0].astype(np.float32) - np.float32(0.5) - np.float32(-border)
+    py = pos[:, 1].astype(np.float32) - np.float32(0.5) - np.float32(-border)
+    r = np.float32(radius)
+    x0 = np.maximum(np.ceil(px - r).astype(np.int64), 0); x1 = np.minimum(np.floor(px + r).astype(np.int64), size_x - 1)
+    y0 = np.maximum(np.ceil(py - r).astype(np.int64), 0); y1 = np.minimum(np.floor(py + r).astype(np.int64), size_y - 1)
+    span = int(np.ceil(2 * radius)) + 1
+    for dy in range(span):
+        y = y0 + dy
+        wy = table[np.minimum((np.abs((y.astype(np.float32) - py)) * scale).astype(np.int64), 31)]
+        for dx in range(span):
+            x = x0 + dx
+            ok = (y <= y1) & (x <= x1)
+            wx = table[np.minimum((np.abs((x.astype(np.float32) - px)) * scale).astype(np.int64), 31)]
+            w = (wx * wy).astype(np.float32)
+            np.add.at(out, (y[ok], x[ok]), (w[ok, None] * values[ok]).astype(np.float64))
+    return out
+
+
+@pytest.mark.parametrize("rfilter", ["gaussian", "box"])
+def test_film_splat_matches_imageblock_put_per_pixel(pkg, ctx, rfilter):
+    """The device film equals, pixel by pixel and channel by channel, ImageBlock::put applied on the host to the very
+    samples the device rendered (position px + u and radiance of every sample come back through
+    mtsb_render_samples_ex).  The Gaussian filter (sigma 0.5, radius 2, border 2) is the one configs 3-5 use; its
+    warp-tiled shared-memory accumulation (render_shade.cuh: splat_kernel) is what this pins."""
     S = pkg.scenes
-    sd = S.cornell_box(24, 20, spp=2, max_depth=3, sampler="ctr", seed=5, rfilter="gaussian")
-    L, film, _ = _li_image(pkg, ctx, sd)
+    sd = S.cornell_box(40, 28, spp=3, max_depth=3, sampler="ctr", seed=5, rfilter=rfilter)
+    L, film, _ = _li_image(pkg, ctx, sd, positions=True)
     fd = sd.film()
-    r, table, border = S.filter_table("gaussian")
-    assert border == fd.border == 2
+    r, table, border = S.filter_table(rfilter)
+    assert border == fd.border
     h, w, spp = L.shape[0:3]
-    ref = np.zeros_like(film, dtype=np.float64)
-    # sample positions are px + u with u the first two numbers of the stream; recover them from a 1-bounce-free query:
-    # render_samples does not return positions, so compare through total energy and per-channel sums instead
     assert film.shape == (h + 2 * border, w + 2 * border, 5)
-    for c in range(3):
-        assert abs(film[..., c].sum() - L[..., c].sum()) <= 1e-2 * L[..., c].sum()       # the 32-bin table integrates to ~one
-    assert abs(film[..., 4].sum() - h * w * spp) <= 1e-2 * h * w * spp
-    assert (film >= 0).all() and np.isfinite(film).all()
-    del ref
+    flat = L.reshape(-1, 6)
+    values = np.concatenate([flat[:, 0:4], np.ones((flat.shape[0], 1), np.float32)], axis=1).astype(np.float32)
+    ref = _imageblock_put(film.shape, border, r, np.asarray(table, np.float32), flat[:, 4:6], values)
+    # float32 atomics in a different order than the host's float64 sums: 1e-5 relative to the pixel's own magnitude
+    tol = 1e-5 * np.maximum(np.abs(ref), 1.0) + 1e-6
+    bad = np.abs(film - ref) > tol
+    assert not bad.any(), "%d of %d film floats differ, worst %.3g" % (bad.sum(), bad.size, np.abs(film - ref).max())
+    assert abs(film[..., 4].sum() - ref[..., 4].sum()) <= 1e-5 * ref[..., 4].sum()
 
 
 def test_image_is_unbiased_against_live_reference(pkg, ctx, tmp_path):

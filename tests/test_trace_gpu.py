@@ -28,20 +28,44 @@ def test_hits_match_reference_golden(pkg, ctx, golden, kind, builder):
     sd = helpers.desc_from_golden(pkg.scenes, gold, kind)
     sc = sd.upload(ctx, builder)
     try:
-        hits = sc.ray_intersect(gold["rays"])
-        surf = sc.ray_intersect_surface(gold["rays"])
-        bound = 0.9999 if kind == "sphere" else 0.995   # see tests/test_oracle.py for the grazing self-hit rays
-        cos = np.abs((gold["rays"][:, 4:7] * gold["ref_ng"]).sum(axis=1))
-        st = helpers.compare_hits(gold["rays"], hits["t"], hits["prim"].view(np.int32), gold["ref_t"], _global_ref_prim(sd, gold),
-                                  p=surf["p"], ref_p=gold["ref_p"], min_agree=bound, cos=cos)
-        assert st["miss_agree"] >= bound
+        rays = gold["rays"]
+        hits = sc.ray_intersect(rays)
+        surf = sc.ray_intersect_surface(rays)
+        # The Cornell set holds 14 shadow rays that START ON the light rectangle (y = 1.98) and run inside its plane
+        # (|d.n| < 1e-5): whether such a ray "hits" the rectangle it lies in is decided by the last bit of -o.z / d.z in
+        # Rectangle::rayIntersect (rectangle.cpp:125-147).  They are tagged by that geometric criterion and left out;
+        # every other ray is held to the north-star bound.
+        graze = (np.abs(rays[:, 1] - 1.98) < 1e-4) & (np.abs(rays[:, 5]) < 1e-5) if kind == "cornell" else np.zeros(len(rays), bool)
+        assert graze.sum() == (14 if kind == "cornell" else 0)
+        ref_prim = _global_ref_prim(sd, gold)
+        cos = np.abs((rays[:, 4:7] * gold["ref_ng"]).sum(axis=1))
+        st = helpers.compare_hits(rays, hits["t"], hits["prim"].view(np.int32), gold["ref_t"], ref_prim,
+                                  p=surf["p"], ref_p=gold["ref_p"], min_agree=helpers.PRIM_AGREE, cos=cos, exclude=graze)
+        assert st["miss_agree"] >= helpers.PRIM_AGREE
+        # on these sets the UNWEIGHTED relative t error is inside the tolerance too
+        assert st["max_dt_unweighted"] <= helpers.T_REL, st
         # record fill: normals as fillIntersectionRecord computes them
-        m = np.isfinite(gold["ref_t"]) & (surf["prim"].view(np.int32) == _global_ref_prim(sd, gold))
+        m = np.isfinite(gold["ref_t"]) & (surf["prim"].view(np.int32) == ref_prim) & ~graze
         assert np.abs(surf["ng"][m] - gold["ref_ng"][m]).max() < 2e-4
         assert np.abs(surf["ns"][m] - gold["ref_ns"][m]).max() < 2e-4
         assert (surf["t"] == hits["t"]).all() or np.allclose(surf["t"], hits["t"], equal_nan=True)
-        a = sc.ray_intersect_any(gold["rays"])
-        assert (a == gold["ref_any"]).mean() >= bound
+        # its.uv of the reference (ref_u, ref_v): barycentrics (b1, b2) on meshes without texture coordinates
+        # (skdtree.h:409-411), 0.5 (x + 1) on rectangles (rectangle.cpp:160) — against the record's uv
+        is_rect = np.array([s_["type"] != "mesh" for s_ in sd.shapes])[np.maximum(gold["ref_shape"], 0)]
+        if kind == "sphere":
+            f = gold["F"][np.maximum(gold["ref_prim"], 0)]
+            e1, e2 = gold["V"][f[:, 1]] - gold["V"][f[:, 0]], gold["V"][f[:, 2]] - gold["V"][f[:, 0]]
+        else:
+            e1 = e2 = np.full((len(rays), 3), 2.0 / np.sqrt(3.0), np.float32)     # uv spans a wall of side 2 (|e| = 2)
+        mm = m & (is_rect if kind == "cornell" else ~is_rect)
+        bs = helpers.compare_barycentrics(rays[mm], surf["uv"][mm, 0], surf["uv"][mm, 1], gold["ref_u"][mm], gold["ref_v"][mm],
+                                          e1[mm], e2[mm], gold["ref_t"][mm], cos=cos[mm])
+        if kind == "sphere":      # the 16-byte hit record carries the same barycentrics
+            helpers.compare_barycentrics(rays[mm], hits["u"][mm], hits["v"][mm], gold["ref_u"][mm], gold["ref_v"][mm], e1[mm], e2[mm],
+                                         gold["ref_t"][mm], cos=cos[mm])
+        print("golden parity (%s, builder %d):" % (kind, builder), st, bs)
+        a = sc.ray_intersect_any(rays)
+        assert (a == gold["ref_any"])[~graze].mean() >= helpers.PRIM_AGREE
     finally:
         sc.close()
 
