@@ -30,7 +30,7 @@ import __graft_entry__ as graft  # noqa: E402
 SUBDIV = 8                      # 20 * 4^8 = 1 310 720 triangles
 N_RAYS = 1 << 24                # 16 777 216
 BYTES_PER_RAY_CLOSEST = 48      # 32 B ray in + 16 B hit out
-BYTES_PER_RAY_ANY = 33          # 32 B in + 1 B out
+BYTES_PER_RAY_ANY = 36          # 32 B in + 4 B out (the device writes 1 B)
 CPU_SAMPLE_RAYS = 1 << 21       # bounded sample for the CPU legs
 
 
@@ -126,7 +126,29 @@ def reference_arm(args, rank, world):
     emit(line)
 
 
-def cpu_baseline(S, sd, cores):
+def hit_parity(rays, ref, hits):
+    """Hit records of the reference's kd-tree (oracle/raydump.cpp: t,u,v at columns 0-2, global primitive at 4) against
+    the device's on the same rays: share of rays with the same primitive or a tie at equal t (north_star: >= 99.99 %),
+    and the relative t / barycentric differences on the rays that agree."""
+    r = np.asarray(rays).view(np.float32).reshape(-1, 8)
+    ref_t, t = ref[:, 0], hits["t"]
+    ref_hit, hit = np.isfinite(ref_t), np.isfinite(t)
+    ref_prim = np.where(ref_hit, ref[:, 4].copy().view(np.int32), -1).astype(np.int64)
+    prim = np.where(hit, hits["prim"].view(np.int32), -1).astype(np.int64)
+    scale = np.maximum(np.maximum(np.abs(np.where(ref_hit, ref_t, 0)), np.abs(r[:, 0:3]).max(axis=1)), 1.0)
+    with np.errstate(invalid="ignore"):
+        tie = ref_hit & hit & (np.abs(t - ref_t) <= 1e-5 * scale)
+    same = prim == ref_prim
+    m = same & ref_hit
+    dt = np.abs(t[m] - ref_t[m]) / scale[m]
+    return {"n": int(len(r)), "agree": float((same | tie).mean()), "same_primitive": float(same.mean()),
+            "hit_miss_agree": float((hit == ref_hit).mean()), "max_dt": float(dt.max()), "p9999_dt": float(np.quantile(dt, 0.9999)),
+            "share_dt_over_1e-5": float((dt > 1e-5).mean()),
+            "max_du": float(np.abs(hits["u"][m] - ref[m, 1]).max()), "max_dv": float(np.abs(hits["v"][m] - ref[m, 2]).max()),
+            "vs": "oracle/_ref ShapeKDTree::rayIntersect on the first %d chord rays of the timed batch; dt relative to max(t, |o|, 1), unweighted" % len(r)}
+
+
+def cpu_baseline(S, sd, cores, sc=None):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as O
     import tempfile
@@ -141,8 +163,9 @@ def cpu_baseline(S, sd, cores):
                 "sample": "2048 rays, brute-force C restatement (no kd-tree)"}
     with tempfile.TemporaryDirectory() as td:
         xml = sd.to_xml(td, "bench")
-        _, tm = O.ref_trace(xml, rays, threads=cores, repeats=2)
-    return {"value": tm["closest_mrays"], "unit": "Mrays/s", "cores": cores, "kind": "reference",
+        ref, tm = O.ref_trace(xml, rays, threads=cores, repeats=2)
+    parity = hit_parity(rays, ref, sc.ray_intersect(rays)) if sc is not None else None
+    return {"value": tm["closest_mrays"], "parity": parity, "unit": "Mrays/s", "cores": cores, "kind": "reference",
             "sample": "%d of the %d chord rays, best of 2, kd-tree build %s ms excluded; any-hit %.2f Mrays/s" % (
                 rays.shape[0], N_RAYS, tm.get("build_ms"), tm.get("any_mrays", 0.0)),
             "kd_build_ms": tm.get("build_ms")}
@@ -178,6 +201,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-path", action="store_true", help="skip the path-tracer detail runs (short runs under ncu)")
+    ap.add_argument("--no-plugin", action="store_true", help="skip the renders through the reference CLI + overlay plugin (detail.path.plugin)")
     ap.add_argument("--no-config4", action="store_true", help="skip the 3840x2160 multi-GPU render (config 4)")
     ap.add_argument("--spp4", type=int, default=1024, help="samples per pixel of config 4 (BASELINE: 1024)")
     ap.add_argument("--builder", default="lbvh", choices=["lbvh", "ploc"],
@@ -316,8 +340,10 @@ def main():
         sh = S.shadow_rays(np.tile(pts, (int(np.ceil(coh.shape[0] / max(len(pts), 1))), 1))[: coh.shape[0]], light_center=(0, 3.0, 0.5))
         sh_d = torch.from_numpy(sh.view(np.float32).reshape(-1, 8)).cuda()
         out_any = torch.empty(sh.shape[0], dtype=torch.uint8, device="cuda")
+        # the like-for-like figure for ShapeKDTree::rayIntersect(ray, its): the full intersection record (92 B) per ray
+        surf_d = torch.empty((n, 23), dtype=torch.float32, device="cuda")
         for name, mode, buf, out in (("coherent_closest", "closest", coh_d, hits_d), ("shadow_any", "any", sh_d, out_any),
-                                     ("random_any", "any", rays_d, out_any)):
+                                     ("random_any", "any", rays_d, out_any), ("random_surface_record", "surface", rays_d, surf_d)):
             m = min(buf.shape[0], out.shape[0])
             for _ in range(2):
                 sc.trace_device(mode, buf.data_ptr(), m, out.data_ptr())
@@ -332,7 +358,7 @@ def main():
             detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
         if not args.no_path:
             import bench_render
-            detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5), cpu=not args.no_cpu_baseline and world == 1)
+            detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5) + (() if args.no_plugin or world > 1 else ("plugin",)), cpu=not args.no_cpu_baseline and world == 1)
 
     # --- config 4: 3840x2160, 1024 spp split by sample index over the ranks (strong scaling), one NCCL film reduce ---
     if not args.no_path and not args.no_config4:
@@ -369,6 +395,10 @@ def main():
         if os.path.exists(tp) and n == N_RAYS:
             try:
                 tj = json.load(open(tp))
+                sys.path.insert(0, os.path.join(ROOT, "scripts"))
+                import summarise_ncu
+                if tj.get("kernel_source_sha1") != summarise_ncu.kernel_source_sha1():
+                    raise ValueError("profiles/traffic.json was captured from other kernel sources")
                 traffic = tj.get("trace_closest_bytes_per_launch")
                 # the bound that actually binds this kernel: warp instructions issued (ncu smsp__inst_executed.sum of the
                 # same launch on the same rays) against SMs x 4 schedulers x max SM clock
@@ -382,7 +412,7 @@ def main():
                 traffic, issue = None, None
         cpu = None
         if not args.no_cpu_baseline and world == 1:
-            cpu = cpu_baseline(S, sd, os.cpu_count() or 1)
+            cpu = cpu_baseline(S, sd, os.cpu_count() or 1, sc)
         line = {
             "metric": "closest-hit Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -399,6 +429,7 @@ def main():
                          "algorithmic_bytes": algo_bytes, "nodes_per_ray": nodes_per_ray, "prim_tests_per_ray": prims_per_ray,
                          "traversal_bytes_per_ray": nodes_per_ray * 80 + prims_per_ray * 48 + 48, "issue": issue},
             "cpu_baseline": cpu,
+            "parity": cpu.pop("parity", None) if cpu else None,
             "detail": dict(detail, hit_rate=hit_rate, build=bstats),
         }
         emit(line)

@@ -174,6 +174,75 @@ def cpu_reference(pkg, sd_small, threads):
             "sample": "config 1 at %d spp (of 64), mitsuba -C, 'Render time' %.3f s" % (sd_small.sampler["spp"], t)}
 
 
+def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
+    """The drop-in measured as a user meets it: the UNMODIFIED reference CLI (oracle/_ref/mitsuba) renders config 1 (and
+    config 3) with `-a <overlay>` mapping `path` to gpupath.so, under both schedulers — classic (`-C`, Integrator::render)
+    and responsive (default, ResponsiveIntegrator) — beside the same scene file through the stock `path.so` on the host
+    cores.  samples/s come from the plugin's own log lines (render loop only: "gpupath: ... M samples/s" and
+    "gpupath: responsive round"), `render_time_s` is the reference's RenderJob "Render time" where it prints one."""
+    import re
+    import subprocess
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    overlay = os.path.join(ROOT, "mitsuba-im_b200", "plugin", "overlay")
+    if not O.have_reference() or not os.path.exists(os.path.join(overlay, "plugins", "path.so")):
+        return {"unavailable": "oracle/_ref or the plugin overlay is not built"}
+    threads = threads or (os.cpu_count() or 1)
+
+    def cli(xml, out, classic, use_overlay, defines=None, ngpu=1):
+        cmd = [os.path.join(O.REF_DIR, "mitsuba"), "-p", str(threads)]
+        if classic:
+            cmd.append("-C")
+        if use_overlay:
+            cmd += ["-a", overlay]
+        for k, v in (defines or {}).items():
+            cmd += ["-D", "%s=%s" % (k, v)]
+        cmd += ["-o", out, xml]
+        t0 = time.perf_counter()
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1800)
+        wall = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"error": r.stdout[-600:]}
+        res = {"process_wall_s": wall}
+        m = re.search(r"Render time: ([0-9.]+)(ms|s|m)", r.stdout)
+        if m:
+            res["render_time_s"] = float(m.group(1)) * {"ms": 1e-3, "s": 1.0, "m": 60.0}[m.group(2)]
+        m = re.search(r"gpupath: .* ([0-9.]+) M samples/s", r.stdout) if classic else None
+        if m:
+            res["samples_per_s"] = float(m.group(1)) * 1e6
+        rounds = re.findall(r"responsive round: ([0-9.]+) samples in ([0-9.]+) s", r.stdout)
+        if rounds:
+            n, sec = float(rounds[-1][0]), float(rounds[-1][1])
+            res.update(samples_per_s=n / max(sec, 1e-9), round_s=sec, samples=n)
+        return res
+
+    out = {"threads": threads}
+    with tempfile.TemporaryDirectory() as td:
+        x1 = os.path.join(ROOT, "tests", "golden", "cbox_config1.xml")
+        d1 = dict(sampler="independent", spp=64, res=512, rfilter="box")
+        n1 = 512 * 512 * 64
+        stock = cli(x1, os.path.join(td, "s.pfm"), True, False, d1)
+        if "render_time_s" in stock:
+            stock["samples_per_s"] = n1 / stock["render_time_s"]
+        out["config1_stock_path_classic_cpu"] = stock
+        out["config1_gpu_classic"] = cli(x1, os.path.join(td, "c.pfm"), True, True, d1)
+        out["config1_gpu_responsive"] = cli(x1, os.path.join(td, "r.pfm"), False, True, d1)
+        if sd3 is not None:
+            t0 = time.perf_counter()
+            x3 = sd3.to_xml(td, "c3")
+            out["config3_scene_files_s"] = time.perf_counter() - t0
+            out["config3_gpu_classic"] = cli(x3, os.path.join(td, "c3c.pfm"), True, True)
+            out["config3_gpu_responsive"] = cli(x3, os.path.join(td, "c3r.pfm"), False, True)
+            for g in gpus:
+                if g > 1:
+                    xg = os.path.join(td, "c3_%dgpu.xml" % g)
+                    open(xg, "w").write(open(x3).read().replace('<integrator type="path">', '<integrator type="path"><integer name="gpus" value="%d"/>' % g))
+                    out["config3_gpu_classic_%dgpus" % g] = cli(xg, os.path.join(td, "c3c%d.pfm" % g), True, True)
+                    out["config3_gpu_responsive_%dgpus" % g] = cli(xg, os.path.join(td, "c3r%d.pfm" % g), False, True)
+    return out
+
+
 def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024, spp3=256, builder=None):
     S = pkg.scenes
     out = {}
@@ -182,7 +251,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         if cpu:
             out["config1_cpu_reference"] = cpu_reference(pkg, S.cornell_box(512, 512, spp=16, max_depth=5), os.cpu_count() or 1)
     sd = None
-    if {3, 4, 5} & set(configs):
+    if {3, 4, 5, "plugin"} & set(configs):
         t0 = time.perf_counter()
         sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian")
         gen_s = time.perf_counter() - t0
@@ -190,6 +259,9 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         r = render_config(pkg, ctx, stream, sd, spp3, warmup=1, builder=builder)
         r["scene_generation_s"] = gen_s
         out["config3_spherefield_10Mtri_1920x1080_%dspp" % spp3] = r
+    if "plugin" in configs and rank == 0:
+        import torch
+        out["plugin"] = plugin_bench(pkg, sd, gpus=(1, 2) if torch.cuda.device_count() >= 2 else (1,))
     if 5 in configs and rank == 0:
         sd.sensor["width"], sd.sensor["height"] = 1280, 720
         out["config5_interactive_1280x720_1spp"] = render_config5(pkg, ctx, stream, sd)
@@ -201,7 +273,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, nargs="*", default=[1, 3, 5])
+    ap.add_argument("--config", nargs="*", default=["1", "3", "5"], help="1 3 4 5 and/or plugin")
     ap.add_argument("--spp4", type=int, default=1024)
     ap.add_argument("--builder", default=None, choices=["lbvh", "ploc"])
     ap.add_argument("--spp3", type=int, default=256, help="samples per pixel of config 3 (BASELINE: 256; smaller only for ncu runs)")
@@ -212,5 +284,5 @@ if __name__ == "__main__":
     ctx = pkg.binding.Context(0)
     torch.cuda.set_device(0)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", 0))
-    print(json.dumps(run(pkg, ctx, stream, tuple(args.config), cpu=not args.no_cpu, spp4=args.spp4, spp3=args.spp3,
+    print(json.dumps(run(pkg, ctx, stream, tuple(int(c) if c.isdigit() else c for c in args.config), cpu=not args.no_cpu, spp4=args.spp4, spp3=args.spp3,
                          builder=None if args.builder is None else dict(lbvh=0, ploc=1)[args.builder])))

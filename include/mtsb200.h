@@ -237,6 +237,14 @@ MTSB_API int  mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, c
 MTSB_API void mtsb_render_destroy(mtsb_render *r);
 MTSB_API int  mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera);
 MTSB_API int  mtsb_render_clear(mtsb_render *r);
+/* Gives the render a CUDA stream of its own (default: the context stream).  Renders are independent — own path state,
+ * own film — so passes of several renders on one GPU then overlap; this is what lets the `threadCount` host threads of
+ * ResponsiveIntegrator::render (include/mitsuba/render/integrator2.h:49-100), one render each, fill the device together. */
+MTSB_API int  mtsb_render_private_stream(mtsb_render *r);
+/* Optional, before the first pass: allocates the path state for passes of `spp_per_pass` samples per pixel over the whole
+ * crop window and runs one 8x4-pixel pass (kernel loading, graph instantiation), then clears the film — the GPU
+ * counterpart of the work the reference does in preprocess(), outside its render timer.  Blocks until done. */
+MTSB_API int  mtsb_render_reserve(mtsb_render *r, uint32_t spp_per_pass);
 /* Live-path count below which one persistent kernel carries the surviving paths through all their remaining bounces
  * instead of one wavefront round per bounce (csrc/render_tail.cuh).  0 = wavefront stages only, < 0 = the context's
  * default (131072).  Results do not depend on it (same estimator, same random numbers); it exists so that tests can

@@ -130,8 +130,8 @@ static int film_collective(mtsb_render *r, mtsb_comm *c, int root, const char *w
 	if (root >= c->nranks) MTSB_FAIL(MTSB_EINVAL, "%s: root %d of %d ranks", who, root, c->nranks);
 	MTSB_CUDA(cudaSetDevice(c->ctx->device));
 	float *film = r->dFilm.ptr;
-	if (root < 0) MTSB_NCCL(g_nccl.AllReduce(film, film, r->dFilm.count, ncclFloat, ncclSum, c->comm, c->ctx->stream));
-	else MTSB_NCCL(g_nccl.Reduce(film, film, r->dFilm.count, ncclFloat, ncclSum, root, c->comm, c->ctx->stream));
+	if (root < 0) MTSB_NCCL(g_nccl.AllReduce(film, film, r->dFilm.count, ncclFloat, ncclSum, c->comm, r->stream));
+	else MTSB_NCCL(g_nccl.Reduce(film, film, r->dFilm.count, ncclFloat, ncclSum, root, c->comm, r->stream));
 	return 0;
 }
 

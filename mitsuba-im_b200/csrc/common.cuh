@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include <mutex>
+#include <utility>
 #include <vector>
 #include "../../include/mtsb200.h"
 
@@ -158,7 +160,11 @@ struct mtsb_ctx {
 	int collapseDp = 1;                    // MTSB_COLLAPSE_DP: cost-driven BVH8 collapse (0 = greedy)
 	float dpCNode = 1.0f, dpCPrim = 0.7f;  // MTSB_DP_CNODE / MTSB_DP_CPRIM
 	int tailPaths = 0;                     // MTSB_TAIL_PATHS: live-path count below which the late-bounce kernel takes over (render)
+	int useGraph = 1;                      // MTSB_GRAPH: bounce loop as a CUDA graph with a device-driven WHILE node (0 = plain launches)
 	// L2 residency of the acceleration structure (cudaAccessPolicyWindow, see l2_window in scene.cuh)
-	size_t l2Persist = 0;                  // bytes of persisting L2 set aside for this device (0 = off, MTSB_L2_PERSIST=0)
+	size_t l2PersistMax = 0;               // ceiling of the persisting set-aside (device maximum, or MTSB_L2_PERSIST in MB; 0 = off)
+	size_t l2Persist = 0;                  // current cudaLimitPersistingL2CacheSize = the largest claim of a live scene
 	size_t l2WindowMax = 0;                // cudaDevAttrMaxAccessPolicyWindowSize
+	std::mutex l2Mutex;
+	std::vector<std::pair<const void *, size_t> > l2Claims;   // (scene, bytes) of committed scenes whose structure fits
 };

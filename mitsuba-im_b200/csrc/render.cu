@@ -145,20 +145,25 @@ struct ConnectIO {
 	}
 };
 
+// Both kernels find the live queue through counters[CTR_PARITY] (flipped by advance_kernel between bounces), so the same
+// launch — the same graph node — serves every bounce.
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
-extend_kernel(SceneDev S, PathState ps, const uint32_t *queue, const uint32_t *count) {
+extend_kernel(SceneDev S, PathState ps) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
-	ExtendIO io; io.S = S; io.ps = ps; io.queue = queue;
-	const unsigned long long n = *count;
+	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
+	const unsigned long long n = ps.counters[parity];
+	if (n == 0) return;
+	ExtendIO io; io.S = S; io.ps = ps; io.queue = parity ? ps.queueB : ps.queueA;
 	trace_persistent<false, false>(S, io, n, ps.work + 0, shStack + threadIdx.x);
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
 }
 
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
-connect_kernel(SceneDev S, PathState ps, const uint32_t *count) {
+connect_kernel(SceneDev S, PathState ps) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
+	const unsigned long long n = ps.counters[CTR_SHADOW];
+	if (n == 0) return;
 	ConnectIO io; io.S = S; io.ps = ps;
-	const unsigned long long n = *count;
 	trace_persistent<true, false>(S, io, n, ps.work + 1, shStack + threadIdx.x);
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 2, n);
 }

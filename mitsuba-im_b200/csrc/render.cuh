@@ -18,11 +18,15 @@ struct PathState {
 	uint4  *rng;
 	float4 *shO, *shD, *shL;
 	uint32_t *queueA, *queueB;     // live path slots (ping-pong)
-	uint32_t *counters;            // [0] queue A count, [1] queue B count, [2] shadow count, [4..7] hand-over to the tail kernel (render_tail.cuh)
+	uint32_t *counters;            // 16 words, see the CTR_* enum below
 	unsigned long long *work;      // work counters of the persistent kernels [0] extend, [1] connect, [2] tail
-	volatile uint32_t *feedback;   // pinned host word (mapped): bounce at which the last chunk went to the tail kernel
-	unsigned long long *stats;     // [0] camera paths, [1] closest rays, [2] shadow rays, [3] depth sum
+	unsigned long long *stats;     // [0] camera paths, [1] closest rays, [2] shadow rays, [3] depth sum, [5] kernels run inside the bounce graph
 };
+
+// counters[]: the bounce loop is driven from the device (render_tail.cuh: begin_kernel / advance_kernel), so which queue
+// is the live one and how deep the wavefront is live here, not in kernel arguments
+enum { CTR_COUNT_A = 0, CTR_COUNT_B = 1, CTR_SHADOW = 2, CTR_PARITY = 3,
+       CTR_TAIL = 4, CTR_TAIL_COUNT = 5, CTR_TAIL_PARITY = 6, CTR_TAIL_BOUNCE = 7, CTR_BOUNCE = 8, CTR_WORDS = 16 };
 
 enum { PF_FROM_BSDF = 1, PF_SCATTERED = 2, PF_DELTA = 4 };
 
@@ -50,6 +54,8 @@ struct mtsb_render {
 	mtsb::FilmDev film;
 	mtsb::IntegratorDev integ;
 	uint32_t seed = 0;
+	cudaStream_t stream = nullptr; // the context stream, or a stream of its own (mtsb_render_private_stream)
+	bool ownStream = false;
 	size_t capacity = 0;           // paths in flight
 	mtsb::PathState ps;
 	mtsb::DevBuf<float> dFilm;
@@ -58,8 +64,12 @@ struct mtsb_render {
 	mtsb::DevBuf<uint32_t> bufQueue, bufCounters;
 	mtsb::DevBuf<unsigned long long> bufWork;
 	unsigned long long launches = 0;
-	uint32_t *hostFeedback = nullptr;   // pinned + mapped, see PathState::feedback
 	int tailPaths = 0;                  // live-path count below which the tail kernel takes over (0 = never; mtsb_render_set_tail)
-	int waveBounces = 0;                // wavefront bounces enqueued per chunk before the tail kernel (adapted from hostFeedback)
+	// the bounce loop as a CUDA graph with a device-driven WHILE node (render_host.cuh: bounce_graph); rebuilt when the
+	// path-state arrays move or the tail threshold changes
+	cudaGraph_t bounceGraph = nullptr;
+	cudaGraphExec_t bounceExec = nullptr;
+	const void *graphKey = nullptr; int graphTail = -1;
+	bool graphFailed = false;
 	float *hostStage = nullptr;    // page-locked staging for mtsb_film_to_host(accumulate = 1), allocated on first use
 };

@@ -34,63 +34,122 @@ static int launch_trav(mtsb_scene *scene, void (*kernel)(KArgs...), unsigned gri
 	return 0;
 }
 
-// Runs generate -> bounces -> splat for one chunk of `count` path slots.  Nothing here waits for the device: every
-// kernel reads its counts from device memory, the wavefront stages run for a number of bounces chosen from the
-// previous chunks' feedback word, and the tail kernel (render_tail.cuh) finishes whatever is alive after them — so the
-// call returns as soon as the launches are queued (mtsb_render_pass is asynchronous, as include/mtsb200.h says).
+struct LoopShape { unsigned traceGrid, shadeGrid, tailGrid; };
+
+static void destroy_bounce_graph(mtsb_render *r) {
+	if (r->bounceExec) cudaGraphExecDestroy(r->bounceExec);
+	if (r->bounceGraph) cudaGraphDestroy(r->bounceGraph);
+	r->bounceExec = nullptr; r->bounceGraph = nullptr; r->graphKey = nullptr; r->graphTail = -1;
+}
+
+// Adds one kernel node (optionally with the L2 access-policy window of the traversal kernels) behind `dep`.
+static cudaError_t add_kernel(cudaGraph_t g, cudaGraphNode_t *node, cudaGraphNode_t dep, void *func, unsigned grid, unsigned block,
+		void **args, mtsb_scene *windowOf) {
+	cudaKernelNodeParams kp; memset(&kp, 0, sizeof(kp));
+	kp.func = func; kp.gridDim = dim3(grid); kp.blockDim = dim3(block); kp.sharedMemBytes = 0; kp.kernelParams = args; kp.extra = nullptr;
+	cudaError_t e = cudaGraphAddKernelNode(node, g, dep ? &dep : nullptr, dep ? 1 : 0, &kp);
+	if (e != cudaSuccess || !windowOf) return e;
+	cudaLaunchAttribute attr[1];
+	if (l2_window(windowOf, attr) == 1) e = cudaGraphKernelNodeSetAttribute(*node, cudaLaunchAttributeAccessPolicyWindow, &attr[0].val);
+	return e;
+}
+
+// The bounce loop of one chunk as ONE graph:   begin -> WHILE { extend -> shade -> connect -> advance } -> tail
+// The WHILE condition is written by begin_kernel / advance_kernel on the device (render_tail.cuh).  All kernel arguments
+// are constants of the render (path-state pointers, integrator, seed): per-chunk quantities travel through ps.counters.
+static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tailBelow, uint32_t maxBounces) {
+	destroy_bounce_graph(r);
+	mtsb_scene *scene = r->scene;
+	SceneDev S = scene->dev; S.counters = nullptr;
+	PathState ps = r->ps;
+	IntegratorDev integ = r->integ;
+	uint32_t seed = r->seed;
+	cudaGraph_t g = nullptr;
+	MTSB_CUDA(cudaGraphCreate(&g, 0));
+	r->bounceGraph = g;
+	LoopCtl ctl; ctl.tailBelow = tailBelow; ctl.maxBounces = maxBounces; ctl.inGraph = 1;
+	MTSB_CUDA(cudaGraphConditionalHandleCreate(&ctl.cond, g, 0, cudaGraphCondAssignDefault));
+	cudaGraphNode_t nBegin, nWhile, nTail, n1, n2, n3, n4;
+	void *aCtl[] = { &ps, &ctl };
+	MTSB_CUDA(add_kernel(g, &nBegin, nullptr, (void *) begin_kernel, 1, 1, aCtl, nullptr));
+	cudaGraphNodeParams wp = { cudaGraphNodeTypeConditional };
+	wp.conditional.handle = ctl.cond; wp.conditional.type = cudaGraphCondTypeWhile; wp.conditional.size = 1;
+	MTSB_CUDA(cudaGraphAddNode(&nWhile, g, &nBegin, 1, &wp));
+	cudaGraph_t body = wp.conditional.phGraph_out[0];
+	void *aTrace[] = { &S, &ps };
+	void *aShade[] = { &S, &ps, &integ, &seed };
+	MTSB_CUDA(add_kernel(body, &n1, nullptr, (void *) extend_kernel, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	MTSB_CUDA(add_kernel(body, &n2, n1, (void *) shade_kernel, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+	MTSB_CUDA(add_kernel(body, &n3, n2, (void *) connect_kernel, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	MTSB_CUDA(add_kernel(body, &n4, n3, (void *) advance_kernel, 1, 1, aCtl, nullptr));
+	if (tailBelow) MTSB_CUDA(add_kernel(g, &nTail, nWhile, (void *) tail_kernel, sh.tailGrid, MTSB_TRACE_BLOCK, aShade, scene));
+	MTSB_CUDA(cudaGraphInstantiate(&r->bounceExec, g, 0));
+	r->graphKey = r->bufF4.ptr; r->graphTail = (int) tailBelow;
+	return 0;
+}
+
+// Runs generate -> bounces -> splat for one chunk of `count` path slots.  Nothing here waits for the device: the bounce
+// loop is a graph whose WHILE node is steered from the device, and the tail kernel (render_tail.cuh) finishes whatever is
+// alive when the wavefront stops paying — so the call returns as soon as four launches are queued (mtsb_render_pass is
+// asynchronous, as include/mtsb200.h says).
 static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, float *posOut = nullptr) {
 	mtsb_scene *scene = r->scene;
 	mtsb_ctx *ctx = scene->ctx;
-	cudaStream_t st = ctx->stream;
+	cudaStream_t st = r->stream;
 	PathState &ps = r->ps;
-	uint32_t *cnt = ps.counters;       // [0] queue A count, [1] queue B count, [2] shadow count, [4..7] tail hand-over
-	const unsigned traceGrid = (unsigned) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM;
-	const unsigned shadeGrid = std::min(blocks_for(g.count, RENDER_BLOCK), (unsigned) ctx->smCount * MTSB_SHADE_MIN_BLOCKS * 2u);
+	uint32_t *cnt = ps.counters;
+	LoopShape sh;
+	sh.traceGrid = (unsigned) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM;
+	// sized to the machine and to the chunk the render was made for (r->capacity), not to this chunk: graph nodes are fixed
+	sh.shadeGrid = std::min(blocks_for(r->capacity, RENDER_BLOCK), (unsigned) ctx->smCount * MTSB_SHADE_MIN_BLOCKS * 2u);
+	sh.tailGrid = (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS;
 	SceneDev S = scene->dev; S.counters = nullptr;
+	l2_phase(scene, false);
 
-	MTSB_CUDA(cudaMemsetAsync(cnt, 0, 8 * sizeof(uint32_t), st));
+	MTSB_CUDA(cudaMemsetAsync(cnt, 0, CTR_WORDS * sizeof(uint32_t), st));
 	generate_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(g, r->cam, ps, ps.queueA);
 	r->launches += 1;
-	uint32_t *qIn = ps.queueA, *qOut = ps.queueB, *cIn = cnt + 0, *cOut = cnt + 1;
 	const int maxDepth = r->integ.maxDepth;
-	const int bounded = maxDepth > 0 ? maxDepth : 1 << 30;
 	const uint32_t tailBelow = (uint32_t) std::max(0, r->tailPaths);
-	// wavefront bounces to enqueue: all of them without the tail kernel, else what the feedback of earlier chunks suggests
-	if (tailBelow && r->hostFeedback) {
-		const uint32_t fb = r->hostFeedback[0], live = r->hostFeedback[1];
-		if (fb != 0xffffffffu) {
-			const bool forced = (fb & 0x80000000u) != 0;
-			const int at = (int) (fb & 0x7fffffffu);
-			if (!forced) r->waveBounces = at;
-			else if (live > 8u * tailBelow) r->waveBounces = at + 2;
-			else if (live > 2u * tailBelow) r->waveBounces = at + 1;
-			r->hostFeedback[0] = 0xffffffffu;
+	const uint32_t bounded = maxDepth > 0 ? (uint32_t) maxDepth : 0x7fffffffu;
+
+	if (ctx->useGraph && !r->graphFailed) {
+		if (!r->bounceExec || r->graphKey != (const void *) r->bufF4.ptr || r->graphTail != (int) tailBelow) {
+			if (build_bounce_graph(r, sh, tailBelow, bounded) < 0) {
+				// a driver without conditional graph nodes: the same kernels as plain launches (still no host round trip)
+				cudaGetLastError();
+				destroy_bounce_graph(r);
+				r->graphFailed = true;
+			}
 		}
 	}
-	const int waves = tailBelow ? std::min(bounded, std::max(0, r->waveBounces)) : bounded;
-	uint32_t parity = 0;
-	int bounce = 0;
-	for (; bounce < waves; ++bounce) {
-		prep_kernel<<<1, 1, 0, st>>>(ps, cIn, cOut, cnt + 2, parity, (uint32_t) bounce, tailBelow, 0u);
-		MTSB_CHECK(launch_trav(scene, extend_kernel, traceGrid, st, S, ps, (const uint32_t *) qIn, (const uint32_t *) cIn));
-		shade_kernel<<<shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, qIn, qOut, cIn, cOut, cnt + 2);
-		MTSB_CHECK(launch_trav(scene, connect_kernel, traceGrid, st, S, ps, (const uint32_t *) (cnt + 2)));
-		r->launches += 4;
-		std::swap(qIn, qOut); std::swap(cIn, cOut); parity ^= 1u;
-		// debugging configuration only (tail kernel switched off AND unbounded depth): the host has to look at the count
-		if (!tailBelow && maxDepth < 0 && (bounce & 7) == 7) {
-			uint32_t live = 0;
-			MTSB_CUDA(cudaMemcpyAsync(&live, cIn, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-			MTSB_CUDA(cudaStreamSynchronize(st));
-			if (live == 0) break;
-			if (bounce > 100000) MTSB_FAIL(MTSB_EINVAL, "render: path depth exceeded 100000 bounces");
+	if (r->bounceExec) {
+		MTSB_CUDA(cudaGraphLaunch(r->bounceExec, st));
+		r->launches += tailBelow ? 2 : 1;               // begin + tail; the kernels inside the WHILE node are counted on the device
+	} else {
+		// plain launches: every bounded bounce is enqueued (an unbounded integrator gets 16, the tail kernel takes the rest)
+		const bool poll = !tailBelow && maxDepth < 0;   // debugging configuration only: no tail kernel AND unbounded depth
+		LoopCtl ctl; ctl.tailBelow = tailBelow; ctl.inGraph = 0; ctl.cond = 0;
+		ctl.maxBounces = (maxDepth > 0 || poll) ? bounded : 16u;
+		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
+		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
+			MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+			shade_kernel<<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+			MTSB_CHECK(launch_trav(scene, connect_kernel, sh.traceGrid, st, S, ps));
+			advance_kernel<<<1, 1, 0, st>>>(ps, ctl);
+			if (poll && (bounce & 7) == 7) {
+				uint32_t live[2] = { 0, 0 };
+				MTSB_CUDA(cudaMemcpyAsync(live, cnt, sizeof(live), cudaMemcpyDeviceToHost, st));
+				MTSB_CUDA(cudaStreamSynchronize(st));
+				if (live[0] + live[1] == 0) break;
+				if (bounce > 100000) MTSB_FAIL(MTSB_EINVAL, "render: path depth exceeded 100000 bounces");
+			}
 		}
-	}
-	if (tailBelow && bounce < bounded) {
-		// hand whatever is alive to the tail kernel (a no-op if the hand-over already happened or nothing is left)
-		prep_kernel<<<1, 1, 0, st>>>(ps, cIn, nullptr, cnt + 2, parity, (uint32_t) bounce, tailBelow, 1u);
-		MTSB_CHECK(launch_trav(scene, tail_kernel, (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS, st, S, ps, r->integ, r->seed));
-		r->launches += 2;
+		r->launches += 1;
+		if (tailBelow) {
+			MTSB_CHECK(launch_trav(scene, tail_kernel, sh.tailGrid, st, S, ps, r->integ, r->seed));
+			r->launches += 1;
+		}
 	}
 	splat_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(ps, r->film, g.count, samplesOut, posOut);
 	r->launches += 1;
@@ -138,20 +197,15 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 	r->seed = (uint32_t) seed;
 	const size_t filmFloats = (size_t) (f.width + 2 * f.border) * (f.height + 2 * f.border) * f.channels;
 	int rc = r->dFilm.alloc(filmFloats);
-	if (rc == 0) rc = r->bufCounters.alloc(16);
+	if (rc == 0) rc = r->bufCounters.alloc(CTR_WORDS);
 	if (rc == 0) rc = r->bufWork.alloc(16 + 2 * SPLAT_STAT_STRIPES);
 	if (rc < 0) { delete r; return rc; }
 	f.data = r->dFilm.ptr;
 	r->ps.counters = r->bufCounters.ptr;
 	r->ps.work = r->bufWork.ptr; r->ps.stats = r->bufWork.ptr + 4;
-	r->tailPaths = scene->ctx->tailPaths; r->waveBounces = 3;
-	r->ps.feedback = nullptr;
-	if (cudaHostAlloc((void **) &r->hostFeedback, 2 * sizeof(uint32_t), cudaHostAllocMapped) == cudaSuccess) {
-		r->hostFeedback[0] = 0xffffffffu; r->hostFeedback[1] = 0;
-		uint32_t *dp = nullptr;
-		if (cudaHostGetDevicePointer((void **) &dp, r->hostFeedback, 0) == cudaSuccess) r->ps.feedback = dp;
-	} else { cudaGetLastError(); r->hostFeedback = nullptr; }     // stats[12 ..): striped path / depth counters of splat_kernel
-	cudaStream_t st = scene->ctx->stream;
+	r->tailPaths = scene->ctx->tailPaths;
+	r->stream = scene->ctx->stream;
+	cudaStream_t st = r->stream;
 	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, filmFloats * sizeof(float), st));
 	MTSB_CUDA(cudaMemsetAsync(r->bufWork.ptr, 0, (16 + 2 * SPLAT_STAT_STRIPES) * sizeof(unsigned long long), st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
@@ -162,9 +216,10 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 void mtsb_render_destroy(mtsb_render *r) {
 	if (!r) return;
 	cudaSetDevice(r->scene->ctx->device);
-	cudaStreamSynchronize(r->scene->ctx->stream);     // passes are asynchronous: nothing of this render may still be queued
+	cudaStreamSynchronize(r->stream);                 // passes are asynchronous: nothing of this render may still be queued
+	if (r->ownStream) cudaStreamDestroy(r->stream);
 	if (r->hostStage) cudaFreeHost(r->hostStage);
-	if (r->hostFeedback) cudaFreeHost(r->hostFeedback);
+	destroy_bounce_graph(r);
 	delete r;
 }
 
@@ -177,15 +232,24 @@ int mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera) {
 int mtsb_render_set_tail(mtsb_render *r, int paths) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_tail: NULL argument");
 	r->tailPaths = paths < 0 ? r->scene->ctx->tailPaths : paths;
-	r->waveBounces = 3;
-	if (r->hostFeedback) r->hostFeedback[0] = 0xffffffffu;
+	return 0;
+}
+
+int mtsb_render_private_stream(mtsb_render *r) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_private_stream: NULL argument");
+	if (r->ownStream) return 0;
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	MTSB_CUDA(cudaStreamSynchronize(r->stream));
+	cudaStream_t s = nullptr;
+	MTSB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+	r->stream = s; r->ownStream = true;
 	return 0;
 }
 
 int mtsb_render_clear(mtsb_render *r) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_clear: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	cudaStream_t st = r->scene->ctx->stream;
+	cudaStream_t st = r->stream;
 	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, r->dFilm.bytes(), st));
 	MTSB_CUDA(cudaMemsetAsync(r->ps.stats, 0, (12 + 2 * SPLAT_STAT_STRIPES) * sizeof(unsigned long long), st));
 	r->launches = 0;
@@ -213,7 +277,7 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	// chunks hold whole sample planes when possible so that a warp covers an 8x4 pixel tile of one sample index
 	size_t chunk = std::min<unsigned long long>(total, MAX_PATHS_IN_FLIGHT);
 	if (chunk > g.pixPadded) chunk = (chunk / g.pixPadded) * g.pixPadded;
-	MTSB_CHECK(ensure_capacity(r, chunk));
+	if (chunk > r->capacity) MTSB_CHECK(ensure_capacity(r, chunk));
 	for (unsigned long long first = 0; first < total; first += chunk) {
 		g.first = first; g.count = (uint32_t) std::min<unsigned long long>(chunk, total - first);
 		MTSB_CHECK(run_chunk(r, g, nullptr));
@@ -221,10 +285,26 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	return 0;
 }
 
+int mtsb_render_reserve(mtsb_render *r, uint32_t spp_per_pass) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_reserve: NULL argument");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	const unsigned long long pixPadded = (unsigned long long) ((r->film.cropW + 7) / 8) * ((r->film.cropH + 3) / 4) * 32;
+	const unsigned long long total = pixPadded * std::max(1u, spp_per_pass);
+	size_t chunk = (size_t) std::min<unsigned long long>(total, MAX_PATHS_IN_FLIGHT);
+	if (chunk > pixPadded) chunk = (chunk / pixPadded) * pixPadded;
+	MTSB_CHECK(ensure_capacity(r, chunk));
+	// one 8x4-pixel pass: loads every kernel of the pipeline, instantiates the bounce graph for this capacity
+	const int32_t rect[4] = { 0, 0, std::min(8, r->film.cropW), std::min(4, r->film.cropH) };
+	MTSB_CHECK(mtsb_render_pass(r, 0, 1, 1, rect, 1, 0));
+	MTSB_CHECK(mtsb_render_clear(r));
+	MTSB_CUDA(cudaStreamSynchronize(r->stream));
+	return 0;
+}
+
 int mtsb_render_sync(mtsb_render *r) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_sync: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	MTSB_CUDA(cudaStreamSynchronize(r->scene->ctx->stream));
+	MTSB_CUDA(cudaStreamSynchronize(r->stream));
 	return 0;
 }
 
@@ -238,7 +318,7 @@ int mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumu
 	if (!r || !dst) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_to_host: NULL argument");
 	if (float_count != r->dFilm.count) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_to_host: %zu floats given, film has %zu", float_count, r->dFilm.count);
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	cudaStream_t st = r->scene->ctx->stream;
+	cudaStream_t st = r->stream;
 	if (!accumulate) {
 		MTSB_CUDA(cudaMemcpyAsync(dst, r->dFilm.ptr, float_count * sizeof(float), cudaMemcpyDeviceToHost, st));
 		MTSB_CUDA(cudaStreamSynchronize(st));
@@ -258,7 +338,7 @@ int mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, int accumu
 int mtsb_film_stage(mtsb_render *r, const float **stage_out, size_t *float_count_out) {
 	if (!r || !stage_out) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_stage: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	cudaStream_t st = r->scene->ctx->stream;
+	cudaStream_t st = r->stream;
 	const size_t n = r->dFilm.count;
 	if (!r->hostStage) MTSB_CUDA(cudaMallocHost((void **) &r->hostStage, n * sizeof(float)));
 	MTSB_CUDA(cudaMemcpyAsync(r->hostStage, r->dFilm.ptr, n * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -272,11 +352,11 @@ int mtsb_render_stats(mtsb_render *r, uint64_t out[8]) {
 	if (!r || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_stats: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
 	unsigned long long h[12 + 2 * SPLAT_STAT_STRIPES];
-	MTSB_CUDA(cudaMemcpyAsync(h, r->ps.stats, sizeof(h), cudaMemcpyDeviceToHost, r->scene->ctx->stream));
-	MTSB_CUDA(cudaStreamSynchronize(r->scene->ctx->stream));
+	MTSB_CUDA(cudaMemcpyAsync(h, r->ps.stats, sizeof(h), cudaMemcpyDeviceToHost, r->stream));
+	MTSB_CUDA(cudaStreamSynchronize(r->stream));
 	for (int i = 0; i < SPLAT_STAT_STRIPES; ++i) { h[0] += h[12 + 2 * i]; h[3] += h[12 + 2 * i + 1]; }
 	for (int i = 0; i < 8; ++i) out[i] = 0;
-	out[0] = h[0]; out[1] = h[1]; out[2] = h[2]; out[3] = h[3]; out[4] = r->launches;
+	out[0] = h[0]; out[1] = h[1]; out[2] = h[2]; out[3] = h[3]; out[4] = r->launches + h[5];
 	return 0;
 }
 
@@ -290,7 +370,7 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	if (n == 0) return 0;
 	if (n > MAX_PATHS_IN_FLIGHT) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_samples: at most %zu samples per call", MAX_PATHS_IN_FLIGHT);
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
-	cudaStream_t st = r->scene->ctx->stream;
+	cudaStream_t st = r->stream;
 	MTSB_CHECK(ensure_capacity(r, n));
 	DevBuf<uint32_t> dS; DevBuf<float> dO, dP;
 	MTSB_CHECK(dS.upload(samples, n * 4, st)); MTSB_CHECK(dO.alloc(n * 4));

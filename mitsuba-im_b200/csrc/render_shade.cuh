@@ -155,9 +155,12 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 #define MTSB_SHADE_MIN_BLOCKS 5
 #endif
 __global__ void __launch_bounds__(RENDER_BLOCK, MTSB_SHADE_MIN_BLOCKS)
-shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed, const uint32_t *queueIn, uint32_t *queueOut,
-		const uint32_t *countIn, uint32_t *countOut, uint32_t *countShadow) {
-	const uint32_t n = *countIn;
+shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
+	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
+	const uint32_t n = ps.counters[parity];
+	const uint32_t *queueIn = parity ? ps.queueB : ps.queueA;
+	uint32_t *queueOut = parity ? ps.queueA : ps.queueB;
+	uint32_t *countOut = ps.counters + (parity ^ 1u), *countShadow = ps.counters + CTR_SHADOW;
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
 		const uint32_t slot = queueIn[i];
 		ShadeOut so;

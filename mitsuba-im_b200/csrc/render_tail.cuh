@@ -13,29 +13,49 @@
 
 namespace mtsb {
 
-// counters[] slots shared with render_host.cuh
-enum { CTR_COUNT_A = 0, CTR_COUNT_B = 1, CTR_SHADOW = 2, CTR_TAIL = 4, CTR_TAIL_COUNT = 5, CTR_TAIL_PARITY = 6, CTR_TAIL_BOUNCE = 7 };
+// ---- the device-driven bounce loop -----------------------------------------------------------------------------------
+// One wavefront bounce is  extend -> shade -> connect -> advance.  Whether there is another one is decided ON THE DEVICE:
+// `advance` (one thread) looks at the live count the shade kernel left behind and either flips the queues for the next
+// bounce or hands the survivors to the tail kernel, and writes that decision into the condition of the CUDA-graph WHILE
+// node that holds the four kernels (render_host.cuh: bounce_graph).  The host launches ONE graph per chunk and never
+// reads a count back.  The same kernels also run as plain launches (MTSB_GRAPH=0): every bounded bounce is enqueued and
+// the ones after the hand-over find empty queues.
+struct LoopCtl {
+	uint32_t tailBelow;                  // live-path count below which the tail kernel takes over (0: never)
+	uint32_t maxBounces;                 // wavefront bounces at most (the integrator's depth bound, or "unbounded")
+	cudaGraphConditionalHandle cond;     // WHILE-node condition
+	uint32_t inGraph;                    // 0: plain launches, `cond` is not valid
+};
 
-// Between bounces (one thread): resets the work counters and the output counts; when the live count has dropped below
-// `tailBelow` the queue is handed to the tail kernel — its count moves to counters[CTR_TAIL_COUNT] and the wavefront
-// stages of this and all later bounces find an empty queue.  The bounce at which that happened goes to pinned host
-// memory so that the host enqueues about that many wavefront bounces next time (a hint only: the tail kernel finishes
-// whatever is left, however many paths that is).
-__global__ void prep_kernel(PathState ps, uint32_t *countIn, uint32_t *countOut, uint32_t *countShadow, uint32_t parity,
-		uint32_t bounce, uint32_t tailBelow, uint32_t force) {
-	ps.work[0] = 0; ps.work[1] = 0;
-	if (countOut) *countOut = 0;
-	if (countShadow) *countShadow = 0;
+__device__ __forceinline__ void loop_decide(const PathState &ps, const LoopCtl &ctl, uint32_t live, uint32_t parity, uint32_t bounce) {
 	uint32_t *c = ps.counters;
-	if (countIn && c[CTR_TAIL] == 0) {
-		const uint32_t live = *countIn;
-		if (force || live < tailBelow) {
-			c[CTR_TAIL] = 1; c[CTR_TAIL_COUNT] = live; c[CTR_TAIL_PARITY] = parity; c[CTR_TAIL_BOUNCE] = bounce;
-			*countIn = 0;
-			ps.work[2] = 0;
-			if (ps.feedback) { ps.feedback[1] = live; ps.feedback[0] = bounce | (force ? 0x80000000u : 0u); }
-		}
+	const bool go = live > 0 && live >= ctl.tailBelow && bounce < ctl.maxBounces;
+	if (!go && c[CTR_TAIL] == 0) {
+		// hand-over: the wavefront stages of any later (plain-launch) bounce find an empty queue
+		c[CTR_TAIL] = 1; c[CTR_TAIL_COUNT] = live; c[CTR_TAIL_PARITY] = parity; c[CTR_TAIL_BOUNCE] = bounce;
+		c[parity] = 0;
+		ps.work[2] = 0;
 	}
+	if (ctl.inGraph) cudaGraphSetConditional(ctl.cond, go ? 1u : 0u);
+}
+
+// before the first bounce (counters were zeroed by a memset, generate_kernel filled queue A)
+__global__ void begin_kernel(PathState ps, LoopCtl ctl) {
+	ps.work[0] = 0; ps.work[1] = 0; ps.work[2] = 0;
+	loop_decide(ps, ctl, ps.counters[CTR_COUNT_A], 0u, 0u);
+}
+
+// after the connect kernel of every bounce
+__global__ void advance_kernel(PathState ps, LoopCtl ctl) {
+	uint32_t *c = ps.counters;
+	const uint32_t parity = c[CTR_PARITY] & 1u;
+	const uint32_t live = c[parity ^ 1u];          // what shade appended to the other queue
+	c[parity] = 0; c[CTR_SHADOW] = 0;              // this bounce's input queue becomes the next bounce's output queue
+	ps.work[0] = 0; ps.work[1] = 0;
+	c[CTR_PARITY] = parity ^ 1u;
+	const uint32_t bounce = ++c[CTR_BOUNCE];
+	ps.stats[5] += 4;
+	loop_decide(ps, ctl, live, parity ^ 1u, bounce);
 }
 
 #ifndef MTSB_TAIL_MIN_BLOCKS

@@ -79,16 +79,14 @@ int mtsb_ctx_create(int device, mtsb_ctx **out) {
 	if (const char *e = getenv("MTSB_DP_CPRIM")) ctx->dpCPrim = (float) atof(e);
 	ctx->tailPaths = 1 << 17;
 	if (const char *e = getenv("MTSB_TAIL_PATHS")) ctx->tailPaths = std::max(0, atoi(e));
+	if (const char *e = getenv("MTSB_GRAPH")) ctx->useGraph = atoi(e) != 0;
 	// L2 residency: set aside as much persisting L2 as the device grants (B200: 126 MB of L2); the traversal launches
-	// attach an access-policy window over the acceleration structure (scene.cuh: l2_window)
-	{
-		size_t want = (size_t) prop.persistingL2CacheMaxSize;
-		if (const char *e = getenv("MTSB_L2_PERSIST")) want = std::min<size_t>(want, (size_t) std::max(0L, atol(e)) << 20);
-		if (want > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
-			size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitPersistingL2CacheSize);
-			ctx->l2Persist = got; ctx->l2WindowMax = (size_t) prop.accessPolicyMaxWindowSize;
-		} else cudaGetLastError();
-	}
+	// L2 residency of acceleration structures (scene.cuh: l2_window / l2_claim): only the ceiling is fixed here; the
+	// persisting set-aside itself is sized by the scenes that can use it, because every byte of it is taken from the L2
+	// that the streaming kernels (shade, splat) live on — a fixed maximal set-aside cost config 1 a third of its speed
+	ctx->l2PersistMax = (size_t) prop.persistingL2CacheMaxSize;
+	if (const char *e = getenv("MTSB_L2_PERSIST")) ctx->l2PersistMax = std::min<size_t>(ctx->l2PersistMax, (size_t) std::max(0L, atol(e)) << 20);
+	ctx->l2WindowMax = (size_t) prop.accessPolicyMaxWindowSize;
 	cudaError_t e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
 	if (e != cudaSuccess) { delete ctx; MTSB_FAIL(MTSB_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
 	*out = ctx;
@@ -125,6 +123,7 @@ void mtsb_scene_destroy(mtsb_scene *scene) {
 	if (!scene) return;
 	cudaSetDevice(scene->ctx->device);
 	mtsb_release_pipe(scene);
+	mtsb::l2_claim(scene, 0);
 	delete scene;
 }
 
@@ -338,6 +337,7 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));
+	mtsb::l2_claim(scene, scene->bvh.accel.bytes());
 	scene->committed = true;
 	return 0;
 }

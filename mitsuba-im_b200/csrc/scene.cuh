@@ -38,23 +38,60 @@ struct mtsb_scene {
 	// staging ring + streams of the host-pointer ray queries (trace.cu), created on first use
 	std::mutex pipeMutex;
 	mtsb::TracePipe *pipe = nullptr;
+	size_t l2Bytes = 0;                   // persisting-L2 claim of this scene (l2_claim below), 0 = none
 };
 
 namespace mtsb {
 
-// Launch attribute that keeps the acceleration structure resident in L2 while a traversal kernel runs: a window over
-// the head of the `accel` allocation (nodes first, then TriAccel records) whose hits are marked persisting — as large a
-// share of it as the device's persisting set-aside holds — while everything outside the window (rays, hit records, path
-// state) takes the normal, evictable path.  Returns 0 attributes when the set-aside is unavailable or switched off.
+// L2 residency of the acceleration structure.  A scene whose structure (nodes + TriAccel records) fits the device's
+// persisting-L2 ceiling claims that many bytes at commit.  The device-wide set-aside (cudaLimitPersistingL2CacheSize) is
+// raised to the largest live claim only while BATCHED RAY QUERIES run (l2_phase(scene, true), trace.cu) and dropped to
+// zero for path-tracing passes (l2_phase(scene, false), render_host.cuh): every byte of it is L2 taken away from the
+// streaming kernels — with a 78 MB set-aside the shade kernel of config 1 ran 2.4x slower (11.2 -> 18.0 ms per frame),
+// while the traversal-only batches of config 2 gain 10 % from it.  Larger scenes claim nothing: a partial window measured
+// no gain on the 10.5 M-triangle scene.
+inline void l2_apply(mtsb_ctx *ctx, size_t want) {       // caller holds ctx->l2Mutex
+	if (want == ctx->l2Persist) return;
+	if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+		size_t got = 0; cudaDeviceGetLimit(&got, cudaLimitPersistingL2CacheSize);
+		ctx->l2Persist = got;
+		if (want == 0) cudaCtxResetPersistingL2Cache();
+	} else cudaGetLastError();
+}
+
+inline void l2_claim(mtsb_scene *scene, size_t bytes) {
+	mtsb_ctx *ctx = scene->ctx;
+	std::lock_guard<std::mutex> lock(ctx->l2Mutex);
+	auto &v = ctx->l2Claims;
+	for (size_t i = 0; i < v.size(); ++i) if (v[i].first == scene) { v.erase(v.begin() + i); break; }
+	scene->l2Bytes = 0;
+	if (bytes > 0 && bytes <= ctx->l2PersistMax && bytes <= ctx->l2WindowMax) { v.push_back(std::make_pair((const void *) scene, bytes)); scene->l2Bytes = bytes; }
+	if (v.empty()) l2_apply(ctx, 0);
+}
+
+// queries = true: a batched query on `scene` is about to be launched; false: a path-tracing pass is.
+inline void l2_phase(mtsb_scene *scene, bool queries) {
+	mtsb_ctx *ctx = scene->ctx;
+	if (ctx->l2PersistMax == 0) return;
+	if (!queries && ctx->l2Persist == 0) return;                       // the common case of a render loop: nothing to do
+	if (queries && (scene->l2Bytes == 0 || ctx->l2Persist >= scene->l2Bytes)) return;
+	std::lock_guard<std::mutex> lock(ctx->l2Mutex);
+	size_t want = 0;
+	if (queries) for (auto &c : ctx->l2Claims) want = std::max(want, c.second);
+	l2_apply(ctx, want);
+}
+
+// Launch attribute of the traversal kernels: hits inside the scene's structure are marked persisting; everything outside
+// the window (rays, hit records, path state) takes the normal, evictable path.  0 attributes when the scene made no claim.
 inline int l2_window(const mtsb_scene *scene, cudaLaunchAttribute *attr) {
 	const mtsb_ctx *ctx = scene->ctx;
-	const size_t bytes = std::min(scene->bvh.accel.bytes(), ctx->l2WindowMax);
-	if (ctx->l2Persist == 0 || bytes == 0) return 0;
+	const size_t bytes = scene->l2Bytes;
+	if (bytes == 0 || ctx->l2Persist < bytes) return 0;
 	attr->id = cudaLaunchAttributeAccessPolicyWindow;
 	cudaAccessPolicyWindow &w = attr->val.accessPolicyWindow;
 	w.base_ptr = (void *) scene->bvh.accel.ptr;
 	w.num_bytes = bytes;
-	w.hitRatio = (float) std::min(1.0, (double) ctx->l2Persist / (double) bytes);
+	w.hitRatio = 1.0f;
 	w.hitProp = cudaAccessPropertyPersisting;
 	w.missProp = cudaAccessPropertyStreaming;
 	return 1;

@@ -84,6 +84,7 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 		cudaStream_t st, bool count) {
 	if (n == 0) return 0;
 	mtsb_ctx *ctx = scene->ctx;
+	l2_phase(scene, true);
 	MTSB_CUDA(cudaMemsetAsync(dWork, 0, sizeof(unsigned long long), st));
 	const int blocksPerSm = MTSB_TRACE_BLOCKS_PER_SM;
 	unsigned grid = (unsigned) std::min<size_t>((size_t) ctx->smCount * blocksPerSm, (n + MTSB_TRACE_BLOCK - 1) / MTSB_TRACE_BLOCK);

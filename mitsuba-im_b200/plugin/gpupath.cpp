@@ -54,15 +54,22 @@ public:
 protected:
 	virtual ~GPUResponsiveIntegrator();
 	Mutex *targetLock(const ImageBlock *target);
+	mtsb_render *renderFor(int threadIdx, const Scene &scene, const Sensor &sensor, const Sampler &sampler, const ImageBlock &target);
+	uint32_t passSize(const ImageBlock &target) const;
+public:
+	void prepare(const Scene &scene);
+protected:
 	ref<GPUPathTracer> m_parent;
 	std::vector<mtsb_render *> m_renders;      // one per thread
 	std::map<const ImageBlock *, ref<Mutex> > m_targetLocks;
 	std::string m_stats;
+	std::vector<ImageBlock *> m_allocTargets; std::vector<Sampler *> m_allocSamplers;   // from allocate(), for prepare()
+	int m_active; double m_roundSamples; ref<Timer> m_roundTimer;   // one render() round over all threads (guarded by the parent's mutex)
 };
 
 class GPUPathTracer : public MonteCarloIntegrator {
 public:
-	GPUPathTracer(const Properties &props) : MonteCarloIntegrator(props), m_cancel(false) {
+	GPUPathTracer(const Properties &props) : MonteCarloIntegrator(props), m_cancel(false), m_responsive(NULL) {
 		m_gpus = props.getInteger("gpus", 1);
 		m_sppPerPass = props.getInteger("sppPerPass", 0);
 		m_seed = props.getInteger("seed", 0);
@@ -111,6 +118,7 @@ public:
 
 	bool preprocess(const Scene *scene, RenderQueue *, const RenderJob *, int, int, int) {
 		for (int i = 0; i < m_gpus; ++i) device(i, scene);
+		if (m_responsive) m_responsive->prepare(*scene);
 		return true;
 	}
 
@@ -132,14 +140,17 @@ public:
 		std::vector<mtsb_render *> renders(m_gpus, (mtsb_render *) NULL);
 		for (int g = 0; g < m_gpus; ++g)
 			MTSB_CALL(mtsb_render_create(device(g, scene).scene, &cam, &fd, &id, seedFor(sampler), &renders[g]));
+		const size_t pixels = (size_t) film->getCropSize().x * film->getCropSize().y;
+		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixels, 1));
+		// path state, kernels and the bounce graph are set up before the clock starts (the reference's kd-tree build and
+		// its preprocess() are outside its render timer too)
+		for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_reserve(renders[g], pass));
 		ref<Timer> timer = new Timer();
 		// GPU g renders sample indices s = g (mod gpus).  mtsb_render_pass only QUEUES work (no host wait inside), so this one
 		// thread keeps all devices busy: pass k goes to every GPU before anything is waited for.  A pass covers about one
 		// chunk of paths in flight (8 M) so that cancel() is looked at every few tens of milliseconds; the host waits for
 		// the devices only every fourth pass.
 		const uint32_t perGpu = (sampleCount + m_gpus - 1) / m_gpus;
-		const size_t pixels = (size_t) film->getCropSize().x * film->getCropSize().y;
-		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixels, 1));
 		uint32_t passIdx = 0;
 		for (uint32_t done = 0; done < perGpu && !m_cancel; done += pass, ++passIdx) {
 			for (int g = 0; g < m_gpus; ++g) {
@@ -166,6 +177,8 @@ public:
 			MTSB_CALL(mtsb_film_reduce_all(renders.data(), m_comms.data(), m_gpus, 0));
 		}
 		MTSB_CALL(mtsb_film_to_host(renders[0], dst, n, 0));
+		// the clock stops with the film in host memory; what follows is the reference's own CPU code (Film::put, develop)
+		const double s = timer->getMicroseconds() * 1e-6;
 		for (int g = 0; g < m_gpus; ++g) {
 			mtsb_render_stats(renders[g], st);
 			for (int i = 0; i < 8; ++i) tot[i] += st[i];
@@ -173,15 +186,14 @@ public:
 		}
 		film->put(block);
 		if (queue && job) queue->signalRefresh(job);
-		const double s = timer->getMilliseconds() * 1e-3;
-		Log(EInfo, "gpupath: %llu paths, %llu closest-hit + %llu shadow rays, average path length %.2f, %.1f M samples/s",
+		Log(EInfo, "gpupath: %llu paths, %llu closest-hit + %llu shadow rays, average path length %.2f, %.4f s to the film in host memory, %.1f M samples/s",
 			(unsigned long long) tot[0], (unsigned long long) tot[1], (unsigned long long) tot[2],
-			tot[0] ? (double) tot[3] / tot[0] : 0.0, tot[0] / std::max(s, 1e-9) / 1e6);
+			tot[0] ? (double) tot[3] / tot[0] : 0.0, s, tot[0] / std::max(s, 1e-9) / 1e6);
 		return !m_cancel;
 	}
 
 	void cancel() { m_cancel = true; }
-	ref<ResponsiveIntegrator> makeResponsiveIntegrator() { return new GPUResponsiveIntegrator(this); }
+	ref<ResponsiveIntegrator> makeResponsiveIntegrator() { m_responsive = new GPUResponsiveIntegrator(this); return m_responsive; }
 	void serialize(Stream *stream, InstanceManager *manager) const { MonteCarloIntegrator::serialize(stream, manager); }
 	std::string toString() const {
 		std::ostringstream oss;
@@ -194,6 +206,7 @@ public:
 	int m_gpus, m_sppPerPass, m_seed, m_builder, m_emitterSamples, m_bsdfSamples;
 	bool m_direct;
 	volatile bool m_cancel;
+	GPUResponsiveIntegrator *m_responsive;      // the adapter made by makeResponsiveIntegrator (not owned; clears itself)
 	ref<Mutex> m_mutex;
 	std::vector<GPUDevice> m_devices;
 	std::vector<mtsb_comm *> m_comms;

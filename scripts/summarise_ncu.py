@@ -20,6 +20,16 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__inst_executed_pipe_lsu.sum", "lts__t_bytes.sum", "l1tex__t_bytes.sum"]
 
 
+def kernel_source_sha1():
+    """Hash of the sources the traversal kernel and its tree are compiled from; bench.py prints roofline.traffic only
+    while profiles/traffic.json carries the hash of the sources it runs (a stale capture reads as null)."""
+    import hashlib
+    h = hashlib.sha1()
+    for f in ("trace.cu", "trace.cuh", "bvh.cu", "common.cuh"):
+        h.update(open(os.path.join(ROOT, "mitsuba-im_b200", "csrc", f), "rb").read())
+    return h.hexdigest()
+
+
 def launches(name, tag):
     path = os.path.join(OUT, name)
     if not os.path.exists(path):
@@ -81,5 +91,6 @@ if __name__ == "__main__":
         d = t[0]
         json.dump({"trace_closest_bytes_per_launch": to_bytes(d["dram__bytes_read.sum"]) + to_bytes(d["dram__bytes_write.sum"]),
                    "trace_closest_warp_inst_per_launch": num(d["smsp__inst_executed.sum"]),
+                   "kernel_source_sha1": kernel_source_sha1(),
                    "source": "%s_ncu_full_trace.json (ncu --set full, 16 777 216 chord rays, 1.31 M triangles)" % tag},
                   open(os.path.join(PROF, "traffic.json"), "w"), indent=1)
