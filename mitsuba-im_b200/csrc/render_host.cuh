@@ -101,7 +101,8 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 	LoopShape sh;
 	sh.traceGrid = (unsigned) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM;
 	// sized to the machine and to the chunk the render was made for (r->capacity), not to this chunk: graph nodes are fixed
-	sh.shadeGrid = std::min(blocks_for(r->capacity, RENDER_BLOCK), (unsigned) ctx->smCount * MTSB_SHADE_MIN_BLOCKS * 2u);
+	sh.shadeGrid = blocks_for(r->capacity, RENDER_BLOCK);
+	if (ctx->shadeWaves > 0) sh.shadeGrid = std::min(sh.shadeGrid, (unsigned) ctx->smCount * MTSB_SHADE_MIN_BLOCKS * (unsigned) ctx->shadeWaves);
 	sh.tailGrid = (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS;
 	SceneDev S = scene->dev; S.counters = nullptr;
 	l2_phase(scene, false);

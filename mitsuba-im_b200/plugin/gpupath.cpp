@@ -53,15 +53,17 @@ public:
 	MTS_DECLARE_CLASS()
 protected:
 	virtual ~GPUResponsiveIntegrator();
-	Mutex *targetLock(const ImageBlock *target);
-	mtsb_render *renderFor(int threadIdx, const Scene &scene, const Sensor &sensor, const Sampler &sampler, const ImageBlock &target);
-	uint32_t passSize(const ImageBlock &target) const;
+	mtsb_render *renderFor(int gpu, const Scene &scene, const Sensor &sensor, const Sampler &sampler, const ImageBlock &target);
+	uint32_t maxPass(const ImageBlock &target) const;
+	/// state of one device group during a render() round (guarded by the parent's mutex)
+	struct Group { int entered, roundSize; double landed; bool done; int rc; Group() : entered(0), roundSize(0), landed(0), done(false), rc(0) { } };
 public:
 	void prepare(const Scene &scene);
 protected:
 	ref<GPUPathTracer> m_parent;
-	std::vector<mtsb_render *> m_renders;      // one per thread
-	std::map<const ImageBlock *, ref<Mutex> > m_targetLocks;
+	std::vector<mtsb_render *> m_renders;      // one per device group
+	std::vector<Group> m_groups;
+	ref<Mutex> m_addLock;                      // host-side add into a target (leaders only)
 	std::string m_stats;
 	std::vector<ImageBlock *> m_allocTargets; std::vector<Sampler *> m_allocSamplers;   // from allocate(), for prepare()
 	int m_active; double m_roundSamples; ref<Timer> m_roundTimer;   // one render() round over all threads (guarded by the parent's mutex)

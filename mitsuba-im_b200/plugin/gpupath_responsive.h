@@ -2,23 +2,35 @@
 //
 // Contract served (include/mitsuba/render/integrator2.h:49-100; callers src/mitsuba/im_render.cpp:103-266 and
 // src/im-mts/scene.cpp): render() is entered concurrently by `threadCount` mitsuba::Threads that may share their
-// ImageBlock; each accumulates un-normalised sums into it, reports its own sample count through progress() — the caller
-// divides the summed targets by the summed counts — and polls abort / continu.
+// ImageBlock; each accumulates un-normalised sums into its target, reports a sample count through progress() — the
+// caller divides the SUM of the targets by the SUM of the counts (InteractiveSceneProcess::develop) — and polls
+// abort / continu.
 //
-// How it maps to the GPU: thread t owns the sample indices s = t (mod threadCount) of every pixel and renders them on
-// GPU t % gpus, one asynchronous mtsb_render_pass per pass into ITS OWN device film, which keeps the running sum of the
-// passes not yet handed to the host.  A flush (D2H into page-locked staging + add into the caller's target under that
-// target's lock + device clear) happens after the first pass — an interactive viewer sees the first frame at once — and
-// then whenever the unflushed passes reach half of what has already landed (or after 250 ms), so an N-pass render costs
-// O(log N) film read-backs instead of N.  progress() is only ever told about samples that HAVE landed in the target.
-// Every thread's render owns a CUDA stream (mtsb_render_private_stream), so the passes of the threads that share a GPU
-// overlap on it.  Only lock: one per distinct target, held for the host-side add.
+// How it maps to the GPU.  The host threads exist to keep CPU cores busy; a GPU wants ONE submitter and large passes.
+// The threads are therefore grouped by device (thread t -> GPU t % G, G = min(gpus, threadCount)); the lowest thread of a
+// group is its LEADER and renders the group's whole share — sample indices s = g (mod G) of every pixel — into one device
+// film, in asynchronous passes that grow from one sample per pixel (an interactive viewer sees a first frame at once) to
+// a full chunk of paths in flight.  The film keeps the running sum of the passes not yet handed to the host; a flush (D2H
+// into page-locked staging + add into the leader's target + device clear) happens after the first pass and then whenever
+// the unflushed passes reach half of what has already landed (or after 250 ms): O(log N) read-backs for N passes.
+// The other threads of the group are FOLLOWERS: they render nothing, watch the group's landed count and report their
+// equal share of it (landed / group size — progress() takes a double) so that the caller's per-thread accounting
+// (sum of counts; `spp * threadCount >= sampleCount` as the stop test) holds exactly as if every thread had rendered.
+// Measured: 16 threads each driving 1/16 of a 512x512x64 frame through a stream of their own took 44 ms for 11 ms of
+// device work (every small pass pays the per-bounce latency floor of the wavefront); one leader runs at the classic
+// path's speed.
 #pragma once
+#include <unistd.h>
 
 MTS_NAMESPACE_BEGIN
 
+static inline double self_now() {      // milliseconds on a process-wide clock (timing log only)
+	struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+	return (double) (ts.tv_sec % 1000) * 1e3 + ts.tv_nsec * 1e-6;
+}
+
 GPUResponsiveIntegrator::GPUResponsiveIntegrator(GPUPathTracer *parent) : ResponsiveIntegrator(parent->getProperties()), m_parent(parent),
-	m_active(0), m_roundSamples(0) { m_roundTimer = new Timer(); }
+	m_active(0), m_roundSamples(0) { m_roundTimer = new Timer(); m_addLock = new Mutex(); m_groups.resize(std::max(1, parent->m_gpus)); }
 
 GPUResponsiveIntegrator::~GPUResponsiveIntegrator() {
 	if (m_parent->m_responsive == this) m_parent->m_responsive = NULL;
@@ -32,15 +44,15 @@ bool GPUResponsiveIntegrator::preprocess(const Scene *scene, const Sensor *, con
 	return true;
 }
 
-/// The render of thread `threadIdx` (created on first use): own film on GPU threadIdx % gpus, own stream, path state
-/// reserved and kernels loaded — all of it before the first timed pass.
-mtsb_render *GPUResponsiveIntegrator::renderFor(int threadIdx, const Scene &scene, const Sensor &sensor, const Sampler &sampler, const ImageBlock &target) {
+/// The render of device group `gpu` (created on first use): own film, own stream, path state reserved and kernels
+/// loaded — all of it before the first timed pass.
+mtsb_render *GPUResponsiveIntegrator::renderFor(int gpu, const Scene &scene, const Sensor &sensor, const Sampler &sampler, const ImageBlock &target) {
 	GPUPathTracer *p = m_parent.get();
-	GPUDevice &dev = p->device(threadIdx % p->m_gpus, &scene);
+	GPUDevice &dev = p->device(gpu, &scene);
 	{
 		LockGuard lock(p->m_mutex);
-		if ((int) m_renders.size() <= threadIdx) m_renders.resize(threadIdx + 1, (mtsb_render *) NULL);
-		if (m_renders[threadIdx]) return m_renders[threadIdx];
+		if ((int) m_renders.size() <= gpu) m_renders.resize(gpu + 1, (mtsb_render *) NULL);
+		if (m_renders[gpu]) return m_renders[gpu];
 	}
 	mtsb_camera cam; describeCamera(&sensor, cam);
 	mtsb_film_desc fd; describeFilm(target, scene.getFilm()->getReconstructionFilter(), scene.getFilm(), fd);
@@ -50,28 +62,23 @@ mtsb_render *GPUResponsiveIntegrator::renderFor(int threadIdx, const Scene &scen
 	mtsb_integrator_desc id; p->describeIntegrator(id);
 	mtsb_render *r = NULL;
 	MTSB_CALL(mtsb_render_create(dev.scene, &cam, &fd, &id, p->seedFor(&sampler), &r));
-	MTSB_CALL(mtsb_render_private_stream(r));       // the threads' passes overlap on the device
-	MTSB_CALL(mtsb_render_reserve(r, passSize(target)));
+	MTSB_CALL(mtsb_render_private_stream(r));
+	MTSB_CALL(mtsb_render_reserve(r, maxPass(target)));
 	LockGuard lock(p->m_mutex);
-	m_renders[threadIdx] = r;
+	m_renders[gpu] = r;
 	return r;
 }
 
-/// Samples per pixel of one pass: about a million paths (1 spp from 1024^2 up) — abort / camera changes take effect
-/// within one wave of the wavefront, while small frames do not pay the per-bounce launch floor once per sample.
-uint32_t GPUResponsiveIntegrator::passSize(const ImageBlock &target) const {
+/// Largest pass, in samples per pixel: one full chunk of paths in flight (8 M) — or the `sppPerPass` property.
+uint32_t GPUResponsiveIntegrator::maxPass(const ImageBlock &target) const {
 	if (m_parent->m_sppPerPass > 0) return (uint32_t) m_parent->m_sppPerPass;
 	const size_t pixelCount = (size_t) target.getSize().x * target.getSize().y;
-	return (uint32_t) std::max<size_t>(1, ((size_t) 1 << 20) / std::max<size_t>(pixelCount, 1));
+	return (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixelCount, 1));
 }
 
-bool GPUResponsiveIntegrator::allocate(const Scene &scene, Sampler *const *samplers, ImageBlock *const *targets, int threadCount) {
+bool GPUResponsiveIntegrator::allocate(const Scene &, Sampler *const *samplers, ImageBlock *const *targets, int threadCount) {
 	for (size_t i = 0; i < m_renders.size(); ++i) if (m_renders[i]) mtsb_render_destroy(m_renders[i]);
-	m_renders.assign(threadCount, (mtsb_render *) NULL);
-	// one lock per distinct target (the CLI hands one ImageBlock to every 8 threads, the GUI one to all)
-	m_targetLocks.clear();
-	for (int i = 0; i < threadCount; ++i)
-		if (targets && targets[i] && !m_targetLocks.count(targets[i])) m_targetLocks[targets[i]] = new Mutex();
+	m_renders.assign(m_parent->m_gpus, (mtsb_render *) NULL);
 	// remembered for prepare(): the scene is not initialised yet when the CLI calls this (im_render.cpp:52-57 runs in the
 	// process constructor, Scene::initialize() in Scene::preprocess), so nothing touches the device here
 	m_allocTargets.assign(threadCount, (ImageBlock *) NULL); m_allocSamplers.assign(threadCount, (Sampler *) NULL);
@@ -83,34 +90,43 @@ bool GPUResponsiveIntegrator::allocate(const Scene &scene, Sampler *const *sampl
 }
 
 /// Called from GPUPathTracer::preprocess (i.e. from Scene::preprocess, after Scene::initialize and before the threads
-/// enter render()): device-side allocation of every thread's render happens here, not inside the first timed round.
+/// enter render()): device-side allocation of every group's render happens here, not inside the first timed round.
 void GPUResponsiveIntegrator::prepare(const Scene &scene) {
 	if (!scene.getSensor()) return;
-	for (size_t i = 0; i < m_allocTargets.size(); ++i)
-		if (m_allocTargets[i] && m_allocSamplers[i]) renderFor((int) i, scene, *scene.getSensor(), *m_allocSamplers[i], *m_allocTargets[i]);
-}
-
-Mutex *GPUResponsiveIntegrator::targetLock(const ImageBlock *target) {
-	LockGuard lock(m_parent->m_mutex);
-	ref<Mutex> &m = m_targetLocks[target];
-	if (!m) m = new Mutex();
-	return m.get();
+	const int G = std::min<int>(m_parent->m_gpus, (int) m_allocTargets.size());
+	for (int g = 0; g < G; ++g)        // the leader of group g is thread g
+		if (m_allocTargets[g] && m_allocSamplers[g]) renderFor(g, scene, *scene.getSensor(), *m_allocSamplers[g], *m_allocTargets[g]);
 }
 
 int GPUResponsiveIntegrator::render(const Scene &scene, const Sensor &sensor, Sampler &sampler, ImageBlock &target,
 		Controls controls, int threadIdx, int threadCount) {
 	GPUPathTracer *p = m_parent.get();
+	const int G = std::min(p->m_gpus, threadCount), gpu = threadIdx % G;
+	const bool leader = threadIdx == gpu;
+	int groupSize = 0;
+	for (int t = gpu; t < threadCount; t += G) ++groupSize;
+	Group &grp = m_groups[gpu];
 	const uint32_t sampleCount = (uint32_t) sampler.getSampleCount();
-	mtsb_camera cam; describeCamera(&sensor, cam);
-	mtsb_render *r = renderFor(threadIdx, scene, sensor, sampler, target);
-	MTSB_CALL(mtsb_render_set_camera(r, &cam));     // camera change = new kernel parameters, nothing else
-	// wall time of one render() round over all threads, logged by the last thread out (the responsive CLI path prints no
-	// "Render time" of its own: src/mitsuba/mitsuba.cpp:387-400)
+	const size_t pixels = (size_t) target.getSize().x * target.getSize().y;
+	mtsb_render *r = NULL;
+	if (leader) {
+		mtsb_camera cam; describeCamera(&sensor, cam);
+		r = renderFor(gpu, scene, sensor, sampler, target);
+		MTSB_CALL(mtsb_render_set_camera(r, &cam));     // camera change = new kernel parameters, nothing else
+	}
+
+	// One render() round over all threads: group state is reset by whoever enters first, the wall time of the round is
+	// logged by the last thread out (the responsive CLI path prints no "Render time": src/mitsuba/mitsuba.cpp:387-400).
 	struct Round {
-		GPUResponsiveIntegrator *self; const uint32_t *landed; size_t pixels;
-		Round(GPUResponsiveIntegrator *s, const uint32_t *l, size_t px) : self(s), landed(l), pixels(px) {
+		GPUResponsiveIntegrator *self; Group *grp; const uint32_t *landed; size_t pixels;
+		Round(GPUResponsiveIntegrator *s, Group *g, int groupSize, const uint32_t *l, size_t px) : self(s), grp(g), landed(l), pixels(px) {
 			LockGuard lock(self->m_parent->m_mutex);
 			if (self->m_active++ == 0) { self->m_roundTimer->reset(); self->m_roundSamples = 0; }
+			// every thread of the group enters every round exactly once (the caller joins them all before the next one), so
+			// the first entrant is recognised by count — not by "nobody is inside", which a fast leader would defeat
+			if (grp->entered == grp->roundSize) grp->entered = 0;
+			if (grp->entered == 0) { grp->landed = 0; grp->done = false; grp->rc = 0; grp->roundSize = groupSize; }
+			++grp->entered;
 		}
 		~Round() {
 			LockGuard lock(self->m_parent->m_mutex);
@@ -122,27 +138,55 @@ int GPUResponsiveIntegrator::render(const Scene &scene, const Sensor &sensor, Sa
 			}
 		}
 	};
+	uint32_t queued = 0, landed = 0;          // samples per pixel handed to the GPU / present in `target` (leader only)
+	Round round(this, &grp, groupSize, &landed, pixels);
+
+	if (!leader) {
+		// ---- follower: report an equal share of what the group's leader has landed
+		double seen = -1;
+		while (true) {
+			if (controls.abort && *controls.abort) return -1;
+			if (controls.continu && !*controls.continu) return -2;
+			double now; bool done; int rc;
+			{ LockGuard lock(p->m_mutex); now = grp.landed; done = grp.done; rc = grp.rc; }
+			if (now != seen && controls.interrupt) {
+				seen = now;
+				const int prc = controls.interrupt->progress(this, scene, sensor, sampler, target, now / groupSize, controls, threadIdx, threadCount);
+				if (prc != 0) return prc;
+			}
+			if (done) return rc;
+			usleep(200);
+		}
+	}
+
+	// ---- leader
+	struct Finish {      // whatever way the leader leaves, its followers are released with its return code
+		GPUPathTracer *p; Group *grp; int rc;
+		~Finish() { LockGuard lock(p->m_mutex); grp->done = true; grp->rc = rc; }
+	} fin = { p, &grp, 0 };
 	float *dst = target.getBitmap()->getFloatData();
 	const size_t n = (size_t) target.getBitmap()->getSize().x * target.getBitmap()->getSize().y * target.getChannelCount();
-	Mutex *tlock = targetLock(&target);
-
-	// this thread's share: sample indices threadIdx, threadIdx + threadCount, ...
+	// the group's share: sample indices gpu, gpu + G, ...
 	uint32_t mine = 0;
-	for (uint32_t s = (uint32_t) threadIdx; s < sampleCount; s += (uint32_t) threadCount) ++mine;
-	const uint32_t pass = passSize(target);
-	uint32_t queued = 0, landed = 0;          // samples per pixel handed to the GPU / present in `target`
+	for (uint32_t s = (uint32_t) gpu; s < sampleCount; s += (uint32_t) G) ++mine;
+	const uint32_t passCap = maxPass(target);
+	uint32_t pass = p->m_sppPerPass > 0 ? passCap : 1u;     // grows 1, 4, 16, ... up to a full chunk of paths
 	int sinceSync = 0;
-	Round round(this, &landed, (size_t) target.getSize().x * target.getSize().y);
 	ref<Timer> sinceFlush = new Timer();
+	static const bool timing = getenv("MTSB_PLUGIN_TIMING") != NULL;      // breakdown of a round in the log
+	ref<Timer> tt = new Timer();
+	double tSubmit = 0, tStage = 0, tAdd = 0, tProgress = 0; const double tEnter = self_now();
 	MTSB_CALL(mtsb_render_clear(r));          // the device film holds only what has not landed yet
 	while (true) {
-		if (controls.abort && *controls.abort) return -1;
-		if (controls.continu && !*controls.continu) return -2;
+		if (controls.abort && *controls.abort) return fin.rc = -1;
+		if (controls.continu && !*controls.continu) return fin.rc = -2;
 		// flush policy: first pass at once, then geometrically (or every 250 ms), and always at the end of the share
 		const uint32_t unflushed = queued - landed;
 		if (unflushed && (queued >= mine || unflushed >= std::max(1u, landed / 2) || sinceFlush->getMilliseconds() >= 250)) {
 			const float *src = NULL; size_t cnt = 0;
-			MTSB_CALL(mtsb_film_stage(r, &src, &cnt));     // waits for this thread's passes only up to here
+			tt->reset();
+			MTSB_CALL(mtsb_film_stage(r, &src, &cnt));     // waits for the passes queued so far
+			tStage += tt->getMicroseconds() * 1e-3;
 			if (cnt != n) Log(EError, "gpupath: target holds %zu floats, the device film %zu", n, cnt);
 			if (threadIdx == 0) {
 				uint64_t st[8]; mtsb_render_stats(r, st);
@@ -152,23 +196,37 @@ int GPUResponsiveIntegrator::render(const Scene &scene, const Sensor &sensor, Sa
 				m_stats = buf;
 			}
 			MTSB_CALL(mtsb_render_clear(r));
+			tt->reset();
 			{
-				LockGuard lock(tlock);
+				// only leaders write targets; they can meet in one ImageBlock when the caller shares it between GPUs' threads
+				LockGuard lock(m_addLock);
 				for (size_t i = 0; i < n; ++i) dst[i] += src[i];
 			}
+			tAdd += tt->getMicroseconds() * 1e-3;
 			landed = queued;
+			{ LockGuard lock(p->m_mutex); grp.landed = (double) landed; }
 			sinceFlush->reset();
+			sinceSync = 0;
 		}
 		if (controls.interrupt) {
-			const int rc = controls.interrupt->progress(this, scene, sensor, sampler, target, (double) landed, controls, threadIdx, threadCount);
-			if (rc != 0) return rc;
+			tt->reset();
+			const int rc = controls.interrupt->progress(this, scene, sensor, sampler, target, (double) landed / groupSize, controls, threadIdx, threadCount);
+			tProgress += tt->getMicroseconds() * 1e-3;
+			if (rc != 0) return fin.rc = rc;
 		}
-		if (queued >= mine) return 0;                    // "sampler exhausted"
+		if (queued >= mine) {                            // "sampler exhausted"
+			if (timing) SLog(EInfo, "gpupath: leader %d (group of %d): %.2f ms in render(); submit %.2f, stage (sync + D2H) %.2f, add %.2f, progress %.2f ms",
+				threadIdx, groupSize, self_now() - tEnter, tSubmit, tStage, tAdd, tProgress);
+			return fin.rc = 0;
+		}
 		const uint32_t cnt = std::min(pass, mine - queued);
-		// queueing only: mtsb_render_pass does not wait for the device, and touches nothing but this thread's render
-		MTSB_CALL(mtsb_render_pass(r, queued * threadCount, cnt, sampleCount, NULL, (uint32_t) threadCount, (uint32_t) threadIdx));
+		tt->reset();
+		// queueing only: mtsb_render_pass does not wait for the device
+		MTSB_CALL(mtsb_render_pass(r, queued * G, cnt, sampleCount, NULL, (uint32_t) G, (uint32_t) gpu));
+		tSubmit += tt->getMicroseconds() * 1e-3;
 		queued += cnt;
-		// keep at most a few passes in flight per thread so that abort / camera changes take effect within a few waves
+		pass = std::min(passCap, pass * 4);
+		// keep at most a few passes in flight so that abort / camera changes take effect within a few waves
 		if (++sinceSync >= 4) { MTSB_CALL(mtsb_render_sync(r)); sinceSync = 0; }
 	}
 }
