@@ -171,4 +171,5 @@ connect_kernel(SceneDev S, PathState ps) {
 } // namespace mtsb
 #include "render_shade.cuh"
 #include "render_tail.cuh"
+#include "render_direct.cuh"
 #include "render_host.cuh"

@@ -5,16 +5,32 @@ using namespace mtsb;
 
 static const size_t MAX_PATHS_IN_FLIGHT = (size_t) 1 << 23;
 
+// `direct` with emitterSamples / bsdfSamples other than 1/1 fans one camera path out into N shadow + M BSDF rays
+// (render_direct.cuh); everything else runs one shadow ray and one continuation ray per path slot.
+static inline bool fan_mode(const mtsb_render *r) {
+	return r->integ.type == MTSB_INTEGRATOR_DIRECT && (r->integ.emitterSamples != 1 || r->integ.bsdfSamples != 1);
+}
+
+// camera paths per chunk: the fan-out of `direct` shares the same budget of rays in flight
+static inline size_t max_paths(const mtsb_render *r) {
+	if (!fan_mode(r)) return MAX_PATHS_IN_FLIGHT;
+	return MAX_PATHS_IN_FLIGHT / (size_t) (1 + std::max(r->integ.emitterSamples, r->integ.bsdfSamples));
+}
+
 static int ensure_capacity(mtsb_render *r, size_t paths) {
 	if (paths <= r->capacity) return 0;
-	size_t cap = std::max<size_t>(paths, 1024);
-	MTSB_CHECK(r->bufF4.alloc(cap * 10));
+	const size_t cap = std::max<size_t>(paths, 1024);
+	const size_t M = fan_mode(r) ? (size_t) r->integ.bsdfSamples : 0, N = fan_mode(r) ? (size_t) std::max(1, r->integ.emitterSamples) : 1;
+	const size_t wide = cap * (1 + M);            // camera slots + secondary slots (one per BSDF sample)
+	MTSB_CHECK(r->bufF4.alloc(wide * 6 + cap + cap * N * 3));
 	MTSB_CHECK(r->bufRng.alloc(cap));
-	MTSB_CHECK(r->bufQueue.alloc(cap * 2));
+	MTSB_CHECK(r->bufQueue.alloc(cap + std::max(cap, cap * M)));
 	PathState &ps = r->ps;
 	float4 *f = r->bufF4.ptr;
-	ps.rayO = f; ps.rayD = f + cap; ps.hit = f + 2 * cap; ps.thr = f + 3 * cap; ps.L = f + 4 * cap; ps.prev = f + 5 * cap;
-	ps.misc = f + 6 * cap; ps.shO = f + 7 * cap; ps.shD = f + 8 * cap; ps.shL = f + 9 * cap;
+	ps.rayO = f; ps.rayD = f + wide; ps.hit = f + 2 * wide; ps.thr = f + 3 * wide; ps.prev = f + 4 * wide; ps.misc = f + 5 * wide;
+	f += 6 * wide;
+	ps.L = f; f += cap;
+	ps.shO = f; ps.shD = f + cap * N; ps.shL = f + 2 * cap * N;
 	ps.rng = r->bufRng.ptr;
 	ps.queueA = r->bufQueue.ptr; ps.queueB = r->bufQueue.ptr + cap;
 	r->capacity = cap;
@@ -114,7 +130,25 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 	const uint32_t tailBelow = (uint32_t) std::max(0, r->tailPaths);
 	const uint32_t bounded = maxDepth > 0 ? (uint32_t) maxDepth : 0x7fffffffu;
 
-	if (ctx->useGraph && !r->graphFailed) {
+	if (fan_mode(r)) {
+		// MIDirectIntegrator with N emitter / M BSDF samples: a fixed sequence, no loop (render_direct.cuh)
+		const int N = r->integ.emitterSamples, M = r->integ.bsdfSamples;
+		DirectFan fan; fan.capacity = (uint32_t) r->capacity;
+		fan.weightBSDF = 1.0f / (float) M; fan.weightLum = 1.0f / (float) N;                 // direct.cpp:128-137 (inf for a count of 0, never used)
+		fan.fracBSDF = (float) M / (float) (N + M); fan.fracLum = (float) N / (float) (N + M);
+		LoopCtl ctl; ctl.tailBelow = 0; ctl.maxBounces = 2; ctl.inGraph = 0; ctl.cond = 0;
+		const unsigned fanGrid = std::min(blocks_for(g.count, RENDER_BLOCK), (unsigned) ctx->smCount * 16u);
+		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
+		MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+		direct_head_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, fan);
+		MTSB_CHECK(launch_trav(scene, connect_fan_kernel, sh.traceGrid, st, S, ps));
+		if (M > 0) {
+			fan_flip_kernel<<<1, 1, 0, st>>>(ps);
+			MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+			direct_tail_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, fan);
+		}
+		r->launches += M > 0 ? 7 : 4;
+	} else if (ctx->useGraph && !r->graphFailed) {
 		if (!r->bounceExec || r->graphKey != (const void *) r->bufF4.ptr || r->graphTail != (int) tailBelow) {
 			if (build_bounce_graph(r, sh, tailBelow, bounded) < 0) {
 				// a driver without conditional graph nodes: the same kernels as plain launches (still no host round trip)
@@ -124,7 +158,9 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 			}
 		}
 	}
-	if (r->bounceExec) {
+	if (fan_mode(r)) {
+		// queued above
+	} else if (r->bounceExec) {
 		MTSB_CUDA(cudaGraphLaunch(r->bounceExec, st));
 		r->launches += tailBelow ? 2 : 1;               // begin + tail; the kernels inside the WHILE node are counted on the device
 	} else {
@@ -176,8 +212,9 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: bad film description (%dx%d, %d channels)", film->width, film->height, film->channels);
 	if (integrator->type != MTSB_INTEGRATOR_PATH && integrator->type != MTSB_INTEGRATOR_DIRECT)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_create: integrator type %d is outside the GPU subset", integrator->type);
-	if (integrator->type == MTSB_INTEGRATOR_DIRECT && (integrator->emitter_samples != 1 || integrator->bsdf_samples != 1))
-		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_create: direct integrator supported with emitterSamples = bsdfSamples = 1 only");
+	if (integrator->type == MTSB_INTEGRATOR_DIRECT && (integrator->emitter_samples < 0 || integrator->bsdf_samples < 0 ||
+			integrator->emitter_samples + integrator->bsdf_samples <= 0 || integrator->emitter_samples > 4096 || integrator->bsdf_samples > 4096))
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: direct integrator needs emitterSamples + bsdfSamples > 0 (direct.cpp:109)");
 	MTSB_CUDA(cudaSetDevice(scene->ctx->device));
 	mtsb_render *r = new mtsb_render();
 	r->scene = scene;
@@ -276,7 +313,7 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	g.samples = nullptr;
 	const unsigned long long total = (unsigned long long) g.pixPadded * spp_count;
 	// chunks hold whole sample planes when possible so that a warp covers an 8x4 pixel tile of one sample index
-	size_t chunk = std::min<unsigned long long>(total, MAX_PATHS_IN_FLIGHT);
+	size_t chunk = std::min<unsigned long long>(total, max_paths(r));
 	if (chunk > g.pixPadded) chunk = (chunk / g.pixPadded) * g.pixPadded;
 	if (chunk > r->capacity) MTSB_CHECK(ensure_capacity(r, chunk));
 	for (unsigned long long first = 0; first < total; first += chunk) {
@@ -291,7 +328,7 @@ int mtsb_render_reserve(mtsb_render *r, uint32_t spp_per_pass) {
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
 	const unsigned long long pixPadded = (unsigned long long) ((r->film.cropW + 7) / 8) * ((r->film.cropH + 3) / 4) * 32;
 	const unsigned long long total = pixPadded * std::max(1u, spp_per_pass);
-	size_t chunk = (size_t) std::min<unsigned long long>(total, MAX_PATHS_IN_FLIGHT);
+	size_t chunk = (size_t) std::min<unsigned long long>(total, max_paths(r));
 	if (chunk > pixPadded) chunk = (chunk / pixPadded) * pixPadded;
 	MTSB_CHECK(ensure_capacity(r, chunk));
 	// one 8x4-pixel pass: loads every kernel of the pipeline, instantiates the bounce graph for this capacity

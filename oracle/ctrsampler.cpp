@@ -11,6 +11,11 @@
  *     float = bitcast((word >> 9) | 0x3f800000) - 1      (same 23-bit trick as Random::nextFloat,
  *                                                        src/libcore/random.cpp:626-635)
  *
+ * Sample ARRAYS (Sampler::request2DArray / next2DArray, src/librender/sampler.cpp:78-93 — MIDirectIntegrator asks for them when
+ * emitterSamples or bsdfSamples > 1, direct.cpp:140-145) are counter-based too: entry j of the a-th requested 2D array
+ * for sample index s of pixel (x, y) is the first two words of Philox4x32-10(ctr = {x, y, s, j}, key = {seed,
+ * 0x32446100 + a}); 1D arrays use key 0x31446100 + a and the first word.
+ *
  * `dim` counts next1D()/next2D() draws since generate()/advance().  With it the reference's own `path`
  * plugin consumes exactly the random numbers of the CUDA wavefront, so per-sample radiance can be
  * compared directly (classic block renderer: SamplingIntegrator::renderBlock,
@@ -61,6 +66,25 @@ public:
 		if (nextSampleIdx != (size_t) ~0) m_sampleIndex = nextSampleIdx;
 		m_dim = 0; m_block = 0xFFFFFFFFu;
 		m_dimension1DArray = m_dimension2DArray = 0;
+		// the stock samplers fill their arrays for the whole pixel here as well (independent.cpp:75-90)
+		uint32_t w[4];
+		for (size_t a = 0; a < m_req2D.size(); ++a)
+			for (size_t smp = 0; smp < m_sampleCount; ++smp)
+				for (size_t j = 0; j < m_req2D[a]; ++j) {
+					philox4x32_10(m_px, m_py, (uint32_t) smp, (uint32_t) j, m_seed, 0x32446100u + (uint32_t) a, w);
+					m_sampleArrays2D[a][smp * m_req2D[a] + j] = Point2(toFloat(w[0]), toFloat(w[1]));
+				}
+		for (size_t a = 0; a < m_req1D.size(); ++a)
+			for (size_t smp = 0; smp < m_sampleCount; ++smp)
+				for (size_t j = 0; j < m_req1D[a]; ++j) {
+					philox4x32_10(m_px, m_py, (uint32_t) smp, (uint32_t) j, m_seed, 0x31446100u + (uint32_t) a, w);
+					m_sampleArrays1D[a][smp * m_req1D[a] + j] = toFloat(w[0]);
+				}
+	}
+	static inline Float toFloat(uint32_t w) {
+		union { uint32_t u; float f; } x;
+		x.u = (w >> 9) | 0x3f800000u;
+		return x.f - 1.0f;
 	}
 	void advance() { Sampler::advance(); m_dim = 0; m_block = 0xFFFFFFFFu; }
 	void setSampleIndex(size_t idx) { Sampler::setSampleIndex(idx); m_dim = 0; m_block = 0xFFFFFFFFu; }

@@ -96,6 +96,14 @@ def direct_case(td):
     li_case(td, "direct", sd)
 
 
+def direct_fan_case(td, n_em, n_bsdf):
+    """MIDirectIntegrator with emitterSamples / bsdfSamples other than 1: the sample ARRAYS of the sampler come into play
+    (direct.cpp:140-145, 200-204, 250-254), which the counter sampler defines as a second Philox stream."""
+    sd = S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=29)
+    sd.set_integrator("direct", emitter_samples=n_em, bsdf_samples=n_bsdf)
+    li_case(td, "direct_%d_%d" % (n_em, n_bsdf), sd)
+
+
 def strict_case(td):
     """MonteCarloIntegrator's strictNormals and hideEmitters switches (src/librender/integrator.cpp:191-226,
     src/integrators/path/path.cpp:136-165,196-199,218-222) on meshes with interpolated normals."""
@@ -114,6 +122,11 @@ def thinlens_case(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "direct_fan":       # only the cases added in round 2
+        with tempfile.TemporaryDirectory() as td:
+            for n_em, n_bsdf in ((4, 2), (1, 3), (3, 1), (2, 0)):
+                direct_fan_case(td, n_em, n_bsdf)
+        sys.exit(0)
     with tempfile.TemporaryDirectory() as td:
         bsdf_case(td)
         emitter_case(td)
@@ -123,3 +136,5 @@ if __name__ == "__main__":
         direct_case(td)
         thinlens_case(td)
         strict_case(td)
+        for n_em, n_bsdf in ((4, 2), (1, 3), (3, 1), (2, 0)):
+            direct_fan_case(td, n_em, n_bsdf)

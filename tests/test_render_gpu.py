@@ -98,7 +98,8 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 
 
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
-@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict"])
+@pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
+                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -115,6 +116,12 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
         # MIDirectIntegrator::Li (src/integrators/direct/direct.cpp:146-309) with emitterSamples = bsdfSamples = 1
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
         sd.set_integrator("direct")
+    elif name.startswith("direct_"):
+        # emitterSamples / bsdfSamples other than 1/1 (direct.cpp:95-107, 195-306): sample arrays, fraction-weighted power
+        # heuristic; parameters of make_golden_render.direct_fan_case
+        n_em, n_bsdf = (int(x) for x in name.split("_")[1:])
+        sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+        sd.set_integrator("direct", emitter_samples=n_em, bsdf_samples=n_bsdf)
     elif name == "strict":
         # strictNormals + hideEmitters (path.cpp:136-165,196-199,218-222); parameters of make_golden_render.strict_case
         sd = S.materials_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)
