@@ -79,6 +79,18 @@ typedef struct mtsb_surface {
 	float uv[2];                        /* its.uv                                              */
 } mtsb_surface;
 
+/* Light record: what ShapeKDTree::rayIntersect(ray, t, shape, n, uv) returns (src/librender/skdtree.cpp:144-204; used by
+ * Scene::rayIntersect(ray, t, shape, n, uv), include/mitsuba/render/scene.h:216-222, for bidirectional vertex queries):
+ * the UN-FLOORED adaptive epsilon of the shadow-ray overload, closest hit, the face normal normalize((p1-p0) x (p2-p0))
+ * (rectangle: its frame normal) and the interpolated texture coordinates — (0,0) for a mesh without any.  32 bytes. */
+typedef struct mtsb_light_hit {
+	float t;                            /* +inf on a miss                                      */
+	uint32_t shape;                     /* shape index (addShape order), MTSB_NO_HIT on a miss */
+	float n[3];
+	float uv[2];
+	uint32_t pad;
+} mtsb_light_hit;
+
 /* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor,conductor,roughdielectric}.cpp), constant textures only. */
 enum {
 	MTSB_BSDF_DIFFUSE        = 0,  /* p[0..2] reflectance                                                    */
@@ -202,6 +214,8 @@ MTSB_API int  mtsb_trace_closest(mtsb_scene *scene, const mtsb_ray *rays, size_t
 MTSB_API int  mtsb_trace_any(mtsb_scene *scene, const mtsb_ray *rays, size_t n, uint8_t *out, int on_device);
 /* Batched closest hit + ShapeKDTree::fillIntersectionRecord<true> (include/mitsuba/render/skdtree.h:343-428). */
 MTSB_API int  mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_surface *out, int on_device);
+/* replaces ShapeKDTree::rayIntersect(ray, t, shape, n, uv), src/librender/skdtree.cpp:144-204 */
+MTSB_API int  mtsb_trace_light(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_light_hit *out, int on_device);
 /* Traversal counters of the last trace call when built with counters enabled, else zeros:
  * out[0]=nodes visited, out[1]=primitive tests, out[2]=rays. */
 MTSB_API int  mtsb_trace_counters(mtsb_scene *scene, uint64_t out[4]);

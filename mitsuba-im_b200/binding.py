@@ -30,6 +30,8 @@ hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]
 surface_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4"), ("shape", "<u4"),
                           ("prim_local", "<u4"), ("p", "<f4", 3), ("ng", "<f4", 3), ("ns", "<f4", 3),
                           ("s", "<f4", 3), ("tt", "<f4", 3), ("uv", "<f4", 2)])
+light_dtype = np.dtype([("t", "<f4"), ("shape", "<u4"), ("n", "<f4", 3), ("uv", "<f4", 2), ("pad", "<u4")])
+assert light_dtype.itemsize == 32
 assert ray_dtype.itemsize == 32 and hit_dtype.itemsize == 16 and surface_dtype.itemsize == 92
 
 
@@ -96,7 +98,7 @@ def lib():
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
         "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
         "mtsb_trace_closest": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_any": (i32, [vp, vp, sz, vp, i32]),
-        "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
+        "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_light": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
         "mtsb_trace_count": (i32, [vp, vp, sz, i32, i32, vp]),
         "mtsb_host_alloc": (vp, [sz]), "mtsb_host_free": (None, [vp]),
         "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
@@ -262,6 +264,13 @@ class Scene:
         r = self._rays(rays)
         out = np.empty(r.shape[0], surface_dtype)
         _check(lib().mtsb_trace_surface(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def ray_intersect_light(self, rays):
+        """ShapeKDTree::rayIntersect(ray, t, shape, n, uv) (src/librender/skdtree.cpp:144-204) for a batch."""
+        r = self._rays(rays)
+        out = np.empty(r.shape[0], light_dtype)
+        _check(lib().mtsb_trace_light(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
         return out
 
     def trace_device(self, mode, d_rays, n, d_out):

@@ -14,7 +14,7 @@
 
 namespace mtsb {
 
-enum { MODE_CLOSEST = 0, MODE_ANY = 1, MODE_SURFACE = 2 };
+enum { MODE_CLOSEST = 0, MODE_ANY = 1, MODE_SURFACE = 2, MODE_LIGHT = 3 };
 
 // Ray source / record sink of the batched C-ABI queries: AoS mtsb_ray in, mtsb_hit / byte / mtsb_surface out.
 template <int MODE>
@@ -26,7 +26,10 @@ struct BatchIO {
 	__device__ __forceinline__ void write_miss(unsigned long long i) const {
 		if (MODE == MODE_ANY) ((uint8_t *) out)[i] = 0;
 		else if (MODE == MODE_CLOSEST) __stcs((float4 *) out + i, make_float4(INFINITY, 0.0f, 0.0f, __uint_as_float(MTSB_NO_HIT)));
-		else {
+		else if (MODE == MODE_LIGHT) {
+			((float4 *) out)[2 * i] = make_float4(INFINITY, __uint_as_float(MTSB_NO_HIT), 0.0f, 0.0f);
+			((float4 *) out)[2 * i + 1] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+		} else {
 			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
 			rec.t = INFINITY; rec.prim = MTSB_NO_HIT; rec.shape = MTSB_NO_HIT;
 			((mtsb_surface *) out)[i] = rec;
@@ -37,7 +40,8 @@ struct BatchIO {
 		// acceleration structure out of L2
 		const float4 r0 = __ldcs(rays + 2 * i), r1 = __ldcs(rays + 2 * i + 1);
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
-		if (clip_ray(S, o, d, r0.w, r1.w, MODE != MODE_ANY, tmin, tmax, rcp)) return true;
+		// the closest-hit overload floors the epsilon scale at Epsilon, the shadow-ray and light-record overloads do not
+		if (clip_ray(S, o, d, r0.w, r1.w, MODE == MODE_CLOSEST || MODE == MODE_SURFACE, tmin, tmax, rcp)) return true;
 		write_miss(i);
 		return false;
 	}
@@ -49,6 +53,13 @@ struct BatchIO {
 			const float4 c = __ldg(S.tris + (size_t) hit.slot * 3 + 2);
 			const uint32_t prim = S.shapes[__float_as_uint(c.z)].primOffset + __float_as_uint(c.w);
 			__stcs((float4 *) out + i, make_float4(hit.t, hit.u, hit.v, __uint_as_float(prim)));
+		} else if (MODE == MODE_LIGHT) {
+			Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
+			// a mesh without texture coordinates reports uv = 0 here (skdtree.cpp:182-184), not the barycentrics of its.uv
+			const ShapeRec &sr = S.shapes[sf.shape];
+			const bool noUv = sr.type == SHAPE_MESH && !(sr.flags & SHAPE_HAS_UV);
+			((float4 *) out)[2 * i] = make_float4(hit.t, __uint_as_float(sf.shape), sf.ng.x, sf.ng.y);
+			((float4 *) out)[2 * i + 1] = make_float4(sf.ng.z, noUv ? 0.0f : sf.u, noUv ? 0.0f : sf.v, 0.0f);
 		} else {
 			mtsb_surface rec; memset(&rec, 0, sizeof(rec));
 			Surf sf; fill_surface(S, hit.slot, hit.t, hit.u, hit.v, o, d, sf);
@@ -76,7 +87,7 @@ trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, 
 }
 
 static size_t out_stride(int mode) {
-	return mode == MODE_ANY ? 1 : (mode == MODE_CLOSEST ? sizeof(mtsb_hit) : sizeof(mtsb_surface));
+	return mode == MODE_ANY ? 1 : (mode == MODE_CLOSEST ? sizeof(mtsb_hit) : (mode == MODE_LIGHT ? sizeof(mtsb_light_hit) : sizeof(mtsb_surface)));
 }
 
 // launches one persistent grid over n rays that already live on the device
@@ -100,6 +111,7 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 		else MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, false>, S, r, nn, dOut, dWork)); } while (0)
 	if (mode == MODE_CLOSEST) LAUNCH(MODE_CLOSEST);
 	else if (mode == MODE_ANY) LAUNCH(MODE_ANY);
+	else if (mode == MODE_LIGHT) LAUNCH(MODE_LIGHT);
 	else LAUNCH(MODE_SURFACE);
 	#undef LAUNCH
 	return 0;
@@ -227,6 +239,9 @@ int mtsb_trace_any(mtsb_scene *scene, const mtsb_ray *rays, size_t n, uint8_t *o
 }
 int mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_surface *out, int on_device) {
 	return trace_common(scene, MODE_SURFACE, rays, n, out, on_device, "mtsb_trace_surface");
+}
+int mtsb_trace_light(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_light_hit *out, int on_device) {
+	return trace_common(scene, MODE_LIGHT, rays, n, out, on_device, "mtsb_trace_light");
 }
 
 // counting variant: re-traces a device or host batch with node / primitive-test counters enabled

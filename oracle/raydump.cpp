@@ -183,6 +183,31 @@ public:
 		return 0;
 	}
 
+	/* ShapeKDTree::rayIntersect(ray, t, shape, n, uv) — the "light record" overload (src/librender/skdtree.cpp:144-204):
+	   8 floats per ray {t, shape index, n.xyz, uv.xy, 0}; t = +inf and shape = -1 on a miss */
+	int light(int argc, char **argv) {
+		if (argc < 5) { cout << "light <scene> <rays> <out>" << endl; return 1; }
+		load(argv[2]);
+		std::vector<float> rays = readFloats(argv[3]);
+		size_t n = rays.size() / 8;
+		std::vector<float> out(n * 8, 0.0f);
+		const ShapeKDTree *kd = m_kdtree.get();
+		for (size_t i = 0; i < n; ++i) {
+			const float *r = &rays[i*8];
+			float *o = &out[i*8];
+			Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7], 0.0f);
+			Float t; ConstShapePtr shape = NULL; Normal nrm(0.0f); Point2 uv(0.0f);
+			if (kd->rayIntersect(ray, t, shape, nrm, uv)) {
+				o[0] = t; o[1] = i2f(shapeIndex(shape));
+				o[2] = nrm.x; o[3] = nrm.y; o[4] = nrm.z; o[5] = uv.x; o[6] = uv.y;
+			} else {
+				o[0] = std::numeric_limits<float>::infinity(); o[1] = i2f(-1);
+			}
+		}
+		writeFloats(argv[4], out);
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -248,8 +273,9 @@ public:
 	}
 
 	int run(int argc, char **argv) {
-		if (argc < 2) { cout << "raydump trace|bsdf|emitter ..." << endl; return 1; }
+		if (argc < 2) { cout << "raydump trace|light|bsdf|emitter ..." << endl; return 1; }
 		if (!strcmp(argv[1], "trace")) return trace(argc, argv);
+		if (!strcmp(argv[1], "light")) return light(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

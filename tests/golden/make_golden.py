@@ -77,7 +77,37 @@ def cornell_case(td, n=1536):
     print("cornell:", rays.shape[0], "rays, hit rate", np.isfinite(out[:, 0]).mean(), "any rate", pack(out)["ref_any"].mean())
 
 
+def light_case(td):
+    """ShapeKDTree::rayIntersect(ray, t, shape, n, uv) (skdtree.cpp:144-204) on the ray sets of the two files above plus a
+    mesh WITH texture coordinates -> light.npz (raydump `light`: t, shape, n, uv)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers
+    res = {}
+    for kind in ("sphere", "cornell", "uvsphere"):
+        gold = np.load(os.path.join(ROOT, "tests", "golden", "hits_%s.npz" % ("sphere" if kind == "uvsphere" else kind)))
+        if kind == "uvsphere":
+            sd = helpers.uv_sphere_desc(S, gold)
+        else:
+            sd = helpers.desc_from_golden(S, gold, kind)
+        xml = sd.to_xml(td, "light_" + kind)
+        rays = gold["rays"]
+        rp, op = os.path.join(td, "rays.bin"), os.path.join(td, "out.bin")
+        np.ascontiguousarray(rays, np.float32).tofile(rp)
+        r = subprocess.run([os.path.join(REF, "mtsutil"), "raydump", "light", xml, rp, op], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0 or not os.path.exists(op):
+            raise RuntimeError(r.stdout[-3000:])
+        out = np.fromfile(op, np.float32).reshape(-1, 8)
+        res[kind] = out
+        print("light/%s: hit rate %.3f, mean |uv| %.3f" % (kind, np.isfinite(out[:, 0]).mean(), np.abs(out[:, 5:7]).mean()))
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "light.npz"), **res)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "light":
+        with tempfile.TemporaryDirectory() as td:
+            light_case(td)
+        sys.exit(0)
     with tempfile.TemporaryDirectory() as td:
         sphere_case(td)
         cornell_case(td)
+        light_case(td)

@@ -124,3 +124,14 @@ def desc_from_golden(S, gold, kind):
         sd.add_point_light((0, 5, 0), (1, 1, 1))
         return sd
     return S.cornell_box(64, 64, 1)
+
+
+def uv_sphere_desc(S, gold):
+    """The golden sphere mesh with spherical texture coordinates per vertex (for the light-record overload's uv)."""
+    V = gold["V"]
+    n = V / np.linalg.norm(V, axis=1, keepdims=True)
+    UV = np.stack([np.arctan2(n[:, 2], n[:, 0]) / (2 * np.pi) + 0.5, np.arccos(np.clip(n[:, 1], -1, 1)) / np.pi], axis=1).astype(np.float32)
+    sd = S.SceneDesc()
+    sd.add_mesh(V, gold["N"], gold["F"], UV=UV)
+    sd.add_point_light((0, 5, 0), (1, 1, 1))
+    return sd

@@ -54,6 +54,49 @@ def test_reference_cli_with_gpu_plugin(tmp_path):
     assert close.mean() >= 0.999, (float(close.mean()), float(np.abs(gpu_r - gpu_c * ratio).max()))
 
 
+def _si(text):
+    """'59.345 K' / '1.2 M' / '812' of Mitsuba's statistics printer -> float."""
+    parts = text.split()
+    return float(parts[0]) * {"K": 1e3, "M": 1e6, "G": 1e9}.get(parts[1] if len(parts) > 1 else "", 1.0)
+
+
+def test_ray_statistics_match_the_reference_counters(tmp_path):
+    """The reference's own StatsCounters — "Normal rays traced", "Shadow rays traced" (src/librender/skdtree.cpp:46-47,
+    118,209) and "Average path length" (src/integrators/path/path.cpp:24,290-291) — against the counters the wavefront
+    keeps, same scene, same random numbers (ctr sampler): the two renderers trace the same number of rays."""
+    import re
+    d = dict(sampler="ctr", spp=16, res=128, rfilter="box")
+    _, log_ref = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, d)
+    _, log_gpu = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d)
+    normal = _si(re.search(r"Normal rays traced : ([0-9.]+(?: [KMG])?)", log_ref).group(1))
+    shadow = _si(re.search(r"Shadow rays traced : ([0-9.]+(?: [KMG])?)", log_ref).group(1))
+    m = re.search(r"Average path length : ([0-9.]+) \(([0-9.]+(?: [KMG])?) / ([0-9.]+(?: [KMG])?)\)", log_ref)
+    avg, depth_sum, paths = float(m.group(1)), _si(m.group(2)), _si(m.group(3))
+    g = re.search(r"gpupath: (\d+) paths, (\d+) closest-hit \+ (\d+) shadow rays, average path length ([0-9.]+)", log_gpu)
+    assert g, log_gpu[-1500:]
+    gp, gn, gs, gavg = int(g.group(1)), int(g.group(2)), int(g.group(3)), float(g.group(4))
+    print("reference: %g normal, %g shadow rays, %g paths, avg length %.2f | gpu: %d, %d, %d, %.2f" % (normal, shadow, paths, avg, gn, gs, gp, gavg))
+    assert gp == 128 * 128 * 16 and abs(paths - gp) <= 0.001 * gp          # the printer keeps 3-5 significant digits
+    assert abs(gn - normal) <= 0.005 * normal and abs(gs - shadow) <= 0.005 * shadow
+    assert abs(gavg - avg) <= 0.011 and abs(depth_sum / paths - gavg) <= 0.01
+
+
+def test_direct_integrator_with_shading_samples_through_the_loader(tmp_path):
+    """`direct` with shadingSamples = 4 (the setting the reference's documentation recommends raising, direct.cpp:95-107)
+    through the unmodified CLI: overlay direct.so vs the stock plugin, same samples (ctr arrays), per pixel."""
+    xml = open(XML).read().replace('<integrator type="path"><integer name="maxDepth" value="5"/></integrator>',
+                                   '<integrator type="direct"><integer name="shadingSamples" value="4"/></integrator>')
+    path = str(tmp_path / "cbox_direct.xml")
+    open(path, "w").write(xml)
+    d = dict(sampler="ctr", spp=4, res=64, rfilter="box")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, d, xml=path)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d, xml=path)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.97, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
 def test_thinlens_conductor_roughdielectric_through_the_loader(tmp_path):
     """plugin/extract.h for the SURVEY 8f item-2 plugins: `thinlens`, `conductor` (measured gold from data/ior) and
     `roughdielectric` instantiated by the stock XML loader; same samples (ctr), classic scheduler, per-pixel match."""
