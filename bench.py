@@ -310,6 +310,33 @@ def main():
         e2e_ms = float(tt.item())
     assert np.array_equal(pin_h.array.view(np.uint32).reshape(-1, 4), hits_h.view(np.uint32)), "host-path hits differ from device-path hits"
     e2e_value = world * n / e2e_ms / 1e3
+    # the ceiling the host-buffer path runs against, measured in the same processes: the step's H2D (rays) and D2H (hits)
+    # alone, concurrently on two streams, all ranks at once — no kernel.  With N ranks this is the N-process aggregate
+    # of the box's host memory system / PCIe root, which is what stops e2e from scaling.
+    t_in = torch.from_numpy(pin_r.array.view(np.uint8).reshape(-1))
+    t_out = torch.from_numpy(pin_h.array.view(np.uint8).reshape(-1))
+    d_in = torch.empty(t_in.shape[0], dtype=torch.uint8, device="cuda")
+    d_out = torch.empty(t_out.shape[0], dtype=torch.uint8, device="cuda")
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    copy_ms = []
+    for _ in range(4):
+        barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(s_in):
+            d_in.copy_(t_in, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            t_out.copy_(d_out, non_blocking=True)
+        s_in.synchronize()
+        s_out.synchronize()
+        copy_ms.append((time.perf_counter() - t0) * 1e3)
+    copy_ms = min(copy_ms[1:])
+    if world > 1:
+        tt = torch.tensor([copy_ms], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        copy_ms = float(tt.item())
+    copy_ceiling = world * n / copy_ms / 1e3
+    sc.ray_intersect(pin_r.array, out=pin_h.array)      # the copy test overwrote the pinned hit buffer
+    del d_in, d_out
 
     # --- other ray sets of config 2 (detail only) ---
     detail = {}
@@ -361,6 +388,7 @@ def main():
             detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5) + (() if args.no_plugin or world > 1 else ("plugin",)), cpu=not args.no_cpu_baseline and world == 1)
 
     # --- config 4: 3840x2160, 1024 spp split by sample index over the ranks (strong scaling), one NCCL film reduce ---
+    c4s = None
     if not args.no_path and not args.no_config4:
         import bench_render
         comm = None
@@ -382,6 +410,7 @@ def main():
                       mrays_per_s=float(ss[1].item()) / (total_ms * 1e-3) / 1e6, launches_all_ranks=int(ss[2].item()), scaling="strong",
                       split="sample index s mod %d, scene replicated, ncclReduce(sum) of the %d-byte film into rank 0" % (world, c4["film_bytes"]))
             detail.setdefault("path", {})["config4_3840x2160_%dspp_%dgpu" % (args.spp4, world)] = c4
+            c4s = c4
         if comm is not None:
             comm.close()
 
@@ -422,7 +451,9 @@ def main():
                        "parallelism": "rays sharded across %d GPU(s), scene replicated, no collective" % world},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
-                    "ms_per_step": e2e_ms, "api": "mtsb_trace_closest(host pointers), pinned buffers, 2M-ray chunks pipelined over 3 streams and a 4-buffer ring"},
+                    "ms_per_step": e2e_ms, "api": "mtsb_trace_closest(host pointers), pinned buffers, 2M-ray chunks pipelined over 3 streams and a 4-buffer ring",
+                    "copy_only_ceiling": copy_ceiling, "copy_only_ms": copy_ms, "frac_of_copy_ceiling": e2e_value / copy_ceiling,
+                    "limiter": "host<->device copies: the same bytes moved with no kernel at all, by the same %d process(es) at once, run at copy_only_ceiling" % world},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>", "kernel_ms": kern_ms,
@@ -430,6 +461,9 @@ def main():
                          "traversal_bytes_per_ray": nodes_per_ray * 80 + prims_per_ray * 48 + 48, "issue": issue},
             "cpu_baseline": cpu,
             "parity": cpu.pop("parity", None) if cpu else None,
+            # the multi-GPU result that has a collective in it (strong scaling of config 4, one ncclReduce of the film)
+            "config4": {k: c4s.get(k) for k in ("samples_per_s", "total_ms_max_over_ranks", "render_ms_max_over_ranks", "reduce_ms_max_over_ranks",
+                                               "film_bytes", "spp", "width", "height", "scaling", "split")} if c4s else None,
             "detail": dict(detail, hit_rate=hit_rate, build=bstats),
         }
         emit(line)

@@ -120,12 +120,26 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		toRGB(props.getSpectrum("eta", intEta) / extEta, d.p + 0);
 		toRGB(props.getSpectrum("k", intK) / extEta, d.p + 3);
 		toRGB(props.getSpectrum("specularReflectance", Spectrum(1.0f)), d.p + 6);
-	} else if (cls == "TwoSidedBRDF") {                             // src/bsdfs/twosided.cpp — nested diffuse only
+	} else if (cls == "TwoSidedBRDF") {                             // src/bsdfs/twosided.cpp:67-186 around any BRDF of the subset
+		// The adapter keeps its children in `protected: ref<BSDF> m_nestedBRDF[2]` (twosided.cpp:232), its only data members,
+		// and offers no accessor; the class lives in a .cpp, so it cannot be subclassed either.  Its object is therefore read
+		// through a layout mirror — BSDF base, then two pointers — compiled with the reference's own headers and flags
+		// (plugin/Makefile).  What comes out is checked three ways: both must be BSDFs by RTTI, must be named in toString(),
+		// and selfCheckBSDF() compares the resulting device BSDF with TwoSidedBRDF::eval/pdf at load.
+		struct Mirror { char base[sizeof(BSDF)]; const BSDF *nested[2]; };
+		const Mirror *mir = reinterpret_cast<const Mirror *>(static_cast<const BSDF *>(bsdf));
+		const BSDF *n0 = mir->nested[0], *n1 = mir->nested[1];
 		const std::string desc = bsdf->toString();
-		if (desc.find("nestedBRDF[0] = SmoothDiffuse[") == std::string::npos || desc.find("nestedBRDF[1] = SmoothDiffuse[") == std::string::npos)
-			SLog(EError, "gpupath: twosided is supported around `diffuse` only — got %s", desc.c_str());
-		d.type = MTSB_BSDF_DIFFUSE | MTSB_BSDF_TWOSIDED_FLAG;
-		toRGB(bsdf->getDiffuseReflectance(its), d.p);
+		if (!n0 || !n1 || !n0->getClass()->derivesFrom(MTS_CLASS(BSDF)) || !n1->getClass()->derivesFrom(MTS_CLASS(BSDF))
+				|| desc.find("nestedBRDF[0] = " + n0->getClass()->getName().substr(0, 6)) == std::string::npos)
+			SLog(EError, "gpupath: cannot read the nested BRDFs of %s", desc.c_str());
+		mtsb_bsdf_desc d1;
+		if (!describeBSDF(n0, d) || !describeBSDF(n1, d1))
+			SLog(EError, "gpupath: twosided around a BRDF outside the GPU subset: %s", desc.c_str());
+		if (memcmp(&d, &d1, sizeof(d)) != 0)
+			SLog(EError, "gpupath: twosided with two DIFFERENT nested BRDFs is outside the GPU subset: %s", desc.c_str());
+		if (d.type & MTSB_BSDF_TWOSIDED_FLAG) SLog(EError, "gpupath: nested twosided adapters are not supported");
+		d.type |= MTSB_BSDF_TWOSIDED_FLAG;
 	} else {
 		return false;
 	}

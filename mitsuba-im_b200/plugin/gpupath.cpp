@@ -147,6 +147,16 @@ public:
 		// path state, kernels and the bounce graph are set up before the clock starts (the reference's kd-tree build and
 		// its preprocess() are outside its render timer too)
 		for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_reserve(renders[g], pass));
+		// so is the NCCL communicator of the film reduce (about a second of bootstrap, once per integrator)
+		if (m_gpus > 1 && m_comms.empty()) {
+			std::vector<mtsb_ctx *> ctxs(m_gpus);
+			for (int g = 0; g < m_gpus; ++g) ctxs[g] = m_devices[g].ctx;
+			m_comms.assign(m_gpus, (mtsb_comm *) NULL);
+			MTSB_CALL(mtsb_comm_create_all(ctxs.data(), m_gpus, m_comms.data()));
+			// first collective on a fresh communicator sets up its channels: run it on the still empty films
+			MTSB_CALL(mtsb_film_reduce_all(renders.data(), m_comms.data(), m_gpus, 0));
+			for (int g = 0; g < m_gpus; ++g) MTSB_CALL(mtsb_render_sync(renders[g]));
+		}
 		ref<Timer> timer = new Timer();
 		// GPU g renders sample indices s = g (mod gpus).  mtsb_render_pass only QUEUES work (no host wait inside), so this one
 		// thread keeps all devices busy: pass k goes to every GPU before anything is waited for.  A pass covers about one
@@ -169,15 +179,7 @@ public:
 		const size_t n = (size_t) block->getBitmap()->getSize().x * block->getBitmap()->getSize().y * block->getChannelCount();
 		uint64_t st[8] = { 0 }, tot[8] = { 0 };
 		// the per-GPU films meet on the device: one NCCL reduce into GPU 0's film, then a single D2H into the ImageBlock
-		if (m_gpus > 1) {
-			if (m_comms.empty()) {
-				std::vector<mtsb_ctx *> ctxs(m_gpus);
-				for (int g = 0; g < m_gpus; ++g) ctxs[g] = m_devices[g].ctx;
-				m_comms.assign(m_gpus, (mtsb_comm *) NULL);
-				MTSB_CALL(mtsb_comm_create_all(ctxs.data(), m_gpus, m_comms.data()));
-			}
-			MTSB_CALL(mtsb_film_reduce_all(renders.data(), m_comms.data(), m_gpus, 0));
-		}
+		if (m_gpus > 1) MTSB_CALL(mtsb_film_reduce_all(renders.data(), m_comms.data(), m_gpus, 0));
 		MTSB_CALL(mtsb_film_to_host(renders[0], dst, n, 0));
 		// the clock stops with the film in host memory; what follows is the reference's own CPU code (Film::put, develop)
 		const double s = timer->getMicroseconds() * 1e-6;

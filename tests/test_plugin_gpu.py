@@ -109,6 +109,27 @@ def test_thinlens_conductor_roughdielectric_through_the_loader(tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_twosided_around_plastic_and_roughconductor(tmp_path):
+    """`twosided` around BRDFs other than diffuse (src/bsdfs/twosided.cpp:67-186): the plugin reads the nested BRDF out of
+    the adapter (plugin/extract.h) — cube in two-sided plastic, back wall in two-sided GGX copper, seen from both sides by
+    the bounced light — per-pixel match with the stock plugins under the shared sampler."""
+    xml = open(XML).read()
+    cube = '<shape type="cube"><transform name="toWorld"><scale value="0.3"/><rotate y="1" angle="20"/><translate x="0.3" y="0.3" z="0.2"/></transform><bsdf type="diffuse"/></shape>'
+    wall = '<shape type="rectangle"><transform name="toWorld"><translate y="1" z="-1"/></transform><bsdf type="diffuse"/></shape>'
+    assert cube in xml and wall in xml
+    xml = xml.replace(cube, cube.replace('<bsdf type="diffuse"/>', '<bsdf type="twosided"><bsdf type="plastic"><rgb name="diffuseReflectance" value=".2 .3 .6"/></bsdf></bsdf>'))
+    xml = xml.replace(wall, wall.replace('<bsdf type="diffuse"/>', '<bsdf type="twosided"><bsdf type="roughconductor"><string name="distribution" value="ggx"/><float name="alpha" value="0.2"/></bsdf></bsdf>'))
+    path = str(tmp_path / "cbox_twosided.xml")
+    open(path, "w").write(xml)
+    d = dict(sampler="ctr", spp=8, res=64, rfilter="box")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, d, xml=path)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, d, xml=path)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
 def test_crop_window(tmp_path):
     """Film crop window (hdrfilm cropOffsetX/Y, cropWidth/Height): the sensor's sample-to-camera matrix and the
     ImageBlock size follow the crop (src/sensors/perspective.cpp:126-180, src/librender/film.cpp), per-pixel match."""
