@@ -124,15 +124,13 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		// The adapter keeps its children in `protected: ref<BSDF> m_nestedBRDF[2]` (twosided.cpp:232), its only data members,
 		// and offers no accessor; the class lives in a .cpp, so it cannot be subclassed either.  Its object is therefore read
 		// through a layout mirror — BSDF base, then two pointers — compiled with the reference's own headers and flags
-		// (plugin/Makefile).  What comes out is checked three ways: both must be BSDFs by RTTI, must be named in toString(),
-		// and selfCheckBSDF() compares the resulting device BSDF with TwoSidedBRDF::eval/pdf at load.
+		// (plugin/Makefile).  What comes out is checked twice: both must be BSDFs by RTTI, and selfCheckBSDF() compares the resulting device BSDF with TwoSidedBRDF::eval/pdf at load.
 		struct Mirror { char base[sizeof(BSDF)]; const BSDF *nested[2]; };
 		const Mirror *mir = reinterpret_cast<const Mirror *>(static_cast<const BSDF *>(bsdf));
 		const BSDF *n0 = mir->nested[0], *n1 = mir->nested[1];
 		const std::string desc = bsdf->toString();
-		if (!n0 || !n1 || !n0->getClass()->derivesFrom(MTS_CLASS(BSDF)) || !n1->getClass()->derivesFrom(MTS_CLASS(BSDF))
-				|| desc.find("nestedBRDF[0] = " + n0->getClass()->getName().substr(0, 6)) == std::string::npos)
-			SLog(EError, "gpupath: cannot read the nested BRDFs of %s", desc.c_str());
+		if (!n0 || !n1 || !n0->getClass()->derivesFrom(MTS_CLASS(BSDF)) || !n1->getClass()->derivesFrom(MTS_CLASS(BSDF)))
+			SLog(EError, "gpupath: cannot read the nested BRDFs of %s", desc.substr(0, 200).c_str());
 		mtsb_bsdf_desc d1;
 		if (!describeBSDF(n0, d) || !describeBSDF(n1, d1))
 			SLog(EError, "gpupath: twosided around a BRDF outside the GPU subset: %s", desc.c_str());

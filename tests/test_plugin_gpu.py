@@ -28,8 +28,8 @@ def run_mitsuba(out, classic, overlay, defines, threads=4, xml=XML):
     for k, v in defines.items():
         cmd += ["-D", "%s=%s" % (k, v)]
     cmd += ["-o", out, xml]
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
-    assert r.returncode == 0, r.stdout[-3000:]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, errors="replace", timeout=900)
+    assert r.returncode == 0 and os.path.exists(out), r.stdout[-3000:]
     return O.read_pfm(out), r.stdout
 
 
