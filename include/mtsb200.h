@@ -191,6 +191,12 @@ MTSB_API int  mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, con
 /* Analytic rectangle (src/shapes/rectangle.cpp): object-to-world 4x4 row-major, flipNormals. */
 MTSB_API int  mtsb_scene_add_rectangle(mtsb_scene *scene, const float object_to_world[16],
                                        int flip_normals, int bsdf, int emitter);
+/* Analytic `disk` (src/shapes/disk.cpp: unit disk in the object-space xy plane, to_world without shear / non-uniform scale)
+ * and `sphere` (src/shapes/sphere.cpp: object_to_world = m_objectToWorld with the scale removed as the constructor does,
+ * :113-121; the quadratic is solved in double precision like the reference's).  Leaf primitives of the BVH like the
+ * rectangle; as area emitters they are outside the GPU subset (MTSB_EUNSUPPORTED). */
+MTSB_API int  mtsb_scene_add_disk(mtsb_scene *scene, const float to_world[16], int flip_normals, int bsdf, int emitter);
+MTSB_API int  mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], float radius, int flip_normals, int bsdf, int emitter);
 /* Builds TriAccel records, the BVH and the emitter tables on the device. */
 MTSB_API int  mtsb_scene_commit(mtsb_scene *scene, int builder);
 /* Scene AABB as ShapeKDTree::getAABB() returns it (enlarged, include/mitsuba/render/gkdtree.h:1217-1220). */

@@ -63,6 +63,13 @@ __global__ void prim_bounds_kernel(SceneDev S, uint32_t primCount, float4 *lo, f
 		if (sh.type == SHAPE_MESH) {
 			V3 A, B, C; load_tri(S, sh, i - sh.primOffset, A, B, C);
 			mn = vmin3(A, vmin3(B, C)); mx = vmax3(A, vmax3(B, C));
+		} else if (sh.type == SHAPE_SPHERE) {                // Sphere::getAABB, src/shapes/sphere.cpp:147-152
+			const RectRec &r = S.rects[sh.rect];
+			mn = r.dpdu - v3(r.dpdv.x); mx = r.dpdu + v3(r.dpdv.x);
+		} else if (sh.type == SHAPE_DISK) {                  // Disk::getAABB, src/shapes/disk.cpp:117-130
+			const float *m = S.rects[sh.rect].toWorld;
+			V3 c0 = xform_point(m, 1, 0, 0), c1 = xform_point(m, -1, 0, 0), c2 = xform_point(m, 0, 1, 0), c3 = xform_point(m, 0, -1, 0);
+			mn = vmin3(vmin3(c0, c1), vmin3(c2, c3)); mx = vmax3(vmax3(c0, c1), vmax3(c2, c3));
 		} else {
 			const float *m = S.rects[sh.rect].toWorld;   // Rectangle::getAABB, src/shapes/rectangle.cpp:111-118
 			V3 c0 = xform_point(m, -1, -1, 0), c1 = xform_point(m, 1, -1, 0), c2 = xform_point(m, 1, 1, 0), c3 = xform_point(m, -1, 1, 0);

@@ -54,7 +54,7 @@ __host__ __device__ inline V3 vmax3(V3 a, V3 b) { return v3(fmaxf(a.x,b.x), fmax
 
 // ----------------------------------------------------------------------------- device scene layout (HBM)
 // Per-shape record; shape order = Scene::getShapes() order = ShapeKDTree::addShape order.
-enum { SHAPE_MESH = 0, SHAPE_RECT = 1 };
+enum { SHAPE_MESH = 0, SHAPE_RECT = 1, SHAPE_DISK = 2, SHAPE_SPHERE = 3 };
 struct ShapeRec {
 	uint32_t type;
 	uint32_t primOffset;   // global primitive index of first primitive (m_shapeMap prefix)
@@ -70,7 +70,9 @@ struct ShapeRec {
 };
 enum { SHAPE_HAS_NORMALS = 1, SHAPE_HAS_UV = 2 };
 
-// Analytic rectangle (src/shapes/rectangle.cpp): both transforms + the precomputed frame.
+// Analytic shapes share one record.  Rectangle (src/shapes/rectangle.cpp) and disk (src/shapes/disk.cpp): both transforms +
+// the precomputed frame.  Sphere (src/shapes/sphere.cpp): toWorld / toObject = m_objectToWorld / m_worldToObject (scale
+// removed, sphere.cpp:113-121), dpdu = m_center, dpdv.x = m_radius, pad[0] = flipNormals.
 struct RectRec {
 	float toWorld[12];     // 3x4 affine object->world
 	float toObject[12];    // 3x4 affine world->object

@@ -224,6 +224,59 @@ int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_norm
 	return (int) scene->shapes.size() - 1;
 }
 
+int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, int bsdf, int emitter) {
+	if (!scene || !m) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_disk"));
+	if (emitter >= 0) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_disk: area emitters on analytic disks are outside the GPU subset");
+	float ow[16]; memcpy(ow, m, sizeof(ow));
+	if (flip_normals)   // m_objectToWorld->prependScale(Vector(1, 1, -1))  (disk.cpp:86-87)
+		for (int r = 0; r < 4; ++r) ow[r*4+2] = -ow[r*4+2];
+	RectRec rr; memset(&rr, 0, sizeof(rr));
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) rr.toWorld[r*4+c] = ow[r*4+c];
+	invert_affine(ow, rr.toObject);
+	rr.dpdu = v3(ow[0], ow[4], ow[8]);
+	rr.dpdv = v3(ow[1], ow[5], ow[9]);
+	V3 n = v3(rr.toObject[8], rr.toObject[9], rr.toObject[10]);      // trafo(Normal(0,0,1)): inverse transpose
+	float len = sqrtf(n.x*n.x + n.y*n.y + n.z*n.z);
+	rr.n = v3(n.x/len, n.y/len, n.z/len);
+	const float lu = sqrtf(dot(rr.dpdu, rr.dpdu)), lv = sqrtf(dot(rr.dpdv, rr.dpdv));
+	if (fabsf(dot(rr.dpdu, rr.dpdv) / (lu * lv)) > 1e-3f) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: 'toWorld' transformation contains shear!");           // disk.cpp:108-109
+	if (fabsf(lu / lv - 1) > 1e-3f) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: 'toWorld' transformation contains a non-uniform scale!");                  // disk.cpp:111-112
+	rr.invSurfaceArea = 1.0f / (3.14159265358979323846f * lu * lu);
+	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	sh.type = SHAPE_DISK; sh.primOffset = scene->primCount; sh.primCount = 1;
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.invArea = rr.invSurfaceArea;
+	scene->rects.push_back(rr);
+	scene->shapes.push_back(sh);
+	scene->primCount += 1;
+	scene->shapeOffsets.push_back(scene->primCount);
+	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], float radius, int flip_normals, int bsdf, int emitter) {
+	if (!scene || !object_to_world) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_sphere: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_sphere"));
+	if (emitter >= 0) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_sphere: area emitters on analytic spheres are outside the GPU subset");
+	if (!(radius > 0)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_sphere: cannot create spheres of radius <= 0");                                                  // sphere.cpp:130-131
+	RectRec rr; memset(&rr, 0, sizeof(rr));
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) rr.toWorld[r*4+c] = object_to_world[r*4+c];
+	invert_affine(object_to_world, rr.toObject);
+	rr.dpdu = v3(object_to_world[3], object_to_world[7], object_to_world[11]);     // m_center = m_objectToWorld(Point(0,0,0))
+	rr.dpdv = v3(radius, 0.0f, 0.0f);
+	rr.pad[0] = flip_normals ? 1u : 0u;
+	rr.invSurfaceArea = 1.0f / (4 * 3.14159265358979323846f * radius * radius);
+	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	sh.type = SHAPE_SPHERE; sh.primOffset = scene->primCount; sh.primCount = 1;
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.invArea = rr.invSurfaceArea;
+	scene->rects.push_back(rr);
+	scene->shapes.push_back(sh);
+	scene->primCount += 1;
+	scene->shapeOffsets.push_back(scene->primCount);
+	return (int) scene->shapes.size() - 1;
+}
+
 int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: NULL scene");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: already committed");

@@ -69,6 +69,34 @@ __device__ inline void fill_surface(const SceneDev &S, uint32_t slot, float t, f
 			out.ns = faceNormal;
 		}
 		out.ng = faceNormal;
+	} else if (sh.type == SHAPE_SPHERE) {                   // Sphere::fillIntersectionRecord, src/shapes/sphere.cpp:205-252
+		const RectRec &r = S.rects[sh.rect];
+		const V3 center = r.dpdu; const float radius = r.dpdv.x;
+		out.p = center + normalize((o + d * t) - center) * radius;         // re-projection (SINGLE_PRECISION branch)
+		const V3 rel = out.p - center;
+		const float *m = r.toObject;
+		const V3 local = v3(m[0]*rel.x + m[1]*rel.y + m[2]*rel.z, m[4]*rel.x + m[5]*rel.y + m[6]*rel.z, m[8]*rel.x + m[9]*rel.y + m[10]*rel.z);
+		const float theta = acosf(fminf(1.0f, fmaxf(-1.0f, local.z / radius)));   // math::safe_acos
+		float phi = atan2f(local.y, local.x);
+		if (phi < 0) phi += 2 * 3.14159265358979323846f;
+		out.u = phi * (0.5f * 0.31830988618379067154f); out.v = theta * 0.31830988618379067154f;
+		const float *w = r.toWorld;
+		const V3 lu = v3(-local.y, local.x, 0.0f) * (2 * 3.14159265358979323846f);
+		dpdu = v3(w[0]*lu.x + w[1]*lu.y + w[2]*lu.z, w[4]*lu.x + w[5]*lu.y + w[6]*lu.z, w[8]*lu.x + w[9]*lu.y + w[10]*lu.z);
+		out.ng = normalize(out.p - center);
+		if (r.pad[0]) out.ng = -out.ng;                                     // m_flipNormals
+		out.ns = out.ng;
+	} else if (sh.type == SHAPE_DISK) {                     // Disk::fillIntersectionRecord, src/shapes/disk.cpp:168-197
+		const RectRec &r = S.rects[sh.rect];
+		const float rr = sqrtf(bu * bu + bv * bv), invR = rr == 0 ? 0.0f : 1.0f / rr;
+		float phi = atan2f(bv, bu);
+		if (phi < 0) phi += 2 * 3.14159265358979323846f;
+		const float *w = r.toWorld;
+		const V3 lu = rr != 0 ? v3(bu * invR, bv * invR, 0.0f) : v3(1.0f, 0.0f, 0.0f);
+		dpdu = v3(w[0]*lu.x + w[1]*lu.y, w[4]*lu.x + w[5]*lu.y, w[8]*lu.x + w[9]*lu.y);
+		out.ns = r.n; out.ng = r.n;           // the reference leaves geoFrame unset here; the shading normal is the sensible stand-in
+		out.u = rr; out.v = phi * (0.5f * 0.31830988618379067154f);
+		out.p = o + d * t;
 	} else {
 		const RectRec &r = S.rects[sh.rect];
 		out.ng = r.n; out.ns = r.n;

@@ -72,6 +72,73 @@ __device__ __forceinline__ bool rect_test(const RectRec &r, const V3 &o, const V
 	return false;
 }
 
+// Disk::rayIntersect (src/shapes/disk.cpp:139-165): object-space plane z = 0, x^2 + y^2 <= 1; u, v = the local x, y.
+__device__ __forceinline__ bool disk_test(const RectRec &r, const V3 &o, const V3 &d,
+		float mint, float maxt, float &t, float &u, float &v) {
+	const float *m = r.toObject;
+	float ox = m[0]*o.x + m[1]*o.y + m[2]*o.z + m[3];
+	float oy = m[4]*o.x + m[5]*o.y + m[6]*o.z + m[7];
+	float oz = m[8]*o.x + m[9]*o.y + m[10]*o.z + m[11];
+	float dx = m[0]*d.x + m[1]*d.y + m[2]*d.z;
+	float dy = m[4]*d.x + m[5]*d.y + m[6]*d.z;
+	float dz = m[8]*d.x + m[9]*d.y + m[10]*d.z;
+	float hit = -oz / dz;
+	if (!(hit >= mint && hit <= maxt)) return false;
+	float lx = ox + dx * hit, ly = oy + dy * hit;
+	if (lx * lx + ly * ly <= 1) { t = hit; u = lx; v = ly; return true; }
+	return false;
+}
+
+// Sphere::rayIntersect (src/shapes/sphere.cpp:158-183) with solveQuadraticDouble (src/libcore/util.cpp:489-527): the
+// reference solves the quadratic in double precision, so does this (B200 has full-rate-enough FP64 for one leaf test).
+__device__ __forceinline__ bool sphere_test(const RectRec &r, const V3 &o, const V3 &d,
+		float mint, float maxt, float &t, float &u, float &v) {
+	const double ox = (double) o.x - (double) r.dpdu.x, oy = (double) o.y - (double) r.dpdu.y, oz = (double) o.z - (double) r.dpdu.z;
+	const double dx = d.x, dy = d.y, dz = d.z, rad = r.dpdv.x;
+	const double A = dx*dx + dy*dy + dz*dz, B = 2 * (ox*dx + oy*dy + oz*dz), C = ox*ox + oy*oy + oz*oz - rad * rad;
+	double nearT, farT;
+	if (A == 0) {
+		if (B == 0) return false;
+		nearT = farT = -C / B;
+	} else {
+		const double discrim = B*B - 4.0 * A * C;
+		if (discrim < 0) return false;
+		const double sq = sqrt(discrim);
+		const double temp = B < 0 ? -0.5 * (B - sq) : -0.5 * (B + sq);
+		nearT = temp / A; farT = C / temp;
+		if (nearT > farT) { const double tmp = nearT; nearT = farT; farT = tmp; }
+	}
+	if (!(nearT <= (double) maxt && farT >= (double) mint)) return false;
+	if (nearT < (double) mint) {
+		if (farT > (double) maxt) return false;
+		t = (float) farT;
+	} else t = (float) nearT;
+	u = 0; v = 0;
+	return true;
+}
+
+// disk and sphere behind a real call: their registers (FP64 quadratic) must not weigh on the traversal loop
+static __device__ __noinline__ bool disk_or_sphere_test(const RectRec *r, uint32_t type, float ox, float oy, float oz, float dx, float dy, float dz,
+		float mint, float maxt, float *tuv) {
+	const V3 o = v3(ox, oy, oz), d = v3(dx, dy, dz);
+	float t, u, v;
+	const bool h = type == SHAPE_DISK ? disk_test(*r, o, d, mint, maxt, t, u, v) : sphere_test(*r, o, d, mint, maxt, t, u, v);
+	if (h) { tuv[0] = t; tuv[1] = u; tuv[2] = v; }
+	return h;
+}
+
+// leaf test of a non-triangle slot: the shape's own rayIntersect
+__device__ __forceinline__ bool analytic_test(const SceneDev &S, uint32_t shapeIdx, const V3 &o, const V3 &d,
+		float mint, float maxt, float &t, float &u, float &v) {
+	const ShapeRec &sh = S.shapes[shapeIdx];
+	const RectRec &r = S.rects[sh.rect];
+	if (sh.type == SHAPE_RECT) return rect_test(r, o, d, mint, maxt, t, u, v);
+	float tuv[3];
+	const bool h = disk_or_sphere_test(&r, sh.type, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, tuv);
+	if (h) { t = tuv[0]; u = tuv[1]; v = tuv[2]; }
+	return h;
+}
+
 // Byte j of `word` placed in bits 8..15 of the mantissa of 1.0f: 1 + q * 2^-15, exact, ONE PRMT and no arithmetic.
 // The slab distance q * step * idir + (p - o) * idir is then a single FMA with the 2^15 folded into the scale and
 // the "1 +" folded into the offset (node_test).  `one` = 0x3F800000 comes from the kernel parameter bank: PRMT has a single immediate slot, and with both the
@@ -256,7 +323,7 @@ struct Trav {
 				if (__float_as_uint(a.x) != K_NO_TRIANGLE)
 					h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
 				else
-					h = rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
+					h = analytic_test(S, __float_as_uint(c.z), o, d, tmin, hit.t, t, u, v);
 				if (h) {
 					hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
 					if (ANY) { tg.y = 0; ng = make_uint2(0u, 0u); st.n = 0; }

@@ -70,8 +70,24 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 			const Properties &props = shape->getProperties();
 			float m[16]; matrixToArray(props.getTransform("toWorld", Transform()).getMatrix(), m);
 			rc = mtsb_scene_add_rectangle(out, m, props.getBoolean("flipNormals", false) ? 1 : 0, bid, eid);
+		} else if (shape->getClass()->getName() == "Disk") {        // src/shapes/disk.cpp:83-88
+			const Properties &props = shape->getProperties();
+			float m[16]; matrixToArray(props.getTransform("toWorld", Transform()).getMatrix(), m);
+			rc = mtsb_scene_add_disk(out, m, props.getBoolean("flipNormals", false) ? 1 : 0, bid, eid);
+		} else if (shape->getClass()->getName() == "Sphere") {      // src/shapes/sphere.cpp:108-131
+			const Properties &props = shape->getProperties();
+			Transform objectToWorld = Transform::translate(Vector(props.getPoint("center", Point(0.0f))));
+			Float radius = props.getFloat("radius", 1.0f);
+			if (props.hasProperty("toWorld")) {
+				const Transform toWorld = props.getTransform("toWorld");
+				const Float scale = toWorld(Vector(1, 0, 0)).length();
+				objectToWorld = toWorld * Transform::scale(Vector(1 / scale)) * objectToWorld;     // the scale moves into the radius
+				radius *= scale;
+			}
+			float m[16]; matrixToArray(objectToWorld.getMatrix(), m);
+			rc = mtsb_scene_add_sphere(out, m, (float) radius, props.getBoolean("flipNormals", false) ? 1 : 0, bid, eid);
 		} else {
-			SLog(EError, "gpupath: shape \"%s\" is outside the GPU subset (triangle meshes, rectangle)", shape->getClass()->getName().c_str());
+			SLog(EError, "gpupath: shape \"%s\" is outside the GPU subset (triangle meshes, rectangle, disk, sphere)", shape->getClass()->getName().c_str());
 			rc = -1;
 		}
 		if (rc < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());

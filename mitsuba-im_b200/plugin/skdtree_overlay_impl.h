@@ -33,8 +33,30 @@ Overlay *buildOverlay(const std::vector<const Shape *> &shapes) {
 			for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m[r * 4 + c] = (float) mtx(r, c);
 			rc = mtsb_scene_add_rectangle(ov->scene, m, props.getBoolean("flipNormals", false) ? 1 : 0, bid, -1);
 			prims += 1;
+		} else if (shape->getClass()->getName() == "Disk") {        // src/shapes/disk.cpp:83-88
+			const Properties &props = shape->getProperties();
+			const Matrix4x4 &mtx = props.getTransform("toWorld", Transform()).getMatrix();
+			float m[16];
+			for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m[r * 4 + c] = (float) mtx(r, c);
+			rc = mtsb_scene_add_disk(ov->scene, m, props.getBoolean("flipNormals", false) ? 1 : 0, bid, -1);
+			prims += 1;
+		} else if (shape->getClass()->getName() == "Sphere") {      // src/shapes/sphere.cpp:108-131
+			const Properties &props = shape->getProperties();
+			Transform objectToWorld = Transform::translate(Vector(props.getPoint("center", Point(0.0f))));
+			Float radius = props.getFloat("radius", 1.0f);
+			if (props.hasProperty("toWorld")) {
+				const Transform toWorld = props.getTransform("toWorld");
+				const Float scale = toWorld(Vector(1, 0, 0)).length();
+				objectToWorld = toWorld * Transform::scale(Vector(1 / scale)) * objectToWorld;
+				radius *= scale;
+			}
+			const Matrix4x4 &mtx = objectToWorld.getMatrix();
+			float m[16];
+			for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m[r * 4 + c] = (float) mtx(r, c);
+			rc = mtsb_scene_add_sphere(ov->scene, m, (float) radius, props.getBoolean("flipNormals", false) ? 1 : 0, bid, -1);
+			prims += 1;
 		} else {
-			SLog(EError, "mtsb overlay: shape \"%s\" is outside the GPU subset (triangle meshes, rectangle)", shape->getClass()->getName().c_str());
+			SLog(EError, "mtsb overlay: shape \"%s\" is outside the GPU subset (triangle meshes, rectangle, disk, sphere)", shape->getClass()->getName().c_str());
 			rc = -1;
 		}
 		if (rc < 0) SLog(EError, "mtsb overlay: %s", mtsb_last_error());

@@ -232,6 +232,18 @@ class SceneDesc:
                                 emitter=emitter, flip_normals=flip_normals))
         return len(self.shapes) - 1
 
+    def add_sphere(self, center, radius, bsdf=None, flip_normals=False):
+        """Analytic `sphere` (src/shapes/sphere.cpp) given by center + radius."""
+        self.shapes.append(dict(type="sphere", center=tuple(float(x) for x in center), radius=float(radius), bsdf=bsdf or dict(type="diffuse"),
+                                emitter=None, flip_normals=flip_normals))
+        return len(self.shapes) - 1
+
+    def add_disk(self, to_world, bsdf=None, flip_normals=False):
+        """Analytic `disk` (src/shapes/disk.cpp): the unit disk of the object-space xy plane under `to_world`."""
+        self.shapes.append(dict(type="disk", to_world=np.asarray(to_world, np.float64), bsdf=bsdf or dict(type="diffuse"), emitter=None,
+                                flip_normals=flip_normals))
+        return len(self.shapes) - 1
+
     def add_point_light(self, pos, intensity):
         self.emitters.append(dict(type="point", pos=tuple(pos), intensity=tuple(intensity)))
 
@@ -316,6 +328,10 @@ class SceneDesc:
                 eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
             if s["type"] == "mesh":
                 sc.add_mesh(s["V"], s["F"], normals=s["N"], texcoords=s.get("UV"), bsdf=bid, emitter=eid)
+            elif s["type"] == "sphere":
+                sc.add_sphere(translate(*s["center"]), s["radius"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
+            elif s["type"] == "disk":
+                sc.add_disk(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
             else:
                 sc.add_rectangle(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
         sc.commit(builder)
@@ -421,6 +437,13 @@ class SceneDesc:
                 write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"], s.get("UV"))
                 face = "" if s["N"] is not None else '<boolean name="faceNormals" value="true"/>'
                 out.append('<shape type="ply"><string name="filename" value="%s"/>%s%s%s</shape>' % (fn, face, bs, em))
+            elif s["type"] == "sphere":
+                flip = '<boolean name="flipNormals" value="true"/>' if s["flip_normals"] else ""
+                out.append('<shape type="sphere"><point name="center" x="%r" y="%r" z="%r"/><float name="radius" value="%r"/>%s%s%s</shape>' % (
+                    s["center"][0], s["center"][1], s["center"][2], s["radius"], flip, bs, em))
+            elif s["type"] == "disk":
+                flip = '<boolean name="flipNormals" value="true"/>' if s["flip_normals"] else ""
+                out.append('<shape type="disk"><transform name="toWorld">%s</transform>%s%s%s</shape>' % (_mat_xml(s["to_world"]), flip, bs, em))
             else:
                 flip = '<boolean name="flipNormals" value="true"/>' if s["flip_normals"] else ""
                 out.append('<shape type="rectangle"><transform name="toWorld">%s</transform>%s%s%s</shape>' % (_mat_xml(s["to_world"]), flip, bs, em))
@@ -580,6 +603,29 @@ MATERIALS = [
     dict(type="roughdielectric", distribution="ggx", alpha=0.15, specular_transmittance=(0.9, 1.0, 0.9)),
     dict(type="roughdielectric", distribution="beckmann", alpha_u=0.1, alpha_v=0.25, int_ior=1.33, sample_visible=False),
 ]
+
+
+def analytic_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0):
+    """Analytic `sphere` and `disk` shapes (src/shapes/sphere.cpp, disk.cpp) beside meshes: a glass, a diffuse and a GGX sphere,
+    a tilted plastic disk and a flipped diffuse one, on a mesh floor under a mesh area light, a point light and an environment."""
+    sd = SceneDesc()
+    sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
+    sd.add_constant_env((0.3, 0.35, 0.5))
+    sd.add_sphere((-1.1, 0.5, 0.2), 0.5, bsdf=dict(type="dielectric"))
+    sd.add_sphere((0.1, 0.4, -0.3), 0.4, bsdf=dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
+    sd.add_sphere((1.2, 0.45, 0.4), 0.45, bsdf=dict(type="roughconductor", distribution="ggx", alpha=0.1))
+    sd.add_sphere((0.3, 1.5, 1.4), 0.35, bsdf=dict(type="diffuse", reflectance=(0.2, 0.5, 0.3)), flip_normals=True)
+    sd.add_disk(translate(-0.4, 0.8, 1.2) @ rotate((1, 0, 0), -60) @ scale(0.6), bsdf=dict(type="plastic", diffuse_reflectance=(0.2, 0.3, 0.6)))
+    sd.add_disk(translate(1.6, 0.9, -0.8) @ rotate((0, 1, 0), 70) @ scale(0.5), bsdf=dict(type="diffuse", twosided=True), flip_normals=True)
+    g = 4.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
+    lV, lN, lF = displaced_sphere(1, seed=99, radius=0.4, center=(0.5, 2.6, 0.3), amplitude=0.0)
+    sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
+    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd
 
 
 def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, subdiv=2, env=True, point=True):

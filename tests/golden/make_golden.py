@@ -77,6 +77,23 @@ def cornell_case(td, n=1536):
     print("cornell:", rays.shape[0], "rays, hit rate", np.isfinite(out[:, 0]).mean(), "any rate", pack(out)["ref_any"].mean())
 
 
+def analytic_case(td, n=2048):
+    """Analytic `sphere` / `disk` shapes among meshes (scenes.analytic_scene): chord rays, primary rays, shadow segments."""
+    sd = S.analytic_scene(48, 32, 1)
+    xml = sd.to_xml(td, "analytic")
+    r0 = S.chord_rays(n, center=(0.2, 0.7, 0.3), radius=2.4, seed=5, mint=S.EPSILON)
+    r1 = S.pinhole_rays(48, origin=(0.3, 3.0, -4.5), target=(0, 0.4, 0), fov_deg=40.0)
+    first = ref_trace(xml, r1)
+    hitp = first[np.isfinite(first[:, 0])][:, 5:8]
+    r2 = S.shadow_rays(hitp, light_center=(0.5, 2.6, 0.3), light_half=0.3)
+    rays = np.concatenate([r0, r1, r2])
+    out = ref_trace(xml, rays)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "hits_analytic.npz"),
+                        rays=rays.view(np.float32).reshape(-1, 8), **pack(out))
+    sh = pack(out)["ref_shape"]
+    print("analytic:", rays.shape[0], "rays, hit rate", np.isfinite(out[:, 0]).mean(), "hits per shape", np.bincount(sh[sh >= 0]))
+
+
 def light_case(td):
     """ShapeKDTree::rayIntersect(ray, t, shape, n, uv) (skdtree.cpp:144-204) on the ray sets of the two files above plus a
     mesh WITH texture coordinates -> light.npz (raydump `light`: t, shape, n, uv)."""
@@ -103,6 +120,10 @@ def light_case(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "analytic":
+        with tempfile.TemporaryDirectory() as td:
+            analytic_case(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "light":
         with tempfile.TemporaryDirectory() as td:
             light_case(td)
@@ -111,3 +132,4 @@ if __name__ == "__main__":
         sphere_case(td)
         cornell_case(td)
         light_case(td)
+        analytic_case(td)

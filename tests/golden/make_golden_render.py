@@ -122,6 +122,10 @@ def thinlens_case(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "analytic":         # analytic sphere / disk shapes (round 2)
+        with tempfile.TemporaryDirectory() as td:
+            li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "direct_fan":       # only the cases added in round 2
         with tempfile.TemporaryDirectory() as td:
             for n_em, n_bsdf in ((4, 2), (1, 3), (3, 1), (2, 0)):
@@ -138,3 +142,4 @@ if __name__ == "__main__":
         strict_case(td)
         for n_em, n_bsdf in ((4, 2), (1, 3), (3, 1), (2, 0)):
             direct_fan_case(td, n_em, n_bsdf)
+        li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))

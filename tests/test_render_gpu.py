@@ -99,7 +99,7 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
-                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0"])
+                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -122,6 +122,9 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
         n_em, n_bsdf = (int(x) for x in name.split("_")[1:])
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
         sd.set_integrator("direct", emitter_samples=n_em, bsdf_samples=n_bsdf)
+    elif name == "analytic":
+        # analytic sphere / disk shapes (src/shapes/sphere.cpp, disk.cpp) through the path tracer
+        sd = S.analytic_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
     elif name == "strict":
         # strictNormals + hideEmitters (path.cpp:136-165,196-199,218-222); parameters of make_golden_render.strict_case
         sd = S.materials_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)

@@ -70,6 +70,45 @@ def test_hits_match_reference_golden(pkg, ctx, golden, kind, builder):
         sc.close()
 
 
+def test_analytic_sphere_and_disk_match_reference(pkg, ctx, golden):
+    """Analytic `sphere` (double-precision quadratic, re-projected hit point, spherical uv) and `disk` leaf primitives among
+    meshes (src/shapes/sphere.cpp:158-252, disk.cpp:139-197) against hit records of the unmodified reference."""
+    gold = golden("hits_analytic.npz")
+    sd = pkg.scenes.analytic_scene(48, 32, 1)
+    kinds = np.array([dict(mesh=0, rectangle=1, disk=2, sphere=3)[s_["type"]] for s_ in sd.shapes])
+    for builder in (0, 1):
+        sc = sd.upload(ctx, builder)
+        try:
+            rays = gold["rays"]
+            surf = sc.ray_intersect_surface(rays)
+            ref_t, ref_shape = gold["ref_t"], gold["ref_shape"]
+            hit, rhit = np.isfinite(surf["t"]), np.isfinite(ref_t)
+            same = (hit == rhit) & (np.where(rhit, surf["shape"].view(np.int32), -1) == ref_shape)
+            scale = np.maximum(np.maximum(np.abs(np.where(rhit, ref_t, 0)), np.abs(rays[:, 0:3]).max(axis=1)), 1.0)
+            with np.errstate(invalid="ignore"):
+                tie = hit & rhit & (np.abs(surf["t"] - ref_t) <= helpers.T_REL * scale)
+            assert (same | tie).mean() >= helpers.PRIM_AGREE, ((same | tie).mean(), np.nonzero(~(same | tie))[0][:8])
+            m = same & rhit
+            k = kinds[np.maximum(ref_shape, 0)]
+            # spheres: t comes out of the same double-precision quadratic -> held to T_REL without any conditioning weight
+            for name, sel in (("sphere", m & (k == 3)), ("disk", m & (k == 2))):
+                assert sel.sum() > 100
+                dt = np.abs(surf["t"][sel] - ref_t[sel]) / scale[sel]
+                assert dt.max() <= helpers.T_REL, (name, dt.max())
+                assert np.abs(surf["p"][sel] - gold["ref_p"][sel]).max() <= 2e-5 * 4, name
+                assert np.abs(surf["ns"][sel] - gold["ref_ns"][sel]).max() < 2e-4, name
+                duv = np.abs(surf["uv"][sel] - np.stack([gold["ref_u"][sel], gold["ref_v"][sel]], axis=1))
+                duv[:, 0] = np.minimum(duv[:, 0], 1 - duv[:, 0])              # phi wraps around
+                assert duv.max() < 2e-4, (name, duv.max())
+                print("analytic %s (builder %d): %d hits, max dt %.3g, max duv %.3g" % (name, builder, sel.sum(), dt.max(), duv.max()))
+            sph = m & (k == 3)
+            assert np.abs(surf["ng"][sph] - gold["ref_ng"][sph]).max() < 2e-4      # (the reference leaves a disk's geoFrame unset)
+            a = sc.ray_intersect_any(rays)
+            assert (a == gold["ref_any"]).mean() >= helpers.PRIM_AGREE
+        finally:
+            sc.close()
+
+
 @pytest.mark.parametrize("kind", ["sphere", "cornell", "uvsphere"])
 def test_light_record_matches_reference(pkg, ctx, golden, kind):
     """mtsb_trace_light vs ShapeKDTree::rayIntersect(ray, t, shape, n, uv) (src/librender/skdtree.cpp:144-204) of the
