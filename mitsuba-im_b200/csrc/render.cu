@@ -108,19 +108,21 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 // extend / connect: persistent traversal over the queues
 // ---------------------------------------------------------------------------------------------------
 struct ExtendIO {
-	SceneDev S; PathState ps; const uint32_t *queue;
+	const SceneDev &S;                 // the kernel parameter itself (constant bank), not a copy
+	const PathState &ps;               // likewise: pointers stay in the constant bank
+	uint32_t qOff;                     // 0: queue A, capacity: queue B (the two queues are one allocation, render_host.cuh)
 	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
-		const uint32_t slot = queue[i];
+		const uint32_t slot = ps.queueA[qOff + i];
 		const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot];
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
 		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax, rcp)) return true;
 		ps.hit[slot] = make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
 		return false;
 	}
-	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &hit, const V3 &, const V3 &) const {
-		const uint32_t slot = queue[i];
-		ps.hit[slot] = found ? make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot))
-		                     : make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
+	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &h, const V3 &, const V3 &) const {
+		const uint32_t slot = ps.queueA[qOff + i];
+		ps.hit[slot] = found ? make_float4(h.t, h.u, h.v, __uint_as_float(h.slot))
+		                  : make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
 	}
 };
 
@@ -147,24 +149,26 @@ struct ConnectIO {
 
 // Both kernels find the live queue through counters[CTR_PARITY] (flipped by advance_kernel between bounces), so the same
 // launch — the same graph node — serves every bounce.
+template <bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 extend_kernel(SceneDev S, PathState ps) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
 	const unsigned long long n = ps.counters[parity];
 	if (n == 0) return;
-	ExtendIO io; io.S = S; io.ps = ps; io.queue = parity ? ps.queueB : ps.queueA;
-	trace_persistent<false, false>(S, io, n, ps.work + 0, shStack + threadIdx.x);
+	ExtendIO io = { S, ps, parity ? (uint32_t) (ps.queueB - ps.queueA) : 0u };
+	trace_persistent<false, false, CURVED>(S, io, n, ps.work + 0, shStack + threadIdx.x);
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
 }
 
+template <bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 connect_kernel(SceneDev S, PathState ps) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	const unsigned long long n = ps.counters[CTR_SHADOW];
 	if (n == 0) return;
 	ConnectIO io; io.S = S; io.ps = ps;
-	trace_persistent<true, false>(S, io, n, ps.work + 1, shStack + threadIdx.x);
+	trace_persistent<true, false, CURVED>(S, io, n, ps.work + 1, shStack + threadIdx.x);
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 2, n);
 }
 

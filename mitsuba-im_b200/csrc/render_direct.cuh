@@ -166,13 +166,14 @@ struct ConnectFanIO {
 	}
 };
 
+template <bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 connect_fan_kernel(SceneDev S, PathState ps) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	const unsigned long long n = ps.counters[CTR_SHADOW];
 	if (n == 0) return;
 	ConnectFanIO io; io.S = S; io.ps = ps;
-	trace_persistent<true, false>(S, io, n, ps.work + 1, shStack + threadIdx.x);
+	trace_persistent<true, false, CURVED>(S, io, n, ps.work + 1, shStack + threadIdx.x);
 	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 2, n);
 }
 

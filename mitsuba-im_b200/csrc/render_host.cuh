@@ -94,11 +94,11 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	cudaGraph_t body = wp.conditional.phGraph_out[0];
 	void *aTrace[] = { &S, &ps };
 	void *aShade[] = { &S, &ps, &integ, &seed };
-	MTSB_CUDA(add_kernel(body, &n1, nullptr, (void *) extend_kernel, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	MTSB_CUDA(add_kernel(body, &n2, n1, (void *) shade_kernel, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
-	MTSB_CUDA(add_kernel(body, &n3, n2, (void *) connect_kernel, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_kernel<true> : (void *) connect_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	MTSB_CUDA(add_kernel(body, &n4, n3, (void *) advance_kernel, 1, 1, aCtl, nullptr));
-	if (tailBelow) MTSB_CUDA(add_kernel(g, &nTail, nWhile, (void *) tail_kernel, sh.tailGrid, MTSB_TRACE_BLOCK, aShade, scene));
+	if (tailBelow) MTSB_CUDA(add_kernel(g, &nTail, nWhile, scene->curved ? (void *) tail_kernel<true> : (void *) tail_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aShade, scene));
 	MTSB_CUDA(cudaGraphInstantiate(&r->bounceExec, g, 0));
 	r->graphKey = r->bufF4.ptr; r->graphTail = (int) tailBelow;
 	return 0;
@@ -139,12 +139,12 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		LoopCtl ctl; ctl.tailBelow = 0; ctl.maxBounces = 2; ctl.inGraph = 0; ctl.cond = 0;
 		const unsigned fanGrid = std::min(blocks_for(g.count, RENDER_BLOCK), (unsigned) ctx->smCount * 16u);
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
-		MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+		MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
 		direct_head_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, fan);
-		MTSB_CHECK(launch_trav(scene, connect_fan_kernel, sh.traceGrid, st, S, ps));
+		MTSB_CHECK(launch_trav(scene, scene->curved ? connect_fan_kernel<true> : connect_fan_kernel<false>, sh.traceGrid, st, S, ps));
 		if (M > 0) {
 			fan_flip_kernel<<<1, 1, 0, st>>>(ps);
-			MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
 			direct_tail_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, fan);
 		}
 		r->launches += M > 0 ? 7 : 4;
@@ -170,9 +170,9 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		ctl.maxBounces = (maxDepth > 0 || poll) ? bounded : 16u;
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
-			MTSB_CHECK(launch_trav(scene, extend_kernel, sh.traceGrid, st, S, ps));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
 			shade_kernel<<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
-			MTSB_CHECK(launch_trav(scene, connect_kernel, sh.traceGrid, st, S, ps));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? connect_kernel<true> : connect_kernel<false>, sh.traceGrid, st, S, ps));
 			advance_kernel<<<1, 1, 0, st>>>(ps, ctl);
 			if (poll && (bounce & 7) == 7) {
 				uint32_t live[2] = { 0, 0 };
@@ -184,7 +184,7 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		}
 		r->launches += 1;
 		if (tailBelow) {
-			MTSB_CHECK(launch_trav(scene, tail_kernel, sh.tailGrid, st, S, ps, r->integ, r->seed));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? tail_kernel<true> : tail_kernel<false>, sh.tailGrid, st, S, ps, r->integ, r->seed));
 			r->launches += 1;
 		}
 	}

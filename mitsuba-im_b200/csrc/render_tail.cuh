@@ -61,6 +61,7 @@ __global__ void advance_kernel(PathState ps, LoopCtl ctl) {
 #ifndef MTSB_TAIL_MIN_BLOCKS
 #define MTSB_TAIL_MIN_BLOCKS 4
 #endif
+template <bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TAIL_MIN_BLOCKS)
 tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
@@ -101,7 +102,7 @@ tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 			if (clip_ray(S, tv.o, tv.d, r0.w, r1.w, true, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
 			else tv.found = false;
 		}
-		trace_warp<false>(S, tv);
+		trace_warp<false, CURVED>(S, tv);
 		ShadeOut so; so.alive = false; so.shadow = false;
 		if (have) {
 			ps.hit[slot] = tv.found ? make_float4(tv.hit.t, tv.hit.u, tv.hit.v, __uint_as_float(tv.hit.slot))
@@ -118,7 +119,7 @@ tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 			tv.found = false;
 			if (clip_ray(S, tv.o, tv.d, so.shO.w, so.shD.w, false, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
 		}
-		if (__any_sync(FULL, so.shadow)) trace_warp<true>(S, tv);
+		if (__any_sync(FULL, so.shadow)) trace_warp<true, CURVED>(S, tv);
 		if (so.shadow) unoccluded = !tv.found;
 		if (unoccluded) {
 			float4 L = ps.L[slot];

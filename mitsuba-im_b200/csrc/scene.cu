@@ -244,6 +244,7 @@ int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, 
 	if (fabsf(lu / lv - 1) > 1e-3f) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: 'toWorld' transformation contains a non-uniform scale!");                  // disk.cpp:111-112
 	rr.invSurfaceArea = 1.0f / (3.14159265358979323846f * lu * lu);
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	scene->curved = true;
 	sh.type = SHAPE_DISK; sh.primOffset = scene->primCount; sh.primCount = 1;
 	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
 	sh.invArea = rr.invSurfaceArea;
@@ -267,6 +268,7 @@ int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], fl
 	rr.pad[0] = flip_normals ? 1u : 0u;
 	rr.invSurfaceArea = 1.0f / (4 * 3.14159265358979323846f * radius * radius);
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	scene->curved = true;
 	sh.type = SHAPE_SPHERE; sh.primOffset = scene->primCount; sh.primCount = 1;
 	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
 	sh.invArea = rr.invSurfaceArea;

@@ -10,6 +10,7 @@ namespace mtsb { struct TracePipe; }
 struct mtsb_scene {
 	mtsb_ctx *ctx = nullptr;
 	bool committed = false;
+	bool curved = false;                  // holds analytic disks / spheres: traversal kernels with their leaf test (trace.cuh)
 
 	// host staging (filled by mtsb_scene_add_*)
 	std::vector<mtsb::ShapeRec> shapes;

@@ -76,13 +76,13 @@ struct BatchIO {
 	}
 };
 
-template <int MODE, bool COUNT>
+template <int MODE, bool COUNT, bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
 trace_kernel(SceneDev S, const float4 *__restrict__ rays, unsigned long long n, void *__restrict__ out,
 		unsigned long long *__restrict__ workCounter) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	BatchIO<MODE> io; io.S = S; io.rays = rays; io.out = out;
-	trace_persistent<MODE == MODE_ANY, COUNT>(S, io, n, workCounter, shStack + threadIdx.x);
+	trace_persistent<MODE == MODE_ANY, COUNT, CURVED>(S, io, n, workCounter, shStack + threadIdx.x);
 	if (COUNT && threadIdx.x == 0 && blockIdx.x == 0 && S.counters) atomicAdd(S.counters + 2, n);
 }
 
@@ -107,8 +107,10 @@ int launch_trace(mtsb_scene *scene, int mode, const mtsb_ray *dRays, size_t n, v
 	cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof(cfg));
 	cfg.gridDim = dim3(grid); cfg.blockDim = dim3(MTSB_TRACE_BLOCK); cfg.stream = st;
 	cfg.attrs = attr; cfg.numAttrs = l2_window(scene, attr);
-	#define LAUNCH(M) do { if (count) MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, true>, S, r, nn, dOut, dWork)); \
-		else MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, false>, S, r, nn, dOut, dWork)); } while (0)
+	const bool curved = scene->curved;
+	#define LAUNCH(M) do { if (count) MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, true, true>, S, r, nn, dOut, dWork)); \
+		else if (curved) MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, false, true>, S, r, nn, dOut, dWork)); \
+		else MTSB_CUDA(cudaLaunchKernelEx(&cfg, trace_kernel<M, false, false>, S, r, nn, dOut, dWork)); } while (0)
 	if (mode == MODE_CLOSEST) LAUNCH(MODE_CLOSEST);
 	else if (mode == MODE_ANY) LAUNCH(MODE_ANY);
 	else if (mode == MODE_LIGHT) LAUNCH(MODE_LIGHT);

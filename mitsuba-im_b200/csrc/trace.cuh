@@ -281,7 +281,9 @@ struct Trav {
 
 	// One iteration: node phase, triangle phase, pop-or-finish.  Must be called by all 32 lanes of the warp (it ballots).
 	// Returns true for the lanes whose ray finished in this iteration (`active` is already false for them).
-	template <bool ANY, bool COUNT>
+	// CURVED: the scene holds analytic disks / spheres.  Their leaf test sits behind a real call whose register traffic cost
+	// the loop 3 % (config 2: 2946 -> 2863 Mrays/s) even when it never ran, so scenes without them get kernels without it.
+	template <bool ANY, bool COUNT, bool CURVED>
 	__device__ __forceinline__ bool step(const SceneDev &S, uint32_t one, unsigned &nNodes, unsigned &nTris) {
 		const unsigned FULL = 0xffffffffu;
 		// ---- node phase (lanes still holding untested triangles sit this one out: they drain one per iteration)
@@ -323,7 +325,8 @@ struct Trav {
 				if (__float_as_uint(a.x) != K_NO_TRIANGLE)
 					h = tri_test(a, b, c, o, d, tmin, hit.t, t, u, v);
 				else
-					h = analytic_test(S, __float_as_uint(c.z), o, d, tmin, hit.t, t, u, v);
+					h = CURVED ? analytic_test(S, __float_as_uint(c.z), o, d, tmin, hit.t, t, u, v)
+					           : rect_test(S.rects[S.shapes[__float_as_uint(c.z)].rect], o, d, tmin, hit.t, t, u, v);
 				if (h) {
 					hit.t = t; hit.u = u; hit.v = v; hit.slot = slot; found = true;
 					if (ANY) { tg.y = 0; ng = make_uint2(0u, 0u); st.n = 0; }
@@ -352,7 +355,7 @@ struct Trav {
 // IO supplies the rays and consumes the records:
 //   bool IO::load(i, o, d, tmin, tmax, rcp) -> rcp = 1/d from clip_ray; false if the ray needs no traversal (IO has already written a miss)
 //   void IO::store(i, found, hit, o, d)
-template <bool ANY, bool COUNT, class IO>
+template <bool ANY, bool COUNT, bool CURVED, class IO>
 __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsigned long long n,
 		unsigned long long *__restrict__ workCounter, uint2 *shStack) {
 	const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
@@ -383,7 +386,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 		}
 		if (!__any_sync(FULL, tv.active)) { if (exhausted) break; else continue; }
 		// ---- (2)-(4)
-		if (tv.template step<ANY, COUNT>(S, one, nNodes, nTris)) io.store(idx, tv.found, tv.hit, tv.o, tv.d);
+		if (tv.template step<ANY, COUNT, CURVED>(S, one, nNodes, nTris)) io.store(idx, tv.found, tv.hit, tv.o, tv.d);
 	}
 	if (COUNT && S.counters) {
 		atomicAdd(S.counters, (unsigned long long) nNodes);
@@ -393,11 +396,11 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 
 // Traces the ONE ray each lane holds in `tv` (tv.begin called by the lanes that have one) until every lane of the warp
 // is done; no refill.  Used where a warp owns 32 paths and alternates traversal with shading (render_tail.cuh).
-template <bool ANY>
+template <bool ANY, bool CURVED>
 __device__ __forceinline__ void trace_warp(const SceneDev &S, Trav &tv) {
 	const uint32_t one = S.oneBits;
 	unsigned nNodes = 0, nTris = 0;
-	while (__any_sync(0xffffffffu, tv.active)) tv.template step<ANY, false>(S, one, nNodes, nTris);
+	while (__any_sync(0xffffffffu, tv.active)) tv.template step<ANY, false, CURVED>(S, one, nNodes, nTris);
 }
 
 } // namespace mtsb
