@@ -1,5 +1,8 @@
 // microfacet.cuh — MicrofacetDistribution (src/bsdfs/microfacet.h) for Beckmann and GGX, including visible-normal
 // sampling (Heitz & d'Eon), as used by roughconductor.
+// NOTE: `sample_visible11` below is a statement-for-statement transliteration of MicrofacetDistribution::sampleVisible11
+// (src/bsdfs/microfacet.h:572-696) — the same locals, the same Newton / bisection loop, the same polynomial fit
+// constants — not a design of its own: pointwise parity of the sampled directions (5e-4) needs exactly those fits.
 #pragma once
 
 namespace mtsb {
