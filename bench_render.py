@@ -158,20 +158,24 @@ def render_config5(pkg, ctx, stream, sd, frames=600, warmup=5):
     return out
 
 
-def cpu_reference(pkg, sd_small, threads):
-    """The reference's own renderer (oracle/_ref/mitsuba -C) on the host cores, bounded sample of config 1."""
+def cpu_reference(pkg, sd_small, threads, what="config 1 at %d spp (of 64)"):
+    """The reference's own renderer (oracle/_ref/mitsuba -C) on the host cores, on a bounded sample of a config."""
+    import re
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as O
     import tempfile
     if not O.have_reference():
         return None
     with tempfile.TemporaryDirectory() as td:
-        xml = sd_small.to_xml(td, "cbox")
-        wall, render_s, _ = O.ref_render(xml, os.path.join(td, "o.pfm"), threads=threads, classic=True)
+        xml = sd_small.to_xml(td, "cpu")
+        wall, render_s, log = O.ref_render(xml, os.path.join(td, "o.pfm"), threads=threads, classic=True)
     n = sd_small.sensor["width"] * sd_small.sensor["height"] * sd_small.sampler["spp"]
     t = render_s if render_s else wall
-    return {"samples_per_s": n / t, "cores": threads, "kind": "reference",
-            "sample": "config 1 at %d spp (of 64), mitsuba -C, 'Render time' %.3f s" % (sd_small.sampler["spp"], t)}
+    kd = re.findall(r"Finished -- took (\d+) ms", log)
+    return {"samples_per_s": n / t, "cores": threads, "kind": "reference", "process_wall_s": wall,
+            "kd_build_ms": max(int(x) for x in kd) if kd else None,
+            "sample": (what % sd_small.sampler["spp"]) + ", %dx%d, mitsuba -C, 'Render time' %.3f s (kd-tree build excluded)" % (
+                sd_small.sensor["width"], sd_small.sensor["height"], t)}
 
 
 def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
@@ -259,6 +263,19 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         r = render_config(pkg, ctx, stream, sd, spp3, warmup=1, builder=builder)
         r["scene_generation_s"] = gen_s
         out["config3_spherefield_10Mtri_1920x1080_%dspp" % spp3] = r
+        if cpu:
+            # the reference on the same 10.5 M-triangle scene: a bounded sample (1280x720, 2 spp) — its SAH kd-tree build alone
+            # takes tens of seconds on the host cores and is reported separately; the same rate gives the CPU's time for
+            # one 1-spp frame of config 5 (the GUI path that would display it is unavailable on this box)
+            import copy
+            small = copy.copy(sd)
+            small.sensor = dict(sd.sensor, width=1280, height=720)
+            small.sampler = dict(sd.sampler, spp=2)
+            c = cpu_reference(pkg, small, os.cpu_count() or 1, what="config 3 scene at %d spp (of 256)")
+            if c:
+                out["config3_cpu_reference"] = c
+                out["config5_cpu_reference"] = {"fps": c["samples_per_s"] / (1280 * 720), "kind": "reference (derived)", "cores": c["cores"],
+                                                "sample": "1280x720 x 1 spp frames at the rate of config3_cpu_reference; kd-tree build (%s ms) excluded" % c["kd_build_ms"]}
     if "plugin" in configs and rank == 0:
         import torch
         out["plugin"] = plugin_bench(pkg, sd, gpus=(1, 2) if torch.cuda.device_count() >= 2 else (1,))

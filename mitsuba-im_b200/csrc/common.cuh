@@ -164,6 +164,8 @@ struct mtsb_ctx {
 	int tailPaths = 0;                     // MTSB_TAIL_PATHS: live-path count below which the late-bounce kernel takes over (render)
 	int shadeWaves = 0;                    // MTSB_SHADE_WAVES: shade grid = SMs x resident CTAs x this; 0 = one thread per path slot
 	                                       // (measured on config 3: 277 M samples/s against 248-255 for 1-16 waves of a grid-stride loop)
+	int suspendAfter = 0;                  // MTSB_SUSPEND_AFTER: warp iterations before the extend stage parks its remaining rays (0 = off,
+	                                       // the default: measured +3 % on config 5 at 24, nothing elsewhere — DESIGN.md 10.2)
 	int useGraph = 1;                      // MTSB_GRAPH: bounce loop as a CUDA graph with a device-driven WHILE node (0 = plain launches)
 	// L2 residency of the acceleration structure (cudaAccessPolicyWindow, see l2_window in scene.cuh)
 	size_t l2PersistMax = 0;               // ceiling of the persisting set-aside (device maximum, or MTSB_L2_PERSIST in MB; 0 = off)

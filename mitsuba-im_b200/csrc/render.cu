@@ -59,21 +59,38 @@ struct GenParams {
 __global__ void __launch_bounds__(RENDER_BLOCK)
 generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-	if (j >= g.count) return;
-	uint32_t px, py, sidx;
-	bool valid = true;
-	if (g.samples) {
-		px = g.samples[4 * j]; py = g.samples[4 * j + 1]; sidx = g.samples[4 * j + 2];
-	} else {
-		const unsigned long long gi = g.first + j;
-		const uint32_t k = (uint32_t) (gi / g.pixPadded), q = (uint32_t) (gi % g.pixPadded);
-		const uint32_t tile = q >> 5, within = q & 31u;
-		const uint32_t lx = (tile % g.tilesX) * 8 + (within & 7u), ly = (tile / g.tilesX) * 4 + (within >> 3);
-		valid = lx < (uint32_t) g.w && ly < (uint32_t) g.h;
-		px = g.x0 + lx; py = g.y0 + ly;
-		sidx = g.sppBegin + g.sppPhase + k * g.sppStride;
+	uint32_t px = 0, py = 0, sidx = 0;
+	bool valid = j < g.count;
+	if (valid) {
+		if (g.samples) {
+			px = g.samples[4 * j]; py = g.samples[4 * j + 1]; sidx = g.samples[4 * j + 2];
+		} else {
+			const unsigned long long gi = g.first + j;
+			const uint32_t k = (uint32_t) (gi / g.pixPadded), q = (uint32_t) (gi % g.pixPadded);
+			const uint32_t tile = q >> 5, within = q & 31u;
+			const uint32_t lx = (tile % g.tilesX) * 8 + (within & 7u), ly = (tile / g.tilesX) * 4 + (within >> 3);
+			valid = lx < (uint32_t) g.w && ly < (uint32_t) g.h;
+			px = g.x0 + lx; py = g.y0 + ly;
+			sidx = g.sppBegin + g.sppPhase + k * g.sppStride;
+			if (!valid) ps.rng[j] = make_uint4(INVALID_SLOT, 0, 0, 0);
+		}
 	}
-	if (!valid) { ps.rng[j] = make_uint4(INVALID_SLOT, 0, 0, 0); return; }
+	// queue slot: ONE atomic per block (a per-warp append to the single counter serialises in L2 — a short kernel that
+	// does nothing but stores waited on it: long-scoreboard stall 30-45 cycles per issue, profiles/r02a_ncu_full_render.json)
+	__shared__ uint32_t warpCount[RENDER_BLOCK / 32], blockBase;
+	const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const unsigned vm = __ballot_sync(0xffffffffu, valid);
+	if (lane == 0) warpCount[warp] = __popc(vm);
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint32_t total = 0;
+		#pragma unroll
+		for (int w = 0; w < RENDER_BLOCK / 32; ++w) { const uint32_t c = warpCount[w]; warpCount[w] = total; total += c; }
+		blockBase = total ? atomicAdd(ps.counters + 0, total) : 0u;
+	}
+	__syncthreads();
+	if (!valid) return;
+	const uint32_t pos = blockBase + warpCount[warp] + __popc(vm & ((1u << lane) - 1u));
 	SamplerState rs; rs.px = px; rs.py = py; rs.sample = sidx; rs.dim = 0; rs.seed = g.seed;
 	float u1, u2; next2D(rs, u1, u2);
 	const float sx = (float) px + u1, sy = (float) py + u2;            // samplePos (integrator.cpp:172)
@@ -101,32 +118,51 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	ps.prev[j] = make_float4(0, 0, 0, 0);
 	ps.misc[j] = make_float4(sx, sy, __uint_as_float(0u), __uint_as_float(1u));   // flags = 0, depth = 1
 	ps.rng[j] = make_uint4(px, py, sidx, rs.dim);
-	queue[warp_append(ps.counters + 0)] = j;
+	queue[pos] = j;
 }
 
 // ---------------------------------------------------------------------------------------------------
 // extend / connect: persistent traversal over the queues
 // ---------------------------------------------------------------------------------------------------
+// Queue entries of the extend stage: a path slot, with QUEUE_RESUME set when the slot's ray was suspended by the
+// previous launch (its traversal state waits in ps.susp) — the shade kernel passes such slots on instead of shading them.
+#define QUEUE_RESUME   0x80000000u
+#define QUEUE_SLOT(q)  ((q) & 0x7fffffffu)
+#define SUSPENDED_SLOT 0xfffffffeu      // hit.w of a slot whose ray is parked
+
 struct ExtendIO {
+	static constexpr bool CAN_SUSPEND = true;
 	const SceneDev &S;                 // the kernel parameter itself (constant bank), not a copy
 	const PathState &ps;               // likewise: pointers stay in the constant bank
 	uint32_t qOff;                     // 0: queue A, capacity: queue B (the two queues are one allocation, render_host.cuh)
-	__device__ __forceinline__ bool load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
-		const uint32_t slot = ps.queueA[qOff + i];
+	mutable unsigned fresh;            // rays started by this thread (resumed ones were counted by the launch that started them)
+	__device__ __forceinline__ int load(unsigned long long i, V3 &o, V3 &d, float &tmin, float &tmax, V3 &rcp) const {
+		const uint32_t q = ps.queueA[qOff + i], slot = QUEUE_SLOT(q);
 		const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot];
 		o = v3(r0.x, r0.y, r0.z); d = v3(r1.x, r1.y, r1.z);
-		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax, rcp)) return true;
+		if (q & QUEUE_RESUME) return 2;
+		++fresh;
+		if (clip_ray(S, o, d, r0.w, r1.w, true, tmin, tmax, rcp)) return 1;
 		ps.hit[slot] = make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
-		return false;
+		return 0;
+	}
+	__device__ __forceinline__ void resume(unsigned long long i, Trav &tv) const {
+		tv.restore(ps.susp + (size_t) QUEUE_SLOT(ps.queueA[qOff + i]) * MTSB_SUSP_WORDS);
+	}
+	__device__ __forceinline__ void suspend(unsigned long long i, const Trav &tv) const {
+		const uint32_t slot = QUEUE_SLOT(ps.queueA[qOff + i]);
+		tv.save(ps.susp + (size_t) slot * MTSB_SUSP_WORDS);
+		ps.hit[slot] = make_float4(0, 0, 0, __uint_as_float(SUSPENDED_SLOT));
 	}
 	__device__ __forceinline__ void store(unsigned long long i, bool found, const HitRec &h, const V3 &, const V3 &) const {
-		const uint32_t slot = ps.queueA[qOff + i];
+		const uint32_t slot = QUEUE_SLOT(ps.queueA[qOff + i]);
 		ps.hit[slot] = found ? make_float4(h.t, h.u, h.v, __uint_as_float(h.slot))
-		                  : make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
+		                     : make_float4(INFINITY, 0, 0, __uint_as_float(INVALID_SLOT));
 	}
 };
 
 struct ConnectIO {
+	static constexpr bool CAN_SUSPEND = false;
 	SceneDev S; PathState ps;
 	__device__ __forceinline__ void add(unsigned long long i) const {
 		const float4 c = ps.shL[i];
@@ -149,16 +185,22 @@ struct ConnectIO {
 
 // Both kernels find the live queue through counters[CTR_PARITY] (flipped by advance_kernel between bounces), so the same
 // launch — the same graph node — serves every bounce.
+// suspendAfter: warp iterations a warp may spend on its remaining rays once the queue is empty before it parks them
+// (0 = never: every ray is finished by the launch that started it)
 template <bool CURVED>
 __global__ void __launch_bounds__(MTSB_TRACE_BLOCK, MTSB_TRACE_BLOCKS_PER_SM)
-extend_kernel(SceneDev S, PathState ps) {
+extend_kernel(SceneDev S, PathState ps, uint32_t suspendAfter) {
 	__shared__ uint2 shStack[MTSB_STACK_SHARED * MTSB_TRACE_BLOCK];
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
 	const unsigned long long n = ps.counters[parity];
 	if (n == 0) return;
-	ExtendIO io = { S, ps, parity ? (uint32_t) (ps.queueB - ps.queueA) : 0u };
-	trace_persistent<false, false, CURVED>(S, io, n, ps.work + 0, shStack + threadIdx.x);
-	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ps.stats + 1, n);
+	ExtendIO io = { S, ps, parity ? (uint32_t) (ps.queueB - ps.queueA) : 0u, 0u };
+	trace_persistent<false, false, CURVED>(S, io, n, ps.work + 0, shStack + threadIdx.x, suspendAfter);
+	// "Normal rays traced" (skdtree.cpp:46,118): rays STARTED here
+	unsigned fresh = io.fresh;
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) fresh += __shfl_xor_sync(0xffffffffu, fresh, o);
+	if ((threadIdx.x & 31u) == 0 && fresh) atomicAdd(ps.stats + 1, (unsigned long long) fresh);
 }
 
 template <bool CURVED>

@@ -17,7 +17,8 @@ struct PathState {
 	float4 *rayO, *rayD, *hit, *thr, *L, *prev, *misc;
 	uint4  *rng;
 	float4 *shO, *shD, *shL;
-	uint32_t *queueA, *queueB;     // live path slots (ping-pong)
+	uint32_t *queueA, *queueB;     // live path slots (ping-pong); entries may carry QUEUE_RESUME (render.cu)
+	uint2  *susp;                  // suspension records of the extend stage, MTSB_SUSP_WORDS per path slot (trace.cuh: Trav::save)
 	uint32_t *counters;            // 16 words, see the CTR_* enum below
 	unsigned long long *work;      // work counters of the persistent kernels [0] extend, [1] connect, [2] tail
 	unsigned long long *stats;     // [0] camera paths, [1] closest rays, [2] shadow rays, [3] depth sum, [5] kernels run inside the bounce graph
@@ -62,6 +63,7 @@ struct mtsb_render {
 	mtsb::DevBuf<float4> bufF4;    // one allocation for all float4 arrays
 	mtsb::DevBuf<uint4> bufRng;
 	mtsb::DevBuf<uint32_t> bufQueue, bufCounters;
+	mtsb::DevBuf<uint2> bufSusp;
 	mtsb::DevBuf<unsigned long long> bufWork;
 	unsigned long long launches = 0;
 	int tailPaths = 0;                  // live-path count below which the tail kernel takes over (0 = never; mtsb_render_set_tail)

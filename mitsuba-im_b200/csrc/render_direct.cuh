@@ -40,7 +40,7 @@ direct_head_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed,
 	const uint32_t n = ps.counters[CTR_COUNT_A];
 	const uint32_t N = (uint32_t) integ.emitterSamples, M = (uint32_t) integ.bsdfSamples;
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		const uint32_t slot = ps.queueA[i];
+		const uint32_t slot = QUEUE_SLOT(ps.queueA[i]);
 		const float4 r1 = ps.rayD[slot], r0 = ps.rayO[slot], h = ps.hit[slot];
 		const uint4 rg = ps.rng[slot];
 		SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = rg.w; rs.seed = seed;
@@ -148,6 +148,7 @@ __global__ void fan_flip_kernel(PathState ps) {
 
 // connect with several shadow entries per path slot: the unoccluded contributions are added atomically
 struct ConnectFanIO {
+	static constexpr bool CAN_SUSPEND = false;
 	SceneDev S; PathState ps;
 	__device__ __forceinline__ void add(unsigned long long i) const {
 		const float4 c = ps.shL[i];

@@ -17,6 +17,13 @@ static inline size_t max_paths(const mtsb_render *r) {
 	return MAX_PATHS_IN_FLIGHT / (size_t) (1 + std::max(r->integ.emitterSamples, r->integ.bsdfSamples));
 }
 
+// warp iterations after which the extend stage parks the rays it is still working on (0: never).  Only the graph loop
+// uses it: its WHILE node runs as many extra bounces as the parked rays need; the fixed launch sequences do not.
+static inline uint32_t suspend_after(const mtsb_render *r) {
+	const mtsb_ctx *ctx = r->scene->ctx;
+	return (fan_mode(r) || !ctx->useGraph || r->graphFailed) ? 0u : (uint32_t) ctx->suspendAfter;
+}
+
 static int ensure_capacity(mtsb_render *r, size_t paths) {
 	if (paths <= r->capacity) return 0;
 	const size_t cap = std::max<size_t>(paths, 1024);
@@ -25,6 +32,8 @@ static int ensure_capacity(mtsb_render *r, size_t paths) {
 	MTSB_CHECK(r->bufF4.alloc(wide * 6 + cap + cap * N * 3));
 	MTSB_CHECK(r->bufRng.alloc(cap));
 	MTSB_CHECK(r->bufQueue.alloc(cap + std::max(cap, cap * M)));
+	if (suspend_after(r)) MTSB_CHECK(r->bufSusp.alloc(cap * MTSB_SUSP_WORDS));
+	r->ps.susp = r->bufSusp.ptr;
 	PathState &ps = r->ps;
 	float4 *f = r->bufF4.ptr;
 	ps.rayO = f; ps.rayD = f + wide; ps.hit = f + 2 * wide; ps.thr = f + 3 * wide; ps.prev = f + 4 * wide; ps.misc = f + 5 * wide;
@@ -92,9 +101,11 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	wp.conditional.handle = ctl.cond; wp.conditional.type = cudaGraphCondTypeWhile; wp.conditional.size = 1;
 	MTSB_CUDA(cudaGraphAddNode(&nWhile, g, &nBegin, 1, &wp));
 	cudaGraph_t body = wp.conditional.phGraph_out[0];
+	uint32_t suspendAfter = suspend_after(r);
 	void *aTrace[] = { &S, &ps };
+	void *aExtend[] = { &S, &ps, &suspendAfter };
 	void *aShade[] = { &S, &ps, &integ, &seed };
-	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aExtend, scene));
 	MTSB_CUDA(add_kernel(body, &n2, n1, (void *) shade_kernel, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
 	MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_kernel<true> : (void *) connect_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	MTSB_CUDA(add_kernel(body, &n4, n3, (void *) advance_kernel, 1, 1, aCtl, nullptr));
@@ -139,18 +150,20 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		LoopCtl ctl; ctl.tailBelow = 0; ctl.maxBounces = 2; ctl.inGraph = 0; ctl.cond = 0;
 		const unsigned fanGrid = std::min(blocks_for(g.count, RENDER_BLOCK), (unsigned) ctx->smCount * 16u);
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
-		MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
+		MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
 		direct_head_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed, fan);
 		MTSB_CHECK(launch_trav(scene, scene->curved ? connect_fan_kernel<true> : connect_fan_kernel<false>, sh.traceGrid, st, S, ps));
 		if (M > 0) {
 			fan_flip_kernel<<<1, 1, 0, st>>>(ps);
-			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
 			direct_tail_kernel<<<fanGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, fan);
 		}
 		r->launches += M > 0 ? 7 : 4;
 	} else if (ctx->useGraph && !r->graphFailed) {
 		if (!r->bounceExec || r->graphKey != (const void *) r->bufF4.ptr || r->graphTail != (int) tailBelow) {
-			if (build_bounce_graph(r, sh, tailBelow, bounded) < 0) {
+			// parked rays cost their paths extra trips round the loop; it ends when nothing is alive, whatever the bound
+			const uint32_t loopBound = suspend_after(r) && bounded < 0x10000000u ? bounded * 4u + 16u : bounded;
+			if (build_bounce_graph(r, sh, tailBelow, loopBound) < 0) {
 				// a driver without conditional graph nodes: the same kernels as plain launches (still no host round trip)
 				cudaGetLastError();
 				destroy_bounce_graph(r);
@@ -170,7 +183,7 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		ctl.maxBounces = (maxDepth > 0 || poll) ? bounded : 16u;
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
-			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps));
+			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
 			shade_kernel<<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
 			MTSB_CHECK(launch_trav(scene, scene->curved ? connect_kernel<true> : connect_kernel<false>, sh.traceGrid, st, S, ps));
 			advance_kernel<<<1, 1, 0, st>>>(ps, ctl);

@@ -162,7 +162,9 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	uint32_t *queueOut = parity ? ps.queueA : ps.queueB;
 	uint32_t *countOut = ps.counters + (parity ^ 1u), *countShadow = ps.counters + CTR_SHADOW;
 	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		const uint32_t slot = queueIn[i];
+		const uint32_t slot = QUEUE_SLOT(queueIn[i]);
+		// a slot whose ray the extend stage parked is not shaded yet: it travels on to the next bounce's queue, flagged
+		if (__float_as_uint(ps.hit[slot].w) == SUSPENDED_SLOT) { queueOut[warp_append(countOut)] = slot | QUEUE_RESUME; continue; }
 		ShadeOut so;
 		shade_path(S, ps, integ, seed, slot, so);
 		if (so.alive) queueOut[warp_append(countOut)] = slot;

@@ -87,7 +87,7 @@ tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 			base = __shfl_sync(FULL, base, 0);
 			if (!have) {
 				const unsigned long long idx = base + __popc(idleMask & ltMask);
-				if (idx < n) { slot = queue[idx]; have = true; }
+				if (idx < n) { slot = queue[idx]; have = true; }      // may carry QUEUE_RESUME: first extend below picks the parked ray up
 			}
 			if (base + nIdle >= n) exhausted = true;
 		}
@@ -95,12 +95,17 @@ tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 
 		// ---- extend: ShapeKDTree::rayIntersect(ray, its) for the path's current ray
 		if (have) {
+			const bool parked = (slot & QUEUE_RESUME) != 0;
+			slot = QUEUE_SLOT(slot);
 			const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot];
 			tv.o = v3(r0.x, r0.y, r0.z); tv.d = v3(r1.x, r1.y, r1.z);
 			float tmax; V3 rcp;
-			++nClosest;
-			if (clip_ray(S, tv.o, tv.d, r0.w, r1.w, true, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
-			else tv.found = false;
+			if (parked) tv.restore(ps.susp + (size_t) slot * MTSB_SUSP_WORDS);
+			else {
+				++nClosest;
+				if (clip_ray(S, tv.o, tv.d, r0.w, r1.w, true, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
+				else tv.found = false;
+			}
 		}
 		trace_warp<false, CURVED>(S, tv);
 		ShadeOut so; so.alive = false; so.shadow = false;

@@ -80,6 +80,7 @@ int mtsb_ctx_create(int device, mtsb_ctx **out) {
 	ctx->tailPaths = 1 << 17;
 	if (const char *e = getenv("MTSB_TAIL_PATHS")) ctx->tailPaths = std::max(0, atoi(e));
 	if (const char *e = getenv("MTSB_GRAPH")) ctx->useGraph = atoi(e) != 0;
+	if (const char *e = getenv("MTSB_SUSPEND_AFTER")) ctx->suspendAfter = std::max(0, atoi(e));
 	if (const char *e = getenv("MTSB_SHADE_WAVES")) ctx->shadeWaves = std::max(0, atoi(e));
 	// L2 residency: set aside as much persisting L2 as the device grants (B200: 126 MB of L2); the traversal launches
 	// L2 residency of acceleration structures (scene.cuh: l2_window / l2_claim): only the ceiling is fixed here; the

@@ -19,6 +19,7 @@ enum { MODE_CLOSEST = 0, MODE_ANY = 1, MODE_SURFACE = 2, MODE_LIGHT = 3 };
 // Ray source / record sink of the batched C-ABI queries: AoS mtsb_ray in, mtsb_hit / byte / mtsb_surface out.
 template <int MODE>
 struct BatchIO {
+	static constexpr bool CAN_SUSPEND = false;
 	SceneDev S;
 	const float4 *__restrict__ rays;
 	void *__restrict__ out;

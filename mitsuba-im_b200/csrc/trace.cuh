@@ -23,6 +23,8 @@ namespace mtsb {
 #define MTSB_STACK_SHARED 8      // stack entries per thread kept in shared memory
 #define MTSB_STACK_LOCAL  56     // overflow entries in local memory
 #define MTSB_TRACE_BLOCK  128    // threads per block of every traversal kernel
+#define MTSB_SUSP_STACK   32     // deepest stack a suspended ray can carry (deeper ones keep running)
+#define MTSB_SUSP_WORDS   (5 + MTSB_SUSP_STACK)   // uint2 words of a suspension record (Trav::save)
 #ifndef MTSB_TRACE_BLOCKS_PER_SM
 #define MTSB_TRACE_BLOCKS_PER_SM 8   // resident CTAs per SM of the persistent traversal grids (bounds the register budget)
 #endif
@@ -279,6 +281,29 @@ struct Trav {
 		found = false; st.n = 0; active = true;
 	}
 
+	// Suspension (extend stage of the wavefront, render.cu): a ray that is still traversing when its launch has run out of
+	// other work parks its whole state — pending groups, best hit, stack — in MTSB_SUSP_WORDS 8-byte words and is picked up
+	// again by the next launch, so that a launch lasts as long as its typical rays, not as its longest one.
+	__device__ __forceinline__ void save(uint2 *rec) const {
+		rec[0] = ng; rec[1] = tg;
+		rec[2] = make_uint2(__float_as_uint(hit.t), __float_as_uint(hit.u));
+		rec[3] = make_uint2(__float_as_uint(hit.v), hit.slot);
+		rec[4] = make_uint2((uint32_t) st.n | (found ? 0x80000000u : 0u), __float_as_uint(tmin));
+		for (int k = 0; k < st.n; ++k) rec[5 + k] = k < MTSB_STACK_SHARED ? st.sh[k * MTSB_TRACE_BLOCK] : st.loc[k - MTSB_STACK_SHARED];
+	}
+	// o and d already set (from the path's ray); everything else comes back from the record
+	__device__ __forceinline__ void restore(const uint2 *rec) {
+		const V3 rcp = v3(d.x != 0 ? __frcp_rn(d.x) : 0.0f, d.y != 0 ? __frcp_rn(d.y) : 0.0f, d.z != 0 ? __frcp_rn(d.z) : 0.0f);   // as clip_ray
+		begin(0.0f, rcp);
+		ng = rec[0]; tg = rec[1];
+		const uint2 h0 = rec[2], h1 = rec[3], m = rec[4];
+		hit.t = __uint_as_float(h0.x); hit.u = __uint_as_float(h0.y); hit.v = __uint_as_float(h1.x); hit.slot = h1.y;
+		found = (m.x & 0x80000000u) != 0; tmin = __uint_as_float(m.y);
+		const int n = (int) (m.x & 0xffffu);
+		st.n = 0;
+		for (int k = 0; k < n; ++k) st.push(rec[5 + k]);
+	}
+
 	// One iteration: node phase, triangle phase, pop-or-finish.  Must be called by all 32 lanes of the warp (it ballots).
 	// Returns true for the lanes whose ray finished in this iteration (`active` is already false for them).
 	// CURVED: the scene holds analytic disks / spheres.  Their leaf test sits behind a real call whose register traffic cost
@@ -357,14 +382,14 @@ struct Trav {
 //   void IO::store(i, found, hit, o, d)
 template <bool ANY, bool COUNT, bool CURVED, class IO>
 __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsigned long long n,
-		unsigned long long *__restrict__ workCounter, uint2 *shStack) {
+		unsigned long long *__restrict__ workCounter, uint2 *shStack, unsigned suspendAfter = 0) {
 	const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
 	const unsigned FULL = 0xffffffffu;
 	bool exhausted = false;
 	uint2 locStack[MTSB_STACK_LOCAL];
 	Trav tv; tv.init(shStack, locStack);
 	unsigned long long idx = 0;
-	unsigned nNodes = 0, nTris = 0;
+	unsigned nNodes = 0, nTris = 0, sinceExhausted = 0;
 	const uint32_t one = S.oneBits;                 // 1.0f bit pattern from the parameter bank (see q_to_unit)
 
 	for (;;) {
@@ -379,12 +404,21 @@ __device__ __forceinline__ void trace_persistent(const SceneDev &S, IO &io, unsi
 				idx = base + __popc(idleMask & ltMask);
 				if (idx < n) {
 					float tmax; V3 rcp;
-					if (io.load(idx, tv.o, tv.d, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
+					const int how = io.load(idx, tv.o, tv.d, tv.tmin, tmax, rcp);     // 0: no traversal, 1: fresh ray, 2: suspended ray
+					if (how == 1) tv.begin(tmax, rcp);
+					else if constexpr (IO::CAN_SUSPEND) { if (how == 2) io.resume(idx, tv); }
 				}
 			}
 			if (base + nIdle >= n) exhausted = true;
 		}
 		if (!__any_sync(FULL, tv.active)) { if (exhausted) break; else continue; }
+		// ---- suspension: the queue is empty and this warp has spent its allowance on what is left -> park it
+		if constexpr (IO::CAN_SUSPEND) {
+			if (suspendAfter && exhausted && ++sinceExhausted > suspendAfter) {
+				if (tv.active && tv.st.n <= MTSB_SUSP_STACK) { io.suspend(idx, tv); tv.active = false; }
+				// (lanes with a deeper stack run on until it fits, or they finish)
+			}
+		}
 		// ---- (2)-(4)
 		if (tv.template step<ANY, COUNT, CURVED>(S, one, nNodes, nTris)) io.store(idx, tv.found, tv.hit, tv.o, tv.d);
 	}
