@@ -288,6 +288,13 @@ MTSB_API int  mtsb_film_to_host(mtsb_render *r, float *dst, size_t float_count, 
  * (the ResponsiveIntegrator adapter; the reference's counterpart is ImageBlock::putAtomic, imageblock.h:223-318).
  * The pointer stays valid until the next mtsb_film_stage / mtsb_film_to_host(accumulate) / mtsb_render_destroy. */
 MTSB_API int  mtsb_film_stage(mtsb_render *r, const float **stage_out, size_t *float_count_out);
+/* The same hand-over split in two, so that the host's share of it overlaps the next pass: _begin queues, in stream order,
+ * the copy of the film into the render's page-locked staging buffer and the clearing of the film — passes queued afterwards
+ * accumulate into the cleared film; _wait blocks until the COPY has landed (not until the stream is idle) and returns the
+ * staging buffer.  One flush at a time per render.  (ResponsiveIntegrator: un-normalised sums are added to the caller's
+ * ImageBlock while the device renders on, include/mitsuba/render/integrator2.h:49-100.) */
+MTSB_API int  mtsb_film_flush_begin(mtsb_render *r);
+MTSB_API int  mtsb_film_flush_wait(mtsb_render *r, const float **stage_out, size_t *float_count_out);
 /* Statistics of the passes since the last clear: out[0]=camera paths, out[1]=closest-hit rays,
  * out[2]=shadow rays, out[3]=sum of path depths (avgPathLength numerator, path.cpp:290-291),
  * out[4]=kernel launches. */

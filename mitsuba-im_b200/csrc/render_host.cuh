@@ -270,6 +270,7 @@ void mtsb_render_destroy(mtsb_render *r) {
 	cudaStreamSynchronize(r->stream);                 // passes are asynchronous: nothing of this render may still be queued
 	if (r->ownStream) cudaStreamDestroy(r->stream);
 	if (r->hostStage) cudaFreeHost(r->hostStage);
+	if (r->flushDone) cudaEventDestroy(r->flushDone);
 	destroy_bounce_graph(r);
 	delete r;
 }
@@ -396,6 +397,29 @@ int mtsb_film_stage(mtsb_render *r, const float **stage_out, size_t *float_count
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	*stage_out = r->hostStage;
 	if (float_count_out) *float_count_out = n;
+	return 0;
+}
+
+int mtsb_film_flush_begin(mtsb_render *r) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_flush_begin: NULL argument");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	cudaStream_t st = r->stream;
+	const size_t n = r->dFilm.count;
+	if (!r->hostStage) MTSB_CUDA(cudaMallocHost((void **) &r->hostStage, n * sizeof(float)));
+	if (!r->flushDone) MTSB_CUDA(cudaEventCreateWithFlags(&r->flushDone, cudaEventDisableTiming));
+	// in stream order: [passes queued so far] -> film to the staging buffer -> film cleared -> [passes queued from now on]
+	MTSB_CUDA(cudaMemcpyAsync(r->hostStage, r->dFilm.ptr, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaEventRecord(r->flushDone, st));
+	MTSB_CUDA(cudaMemsetAsync(r->dFilm.ptr, 0, r->dFilm.bytes(), st));
+	return 0;
+}
+
+int mtsb_film_flush_wait(mtsb_render *r, const float **stage_out, size_t *float_count_out) {
+	if (!r || !stage_out || !r->flushDone) MTSB_FAIL(MTSB_EINVAL, "mtsb_film_flush_wait: NULL argument or no flush begun");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	MTSB_CUDA(cudaEventSynchronize(r->flushDone));       // the copy only — passes queued after flush_begin keep running
+	*stage_out = r->hostStage;
+	if (float_count_out) *float_count_out = r->dFilm.count;
 	return 0;
 }
 

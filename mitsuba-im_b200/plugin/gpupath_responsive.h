@@ -182,20 +182,28 @@ int GPUResponsiveIntegrator::render(const Scene &scene, const Sensor &sensor, Sa
 		if (controls.continu && !*controls.continu) return fin.rc = -2;
 		// flush policy: first pass at once, then geometrically (or every 250 ms), and always at the end of the share
 		const uint32_t unflushed = queued - landed;
-		if (unflushed && (queued >= mine || unflushed >= std::max(1u, landed / 2) || sinceFlush->getMilliseconds() >= 250)) {
+		const bool flush = unflushed && (queued >= mine || unflushed >= std::max(1u, landed / 2) || sinceFlush->getMilliseconds() >= 250);
+		if (flush) {
+			// in stream order: film -> staging buffer, film cleared; whatever is queued next accumulates into the cleared film
+			MTSB_CALL(mtsb_film_flush_begin(r));
+		}
+		const uint32_t flushedUpTo = queued;
+		// queue the next pass BEFORE the host's share of the flush, so that the device renders while the host adds
+		if (queued < mine) {
+			const uint32_t cnt = std::min(pass, mine - queued);
+			tt->reset();
+			MTSB_CALL(mtsb_render_pass(r, queued * G, cnt, sampleCount, NULL, (uint32_t) G, (uint32_t) gpu));
+			tSubmit += tt->getMicroseconds() * 1e-3;
+			queued += cnt;
+			pass = std::min(passCap, pass * 4);
+			++sinceSync;
+		}
+		if (flush) {
 			const float *src = NULL; size_t cnt = 0;
 			tt->reset();
-			MTSB_CALL(mtsb_film_stage(r, &src, &cnt));     // waits for the passes queued so far
+			MTSB_CALL(mtsb_film_flush_wait(r, &src, &cnt));    // waits for the copy, not for the pass queued above
 			tStage += tt->getMicroseconds() * 1e-3;
 			if (cnt != n) Log(EError, "gpupath: target holds %zu floats, the device film %zu", n, cnt);
-			if (threadIdx == 0) {
-				uint64_t st[8]; mtsb_render_stats(r, st);
-				char buf[160];
-				snprintf(buf, sizeof(buf), "GPU wavefront: %.2f rays/sample, avg path length %.2f", st[0] ? (double) (st[1] + st[2]) / st[0] : 0.0,
-					st[0] ? (double) st[3] / st[0] : 0.0);
-				m_stats = buf;
-			}
-			MTSB_CALL(mtsb_render_clear(r));
 			tt->reset();
 			{
 				// only leaders write targets; they can meet in one ImageBlock when the caller shares it between GPUs' threads
@@ -203,31 +211,32 @@ int GPUResponsiveIntegrator::render(const Scene &scene, const Sensor &sensor, Sa
 				for (size_t i = 0; i < n; ++i) dst[i] += src[i];
 			}
 			tAdd += tt->getMicroseconds() * 1e-3;
-			landed = queued;
+			landed = flushedUpTo;
 			{ LockGuard lock(p->m_mutex); grp.landed = (double) landed; }
 			sinceFlush->reset();
 			sinceSync = 0;
+		} else if (sinceSync >= 4) {
+			// keep at most a few passes in flight so that abort / camera changes take effect within a few waves
+			MTSB_CALL(mtsb_render_sync(r)); sinceSync = 0;
 		}
 		if (controls.interrupt) {
 			tt->reset();
 			const int rc = controls.interrupt->progress(this, scene, sensor, sampler, target, (double) landed / groupSize, controls, threadIdx, threadCount);
 			tProgress += tt->getMicroseconds() * 1e-3;
-			if (rc != 0) return fin.rc = rc;
+			if (rc != 0) { mtsb_render_sync(r); return fin.rc = rc; }
 		}
-		if (queued >= mine) {                            // "sampler exhausted"
-			if (timing) SLog(EInfo, "gpupath: leader %d (group of %d): %.2f ms in render(); submit %.2f, stage (sync + D2H) %.2f, add %.2f, progress %.2f ms",
+		if (landed >= mine) {                            // "sampler exhausted" — and everything is in the target
+			if (threadIdx == 0) {
+				uint64_t st[8]; mtsb_render_stats(r, st);
+				char buf[160];
+				snprintf(buf, sizeof(buf), "GPU wavefront: %.2f rays/sample, avg path length %.2f", st[0] ? (double) (st[1] + st[2]) / st[0] : 0.0,
+					st[0] ? (double) st[3] / st[0] : 0.0);
+				m_stats = buf;
+			}
+			if (timing) SLog(EInfo, "gpupath: leader %d (group of %d): %.2f ms in render(); submit %.2f, flush wait %.2f, add %.2f, progress %.2f ms",
 				threadIdx, groupSize, self_now() - tEnter, tSubmit, tStage, tAdd, tProgress);
 			return fin.rc = 0;
 		}
-		const uint32_t cnt = std::min(pass, mine - queued);
-		tt->reset();
-		// queueing only: mtsb_render_pass does not wait for the device
-		MTSB_CALL(mtsb_render_pass(r, queued * G, cnt, sampleCount, NULL, (uint32_t) G, (uint32_t) gpu));
-		tSubmit += tt->getMicroseconds() * 1e-3;
-		queued += cnt;
-		pass = std::min(passCap, pass * 4);
-		// keep at most a few passes in flight so that abort / camera changes take effect within a few waves
-		if (++sinceSync >= 4) { MTSB_CALL(mtsb_render_sync(r)); sinceSync = 0; }
 	}
 }
 
