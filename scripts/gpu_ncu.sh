@@ -1,5 +1,6 @@
 # ncu evidence for the two halves of the hot path (B200_PROFILING.md recipe). Each ncu run follows a plain run of the same command.
 T="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-path"
+export MTSB_GRAPH=0   # ncu does not list the kernels inside a conditional graph node: same kernels as plain launches
 R1="python bench_render.py --config 1 --no-cpu"
 R3="python bench_render.py --config 3 --no-cpu --spp3 8"
 $T > gpurun_out/ncu_plain_trace.log 2>&1 &&
