@@ -134,6 +134,11 @@ __device__ inline V3 roughdielectric_sample(const BsdfRec &b, const V3 &wi, floa
 }
 
 
+// LEAN: the scene's BSDFs are all of {diffuse, null, dielectric, roughconductor with GGX + visible-normal sampling} (the
+// set of configs 1, 3, 4, 5).  The other cases are then unreachable and their code — rough dielectric, Beckmann's
+// visible-normal inversion, plastic, smooth conductor — is left out of the kernel: the full shade kernel stalls 6-11
+// cycles per issue on instruction fetch on config 3 (profiles/r02m_ncu_full_render.json).
+template <bool LEAN = false>
 __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 	switch (b.type & 0xff) {
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL: {
@@ -141,8 +146,9 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 			return v3(b.p[0], b.p[1], b.p[2]) * (MTS_INV_PI * wo.z);
 		}
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return v3(0.0f);     // discrete measure only
-		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_eval(b, wi, wo);
+		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_eval(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
+			if (LEAN) __builtin_unreachable();
 			if (wo.z <= 0 || wi.z <= 0) return v3(0.0f);
 			const float eta = b.p[0];
 			const float Fi = fresnel_dielectric_ext(wi.z, eta), Fo = fresnel_dielectric_ext(wo.z, eta);
@@ -151,7 +157,7 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 		default: {
 			if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
 			const V3 H = normalize(wo + wi);
-			Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+			Microfacet distr; distr.init(LEAN ? 1 : (int) b.p[11], b.p[0], b.p[1], LEAN ? true : b.p[12] != 0);
 			const float D = distr.eval(H);
 			if (D == 0) return v3(0.0f);
 			const V3 F = fresnel_conductor_exact(dot(wi, H), v3(b.p[2], b.p[3], b.p[4]), v3(b.p[5], b.p[6], b.p[7])) * v3(b.p[8], b.p[9], b.p[10]);
@@ -161,14 +167,16 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 	}
 }
 
+template <bool LEAN = false>
 __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 	switch (b.type & 0xff) {
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL:
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return MTS_INV_PI * wo.z;
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return 0.0f;
-		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_pdf(b, wi, wo);
+		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_pdf(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
+			if (LEAN) __builtin_unreachable();
 			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
 			const float Fi = fresnel_dielectric_ext(wi.z, b.p[0]);
 			return MTS_INV_PI * wo.z * (1 - plastic_prob_specular(b, Fi));
@@ -184,6 +192,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 }
 
 // returns the importance weight (f cos / pdf); zero weight = failed sample
+template <bool LEAN = false>
 __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, float sy, float sz, BsdfSample &out) {
 	out.pdf = 0; out.eta = 1.0f; out.type = 0; out.wo = v3(0.0f);
 	switch (b.type & 0xff) {
@@ -211,6 +220,7 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			return v3(b.p[4], b.p[5], b.p[6]) * (factor * factor);
 		}
 		case MTSB_BSDF_PLASTIC: {
+			if (LEAN) __builtin_unreachable();
 			if (wi.z <= 0) return v3(0.0f);
 			const float eta = b.p[0];
 			const float Fi = fresnel_dielectric_ext(wi.z, eta);
@@ -225,15 +235,16 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			out.pdf = (1 - probSpecular) * (MTS_INV_PI * out.wo.z);
 			return plastic_diffuse(b) * ((1 / (eta * eta)) * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
 		}
-		case MTSB_BSDF_ROUGHDIELECTRIC: return roughdielectric_sample(b, wi, sx, sy, sz, out);
+		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_sample(b, wi, sx, sy, sz, out);
 		case MTSB_BSDF_CONDUCTOR: {                                // conductor.cpp:214-235
+			if (LEAN) __builtin_unreachable();
 			if (wi.z <= 0) return v3(0.0f);
 			out.type = B_DELTA_REFL; out.wo = v3(-wi.x, -wi.y, wi.z); out.pdf = 1.0f;
 			return v3(b.p[6], b.p[7], b.p[8]) * fresnel_conductor_exact(wi.z, v3(b.p[0], b.p[1], b.p[2]), v3(b.p[3], b.p[4], b.p[5]));
 		}
 		default: {
 			if (wi.z < 0) return v3(0.0f);
-			Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[1], b.p[12] != 0);
+			Microfacet distr; distr.init(LEAN ? 1 : (int) b.p[11], b.p[0], b.p[1], LEAN ? true : b.p[12] != 0);
 			float pdf;
 			const V3 m = distr.sample(wi, sx, sy, pdf);
 			if (pdf == 0) return v3(0.0f);
@@ -251,22 +262,25 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 }
 
 // --- public entry points: add the twosided adapter ---
+template <bool LEAN = false>
 __device__ inline V3 bsdf_eval(const BsdfRec &b, V3 wi, V3 wo) {
 	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && !(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; }
-	return bsdf_eval_1(b, wi, wo);
+	return bsdf_eval_1<LEAN>(b, wi, wo);
 }
+template <bool LEAN = false>
 __device__ inline float bsdf_pdf(const BsdfRec &b, V3 wi, V3 wo) {
 	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && !(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; }
-	return bsdf_pdf_1(b, wi, wo);
+	return bsdf_pdf_1<LEAN>(b, wi, wo);
 }
 // true for the plugins whose sample() takes one more draw from bRec.sampler (EUsesSampler); the caller draws it
 // right after the 2D sample, which is where the plugin's next1D() lands in the stream
 __device__ inline bool bsdf_uses_sampler(const BsdfRec &b) { return (b.type & 0xff) == MTSB_BSDF_ROUGHDIELECTRIC; }
 
+template <bool LEAN = false>
 __device__ inline V3 bsdf_sample(const BsdfRec &b, V3 wi, float sx, float sy, float sz, BsdfSample &out) {
 	bool flipped = false;
 	if ((b.type & MTSB_BSDF_TWOSIDED_FLAG) && wi.z < 0) { wi.z = -wi.z; flipped = true; }
-	const V3 w = bsdf_sample_1(b, wi, sx, sy, sz, out);
+	const V3 w = bsdf_sample_1<LEAN>(b, wi, sx, sy, sz, out);
 	if (flipped && !is_zero(w) && out.pdf != 0) out.wo.z = -out.wo.z;
 	return w;
 }

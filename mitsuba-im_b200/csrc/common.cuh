@@ -166,6 +166,7 @@ struct mtsb_ctx {
 	                                       // (measured on config 3: 277 M samples/s against 248-255 for 1-16 waves of a grid-stride loop)
 	int suspendAfter = 0;                  // MTSB_SUSPEND_AFTER: warp iterations before the extend stage parks its remaining rays (0 = off,
 	                                       // the default: measured +3 % on config 5 at 24, nothing elsewhere — DESIGN.md 10.2)
+	int shadeLean = 1;                     // MTSB_SHADE_LEAN: scenes whose BSDFs allow it shade with the kernel compiled without the rest (bsdf.cuh)
 	int useGraph = 1;                      // MTSB_GRAPH: bounce loop as a CUDA graph with a device-driven WHILE node (0 = plain launches)
 	// L2 residency of the acceleration structure (cudaAccessPolicyWindow, see l2_window in scene.cuh)
 	size_t l2PersistMax = 0;               // ceiling of the persisting set-aside (device maximum, or MTSB_L2_PERSIST in MB; 0 = off)

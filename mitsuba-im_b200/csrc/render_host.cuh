@@ -106,7 +106,7 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	void *aExtend[] = { &S, &ps, &suspendAfter };
 	void *aShade[] = { &S, &ps, &integ, &seed };
 	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aExtend, scene));
-	MTSB_CUDA(add_kernel(body, &n2, n1, (void *) shade_kernel, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+	MTSB_CUDA(add_kernel(body, &n2, n1, scene->lean ? (void *) shade_kernel<true> : (void *) shade_kernel<false>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
 	MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_kernel<true> : (void *) connect_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	MTSB_CUDA(add_kernel(body, &n4, n3, (void *) advance_kernel, 1, 1, aCtl, nullptr));
 	if (tailBelow) MTSB_CUDA(add_kernel(g, &nTail, nWhile, scene->curved ? (void *) tail_kernel<true> : (void *) tail_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aShade, scene));
@@ -184,7 +184,8 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
 			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
-			shade_kernel<<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+			if (scene->lean) shade_kernel<true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+			else shade_kernel<false><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
 			MTSB_CHECK(launch_trav(scene, scene->curved ? connect_kernel<true> : connect_kernel<false>, sh.traceGrid, st, S, ps));
 			advance_kernel<<<1, 1, 0, st>>>(ps, ctl);
 			if (poll && (bounce & 7) == 7) {

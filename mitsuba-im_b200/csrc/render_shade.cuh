@@ -14,6 +14,7 @@ __device__ __forceinline__ float mi_weight(float pdfA, float pdfB) {   // path.c
 struct ShadeOut { bool alive, shadow; float4 shO, shD, shL; };
 
 // One shading step of one path; state lives in ps.*[slot].  Line references are to src/integrators/path/path.cpp.
+template <bool LEAN = false>
 __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, ShadeOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
@@ -105,11 +106,11 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 				const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
 				if (!is_zero(value)) {
 					const V3 wo = to_local(sf, ds.d);
-					const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
+					const V3 bsdfVal = bsdf_eval<LEAN>(bsdf, wi, wo);
 					if (!is_zero(bsdfVal) && (!integ.strictNormals || dot(sf.ng, ds.d) * wo.z > 0)) {
 						// Emitter::isOnSurface(): area (area.cpp:72) and constant environment (constant.cpp:50) set EOnSurface, point does not
 						const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
-						const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf(bsdf, wi, wo) : 0;
+						const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf<LEAN>(bsdf, wi, wo) : 0;
 						const V3 c = thr * value * bsdfVal * mi_weight(ds.pdf, bp);
 						shadow = true;      // visibility test of Scene::sampleEmitterDirect (scene.cpp:871-876), deferred to `connect`
 						shO = make_float4(sf.p.x, sf.p.y, sf.p.z, MTS_EPSILON);
@@ -120,9 +121,9 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 			}
 			// ---- BSDF sampling (:205-222)
 			next2D(rs, sx, sy);
-			const float sz = bsdf_uses_sampler(bsdf) ? next1D(rs) : 0.0f;
+			const float sz = (!LEAN && bsdf_uses_sampler(bsdf)) ? next1D(rs) : 0.0f;
 			BsdfSample bs;
-			const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, sz, bs);
+			const V3 bsdfWeight = bsdf_sample<LEAN>(bsdf, wi, sx, sy, sz, bs);
 			if (is_zero(bsdfWeight)) alive = false;
 			else {
 				flags |= PF_SCATTERED;
@@ -154,6 +155,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 #ifndef MTSB_SHADE_MIN_BLOCKS
 #define MTSB_SHADE_MIN_BLOCKS 5
 #endif
+template <bool LEAN>
 __global__ void __launch_bounds__(RENDER_BLOCK, MTSB_SHADE_MIN_BLOCKS)
 shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
@@ -166,7 +168,7 @@ shade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 		// a slot whose ray the extend stage parked is not shaded yet: it travels on to the next bounce's queue, flagged
 		if (__float_as_uint(ps.hit[slot].w) == SUSPENDED_SLOT) { queueOut[warp_append(countOut)] = slot | QUEUE_RESUME; continue; }
 		ShadeOut so;
-		shade_path(S, ps, integ, seed, slot, so);
+		shade_path<LEAN>(S, ps, integ, seed, slot, so);
 		if (so.alive) queueOut[warp_append(countOut)] = slot;
 		if (so.shadow) {
 			const uint32_t k = warp_append(countShadow);

@@ -80,6 +80,7 @@ int mtsb_ctx_create(int device, mtsb_ctx **out) {
 	ctx->tailPaths = 1 << 17;
 	if (const char *e = getenv("MTSB_TAIL_PATHS")) ctx->tailPaths = std::max(0, atoi(e));
 	if (const char *e = getenv("MTSB_GRAPH")) ctx->useGraph = atoi(e) != 0;
+	if (const char *e = getenv("MTSB_SHADE_LEAN")) ctx->shadeLean = atoi(e) != 0;
 	if (const char *e = getenv("MTSB_SUSPEND_AFTER")) ctx->suspendAfter = std::max(0, atoi(e));
 	if (const char *e = getenv("MTSB_SHADE_WAVES")) ctx->shadeWaves = std::max(0, atoi(e));
 	// L2 residency: set aside as much persisting L2 as the device grants (B200: 126 MB of L2); the traversal launches
@@ -394,6 +395,13 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));
+	scene->lean = !(ctx->shadeLean == 0);
+	for (const BsdfRec &b : scene->bsdfs) {
+		const int t = b.type & 0xff;
+		const bool ok = t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_NULL || t == MTSB_BSDF_DIELECTRIC ||
+			(t == MTSB_BSDF_ROUGHCONDUCTOR && b.p[11] == 1.0f && b.p[12] != 0.0f);
+		if (!ok) scene->lean = false;
+	}
 	mtsb::l2_claim(scene, scene->bvh.accel.bytes());
 	scene->committed = true;
 	return 0;

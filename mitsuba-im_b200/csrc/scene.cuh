@@ -10,6 +10,7 @@ namespace mtsb { struct TracePipe; }
 struct mtsb_scene {
 	mtsb_ctx *ctx = nullptr;
 	bool committed = false;
+	bool lean = false;                    // every BSDF is diffuse / null / dielectric / GGX roughconductor with visible-normal sampling (bsdf.cuh: LEAN)
 	bool curved = false;                  // holds analytic disks / spheres: traversal kernels with their leaf test (trace.cuh)
 
 	// host staging (filled by mtsb_scene_add_*)
