@@ -680,7 +680,7 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 		MTSB_CUDA(cudaMemcpyAsync(&inCount, counters.ptr + 2, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		MTSB_CUDA(cudaStreamSynchronize(st));
 		std::swap(qi, qo); ++depth;
-		if (depth > 256) MTSB_FAIL(MTSB_EINVAL, "build_bvh: collapse did not terminate");
+		if (depth > 256) MTSB_FAIL(MTSB_EINVAL, "build_bvh: wide tree is more than 256 levels deep, the traversal stack holds 64 (degenerate geometry: many coincident primitives? the LBVH builder copes with them)");
 	}
 	uint32_t fin[8];
 	MTSB_CUDA(cudaMemcpy(fin, counters.ptr, sizeof(fin), cudaMemcpyDeviceToHost));

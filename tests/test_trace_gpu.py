@@ -70,6 +70,55 @@ def test_hits_match_reference_golden(pkg, ctx, golden, kind, builder):
         sc.close()
 
 
+@pytest.mark.parametrize("builder", [0, 1])
+def test_thousands_of_coincident_triangles(pkg, ctx, builder):
+    """Degenerate input: 4096 copies of the SAME triangle (identical centroids -> identical Morton keys) beside a normal
+    mesh.  The wide tree either stays inside the traversal stack (8 shared + 56 local entries) and every ray through the
+    stack of triangles hits one of them at the exact distance, or the build refuses the scene with MTSB_EINVAL — what must
+    not happen is a silently dropped stack entry, i.e. a missed hit."""
+    S, B = pkg.scenes, pkg.binding
+    n = 4096
+    tri = np.array([[-1, -1, 2.0], [1, -1, 2.0], [0, 1, 2.0]], np.float32)
+    V = np.tile(tri, (n, 1))
+    F = np.arange(3 * n, dtype=np.uint32).reshape(n, 3)
+    sd = S.SceneDesc()
+    sd.add_mesh(V, None, F)
+    Vs, Ns, Fs = S.displaced_sphere(3, seed=2, radius=0.5, center=(0, 0, -2.0))
+    sd.add_mesh(Vs, Ns, Fs)
+    sd.add_point_light((0, 5, 0), (1, 1, 1))
+    try:
+        sc = sd.upload(ctx, builder)
+    except B.MtsbError as e:
+        assert "levels deep" in str(e) or "degenerate" in str(e), str(e)
+        return
+    try:
+        rng = np.random.default_rng(3)
+        m = 4096
+        rays = np.zeros(m, B.ray_dtype)
+        # rays from z = 0 towards points inside the triangle (barycentric, away from the edges)
+        b = rng.dirichlet((2, 2, 2), m).astype(np.float32)
+        tgt = b @ tri
+        rays["o"] = np.array([0.1, -0.1, 0.0], np.float32)
+        d = tgt - rays["o"]
+        dist = np.linalg.norm(d, axis=1)
+        rays["d"] = d / dist[:, None]
+        rays["mint"] = 0.0
+        rays["maxt"] = np.inf
+        h = sc.ray_intersect(rays)
+        assert (h["prim"] < n).all(), "a ray through 4096 coincident triangles missed all of them"
+        assert np.abs(h["t"] - dist).max() <= 1e-5 * 3
+        assert sc.ray_intersect_any(rays).all()
+        # and the other mesh is still found behind the camera side
+        back = rays.copy()
+        back["d"] = -rays["d"] * np.array([0, 0, 1], np.float32) + np.array([0, 0, 0], np.float32)
+        back["d"] = np.array([0, 0, -1.0], np.float32)
+        back["o"] = np.stack([rng.uniform(-0.2, 0.2, m), rng.uniform(-0.2, 0.2, m), np.zeros(m)], axis=1).astype(np.float32)
+        hb = sc.ray_intersect(back)
+        assert (hb["prim"][np.isfinite(hb["t"])] >= n).all() and np.isfinite(hb["t"]).mean() > 0.9
+    finally:
+        sc.close()
+
+
 def test_analytic_sphere_and_disk_match_reference(pkg, ctx, golden):
     """Analytic `sphere` (double-precision quadratic, re-projected hit point, spherical uv) and `disk` leaf primitives among
     meshes (src/shapes/sphere.cpp:158-252, disk.cpp:139-197) against hit records of the unmodified reference."""
