@@ -114,10 +114,9 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	ps.rayO[j] = make_float4(o.x, o.y, o.z, cam.nearClip * invZ);
 	ps.rayD[j] = make_float4(dw.x, dw.y, dw.z, cam.farClip * invZ);
 	ps.thr[j] = make_float4(1, 1, 1, 1);
-	ps.L[j] = make_float4(0, 0, 0, 0);
 	ps.prev[j] = make_float4(0, 0, 0, 0);
-	ps.misc[j] = make_float4(sx, sy, __uint_as_float(0u), __uint_as_float(1u));   // flags = 0, depth = 1
-	ps.rng[j] = make_uint4(px, py, sidx, rs.dim);
+	ps.misc[j] = make_float4(sx, sy, 0.0f, 0.0f);
+	ps.rng[j] = make_uint4(px, py, sidx, PATH_PACK(rs.dim, 0u, 1u));              // flags = 0, depth = 1; L is started by the first shade
 	queue[pos] = j;
 }
 

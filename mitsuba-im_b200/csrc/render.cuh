@@ -4,8 +4,8 @@
 //   rayO   {o.xyz, mint}          rayD  {d.xyz, maxt}            written by generate / shade, read by extend
 //   hit    {t, u, v, slot}                                        written by extend, read by shade
 //   thr    {throughput.rgb, eta}  L     {Li.rgb, alpha}
-//   prev   {refN.xyz, bsdfPdf}    misc  {samplePos.xy, flags, depth}
-//   rng    {px, py, sampleIndex, dim}
+//   prev   {refN.xyz, bsdfPdf}    misc  {samplePos.xy, -, -}  (written by generate, read by splat)
+//   rng    {px, py, sampleIndex, dim | flags << 16 | depth << 20}
 //   shO/shD shadow ray            shL   {contribution.rgb, path slot}   shadow queue written by shade, read by connect
 // Queues of path slots (uint32) are compacted with warp-aggregated atomics.
 #pragma once
@@ -30,6 +30,11 @@ enum { CTR_COUNT_A = 0, CTR_COUNT_B = 1, CTR_SHADOW = 2, CTR_PARITY = 3,
        CTR_TAIL = 4, CTR_TAIL_COUNT = 5, CTR_TAIL_PARITY = 6, CTR_TAIL_BOUNCE = 7, CTR_BOUNCE = 8, CTR_WORDS = 16 };
 
 enum { PF_FROM_BSDF = 1, PF_SCATTERED = 2, PF_DELTA = 4 };
+// rng.w of a path slot: sampler dimension (16 bits) | PF_* flags (4 bits) | depth (12 bits, saturating)
+#define PATH_DIM(w)    ((w) & 0xffffu)
+#define PATH_FLAGS(w)  (((w) >> 16) & 0xfu)
+#define PATH_DEPTH(w)  ((w) >> 20)
+#define PATH_PACK(dim, flags, depth) (((dim) & 0xffffu) | (((flags) & 0xfu) << 16) | (min((uint32_t) (depth), 4095u) << 20))
 
 struct CameraDev {
 	float s2c[16], c2w[16];

@@ -17,14 +17,19 @@ struct ShadeOut { bool alive, shadow; float4 shO, shD, shL; };
 template <bool LEAN = false>
 __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, ShadeOut &out) {
+	// Path state touched per bounce (HBM-bound on small scenes, so every 16 bytes count): rayO rayD hit thr prev rng are read,
+	// rayO rayD thr prev rng written.  Flags and depth ride in rng.w beside the sampler dimension (PATH_* below); the
+	// radiance L is read and written only by the bounces that add to it (an emitter was hit); the sample position stays in
+	// `misc`, written once by generate and read once by splat.
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
-	float4 thr4 = ps.thr[slot], L4 = ps.L[slot], prev = ps.prev[slot], misc = ps.misc[slot];
+	float4 thr4 = ps.thr[slot], prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = rg.w; rs.seed = seed;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed;
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
-	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(L4.x, L4.y, L4.z);
+	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);          // Li: what THIS bounce adds
 	float eta = thr4.w;
-	uint32_t flags = __float_as_uint(misc.z), depth = __float_as_uint(misc.w);
+	uint32_t flags = PATH_FLAGS(rg.w), depth = PATH_DEPTH(rg.w);
+	float alpha = 0.0f; bool first = false;
 	const uint32_t hitSlot = __float_as_uint(h.w);
 	const bool valid = hitSlot != INVALID_SLOT;
 	bool alive = true;
@@ -76,7 +81,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 		if (alive && !((int) depth <= integ.maxDepth || integ.maxDepth < 0)) alive = false;   // while condition (:135)
 	} else {
 		// ---- first iteration: the sensor ray (:129-150)
-		L4.w = valid ? 1.0f : 0.0f;                     // RadianceQueryRecord::rayIntersect sets alpha
+		first = true; alpha = valid ? 1.0f : 0.0f;      // RadianceQueryRecord::rayIntersect sets alpha
 		if (!valid) {
 			if (!integ.hideEmitters && S.envEmitter >= 0) Li += thr * S.emitters[S.envEmitter].radiance;
 			alive = false;
@@ -141,12 +146,14 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 		}
 	}
 
-	ps.L[slot] = make_float4(Li.x, Li.y, Li.z, L4.w);
-	ps.misc[slot] = make_float4(misc.x, misc.y, __uint_as_float(flags), __uint_as_float(depth));
-	if (alive) {
-		ps.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
-		ps.rng[slot] = make_uint4(rg.x, rg.y, rg.z, rs.dim);
+	if (first) ps.L[slot] = make_float4(Li.x, Li.y, Li.z, alpha);             // the sensor ray's bounce starts the sum
+	else if (!is_zero(Li)) {
+		float4 L4 = ps.L[slot];
+		L4.x += Li.x; L4.y += Li.y; L4.z += Li.z;
+		ps.L[slot] = L4;
 	}
+	ps.rng[slot] = make_uint4(rg.x, rg.y, rg.z, PATH_PACK(rs.dim, flags, depth));  // always: splat reads the depth
+	if (alive) ps.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
 	out.alive = alive; out.shadow = shadow; out.shO = shO; out.shD = shD; out.shL = shL;
 }
 
@@ -204,7 +211,7 @@ splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut, floa
 	if (j < count && ps.rng[j].x != INVALID_SLOT) {
 		one = 1;
 		const float4 L = ps.L[j], misc = ps.misc[j];
-		depth = __float_as_uint(misc.w);
+		depth = PATH_DEPTH(ps.rng[j].w);
 		if (samplesOut) {
 			((float4 *) samplesOut)[j] = L;
 			if (posOut) { posOut[2 * j] = misc.x; posOut[2 * j + 1] = misc.y; }
