@@ -197,6 +197,11 @@ MTSB_API int  mtsb_scene_add_rectangle(mtsb_scene *scene, const float object_to_
  * rectangle; as area emitters they are outside the GPU subset (MTSB_EUNSUPPORTED). */
 MTSB_API int  mtsb_scene_add_disk(mtsb_scene *scene, const float to_world[16], int flip_normals, int bsdf, int emitter);
 MTSB_API int  mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], float radius, int flip_normals, int bsdf, int emitter);
+/* Before commit: an AABB that Scene::getAABB() holds beside the geometry when the constant environment emitter sizes its
+ * bounding sphere — the sensor's AABB (Scene::initializeBidirectional, src/librender/scene.cpp:394-404;
+ * ConstantBackgroundEmitter::createShape, src/emitters/constant.cpp:69-80).  Only the far end of environment shadow rays
+ * (DirectSamplingRecord::dist) depends on it. */
+MTSB_API int  mtsb_scene_expand_bounds(mtsb_scene *scene, const float min[3], const float max[3]);
 /* Builds TriAccel records, the BVH and the emitter tables on the device. */
 MTSB_API int  mtsb_scene_commit(mtsb_scene *scene, int builder);
 /* Scene AABB as ShapeKDTree::getAABB() returns it (enlarged, include/mitsuba/render/gkdtree.h:1217-1220). */

@@ -93,7 +93,7 @@ def lib():
         "mtsb_scene_create": (i32, [vp, C.POINTER(vp)]), "mtsb_scene_destroy": (None, [vp]),
         "mtsb_scene_add_bsdf": (i32, [vp, C.POINTER(BsdfDesc)]), "mtsb_scene_add_emitter": (i32, [vp, C.POINTER(EmitterDesc)]),
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
-        "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]),
+        "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
         "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
@@ -212,6 +212,10 @@ class Scene:
     def add_rectangle(self, to_world, flip_normals=False, bsdf=0, emitter=-1):
         M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
         return _check(lib().mtsb_scene_add_rectangle(self.h, _ptr(M), int(flip_normals), bsdf, emitter))
+
+    def expand_bounds(self, lo, hi):
+        a, b = np.ascontiguousarray(lo, dtype=np.float32), np.ascontiguousarray(hi, dtype=np.float32)
+        _check(lib().mtsb_scene_expand_bounds(self.h, _ptr(a), _ptr(b)))
 
     def add_disk(self, to_world, flip_normals=False, bsdf=0, emitter=-1):
         M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)

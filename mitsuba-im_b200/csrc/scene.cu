@@ -226,6 +226,17 @@ int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_norm
 	return (int) scene->shapes.size() - 1;
 }
 
+int mtsb_scene_expand_bounds(mtsb_scene *scene, const float min[3], const float max[3]) {
+	if (!scene || !min || !max) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_expand_bounds: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_expand_bounds: scene already committed");
+	for (int a = 0; a < 3; ++a) {
+		scene->extraMin[a] = scene->hasExtra ? fminf(scene->extraMin[a], min[a]) : min[a];
+		scene->extraMax[a] = scene->hasExtra ? fmaxf(scene->extraMax[a], max[a]) : max[a];
+	}
+	scene->hasExtra = true;
+	return 0;
+}
+
 int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, int bsdf, int emitter) {
 	if (!scene || !m) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: NULL argument");
 	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_disk"));
@@ -387,8 +398,13 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	for (size_t i = 0; i < scene->emitters.size(); ++i) {
 		EmitterRec &e = scene->emitters[i];
 		if (e.type != MTSB_EMITTER_CONSTANT) continue;
-		V3 c = 0.5f * (D.aabbMin + D.aabbMax);
-		V3 h = D.aabbMax - c;
+		V3 lo = D.aabbMin, hi = D.aabbMax;
+		if (scene->hasExtra) {
+			lo = vmin3(lo, v3(scene->extraMin[0], scene->extraMin[1], scene->extraMin[2]));
+			hi = vmax3(hi, v3(scene->extraMax[0], scene->extraMax[1], scene->extraMax[2]));
+		}
+		V3 c = 0.5f * (lo + hi);
+		V3 h = hi - c;
 		e.sphereCenter = c;
 		e.sphereRadius = fmaxf(MTS_EPSILON, sqrtf(dot(h, h)) * 1.5f);
 	}

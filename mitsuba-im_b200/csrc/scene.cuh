@@ -36,6 +36,9 @@ struct mtsb_scene {
 
 	mtsb::SceneDev dev;                   // kernel parameter block
 	float aabbMin[3], aabbMax[3];         // enlarged (ShapeKDTree::getAABB)
+	// what Scene::getAABB() holds beside the geometry when the environment emitter sizes its sphere: the sensor's AABB
+	// (scene.cpp:394-404, constant.cpp:69-80) — mtsb_scene_expand_bounds
+	float extraMin[3] = { 0, 0, 0 }, extraMax[3] = { 0, 0, 0 }; bool hasExtra = false;
 
 	// staging ring + streams of the host-pointer ray queries (trace.cu), created on first use
 	std::mutex pipeMutex;

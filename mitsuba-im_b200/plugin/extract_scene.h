@@ -92,6 +92,13 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		}
 		if (rc < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
 	}
+	if (scene->getSensor()) {       // the part of Scene::getAABB() the environment emitter saw beside the geometry (scene.cpp:394-404)
+		const AABB sa = scene->getSensor()->getAABB();
+		if (sa.isValid()) {
+			const float lo[3] = { (float) sa.min.x, (float) sa.min.y, (float) sa.min.z }, hi[3] = { (float) sa.max.x, (float) sa.max.y, (float) sa.max.z };
+			MTSB_CALL(mtsb_scene_expand_bounds(out, lo, hi));
+		}
+	}
 	MTSB_CALL(mtsb_scene_commit(out, builder));
 	for (std::map<const BSDF *, int>::const_iterator it = bsdfIds.begin(); it != bsdfIds.end(); ++it)
 		selfCheckBSDF(out, it->second, it->first);

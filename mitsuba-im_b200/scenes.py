@@ -334,6 +334,10 @@ class SceneDesc:
                 sc.add_disk(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
             else:
                 sc.add_rectangle(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
+        if self.sensor is not None:
+            # Scene::getAABB() includes the sensor's AABB (the camera position) when the environment emitter is sized
+            pos = np.asarray(self.sensor["to_world"], np.float64)[0:3, 3].astype(np.float32)
+            sc.expand_bounds(pos, pos)
         sc.commit(builder)
         return sc
 
