@@ -284,6 +284,11 @@ MTSB_API int  mtsb_render_set_tail(mtsb_render *r, int paths);
 MTSB_API int  mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total,
                                const int32_t rect[4], uint32_t sample_stride, uint32_t sample_phase);
 MTSB_API int  mtsb_render_sync(mtsb_render *r);
+/* Headless stand-in for the frame the im-mts preview puts on screen (src/im-mts/preview_opengl2.cpp:188-270; the GL path
+ * itself is unavailable on a compute-only box): the un-normalised films of `n` renders (the worker framebuffers) are
+ * stacked as the preview's additive blend does — rgb = sum_k film_k.rgb / max(sum_k spp[k], 1), alpha = 1 — on the device
+ * and land as float RGBA in host memory (`pixel_count` = pixels of the film INCLUDING its border, as the GUI uploads it). */
+MTSB_API int  mtsb_preview_stack(mtsb_render *const *renders, const double *spp, int n, float *rgba_out, size_t pixel_count);
 /* Device pointer + float count of the film accumulation buffer (for NCCL reduce by the caller). */
 MTSB_API int  mtsb_film_device_ptr(mtsb_render *r, void **ptr_out, size_t *float_count_out);
 /* dst[i] += film[i] (accumulate != 0) or dst[i] = film[i]; dst is ImageBlock::getBitmap()->getFloatData(). */

@@ -105,7 +105,7 @@ def lib():
         "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
         "mtsb_render_create": (i32, [vp, C.POINTER(Camera), C.POINTER(FilmDesc), C.POINTER(IntegratorDesc), u64, C.POINTER(vp)]),
         "mtsb_render_destroy": (None, [vp]), "mtsb_render_set_camera": (i32, [vp, C.POINTER(Camera)]),
-        "mtsb_render_clear": (i32, [vp]), "mtsb_render_private_stream": (i32, [vp]), "mtsb_film_flush_begin": (i32, [vp]), "mtsb_film_flush_wait": (i32, [vp, vp, vp]), "mtsb_render_reserve": (i32, [vp, u32]), "mtsb_render_set_tail": (i32, [vp, i32]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
+        "mtsb_render_clear": (i32, [vp]), "mtsb_render_private_stream": (i32, [vp]), "mtsb_film_flush_begin": (i32, [vp]), "mtsb_preview_stack": (i32, [vp, vp, i32, vp, sz]), "mtsb_film_flush_wait": (i32, [vp, vp, vp]), "mtsb_render_reserve": (i32, [vp, u32]), "mtsb_render_set_tail": (i32, [vp, i32]), "mtsb_render_pass": (i32, [vp, u32, u32, u32, vp, u32, u32]),
         "mtsb_render_sync": (i32, [vp]), "mtsb_film_device_ptr": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]),
         "mtsb_film_to_host": (i32, [vp, vp, sz, i32]), "mtsb_film_stage": (i32, [vp, C.POINTER(vp), C.POINTER(sz)]), "mtsb_render_stats": (i32, [vp, vp]),
         "mtsb_render_samples": (i32, [vp, vp, sz, u32, vp]), "mtsb_render_samples_ex": (i32, [vp, vp, sz, u32, vp, vp]),
@@ -157,6 +157,16 @@ class Context:
         if self.h:
             lib().mtsb_ctx_destroy(self.h)
             self.h = C.c_void_p()
+
+
+def preview_stack(renders, spp):
+    """mtsb_preview_stack: float RGBA image (film size including the border) of the stacked, normalised films."""
+    shape = renders[0].film_shape()
+    out = np.empty((shape[0], shape[1], 4), np.float32)
+    handles = (C.c_void_p * len(renders))(*[r.h for r in renders])
+    s = np.ascontiguousarray(spp, dtype=np.float64)
+    _check(lib().mtsb_preview_stack(handles, _ptr(s), len(renders), _ptr(out), shape[0] * shape[1]))
+    return out
 
 
 class PinnedArray:

@@ -78,6 +78,7 @@ struct mtsb_render {
 	cudaGraphExec_t bounceExec = nullptr;
 	const void *graphKey = nullptr; int graphTail = -1;
 	bool graphFailed = false;
+	float4 *previewDev = nullptr, *previewHost = nullptr; size_t previewCount = 0;   // mtsb_preview_stack
 	cudaEvent_t flushDone = nullptr;   // mtsb_film_flush_begin / _wait
 	float *hostStage = nullptr;    // page-locked staging for mtsb_film_to_host(accumulate = 1), allocated on first use
 };

@@ -272,6 +272,8 @@ void mtsb_render_destroy(mtsb_render *r) {
 	if (r->ownStream) cudaStreamDestroy(r->stream);
 	if (r->hostStage) cudaFreeHost(r->hostStage);
 	if (r->flushDone) cudaEventDestroy(r->flushDone);
+	if (r->previewDev) cudaFree(r->previewDev);
+	if (r->previewHost) cudaFreeHost(r->previewHost);
 	destroy_bounce_graph(r);
 	delete r;
 }
@@ -421,6 +423,38 @@ int mtsb_film_flush_wait(mtsb_render *r, const float **stage_out, size_t *float_
 	MTSB_CUDA(cudaEventSynchronize(r->flushDone));       // the copy only — passes queued after flush_begin keep running
 	*stage_out = r->hostStage;
 	if (float_count_out) *float_count_out = r->dFilm.count;
+	return 0;
+}
+
+int mtsb_preview_stack(mtsb_render *const *renders, const double *spp, int n, float *rgba_out, size_t pixel_count) {
+	if (!renders || !spp || !rgba_out || n < 1 || n > 8) MTSB_FAIL(MTSB_EINVAL, "mtsb_preview_stack: bad argument (1..8 renders)");
+	mtsb_render *r0 = renders[0];
+	if (!r0) MTSB_FAIL(MTSB_EINVAL, "mtsb_preview_stack: NULL render");
+	const size_t pixels = r0->dFilm.count / (size_t) r0->film.channels;
+	if (pixel_count != pixels) MTSB_FAIL(MTSB_EINVAL, "mtsb_preview_stack: %zu pixels given, the film (with its border) has %zu", pixel_count, pixels);
+	StackIn in; memset(&in, 0, sizeof(in));
+	double total = 0;
+	for (int k = 0; k < n; ++k) {
+		if (!renders[k] || renders[k]->scene->ctx != r0->scene->ctx || renders[k]->dFilm.count != r0->dFilm.count)
+			MTSB_FAIL(MTSB_EINVAL, "mtsb_preview_stack: renders must share one context and one film size");
+		in.film[k] = renders[k]->dFilm.ptr; total += spp[k];
+	}
+	in.n = n; in.channels = r0->film.channels; in.scale = 1.0f / std::max((float) total, 1.0f);
+	MTSB_CUDA(cudaSetDevice(r0->scene->ctx->device));
+	cudaStream_t st = r0->stream;
+	// every film must be complete before it is read: the renders may run on streams of their own
+	for (int k = 1; k < n; ++k) if (renders[k]->stream != st) MTSB_CUDA(cudaStreamSynchronize(renders[k]->stream));
+	if (r0->previewCount < pixels) {
+		if (r0->previewDev) cudaFree(r0->previewDev);
+		if (r0->previewHost) cudaFreeHost(r0->previewHost);
+		MTSB_CUDA(cudaMalloc((void **) &r0->previewDev, pixels * sizeof(float4)));
+		MTSB_CUDA(cudaMallocHost((void **) &r0->previewHost, pixels * sizeof(float4)));
+		r0->previewCount = pixels;
+	}
+	preview_stack_kernel<<<blocks_for(pixels, 256), 256, 0, st>>>(in, pixels, r0->previewDev);
+	MTSB_CUDA(cudaMemcpyAsync(r0->previewHost, r0->previewDev, pixels * sizeof(float4), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	memcpy(rgba_out, r0->previewHost, pixels * sizeof(float4));
 	return 0;
 }
 

@@ -283,6 +283,22 @@ splat_kernel(PathState ps, FilmDev film, uint32_t count, float *samplesOut, floa
 	}
 }
 
+// Headless stand-in for the stacking arithmetic of the im-mts preview (src/im-mts/preview_opengl2.cpp:188-270): the GUI
+// uploads every worker framebuffer (un-normalised RGBA sums) as a texture and blends them into one target with
+// glBlendFunc(GL_CONSTANT_COLOR, GL_ONE), blend colour (s, s, s, 0), s = 1 / max(sum of the buffers' sample counts, 1), over
+// a clear colour of alpha 1 — i.e. rgb = s * sum_k film_k.rgb, a = 1.  Same arithmetic here, on the device films directly.
+struct StackIn { const float *film[8]; int n, channels; float scale; };
+__global__ void preview_stack_kernel(StackIn in, size_t pixels, float4 *out) {
+	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
+	if (i >= pixels) return;
+	float r = 0, g = 0, b = 0;
+	for (int k = 0; k < in.n; ++k) {
+		const float *p = in.film[k] + i * in.channels;
+		r += p[0]; g += p[1]; b += p[2];
+	}
+	out[i] = make_float4(r * in.scale, g * in.scale, b * in.scale, 1.0f);
+}
+
 // ---- pointwise plugin math for parity tests (mtsb_eval_bsdf / mtsb_eval_emitter) ----
 __global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, const float *s3, size_t n, float *out) {
 	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;

@@ -202,6 +202,37 @@ def test_film_splat_matches_imageblock_put_per_pixel(pkg, ctx, rfilter):
     assert abs(film[..., 4].sum() - ref[..., 4].sum()) <= 1e-5 * ref[..., 4].sum()
 
 
+def test_headless_preview_stack_matches_the_preview_arithmetic(pkg, ctx, tmp_path):
+    """mtsb_preview_stack against the stacking arithmetic of the im-mts preview (src/im-mts/preview_opengl2.cpp:188-270,
+    additive blend with constant colour 1 / max(sum spp, 1) over alpha 1) restated in numpy, on two worker films that hold
+    the interleaved sample indices of one frame — and the frame lands in a PFM file, as a headless preview has to."""
+    S, B = pkg.scenes, pkg.binding
+    sd = S.cornell_box(48, 32, spp=6, max_depth=4, sampler="ctr", seed=9, rfilter="gaussian")
+    sc = sd.upload(ctx)
+    try:
+        renders = [B.Render(sc, sd.camera(), sd.film(channels=4), sd.integrator_desc(), seed=9) for _ in range(2)]
+        for k, rd in enumerate(renders):
+            rd.render_pass(0, 3, 6, stride=2, phase=k)           # worker k: sample indices k, k + 2, k + 4
+        frame = B.preview_stack(renders, [3.0, 3.0])
+        films = [rd.film_to_host().astype(np.float64) for rd in renders]
+        ref = (films[0][..., 0:3] + films[1][..., 0:3]) / 6.0
+        assert frame.shape == films[0].shape[0:2] + (4,)
+        assert np.allclose(frame[..., 0:3], ref, rtol=1e-6, atol=1e-7) and (frame[..., 3] == 1).all()
+        # fewer than one sample per pixel on average: the scale is clamped at 1 (std::max(avgSamples, 1.f))
+        half = B.preview_stack(renders[0:1], [0.5])
+        assert np.allclose(half[..., 0:3], films[0][..., 0:3], rtol=1e-6, atol=1e-7)
+        # the frame as a file
+        path = str(tmp_path / "frame.pfm")
+        with open(path, "wb") as f:
+            f.write(b"PF\n%d %d\n-1.0\n" % (frame.shape[1], frame.shape[0]))
+            f.write(np.ascontiguousarray(frame[::-1, :, 0:3], "<f4").tobytes())
+        assert np.allclose(O.read_pfm(path), frame[..., 0:3])
+        for rd in renders:
+            rd.close()
+    finally:
+        sc.close()
+
+
 def test_image_is_unbiased_against_live_reference(pkg, ctx, tmp_path):
     """relMSE of the GPU render against a high-spp render of the unmodified reference shrinks like 1/spp (unbiased
     estimator), and the converged means agree — materials scene, independent reference sampler."""
