@@ -105,6 +105,8 @@ enum {
 	MTSB_BSDF_ROUGHDIELECTRIC = 6, /* p[0] alphaU, p[1] alphaV, p[2] eta=intIOR/extIOR, p[3..5] specularReflectance,
 	                                  p[6..8] specularTransmittance, p[11] distribution, p[12] sampleVisible
 	                                  (src/bsdfs/roughdielectric.cpp:186-214)                                 */
+	MTSB_BSDF_PASSTHROUGH    = 7,  /* `null` (src/bsdfs/null.cpp): index-matched boundary of a participating medium — the only
+	                                  lobe is wo = -wi with weight 1 (ENull); emitter sampling sees through it              */
 	MTSB_BSDF_TWOSIDED_FLAG  = 0x100 /* OR-ed in: wrapped by `twosided` (src/bsdfs/twosided.cpp), same BSDF both sides */
 };
 typedef struct mtsb_bsdf_desc {
@@ -150,7 +152,9 @@ typedef struct mtsb_film_desc {
 	int32_t crop_size[2];
 } mtsb_film_desc;
 
-enum { MTSB_INTEGRATOR_PATH = 0, MTSB_INTEGRATOR_DIRECT = 1 };
+/* MTSB_INTEGRATOR_VOLPATH_SIMPLE: SimpleVolumetricPathTracer (src/integrators/path/volpath_simple.cpp:92-300) — path tracing
+ * with homogeneous participating media, emitter sampling attenuated through index-matched boundaries, no MIS. */
+enum { MTSB_INTEGRATOR_PATH = 0, MTSB_INTEGRATOR_DIRECT = 1, MTSB_INTEGRATOR_VOLPATH_SIMPLE = 2 };
 typedef struct mtsb_integrator_desc {
 	int32_t type;
 	int32_t max_depth;           /* MonteCarloIntegrator maxDepth (-1 = unbounded)  (src/librender/integrator.cpp:191-226) */
@@ -202,6 +206,21 @@ MTSB_API int  mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_wor
  * ConstantBackgroundEmitter::createShape, src/emitters/constant.cpp:69-80).  Only the far end of environment shadow rays
  * (DirectSamplingRecord::dist) depends on it. */
 MTSB_API int  mtsb_scene_expand_bounds(mtsb_scene *scene, const float min[3], const float max[3]);
+/* Homogeneous participating medium (src/medium/homogeneous.cpp:156-400) with an isotropic or Henyey-Greenstein phase function
+ * (src/phase/isotropic.cpp, hg.cpp).  sigma_a / sigma_s already carry the `scale` (densityMultiplier) of the Medium base
+ * class.  strategy: 0 = balance (a random channel per distance sample), 1 = single / manual (sampling_density given);
+ * medium_sampling_weight as the constructor derives it (:171-186). */
+typedef struct mtsb_medium_desc {
+	float   sigma_a[3], sigma_s[3];
+	int32_t strategy;
+	float   sampling_density;
+	float   medium_sampling_weight;
+	int32_t phase;               /* 0 isotropic, 1 Henyey-Greenstein */
+	float   g;
+} mtsb_medium_desc;
+MTSB_API int  mtsb_scene_add_medium(mtsb_scene *scene, const mtsb_medium_desc *desc);
+/* Shape::getInteriorMedium / getExteriorMedium (include/mitsuba/render/shape.h:427-431); -1 = none (vacuum) */
+MTSB_API int  mtsb_scene_set_shape_media(mtsb_scene *scene, int shape, int interior, int exterior);
 /* Builds TriAccel records, the BVH and the emitter tables on the device. */
 MTSB_API int  mtsb_scene_commit(mtsb_scene *scene, int builder);
 /* Scene AABB as ShapeKDTree::getAABB() returns it (enlarged, include/mitsuba/render/gkdtree.h:1217-1220). */
@@ -262,6 +281,8 @@ MTSB_API int  mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, c
 MTSB_API void mtsb_render_destroy(mtsb_render *r);
 MTSB_API int  mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera);
 MTSB_API int  mtsb_render_clear(mtsb_render *r);
+/* Sensor::getMedium(): the medium the camera sits in (-1 = none, the default); volpath_simple starts its paths there. */
+MTSB_API int  mtsb_render_set_camera_medium(mtsb_render *r, int medium);
 /* Gives the render a CUDA stream of its own (default: the context stream).  Renders are independent — own path state,
  * own film — so passes of several renders on one GPU then overlap; this is what lets the `threadCount` host threads of
  * ResponsiveIntegrator::render (include/mitsuba/render/integrator2.h:49-100), one render each, fill the device together. */

@@ -22,6 +22,7 @@ __device__ inline uint32_t bsdf_type(const BsdfRec &b) {   // m_combinedType of 
 		case MTSB_BSDF_PLASTIC: t = B_DELTA_REFL | B_DIFFUSE_REFL | B_FRONT; break;
 		case MTSB_BSDF_CONDUCTOR: t = B_DELTA_REFL | B_FRONT; break;
 		case MTSB_BSDF_ROUGHDIELECTRIC: t = B_GLOSSY_REFL | B_GLOSSY_TRANS | B_FRONT | B_BACK; break;
+		case MTSB_BSDF_PASSTHROUGH: t = B_NULL | B_FRONT | B_BACK; break;        // null.cpp:35-38
 		default: t = B_GLOSSY_REFL | B_FRONT; break;
 	}
 	if (b.type & MTSB_BSDF_TWOSIDED_FLAG) t |= B_BACK;
@@ -145,7 +146,7 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 			if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
 			return v3(b.p[0], b.p[1], b.p[2]) * (MTS_INV_PI * wo.z);
 		}
-		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return v3(0.0f);     // discrete measure only
+		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: case MTSB_BSDF_PASSTHROUGH: return v3(0.0f);     // discrete measure only
 		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_eval(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (LEAN) __builtin_unreachable();
@@ -173,7 +174,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 		case MTSB_BSDF_DIFFUSE: case MTSB_BSDF_NULL:
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return MTS_INV_PI * wo.z;
-		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: return 0.0f;
+		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: case MTSB_BSDF_PASSTHROUGH: return 0.0f;
 		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_pdf(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (LEAN) __builtin_unreachable();
@@ -202,6 +203,11 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			out.type = B_DIFFUSE_REFL;
 			out.pdf = MTS_INV_PI * out.wo.z;
 			return v3(b.p[0], b.p[1], b.p[2]);
+		}
+		case MTSB_BSDF_PASSTHROUGH: {                              // null.cpp:55-78
+			if (LEAN) __builtin_unreachable();
+			out.wo = v3(-wi.x, -wi.y, -wi.z); out.type = B_NULL; out.pdf = 1.0f;
+			return v3(1.0f);
 		}
 		case MTSB_BSDF_DIELECTRIC: {
 			const float eta = b.p[0], invEta = 1 / eta;

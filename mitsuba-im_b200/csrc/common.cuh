@@ -66,7 +66,7 @@ struct ShapeRec {
 	int32_t  emitter;
 	uint32_t rect;         // index into rect table (SHAPE_RECT)
 	float    invArea;      // 1/surface area (Shape::pdfPosition)
-	uint32_t pad[2];
+	int32_t  interior, exterior;   // participating media on the two sides (-1: none); Shape::isMediumTransition() = either set
 };
 enum { SHAPE_HAS_NORMALS = 1, SHAPE_HAS_UV = 2 };
 
@@ -92,6 +92,13 @@ struct EmitterRec {
 
 struct BsdfRec { int32_t type; float p[15]; };
 
+// HomogeneousMedium + its phase function (src/medium/homogeneous.cpp, src/phase/{isotropic,hg}.cpp)
+struct MediumRec {
+	V3 sigmaA, sigmaS, sigmaT;
+	int32_t strategy; float samplingDensity, mediumSamplingWeight;
+	int32_t phase; float g;
+};
+
 // Everything the kernels read, passed by value as a kernel parameter.
 struct SceneDev {
 	// BVH8: 5 x uint4 per node (layout in bvh.cuh)
@@ -111,6 +118,7 @@ struct SceneDev {
 	const uint32_t *indices;     // 3 per triangle, local to the mesh (add vtxBase)
 	const BsdfRec  *bsdfs;
 	const EmitterRec *emitters;
+	const MediumRec *media;
 	const float    *emitterCdf;  // DiscreteDistribution m_cdf (n+1 entries), normalised
 	const float    *triAreaCdf;  // per emitting mesh: concatenated normalised area CDFs (T+1 entries each)
 	const uint32_t *triAreaCdfOffset; // per shape: offset into triAreaCdf or 0xFFFFFFFF

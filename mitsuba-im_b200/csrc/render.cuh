@@ -60,6 +60,7 @@ struct mtsb_render {
 	mtsb::FilmDev film;
 	mtsb::IntegratorDev integ;
 	uint32_t seed = 0;
+	int cameraMedium = -1;         // Sensor::getMedium() (volpath_simple starts its paths in it)
 	cudaStream_t stream = nullptr; // the context stream, or a stream of its own (mtsb_render_private_stream)
 	bool ownStream = false;
 	size_t capacity = 0;           // paths in flight

@@ -301,6 +301,13 @@ int mtsb_render_private_stream(mtsb_render *r) {
 	return 0;
 }
 
+int mtsb_render_set_camera_medium(mtsb_render *r, int medium) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: NULL argument");
+	if (medium < -1 || medium >= (int) r->scene->media.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: medium %d unknown", medium);
+	r->cameraMedium = medium;
+	return 0;
+}
+
 int mtsb_render_clear(mtsb_render *r) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_clear: NULL argument");
 	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));

@@ -134,7 +134,7 @@ int mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc) {
 	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: NULL argument");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: scene already committed");
 	int base = desc->type & 0xff;
-	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_ROUGHDIELECTRIC)
+	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_PASSTHROUGH)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_bsdf: BSDF type %d is outside the GPU subset", desc->type);
 	BsdfRec r; r.type = desc->type; memcpy(r.p, desc->p, sizeof(r.p));
 	scene->bsdfs.push_back(r);
@@ -180,7 +180,7 @@ int mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *
 	sh.vtxBase = (uint32_t) (scene->positions.size() / 3);
 	sh.triBase = (uint32_t) (scene->indices.size() / 3);
 	sh.flags = (normals ? SHAPE_HAS_NORMALS : 0) | (texcoords ? SHAPE_HAS_UV : 0);
-	sh.bsdf = bsdf; sh.emitter = emitter;
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.interior = -1; sh.exterior = -1;
 	scene->positions.insert(scene->positions.end(), positions, positions + vertex_count * 3);
 	if (normals) scene->normals.insert(scene->normals.end(), normals, normals + vertex_count * 3);
 	else scene->normals.resize(scene->normals.size() + vertex_count * 3, 0.0f);
@@ -216,7 +216,7 @@ int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_norm
 	rr.invSurfaceArea = 1.0f / (lu * lv);
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
 	sh.type = SHAPE_RECT; sh.primOffset = scene->primCount; sh.primCount = 1;
-	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.interior = -1; sh.exterior = -1; sh.rect = (uint32_t) scene->rects.size();
 	sh.invArea = rr.invSurfaceArea;
 	scene->rects.push_back(rr);
 	scene->shapes.push_back(sh);
@@ -224,6 +224,31 @@ int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_norm
 	scene->shapeOffsets.push_back(scene->primCount);
 	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
 	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_add_medium(mtsb_scene *scene, const mtsb_medium_desc *desc) {
+	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_medium: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_medium: scene already committed");
+	if (desc->strategy < 0 || desc->strategy > 1 || desc->phase < 0 || desc->phase > 1)
+		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_medium: sampling strategy %d / phase function %d is outside the GPU subset", desc->strategy, desc->phase);
+	MediumRec m; memset(&m, 0, sizeof(m));
+	m.sigmaA = v3(desc->sigma_a[0], desc->sigma_a[1], desc->sigma_a[2]);
+	m.sigmaS = v3(desc->sigma_s[0], desc->sigma_s[1], desc->sigma_s[2]);
+	m.sigmaT = m.sigmaA + m.sigmaS;                       // Medium::Medium (src/librender/medium.cpp)
+	m.strategy = desc->strategy; m.samplingDensity = desc->sampling_density; m.mediumSamplingWeight = desc->medium_sampling_weight;
+	m.phase = desc->phase; m.g = desc->g;
+	scene->media.push_back(m);
+	return (int) scene->media.size() - 1;
+}
+
+int mtsb_scene_set_shape_media(mtsb_scene *scene, int shape, int interior, int exterior) {
+	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_shape_media: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_shape_media: scene already committed");
+	const int n = (int) scene->media.size();
+	if (shape < 0 || shape >= (int) scene->shapes.size() || interior < -1 || interior >= n || exterior < -1 || exterior >= n)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_shape_media: shape %d / media %d, %d unknown", shape, interior, exterior);
+	scene->shapes[shape].interior = interior; scene->shapes[shape].exterior = exterior;
+	return 0;
 }
 
 int mtsb_scene_expand_bounds(mtsb_scene *scene, const float min[3], const float max[3]) {
@@ -259,7 +284,7 @@ int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, 
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
 	scene->curved = true;
 	sh.type = SHAPE_DISK; sh.primOffset = scene->primCount; sh.primCount = 1;
-	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.interior = -1; sh.exterior = -1; sh.rect = (uint32_t) scene->rects.size();
 	sh.invArea = rr.invSurfaceArea;
 	scene->rects.push_back(rr);
 	scene->shapes.push_back(sh);
@@ -283,7 +308,7 @@ int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], fl
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
 	scene->curved = true;
 	sh.type = SHAPE_SPHERE; sh.primOffset = scene->primCount; sh.primCount = 1;
-	sh.bsdf = bsdf; sh.emitter = emitter; sh.rect = (uint32_t) scene->rects.size();
+	sh.bsdf = bsdf; sh.emitter = emitter; sh.interior = -1; sh.exterior = -1; sh.rect = (uint32_t) scene->rects.size();
 	sh.invArea = rr.invSurfaceArea;
 	scene->rects.push_back(rr);
 	scene->shapes.push_back(sh);
@@ -408,6 +433,8 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 		e.sphereCenter = c;
 		e.sphereRadius = fmaxf(MTS_EPSILON, sqrtf(dot(h, h)) * 1.5f);
 	}
+	MTSB_CHECK(scene->dMedia.upload(scene->media, st));
+	D.media = scene->dMedia.ptr;
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));

@@ -18,6 +18,7 @@ struct mtsb_scene {
 	std::vector<mtsb::RectRec> rects;
 	std::vector<mtsb::BsdfRec> bsdfs;
 	std::vector<mtsb::EmitterRec> emitters;
+	std::vector<mtsb::MediumRec> media;
 	std::vector<float> emitterWeights;
 	std::vector<float> positions, normals, texcoords;
 	std::vector<uint32_t> indices;
@@ -29,6 +30,7 @@ struct mtsb_scene {
 	mtsb::DevBuf<mtsb::RectRec> dRects;
 	mtsb::DevBuf<mtsb::BsdfRec> dBsdfs;
 	mtsb::DevBuf<mtsb::EmitterRec> dEmitters;
+	mtsb::DevBuf<mtsb::MediumRec> dMedia;
 	mtsb::DevBuf<float> dPositions, dNormals, dTexcoords, dEmitterCdf, dTriAreaCdf;
 	mtsb::DevBuf<uint32_t> dIndices, dTriAreaCdfOffset;
 	mtsb::DevBuf<unsigned long long> dCounters;

@@ -217,6 +217,7 @@ class SceneDesc:
     def __init__(self):
         self.shapes = []
         self.emitters = []          # free emitters: dict(type='point'|'constant', ...)
+        self.media = []             # homogeneous media: dict(sigma_a, sigma_s, phase='isotropic'|'hg', g, strategy)
         self.sensor = None
         self.integrator = dict(kind="path", max_depth=-1, rr_depth=5)
         self.sampler = dict(kind="independent", spp=4, seed=0)
@@ -243,6 +244,16 @@ class SceneDesc:
         self.shapes.append(dict(type="disk", to_world=np.asarray(to_world, np.float64), bsdf=bsdf or dict(type="diffuse"), emitter=None,
                                 flip_normals=flip_normals))
         return len(self.shapes) - 1
+
+    def add_medium(self, sigma_a, sigma_s, phase="isotropic", g=0.0, strategy="balance"):
+        """Homogeneous participating medium (src/medium/homogeneous.cpp); returns its index.  A shape refers to it through
+        set_media(shape, interior=, exterior=)."""
+        self.media.append(dict(sigma_a=tuple(float(x) for x in sigma_a), sigma_s=tuple(float(x) for x in sigma_s), phase=phase,
+                               g=float(g), strategy=strategy))
+        return len(self.media) - 1
+
+    def set_media(self, shape, interior=None, exterior=None):
+        self.shapes[shape]["interior"], self.shapes[shape]["exterior"] = interior, exterior
 
     def add_point_light(self, pos, intensity):
         self.emitters.append(dict(type="point", pos=tuple(pos), intensity=tuple(intensity)))
@@ -361,6 +372,8 @@ class SceneDesc:
         rgb = lambda name, v: '<rgb name="%s" value="%s"/>' % (name, ", ".join(repr(float(x)) for x in v))
         if t == "null":
             return ""
+        if t == "passthrough":          # index-matched medium boundary (src/bsdfs/null.cpp)
+            return '<bsdf type="null"/>'
         inner = ""
         if t == "diffuse":
             inner = '<bsdf type="diffuse">%s</bsdf>' % rgb("reflectance", b.get("reflectance", (0.5, 0.5, 0.5)))
@@ -431,11 +444,19 @@ class SceneDesc:
                     e["pos"][0], e["pos"][1], e["pos"][2], ", ".join(repr(float(x)) for x in e["intensity"])))
             else:
                 out.append('<emitter type="constant"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in e["radiance"]))
+        for k, m in enumerate(self.media):
+            ph = '<phase type="hg"><float name="g" value="%r"/></phase>' % m["g"] if m["phase"] == "hg" else '<phase type="isotropic"/>'
+            out.append('<medium type="homogeneous" id="medium%d"><rgb name="sigmaA" value="%s"/><rgb name="sigmaS" value="%s"/>'
+                       '<string name="strategy" value="%s"/>%s</medium>' % (k, ", ".join(repr(x) for x in m["sigma_a"]),
+                                                                           ", ".join(repr(x) for x in m["sigma_s"]), m["strategy"], ph))
         for i, s in enumerate(self.shapes):
             em = ""
             if s["emitter"] is not None:
                 em = '<emitter type="area"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in s["emitter"])
             bs = self._bsdf_xml(s["bsdf"]) if s["bsdf"] is not None else ""
+            for side in ("interior", "exterior"):
+                if s.get(side) is not None:
+                    bs += '<ref name="%s" id="medium%d"/>' % (side, s[side])
             if s["type"] == "mesh":
                 fn = "%s_mesh%d.ply" % (name, i)
                 write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"], s.get("UV"))
@@ -629,6 +650,34 @@ def analytic_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent
     sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
     sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
     sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd
+
+
+def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple"):
+    """Participating media: a ball of isotropic fog behind an index-matched boundary (no BSDF: `null`), a
+    glass ball filled with a forward-scattering (HG, g = 0.6) coloured medium, a diffuse ball, on a mesh floor under a mesh
+    area light, a point light and a constant environment; camera outside the media."""
+    sd = SceneDesc()
+    sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
+    sd.add_constant_env((0.3, 0.35, 0.5))
+    fog = sd.add_medium((0.2, 0.2, 0.2), (1.6, 1.8, 2.2))
+    milk = sd.add_medium((0.05, 0.4, 0.8), (3.0, 2.5, 1.5), phase="hg", g=0.6)
+    V, N, F = displaced_sphere(2, seed=41, radius=0.6, center=(-1.0, 0.65, 0.1), amplitude=0.0)
+    a = sd.add_mesh(V, N, F, bsdf=dict(type="passthrough"))
+    sd.set_media(a, interior=fog)
+    V, N, F = displaced_sphere(2, seed=42, radius=0.5, center=(0.4, 0.55, -0.2), amplitude=0.0)
+    b = sd.add_mesh(V, N, F, bsdf=dict(type="dielectric"))
+    sd.set_media(b, interior=milk)
+    V, N, F = displaced_sphere(2, seed=43, radius=0.4, center=(1.5, 0.45, 0.5), amplitude=0.03)
+    sd.add_mesh(V, N, F, bsdf=dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
+    g = 4.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
+    lV, lN, lF = displaced_sphere(1, seed=99, radius=0.4, center=(0.5, 2.6, 0.3), amplitude=0.0)
+    sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
+    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator(kind, max_depth=max_depth, rr_depth=3)
     return sd
 
 
