@@ -20,9 +20,10 @@ HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
+BSDF_PASSTHROUGH = 7
 BSDF_TWOSIDED_FLAG = 0x100
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
-INTEGRATOR_PATH, INTEGRATOR_DIRECT = 0, 1
+INTEGRATOR_PATH, INTEGRATOR_DIRECT, INTEGRATOR_VOLPATH_SIMPLE = 0, 1, 2
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 
 ray_dtype = np.dtype([("o", "<f4", 3), ("mint", "<f4"), ("d", "<f4", 3), ("maxt", "<f4")])
@@ -48,6 +49,12 @@ class BsdfDesc(C.Structure):
 class EmitterDesc(C.Structure):
     _fields_ = [("type", C.c_int32), ("shape", C.c_uint32), ("radiance", C.c_float * 3), ("pos", C.c_float * 3),
                 ("sampling_weight", C.c_float)]
+
+
+class MediumDesc(C.Structure):
+    _fields_ = [("sigma_a", C.c_float * 3), ("sigma_s", C.c_float * 3), ("strategy", C.c_int32),
+                ("sampling_density", C.c_float), ("medium_sampling_weight", C.c_float), ("phase", C.c_int32),
+                ("g", C.c_float)]
 
 
 class Camera(C.Structure):
@@ -95,6 +102,8 @@ def lib():
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
+        "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
+        "mtsb_render_set_camera_medium": (i32, [vp, i32]),
         "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
         "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
@@ -235,6 +244,27 @@ class Scene:
         M = np.ascontiguousarray(object_to_world, dtype=np.float32).reshape(4, 4)
         return _check(lib().mtsb_scene_add_sphere(self.h, _ptr(M), float(radius), int(flip_normals), bsdf, emitter))
 
+    def add_medium(self, sigma_a, sigma_s, strategy=0, sampling_density=0.0, medium_sampling_weight=None, phase=0, g=0.0):
+        """Homogeneous medium; the sampling weight defaults to what the reference's constructor derives
+        (src/medium/homogeneous.cpp:171-186): the largest albedo, floored at 0.5 when positive."""
+        d = MediumDesc()
+        sa, ss = np.asarray(sigma_a, np.float32).reshape(3), np.asarray(sigma_s, np.float32).reshape(3)
+        d.sigma_a[:] = [float(x) for x in sa]
+        d.sigma_s[:] = [float(x) for x in ss]
+        if medium_sampling_weight is None:
+            st = sa + ss
+            w = 0.0
+            for i in range(3):
+                if st[i] != 0:
+                    w = max(w, float(ss[i] / st[i]))
+            medium_sampling_weight = max(w, 0.5) if w > 0 else -1.0
+        d.strategy, d.sampling_density, d.medium_sampling_weight = int(strategy), float(sampling_density), float(medium_sampling_weight)
+        d.phase, d.g = int(phase), float(g)
+        return _check(lib().mtsb_scene_add_medium(self.h, C.byref(d)))
+
+    def set_shape_media(self, shape, interior=-1, exterior=-1):
+        _check(lib().mtsb_scene_set_shape_media(self.h, int(shape), int(interior), int(exterior)))
+
     def commit(self, builder=BUILDER_LBVH):
         _check(lib().mtsb_scene_commit(self.h, builder))
 
@@ -354,6 +384,9 @@ class Render:
 
     def set_camera(self, camera):
         _check(lib().mtsb_render_set_camera(self.h, C.byref(camera)))
+
+    def set_camera_medium(self, medium):
+        _check(lib().mtsb_render_set_camera_medium(self.h, int(medium)))
 
     def clear(self):
         _check(lib().mtsb_render_clear(self.h))

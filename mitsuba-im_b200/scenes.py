@@ -202,7 +202,7 @@ def make_film(width, height, rfilter="box", channels=5, stddev=0.5):
 def make_integrator(kind="path", max_depth=-1, rr_depth=5, strict_normals=False, hide_emitters=False,
                     emitter_samples=1, bsdf_samples=1):
     d = B.IntegratorDesc()
-    d.type = B.INTEGRATOR_PATH if kind == "path" else B.INTEGRATOR_DIRECT
+    d.type = dict(path=B.INTEGRATOR_PATH, direct=B.INTEGRATOR_DIRECT, volpath_simple=B.INTEGRATOR_VOLPATH_SIMPLE)[kind]
     d.max_depth, d.rr_depth = max_depth, rr_depth
     d.strict_normals, d.hide_emitters = int(strict_normals), int(hide_emitters)
     d.emitter_samples, d.bsdf_samples = emitter_samples, bsdf_samples
@@ -281,6 +281,8 @@ class SceneDesc:
             return B.BSDF_DIFFUSE | two, list(b.get("reflectance", (0.5, 0.5, 0.5)))
         if t == "null":
             return B.BSDF_NULL, [0, 0, 0]
+        if t == "passthrough":          # src/bsdfs/null.cpp: the boundary of an index-matched medium
+            return B.BSDF_PASSTHROUGH, [0, 0, 0]
         if t == "dielectric":
             eta = b.get("int_ior", 1.5046) / b.get("ext_ior", 1.000277)
             return B.BSDF_DIELECTRIC, [eta] + list(b.get("specular_reflectance", (1, 1, 1))) + list(b.get("specular_transmittance", (1, 1, 1)))
@@ -328,7 +330,10 @@ class SceneDesc:
                 sc.add_emitter(B.EMITTER_POINT, radiance=e["intensity"], pos=e["pos"])
             else:
                 sc.add_emitter(B.EMITTER_CONSTANT, radiance=e["radiance"])
-        for s in self.shapes:
+        for m in self.media:
+            sc.add_medium(m["sigma_a"], m["sigma_s"], strategy=dict(balance=0, single=1, manual=1)[m["strategy"]],
+                          phase=dict(isotropic=0, hg=1)[m["phase"]], g=m["g"])
+        for k, s in enumerate(self.shapes):
             bd = s["bsdf"]
             if s["emitter"] is not None and bd is None:
                 bd = dict(type="null")
@@ -345,6 +350,9 @@ class SceneDesc:
                 sc.add_disk(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
             else:
                 sc.add_rectangle(s["to_world"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)
+            if s.get("interior") is not None or s.get("exterior") is not None:
+                sc.set_shape_media(k, -1 if s.get("interior") is None else s["interior"],
+                                   -1 if s.get("exterior") is None else s["exterior"])
         if self.sensor is not None:
             # Scene::getAABB() includes the sensor's AABB (the camera position) when the environment emitter is sized
             pos = np.asarray(self.sensor["to_world"], np.float64)[0:3, 3].astype(np.float32)
