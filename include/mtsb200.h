@@ -246,6 +246,17 @@ MTSB_API int  mtsb_trace_any(mtsb_scene *scene, const mtsb_ray *rays, size_t n, 
 MTSB_API int  mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_surface *out, int on_device);
 /* replaces ShapeKDTree::rayIntersect(ray, t, shape, n, uv), src/librender/skdtree.cpp:144-204 */
 MTSB_API int  mtsb_trace_light(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_light_hit *out, int on_device);
+/* mtsb_trace_closest without any device allocation.  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results (bit for bit) as mtsb_trace_closest, but the call makes no cudaMalloc /
+ * cudaFree / allocating library call: the persistent kernel's work counter and — for host pointers — the device staging
+ * of rays and hit records live in one fixed static __device__ array of the library (3 MiB + 256 bytes per device).
+ * Limit: n <= MTSB_NOALLOC_MAX_RAYS rays a call; a larger n returns MTSB_EINVAL with a message naming the limit.
+ * The array is shared by every call on a device (whatever the scene or context) and keeps the last call's contents;
+ * the call clears what must start at zero.  Calls that overlap on the GPU (two contexts on one device, two host threads)
+ * RACE on it — serialise them; calls on one context are ordered by its stream.  on_device != 0: rays/hits are device
+ * pointers, asynchronous on the context stream; otherwise host pointers, synchronous. */
+#define MTSB_NOALLOC_MAX_RAYS 65536u
+MTSB_API int  mtsb_trace_closest_noalloc(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device);
 /* Traversal counters of the last trace call when built with counters enabled, else zeros:
  * out[0]=nodes visited, out[1]=primitive tests, out[2]=rays. */
 MTSB_API int  mtsb_trace_counters(mtsb_scene *scene, uint64_t out[4]);

@@ -19,6 +19,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmtsb200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
+NOALLOC_MAX_RAYS = 65536
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
 BSDF_PASSTHROUGH = 7
 BSDF_TWOSIDED_FLAG = 0x100
@@ -109,6 +110,7 @@ def lib():
         "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
         "mtsb_trace_closest": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_any": (i32, [vp, vp, sz, vp, i32]),
         "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_light": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
+        "mtsb_trace_closest_noalloc": (i32, [vp, vp, sz, vp, i32]),
         "mtsb_trace_count": (i32, [vp, vp, sz, i32, i32, vp]),
         "mtsb_host_alloc": (vp, [sz]), "mtsb_host_free": (None, [vp]),
         "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
@@ -330,6 +332,18 @@ class Scene:
         """Asynchronous query on device pointers (ints); mode in {'closest','any','surface'}."""
         fn = {"closest": lib().mtsb_trace_closest, "any": lib().mtsb_trace_any, "surface": lib().mtsb_trace_surface}[mode]
         _check(fn(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_out), 1))
+
+    def ray_intersect_noalloc(self, rays, out=None):
+        """mtsb_trace_closest_noalloc with host buffers: at most NOALLOC_MAX_RAYS rays, no device allocation inside."""
+        r = self._rays(rays)
+        if out is None:
+            out = np.empty(r.shape[0], hit_dtype)
+        _check(lib().mtsb_trace_closest_noalloc(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def trace_device_noalloc(self, d_rays, n, d_hits):
+        """mtsb_trace_closest_noalloc on device pointers (ints); asynchronous on the context stream."""
+        _check(lib().mtsb_trace_closest_noalloc(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_hits), 1))
 
     def trace_count(self, rays, any_hit=False):
         r = self._rays(rays)

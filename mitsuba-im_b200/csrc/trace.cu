@@ -9,6 +9,7 @@
 #include "trace.cuh"
 #include "surface.cuh"
 #include <algorithm>
+#include <mutex>
 #include <stdlib.h>
 #include <string.h>
 
@@ -245,6 +246,80 @@ int mtsb_trace_surface(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_s
 }
 int mtsb_trace_light(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_light_hit *out, int on_device) {
 	return trace_common(scene, MODE_LIGHT, rays, n, out, on_device, "mtsb_trace_light");
+}
+
+// ---- allocation-free closest-hit query (no counterpart in the reference) ----
+//
+// Everything the ordinary entry point takes from cudaMalloc'ed memory — the persistent grid's work counter and, for host
+// pointers, the device staging of the rays and of the hit records (TracePipe above) — lives in ONE file-scope device array
+// of fixed size instead:
+//
+//     [0, 256)                                the work counter (8 bytes used)
+//     [256, 256 + 32 * MAX)                   rays staged from a host pointer
+//     [256 + 32 * MAX, 256 + 48 * MAX)        hit records on their way to a host pointer
+//
+// MAX = MTSB_NOALLOC_MAX_RAYS = 65536 rays a call (3 MiB + 256 bytes per device).  The array belongs to the module, so
+// every call on a device — whatever the scene or the context — shares it, and it keeps the last call's contents: the
+// counter is cleared in stream order before each launch, the staging areas are overwritten by the copy before they are
+// read.  Two calls that overlap on the GPU (two contexts = two streams on one device, or two host threads) race on it;
+// calls on one context are ordered by its stream.
+#define MTSB_NOALLOC_BYTES (256 + (size_t) MTSB_NOALLOC_MAX_RAYS * (sizeof(mtsb_ray) + sizeof(mtsb_hit)))
+static __device__ __align__(256) unsigned char g_noallocScratch[MTSB_NOALLOC_BYTES];
+
+// device address of the array, looked up once per device with that device current
+static std::mutex g_noallocMutex;
+static unsigned char *g_noallocPtr[64];
+
+static int noalloc_scratch(int device, unsigned char **out) {
+	if (device < 0 || device >= 64) MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_closest_noalloc: device %d outside the table (64 devices)", device);
+	std::lock_guard<std::mutex> lock(g_noallocMutex);
+	if (!g_noallocPtr[device]) {
+		MTSB_CUDA(cudaSetDevice(device));
+		unsigned char *ptr = nullptr;
+		MTSB_CUDA(cudaGetSymbolAddress((void **) &ptr, g_noallocScratch));
+		if (!ptr) MTSB_FAIL(MTSB_ECUDA, "mtsb_trace_closest_noalloc: cudaGetSymbolAddress returned a null address on device %d", device);
+		g_noallocPtr[device] = ptr;
+	}
+	*out = g_noallocPtr[device];
+	return 0;
+}
+
+int mtsb_trace_closest_noalloc(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_closest_noalloc: scene not committed");
+	if (n > MTSB_NOALLOC_MAX_RAYS)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_closest_noalloc: %zu rays exceed the fixed scratch of %u rays a call — split the batch or use mtsb_trace_closest",
+			n, (unsigned) MTSB_NOALLOC_MAX_RAYS);
+	if (n == 0) return 0;
+	if (!rays || !hits) MTSB_FAIL(MTSB_EINVAL, "mtsb_trace_closest_noalloc: NULL buffer");
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	unsigned char *scratch = nullptr;
+	MTSB_CHECK(noalloc_scratch(ctx->device, &scratch));
+	cudaStream_t st = ctx->stream;
+	unsigned long long *dWork = (unsigned long long *) scratch;
+	mtsb_ray *dRays = (mtsb_ray *) (scratch + 256);
+	mtsb_hit *dHits = (mtsb_hit *) (scratch + 256 + (size_t) MTSB_NOALLOC_MAX_RAYS * sizeof(mtsb_ray));
+	const mtsb_ray *src = rays;
+	mtsb_hit *dst = hits;
+	if (!on_device) {
+		MTSB_CUDA(cudaMemcpyAsync(dRays, rays, n * sizeof(mtsb_ray), cudaMemcpyHostToDevice, st));
+		src = dRays; dst = dHits;
+	}
+	MTSB_CUDA(cudaMemsetAsync(dWork, 0, sizeof(unsigned long long), st));      // the counter must start at zero
+	const unsigned grid = (unsigned) std::min<size_t>((size_t) ctx->smCount * MTSB_TRACE_BLOCKS_PER_SM, (n + MTSB_TRACE_BLOCK - 1) / MTSB_TRACE_BLOCK);
+	SceneDev S = scene->dev;
+	S.counters = nullptr;
+	const float4 *r = (const float4 *) src;
+	const unsigned long long nn = n;
+	void *o = dst;
+	if (scene->curved) trace_kernel<MODE_CLOSEST, false, true><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, nn, o, dWork);
+	else trace_kernel<MODE_CLOSEST, false, false><<<grid, MTSB_TRACE_BLOCK, 0, st>>>(S, r, nn, o, dWork);
+	MTSB_CUDA(cudaGetLastError());
+	if (!on_device) {
+		MTSB_CUDA(cudaMemcpyAsync(hits, dHits, n * sizeof(mtsb_hit), cudaMemcpyDeviceToHost, st));
+		MTSB_CUDA(cudaStreamSynchronize(st));
+	}
+	return 0;
 }
 
 // counting variant: re-traces a device or host batch with node / primitive-test counters enabled
