@@ -126,6 +126,7 @@ struct SceneDev {
 	int32_t  envEmitter;         // index of the constant environment emitter or -1
 	float    emitterNorm;        // DiscreteDistribution normalisation (1/sum of weights)
 	V3 aabbMin, aabbMax;         // enlarged kd-tree AABB (gkdtree.h:1217-1220)
+	float sceneDiameter;         // 2 x Scene::getBSphere().radius (scene.cpp:394-422): far end of the opacity query, records.inl:128-136
 	unsigned long long *counters; // optional traversal counters (nodes, tris, rays) or NULL
 	uint32_t oneBits;            // 0x3F800000, read as a constant-bank operand by the box test (trace.cuh: q_to_unit)
 	int fetchMinIdle;            // idle lanes a warp waits for before it pulls new rays from the work counter

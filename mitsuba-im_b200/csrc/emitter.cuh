@@ -14,6 +14,7 @@ namespace mtsb {
 struct DirectSample {
 	V3 value;        // radiance / pdf (already divided by the emitter selection probability)
 	V3 d, n;         // direction ref -> emitter, emitter normal
+	V3 p;            // dRec.p, the sampled position (the far end of Scene::evalTransmittance; render_vol.cuh)
 	float dist, pdf;
 	int measure, emitter;
 };
@@ -84,10 +85,11 @@ __device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeId
 // Emitter::sampleDirect for emitter `e`
 __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
 	const EmitterRec &em = S.emitters[e];
-	out.emitter = (int) e; out.pdf = 0; out.n = v3(0.0f); out.d = v3(0.0f); out.dist = 0; out.measure = M_SOLID_ANGLE;
+	out.emitter = (int) e; out.pdf = 0; out.n = v3(0.0f); out.d = v3(0.0f); out.dist = 0; out.measure = M_SOLID_ANGLE; out.p = ref;
 	if (em.type == MTSB_EMITTER_AREA) {
 		V3 p; float pdf;
 		shape_sample_position(S, em.shape, sx, sy, p, out.n, pdf);
+		out.p = p;
 		V3 d = p - ref;
 		const float distSquared = dot(d, d);
 		out.dist = sqrtf(distSquared);
@@ -102,7 +104,7 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 		V3 d = em.pos - ref;
 		out.dist = length(d);
 		const float invDist = 1.0f / out.dist;
-		out.d = d * invDist; out.pdf = 1; out.measure = M_DISCRETE;
+		out.d = d * invDist; out.pdf = 1; out.measure = M_DISCRETE; out.p = em.pos;
 		return em.radiance * (invDist * invDist);
 	} else {
 		V3 d; float pdf;
@@ -120,7 +122,7 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 		if (!(nearT < 0 && farT > 0)) return v3(0.0f);
 		const V3 p = ref + d * farT;
 		out.n = normalize(em.sphereCenter - p);
-		out.d = d; out.dist = farT; out.pdf = pdf;
+		out.d = d; out.dist = farT; out.pdf = pdf; out.p = p;
 		if (!is_zero(refN) && dot(d, refN) <= 0) return v3(0.0f);
 		return em.radiance / pdf;
 	}

@@ -217,4 +217,5 @@ connect_kernel(SceneDev S, PathState ps) {
 #include "render_shade.cuh"
 #include "render_tail.cuh"
 #include "render_direct.cuh"
+#include "render_vol.cuh"
 #include "render_host.cuh"

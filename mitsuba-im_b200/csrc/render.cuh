@@ -50,7 +50,7 @@ struct FilmDev {
 	int cropW, cropH;
 };
 
-struct IntegratorDev { int type, maxDepth, rrDepth, strictNormals, hideEmitters, emitterSamples, bsdfSamples; };
+struct IntegratorDev { int type, maxDepth, rrDepth, strictNormals, hideEmitters, emitterSamples, bsdfSamples, cameraMedium; };
 
 } // namespace mtsb
 

@@ -11,6 +11,9 @@ static inline bool fan_mode(const mtsb_render *r) {
 	return r->integ.type == MTSB_INTEGRATOR_DIRECT && (r->integ.emitterSamples != 1 || r->integ.bsdfSamples != 1);
 }
 
+// SimpleVolumetricPathTracer (render_vol.cuh): its own shade / connect kernels, no tail kernel, no ray suspension
+static inline bool vol_mode(const mtsb_render *r) { return r->integ.type == MTSB_INTEGRATOR_VOLPATH_SIMPLE; }
+
 // camera paths per chunk: the fan-out of `direct` shares the same budget of rays in flight
 static inline size_t max_paths(const mtsb_render *r) {
 	if (!fan_mode(r)) return MAX_PATHS_IN_FLIGHT;
@@ -21,13 +24,15 @@ static inline size_t max_paths(const mtsb_render *r) {
 // uses it: its WHILE node runs as many extra bounces as the parked rays need; the fixed launch sequences do not.
 static inline uint32_t suspend_after(const mtsb_render *r) {
 	const mtsb_ctx *ctx = r->scene->ctx;
-	return (fan_mode(r) || !ctx->useGraph || r->graphFailed) ? 0u : (uint32_t) ctx->suspendAfter;
+	return (fan_mode(r) || vol_mode(r) || !ctx->useGraph || r->graphFailed) ? 0u : (uint32_t) ctx->suspendAfter;
 }
 
 static int ensure_capacity(mtsb_render *r, size_t paths) {
 	if (paths <= r->capacity) return 0;
 	const size_t cap = std::max<size_t>(paths, 1024);
-	const size_t M = fan_mode(r) ? (size_t) r->integ.bsdfSamples : 0, N = fan_mode(r) ? (size_t) std::max(1, r->integ.emitterSamples) : 1;
+	// connection-queue entries per camera slot: N emitter samples in fan mode; 2 for volpath_simple (the opacity query of
+	// the sensor ray travels through the same queue as its emitter sample, render_vol.cuh)
+	const size_t M = fan_mode(r) ? (size_t) r->integ.bsdfSamples : 0, N = fan_mode(r) ? (size_t) std::max(1, r->integ.emitterSamples) : (vol_mode(r) ? 2 : 1);
 	const size_t wide = cap * (1 + M);            // camera slots + secondary slots (one per BSDF sample)
 	MTSB_CHECK(r->bufF4.alloc(wide * 6 + cap + cap * N * 3));
 	MTSB_CHECK(r->bufRng.alloc(cap));
@@ -106,8 +111,13 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	void *aExtend[] = { &S, &ps, &suspendAfter };
 	void *aShade[] = { &S, &ps, &integ, &seed };
 	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aExtend, scene));
-	MTSB_CUDA(add_kernel(body, &n2, n1, scene->lean ? (void *) shade_kernel<true> : (void *) shade_kernel<false>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
-	MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_kernel<true> : (void *) connect_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	if (vol_mode(r)) {
+		MTSB_CUDA(add_kernel(body, &n2, n1, (void *) volshade_kernel<0>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+		MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_vol_kernel<true> : (void *) connect_vol_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	} else {
+		MTSB_CUDA(add_kernel(body, &n2, n1, scene->lean ? (void *) shade_kernel<true> : (void *) shade_kernel<false>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+		MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_kernel<true> : (void *) connect_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aTrace, scene));
+	}
 	MTSB_CUDA(add_kernel(body, &n4, n3, (void *) advance_kernel, 1, 1, aCtl, nullptr));
 	if (tailBelow) MTSB_CUDA(add_kernel(g, &nTail, nWhile, scene->curved ? (void *) tail_kernel<true> : (void *) tail_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aShade, scene));
 	MTSB_CUDA(cudaGraphInstantiate(&r->bounceExec, g, 0));
@@ -138,7 +148,7 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 	generate_kernel<<<blocks_for(g.count, RENDER_BLOCK), RENDER_BLOCK, 0, st>>>(g, r->cam, ps, ps.queueA);
 	r->launches += 1;
 	const int maxDepth = r->integ.maxDepth;
-	const uint32_t tailBelow = (uint32_t) std::max(0, r->tailPaths);
+	const uint32_t tailBelow = vol_mode(r) ? 0u : (uint32_t) std::max(0, r->tailPaths);
 	const uint32_t bounded = maxDepth > 0 ? (uint32_t) maxDepth : 0x7fffffffu;
 
 	if (fan_mode(r)) {
@@ -184,9 +194,14 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		begin_kernel<<<1, 1, 0, st>>>(ps, ctl);
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
 			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
-			if (scene->lean) shade_kernel<true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
-			else shade_kernel<false><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
-			MTSB_CHECK(launch_trav(scene, scene->curved ? connect_kernel<true> : connect_kernel<false>, sh.traceGrid, st, S, ps));
+			if (vol_mode(r)) {
+				volshade_kernel<0><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+				MTSB_CHECK(launch_trav(scene, scene->curved ? connect_vol_kernel<true> : connect_vol_kernel<false>, sh.tailGrid, st, S, ps));
+			} else {
+				if (scene->lean) shade_kernel<true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+				else shade_kernel<false><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+				MTSB_CHECK(launch_trav(scene, scene->curved ? connect_kernel<true> : connect_kernel<false>, sh.traceGrid, st, S, ps));
+			}
 			advance_kernel<<<1, 1, 0, st>>>(ps, ctl);
 			if (poll && (bounce & 7) == 7) {
 				uint32_t live[2] = { 0, 0 };
@@ -224,7 +239,7 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: NULL argument or scene not committed");
 	if (film->width <= 0 || film->height <= 0 || (film->channels != 4 && film->channels != 5) || film->border < 0 || film->filter_radius <= 0)
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: bad film description (%dx%d, %d channels)", film->width, film->height, film->channels);
-	if (integrator->type != MTSB_INTEGRATOR_PATH && integrator->type != MTSB_INTEGRATOR_DIRECT)
+	if (integrator->type != MTSB_INTEGRATOR_PATH && integrator->type != MTSB_INTEGRATOR_DIRECT && integrator->type != MTSB_INTEGRATOR_VOLPATH_SIMPLE)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_create: integrator type %d is outside the GPU subset", integrator->type);
 	if (integrator->type == MTSB_INTEGRATOR_DIRECT && (integrator->emitter_samples < 0 || integrator->bsdf_samples < 0 ||
 			integrator->emitter_samples + integrator->bsdf_samples <= 0 || integrator->emitter_samples > 4096 || integrator->bsdf_samples > 4096))
@@ -244,6 +259,7 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 	ig.type = integrator->type; ig.maxDepth = integrator->max_depth; ig.rrDepth = integrator->rr_depth;
 	ig.strictNormals = integrator->strict_normals; ig.hideEmitters = integrator->hide_emitters;
 	ig.emitterSamples = integrator->emitter_samples; ig.bsdfSamples = integrator->bsdf_samples;
+	ig.cameraMedium = -1;
 	if (ig.type == MTSB_INTEGRATOR_DIRECT) { ig.maxDepth = 2; ig.rrDepth = 1 << 30; }   // direct(1,1) == one-bounce path
 	if (ig.maxDepth == 0) { delete r; MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: maxDepth must be -1 or > 0"); }
 	r->seed = (uint32_t) seed;
@@ -305,6 +321,7 @@ int mtsb_render_set_camera_medium(mtsb_render *r, int medium) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: NULL argument");
 	if (medium < -1 || medium >= (int) r->scene->media.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: medium %d unknown", medium);
 	r->cameraMedium = medium;
+	if (r->integ.cameraMedium != medium) { r->integ.cameraMedium = medium; destroy_bounce_graph(r); }     // a kernel argument of the graph's nodes
 	return 0;
 }
 

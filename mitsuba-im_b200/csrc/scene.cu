@@ -433,6 +433,20 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 		e.sphereCenter = c;
 		e.sphereRadius = fmaxf(MTS_EPSILON, sqrtf(dot(h, h)) * 1.5f);
 	}
+	// Scene::getBSphere() as Scene::initializeBidirectional leaves m_aabb (scene.cpp:394-422): kd-tree box + sensor box
+	// (mtsb_scene_expand_bounds) + the boxes of the emitters (a point emitter adds its position; area emitters lie inside
+	// the kd-tree box; the constant environment reports an invalid box).  The opacity query of volpath_simple ends at 2 R.
+	{
+		V3 lo = D.aabbMin, hi = D.aabbMax;
+		if (scene->hasExtra) {
+			lo = vmin3(lo, v3(scene->extraMin[0], scene->extraMin[1], scene->extraMin[2]));
+			hi = vmax3(hi, v3(scene->extraMax[0], scene->extraMax[1], scene->extraMax[2]));
+		}
+		for (const EmitterRec &e : scene->emitters)
+			if (e.type == MTSB_EMITTER_POINT) { lo = vmin3(lo, e.pos); hi = vmax3(hi, e.pos); }
+		const V3 c = 0.5f * (lo + hi), hd = hi - c;
+		D.sceneDiameter = 2.0f * sqrtf(dot(hd, hd));
+	}
 	MTSB_CHECK(scene->dMedia.upload(scene->media, st));
 	D.media = scene->dMedia.ptr;
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));

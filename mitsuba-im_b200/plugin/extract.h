@@ -106,6 +106,8 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		toRGB(props.getSpectrum("specularTransmittance", Spectrum(1.0f)), d.p + 6);
 		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
 		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
+	} else if (cls == "Null") {                                     // src/bsdfs/null.cpp:33-38: index-matched medium boundary
+		d.type = MTSB_BSDF_PASSTHROUGH;
 	} else if (cls == "SmoothConductor") {                          // src/bsdfs/conductor.cpp:155-177
 		d.type = MTSB_BSDF_CONDUCTOR;
 		ref<FileResolver> fResolver = Thread::getThread()->getFileResolver();

@@ -3,6 +3,61 @@
 
 MTS_NAMESPACE_BEGIN
 
+/// The scene's participating media in a fixed order (index = position): Scene::getMedia(), then whatever only the sensor
+/// or a shape refers to.  uploadScene and the camera-medium lookup of the render both go through this list.
+static std::vector<const Medium *> collectMedia(const Scene *scene) {
+	std::vector<const Medium *> media;
+	struct Add { static void one(std::vector<const Medium *> &v, const Medium *m) {
+		if (m && std::find(v.begin(), v.end(), m) == v.end()) v.push_back(m); } };
+	const ref_vector<Medium> &declared = scene->getMedia();
+	for (size_t i = 0; i < declared.size(); ++i) Add::one(media, declared[i].get());
+	if (scene->getSensor()) Add::one(media, scene->getSensor()->getMedium());
+	const ref_vector<Shape> &shapes = scene->getShapes();
+	for (size_t i = 0; i < shapes.size(); ++i) { Add::one(media, shapes[i]->getInteriorMedium()); Add::one(media, shapes[i]->getExteriorMedium()); }
+	return media;
+}
+static int mediumIndex(const std::vector<const Medium *> &media, const Medium *m) {
+	if (!m) return -1;
+	return (int) (std::find(media.begin(), media.end(), m) - media.begin());
+}
+
+/// HomogeneousMedium -> mtsb_medium_desc.  The sampling parameters are private to the plugin class, so they are re-derived
+/// from its Properties exactly as its constructor does (src/medium/homogeneous.cpp:156-226).
+static void describeMedium(const Medium *medium, mtsb_medium_desc &d) {
+	memset(&d, 0, sizeof(d));
+	const std::string cls = medium->getClass()->getName();
+	if (cls != "HomogeneousMedium")
+		SLog(EError, "gpupath: medium \"%s\" is outside the GPU subset (homogeneous)", cls.c_str());
+	const Properties &props = medium->getProperties();
+	Spectrum sigmaA = medium->getSigmaA(), sigmaS = medium->getSigmaS(), sigmaT = medium->getSigmaT();
+	const std::string strategy = props.getString("strategy", "balance");
+	Float weight = props.getFloat("mediumSamplingWeight", -1);
+	if (weight == -1) {
+		for (int i = 0; i < SPECTRUM_SAMPLES; ++i) {
+			const Float albedo = sigmaS[i] / sigmaT[i];
+			if (albedo > weight && sigmaT[i] != 0) weight = albedo;
+		}
+		if (weight > 0) weight = std::max(weight, (Float) 0.5f);
+	}
+	d.medium_sampling_weight = (float) weight;
+	if (strategy == "balance") d.strategy = 0;
+	else if (strategy == "single") {
+		int channel = 0;
+		Float smallest = std::numeric_limits<Float>::infinity();
+		for (int i = 0; i < SPECTRUM_SAMPLES; ++i) if (sigmaT[i] < smallest) { smallest = sigmaT[i]; channel = i; }
+		channel = props.getInteger("channel", channel);
+		d.strategy = 1; d.sampling_density = (float) sigmaT[channel];
+		if (props.getBoolean("monochromatic", false)) SLog(EError, "gpupath: monochromatic media are outside the GPU subset");
+	} else if (strategy == "manual") { d.strategy = 1; d.sampling_density = (float) props.getFloat("samplingDensity"); }
+	else SLog(EError, "gpupath: medium sampling strategy \"%s\" is outside the GPU subset (balance, single, manual)", strategy.c_str());
+	toRGB(sigmaA, d.sigma_a); toRGB(sigmaS, d.sigma_s);
+	const PhaseFunction *phase = medium->getPhaseFunction();
+	const std::string pcls = phase->getClass()->getName();
+	if (pcls == "IsotropicPhaseFunction") d.phase = 0;
+	else if (pcls == "HGPhaseFunction") { d.phase = 1; d.g = (float) phase->getProperties().getFloat("g", 0.8f); }
+	else SLog(EError, "gpupath: phase function \"%s\" is outside the GPU subset (isotropic, hg)", pcls.c_str());
+}
+
 /// Uploads shapes / BSDFs / emitters in Scene order and commits (BVH build on the device).
 static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 	mtsb_scene *out = NULL;
@@ -34,14 +89,19 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		if (id < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
 		emitterIds[e] = id;
 	}
+	const std::vector<const Medium *> media = collectMedia(scene);
+	for (size_t i = 0; i < media.size(); ++i) {
+		mtsb_medium_desc md; describeMedium(media[i], md);
+		if (mtsb_scene_add_medium(out, &md) < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+	}
 	const ref_vector<Shape> &shapes = scene->getShapes();
 	std::map<const BSDF *, int> bsdfIds;
 	for (size_t i = 0; i < shapes.size(); ++i) {
 		const Shape *shape = shapes[i].get();
 		const BSDF *bsdf = shape->getBSDF();
 		if (!bsdf) SLog(EError, "gpupath: shape %d has no BSDF", (int) i);
-		if (shape->isMediumTransition() || shape->hasSubsurface())
-			SLog(EError, "gpupath: participating media / subsurface scattering are outside the GPU subset");
+		if (shape->hasSubsurface())
+			SLog(EError, "gpupath: subsurface scattering is outside the GPU subset");
 		int bid;
 		if (bsdfIds.count(bsdf)) bid = bsdfIds[bsdf];
 		else {
@@ -91,6 +151,8 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 			rc = -1;
 		}
 		if (rc < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+		if (shape->isMediumTransition())
+			MTSB_CALL(mtsb_scene_set_shape_media(out, (int) i, mediumIndex(media, shape->getInteriorMedium()), mediumIndex(media, shape->getExteriorMedium())));
 	}
 	if (scene->getSensor()) {       // the part of Scene::getAABB() the environment emitter saw beside the geometry (scene.cpp:394-404)
 		const AABB sa = scene->getSensor()->getAABB();

@@ -80,6 +80,8 @@ public:
 		m_builder = b == "ploc" ? MTSB_BUILDER_PLOC : MTSB_BUILDER_LBVH;
 		// `direct` semantics when installed as direct.so or asked for explicitly
 		m_direct = props.getPluginName() == "direct" || props.getBoolean("direct", false);
+		// SimpleVolumetricPathTracer semantics (participating media) when installed as volpath_simple.so
+		m_volpath = props.getPluginName() == "volpath_simple" || props.getBoolean("volpath", false);
 		m_emitterSamples = props.getInteger("emitterSamples", props.getInteger("shadingSamples", 1));
 		m_bsdfSamples = props.getInteger("bsdfSamples", props.getInteger("shadingSamples", 1));
 		const int n = mtsb_device_count();
@@ -100,7 +102,7 @@ public:
 
 	void describeIntegrator(mtsb_integrator_desc &d) const {
 		memset(&d, 0, sizeof(d));
-		d.type = m_direct ? MTSB_INTEGRATOR_DIRECT : MTSB_INTEGRATOR_PATH;
+		d.type = m_direct ? MTSB_INTEGRATOR_DIRECT : (m_volpath ? MTSB_INTEGRATOR_VOLPATH_SIMPLE : MTSB_INTEGRATOR_PATH);
 		d.max_depth = m_maxDepth; d.rr_depth = m_rrDepth;
 		d.strict_normals = m_strictNormals ? 1 : 0; d.hide_emitters = m_hideEmitters ? 1 : 0;
 		d.emitter_samples = m_emitterSamples; d.bsdf_samples = m_bsdfSamples;
@@ -140,8 +142,10 @@ public:
 		mtsb_film_desc fd; describeFilm(*block, film->getReconstructionFilter(), film, fd);
 		mtsb_integrator_desc id; describeIntegrator(id);
 		std::vector<mtsb_render *> renders(m_gpus, (mtsb_render *) NULL);
-		for (int g = 0; g < m_gpus; ++g)
+		for (int g = 0; g < m_gpus; ++g) {
 			MTSB_CALL(mtsb_render_create(device(g, scene).scene, &cam, &fd, &id, seedFor(sampler), &renders[g]));
+			MTSB_CALL(mtsb_render_set_camera_medium(renders[g], mediumIndex(collectMedia(scene), sensor->getMedium())));
+		}
 		const size_t pixels = (size_t) film->getCropSize().x * film->getCropSize().y;
 		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixels, 1));
 		// path state, kernels and the bounce graph are set up before the clock starts (the reference's kd-tree build and
@@ -208,7 +212,7 @@ public:
 	MTS_DECLARE_CLASS()
 
 	int m_gpus, m_sppPerPass, m_seed, m_builder, m_emitterSamples, m_bsdfSamples;
-	bool m_direct;
+	bool m_direct, m_volpath;
 	volatile bool m_cancel;
 	GPUResponsiveIntegrator *m_responsive;      // the adapter made by makeResponsiveIntegrator (not owned; clears itself)
 	ref<Mutex> m_mutex;

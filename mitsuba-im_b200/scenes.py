@@ -220,6 +220,7 @@ class SceneDesc:
         self.media = []             # homogeneous media: dict(sigma_a, sigma_s, phase='isotropic'|'hg', g, strategy)
         self.sensor = None
         self.integrator = dict(kind="path", max_depth=-1, rr_depth=5)
+        self.camera_medium = None   # index into self.media: the medium the sensor sits in (Sensor::getMedium)
         self.sampler = dict(kind="independent", spp=4, seed=0)
 
     # -- building --------------------------------------------------------------------------------
@@ -251,6 +252,9 @@ class SceneDesc:
         self.media.append(dict(sigma_a=tuple(float(x) for x in sigma_a), sigma_s=tuple(float(x) for x in sigma_s), phase=phase,
                                g=float(g), strategy=strategy))
         return len(self.media) - 1
+
+    def set_camera_medium(self, medium):
+        self.camera_medium = medium
 
     def set_media(self, shape, interior=None, exterior=None):
         self.shapes[shape]["interior"], self.shapes[shape]["exterior"] = interior, exterior
@@ -331,7 +335,9 @@ class SceneDesc:
             else:
                 sc.add_emitter(B.EMITTER_CONSTANT, radiance=e["radiance"])
         for m in self.media:
-            sc.add_medium(m["sigma_a"], m["sigma_s"], strategy=dict(balance=0, single=1, manual=1)[m["strategy"]],
+            # `single` samples with sigma_t of the lowest-variance channel, the smallest one (homogeneous.cpp:190-204)
+            density = float(min(np.float32(a) + np.float32(b) for a, b in zip(m["sigma_a"], m["sigma_s"]))) if m["strategy"] == "single" else m.get("sampling_density", 0.0)
+            sc.add_medium(m["sigma_a"], m["sigma_s"], strategy=dict(balance=0, single=1, manual=1)[m["strategy"]], sampling_density=density,
                           phase=dict(isotropic=0, hg=1)[m["phase"]], g=m["g"])
         for k, s in enumerate(self.shapes):
             bd = s["bsdf"]
@@ -372,6 +378,13 @@ class SceneDesc:
 
     def integrator_desc(self):
         return make_integrator(**self.integrator)
+
+    def render(self, scene, seed=None, channels=5):
+        """binding.Render for this description on an uploaded scene (sensor medium applied)."""
+        rd = B.Render(scene, self.camera(), self.film(channels=channels), self.integrator_desc(), seed=self.sampler["seed"] if seed is None else seed)
+        if self.camera_medium is not None:
+            rd.set_camera_medium(self.camera_medium)
+        return rd
 
     # -- reference back end ----------------------------------------------------------------------
     @staticmethod
@@ -430,6 +443,11 @@ class SceneDesc:
             if k in ig:
                 out.append('<boolean name="%s" value="%s"/>' % (xmlk, "true" if ig[k] else "false"))
         out.append('</integrator>')
+        for k, m in enumerate(self.media):
+            ph = '<phase type="hg"><float name="g" value="%r"/></phase>' % m["g"] if m["phase"] == "hg" else '<phase type="isotropic"/>'
+            out.append('<medium type="homogeneous" id="medium%d"><rgb name="sigmaA" value="%s"/><rgb name="sigmaS" value="%s"/>'
+                       '<string name="strategy" value="%s"/>%s</medium>' % (k, ", ".join(repr(x) for x in m["sigma_a"]),
+                                                                           ", ".join(repr(x) for x in m["sigma_s"]), m["strategy"], ph))
         if self.sensor is not None:
             s, sm = self.sensor, self.sampler
             if s.get("aperture_radius", 0.0) > 0:
@@ -445,6 +463,8 @@ class SceneDesc:
             out.append('<film type="hdrfilm"><integer name="width" value="%d"/><integer name="height" value="%d"/>'
                        '<rfilter type="%s"/><string name="fileFormat" value="%s"/><string name="pixelFormat" value="rgb"/>'
                        '<boolean name="banner" value="false"/></film>' % (s["width"], s["height"], s["rfilter"], film_format))
+            if self.camera_medium is not None:
+                out.append('<ref id="medium%d"/>' % self.camera_medium)
             out.append('</sensor>')
         for e in self.emitters:
             if e["type"] == "point":
@@ -452,11 +472,6 @@ class SceneDesc:
                     e["pos"][0], e["pos"][1], e["pos"][2], ", ".join(repr(float(x)) for x in e["intensity"])))
             else:
                 out.append('<emitter type="constant"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in e["radiance"]))
-        for k, m in enumerate(self.media):
-            ph = '<phase type="hg"><float name="g" value="%r"/></phase>' % m["g"] if m["phase"] == "hg" else '<phase type="isotropic"/>'
-            out.append('<medium type="homogeneous" id="medium%d"><rgb name="sigmaA" value="%s"/><rgb name="sigmaS" value="%s"/>'
-                       '<string name="strategy" value="%s"/>%s</medium>' % (k, ", ".join(repr(x) for x in m["sigma_a"]),
-                                                                           ", ".join(repr(x) for x in m["sigma_s"]), m["strategy"], ph))
         for i, s in enumerate(self.shapes):
             em = ""
             if s["emitter"] is not None:
@@ -661,10 +676,12 @@ def analytic_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent
     return sd
 
 
-def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple"):
+def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False):
     """Participating media: a ball of isotropic fog behind an index-matched boundary (no BSDF: `null`), a
     glass ball filled with a forward-scattering (HG, g = 0.6) coloured medium, a diffuse ball, on a mesh floor under a mesh
-    area light, a point light and a constant environment; camera outside the media."""
+    area light, a point light and a constant environment; camera outside the media.  haze=True wraps all of it in a large
+    index-matched ball of thin haze (`single` sampling strategy) with the camera inside: paths start in a medium, the balls'
+    boundaries separate two media, and rays leave the haze through its boundary to reach the environment."""
     sd = SceneDesc()
     sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
     sd.add_constant_env((0.3, 0.35, 0.5))
@@ -672,10 +689,16 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
     milk = sd.add_medium((0.05, 0.4, 0.8), (3.0, 2.5, 1.5), phase="hg", g=0.6)
     V, N, F = displaced_sphere(2, seed=41, radius=0.6, center=(-1.0, 0.65, 0.1), amplitude=0.0)
     a = sd.add_mesh(V, N, F, bsdf=dict(type="passthrough"))
-    sd.set_media(a, interior=fog)
+    hz = sd.add_medium((0.02, 0.02, 0.02), (0.08, 0.09, 0.1), strategy="single") if haze else None
+    sd.set_media(a, interior=fog, exterior=hz)
     V, N, F = displaced_sphere(2, seed=42, radius=0.5, center=(0.4, 0.55, -0.2), amplitude=0.0)
     b = sd.add_mesh(V, N, F, bsdf=dict(type="dielectric"))
-    sd.set_media(b, interior=milk)
+    sd.set_media(b, interior=milk, exterior=hz)
+    if haze:
+        V, N, F = displaced_sphere(2, seed=44, radius=9.0, center=(0.0, 1.0, 0.0), amplitude=0.0)
+        c = sd.add_mesh(V, N, F, bsdf=dict(type="passthrough"))
+        sd.set_media(c, interior=hz)
+        sd.set_camera_medium(hz)
     V, N, F = displaced_sphere(2, seed=43, radius=0.4, center=(1.5, 0.45, 0.5), amplitude=0.03)
     sd.add_mesh(V, N, F, bsdf=dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
     g = 4.0

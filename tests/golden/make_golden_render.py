@@ -121,10 +121,24 @@ def thinlens_case(td):
     li_case(td, "thinlens", sd)
 
 
+def fog_cases(td):
+    """SimpleVolumetricPathTracer (src/integrators/path/volpath_simple.cpp) over homogeneous media: index-matched and
+    dielectric medium boundaries, isotropic and Henyey-Greenstein phase functions; with the camera outside every medium
+    (depth 6 and the short depth 3, where maxInteractions of Scene::evalTransmittance bites) and inside a haze (unbounded)."""
+    li_case(td, "fog", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=37))
+    li_case(td, "fog_short", S.fog_scene(48, 32, spp=4, max_depth=3, sampler="ctr", seed=41))
+    li_case(td, "fog_haze", S.fog_scene(48, 32, spp=4, max_depth=-1, sampler="ctr", seed=43, haze=True))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "fog":              # participating media (round 2)
+        with tempfile.TemporaryDirectory() as td:
+            fog_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "analytic":         # analytic sphere / disk shapes (round 2)
         with tempfile.TemporaryDirectory() as td:
             li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
+        fog_cases(td)
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "direct_fan":       # only the cases added in round 2
         with tempfile.TemporaryDirectory() as td:
@@ -143,3 +157,4 @@ if __name__ == "__main__":
         for n_em, n_bsdf in ((4, 2), (1, 3), (3, 1), (2, 0)):
             direct_fan_case(td, n_em, n_bsdf)
         li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
+        fog_cases(td)

@@ -77,7 +77,7 @@ TAIL_ALL, TAIL_OFF = 1 << 30, 0     # every path through the late-bounce kernel 
 def _li_image(pkg, ctx, sd, tail=-1, positions=False):
     sc = sd.upload(ctx)
     w, h, spp = sd.sensor["width"], sd.sensor["height"], sd.sampler["spp"]
-    rd = pkg.binding.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=sd.sampler["seed"])
+    rd = sd.render(sc)
     rd.set_tail(tail)
     ys, xs, ss = np.meshgrid(np.arange(h), np.arange(w), np.arange(spp), indexing="ij")
     samples = np.stack([xs.ravel(), ys.ravel(), ss.ravel(), np.zeros(xs.size)], axis=1).astype(np.uint32)
@@ -152,6 +152,35 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     assert np.allclose(dev[nominal], img[nominal], rtol=1e-4, atol=1e-5)
     assert stats["paths"] == img.shape[0] * img.shape[1] * spp * 2      # render_samples + render_pass
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
+
+
+@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze"])
+def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
+    """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
+    (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
+    boundaries (scene.cpp:650-713), against the reference's own plugins on the same random numbers; parameters of
+    make_golden_render.fog_cases."""
+    S = pkg.scenes
+    g = golden("li_%s.npz" % name)
+    ref = g["image"]
+    spp, seed = int(g["spp"]), int(g["seed"])
+    sd = S.fog_scene(48, 32, spp=spp, max_depth=dict(fog=6, fog_short=3, fog_haze=-1)[name], sampler="ctr", seed=seed, haze=name == "fog_haze")
+    L, film, stats = _li_image(pkg, ctx, sd)
+    img = L[..., 0:3].mean(axis=2)
+    ok = _close(img, ref, 2e-3, 2e-4).all(axis=2)
+    print(name, "pixels within tolerance: %.4f" % ok.mean(), "mean", img.mean(), "ref", ref.mean())
+    assert ok.mean() >= 0.97, "only %.4f of the pixels agree" % ok.mean()
+    assert abs(img.mean() - ref.mean()) <= 0.01 * ref.mean()
+    # opacity (records.inl:117-145): 1 on opaque first hits, inside [0, 1] behind index-matched boundaries / in the haze
+    a = L[..., 3]
+    assert np.isfinite(a).all() and a.min() >= 0.0 and a.max() <= 1.0      # a negative channel would be rejected by ImageBlock::put
+    assert (a == 1.0).mean() > 0.3      # an opaque surface behind a fog ball makes the pixel opaque (T = 0 at the occluder)
+    b = sd.film().border
+    wgt = film[b:film.shape[0] - b, b:film.shape[1] - b, 4]
+    nominal = np.isclose(wgt, np.median(wgt), rtol=1e-6)
+    dev = film[b:film.shape[0] - b, b:film.shape[1] - b, 0:3] / wgt[..., None]
+    assert np.allclose(dev[nominal], img[nominal], rtol=1e-4, atol=1e-5)
+    assert stats["paths"] == img.shape[0] * img.shape[1] * spp * 2
 
 
 def _imageblock_put(shape, border, radius, table, pos, values):
