@@ -26,7 +26,7 @@ def render_config(pkg, ctx, stream, sd, spp, warmup=1, builder=None):
     t0 = time.perf_counter()
     sc = sd.upload(ctx, B.BUILDER_PLOC if builder is None else builder)
     upload_s = time.perf_counter() - t0
-    rd = B.Render(sc, sd.camera(), sd.film(), sd.integrator_desc(), seed=1)
+    rd = sd.render(sc, seed=1)
     w, h = sd.sensor["width"], sd.sensor["height"]
     # warm-up: at least `warmup` short passes and at least 0.3 s of rendering, so that clocks and caches are in steady state
     # (warm-up passes are large enough to reach the full path-state capacity, so no allocation lands in the timed pass)
@@ -254,6 +254,13 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         out["config1_cornell_512x512_64spp"] = render_config(pkg, ctx, stream, S.cornell_box(512, 512, spp=64, max_depth=5), 64, builder=builder)
         if cpu:
             out["config1_cpu_reference"] = cpu_reference(pkg, S.cornell_box(512, 512, spp=16, max_depth=5), os.cpu_count() or 1)
+    if "vol" in configs and rank == 0:
+        # SimpleVolumetricPathTracer over homogeneous media (render_vol.cuh) — camera inside a haze, a fog ball behind
+        # an index-matched boundary, a glass ball of HG medium; the reference's own volpath_simple on the host cores beside it
+        out["volpath_fog_1024x768_64spp"] = render_config(pkg, ctx, stream, S.fog_scene(1024, 768, spp=64, max_depth=8, haze=True), 64, builder=builder)
+        if cpu:
+            out["volpath_cpu_reference"] = cpu_reference(pkg, S.fog_scene(1024, 768, spp=8, max_depth=8, haze=True), os.cpu_count() or 1,
+                                                         what="fog scene (volpath_simple) at %d spp (of 64)")
     sd = None
     if {3, 4, 5, "plugin"} & set(configs):
         t0 = time.perf_counter()
@@ -290,7 +297,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", nargs="*", default=["1", "3", "5"], help="1 3 4 5 and/or plugin")
+    ap.add_argument("--config", nargs="*", default=["1", "3", "5"], help="1 3 4 5, vol and/or plugin")
     ap.add_argument("--spp4", type=int, default=1024)
     ap.add_argument("--builder", default=None, choices=["lbvh", "ploc"])
     ap.add_argument("--spp3", type=int, default=256, help="samples per pixel of config 3 (BASELINE: 256; smaller only for ncu runs)")

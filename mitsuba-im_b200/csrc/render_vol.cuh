@@ -27,8 +27,13 @@ enum { VF_EMITTED = 1,        // rRec.type & EEmittedRadiance
 #define VQ_PACK(flags, medium, maxi) ((uint32_t) (flags) | ((uint32_t) ((medium) + 1) << 3) | ((uint32_t) (maxi) << 16))
 
 // math::fastexp / fastlog on Linux x86_64 go through double precision (include/mitsuba/core/math.h:177-199)
+#ifdef MTSB_VOL_FP32_EXP
+__device__ inline float mts_exp(float x) { return expf(x); }
+__device__ inline float mts_log(float x) { return logf(x); }
+#else
 __device__ inline float mts_exp(float x) { return (float) exp((double) x); }
 __device__ inline float mts_log(float x) { return (float) log((double) x); }
+#endif
 
 // HomogeneousMedium::evalTransmittance over a length (homogeneous.cpp:238-245)
 __device__ inline V3 medium_transmittance(const MediumRec &m, float length) {
@@ -273,8 +278,11 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 	}
 }
 
+#ifndef MTSB_VOLSHADE_MIN_BLOCKS
+#define MTSB_VOLSHADE_MIN_BLOCKS 1
+#endif
 template <int DUMMY = 0>
-__global__ void __launch_bounds__(RENDER_BLOCK)
+__global__ void __launch_bounds__(RENDER_BLOCK, MTSB_VOLSHADE_MIN_BLOCKS)
 volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
 	const uint32_t n = ps.counters[parity];
