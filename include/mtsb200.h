@@ -91,7 +91,7 @@ typedef struct mtsb_light_hit {
 	uint32_t pad;
 } mtsb_light_hit;
 
-/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughconductor,conductor,roughdielectric}.cpp), constant textures only. */
+/* BSDF subset (src/bsdfs/{diffuse,dielectric,plastic,roughplastic,roughconductor,conductor,roughdielectric,null,twosided}.cpp), constant textures only. */
 enum {
 	MTSB_BSDF_DIFFUSE        = 0,  /* p[0..2] reflectance                                                    */
 	MTSB_BSDF_DIELECTRIC     = 1,  /* p[0] eta=intIOR/extIOR, p[1..3] specularReflectance, p[4..6] specularTransmittance */
@@ -107,6 +107,11 @@ enum {
 	                                  (src/bsdfs/roughdielectric.cpp:186-214)                                 */
 	MTSB_BSDF_PASSTHROUGH    = 7,  /* `null` (src/bsdfs/null.cpp): index-matched boundary of a participating medium — the only
 	                                  lobe is wo = -wi with weight 1 (ENull); emitter sampling sees through it              */
+	MTSB_BSDF_ROUGHPLASTIC   = 8,  /* `roughplastic` (src/bsdfs/roughplastic.cpp:199-520), constant alpha: p[0] alpha, p[1] eta=intIOR/extIOR,
+	                                  p[2..4] diffuseReflectance, p[5..7] specularReflectance, p[8] specularSamplingWeight,
+	                                  p[9] Fdr = 1 - internal diffuse rough transmittance (RoughTransmittance::evalDiffuse of the
+	                                  1/eta slice), p[10] nonlinear(0/1), p[11] distribution (0 beckmann, 1 ggx), p[12] sampleVisible;
+	                                  p[13..14] are filled in by the library.  Needs mtsb_scene_set_bsdf_table.            */
 	MTSB_BSDF_TWOSIDED_FLAG  = 0x100 /* OR-ed in: wrapped by `twosided` (src/bsdfs/twosided.cpp), same BSDF both sides */
 };
 typedef struct mtsb_bsdf_desc {
@@ -186,6 +191,10 @@ MTSB_API void *mtsb_ctx_stream(mtsb_ctx *ctx);
 MTSB_API int  mtsb_scene_create(mtsb_ctx *ctx, mtsb_scene **out);
 MTSB_API void mtsb_scene_destroy(mtsb_scene *scene);
 MTSB_API int  mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc);          /* returns id >= 0 */
+/* The external rough-transmittance table of a `roughplastic` BSDF: RoughTransmittance after setEta(eta) and setAlpha(alpha)
+ * (src/bsdfs/rtrans.h:277-377) — n values over the warped angle cosTheta^(1/4) in [0, 1], evaluated on the device with
+ * evalCubicInterp1D (src/libcore/spline.cpp:23-60).  The plugin builds it from the reference's own data/microfacet/{beckmann,ggx}.dat. */
+MTSB_API int  mtsb_scene_set_bsdf_table(mtsb_scene *scene, int bsdf, const float *table, size_t n);
 MTSB_API int  mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc);    /* returns id >= 0 */
 /* TriMesh (include/mitsuba/render/trimesh.h): positions 3V, normals 3V or NULL, texcoords 2V or NULL,
  * triangles 3T uint32.  emitter = -1 if none.  Returns the shape index. */

@@ -22,6 +22,7 @@ MTSB_NO_HIT = 0xFFFFFFFF
 NOALLOC_MAX_RAYS = 65536
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
 BSDF_PASSTHROUGH = 7
+BSDF_ROUGHPLASTIC = 8
 BSDF_TWOSIDED_FLAG = 0x100
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
 INTEGRATOR_PATH, INTEGRATOR_DIRECT, INTEGRATOR_VOLPATH_SIMPLE = 0, 1, 2
@@ -100,6 +101,7 @@ def lib():
         "mtsb_ctx_stream": (vp, [vp]),
         "mtsb_scene_create": (i32, [vp, C.POINTER(vp)]), "mtsb_scene_destroy": (None, [vp]),
         "mtsb_scene_add_bsdf": (i32, [vp, C.POINTER(BsdfDesc)]), "mtsb_scene_add_emitter": (i32, [vp, C.POINTER(EmitterDesc)]),
+        "mtsb_scene_set_bsdf_table": (i32, [vp, i32, vp, sz]),
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
@@ -213,6 +215,11 @@ class Scene:
         for i, v in enumerate(params):
             d.p[i] = float(v)
         return _check(lib().mtsb_scene_add_bsdf(self.h, C.byref(d)))
+
+    def set_bsdf_table(self, bsdf, table):
+        """The rough-transmittance slice of a roughplastic BSDF (hostmath.rough_transmittance_slices)."""
+        t = np.ascontiguousarray(table, dtype=np.float32)
+        _check(lib().mtsb_scene_set_bsdf_table(self.h, int(bsdf), _ptr(t), t.shape[0]))
 
     def add_emitter(self, type_, radiance=(1, 1, 1), pos=(0, 0, 0), sampling_weight=1.0):
         d = EmitterDesc()

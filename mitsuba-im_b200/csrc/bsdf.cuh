@@ -7,6 +7,7 @@
 //   plastic        src/bsdfs/plastic.cpp:248-455
 //   roughconductor src/bsdfs/roughconductor.cpp:260-413
 //   twosided       src/bsdfs/twosided.cpp:106-170 (same nested BRDF on both sides)
+//   roughplastic   src/bsdfs/roughplastic.cpp:330-520 (constant alpha; RoughTransmittance table, src/bsdfs/rtrans.h)
 //   null           the black diffuse BSDF Shape::configure gives emitters without one (src/librender/shape.cpp:48-58)
 #pragma once
 
@@ -23,6 +24,7 @@ __device__ inline uint32_t bsdf_type(const BsdfRec &b) {   // m_combinedType of 
 		case MTSB_BSDF_CONDUCTOR: t = B_DELTA_REFL | B_FRONT; break;
 		case MTSB_BSDF_ROUGHDIELECTRIC: t = B_GLOSSY_REFL | B_GLOSSY_TRANS | B_FRONT | B_BACK; break;
 		case MTSB_BSDF_PASSTHROUGH: t = B_NULL | B_FRONT | B_BACK; break;        // null.cpp:35-38
+		case MTSB_BSDF_ROUGHPLASTIC: t = B_GLOSSY_REFL | B_DIFFUSE_REFL | B_FRONT; break;   // roughplastic.cpp:264-269
 		default: t = B_GLOSSY_REFL | B_FRONT; break;
 	}
 	if (b.type & MTSB_BSDF_TWOSIDED_FLAG) t |= B_BACK;
@@ -135,6 +137,82 @@ __device__ inline V3 roughdielectric_sample(const BsdfRec &b, const V3 &wi, floa
 }
 
 
+// ---- roughplastic (src/bsdfs/roughplastic.cpp) ----
+// RoughTransmittance::eval with eta and alpha fixed (rtrans.h:179-191, 243): evalCubicInterp1D (spline.cpp:23-60) of the
+// table over cosTheta^(1/4), clamped to [0, 1].  The record carries the device address of {count, values...} in p[13..14].
+__device__ inline float roughplastic_T(const BsdfRec &b, float cosTheta) {
+	if (!(cosTheta >= 0)) return 0.0f;
+	const unsigned long long addr = (unsigned long long) __float_as_uint(b.p[13]) | ((unsigned long long) __float_as_uint(b.p[14]) << 32);
+	const float *tab = (const float *) addr;
+	const int size = (int) tab[0];
+	const float *values = tab + 1;
+	const float x = powf(fabsf(cosTheta), 0.25f);
+	float result = 0.0f;
+	if (x >= 0.0f && x <= 1.0f) {
+		float t = x * (float) (size - 1);
+		const int k = max(0, min((int) t, size - 2));
+		const float f0 = values[k], f1 = values[k + 1];
+		const float d0 = k > 0 ? 0.5f * (values[k + 1] - values[k - 1]) : values[k + 1] - values[k];
+		const float d1 = k + 2 < size ? 0.5f * (values[k + 2] - values[k]) : values[k + 1] - values[k];
+		t = t - (float) k;
+		const float t2 = t * t, t3 = t2 * t;
+		result = (2 * t3 - 3 * t2 + 1) * f0 + (-2 * t3 + 3 * t2) * f1 + (t3 - 2 * t2 + t) * d0 + (t3 - t2) * d1;
+	}
+	return fminf(1.0f, fmaxf(0.0f, result));
+}
+__device__ inline float roughplastic_prob_specular(const BsdfRec &b, float cosThetaI) {    // :395-402, :449-456
+	float probSpecular = 1 - roughplastic_T(b, cosThetaI);
+	const float ssw = b.p[8];
+	return (probSpecular * ssw) / (probSpecular * ssw + (1 - probSpecular) * (1 - ssw));
+}
+__device__ inline V3 roughplastic_eval(const BsdfRec &b, const V3 &wi, const V3 &wo) {       // :330-381
+	if (wi.z <= 0 || wo.z <= 0) return v3(0.0f);
+	Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[0], b.p[12] != 0);
+	const V3 H = normalize(wo + wi);
+	const float D = distr.eval(H);
+	const float F = fresnel_dielectric_ext(dot(wi, H), b.p[1]);
+	const float G = distr.G(wi, wo, H);
+	const float value = F * D * G / (4.0f * wi.z);
+	V3 result = v3(b.p[5], b.p[6], b.p[7]) * value;
+	V3 diff = v3(b.p[2], b.p[3], b.p[4]);
+	const float T12 = roughplastic_T(b, wi.z), T21 = roughplastic_T(b, wo.z), Fdr = b.p[9];
+	if (b.p[10] != 0) diff = v3(diff.x / (1 - diff.x * Fdr), diff.y / (1 - diff.y * Fdr), diff.z / (1 - diff.z * Fdr));
+	else diff /= 1 - Fdr;
+	const float invEta2 = 1.0f / (b.p[1] * b.p[1]);
+	return result + diff * (MTS_INV_PI * wo.z * T12 * T21 * invEta2);
+}
+__device__ inline float roughplastic_pdf(const BsdfRec &b, const V3 &wi, const V3 &wo) {    // :383-432
+	if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+	Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[0], b.p[12] != 0);
+	const V3 H = normalize(wo + wi);
+	const float probSpecular = roughplastic_prob_specular(b, wi.z), probDiffuse = 1 - probSpecular;
+	const float dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+	const float prob = distr.pdf(wi, H);
+	return prob * dwh_dwo * probSpecular + probDiffuse * (MTS_INV_PI * wo.z);
+}
+__device__ inline V3 roughplastic_sample(const BsdfRec &b, const V3 &wi, float sx, float sy, BsdfSample &out) {   // :434-495
+	if (wi.z <= 0) return v3(0.0f);
+	Microfacet distr; distr.init((int) b.p[11], b.p[0], b.p[0], b.p[12] != 0);
+	bool choseSpecular = true;
+	const float probSpecular = roughplastic_prob_specular(b, wi.z);
+	if (sy < probSpecular) sy /= probSpecular;
+	else { sy = (sy - probSpecular) / (1 - probSpecular); choseSpecular = false; }
+	if (choseSpecular) {
+		float mpdf;
+		const V3 m = distr.sample(wi, sx, sy, mpdf);
+		out.wo = 2 * dot(wi, m) * m - wi;
+		out.type = B_GLOSSY_REFL;
+		if (out.wo.z <= 0) return v3(0.0f);
+	} else {
+		out.type = B_DIFFUSE_REFL;
+		out.wo = square_to_cosine_hemisphere(sx, sy);
+	}
+	out.eta = 1.0f;
+	out.pdf = roughplastic_pdf(b, wi, out.wo);
+	if (out.pdf == 0) return v3(0.0f);
+	return roughplastic_eval(b, wi, out.wo) / out.pdf;
+}
+
 // LEAN: the scene's BSDFs are all of {diffuse, null, dielectric, roughconductor with GGX + visible-normal sampling} (the
 // set of configs 1, 3, 4, 5).  The other cases are then unreachable and their code — rough dielectric, Beckmann's
 // visible-normal inversion, plastic, smooth conductor — is left out of the kernel: the full shade kernel stalls 6-11
@@ -148,6 +226,7 @@ __device__ inline V3 bsdf_eval_1(const BsdfRec &b, const V3 &wi, const V3 &wo) {
 		}
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: case MTSB_BSDF_PASSTHROUGH: return v3(0.0f);     // discrete measure only
 		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_eval(b, wi, wo);
+		case MTSB_BSDF_ROUGHPLASTIC: if (LEAN) __builtin_unreachable(); return roughplastic_eval(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (LEAN) __builtin_unreachable();
 			if (wo.z <= 0 || wi.z <= 0) return v3(0.0f);
@@ -176,6 +255,7 @@ __device__ inline float bsdf_pdf_1(const BsdfRec &b, const V3 &wi, const V3 &wo)
 			return MTS_INV_PI * wo.z;
 		case MTSB_BSDF_DIELECTRIC: case MTSB_BSDF_CONDUCTOR: case MTSB_BSDF_PASSTHROUGH: return 0.0f;
 		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_pdf(b, wi, wo);
+		case MTSB_BSDF_ROUGHPLASTIC: if (LEAN) __builtin_unreachable(); return roughplastic_pdf(b, wi, wo);
 		case MTSB_BSDF_PLASTIC: {
 			if (LEAN) __builtin_unreachable();
 			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
@@ -242,6 +322,7 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			return plastic_diffuse(b) * ((1 / (eta * eta)) * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
 		}
 		case MTSB_BSDF_ROUGHDIELECTRIC: if (LEAN) __builtin_unreachable(); return roughdielectric_sample(b, wi, sx, sy, sz, out);
+		case MTSB_BSDF_ROUGHPLASTIC: if (LEAN) __builtin_unreachable(); return roughplastic_sample(b, wi, sx, sy, out);
 		case MTSB_BSDF_CONDUCTOR: {                                // conductor.cpp:214-235
 			if (LEAN) __builtin_unreachable();
 			if (wi.z <= 0) return v3(0.0f);

@@ -134,11 +134,24 @@ int mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc) {
 	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: NULL argument");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_bsdf: scene already committed");
 	int base = desc->type & 0xff;
-	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_PASSTHROUGH)
+	if (base < MTSB_BSDF_DIFFUSE || base > MTSB_BSDF_ROUGHPLASTIC)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_bsdf: BSDF type %d is outside the GPU subset", desc->type);
 	BsdfRec r; r.type = desc->type; memcpy(r.p, desc->p, sizeof(r.p));
 	scene->bsdfs.push_back(r);
+	scene->bsdfTableOffset.push_back(-1);
 	return (int) scene->bsdfs.size() - 1;
+}
+
+int mtsb_scene_set_bsdf_table(mtsb_scene *scene, int bsdf, const float *table, size_t n) {
+	if (!scene || !table) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_table: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_table: scene already committed");
+	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_table: bsdf id %d unknown", bsdf);
+	if ((scene->bsdfs[bsdf].type & 0xff) != MTSB_BSDF_ROUGHPLASTIC) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_table: bsdf %d takes no table", bsdf);
+	if (n < 2 || n > 4096) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_table: %zu entries (2..4096 expected)", n);
+	scene->bsdfTableOffset[bsdf] = (long) scene->bsdfTables.size();
+	scene->bsdfTables.push_back((float) n);
+	scene->bsdfTables.insert(scene->bsdfTables.end(), table, table + n);
+	return 0;
 }
 
 int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
@@ -378,6 +391,14 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 
 	MTSB_CHECK(scene->dShapes.upload(scene->shapes, st));
 	MTSB_CHECK(scene->dRects.upload(scene->rects, st));
+	// lookup tables first: a roughplastic record carries the device address of its table in p[13..14]
+	if (!scene->bsdfTables.empty()) MTSB_CHECK(scene->dBsdfTables.upload(scene->bsdfTables, st));
+	for (size_t i = 0; i < scene->bsdfs.size(); ++i) {
+		if ((scene->bsdfs[i].type & 0xff) != MTSB_BSDF_ROUGHPLASTIC) continue;
+		if (scene->bsdfTableOffset[i] < 0) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: roughplastic BSDF %zu has no transmittance table (mtsb_scene_set_bsdf_table)", i);
+		const float *dev = scene->dBsdfTables.ptr + scene->bsdfTableOffset[i];
+		memcpy(&scene->bsdfs[i].p[13], &dev, sizeof(dev));
+	}
 	MTSB_CHECK(scene->dBsdfs.upload(scene->bsdfs, st));
 	MTSB_CHECK(scene->dPositions.upload(scene->positions, st));
 	MTSB_CHECK(scene->dNormals.upload(scene->normals, st));

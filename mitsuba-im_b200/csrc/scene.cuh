@@ -17,6 +17,9 @@ struct mtsb_scene {
 	std::vector<mtsb::ShapeRec> shapes;
 	std::vector<mtsb::RectRec> rects;
 	std::vector<mtsb::BsdfRec> bsdfs;
+	std::vector<float> bsdfTables;                 // per-BSDF lookup tables, each stored as {count, values...} (roughplastic)
+	std::vector<long> bsdfTableOffset;             // per BSDF: offset into bsdfTables or -1
+	mtsb::DevBuf<float> dBsdfTables;
 	std::vector<mtsb::EmitterRec> emitters;
 	std::vector<mtsb::MediumRec> media;
 	std::vector<float> emitterWeights;

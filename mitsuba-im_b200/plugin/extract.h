@@ -14,6 +14,8 @@
 #include <mitsuba/render/sampler.h>
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/plugin.h>
+#include "microfacet.h"          /* src/bsdfs/microfacet.h: MicrofacetDistribution(props) reads alpha / distribution / sampleVisible */
+#include "rtrans.h"              /* src/bsdfs/rtrans.h: RoughTransmittance, header-only, as roughplastic.cpp includes it */
 #include "ior.h"                 /* src/bsdfs/ior.h: lookupIOR(), header-only, as the BSDF plugins include it */
 #include "../../include/mtsb200.h"
 #include <map>
@@ -41,7 +43,14 @@ static inline Intersection dummyIntersection() {
 }
 
 /// BSDF plugin -> mtsb_bsdf_desc.  Class names are the reference's RTTI names.
-static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
+/// The reference's own RoughTransmittance, opened up far enough to read the reduced table back
+struct RoughTransmittanceAccess : public RoughTransmittance {
+	RoughTransmittanceAccess(MicrofacetDistribution::EType type) : RoughTransmittance(type) { }
+	const Float *trans() const { return m_trans; }
+	size_t thetaSamples() const { return m_thetaSamples; }
+};
+
+static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float> *table = NULL) {
 	memset(&d, 0, sizeof(d));
 	const std::string cls = bsdf->getClass()->getName();
 	const Properties &props = bsdf->getProperties();
@@ -106,6 +115,33 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		toRGB(props.getSpectrum("specularTransmittance", Spectrum(1.0f)), d.p + 6);
 		d.p[11] = distr == "ggx" ? 1.0f : 0.0f;
 		d.p[12] = props.getBoolean("sampleVisible", true) ? 1.0f : 0.0f;
+	} else if (cls == "RoughPlastic") {                             // src/bsdfs/roughplastic.cpp:199-303
+		d.type = MTSB_BSDF_ROUGHPLASTIC;
+		const Float intIOR = lookupIOR(props, "intIOR", "polypropylene"), extIOR = lookupIOR(props, "extIOR", "air");
+		const Float eta = intIOR / extIOR;
+		MicrofacetDistribution distr(props);
+		if (distr.isAnisotropic()) SLog(EError, "gpupath: anisotropic roughplastic is not supported by the plugin either");
+		if (props.hasProperty("alpha") && props.getType("alpha") != Properties::EFloat)
+			SLog(EError, "gpupath: roughplastic with a textured alpha is outside the GPU subset");
+		const Spectrum diff = props.getSpectrum("diffuseReflectance", Spectrum(0.5f));
+		const Spectrum spec = props.getSpectrum("specularReflectance", Spectrum(1.0f));
+		d.p[0] = (float) distr.getAlpha(); d.p[1] = (float) eta;
+		toRGB(diff, d.p + 2); toRGB(spec, d.p + 5);
+		const Float dAvg = diff.getLuminance(), sAvg = spec.getLuminance();
+		d.p[8] = (float) (sAvg / (dAvg + sAvg));
+		// the reductions RoughPlastic::configure performs (:283-303), by the reference's own class
+		ref<RoughTransmittanceAccess> ext = new RoughTransmittanceAccess(distr.getType());
+		ext->checkEta(eta); ext->checkAlpha(distr.getAlpha());
+		ref<RoughTransmittance> internal = ext->clone();
+		ext->setEta(eta); internal->setEta(1 / eta);
+		ext->setAlpha(distr.getAlpha());
+		d.p[9] = (float) (1 - internal->evalDiffuse(distr.getAlpha()));
+		d.p[10] = props.getBoolean("nonlinear", false) ? 1.0f : 0.0f;
+		d.p[11] = distr.getType() == MicrofacetDistribution::EGGX ? 1.0f : 0.0f;
+		if (distr.getType() != MicrofacetDistribution::EGGX && distr.getType() != MicrofacetDistribution::EBeckmann)
+			SLog(EError, "gpupath: roughplastic distribution outside the GPU subset (beckmann, ggx)");
+		d.p[12] = distr.getSampleVisible() ? 1.0f : 0.0f;
+		if (table) table->assign(ext->trans(), ext->trans() + ext->thetaSamples());
 	} else if (cls == "Null") {                                     // src/bsdfs/null.cpp:33-38: index-matched medium boundary
 		d.type = MTSB_BSDF_PASSTHROUGH;
 	} else if (cls == "SmoothConductor") {                          // src/bsdfs/conductor.cpp:155-177
@@ -134,7 +170,7 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d) {
 		if (!n0 || !n1 || !n0->getClass()->derivesFrom(MTS_CLASS(BSDF)) || !n1->getClass()->derivesFrom(MTS_CLASS(BSDF)))
 			SLog(EError, "gpupath: cannot read the nested BRDFs of %s", desc.substr(0, 200).c_str());
 		mtsb_bsdf_desc d1;
-		if (!describeBSDF(n0, d) || !describeBSDF(n1, d1))
+		if (!describeBSDF(n0, d, table) || !describeBSDF(n1, d1))
 			SLog(EError, "gpupath: twosided around a BRDF outside the GPU subset: %s", desc.c_str());
 		if (memcmp(&d, &d1, sizeof(d)) != 0)
 			SLog(EError, "gpupath: twosided with two DIFFERENT nested BRDFs is outside the GPU subset: %s", desc.c_str());

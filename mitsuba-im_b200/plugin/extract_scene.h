@@ -106,11 +106,13 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		if (bsdfIds.count(bsdf)) bid = bsdfIds[bsdf];
 		else {
 			mtsb_bsdf_desc bd;
-			if (!describeBSDF(bsdf, bd))
-				SLog(EError, "gpupath: BSDF \"%s\" is outside the GPU subset (diffuse, dielectric, plastic, roughconductor, twosided(diffuse))",
+			std::vector<float> table;
+			if (!describeBSDF(bsdf, bd, &table))
+				SLog(EError, "gpupath: BSDF \"%s\" is outside the GPU subset (diffuse, dielectric, plastic, roughplastic, conductor, roughconductor, roughdielectric, null, twosided)",
 					bsdf->getClass()->getName().c_str());
 			bid = mtsb_scene_add_bsdf(out, &bd);
 			if (bid < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+			if (!table.empty()) MTSB_CALL(mtsb_scene_set_bsdf_table(out, bid, table.data(), table.size()));
 			bsdfIds[bsdf] = bid;
 		}
 		int eid = -1;

@@ -14,6 +14,8 @@ import numpy as np
 from . import binding as B
 
 EPSILON = 1e-4
+# the renderer's data/microfacet directory (rough-transmittance tables read by `roughplastic`, src/bsdfs/rtrans.h:95-97)
+MICROFACET_DIR = os.environ.get("MTSB_MICROFACET_DIR")
 SHADOW_EPSILON = 1e-3
 
 
@@ -323,6 +325,22 @@ class SceneDesc:
             dist = dict(beckmann=0, ggx=1)[b.get("distribution", "beckmann")]
             return B.BSDF_ROUGHDIELECTRIC, ([au, av, eta] + list(b.get("specular_reflectance", (1, 1, 1))) + list(b.get("specular_transmittance", (1, 1, 1)))
                                             + [0, 0, dist, 1.0 if b.get("sample_visible", True) else 0.0])
+        if t == "roughplastic":
+            # roughplastic.cpp:199-303; the transmittance slices come from the renderer's data/microfacet tables (MICROFACET_DIR)
+            from . import hostmath as H
+            eta = np.float32(b.get("int_ior", 1.49)) / np.float32(b.get("ext_ior", 1.000277))
+            alpha = b.get("alpha", 0.1)
+            dist = b.get("distribution", "beckmann")
+            dr = list(b.get("diffuse_reflectance", (0.5, 0.5, 0.5)))
+            sr = list(b.get("specular_reflectance", (1, 1, 1)))
+            lum = lambda c: 0.212671 * c[0] + 0.715160 * c[1] + 0.072169 * c[2]
+            ssw = lum(sr) / (lum(dr) + lum(sr))
+            if MICROFACET_DIR is None:
+                raise ValueError("roughplastic needs scenes.MICROFACET_DIR (the renderer's data/microfacet directory)")
+            table, fdr = H.rough_transmittance_slices(H.load_rough_transmittance(os.path.join(MICROFACET_DIR, dist + ".dat")), eta, alpha)
+            b["_table"] = table
+            return B.BSDF_ROUGHPLASTIC | two, [alpha, float(eta)] + dr + sr + [ssw, fdr, 1.0 if b.get("nonlinear") else 0.0,
+                                                                        dict(beckmann=0, ggx=1)[dist], 1.0 if b.get("sample_visible", True) else 0.0]
         raise ValueError("BSDF outside the GPU subset: %s" % t)
 
     def upload(self, ctx, builder=B.BUILDER_LBVH):
@@ -345,6 +363,8 @@ class SceneDesc:
                 bd = dict(type="null")
             tid, params = self._bsdf_params(bd)
             bid = sc.add_bsdf(tid, params)
+            if bd.get("_table") is not None:
+                sc.set_bsdf_table(bid, bd["_table"])
             eid = -1
             if s["emitter"] is not None:
                 eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
@@ -405,6 +425,12 @@ class SceneDesc:
             inner = '<bsdf type="plastic"><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/>%s%s<boolean name="nonlinear" value="%s"/></bsdf>' % (
                 b.get("int_ior", 1.49), b.get("ext_ior", 1.000277), rgb("diffuseReflectance", b.get("diffuse_reflectance", (0.5, 0.5, 0.5))),
                 rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), "true" if b.get("nonlinear") else "false")
+        elif t == "roughplastic":
+            inner = ('<bsdf type="roughplastic"><string name="distribution" value="%s"/><float name="alpha" value="%r"/><float name="intIOR" value="%r"/>'
+                     '<float name="extIOR" value="%r"/>%s%s<boolean name="nonlinear" value="%s"/><boolean name="sampleVisible" value="%s"/></bsdf>') % (
+                b.get("distribution", "beckmann"), b.get("alpha", 0.1), b.get("int_ior", 1.49), b.get("ext_ior", 1.000277),
+                rgb("diffuseReflectance", b.get("diffuse_reflectance", (0.5, 0.5, 0.5))), rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))),
+                "true" if b.get("nonlinear") else "false", "true" if b.get("sample_visible", True) else "false")
         elif t == "roughconductor":
             a = b.get("alpha", 0.1)
             inner = ('<bsdf type="roughconductor"><string name="distribution" value="%s"/><float name="alphaU" value="%r"/>'
@@ -653,6 +679,15 @@ MATERIALS = [
 ]
 
 
+# `roughplastic`: both distributions, nonlinear colour shift, sampling of all normals, two-sided
+ROUGH_PLASTICS = [
+    dict(type="roughplastic", distribution="beckmann", alpha=0.1, diffuse_reflectance=(0.2, 0.3, 0.6)),
+    dict(type="roughplastic", distribution="ggx", alpha=0.3, diffuse_reflectance=(0.7, 0.6, 0.1), nonlinear=True, int_ior=1.9),
+    dict(type="roughplastic", distribution="beckmann", alpha=0.25, sample_visible=False, specular_reflectance=(0.8, 0.9, 1.0)),
+    dict(type="roughplastic", distribution="ggx", alpha=0.05, diffuse_reflectance=(0.5, 0.2, 0.2), twosided=True),
+]
+
+
 def analytic_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0):
     """Analytic `sphere` and `disk` shapes (src/shapes/sphere.cpp, disk.cpp) beside meshes: a glass, a diffuse and a GGX sphere,
     a tilted plastic disk and a flipped diffuse one, on a mesh floor under a mesh area light, a point light and an environment."""
@@ -712,7 +747,7 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
     return sd
 
 
-def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, subdiv=2, env=True, point=True):
+def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, subdiv=2, env=True, point=True, materials=None):
     """Displaced spheres, one per entry of MATERIALS, on a diffuse floor; area light (mesh), point light and a
     constant environment — exercises every BSDF and emitter of the GPU subset."""
     sd = SceneDesc()
@@ -720,7 +755,7 @@ def materials_scene(width=48, height=32, spp=4, max_depth=6, sampler="independen
         sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
     if env:
         sd.add_constant_env((0.3, 0.35, 0.5))
-    for i, m in enumerate(MATERIALS):
+    for i, m in enumerate(MATERIALS if materials is None else materials):
         V, N, F = displaced_sphere(subdiv, seed=20 + i, radius=0.45, center=((i % 4) - 1.5, 0.5, (i // 4) * 1.2 - 0.6))
         c = np.array(((i % 4) - 1.5, 0.5, (i // 4) * 1.2 - 0.6))
         dn = (V - c) / np.linalg.norm(V - c, axis=1, keepdims=True)          # spherical (u,v); required by anisotropic BSDFs

@@ -23,6 +23,7 @@ import oracle as O  # noqa: E402
 
 pkg = g.load_package()
 S = pkg.scenes
+S.MICROFACET_DIR = os.path.join(O.REF_DIR, "data", "microfacet")
 GOLD = os.path.join(ROOT, "tests", "golden")
 
 
@@ -121,6 +122,29 @@ def thinlens_case(td):
     li_case(td, "thinlens", sd)
 
 
+def roughplastic_cases(td):
+    """`roughplastic` (src/bsdfs/roughplastic.cpp + the RoughTransmittance tables of src/bsdfs/rtrans.h): pointwise
+    eval / pdf / sample of scenes.ROUGH_PLASTICS and a per-sample render of the same spheres."""
+    sd = S.materials_scene(materials=S.ROUGH_PLASTICS)
+    xml = sd.to_xml(td, "rp")
+    rng = np.random.default_rng(8)
+    n = 512
+    rows = []
+    for shape in range(len(S.ROUGH_PLASTICS)):
+        inp = np.zeros((n, 12), np.float32)
+        inp[:, 0] = shape
+        inp[:, 1:4] = rand_dirs(rng, n)
+        inp[:, 4:7] = rand_dirs(rng, n, 0.9)
+        inp[:, 7:9] = rng.random((n, 2), dtype=np.float32)
+        inp[:, 9] = rng.random(n, dtype=np.float32)
+        rows.append(inp)
+    inp = np.concatenate(rows)
+    out = run_util("bsdf", xml, inp, 16)
+    np.savez_compressed(os.path.join(GOLD, "bsdf_roughplastic.npz"), inp=inp, out=out)
+    print("bsdf_roughplastic:", inp.shape, "nonzero eval frac", (out[:, 0:3].sum(1) > 0).mean(), "nonzero sample frac", (out[:, 4:7].sum(1) > 0).mean())
+    li_case(td, "roughplastic", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, materials=S.ROUGH_PLASTICS))
+
+
 def fog_cases(td):
     """SimpleVolumetricPathTracer (src/integrators/path/volpath_simple.cpp) over homogeneous media: index-matched and
     dielectric medium boundaries, isotropic and Henyey-Greenstein phase functions; with the camera outside every medium
@@ -131,6 +155,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "roughplastic":     # round 2
+        with tempfile.TemporaryDirectory() as td:
+            roughplastic_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "fog":              # participating media (round 2)
         with tempfile.TemporaryDirectory() as td:
             fog_cases(td)
@@ -138,7 +166,6 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "analytic":         # analytic sphere / disk shapes (round 2)
         with tempfile.TemporaryDirectory() as td:
             li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
-        fog_cases(td)
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "direct_fan":       # only the cases added in round 2
         with tempfile.TemporaryDirectory() as td:
@@ -158,3 +185,4 @@ if __name__ == "__main__":
             direct_fan_case(td, n_em, n_bsdf)
         li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
         fog_cases(td)
+        roughplastic_cases(td)

@@ -15,22 +15,18 @@ def _close(a, b, rtol, atol):
     return np.abs(a - b) <= atol + rtol * np.abs(b)
 
 
-def test_bsdf_pointwise_matches_reference_plugins(pkg, ctx, golden):
-    """mtsb_eval_bsdf vs BSDF::eval / pdf / sample of diffuse, dielectric, plastic (linear, nonlinear), roughconductor
-    (GGX visible, Beckmann visible, anisotropic GGX sampleAll), twosided, conductor and roughdielectric (GGX visible,
-    anisotropic Beckmann sampleAll) — tests/golden/bsdf.npz."""
+def _bsdf_pointwise(pkg, ctx, g, materials):
     S = pkg.scenes
-    g = golden("bsdf.npz")
     inp, ref = g["inp"], g["out"]
-    sd = S.materials_scene()
+    sd = S.materials_scene(materials=materials)
     sc = sd.upload(ctx)
     try:
-        for shape in range(len(S.MATERIALS)):
+        for shape in range(len(materials)):
             rows = inp[:, 0] == shape
             bsdf_id = shape            # materials_scene adds one BSDF per shape in order
             out = sc.eval_bsdf(bsdf_id, inp[rows, 1:4], inp[rows, 4:7], inp[rows, 7:9], s3=inp[rows, 9])
             r = ref[rows]
-            name = S.MATERIALS[shape]
+            name = materials[shape]
             rtol = 2e-3 if name.get("distribution") == "beckmann" else 5e-4      # reference uses math::fastexp / erf fits
             ok_eval = _close(out[:, 0:4], r[:, 0:4], rtol, 1e-6).all(axis=1)
             assert ok_eval.mean() >= 0.995, (name, "eval/pdf", ok_eval.mean())
@@ -46,6 +42,21 @@ def test_bsdf_pointwise_matches_reference_plugins(pkg, ctx, golden):
                 assert (out[zero, 4:7].sum(axis=1) == 0).mean() >= 0.99, (name, "failed samples")
     finally:
         sc.close()
+
+
+def test_bsdf_pointwise_matches_reference_plugins(pkg, ctx, golden):
+    """mtsb_eval_bsdf vs BSDF::eval / pdf / sample of diffuse, dielectric, plastic (linear, nonlinear), roughconductor
+    (GGX visible, Beckmann visible, anisotropic GGX sampleAll), twosided, conductor and roughdielectric (GGX visible,
+    anisotropic Beckmann sampleAll) — tests/golden/bsdf.npz."""
+    _bsdf_pointwise(pkg, ctx, golden("bsdf.npz"), pkg.scenes.MATERIALS)
+
+
+def test_roughplastic_pointwise_matches_reference_plugin(pkg, ctx, golden):
+    """`roughplastic` (src/bsdfs/roughplastic.cpp:330-495): Beckmann / GGX, nonlinear, sampleVisible off, two-sided; the
+    rough-transmittance slices are rebuilt by hostmath.rough_transmittance_slices from the reference's data/microfacet tables
+    (rtrans.h:277-370) — tests/golden/bsdf_roughplastic.npz."""
+    pkg.scenes.MICROFACET_DIR = os.path.join(O.REF_DIR, "data", "microfacet")
+    _bsdf_pointwise(pkg, ctx, golden("bsdf_roughplastic.npz"), pkg.scenes.ROUGH_PLASTICS)
 
 
 def test_emitter_sampling_matches_reference(pkg, ctx, golden):
@@ -97,7 +108,7 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
-                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic"])
+                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -123,6 +134,9 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     elif name == "analytic":
         # analytic sphere / disk shapes (src/shapes/sphere.cpp, disk.cpp) through the path tracer
         sd = S.analytic_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+    elif name == "roughplastic":
+        S.MICROFACET_DIR = os.path.join(O.REF_DIR, "data", "microfacet")
+        sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, materials=S.ROUGH_PLASTICS)
     elif name == "strict":
         # strictNormals + hideEmitters (path.cpp:136-165,196-199,218-222); parameters of make_golden_render.strict_case
         sd = S.materials_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)

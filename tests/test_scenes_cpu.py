@@ -61,3 +61,32 @@ def test_thinlens_sensor_description(pkg, tmp_path):
     assert abs(cam.aperture_radius - 0.05) < 1e-7 and abs(cam.focus_distance - 3.5) < 1e-7
     xml = open(sd.to_xml(str(tmp_path), "tl")).read()
     assert '<sensor type="thinlens">' in xml and 'name="apertureRadius" value="0.05"' in xml and 'name="focusDistance" value="3.5"' in xml
+
+
+def test_rough_transmittance_slices_of_roughplastic(pkg):
+    """hostmath.rough_transmittance_slices restates RoughTransmittance::setEta / setAlpha / evalDiffuse (src/bsdfs/rtrans.h:
+    243-370) on the reference's own data/microfacet tables: smooth limit and packing into the 15-float ABI record."""
+    import importlib
+    import oracle as O
+    H = importlib.import_module(pkg.__name__ + ".hostmath")
+    S, B = pkg.scenes, pkg.binding
+    d = os.path.join(O.REF_DIR, "data", "microfacet")
+    if not os.path.exists(os.path.join(d, "beckmann.dat")):
+        import pytest
+        pytest.fail("oracle/_ref/data/microfacet is missing: run __graft_entry__.build()")
+    eta = 1.49 / 1.000277
+    for dist in ("beckmann", "ggx"):
+        t = H.load_rough_transmittance(os.path.join(d, dist + ".dat"))
+        assert t["trans"].shape == (100, 50, 100) and t["diff"].shape == (100, 50)
+        ext, fdr = H.rough_transmittance_slices(t, eta, 0.01)
+        assert ext.shape == (100,) and ext.dtype == np.float32
+        # near-smooth interface: the transmittance at normal incidence is 1 - F0, the internal diffuse reflectance that of `plastic`
+        f0 = ((eta - 1) / (eta + 1)) ** 2
+        assert abs(ext[-1] - (1 - f0)) < 2e-3
+        assert abs(fdr - H.fresnel_diffuse_reflectance(1 / eta)) < 0.01
+    S.MICROFACET_DIR = d
+    for m in S.ROUGH_PLASTICS:
+        m = dict(m)
+        tid, params = S.SceneDesc._bsdf_params(m)
+        assert (tid & 0xff) == B.BSDF_ROUGHPLASTIC and len(params) == 13 and np.isfinite(params).all()
+        assert m["_table"].shape == (100,) and 'type="roughplastic"' in S.SceneDesc._bsdf_xml(m)
