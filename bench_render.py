@@ -194,7 +194,11 @@ def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
         return {"unavailable": "oracle/_ref or the plugin overlay is not built"}
     threads = threads or (os.cpu_count() or 1)
 
-    def cli(xml, out, classic, use_overlay, defines=None, ngpu=1):
+    preload_lib = os.path.join(overlay, "lib", "libmtsb_overlay.so")
+
+    def cli(xml, out, classic, use_overlay, defines=None, ngpu=1, preload=False):
+        # preload: LD_PRELOAD of the per-ray overlay, whose ShapeKDTree::build() skips the CPU kd-tree
+        env = dict(os.environ, LD_PRELOAD=preload_lib) if preload else None
         cmd = [os.path.join(O.REF_DIR, "mitsuba"), "-p", str(threads)]
         if classic:
             cmd.append("-C")
@@ -204,11 +208,13 @@ def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
             cmd += ["-D", "%s=%s" % (k, v)]
         cmd += ["-o", out, xml]
         t0 = time.perf_counter()
-        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1800)
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, errors="replace", timeout=1800, env=env)
         wall = time.perf_counter() - t0
         if r.returncode != 0:
             return {"error": r.stdout[-600:]}
         res = {"process_wall_s": wall}
+        kd = re.findall(r"Finished -- took (\d+) ms", r.stdout)
+        res["cpu_kd_build_ms"] = max(int(x) for x in kd) if kd else (0 if "the CPU kd-tree is not built" in r.stdout else None)
         m = re.search(r"Render time: ([0-9.]+)(ms|s|m)", r.stdout)
         if m:
             res["render_time_s"] = float(m.group(1)) * {"ms": 1e-3, "s": 1.0, "m": 60.0}[m.group(2)]
@@ -238,6 +244,8 @@ def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
             out["config3_scene_files_s"] = time.perf_counter() - t0
             out["config3_gpu_classic"] = cli(x3, os.path.join(td, "c3c.pfm"), True, True)
             out["config3_gpu_responsive"] = cli(x3, os.path.join(td, "c3r.pfm"), False, True)
+            if os.path.exists(preload_lib):
+                out["config3_gpu_classic_no_cpu_kdtree"] = cli(x3, os.path.join(td, "c3p.pfm"), True, True, preload=True)
             for g in gpus:
                 if g > 1:
                     xg = os.path.join(td, "c3_%dgpu.xml" % g)

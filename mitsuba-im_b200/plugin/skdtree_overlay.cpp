@@ -17,6 +17,8 @@
 //   wake up, turn (t, u, v, primitive) into
 //   an Intersection with the reference's OWN fillIntersectionRecord<true> (skdtree.h:343-428)
 //
+// The fourth interposed member is ShapeKDTree::build(): the CPU SAH build is skipped (a 10 M-triangle scene
+// loads without minutes of kd-tree construction), see skdtree_overlay_impl.h.
 // There is no flush timer: while one batch is on the device the next one accumulates, so the batch size adapts to the
 // number of threads that are blocked.  A per-ray synchronous interface cannot feed a GPU from 16 threads — run the
 // renderer with hundreds of threads (`mitsuba -p 512`: blocked threads cost nothing) and the batches grow with them.
@@ -26,6 +28,9 @@
 #include <mitsuba/render/trimesh.h>
 #include <mitsuba/core/statistics.h>
 #include <mitsuba/core/properties.h>
+#include <mitsuba/core/timer.h>
+#include <dlfcn.h>
+#include <stdlib.h>
 #include "../../include/mtsb200.h"
 #include <atomic>
 #include <algorithm>

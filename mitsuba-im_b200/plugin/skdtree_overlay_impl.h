@@ -97,7 +97,55 @@ struct OverlayReport {      // batch statistics at process exit
 
 } // namespace
 
-// ---- the three interposed members -------------------------------------------------------------------------------------
+// ---- the interposed members ----------------------------------------------------------------------------------------------
+
+/// src/librender/skdtree.cpp:68-110.  With the three query overloads served by the device, nothing reads the SAH kd-tree or
+/// the TriAccel array any more, so the CPU build — seconds at 1 M triangles, minutes at 10 M (gkdtree.h:958-1263) — is
+/// left out.  What the rest of the renderer still needs from build() is kept: the prefix sums of m_shapeMap (global
+/// primitive index -> shape) and the bounding boxes (Scene::initialize takes getAABB(), scene.cpp:353-355; the sensor's
+/// clip planes and the environment emitter's sphere derive from it): the tight box of all primitives and its enlargement
+/// exactly as buildInternal computes them (gkdtree.h:997-1002, 1213-1220).  The node array becomes the single empty leaf
+/// buildInternal makes for a scene without geometry (:972-977), so isBuilt() holds and the destructor frees it; a CPU-side
+/// packet query (rayIntersectPacket), which is not interposed, finds nothing in it.  MTSB_OVERLAY_KDBUILD=1 keeps the
+/// reference's build (it then runs from libmitsuba-render.so's own copy of this symbol via dlsym(RTLD_NEXT)).
+void ShapeKDTree::build() {
+	const char *keep = getenv("MTSB_OVERLAY_KDBUILD");
+	if (keep && atoi(keep) != 0) {
+		typedef void (ShapeKDTree::*BuildFn)();
+		void *sym = dlsym(RTLD_NEXT, "_ZN7mitsuba11ShapeKDTree5buildEv");
+		if (!sym) SLog(EError, "mtsb overlay: the reference's ShapeKDTree::build is not reachable");
+		union { void *p; BuildFn f; } u; memset(&u, 0, sizeof(u)); u.p = sym;
+		(this->*u.f)();
+		return;
+	}
+	ref<Timer> timer = new Timer();
+	for (size_t i = 1; i < m_shapeMap.size(); ++i)
+		m_shapeMap[i] += m_shapeMap[i - 1];
+	AABB aabb;
+	aabb.reset();
+	for (size_t i = 0; i < m_shapes.size(); ++i) {
+		const Shape *shape = m_shapes[i];
+		if (m_triangleFlag[i]) {
+			const TriMesh *mesh = static_cast<const TriMesh *>(shape);
+			const Triangle *tris = mesh->getTriangles();
+			const Point *pos = mesh->getVertexPositions();
+			for (size_t j = 0; j < mesh->getTriangleCount(); ++j)        // per-triangle boxes: unreferenced vertices do not count
+				for (int k = 0; k < 3; ++k) aabb.expandBy(pos[tris[j].idx[k]]);
+		} else {
+			aabb.expandBy(shape->getAABB());
+		}
+	}
+	m_tightAABB = aabb;
+	const Float eps = MTS_KD_AABB_EPSILON;
+	aabb.min -= (aabb.max - aabb.min) * eps + Vector(eps);
+	aabb.max += (aabb.max - aabb.min) * eps + Vector(eps);
+	m_aabb = aabb;
+	m_nodes = static_cast<KDNode *>(allocAligned(sizeof(KDNode) * 2)) + 1;
+	m_nodes[0].initLeafNode(0, 0);
+	SLog(EInfo, "mtsb overlay: ShapeKDTree::build — bounds of %u primitives in %i ms, the CPU kd-tree is not built (queries run on the GPU)",
+		(unsigned) getPrimitiveCount(), timer->getMilliseconds());
+}
+
 
 /// src/librender/skdtree.cpp:112-142.  Scene-box clip, floored adaptive epsilon and traversal happen on the device
 /// (csrc/trace.cuh: clip_ray + trace_persistent); the record is filled by the reference's own inline code.
