@@ -159,7 +159,9 @@ typedef struct mtsb_film_desc {
 
 /* MTSB_INTEGRATOR_VOLPATH_SIMPLE: SimpleVolumetricPathTracer (src/integrators/path/volpath_simple.cpp:92-300) — path tracing
  * with homogeneous participating media, emitter sampling attenuated through index-matched boundaries, no MIS. */
-enum { MTSB_INTEGRATOR_PATH = 0, MTSB_INTEGRATOR_DIRECT = 1, MTSB_INTEGRATOR_VOLPATH_SIMPLE = 2 };
+/* MTSB_INTEGRATOR_VOLPATH: VolumetricPathTracer (src/integrators/path/volpath.cpp:84-425) — the same with multiple importance
+ * sampling of emitter and phase-function / BSDF samples, emitters looked up through index-matched boundaries. */
+enum { MTSB_INTEGRATOR_PATH = 0, MTSB_INTEGRATOR_DIRECT = 1, MTSB_INTEGRATOR_VOLPATH_SIMPLE = 2, MTSB_INTEGRATOR_VOLPATH = 3 };
 typedef struct mtsb_integrator_desc {
 	int32_t type;
 	int32_t max_depth;           /* MonteCarloIntegrator maxDepth (-1 = unbounded)  (src/librender/integrator.cpp:191-226) */

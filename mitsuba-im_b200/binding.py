@@ -25,7 +25,7 @@ BSDF_PASSTHROUGH = 7
 BSDF_ROUGHPLASTIC = 8
 BSDF_TWOSIDED_FLAG = 0x100
 EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
-INTEGRATOR_PATH, INTEGRATOR_DIRECT, INTEGRATOR_VOLPATH_SIMPLE = 0, 1, 2
+INTEGRATOR_PATH, INTEGRATOR_DIRECT, INTEGRATOR_VOLPATH_SIMPLE, INTEGRATOR_VOLPATH = 0, 1, 2, 3
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 
 ray_dtype = np.dtype([("o", "<f4", 3), ("mint", "<f4"), ("d", "<f4", 3), ("maxt", "<f4")])

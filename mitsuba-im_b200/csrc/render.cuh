@@ -17,6 +17,7 @@ struct PathState {
 	float4 *rayO, *rayD, *hit, *thr, *L, *prev, *misc;
 	uint4  *rng;
 	float4 *shO, *shD, *shL;
+	float4 *shX;                   // fourth word of the connection queue (volpath only, render_vol.cuh), else NULL
 	uint32_t *queueA, *queueB;     // live path slots (ping-pong); entries may carry QUEUE_RESUME (render.cu)
 	uint2  *susp;                  // suspension records of the extend stage, MTSB_SUSP_WORDS per path slot (trace.cuh: Trav::save)
 	uint32_t *counters;            // 16 words, see the CTR_* enum below

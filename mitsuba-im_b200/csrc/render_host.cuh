@@ -12,7 +12,8 @@ static inline bool fan_mode(const mtsb_render *r) {
 }
 
 // SimpleVolumetricPathTracer (render_vol.cuh): its own shade / connect kernels, no tail kernel, no ray suspension
-static inline bool vol_mode(const mtsb_render *r) { return r->integ.type == MTSB_INTEGRATOR_VOLPATH_SIMPLE; }
+static inline bool vol_mode(const mtsb_render *r) { return r->integ.type == MTSB_INTEGRATOR_VOLPATH_SIMPLE || r->integ.type == MTSB_INTEGRATOR_VOLPATH; }
+static inline bool volmis_mode(const mtsb_render *r) { return r->integ.type == MTSB_INTEGRATOR_VOLPATH; }
 
 // camera paths per chunk: the fan-out of `direct` shares the same budget of rays in flight
 static inline size_t max_paths(const mtsb_render *r) {
@@ -34,7 +35,7 @@ static int ensure_capacity(mtsb_render *r, size_t paths) {
 	// the sensor ray travels through the same queue as its emitter sample, render_vol.cuh)
 	const size_t M = fan_mode(r) ? (size_t) r->integ.bsdfSamples : 0, N = fan_mode(r) ? (size_t) std::max(1, r->integ.emitterSamples) : (vol_mode(r) ? 2 : 1);
 	const size_t wide = cap * (1 + M);            // camera slots + secondary slots (one per BSDF sample)
-	MTSB_CHECK(r->bufF4.alloc(wide * 6 + cap + cap * N * 3));
+	MTSB_CHECK(r->bufF4.alloc(wide * 6 + cap + cap * N * (volmis_mode(r) ? 4 : 3)));
 	MTSB_CHECK(r->bufRng.alloc(cap));
 	MTSB_CHECK(r->bufQueue.alloc(cap + std::max(cap, cap * M)));
 	if (suspend_after(r)) MTSB_CHECK(r->bufSusp.alloc(cap * MTSB_SUSP_WORDS));
@@ -45,6 +46,7 @@ static int ensure_capacity(mtsb_render *r, size_t paths) {
 	f += 6 * wide;
 	ps.L = f; f += cap;
 	ps.shO = f; ps.shD = f + cap * N; ps.shL = f + 2 * cap * N;
+	ps.shX = volmis_mode(r) ? f + 3 * cap * N : nullptr;
 	ps.rng = r->bufRng.ptr;
 	ps.queueA = r->bufQueue.ptr; ps.queueB = r->bufQueue.ptr + cap;
 	r->capacity = cap;
@@ -112,7 +114,7 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	void *aShade[] = { &S, &ps, &integ, &seed };
 	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aExtend, scene));
 	if (vol_mode(r)) {
-		MTSB_CUDA(add_kernel(body, &n2, n1, (void *) volshade_kernel<0>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+		MTSB_CUDA(add_kernel(body, &n2, n1, volmis_mode(r) ? (void *) volshade_kernel<1> : (void *) volshade_kernel<0>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
 		MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_vol_kernel<true> : (void *) connect_vol_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	} else {
 		MTSB_CUDA(add_kernel(body, &n2, n1, scene->lean ? (void *) shade_kernel<true> : (void *) shade_kernel<false>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
@@ -195,7 +197,8 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
 			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
 			if (vol_mode(r)) {
-				volshade_kernel<0><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+				if (volmis_mode(r)) volshade_kernel<1><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
+				else volshade_kernel<0><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
 				MTSB_CHECK(launch_trav(scene, scene->curved ? connect_vol_kernel<true> : connect_vol_kernel<false>, sh.tailGrid, st, S, ps));
 			} else {
 				if (scene->lean) shade_kernel<true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
@@ -239,7 +242,8 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: NULL argument or scene not committed");
 	if (film->width <= 0 || film->height <= 0 || (film->channels != 4 && film->channels != 5) || film->border < 0 || film->filter_radius <= 0)
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: bad film description (%dx%d, %d channels)", film->width, film->height, film->channels);
-	if (integrator->type != MTSB_INTEGRATOR_PATH && integrator->type != MTSB_INTEGRATOR_DIRECT && integrator->type != MTSB_INTEGRATOR_VOLPATH_SIMPLE)
+	if (integrator->type != MTSB_INTEGRATOR_PATH && integrator->type != MTSB_INTEGRATOR_DIRECT && integrator->type != MTSB_INTEGRATOR_VOLPATH_SIMPLE &&
+			integrator->type != MTSB_INTEGRATOR_VOLPATH)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_create: integrator type %d is outside the GPU subset", integrator->type);
 	if (integrator->type == MTSB_INTEGRATOR_DIRECT && (integrator->emitter_samples < 0 || integrator->bsdf_samples < 0 ||
 			integrator->emitter_samples + integrator->bsdf_samples <= 0 || integrator->emitter_samples > 4096 || integrator->bsdf_samples > 4096))

@@ -16,13 +16,19 @@ namespace mtsb {
 // prev.y of a path slot (bit mask)
 enum { VF_EMITTED = 1,        // rRec.type & EEmittedRadiance
        VF_REST = 2,           // rRec.type & ERadianceNoEmission (direct/indirect surface and medium radiance travel together)
-       VF_NULLCHAIN = 4, VF_SCATTERED = 8 };
+       VF_NULLCHAIN = 4, VF_SCATTERED = 8,
+       // `volpath` only: what the previous iteration left for this one (volmis_path)
+       VF_LOOK = 16,          // its phase / BSDF sample looks for an emitter (MIS-weighted): prev.z = sample pdf, {prev.w, misc.zw} = refN
+       VF_DELTA = 32,         // ... and was drawn from a delta lobe (emitter pdf counts as 0)
+       VF_CONTINUE = 64 };    // it ended with `continue` through an index-matched boundary: no Russian roulette, `scattered` unchanged
 
 // entries of the connection queue (shO.w bits): {p1.xyz, bits} {p2.xyz, -} {contribution.rgb, path slot}
 #define VQ_P1_SURFACE 1u
 #define VQ_P2_SURFACE 2u
 #define VQ_ALPHA      4u       // opacity query of RadianceQueryRecord::rayIntersect (records.inl:117-145): L.w = 1 - average(T)
-#define VQ_MEDIUM(b)  ((int) (((b) >> 3) & 0x1fffu) - 1)
+#define VQ_LOOK       0x8000u  // rayIntersectAndLookForEmitter of `volpath` (volpath.cpp:369-425) beyond its first hit: {o, bits} {d, sample pdf}
+                               // {throughput x transmittance so far, slot} {refN, -}; bit 31 of the pdf's sign = the sample was a delta lobe
+#define VQ_MEDIUM(b)  ((int) (((b) >> 3) & 0xfffu) - 1)
 #define VQ_MAXI(b)    ((b) >> 16)                  // 0xffff: no bound
 #define VQ_PACK(flags, medium, maxi) ((uint32_t) (flags) | ((uint32_t) ((medium) + 1) << 3) | ((uint32_t) (maxi) << 16))
 
@@ -112,13 +118,22 @@ __device__ __forceinline__ int target_medium(const ShapeRec &sh, const V3 &ng, c
 	return dot(d, ng) > 0 ? sh.exterior : sh.interior;
 }
 
-struct VolOut { bool alive; int nReq; float4 qO[2], qD[2], qL[2]; };
+struct VolOut { bool alive; int nReq; float4 qO[2], qD[2], qL[2], qX[2]; };
 
 __device__ __forceinline__ void vol_request(VolOut &out, const V3 &p1, const V3 &p2, uint32_t bits, const V3 &c, uint32_t slot) {
 	const int k = out.nReq++;
 	out.qO[k] = make_float4(p1.x, p1.y, p1.z, __uint_as_float(bits));
 	out.qD[k] = make_float4(p2.x, p2.y, p2.z, 0.0f);
 	out.qL[k] = make_float4(c.x, c.y, c.z, __uint_as_float(slot));
+	out.qX[k] = make_float4(0, 0, 0, 0);
+}
+__device__ __forceinline__ void vol_look_request(VolOut &out, const V3 &o, const V3 &d, uint32_t bits, const V3 &c, uint32_t slot,
+		float samplePdf, bool delta, const V3 &refN) {
+	const int k = out.nReq++;
+	out.qO[k] = make_float4(o.x, o.y, o.z, __uint_as_float(bits | VQ_LOOK));
+	out.qD[k] = make_float4(d.x, d.y, d.z, delta ? -samplePdf : samplePdf);
+	out.qL[k] = make_float4(c.x, c.y, c.z, __uint_as_float(slot));
+	out.qX[k] = make_float4(refN.x, refN.y, refN.z, 0.0f);
 }
 
 __device__ __forceinline__ uint32_t vol_max_interactions(const IntegratorDev &integ, uint32_t depth) {
@@ -278,10 +293,226 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 	}
 }
 
+// One iteration of VolumetricPathTracer::Li (src/integrators/path/volpath.cpp:84-343) — the variant WITH multiple importance
+// sampling.  Its phase / BSDF sample is followed by rayIntersectAndLookForEmitter (:369-425), which (1) finds the first
+// intersection, the one the next iteration starts from, and (2) keeps walking through index-matched boundaries for an
+// emitter whose radiance is weighted against the emitter-sampling density.  Step (1) is the wavefront's `extend`; this
+// function therefore begins with the TAIL of the previous iteration — the emitter found at (or behind) the first hit, then
+// the Russian roulette that closes that iteration — as shade_path does for `path`.  Behind an index-matched first hit the walk
+// goes on in connect_vol_kernel (a VQ_LOOK queue entry).
+__device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
+		uint32_t slot, VolOut &out) {
+	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
+	float4 thr4 = ps.thr[slot];
+	const float4 prev = ps.prev[slot];
+	const uint4 rg = ps.rng[slot];
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed;
+	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
+	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);
+	float eta = thr4.w;
+	uint32_t depth = PATH_DEPTH(rg.w);
+	const bool first = !(PATH_FLAGS(rg.w) & PF_FROM_BSDF);
+	int medium = first ? integ.cameraMedium : __float_as_int(prev.x);
+	uint32_t vf = first ? (uint32_t) (VF_EMITTED | VF_REST) : __float_as_uint(prev.y);
+	const uint32_t hitSlot = __float_as_uint(h.w);
+	const bool valid = hitSlot != INVALID_SLOT;
+	out.alive = true; out.nReq = 0;
+
+	Surf sf;
+	ShapeRec sh;
+	bool transition = false;
+	if (valid) { fill_surface(S, hitSlot, h.x, h.y, h.z, o, d, sf); sh = S.shapes[sf.shape]; transition = sh.interior >= 0 || sh.exterior >= 0; }
+
+	float alpha = 0.0f;
+	if (first) {
+		const V3 far = o + d * S.sceneDiameter;                    // opacity, records.inl:117-145 (as in volshade_path)
+		if (valid) {
+			if (!transition) alpha = 1.0f;
+			else vol_request(out, sf.p, far, VQ_PACK(VQ_P1_SURFACE | VQ_ALPHA, target_medium(sh, sf.ng, d), 0xffffu), v3(0.0f), slot);
+		} else if (medium >= 0) vol_request(out, o, far, VQ_PACK(VQ_ALPHA, medium, 0xffffu), v3(0.0f), slot);
+	} else {
+		// ---- tail of the previous iteration
+		if (vf & VF_LOOK) {
+			// rayIntersectAndLookForEmitter with maxInteractions = m_maxDepth - rRec.depth - 1 (depth not yet incremented)
+			const float samplePdf = prev.z;
+			const bool delta = (vf & VF_DELTA) != 0;
+			const float4 misc = ps.misc[slot];
+			const V3 refN = v3(prev.w, misc.z, misc.w);
+			const uint32_t maxI = vol_max_interactions(integ, depth);
+			const V3 T0 = medium >= 0 ? medium_transmittance(S.media[medium], valid ? h.x : INFINITY) : v3(1.0f);
+			if (valid) {
+				const bool isNull = (bsdf_type(S.bsdfs[sh.bsdf]) & B_NULL) != 0, isEmitter = sh.emitter >= 0;
+				if (maxI == 0 || !isNull || isEmitter) {
+					if (isEmitter) {                                  // dRec.setQuery(ray, its); value = transmittance * Le
+						const V3 value = T0 * area_emitter_eval(S, sh.emitter, sf.ns, -d);
+						if (!is_zero(value)) {
+							const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, sh.emitter, refN, d, h.x, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, sh.emitter);
+							Li += thr * value * mi_weight(samplePdf, emitterPdf);
+						}
+					}
+				} else if (!is_zero(T0)) {
+					// an index-matched boundary: the walk goes on from ray(its.t) in the medium behind it
+					const int med2 = transition ? target_medium(sh, sf.ng, d) : medium;
+					vol_look_request(out, o + d * h.x, d, VQ_PACK(0u, med2, maxI), thr * T0, slot, samplePdf, delta, refN);
+				}
+			} else if (S.envEmitter >= 0) {
+				const EmitterRec &env = S.emitters[S.envEmitter];
+				float nearT, farT;                                  // fillDirectSamplingRecord (constant.cpp:238-256)
+				if (sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
+					const V3 value = T0 * env.radiance;
+					if (!is_zero(value)) {
+						const V3 n = normalize(env.sphereCenter - (o + d * farT));
+						const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
+						Li += thr * value * mi_weight(samplePdf, emitterPdf);
+					}
+				}
+			}
+		}
+		if (!(vf & VF_CONTINUE)) {
+			if (depth++ >= (uint32_t) integ.rrDepth) {                   // :324-336
+				const float q = fminf(vmax(thr) * eta * eta, 0.95f);
+				if (next1D(rs) >= q) out.alive = false;
+				else thr /= q;
+			}
+			vf |= VF_SCATTERED;                                          // :338
+		}
+		vf &= ~(uint32_t) (VF_LOOK | VF_DELTA | VF_CONTINUE);
+		if (out.alive && !((int) depth <= integ.maxDepth || integ.maxDepth < 0)) out.alive = false;     // while condition (:100)
+	}
+
+	float samplePdf = 0.0f;
+	V3 sampleRefN = v3(0.0f);
+	if (out.alive) {
+		MediumSample ms;
+		bool inMedium = false;
+		if (medium >= 0) inMedium = medium_sample_distance(S.media[medium], o, d, h.x, rs, ms);
+		if (inMedium) {
+			// ---- medium interaction (:104-168)
+			const MediumRec &m = S.media[medium];
+			if ((int) depth >= integ.maxDepth && integ.maxDepth != -1) out.alive = false;
+			else {
+				thr *= m.sigmaS * ms.transmittance / ms.pdfSuccess;
+				if (vf & VF_REST) {
+					float sx, sy; next2D(rs, sx, sy);
+					if (S.emitterCount > 0) {
+						DirectSample ds;
+						const V3 value = scene_sample_emitter_direct(S, ms.p, v3(0.0f), sx, sy, ds);
+						if (ds.pdf != 0 && !is_zero(value)) {
+							const float phaseVal = phase_eval(m, -d, ds.d);
+							if (phaseVal != 0) {
+								const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
+								const float phasePdf = (onSurface && ds.measure == M_SOLID_ANGLE) ? phaseVal : 0.0f;   // PhaseFunction::pdf = eval
+								vol_request(out, ms.p, ds.p, VQ_PACK(onSurface ? VQ_P2_SURFACE : 0u, medium, vol_max_interactions(integ, depth)),
+									thr * value * (phaseVal * mi_weight(ds.pdf, phasePdf)), slot);
+							}
+						}
+					}
+				}
+				float sx, sy; next2D(rs, sx, sy);
+				const V3 wo = phase_sample(m, -d, sx, sy);
+				samplePdf = phase_eval(m, -d, wo);                          // sample(pRec, pdf, sampler): pdf = eval(pRec)
+				ps.rayO[slot] = make_float4(ms.p.x, ms.p.y, ms.p.z, 0.0f);
+				ps.rayD[slot] = make_float4(wo.x, wo.y, wo.z, INFINITY);
+				if (!(vf & VF_REST)) out.alive = false;                    // :159-167: nothing is gathered without the medium radiance bits
+				else vf = (vf & ~(uint32_t) VF_EMITTED) | VF_LOOK;         // rRec.type = ERadianceNoEmission
+			}
+		} else {
+			// ---- surface interaction (:169-322)
+			if (medium >= 0) thr *= ms.transmittance / ms.pdfFailure;
+			if (!valid) {
+				if ((vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)) && S.envEmitter >= 0) {
+					V3 value = thr * S.emitters[S.envEmitter].radiance;
+					if (medium >= 0) value *= medium_transmittance(S.media[medium], INFINITY);
+					Li += value;
+				}
+				out.alive = false;
+			} else {
+				if (sh.emitter >= 0 && (vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)))
+					Li += thr * area_emitter_eval(S, sh.emitter, sf.ns, -d);
+				if ((int) depth >= integ.maxDepth && integ.maxDepth != -1) out.alive = false;      // :199-200
+				const V3 wi = to_local(sf, -d);
+				if (out.alive && integ.strictNormals && -dot(sf.ng, d) * wi.z < 0) out.alive = false;
+				if (out.alive) {
+					const BsdfRec bsdf = S.bsdfs[sh.bsdf];
+					const uint32_t btype = bsdf_type(bsdf);
+					const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);
+					// ---- emitter sampling with MIS (:212-247)
+					if ((vf & VF_REST) && (btype & B_SMOOTH)) {
+						float sx, sy; next2D(rs, sx, sy);
+						if (S.emitterCount > 0) {
+							DirectSample ds;
+							const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
+							if (ds.pdf != 0 && !is_zero(value)) {
+								const V3 wo = to_local(sf, ds.d);
+								const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
+								if (!is_zero(bsdfVal) && (!integ.strictNormals || dot(sf.ng, ds.d) * wo.z > 0)) {
+									const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
+									const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf(bsdf, wi, wo) : 0.0f;
+									const int med = transition ? target_medium(sh, sf.ng, ds.d) : medium;
+									vol_request(out, sf.p, ds.p, VQ_PACK(VQ_P1_SURFACE | (onSurface ? VQ_P2_SURFACE : 0u), med, vol_max_interactions(integ, depth)),
+										thr * value * bsdfVal * mi_weight(ds.pdf, bp), slot);
+								}
+							}
+						}
+					}
+					// ---- BSDF sampling (:254-322)
+					float sx, sy; next2D(rs, sx, sy);
+					const float sz = bsdf_uses_sampler(bsdf) ? next1D(rs) : 0.0f;
+					BsdfSample bs;
+					const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, sz, bs);
+					if (is_zero(bsdfWeight)) out.alive = false;
+					else {
+						const V3 wo = to_world(sf, bs.wo);
+						if (dot(sf.ng, wo) * bs.wo.z <= 0 && integ.strictNormals) out.alive = false;
+						else {
+							ps.rayO[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, MTS_EPSILON);
+							ps.rayD[slot] = make_float4(wo.x, wo.y, wo.z, INFINITY);
+							thr *= bsdfWeight; eta *= bs.eta;
+							if (transition) medium = target_medium(sh, sf.ng, wo);
+							if (bs.type == B_NULL) {
+								// an index-matched transition (:283-292): next iteration at once — no emitter look-up, no roulette
+								if (!(vf & VF_REST)) out.alive = false;
+								else {
+									vf = (vf & ~(uint32_t) (VF_EMITTED | VF_REST)) | ((vf & VF_SCATTERED) ? (uint32_t) VF_REST : (uint32_t) (VF_EMITTED | VF_REST)) | VF_CONTINUE;
+									++depth;
+									if (!((int) depth <= integ.maxDepth || integ.maxDepth < 0)) out.alive = false;
+								}
+							} else {
+								if (!(vf & VF_REST)) out.alive = false;        // :299-310: neither the look-up nor the recursion is wanted
+								else {
+									vf = (vf & ~(uint32_t) VF_EMITTED) | VF_LOOK | ((bs.type & B_DELTA) ? (uint32_t) VF_DELTA : 0u);
+									samplePdf = bs.pdf; sampleRefN = refN;
+								}
+							}
+						}
+					}
+				}
+			}
+		}
+	}
+
+	if (first) ps.L[slot] = make_float4(Li.x, Li.y, Li.z, alpha);
+	else if (!is_zero(Li)) {
+		float *L = (float *) (ps.L + slot);          // component-wise: a look-up of this path may be finishing in connect_vol_kernel
+		L[0] += Li.x; L[1] += Li.y; L[2] += Li.z;
+	}
+	ps.rng[slot] = make_uint4(rg.x, rg.y, rg.z, PATH_PACK(rs.dim, PF_FROM_BSDF, depth));
+	if (out.alive) {
+		ps.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
+		ps.prev[slot] = make_float4(__int_as_float(medium), __uint_as_float(vf), samplePdf, sampleRefN.x);
+		if (vf & VF_LOOK) {
+			float4 misc = ps.misc[slot];
+			misc.z = sampleRefN.y; misc.w = sampleRefN.z;
+			ps.misc[slot] = misc;
+		}
+	}
+}
+
 #ifndef MTSB_VOLSHADE_MIN_BLOCKS
 #define MTSB_VOLSHADE_MIN_BLOCKS 1
 #endif
-template <int DUMMY = 0>
+// MIS = 0: volpath_simple (volshade_path), 1: volpath (volmis_path)
+template <int MIS = 0>
 __global__ void __launch_bounds__(RENDER_BLOCK, MTSB_VOLSHADE_MIN_BLOCKS)
 volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
@@ -293,12 +524,14 @@ volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 		const uint32_t slot = QUEUE_SLOT(queueIn[i]);
 		if (__float_as_uint(ps.hit[slot].w) == SUSPENDED_SLOT) { queueOut[warp_append(countOut)] = slot | QUEUE_RESUME; continue; }
 		VolOut vo;
-		volshade_path(S, ps, integ, seed, slot, vo);
+		if (MIS) volmis_path(S, ps, integ, seed, slot, vo);
+		else volshade_path(S, ps, integ, seed, slot, vo);
 		if (vo.alive) queueOut[warp_append(countOut)] = slot;
 		for (int k = 0; k < 2; ++k)
 			if (k < vo.nReq) {
 				const uint32_t q = warp_append(countShadow);
 				ps.shO[q] = vo.qO[k]; ps.shD[q] = vo.qD[k]; ps.shL[q] = vo.qL[k];
+				if (MIS) ps.shX[q] = vo.qX[k];
 			}
 	}
 }
@@ -322,6 +555,8 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 	float remaining = 0, lengthFactor = 1, mint = 0;
 	int medium = -1;
 	uint32_t interactions = 0;
+	float samplePdf = 0;             // VQ_LOOK entries: density of the phase / BSDF sample (sign bit: delta lobe) and refN of its vertex
+	V3 refN = v3(0.0f);
 	unsigned nRays = 0;
 	// A path may have two entries in one bounce (the opacity query of the sensor ray and its emitter sample), handled by
 	// different lanes: the radiance is added component-wise with atomics, the opacity is a plain store to L.w.
@@ -357,6 +592,13 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 					medium = VQ_MEDIUM(bits);
 					interactions = 0;
 					T = v3(1.0f);
+					if (bits & VQ_LOOK) {
+						// the walk of rayIntersectAndLookForEmitter behind an index-matched first hit: a ray, not a segment
+						d = v3(b.x, b.y, b.z); samplePdf = b.w;
+						const float4 x = ps.shX[entry];
+						refN = v3(x.x, x.y, x.z);
+						remaining = INFINITY; lengthFactor = 1.0f; mint = MTS_EPSILON; interactions = 1;
+					} else
 					if (!(remaining > 0)) { finish(v3(1.0f)); have = false; }      // while (remaining > 0): the loop body never runs
 				}
 			}
@@ -370,7 +612,8 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 			float tmax; V3 rcp;
 			tv.o = o; tv.d = d;
 			++nRays;
-			if (clip_ray(S, o, d, mint, remaining * lengthFactor, false, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
+			// evalTransmittance asks the light-record overload (un-floored epsilon), the emitter look-up Scene::rayIntersect(ray, its)
+			if (clip_ray(S, o, d, mint, remaining * lengthFactor, (bits & VQ_LOOK) != 0, tv.tmin, tmax, rcp)) tv.begin(tmax, rcp);
 		}
 		trace_warp<false, CURVED>(S, tv);
 		if (have) {
@@ -384,6 +627,41 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 				sh = S.shapes[sf.shape];
 				isNull = (bsdf_type(S.bsdfs[sh.bsdf]) & B_NULL) != 0;
 			}
+			if (bits & VQ_LOOK) {
+				// volpath.cpp:376-424
+				if (medium >= 0) T *= medium_transmittance(S.media[medium], t);
+				const bool delta = (__float_as_uint(samplePdf) >> 31) != 0;
+				const float pdfS = fabsf(samplePdf);
+				V3 value = v3(0.0f); float emitterPdf = 0.0f;
+				if (surface && (interactions == VQ_MAXI(bits) || !isNull || sh.emitter >= 0)) {
+					if (sh.emitter >= 0) {
+						value = T * area_emitter_eval(S, sh.emitter, sf.ns, -d);
+						if (!delta) emitterPdf = emitter_pdf_direct(S, sh.emitter, refN, d, t, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, sh.emitter);
+					}
+					done = true;
+				} else if (!surface) {
+					if (S.envEmitter >= 0) {
+						const EmitterRec &env = S.emitters[S.envEmitter];
+						float nearT, farT;
+						if (sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
+							value = T * env.radiance;
+							const V3 n = normalize(env.sphereCenter - (o + d * farT));
+							if (!delta) emitterPdf = emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
+						}
+					}
+					done = true;
+				} else if (is_zero(T)) done = true;
+				else {
+					if (sh.interior >= 0 || sh.exterior >= 0) medium = target_medium(sh, sf.ng, d);
+					o = o + d * t;
+					mint = MTS_EPSILON;
+					if (++interactions > 100) done = true;
+				}
+				if (done) {
+					if (!is_zero(value)) finish(value * mi_weight(pdfS, emitterPdf));
+					have = false; done = false;
+				}
+			} else
 			if (surface && (interactions == VQ_MAXI(bits) || !isNull)) { T = v3(0.0f); done = true; }      // an occluder
 			else {
 				if (medium >= 0) T *= medium_transmittance(S.media[medium], fminf(t, remaining));

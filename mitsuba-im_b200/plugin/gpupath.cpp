@@ -82,6 +82,8 @@ public:
 		m_direct = props.getPluginName() == "direct" || props.getBoolean("direct", false);
 		// SimpleVolumetricPathTracer semantics (participating media) when installed as volpath_simple.so
 		m_volpath = props.getPluginName() == "volpath_simple" || props.getBoolean("volpath", false);
+		// VolumetricPathTracer (the variant with multiple importance sampling) when installed as volpath.so
+		m_volmis = props.getPluginName() == "volpath" || props.getBoolean("volpathMIS", false);
 		m_emitterSamples = props.getInteger("emitterSamples", props.getInteger("shadingSamples", 1));
 		m_bsdfSamples = props.getInteger("bsdfSamples", props.getInteger("shadingSamples", 1));
 		const int n = mtsb_device_count();
@@ -102,7 +104,7 @@ public:
 
 	void describeIntegrator(mtsb_integrator_desc &d) const {
 		memset(&d, 0, sizeof(d));
-		d.type = m_direct ? MTSB_INTEGRATOR_DIRECT : (m_volpath ? MTSB_INTEGRATOR_VOLPATH_SIMPLE : MTSB_INTEGRATOR_PATH);
+		d.type = m_direct ? MTSB_INTEGRATOR_DIRECT : (m_volmis ? MTSB_INTEGRATOR_VOLPATH : (m_volpath ? MTSB_INTEGRATOR_VOLPATH_SIMPLE : MTSB_INTEGRATOR_PATH));
 		d.max_depth = m_maxDepth; d.rr_depth = m_rrDepth;
 		d.strict_normals = m_strictNormals ? 1 : 0; d.hide_emitters = m_hideEmitters ? 1 : 0;
 		d.emitter_samples = m_emitterSamples; d.bsdf_samples = m_bsdfSamples;
@@ -212,7 +214,7 @@ public:
 	MTS_DECLARE_CLASS()
 
 	int m_gpus, m_sppPerPass, m_seed, m_builder, m_emitterSamples, m_bsdfSamples;
-	bool m_direct, m_volpath;
+	bool m_direct, m_volpath, m_volmis;
 	volatile bool m_cancel;
 	GPUResponsiveIntegrator *m_responsive;      // the adapter made by makeResponsiveIntegrator (not owned; clears itself)
 	ref<Mutex> m_mutex;

@@ -204,7 +204,7 @@ def make_film(width, height, rfilter="box", channels=5, stddev=0.5):
 def make_integrator(kind="path", max_depth=-1, rr_depth=5, strict_normals=False, hide_emitters=False,
                     emitter_samples=1, bsdf_samples=1):
     d = B.IntegratorDesc()
-    d.type = dict(path=B.INTEGRATOR_PATH, direct=B.INTEGRATOR_DIRECT, volpath_simple=B.INTEGRATOR_VOLPATH_SIMPLE)[kind]
+    d.type = dict(path=B.INTEGRATOR_PATH, direct=B.INTEGRATOR_DIRECT, volpath_simple=B.INTEGRATOR_VOLPATH_SIMPLE, volpath=B.INTEGRATOR_VOLPATH)[kind]
     d.max_depth, d.rr_depth = max_depth, rr_depth
     d.strict_normals, d.hide_emitters = int(strict_normals), int(hide_emitters)
     d.emitter_samples, d.bsdf_samples = emitter_samples, bsdf_samples

@@ -152,6 +152,10 @@ def fog_cases(td):
     li_case(td, "fog", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=37))
     li_case(td, "fog_short", S.fog_scene(48, 32, spp=4, max_depth=3, sampler="ctr", seed=41))
     li_case(td, "fog_haze", S.fog_scene(48, 32, spp=4, max_depth=-1, sampler="ctr", seed=43, haze=True))
+    # VolumetricPathTracer (src/integrators/path/volpath.cpp): the same scenes with multiple importance sampling
+    li_case(td, "fogmis", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=37, kind="volpath"))
+    li_case(td, "fogmis_short", S.fog_scene(48, 32, spp=4, max_depth=3, sampler="ctr", seed=41, kind="volpath"))
+    li_case(td, "fogmis_haze", S.fog_scene(48, 32, spp=4, max_depth=-1, sampler="ctr", seed=43, haze=True, kind="volpath"))
 
 
 if __name__ == "__main__":
