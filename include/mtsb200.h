@@ -268,6 +268,18 @@ MTSB_API int  mtsb_trace_light(mtsb_scene *scene, const mtsb_ray *rays, size_t n
  * pointers, asynchronous on the context stream; otherwise host pointers, synchronous. */
 #define MTSB_NOALLOC_MAX_RAYS 65536u
 MTSB_API int  mtsb_trace_closest_noalloc(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device);
+/* Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-730, 769-792): the kd-tree query, then the scene's "special
+ * shapes" — the shapes Scene::initializeBidirectional creates for the sensor and the emitters (scene.cpp:394-422), which are
+ * not in the kd-tree — tested linearly with the floored adaptive epsilon and no scene-box clip.  In the GPU subset these
+ * are the aperture disk of a `thinlens` sensor (thinlens.cpp:522-534: mtsb_scene_add_special_disk with toWorld x
+ * scale(apertureRadius), added by the caller, any time) and the bounding sphere of the constant environment emitter
+ * (constant.cpp:69-94; known to the library after commit, appended after the caller's shapes as Scene does).  A hit on
+ * special shape i reports prim = MTSB_SPECIAL_PRIM + i (u, v of the disk as for mtsb_scene_add_disk; 0, 0 on the sphere).
+ * Used by bidirectional integrators only; `path` / `direct` / `volpath*` never call it. */
+#define MTSB_SPECIAL_PRIM 0xF0000000u
+MTSB_API int  mtsb_scene_add_special_disk(mtsb_scene *scene, const float to_world[16]);
+MTSB_API int  mtsb_trace_closest_all(mtsb_scene *scene, const mtsb_ray *rays, size_t n, mtsb_hit *hits, int on_device);
+MTSB_API int  mtsb_trace_any_all(mtsb_scene *scene, const mtsb_ray *rays, size_t n, uint8_t *out, int on_device);
 /* Traversal counters of the last trace call when built with counters enabled, else zeros:
  * out[0]=nodes visited, out[1]=primitive tests, out[2]=rays. */
 MTSB_API int  mtsb_trace_counters(mtsb_scene *scene, uint64_t out[4]);

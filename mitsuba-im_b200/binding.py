@@ -20,6 +20,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
 NOALLOC_MAX_RAYS = 65536
+SPECIAL_PRIM = 0xF0000000
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
 BSDF_PASSTHROUGH = 7
 BSDF_ROUGHPLASTIC = 8
@@ -113,6 +114,7 @@ def lib():
         "mtsb_trace_closest": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_any": (i32, [vp, vp, sz, vp, i32]),
         "mtsb_trace_surface": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_light": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_counters": (i32, [vp, vp]),
         "mtsb_trace_closest_noalloc": (i32, [vp, vp, sz, vp, i32]),
+        "mtsb_scene_add_special_disk": (i32, [vp, vp]), "mtsb_trace_closest_all": (i32, [vp, vp, sz, vp, i32]), "mtsb_trace_any_all": (i32, [vp, vp, sz, vp, i32]),
         "mtsb_trace_count": (i32, [vp, vp, sz, i32, i32, vp]),
         "mtsb_host_alloc": (vp, [sz]), "mtsb_host_free": (None, [vp]),
         "mtsb_eval_bsdf": (i32, [vp, i32, vp, sz, vp]), "mtsb_eval_bsdf_s3": (i32, [vp, i32, vp, vp, sz, vp]), "mtsb_eval_emitter": (i32, [vp, vp, sz, vp]),
@@ -339,6 +341,24 @@ class Scene:
         """Asynchronous query on device pointers (ints); mode in {'closest','any','surface'}."""
         fn = {"closest": lib().mtsb_trace_closest, "any": lib().mtsb_trace_any, "surface": lib().mtsb_trace_surface}[mode]
         _check(fn(self.h, C.c_void_p(d_rays), n, C.c_void_p(d_out), 1))
+
+    def add_special_disk(self, to_world):
+        """A special shape of Scene::initializeBidirectional outside the kd-tree: the aperture disk of a thinlens sensor."""
+        M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
+        return _check(lib().mtsb_scene_add_special_disk(self.h, _ptr(M)))
+
+    def ray_intersect_all(self, rays):
+        """Scene::rayIntersectAll(ray, its): closest hit over the kd-tree shapes and the special shapes (prim >= SPECIAL_PRIM)."""
+        r = self._rays(rays)
+        out = np.empty(r.shape[0], hit_dtype)
+        _check(lib().mtsb_trace_closest_all(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def ray_intersect_any_all(self, rays):
+        r = self._rays(rays)
+        out = np.empty(r.shape[0], np.uint8)
+        _check(lib().mtsb_trace_any_all(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
 
     def ray_intersect_noalloc(self, rays, out=None):
         """mtsb_trace_closest_noalloc with host buffers: at most NOALLOC_MAX_RAYS rays, no device allocation inside."""

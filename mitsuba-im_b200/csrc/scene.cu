@@ -306,6 +306,21 @@ int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, 
 	return (int) scene->shapes.size() - 1;
 }
 
+int mtsb_scene_add_special_disk(mtsb_scene *scene, const float m[16]) {
+	if (!scene || !m) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_special_disk: NULL argument");
+	RectRec rr; memset(&rr, 0, sizeof(rr));
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) rr.toWorld[r*4+c] = m[r*4+c];
+	invert_affine(m, rr.toObject);
+	rr.dpdu = v3(m[0], m[4], m[8]);
+	rr.dpdv = v3(m[1], m[5], m[9]);
+	V3 n = v3(rr.toObject[8], rr.toObject[9], rr.toObject[10]);
+	const float len = sqrtf(n.x*n.x + n.y*n.y + n.z*n.z);
+	rr.n = v3(n.x/len, n.y/len, n.z/len);
+	scene->specialRecs.push_back(rr);
+	scene->specialTypes.push_back(SHAPE_DISK);
+	return (int) scene->specialRecs.size() - 1;
+}
+
 int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], float radius, int flip_normals, int bsdf, int emitter) {
 	if (!scene || !object_to_world) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_sphere: NULL argument");
 	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_sphere"));

@@ -20,6 +20,10 @@ struct mtsb_scene {
 	std::vector<float> bsdfTables;                 // per-BSDF lookup tables, each stored as {count, values...} (roughplastic)
 	std::vector<long> bsdfTableOffset;             // per BSDF: offset into bsdfTables or -1
 	mtsb::DevBuf<float> dBsdfTables;
+	// Scene::m_specialShapes of the subset (scene.cpp:394-422): caller-added aperture disks, then the environment spheres
+	std::vector<mtsb::RectRec> specialRecs; std::vector<uint32_t> specialTypes;
+	mtsb::DevBuf<mtsb::RectRec> dSpecialRecs; mtsb::DevBuf<uint32_t> dSpecialTypes;
+	size_t specialUploaded = (size_t) -1;          // number of caller-added specials the device copy was made for
 	std::vector<mtsb::EmitterRec> emitters;
 	std::vector<mtsb::MediumRec> media;
 	std::vector<float> emitterWeights;

@@ -379,10 +379,16 @@ class SceneDesc:
             if s.get("interior") is not None or s.get("exterior") is not None:
                 sc.set_shape_media(k, -1 if s.get("interior") is None else s["interior"],
                                    -1 if s.get("exterior") is None else s["exterior"])
+        if self.sensor is not None and self.sensor.get("aperture_radius", 0.0) > 0:
+            # the thinlens sensor's special shape: a disk of the aperture's radius in the sensor's frame (thinlens.cpp:522-534)
+            sc.add_special_disk(np.asarray(self.sensor["to_world"], np.float64) @ scale(self.sensor["aperture_radius"]))
         if self.sensor is not None:
             # Scene::getAABB() includes the sensor's AABB (the camera position) when the environment emitter is sized
-            pos = np.asarray(self.sensor["to_world"], np.float64)[0:3, 3].astype(np.float32)
-            sc.expand_bounds(pos, pos)
+            M = np.asarray(self.sensor["to_world"], np.float64)
+            r = float(self.sensor.get("aperture_radius", 0.0))
+            # perspective: the camera position; thinlens: the box of its aperture (thinlens.cpp:515-519, getSpatialBounds)
+            corners = np.array([[sx * r, sy * r, 0.0, 1.0] for sx in (-1, 1) for sy in (-1, 1)]) @ M.T
+            sc.expand_bounds(corners[:, 0:3].min(axis=0).astype(np.float32), corners[:, 0:3].max(axis=0).astype(np.float32))
         sc.commit(builder)
         return sc
 

@@ -208,6 +208,39 @@ public:
 		return 0;
 	}
 
+	/// Scene::rayIntersectAll(ray, its) and Scene::rayIntersectAll(ray) (src/librender/scene.cpp:716-730, 769-792): 4 floats per
+	/// ray — t, shape index (kd-tree shapes >= 0, special shape k -> -(2 + k), miss -> -1), any-hit flag, pad
+	int all(int argc, char **argv) {
+		if (argc < 5) { cout << "all <scene.xml> <rays> <out>" << endl; return 1; }
+		load(argv[2]);
+		if (!m_scene) { cout << "all: needs a scene file" << endl; return 1; }
+		std::vector<float> rays = readFloats(argv[3]);
+		size_t n = rays.size() / 8;
+		std::vector<float> out(n * 4, 0.0f);
+		const ref_vector<Shape> &special = m_scene->getSpecialShapes();
+		cout << "special shapes: " << special.size();
+		for (size_t k = 0; k < special.size(); ++k) cout << " " << special[k]->getClass()->getName();
+		cout << endl;
+		for (size_t i = 0; i < n; ++i) {
+			const float *r = &rays[i*8];
+			float *o = &out[i*4];
+			Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7], 0.0f);
+			Intersection its;
+			if (m_scene->rayIntersectAll(ray, its)) {
+				int idx = shapeIndex(its.shape);
+				if (idx < 0)
+					for (size_t k = 0; k < special.size(); ++k)
+						if (special[k].get() == its.shape) idx = -(2 + (int) k);
+				o[0] = its.t; o[1] = i2f(idx);
+			} else {
+				o[0] = std::numeric_limits<float>::infinity(); o[1] = i2f(-1);
+			}
+			o[2] = m_scene->rayIntersectAll(ray) ? 1.0f : 0.0f;
+		}
+		writeFloats(argv[4], out);
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -273,9 +306,10 @@ public:
 	}
 
 	int run(int argc, char **argv) {
-		if (argc < 2) { cout << "raydump trace|light|bsdf|emitter ..." << endl; return 1; }
+		if (argc < 2) { cout << "raydump trace|light|all|bsdf|emitter ..." << endl; return 1; }
 		if (!strcmp(argv[1], "trace")) return trace(argc, argv);
 		if (!strcmp(argv[1], "light")) return light(argc, argv);
+		if (!strcmp(argv[1], "all")) return all(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

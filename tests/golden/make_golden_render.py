@@ -145,6 +145,41 @@ def roughplastic_cases(td):
     li_case(td, "roughplastic", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, materials=S.ROUGH_PLASTICS))
 
 
+def all_case(td):
+    """Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-792; oracle/raydump.cpp `all`): the kd-tree shapes plus the special
+    shapes of Scene::initializeBidirectional — here the aperture disk of the thinlens sensor and the bounding sphere of the
+    constant environment.  Rays: chords through the scene (they end on the environment sphere when they miss the geometry),
+    rays aimed at the aperture, and short segments that stop before anything."""
+    sd = S.materials_scene(48, 32, spp=1, max_depth=4, sampler="ctr", seed=1)
+    s = sd.sensor
+    sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=1, seed=1, sampler="ctr",
+                  aperture_radius=0.12, focus_distance=5.2)
+    xml = sd.to_xml(td, "all")
+    rng = np.random.default_rng(12)
+    n = 6000
+    rays = np.zeros((n, 8), np.float32)
+    a = S.chord_rays(n, center=(0, 0.5, 0), radius=5.0, seed=77, mint=S.EPSILON)
+    rays[:, 0:3], rays[:, 3], rays[:, 4:7], rays[:, 7] = a["o"], a["mint"], a["d"], a["maxt"]
+    cam = np.asarray(s["to_world"], np.float64)[0:3, 3]
+    k = n // 4                                     # a quarter of the rays fly at the aperture (radius 0.12) from inside the scene
+    src = rng.uniform([-2, 0.2, -1.5], [2, 2.0, 1.5], (k, 3))
+    dst = cam + rng.normal(size=(k, 3)) * 0.1
+    d = dst - src
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:k, 0:3], rays[:k, 4:7] = src, d
+    rays[k:k + 500, 7] = rng.uniform(0.05, 2.0, 500)     # bounded segments
+    ip, op = os.path.join(td, "all_in.bin"), os.path.join(td, "all_out.bin")
+    rays.tofile(ip)
+    r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "all", xml, ip, op], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0 or not os.path.exists(op):
+        raise RuntimeError(r.stdout[-3000:])
+    print([l for l in r.stdout.splitlines() if "special shapes" in l])
+    out = np.fromfile(op, np.float32).reshape(n, 4)
+    shape = out[:, 1].copy().view(np.int32)
+    np.savez_compressed(os.path.join(GOLD, "all.npz"), rays=rays, t=out[:, 0], shape=shape, any=out[:, 2].astype(np.uint8))
+    print("all:", n, "rays; hits on kd shapes", (shape >= 0).sum(), "aperture disk", (shape == -2).sum(), "environment sphere", (shape == -3).sum(), "misses", (shape == -1).sum())
+
+
 def fog_cases(td):
     """SimpleVolumetricPathTracer (src/integrators/path/volpath_simple.cpp) over homogeneous media: index-matched and
     dielectric medium boundaries, isotropic and Henyey-Greenstein phase functions; with the camera outside every medium
@@ -159,6 +194,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "all":              # rayIntersectAll (round 2)
+        with tempfile.TemporaryDirectory() as td:
+            all_case(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "roughplastic":     # round 2
         with tempfile.TemporaryDirectory() as td:
             roughplastic_cases(td)
@@ -190,3 +229,4 @@ if __name__ == "__main__":
         li_case(td, "analytic", S.analytic_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=31))
         fog_cases(td)
         roughplastic_cases(td)
+        all_case(td)

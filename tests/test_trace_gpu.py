@@ -366,3 +366,40 @@ def test_against_live_reference(pkg, ctx, tmp_path):
         assert (a == ref[:, 14].copy().view(np.int32)).mean() >= 0.9999
     finally:
         sc.close()
+
+
+def test_ray_intersect_all_matches_reference(pkg, ctx, golden):
+    """Scene::rayIntersectAll(ray, its) / rayIntersectAll(ray) (src/librender/scene.cpp:716-730, 769-792): the kd-tree shapes plus
+    the special shapes of Scene::initializeBidirectional (scene.cpp:394-422) — the aperture disk of the thinlens sensor and the
+    bounding sphere of the constant environment — against tests/golden/all.npz (oracle/raydump.cpp `all`; parameters of
+    make_golden_render.all_case)."""
+    S, B = pkg.scenes, pkg.binding
+    g = golden("all.npz")
+    rays, ref_t, ref_shape, ref_any = g["rays"], g["t"], g["shape"], g["any"]
+    sd = S.materials_scene(48, 32, spp=1, max_depth=4, sampler="ctr", seed=1)
+    s = sd.sensor
+    sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=1, seed=1, sampler="ctr",
+                  aperture_radius=0.12, focus_distance=5.2)
+    sc = sd.upload(ctx, B.BUILDER_PLOC)
+    try:
+        hits = sc.ray_intersect_all(rays)
+        any_ = sc.ray_intersect_any_all(rays)
+        plain = sc.ray_intersect(rays)
+        offs = sc.shape_offsets()
+        prim = hits["prim"]
+        special = prim >= B.SPECIAL_PRIM
+        miss = prim == B.MTSB_NO_HIT
+        shape = np.where(miss, -1, np.where(special & ~miss, -2 - (prim.astype(np.int64) - B.SPECIAL_PRIM), np.searchsorted(offs, prim, side="right") - 1))
+        same = shape == ref_shape
+        assert same.mean() >= helpers.PRIM_AGREE, "shape agreement %.5f" % same.mean()
+        assert (ref_shape == -2).sum() > 300 and (ref_shape == -3).sum() > 1000 and (ref_shape == -1).sum() > 100      # disk, sphere, misses all occur
+        m = same & np.isfinite(ref_t)
+        rel = np.abs(hits["t"][m] - ref_t[m]) / np.maximum(np.abs(ref_t[m]), 1e-6)
+        assert (rel <= helpers.T_REL).mean() >= 1 - helpers.T_UNWEIGHTED_SHARE, float((rel <= helpers.T_REL).mean())
+        assert np.isinf(hits["t"][miss]).all()
+        assert (any_ == ref_any).mean() >= helpers.PRIM_AGREE
+        # the special pass only ever shortens a ray: where it reports a kd-tree shape the record is the plain query's
+        kd = ~special
+        assert (hits[kd] == plain[kd]).all()
+    finally:
+        sc.close()
