@@ -5,6 +5,8 @@
 //   Shape::sampleDirect / pdfDirect                   src/librender/shape.cpp:102-126
 //   TriMesh::samplePosition, Triangle::sample         src/librender/trimesh.cpp:413-425, src/libcore/triangle.cpp:24-60
 //   Rectangle::samplePosition                         src/shapes/rectangle.cpp:210-216
+//   Disk::samplePosition                              src/shapes/disk.cpp:247-255
+//   Sphere::{sampleDirect,pdfDirect}                  src/shapes/sphere.cpp:286-385 (cone sampling from outside)
 //   PointEmitter::{sampleDirect,pdfDirect}            src/emitters/point.cpp:133-153
 //   ConstantBackgroundEmitter::{sampleDirect,pdfDirect,fillDirectSamplingRecord}  src/emitters/constant.cpp:175-256
 #pragma once
@@ -62,6 +64,14 @@ __device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeId
 		n = r.n; pdf = r.invSurfaceArea;
 		return;
 	}
+	if (sh.type == SHAPE_DISK) {
+		const RectRec &r = S.rects[sh.rect];
+		float x, y; square_to_disk_concentric(sx, sy, x, y);
+		const float *m = r.toWorld;
+		p = v3(m[0] * x + m[1] * y + m[3], m[4] * x + m[5] * y + m[7], m[8] * x + m[9] * y + m[11]);
+		n = r.n; pdf = r.invSurfaceArea;
+		return;
+	}
 	const float *cdf = S.triAreaCdf + S.triAreaCdfOffset[shapeIdx];
 	float dummy;
 	const uint32_t tri = cdf_sample_reuse(cdf, sh.primCount, sy, dummy);
@@ -82,20 +92,90 @@ __device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeId
 	pdf = sh.invArea;
 }
 
+// solveQuadratic (src/libcore/util.cpp:449-487)
+__device__ inline bool solve_quadratic(float a, float b, float c, float &x0, float &x1) {
+	if (a == 0) { if (b != 0) { x0 = x1 = -c / b; return true; } return false; }
+	const float discrim = b * b - 4.0f * a * c;
+	if (discrim < 0) return false;
+	const float sq = sqrtf(discrim);
+	const float temp = b < 0 ? -0.5f * (b - sq) : -0.5f * (b + sq);
+	x0 = temp / a; x1 = c / temp;
+	if (x0 > x1) { const float t = x0; x0 = x1; x1 = t; }
+	return true;
+}
+
+// Sphere::sampleDirect (sphere.cpp:286-355): the cone that contains the sphere when the reference point is outside,
+// uniform over the sphere otherwise.  center = r.dpdu, radius = r.dpdv.x, flipNormals = r.pad[0] (scene.cu)
+__device__ inline void sphere_sample_direct(const RectRec &r, const V3 &ref, float sx, float sy, DirectSample &out) {
+	const V3 center = r.dpdu; const float radius = r.dpdv.x;
+	const V3 refToCenter = center - ref;
+	const float refDist2 = dot(refToCenter, refToCenter);
+	const float invRefDist = 1.0f / sqrtf(refDist2);
+	const float sinAlpha = radius * invRefDist;
+	if (sinAlpha < 1 - MTS_EPSILON) {
+		const float cosAlpha = safe_sqrt(1.0f - sinAlpha * sinAlpha);
+		const float cosTheta = (1 - sx) + sx * cosAlpha;                      // warp::squareToUniformCone (warp.cpp:54-63)
+		const float sinTheta = safe_sqrt(1.0f - cosTheta * cosTheta);
+		float sinPhi, cosPhi; sincosf(2.0f * MTS_PI * sy, &sinPhi, &cosPhi);
+		const V3 axis = refToCenter * invRefDist;
+		V3 s, t; coordinate_system(axis, s, t);
+		out.d = s * (cosPhi * sinTheta) + t * (sinPhi * sinTheta) + axis * cosTheta;
+		out.pdf = (1.0f / (2.0f * MTS_PI)) / (1 - cosAlpha);
+		const float projDist = dot(refToCenter, out.d);
+		const float baseT = refDist2 / projDist;
+		const V3 query = ref + out.d * baseT;
+		const V3 queryToCenter = center - query;
+		const float queryDist2 = dot(queryToCenter, queryToCenter), queryProjDist = dot(queryToCenter, out.d);
+		float nearT, farT;
+		if (!solve_quadratic(1.0f, -2 * queryProjDist, queryDist2 - radius * radius, nearT, farT)) nearT = queryProjDist;
+		out.dist = baseT + nearT;
+		out.n = normalize(out.d * nearT - queryToCenter);
+		out.p = center + out.n * radius;
+	} else {
+		const V3 d = square_to_uniform_sphere(sx, sy);
+		out.p = center + d * radius;
+		out.n = d;
+		V3 dd = out.p - ref;
+		const float dist2 = dot(dd, dd);
+		out.dist = sqrtf(dist2);
+		out.d = dd / out.dist;
+		out.pdf = r.invSurfaceArea * dist2 / fabsf(dot(out.d, out.n));
+	}
+	if (r.pad[0]) out.n = v3(-out.n.x, -out.n.y, -out.n.z);
+}
+// Sphere::pdfDirect (sphere.cpp:357-385), solid-angle measure
+__device__ inline float sphere_pdf_direct(const RectRec &r, const V3 &ref, const V3 &d, float dist, const V3 &n) {
+	const V3 refToCenter = r.dpdu - ref;
+	const float invRefDist = 1.0f / length(refToCenter);
+	const float sinAlpha = r.dpdv.x * invRefDist;
+	if (sinAlpha < 1 - MTS_EPSILON) {
+		const float cosAlpha = safe_sqrt(1 - sinAlpha * sinAlpha);
+		return (1.0f / (2.0f * MTS_PI)) / (1 - cosAlpha);
+	}
+	return r.invSurfaceArea * dist * dist / fabsf(dot(d, n));
+}
+
 // Emitter::sampleDirect for emitter `e`
 __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
 	const EmitterRec &em = S.emitters[e];
 	out.emitter = (int) e; out.pdf = 0; out.n = v3(0.0f); out.d = v3(0.0f); out.dist = 0; out.measure = M_SOLID_ANGLE; out.p = ref;
 	if (em.type == MTSB_EMITTER_AREA) {
-		V3 p; float pdf;
-		shape_sample_position(S, em.shape, sx, sy, p, out.n, pdf);
-		out.p = p;
-		V3 d = p - ref;
-		const float distSquared = dot(d, d);
-		out.dist = sqrtf(distSquared);
-		d /= out.dist;
-		const float dp = fabsf(dot(d, out.n));
-		pdf *= dp != 0 ? (distSquared / dp) : 0.0f;
+		V3 d; float pdf;
+		const ShapeRec &esh = S.shapes[em.shape];
+		if (esh.type == SHAPE_SPHERE) {                       // the sphere overrides Shape::sampleDirect
+			sphere_sample_direct(S.rects[esh.rect], ref, sx, sy, out);
+			d = out.d; pdf = out.pdf;
+		} else {
+			V3 p;
+			shape_sample_position(S, em.shape, sx, sy, p, out.n, pdf);
+			out.p = p;
+			d = p - ref;
+			const float distSquared = dot(d, d);
+			out.dist = sqrtf(distSquared);
+			d /= out.dist;
+			const float dp = fabsf(dot(d, out.n));
+			pdf *= dp != 0 ? (distSquared / dp) : 0.0f;
+		}
 		out.d = d; out.pdf = pdf;
 		if (dot(d, refN) >= 0 && dot(d, out.n) < 0 && pdf != 0) return em.radiance / pdf;
 		out.pdf = 0.0f;
@@ -128,11 +208,24 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 	}
 }
 
-// Emitter::pdfDirect for a direction that hit emitter `e` (d, dist, n of the hit; measure = solid angle)
-__device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const V3 &refN, const V3 &d, float dist, const V3 &n, int measure) {
+// Emitter::pdfDirect for a direction that hit emitter `e` (d, dist, n of the hit; measure = solid angle).  `ref` (dRec.ref) is
+// read by sphere emitters only.
+__device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const V3 &refN, const V3 &d, float dist, const V3 &n, int measure,
+		const V3 &ref = V3()) {
 	const EmitterRec &em = S.emitters[e];
 	if (em.type == MTSB_EMITTER_AREA) {
 		if (dot(d, refN) >= 0 && dot(d, n) < 0) {
+			const ShapeRec &esh = S.shapes[em.shape];
+			if (esh.type == SHAPE_SPHERE) {
+				const float pdfSA = sphere_pdf_direct(S.rects[esh.rect], ref, d, dist, n);
+				if (measure == M_SOLID_ANGLE) return pdfSA;
+				if (measure == M_AREA) {
+					const RectRec &r = S.rects[esh.rect];
+					const float sinAlpha = r.dpdv.x / length(r.dpdu - ref);
+					return sinAlpha < 1 - MTS_EPSILON ? pdfSA * fabsf(dot(d, n)) / (dist * dist) : r.invSurfaceArea;
+				}
+				return 0.0f;
+			}
 			if (measure == M_SOLID_ANGLE) return em.invSurfaceArea * (dist * dist) / fabsf(dot(d, n));
 			if (measure == M_AREA) return em.invSurfaceArea;
 		}

@@ -121,7 +121,7 @@ direct_tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, DirectFan fan)
 			if (emitterId < 0) continue;
 			value = area_emitter_eval(S, emitterId, sf.ns, -d);
 			if (!(flags & PF_DELTA))
-				lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, emitterId);
+				lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, emitterId);
 		} else {
 			if (S.envEmitter < 0) continue;
 			const EmitterRec &env = S.emitters[S.envEmitter];

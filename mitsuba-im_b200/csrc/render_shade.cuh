@@ -51,7 +51,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 				value = area_emitter_eval(S, emitterId, sf.ns, -d);
 				hitEmitter = true;
 				if (!(flags & PF_DELTA))
-					lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, emitterId);
+					lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, emitterId);
 			}
 		} else if (S.envEmitter >= 0) {
 			if (integ.hideEmitters && !(flags & PF_SCATTERED)) alive = false;
@@ -323,7 +323,7 @@ __global__ void eval_emitter_kernel(SceneDev S, const float *in, size_t n, float
 	const V3 value = scene_sample_emitter_direct(S, p, refN, r[6], r[7], ds);
 	o[0] = value.x; o[1] = value.y; o[2] = value.z; o[3] = ds.pdf;
 	o[4] = ds.d.x; o[5] = ds.d.y; o[6] = ds.d.z; o[7] = ds.dist; o[8] = (float) ds.measure;
-	o[9] = (ds.pdf > 0 && !is_zero(value)) ? emitter_pdf_direct(S, ds.emitter, refN, ds.d, ds.dist, ds.n, ds.measure) * emitter_pdf_discrete(S, ds.emitter) : 0.0f;
+	o[9] = (ds.pdf > 0 && !is_zero(value)) ? emitter_pdf_direct(S, ds.emitter, refN, ds.d, ds.dist, ds.n, ds.measure, p) * emitter_pdf_discrete(S, ds.emitter) : 0.0f;
 	o[10] = (float) ds.emitter; o[11] = 0;
 }
 

@@ -346,7 +346,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 					if (isEmitter) {                                  // dRec.setQuery(ray, its); value = transmittance * Le
 						const V3 value = T0 * area_emitter_eval(S, sh.emitter, sf.ns, -d);
 						if (!is_zero(value)) {
-							const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, sh.emitter, refN, d, h.x, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, sh.emitter);
+							const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, sh.emitter, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, sh.emitter);
 							Li += thr * value * mi_weight(samplePdf, emitterPdf);
 						}
 					}
@@ -636,7 +636,7 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 				if (surface && (interactions == VQ_MAXI(bits) || !isNull || sh.emitter >= 0)) {
 					if (sh.emitter >= 0) {
 						value = T * area_emitter_eval(S, sh.emitter, sf.ns, -d);
-						if (!delta) emitterPdf = emitter_pdf_direct(S, sh.emitter, refN, d, t, sf.ns, M_SOLID_ANGLE) * emitter_pdf_discrete(S, sh.emitter);
+						if (!delta) emitterPdf = emitter_pdf_direct(S, sh.emitter, refN, d, t, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, sh.emitter);
 					}
 					done = true;
 				} else if (!surface) {

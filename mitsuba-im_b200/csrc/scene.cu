@@ -278,7 +278,6 @@ int mtsb_scene_expand_bounds(mtsb_scene *scene, const float min[3], const float 
 int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, int bsdf, int emitter) {
 	if (!scene || !m) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_disk: NULL argument");
 	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_disk"));
-	if (emitter >= 0) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_disk: area emitters on analytic disks are outside the GPU subset");
 	float ow[16]; memcpy(ow, m, sizeof(ow));
 	if (flip_normals)   // m_objectToWorld->prependScale(Vector(1, 1, -1))  (disk.cpp:86-87)
 		for (int r = 0; r < 4; ++r) ow[r*4+2] = -ow[r*4+2];
@@ -303,6 +302,7 @@ int mtsb_scene_add_disk(mtsb_scene *scene, const float m[16], int flip_normals, 
 	scene->shapes.push_back(sh);
 	scene->primCount += 1;
 	scene->shapeOffsets.push_back(scene->primCount);
+	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
 	return (int) scene->shapes.size() - 1;
 }
 
@@ -324,7 +324,6 @@ int mtsb_scene_add_special_disk(mtsb_scene *scene, const float m[16]) {
 int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], float radius, int flip_normals, int bsdf, int emitter) {
 	if (!scene || !object_to_world) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_sphere: NULL argument");
 	MTSB_CHECK(check_refs(scene, bsdf, emitter, "mtsb_scene_add_sphere"));
-	if (emitter >= 0) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_sphere: area emitters on analytic spheres are outside the GPU subset");
 	if (!(radius > 0)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_sphere: cannot create spheres of radius <= 0");                                                  // sphere.cpp:130-131
 	RectRec rr; memset(&rr, 0, sizeof(rr));
 	for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) rr.toWorld[r*4+c] = object_to_world[r*4+c];
@@ -342,6 +341,7 @@ int mtsb_scene_add_sphere(mtsb_scene *scene, const float object_to_world[16], fl
 	scene->shapes.push_back(sh);
 	scene->primCount += 1;
 	scene->shapeOffsets.push_back(scene->primCount);
+	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
 	return (int) scene->shapes.size() - 1;
 }
 

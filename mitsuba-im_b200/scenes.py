@@ -236,15 +236,17 @@ class SceneDesc:
                                 emitter=emitter, flip_normals=flip_normals))
         return len(self.shapes) - 1
 
-    def add_sphere(self, center, radius, bsdf=None, flip_normals=False):
-        """Analytic `sphere` (src/shapes/sphere.cpp) given by center + radius."""
-        self.shapes.append(dict(type="sphere", center=tuple(float(x) for x in center), radius=float(radius), bsdf=bsdf or dict(type="diffuse"),
-                                emitter=None, flip_normals=flip_normals))
+    def add_sphere(self, center, radius, bsdf=None, flip_normals=False, emitter=None):
+        """Analytic `sphere` (src/shapes/sphere.cpp) given by center + radius; emitter = radiance of an area light on it."""
+        self.shapes.append(dict(type="sphere", center=tuple(float(x) for x in center), radius=float(radius),
+                                bsdf=bsdf if (bsdf is not None or emitter is not None) else dict(type="diffuse"),
+                                emitter=emitter, flip_normals=flip_normals))
         return len(self.shapes) - 1
 
-    def add_disk(self, to_world, bsdf=None, flip_normals=False):
+    def add_disk(self, to_world, bsdf=None, flip_normals=False, emitter=None):
         """Analytic `disk` (src/shapes/disk.cpp): the unit disk of the object-space xy plane under `to_world`."""
-        self.shapes.append(dict(type="disk", to_world=np.asarray(to_world, np.float64), bsdf=bsdf or dict(type="diffuse"), emitter=None,
+        self.shapes.append(dict(type="disk", to_world=np.asarray(to_world, np.float64),
+                                bsdf=bsdf if (bsdf is not None or emitter is not None) else dict(type="diffuse"), emitter=emitter,
                                 flip_normals=flip_normals))
         return len(self.shapes) - 1
 
@@ -712,6 +714,27 @@ def analytic_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent
     sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
     lV, lN, lF = displaced_sphere(1, seed=99, radius=0.4, center=(0.5, 2.6, 0.3), amplitude=0.0)
     sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
+    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd
+
+
+def analytic_lights_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0):
+    """Area lights on analytic shapes: a small emitting `sphere` above the scene (cone sampling from outside,
+    sphere.cpp:286-355), a large emitting sphere the camera and the scene sit INSIDE (uniform-sphere branch, flipped normals so
+    that it shines inwards), and an emitting `disk` (Disk::samplePosition); diffuse, glass and GGX receivers."""
+    sd = SceneDesc()
+    sd.add_sphere((-1.2, 2.2, 0.3), 0.25, emitter=(30, 26, 20))
+    sd.add_sphere((0.0, 1.0, 0.0), 9.0, emitter=(0.15, 0.2, 0.3), flip_normals=True)
+    sd.add_disk(translate(1.4, 1.8, 0.6) @ rotate((1, 0, 0), 110) @ scale(0.35), emitter=(18, 14, 9))
+    sd.add_sphere((-1.1, 0.5, 0.2), 0.5, bsdf=dict(type="dielectric"))
+    V, N, F = displaced_sphere(2, seed=5, radius=0.45, center=(0.2, 0.45, -0.2))
+    sd.add_mesh(V, N, F, bsdf=dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
+    sd.add_sphere((1.3, 0.45, 0.5), 0.45, bsdf=dict(type="roughconductor", distribution="ggx", alpha=0.1))
+    g = 4.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
     sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
     sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
     return sd

@@ -11,6 +11,14 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 import __graft_entry__ as graft  # noqa: E402
 
+# torch first, where it is installed: its bundled NCCL (2.28) must be the libnccl.so.2 of the process before csrc/comm.cu
+# dlopen()s one — otherwise, on a multi-GPU box, the system's older NCCL gets loaded by the film-reduce tests and a later
+# `import torch` in the same process fails on a symbol it lacks (seen on the 2-GPU box: ncclDevCommCreate)
+try:
+    import torch  # noqa: F401,E402
+except ImportError:
+    pass
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")

@@ -145,6 +145,25 @@ def roughplastic_cases(td):
     li_case(td, "roughplastic", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, materials=S.ROUGH_PLASTICS))
 
 
+def analytic_lights_cases(td):
+    """Area lights on analytic spheres / disks (src/shapes/sphere.cpp:286-385, disk.cpp:247-259 under AreaLight): pointwise
+    Scene::sampleEmitterDirect / pdfEmitterDirect from points outside and inside the spheres, and a per-sample render."""
+    sd = S.analytic_lights_scene()
+    xml = sd.to_xml(td, "alights")
+    rng = np.random.default_rng(16)
+    n = 2048
+    inp = np.zeros((n, 8), np.float32)
+    inp[:, 0:3] = rng.uniform([-2.5, 0, -2], [2.5, 3.0, 2], (n, 3))
+    nrm = rand_dirs(rng, n, 0.5)
+    nrm[: n // 4] = 0
+    inp[:, 3:6] = nrm
+    inp[:, 6:8] = rng.random((n, 2), dtype=np.float32)
+    out = run_util("emitter", xml, inp, 12)
+    np.savez_compressed(os.path.join(GOLD, "emitter_analytic.npz"), inp=inp, out=out)
+    print("emitter_analytic:", inp.shape, "nonzero frac", (out[:, 0:3].sum(1) > 0).mean())
+    li_case(td, "analytic_lights", S.analytic_lights_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=59))
+
+
 def all_case(td):
     """Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-792; oracle/raydump.cpp `all`): the kd-tree shapes plus the special
     shapes of Scene::initializeBidirectional — here the aperture disk of the thinlens sensor and the bounding sphere of the
@@ -194,6 +213,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "analytic_lights":  # round 2
+        with tempfile.TemporaryDirectory() as td:
+            analytic_lights_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "all":              # rayIntersectAll (round 2)
         with tempfile.TemporaryDirectory() as td:
             all_case(td)
@@ -230,3 +253,4 @@ if __name__ == "__main__":
         fog_cases(td)
         roughplastic_cases(td)
         all_case(td)
+        analytic_lights_cases(td)

@@ -59,13 +59,16 @@ def test_roughplastic_pointwise_matches_reference_plugin(pkg, ctx, golden):
     _bsdf_pointwise(pkg, ctx, golden("bsdf_roughplastic.npz"), pkg.scenes.ROUGH_PLASTICS)
 
 
-def test_emitter_sampling_matches_reference(pkg, ctx, golden):
+@pytest.mark.parametrize("which", ["emitter", "emitter_analytic"])
+def test_emitter_sampling_matches_reference(pkg, ctx, golden, which):
     """mtsb_eval_emitter vs Scene::sampleEmitterDirect (no visibility) + pdfEmitterDirect over a point light, a constant
-    environment and a mesh area light — tests/golden/emitter.npz."""
+    environment and a mesh area light — tests/golden/emitter.npz; and over area lights on analytic shapes: a sphere seen
+    from outside (cone sampling), a sphere seen from inside, a disk (sphere.cpp:286-385, disk.cpp:247-259) —
+    emitter_analytic.npz."""
     S = pkg.scenes
-    g = golden("emitter.npz")
+    g = golden(which + ".npz")
     inp, ref = g["inp"], g["out"]
-    sc = S.materials_scene().upload(ctx)
+    sc = (S.materials_scene() if which == "emitter" else S.analytic_lights_scene()).upload(ctx)
     try:
         out = sc.eval_emitter(inp[:, 0:3], inp[:, 3:6], inp[:, 6:8])
         same_zero = (out[:, 0:3].sum(axis=1) == 0) == (ref[:, 0:3].sum(axis=1) == 0)
@@ -108,7 +111,7 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
-                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic"])
+                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -134,6 +137,9 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     elif name == "analytic":
         # analytic sphere / disk shapes (src/shapes/sphere.cpp, disk.cpp) through the path tracer
         sd = S.analytic_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+    elif name == "analytic_lights":
+        # area lights on analytic spheres (cone / uniform-sphere sampling, sphere.cpp:286-385) and a disk (disk.cpp:247-259)
+        sd = S.analytic_lights_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
     elif name == "roughplastic":
         S.MICROFACET_DIR = os.path.join(O.REF_DIR, "data", "microfacet")
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, materials=S.ROUGH_PLASTICS)
