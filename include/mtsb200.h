@@ -123,7 +123,8 @@ typedef struct mtsb_bsdf_desc {
 enum {
 	MTSB_EMITTER_AREA     = 0,  /* radiance; attached to shape `shape`            */
 	MTSB_EMITTER_POINT    = 1,  /* intensity; position pos                        */
-	MTSB_EMITTER_CONSTANT = 2   /* radiance; bounding sphere filled in at commit  */
+	MTSB_EMITTER_CONSTANT = 2,  /* radiance; bounding sphere filled in at commit  */
+	MTSB_EMITTER_ENVMAP   = 3   /* `envmap` (src/emitters/envmap.cpp): latitude-longitude radiance map, see mtsb_scene_set_envmap */
 };
 typedef struct mtsb_emitter_desc {
 	int32_t  type;
@@ -197,6 +198,18 @@ MTSB_API int  mtsb_scene_add_bsdf(mtsb_scene *scene, const mtsb_bsdf_desc *desc)
  * (src/bsdfs/rtrans.h:277-377) — n values over the warped angle cosTheta^(1/4) in [0, 1], evaluated on the device with
  * evalCubicInterp1D (src/libcore/spline.cpp:23-60).  The plugin builds it from the reference's own data/microfacet/{beckmann,ggx}.dat. */
 MTSB_API int  mtsb_scene_set_bsdf_table(mtsb_scene *scene, int bsdf, const float *table, size_t n);
+/* The image of an MTSB_EMITTER_ENVMAP emitter as the MIP pyramid the reference builds from it (envmap.cpp:152-178: RGB,
+ * 2-lobed Lanczos downsampling, repeat / clamp boundaries, half-precision texels): `levels` images, level l of sizes[2l] x
+ * sizes[2l+1] pixels, row-major RGB float triples.  The library derives the sampling tables of EnvironmentMap::configure
+ * (:276-333) from level 0.  scale = m_scale; to_world = the emitter's world transform (a rotation). */
+typedef struct mtsb_envmap_desc {
+	int32_t levels;
+	const int32_t *sizes;
+	const float *const *data;
+	float scale;
+	float to_world[16];
+} mtsb_envmap_desc;
+MTSB_API int  mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc *desc);
 MTSB_API int  mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc);    /* returns id >= 0 */
 /* TriMesh (include/mitsuba/render/trimesh.h): positions 3V, normals 3V or NULL, texcoords 2V or NULL,
  * triangles 3T uint32.  emitter = -1 if none.  Returns the shape index. */

@@ -25,7 +25,7 @@ BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSD
 BSDF_PASSTHROUGH = 7
 BSDF_ROUGHPLASTIC = 8
 BSDF_TWOSIDED_FLAG = 0x100
-EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT = 0, 1, 2
+EMITTER_AREA, EMITTER_POINT, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2, 3
 INTEGRATOR_PATH, INTEGRATOR_DIRECT, INTEGRATOR_VOLPATH_SIMPLE, INTEGRATOR_VOLPATH = 0, 1, 2, 3
 BUILDER_LBVH, BUILDER_PLOC = 0, 1
 
@@ -58,6 +58,11 @@ class MediumDesc(C.Structure):
     _fields_ = [("sigma_a", C.c_float * 3), ("sigma_s", C.c_float * 3), ("strategy", C.c_int32),
                 ("sampling_density", C.c_float), ("medium_sampling_weight", C.c_float), ("phase", C.c_int32),
                 ("g", C.c_float)]
+
+
+class EnvmapDesc(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("sizes", C.POINTER(C.c_int32)), ("data", C.POINTER(C.POINTER(C.c_float))),
+                ("scale", C.c_float), ("to_world", C.c_float * 16)]
 
 
 class Camera(C.Structure):
@@ -102,7 +107,7 @@ def lib():
         "mtsb_ctx_stream": (vp, [vp]),
         "mtsb_scene_create": (i32, [vp, C.POINTER(vp)]), "mtsb_scene_destroy": (None, [vp]),
         "mtsb_scene_add_bsdf": (i32, [vp, C.POINTER(BsdfDesc)]), "mtsb_scene_add_emitter": (i32, [vp, C.POINTER(EmitterDesc)]),
-        "mtsb_scene_set_bsdf_table": (i32, [vp, i32, vp, sz]),
+        "mtsb_scene_set_bsdf_table": (i32, [vp, i32, vp, sz]), "mtsb_scene_set_envmap": (i32, [vp, i32, C.POINTER(EnvmapDesc)]),
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
@@ -222,6 +227,18 @@ class Scene:
         """The rough-transmittance slice of a roughplastic BSDF (hostmath.rough_transmittance_slices)."""
         t = np.ascontiguousarray(table, dtype=np.float32)
         _check(lib().mtsb_scene_set_bsdf_table(self.h, int(bsdf), _ptr(t), t.shape[0]))
+
+    def set_envmap(self, emitter, pyramid, scale=1.0, to_world=None):
+        """The MIP pyramid of an EMITTER_ENVMAP emitter: list of [h, w, 3] float arrays, level 0 first (mtsb_scene_set_envmap)."""
+        levels = [np.ascontiguousarray(a, dtype=np.float32) for a in pyramid]
+        d = EnvmapDesc()
+        d.levels = len(levels)
+        sizes = (C.c_int32 * (2 * len(levels)))(*[v for a in levels for v in (a.shape[1], a.shape[0])])
+        ptrs = (C.POINTER(C.c_float) * len(levels))(*[a.ctypes.data_as(C.POINTER(C.c_float)) for a in levels])
+        d.sizes, d.data, d.scale = sizes, ptrs, float(scale)
+        M = np.eye(4, dtype=np.float32) if to_world is None else np.asarray(to_world, np.float32).reshape(4, 4)
+        d.to_world[:] = [float(x) for x in M.ravel()]
+        _check(lib().mtsb_scene_set_envmap(self.h, int(emitter), C.byref(d)))
 
     def add_emitter(self, type_, radiance=(1, 1, 1), pos=(0, 0, 0), sampling_weight=1.0):
         d = EmitterDesc()

@@ -10,6 +10,7 @@
 //   PointEmitter::{sampleDirect,pdfDirect}            src/emitters/point.cpp:133-153
 //   ConstantBackgroundEmitter::{sampleDirect,pdfDirect,fillDirectSamplingRecord}  src/emitters/constant.cpp:175-256
 #pragma once
+#include "envmap.cuh"
 
 namespace mtsb {
 
@@ -186,6 +187,17 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 		const float invDist = 1.0f / out.dist;
 		out.d = d * invDist; out.pdf = 1; out.measure = M_DISCRETE; out.p = em.pos;
 		return em.radiance * (invDist * invDist);
+	} else if (em.type == MTSB_EMITTER_ENVMAP) {                 // EnvironmentMap::sampleDirect (envmap.cpp:525-553)
+		const EnvmapDev &E = *envmap_of(em);
+		V3 value, dl; float pdf;
+		envmap_sample_direction(E, sx, sy, dl, value, pdf);
+		const V3 d = mat3_mul(E.toWorld, dl);
+		float nearT, farT;
+		if (is_zero(value) || pdf == 0 || !sphere_intersect(em.sphereCenter, em.sphereRadius, ref, d, nearT, farT) || nearT >= 0 || farT <= 0) return v3(0.0f);
+		const V3 p = ref + d * farT;
+		out.n = normalize(em.sphereCenter - p);
+		out.d = d; out.dist = farT; out.pdf = pdf; out.p = p;
+		return value / pdf;
 	} else {
 		V3 d; float pdf;
 		if (!is_zero(refN)) {
@@ -232,6 +244,12 @@ __device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const 
 		return 0.0f;
 	} else if (em.type == MTSB_EMITTER_POINT) {
 		return measure == M_DISCRETE ? 1.0f : 0.0f;
+	} else if (em.type == MTSB_EMITTER_ENVMAP) {                 // EnvironmentMap::pdfDirect (envmap.cpp:555-565)
+		const EnvmapDev &E = *envmap_of(em);
+		const float pdfSA = envmap_pdf_direction(E, mat3_mul(E.toLocal, d));
+		if (measure == M_SOLID_ANGLE) return pdfSA;
+		if (measure == M_AREA) return pdfSA * fabsf(dot(d, n)) / (dist * dist);
+		return 0.0f;
 	} else {
 		const float pdfSA = !is_zero(refN) ? MTS_INV_PI * fmaxf(0.0f, dot(d, refN)) : 1.0f / (4.0f * MTS_PI);
 		if (measure == M_SOLID_ANGLE) return pdfSA;
@@ -250,6 +268,19 @@ __device__ inline V3 scene_sample_emitter_direct(const SceneDev &S, const V3 &re
 	V3 value = emitter_sample_direct(S, index, ref, refN, sx, sy, out);
 	if (out.pdf != 0) { out.pdf *= emPdf; return value / emPdf; }
 	return v3(0.0f);
+}
+
+// Scene::evalEnvironment(ray) for the scene's environment emitter (S.envEmitter >= 0): constant.cpp:211-213 / envmap.cpp:383-414.
+// rx, ry: the differential directions of a sensor ray (hasDifferentials); kept out of line — the EWA lookup is large and rare.
+static __device__ __noinline__ V3 envmap_radiance(const EmitterRec *env, float dx, float dy, float dz, bool hasDifferentials,
+		float rxx, float rxy, float rxz, float ryx, float ryy, float ryz) {
+	return envmap_eval(*envmap_of(*env), v3(dx, dy, dz), hasDifferentials, v3(rxx, rxy, rxz), v3(ryx, ryy, ryz));
+}
+template <bool LEAN = false>
+__device__ __forceinline__ V3 env_radiance(const SceneDev &S, const V3 &d, bool hasDifferentials = false, const V3 &rx = V3(), const V3 &ry = V3()) {
+	const EmitterRec &env = S.emitters[S.envEmitter];
+	if (!LEAN && env.type == MTSB_EMITTER_ENVMAP) return envmap_radiance(&env, d.x, d.y, d.z, hasDifferentials, rx.x, rx.y, rx.z, ry.x, ry.y, ry.z);
+	return env.radiance;
 }
 
 // Emitter::eval(its, d) for an area light hit from direction -d (area.cpp:106-111)

@@ -54,6 +54,7 @@ struct GenParams {
 	uint32_t tilesX, pixPadded;
 	uint32_t sppBegin, sppStride, sppPhase, seed;
 	const uint32_t *samples;   // explicit {px,py,sampleIndex,0} list (mtsb_render_samples) or NULL
+	float diffScale;           // > 0: the scene looks ray differentials up (an `envmap` seen by sensor rays): 1 / sqrt(spp), integrator.cpp:145-146
 };
 
 __global__ void __launch_bounds__(RENDER_BLOCK)
@@ -111,10 +112,29 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	}
 	const float invZ = 1.0f / d.z;
 	const V3 dw = xform_vector(cam.c2w, d);
+	float4 prev0 = make_float4(0, 0, 0, 0);
+	if (g.diffScale > 0) {
+		// sampleRayDifferential (perspective.cpp:271-298, thinlens.cpp:325-360) + RayDifferential::scaleDifferential (ray.h:163-168):
+		// the directions through the neighbouring pixels, kept in `prev` / `L` until the first shade of the path reads them
+		const V3 p0 = xform_projective_point(cam.s2c, v3(0.0f, 0.0f, 0.0f));
+		const V3 dxv = xform_projective_point(cam.s2c, v3(cam.invResX, 0.0f, 0.0f)) - p0, dyv = xform_projective_point(cam.s2c, v3(0.0f, cam.invResY, 0.0f)) - p0;
+		V3 rx, ry;
+		if (cam.apertureRadius > 0) {
+			float a1, a2; SamplerState r2 = rs; r2.dim -= 2; next2D(r2, a1, a2);       // the aperture sample drawn above
+			float ax, ay; square_to_disk_concentric(a1, a2, ax, ay);
+			const V3 apertureP = v3(ax * cam.apertureRadius, ay * cam.apertureRadius, 0.0f);
+			const float fDist = cam.focusDistance / nearP.z;
+			rx = normalize((nearP + dxv) * fDist - apertureP); ry = normalize((nearP + dyv) * fDist - apertureP);
+		} else { rx = normalize(nearP + dxv); ry = normalize(nearP + dyv); }
+		rx = xform_vector(cam.c2w, rx); ry = xform_vector(cam.c2w, ry);
+		rx = dw + (rx - dw) * g.diffScale; ry = dw + (ry - dw) * g.diffScale;
+		prev0 = make_float4(rx.x, rx.y, rx.z, 0.0f);
+		ps.L[j] = make_float4(ry.x, ry.y, ry.z, 0.0f);
+	}
 	ps.rayO[j] = make_float4(o.x, o.y, o.z, cam.nearClip * invZ);
 	ps.rayD[j] = make_float4(dw.x, dw.y, dw.z, cam.farClip * invZ);
 	ps.thr[j] = make_float4(1, 1, 1, 1);
-	ps.prev[j] = make_float4(0, 0, 0, 0);
+	ps.prev[j] = prev0;
 	ps.misc[j] = make_float4(sx, sy, 0.0f, 0.0f);
 	ps.rng[j] = make_uint4(px, py, sidx, PATH_PACK(rs.dim, 0u, 1u));              // flags = 0, depth = 1; L is started by the first shade
 	queue[pos] = j;

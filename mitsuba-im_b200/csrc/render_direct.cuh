@@ -49,7 +49,11 @@ direct_head_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed,
 		V3 Li = v3(0.0f);
 		float alpha = 0.0f;
 		if (hitSlot == INVALID_SLOT) {                       // :159-166
-			if (!integ.hideEmitters && S.envEmitter >= 0) Li = S.emitters[S.envEmitter].radiance;
+			if (!integ.hideEmitters && S.envEmitter >= 0) {
+				V3 rx = v3(0.0f), ry = v3(0.0f);             // the sensor ray's differentials (generate_kernel: prev / L)
+				if (S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 a = ps.prev[slot], l = ps.L[slot]; rx = v3(a.x, a.y, a.z); ry = v3(l.x, l.y, l.z); }
+				Li = env_radiance(S, d, true, rx, ry);
+			}
 		} else {
 			alpha = 1.0f;
 			Surf sf; fill_surface(S, hitSlot, h.x, h.y, h.z, o, d, sf);
@@ -125,7 +129,7 @@ direct_tail_kernel(SceneDev S, PathState ps, IntegratorDev integ, DirectFan fan)
 		} else {
 			if (S.envEmitter < 0) continue;
 			const EmitterRec &env = S.emitters[S.envEmitter];
-			value = env.radiance;
+			value = env_radiance(S, d);
 			float nearT, farT;                            // fillDirectSamplingRecord (constant.cpp:238-256)
 			if (!sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) || nearT > 0 || farT < 0) continue;
 			if (!(flags & PF_DELTA)) {

@@ -341,7 +341,7 @@ int mtsb_render_clear(mtsb_render *r) {
 
 int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uint32_t spp_total, const int32_t rect[4],
 		uint32_t sample_stride, uint32_t sample_phase) {
-	(void) spp_total;   // only scales ray differentials in the reference (integrator.cpp:145-146); constant textures ignore them
+	// spp_total only scales ray differentials in the reference (integrator.cpp:145-146); an `envmap` seen by sensor rays reads them
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_pass: NULL argument");
 	if (sample_stride == 0 || sample_phase >= sample_stride) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_pass: bad sample stride/phase");
 	if (spp_count == 0) return 0;
@@ -356,6 +356,7 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	g.pixPadded = g.tilesX * ((g.h + 3) / 4) * 32;
 	g.sppBegin = spp_begin; g.sppStride = sample_stride; g.sppPhase = sample_phase; g.seed = r->seed;
 	g.samples = nullptr;
+	g.diffScale = r->scene->envmapEmitter >= 0 ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	const unsigned long long total = (unsigned long long) g.pixPadded * spp_count;
 	// chunks hold whole sample planes when possible so that a warp covers an 8x4 pixel tile of one sample index
 	size_t chunk = std::min<unsigned long long>(total, max_paths(r));
@@ -503,7 +504,6 @@ int mtsb_render_samples(mtsb_render *r, const uint32_t *samples, size_t n, uint3
 }
 
 int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, uint32_t spp_total, float *out, float *pos_out) {
-	(void) spp_total;
 	if (!r || !samples || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_samples: NULL argument");
 	if (n == 0) return 0;
 	if (n > MAX_PATHS_IN_FLIGHT) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_samples: at most %zu samples per call", MAX_PATHS_IN_FLIGHT);
@@ -515,6 +515,7 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	if (pos_out) MTSB_CHECK(dP.alloc(n * 2));
 	GenParams g; memset(&g, 0, sizeof(g));
 	g.count = (uint32_t) n; g.samples = dS.ptr; g.seed = r->seed; g.pixPadded = 1; g.tilesX = 1; g.sppStride = 1;
+	g.diffScale = r->scene->envmapEmitter >= 0 ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	MTSB_CHECK(run_chunk(r, g, dO.ptr, pos_out ? dP.ptr : nullptr));
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	if (pos_out) MTSB_CUDA(cudaMemcpyAsync(pos_out, dP.ptr, n * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));

@@ -57,7 +57,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 			if (integ.hideEmitters && !(flags & PF_SCATTERED)) alive = false;
 			else {
 				const EmitterRec &env = S.emitters[S.envEmitter];
-				value = env.radiance;
+				value = env_radiance<LEAN>(S, d);
 				float nearT, farT;       // fillDirectSamplingRecord (constant.cpp:238-256)
 				if (!sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) || nearT > 0 || farT < 0) alive = false;
 				else {
@@ -83,7 +83,12 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 		// ---- first iteration: the sensor ray (:129-150)
 		first = true; alpha = valid ? 1.0f : 0.0f;      // RadianceQueryRecord::rayIntersect sets alpha
 		if (!valid) {
-			if (!integ.hideEmitters && S.envEmitter >= 0) Li += thr * S.emitters[S.envEmitter].radiance;
+			if (!integ.hideEmitters && S.envEmitter >= 0) {
+				// the sensor ray carries differentials (generate_kernel left them in prev / L): a filtered lookup for an `envmap`
+				V3 rx = v3(0.0f), ry = v3(0.0f);
+				if (!LEAN && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
+				Li += thr * env_radiance<LEAN>(S, d, true, rx, ry);
+			}
 			alive = false;
 		} else if (emitterId >= 0 && !integ.hideEmitters) {
 			Li += thr * area_emitter_eval(S, emitterId, sf.ns, -d);

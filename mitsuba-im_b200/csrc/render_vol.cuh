@@ -207,7 +207,9 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 		if (medium >= 0) thr *= ms.transmittance / ms.pdfFailure;
 		if (!valid) {
 			if ((vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)) && S.envEmitter >= 0) {
-				V3 value = thr * S.emitters[S.envEmitter].radiance;
+				V3 rx = v3(0.0f), ry = v3(0.0f);           // only the sensor ray carries differentials (generate_kernel: prev / L)
+				if (first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
+				V3 value = thr * env_radiance(S, d, first, rx, ry);
 				// rRec.medium->evalTransmittance(ray): the ray's own [mint, maxt] = an infinite segment
 				if (medium >= 0) value *= medium_transmittance(S.media[medium], INFINITY);
 				Li += value;
@@ -359,7 +361,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 				const EmitterRec &env = S.emitters[S.envEmitter];
 				float nearT, farT;                                  // fillDirectSamplingRecord (constant.cpp:238-256)
 				if (sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
-					const V3 value = T0 * env.radiance;
+					const V3 value = T0 * env_radiance(S, d);
 					if (!is_zero(value)) {
 						const V3 n = normalize(env.sphereCenter - (o + d * farT));
 						const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
@@ -421,7 +423,9 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 			if (medium >= 0) thr *= ms.transmittance / ms.pdfFailure;
 			if (!valid) {
 				if ((vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)) && S.envEmitter >= 0) {
-					V3 value = thr * S.emitters[S.envEmitter].radiance;
+					V3 rx = v3(0.0f), ry = v3(0.0f);           // only the sensor ray carries differentials (generate_kernel: prev / L)
+					if (first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
+					V3 value = thr * env_radiance(S, d, first, rx, ry);
 					if (medium >= 0) value *= medium_transmittance(S.media[medium], INFINITY);
 					Li += value;
 				}
@@ -644,7 +648,7 @@ connect_vol_kernel(SceneDev S, PathState ps) {
 						const EmitterRec &env = S.emitters[S.envEmitter];
 						float nearT, farT;
 						if (sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
-							value = T * env.radiance;
+							value = T * env_radiance(S, d);
 							const V3 n = normalize(env.sphereCenter - (o + d * farT));
 							if (!delta) emitterPdf = emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
 						}

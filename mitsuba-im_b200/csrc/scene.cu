@@ -5,6 +5,7 @@
 // in the order shapes are added (that order defines shape indices and the global primitive index, as
 // m_shapeMap does), uploaded once, and every derived structure is built on the device.
 #include "scene.cuh"
+#include "envmap.cuh"
 #include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
@@ -157,7 +158,7 @@ int mtsb_scene_set_bsdf_table(mtsb_scene *scene, int bsdf, const float *table, s
 int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
 	if (!scene || !desc) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_emitter: NULL argument");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_emitter: scene already committed");
-	if (desc->type < MTSB_EMITTER_AREA || desc->type > MTSB_EMITTER_CONSTANT)
+	if (desc->type < MTSB_EMITTER_AREA || desc->type > MTSB_EMITTER_ENVMAP)
 		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_emitter: emitter type %d is outside the GPU subset", desc->type);
 	EmitterRec r; memset(&r, 0, sizeof(r));
 	r.type = desc->type; r.shape = desc->shape;
@@ -167,6 +168,66 @@ int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
 	scene->emitters.push_back(r);
 	scene->emitterWeights.push_back(desc->sampling_weight);
 	return (int) scene->emitters.size() - 1;
+}
+
+// EnvironmentMap::configure (src/emitters/envmap.cpp:276-333) restated: marginal / conditional CDFs over luminance x sin(theta)
+int mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc *desc) {
+	if (!scene || !desc || !desc->sizes || !desc->data) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: scene already committed");
+	if (emitter < 0 || emitter >= (int) scene->emitters.size() || scene->emitters[emitter].type != MTSB_EMITTER_ENVMAP)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: emitter %d is not an MTSB_EMITTER_ENVMAP", emitter);
+	if (scene->envmapEmitter >= 0 && scene->envmapEmitter != emitter) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_set_envmap: one environment map per scene");
+	if (desc->levels < 1 || desc->levels > MTSB_ENVMAP_MAX_LEVELS) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: %d levels", desc->levels);
+	EnvmapDev E; memset(&E, 0, sizeof(E));
+	E.levels = desc->levels;
+	scene->envData.clear();
+	for (int l = 0; l < desc->levels; ++l) {
+		const int w = desc->sizes[2 * l], h = desc->sizes[2 * l + 1];
+		if (w < 1 || h < 1 || w > 0xFFFF || h > 0xFFFF || !desc->data[l]) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: level %d is %dx%d", l, w, h);
+		E.w[l] = w; E.h[l] = h; E.offset[l] = (unsigned) (scene->envData.size() / 3);
+		E.ratioX[l] = (float) w / (float) desc->sizes[0]; E.ratioY[l] = (float) h / (float) desc->sizes[1];     // mipmap.h:243, 265-267
+		scene->envData.insert(scene->envData.end(), desc->data[l], desc->data[l] + (size_t) w * h * 3);
+	}
+	const int W = E.w[0], H = E.h[0];
+	const float *img = scene->envData.data();
+	scene->envCdfCols.assign((size_t) (W + 1) * H, 0.0f); scene->envCdfRows.assign(H + 1, 0.0f); scene->envRowWeights.assign(H, 0.0f);
+	size_t colPos = 0, rowPos = 0;
+	float rowSum = 0.0f;
+	scene->envCdfRows[rowPos++] = 0;
+	for (int y = 0; y < H; ++y) {
+		float colSum = 0;
+		scene->envCdfCols[colPos++] = 0;
+		for (int x = 0; x < W; ++x) {
+			const float *p = img + ((size_t) y * W + x) * 3;
+			colSum += 0.212671f * p[0] + 0.715160f * p[1] + 0.072169f * p[2];      // Spectrum::getLuminance (RGB build)
+			scene->envCdfCols[colPos++] = colSum;
+		}
+		const float normalization = 1.0f / colSum;
+		for (int x = 1; x < W; ++x) scene->envCdfCols[colPos - x - 1] *= normalization;
+		scene->envCdfCols[colPos - 1] = 1.0f;
+		const float weight = sinf((y + 0.5f) * ENVMAP_PI / H);
+		scene->envRowWeights[y] = weight;
+		rowSum += colSum * weight;
+		scene->envCdfRows[rowPos++] = rowSum;
+	}
+	const float normalization = 1.0f / rowSum;
+	for (int y = 1; y < H; ++y) scene->envCdfRows[rowPos - y - 1] *= normalization;
+	scene->envCdfRows[rowPos - 1] = 1.0f;
+	if (rowSum == 0) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: the environment map is completely black -- this is not allowed.");
+	if (!std::isfinite(rowSum)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: the environment map contains an invalid floating point value (nan/inf)");
+	E.normalization = 1.0f / (rowSum * (2 * ENVMAP_PI / W) * (ENVMAP_PI / H));
+	E.pixelSizeX = 2 * ENVMAP_PI / W; E.pixelSizeY = ENVMAP_PI / H;
+	E.scale = desc->scale;
+	float inv[12];
+	invert_affine(desc->to_world, inv);
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { E.toWorld[r * 3 + c] = desc->to_world[r * 4 + c]; E.toLocal[r * 3 + c] = inv[r * 4 + c]; }
+	for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) {                           // mipmap.h:297-303 (math::fastexp via double)
+		const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1);
+		E.lut[i] = (float) exp((double) (-2.0f * r2)) - (float) exp((double) -2.0f);
+	}
+	scene->envRecord.assign((const unsigned char *) &E, (const unsigned char *) &E + sizeof(E));
+	scene->envmapEmitter = emitter;
+	return 0;
 }
 
 static int check_refs(mtsb_scene *scene, int bsdf, int emitter, const char *who) {
@@ -396,7 +457,7 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	int envEmitter = -1;
 	for (size_t i = 0; i < scene->emitters.size(); ++i) {
 		EmitterRec &e = scene->emitters[i];
-		if (e.type == MTSB_EMITTER_CONSTANT) envEmitter = (int) i;
+		if (e.type == MTSB_EMITTER_CONSTANT || e.type == MTSB_EMITTER_ENVMAP) envEmitter = (int) i;
 		if (e.type == MTSB_EMITTER_AREA) {
 			if (e.shape >= scene->shapes.size() || scene->shapes[e.shape].emitter != (int) i)
 				MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: area emitter %zu is not attached to a shape", i);
@@ -458,7 +519,7 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	// AABB::getBSphere = centre + distance to max corner)
 	for (size_t i = 0; i < scene->emitters.size(); ++i) {
 		EmitterRec &e = scene->emitters[i];
-		if (e.type != MTSB_EMITTER_CONSTANT) continue;
+		if (e.type != MTSB_EMITTER_CONSTANT && e.type != MTSB_EMITTER_ENVMAP) continue;
 		V3 lo = D.aabbMin, hi = D.aabbMax;
 		if (scene->hasExtra) {
 			lo = vmin3(lo, v3(scene->extraMin[0], scene->extraMin[1], scene->extraMin[2]));
@@ -483,12 +544,26 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 		const V3 c = 0.5f * (lo + hi), hd = hi - c;
 		D.sceneDiameter = 2.0f * sqrtf(dot(hd, hd));
 	}
+	// the environment map: tables to the device, their addresses into the EnvmapDev record, its address into the emitter
+	for (size_t i = 0; i < scene->emitters.size(); ++i) {
+		if (scene->emitters[i].type != MTSB_EMITTER_ENVMAP) continue;
+		if ((int) i != scene->envmapEmitter) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: envmap emitter %zu has no image (mtsb_scene_set_envmap)", i);
+		MTSB_CHECK(scene->dEnvData.upload(scene->envData, st));
+		MTSB_CHECK(scene->dEnvCdfRows.upload(scene->envCdfRows, st));
+		MTSB_CHECK(scene->dEnvCdfCols.upload(scene->envCdfCols, st));
+		MTSB_CHECK(scene->dEnvRowWeights.upload(scene->envRowWeights, st));
+		EnvmapDev *E = (EnvmapDev *) scene->envRecord.data();
+		E->data = scene->dEnvData.ptr; E->cdfRows = scene->dEnvCdfRows.ptr; E->cdfCols = scene->dEnvCdfCols.ptr; E->rowWeights = scene->dEnvRowWeights.ptr;
+		MTSB_CHECK(scene->dEnvmap.upload(scene->envRecord, st));
+		const unsigned char *dev = scene->dEnvmap.ptr;
+		memcpy(&scene->emitters[i].pos.x, &dev, sizeof(dev));
+	}
 	MTSB_CHECK(scene->dMedia.upload(scene->media, st));
 	D.media = scene->dMedia.ptr;
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));
-	scene->lean = !(ctx->shadeLean == 0);
+	scene->lean = !(ctx->shadeLean == 0) && scene->envmapEmitter < 0;
 	for (const BsdfRec &b : scene->bsdfs) {
 		const int t = b.type & 0xff;
 		const bool ok = t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_NULL || t == MTSB_BSDF_DIELECTRIC ||

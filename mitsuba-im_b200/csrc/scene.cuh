@@ -24,6 +24,12 @@ struct mtsb_scene {
 	std::vector<mtsb::RectRec> specialRecs; std::vector<uint32_t> specialTypes;
 	mtsb::DevBuf<mtsb::RectRec> dSpecialRecs; mtsb::DevBuf<uint32_t> dSpecialTypes;
 	size_t specialUploaded = (size_t) -1;          // number of caller-added specials the device copy was made for
+	// `envmap` emitter (at most one): pyramid + sampling tables, and the device record that refers to them (envmap.cuh)
+	int envmapEmitter = -1;
+	std::vector<float> envData, envCdfRows, envCdfCols, envRowWeights;
+	mtsb::DevBuf<float> dEnvData, dEnvCdfRows, dEnvCdfCols, dEnvRowWeights;
+	mtsb::DevBuf<unsigned char> dEnvmap;           // one EnvmapDev
+	std::vector<unsigned char> envRecord;          // host copy of the EnvmapDev (pointers patched at commit)
 	std::vector<mtsb::EmitterRec> emitters;
 	std::vector<mtsb::MediumRec> media;
 	std::vector<float> emitterWeights;

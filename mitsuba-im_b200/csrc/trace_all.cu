@@ -45,7 +45,7 @@ static int upload_specials(mtsb_scene *scene, cudaStream_t st, uint32_t *countOu
 	const size_t nUser = scene->specialRecs.size();
 	std::vector<RectRec> recs(scene->specialRecs); std::vector<uint32_t> types(scene->specialTypes);
 	for (const EmitterRec &e : scene->emitters) {
-		if (e.type != MTSB_EMITTER_CONSTANT) continue;
+		if (e.type != MTSB_EMITTER_CONSTANT && e.type != MTSB_EMITTER_ENVMAP) continue;
 		RectRec rr; memset(&rr, 0, sizeof(rr));
 		rr.dpdu = e.sphereCenter; rr.dpdv = v3(e.sphereRadius, 0.0f, 0.0f); rr.pad[0] = 1u;      // constant.cpp:82-91: a flipped sphere
 		recs.push_back(rr); types.push_back(SHAPE_SPHERE);

@@ -107,6 +107,30 @@ def write_ply(path, V, N, F, UV=None):
 
 
 # ------------------------------------------------------------------------------------------------ transforms
+def write_pfm(path, img):
+    """Little-endian colour PFM, rows bottom-up (what the reference's Bitmap reads natively)."""
+    img = np.asarray(img, np.float32)
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (img.shape[1], img.shape[0]))
+        f.write(np.ascontiguousarray(img[::-1]).astype("<f4").tobytes())
+
+
+def sky_image(width=64, height=32, seed=3):
+    """A synthetic latitude-longitude radiance map: horizon gradient, a bright warm sun, a dim cool second light, mild noise."""
+    v, u = np.meshgrid((np.arange(height) + 0.5) / height, (np.arange(width) + 0.5) / width, indexing="ij")
+    theta, phi = v * math.pi, u * 2 * math.pi
+    d = np.stack([np.sin(phi) * np.sin(theta), np.cos(theta), -np.cos(phi) * np.sin(theta)], axis=-1)
+    img = np.empty((height, width, 3), np.float32)
+    up = np.clip(d[..., 1], -1, 1)
+    img[...] = (0.25 + 0.35 * np.clip(up, 0, 1))[..., None] * np.array([0.55, 0.7, 1.0]) + (0.12 * np.clip(-up, 0, 1))[..., None] * np.array([0.5, 0.4, 0.3])
+    for c, w, col in (((0.45, 0.75, -0.48), 40.0, (30.0, 24.0, 15.0)), ((-0.7, 0.35, 0.62), 12.0, (1.5, 2.5, 4.0))):
+        c = np.asarray(c) / np.linalg.norm(c)
+        img += (np.exp(w * ((d * c).sum(axis=-1) - 1.0)))[..., None] * np.array(col, np.float32)
+    rng = np.random.default_rng(seed)
+    img *= (1.0 + 0.05 * rng.standard_normal((height, width, 1))).astype(np.float32)
+    return np.maximum(img, 1e-3).astype(np.float32)
+
+
 def translate(x, y, z):
     M = np.eye(4)
     M[:3, 3] = [x, y, z]
@@ -269,6 +293,13 @@ class SceneDesc:
     def add_constant_env(self, radiance):
         self.emitters.append(dict(type="constant", radiance=tuple(radiance)))
 
+    def add_envmap(self, image, scale=1.0, to_world=None, pyramid=None):
+        """`envmap` emitter (src/emitters/envmap.cpp) from a latitude-longitude float RGB image [H, W, 3].  `pyramid` = the MIP
+        levels the reference builds from it (list of [h, w, 3] arrays: half-precision values, Lanczos-downsampled,
+        envmap.cpp:152-178) — hosts of the C ABI pass them on; the Mitsuba plugin builds them with the reference's own MIPMap."""
+        self.emitters.append(dict(type="envmap", image=np.asarray(image, np.float32), scale=float(scale),
+                                  to_world=np.eye(4) if to_world is None else np.asarray(to_world, np.float64), pyramid=pyramid))
+
     def set_sensor(self, to_world, fov, width, height, rfilter="box", spp=4, seed=0, sampler="independent", fov_axis="x",
                    aperture_radius=0.0, focus_distance=1.0):
         """aperture_radius > 0 selects the `thinlens` sensor (src/sensors/thinlens.cpp), else `perspective`."""
@@ -352,6 +383,11 @@ class SceneDesc:
         for e in self.emitters:
             if e["type"] == "point":
                 sc.add_emitter(B.EMITTER_POINT, radiance=e["intensity"], pos=e["pos"])
+            elif e["type"] == "envmap":
+                if e["pyramid"] is None:
+                    raise ValueError("envmap: pass the MIP pyramid (SceneDesc.add_envmap(..., pyramid=...))")
+                eid = sc.add_emitter(B.EMITTER_ENVMAP, radiance=(0, 0, 0))
+                sc.set_envmap(eid, e["pyramid"], e["scale"], e["to_world"])
             else:
                 sc.add_emitter(B.EMITTER_CONSTANT, radiance=e["radiance"])
         for m in self.media:
@@ -504,6 +540,11 @@ class SceneDesc:
             if e["type"] == "point":
                 out.append('<emitter type="point"><point name="position" x="%r" y="%r" z="%r"/><rgb name="intensity" value="%s"/></emitter>' % (
                     e["pos"][0], e["pos"][1], e["pos"][2], ", ".join(repr(float(x)) for x in e["intensity"])))
+            elif e["type"] == "envmap":
+                fn = "%s_envmap.pfm" % name
+                write_pfm(os.path.join(directory, fn), e["image"])
+                out.append('<emitter type="envmap"><string name="filename" value="%s"/><float name="scale" value="%r"/><boolean name="cache" value="false"/>'
+                           '<transform name="toWorld">%s</transform></emitter>' % (fn, e["scale"], _mat_xml(e["to_world"])))
             else:
                 out.append('<emitter type="constant"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in e["radiance"]))
         for i, s in enumerate(self.shapes):
@@ -737,6 +778,28 @@ def analytic_lights_scene(width=48, height=32, spp=4, max_depth=6, sampler="inde
     sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
     sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
     sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd
+
+
+def envmap_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent", seed=0, pyramid=None, kind="path"):
+    """`envmap` emitter: the synthetic sky of sky_image() rotated about two axes and scaled, as the only light beside a
+    small mesh light; diffuse, glass, GGX and plastic spheres on a floor; the camera sees the sky directly (filtered lookups of
+    sensor rays, envmap.cpp:395-409) and through the glass ball."""
+    sd = SceneDesc()
+    sd.add_envmap(sky_image(), scale=1.3, to_world=rotate((0, 1, 0), 35) @ rotate((1, 0, 0), 20), pyramid=pyramid)
+    mats = [dict(type="diffuse", reflectance=(0.6, 0.5, 0.4)), dict(type="dielectric"), dict(type="roughconductor", distribution="ggx", alpha=0.15),
+            dict(type="plastic", diffuse_reflectance=(0.2, 0.3, 0.6))]
+    for i, m in enumerate(mats):
+        V, N, F = displaced_sphere(2, seed=70 + i, radius=0.45, center=(i - 1.5, 0.5, 0.2 * (i % 2)))
+        sd.add_mesh(V, N, F, bsdf=m)
+    g = 3.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
+    lV, lN, lF = displaced_sphere(1, seed=99, radius=0.2, center=(0.5, 2.2, 0.3), amplitude=0.0)
+    sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(12, 10, 8))
+    sd.set_sensor(look_at((0.3, 1.6, -4.5), (0, 0.9, 0), (0, 1, 0)), 50.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator(kind, max_depth=max_depth, rr_depth=3)
     return sd
 
 

@@ -32,6 +32,9 @@
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/timer.h>
 #include <mitsuba/core/filesystem.h>
+#include <mitsuba/core/fstream.h>
+#include <mitsuba/core/bitmap.h>
+#include <mitsuba/render/mipmap.h>
 #include <thread>
 #include <vector>
 #include <chrono>
@@ -241,6 +244,39 @@ public:
 		return 0;
 	}
 
+	/// The MIP pyramid an `envmap` emitter builds from its image (src/emitters/envmap.cpp:152-178: RGB, half-precision storage,
+	/// 2-lobed Lanczos downsampling, repeat / clamp boundaries): floats {levels, then per level: width, height, w*h*3 values}
+	int mipmap(int argc, char **argv) {
+		if (argc < 4) { cout << "mipmap <image> <out>" << endl; return 1; }
+		typedef TSpectrum<half, SPECTRUM_SAMPLES> SpectrumHalf;
+		typedef TMIPMap<Spectrum, SpectrumHalf> MIPMap;
+		ref<FileStream> fs = new FileStream(fs::pathstr(argv[2]), FileStream::EReadOnly);
+		ref<Bitmap> bitmap = new Bitmap(Bitmap::EAuto, fs);
+		Properties rfilterProps("lanczos");
+		rfilterProps.setInteger("lobes", 2);
+		ref<ReconstructionFilter> rfilter = static_cast<ReconstructionFilter *>(PluginManager::getInstance()->createObject(
+			MTS_CLASS(ReconstructionFilter), rfilterProps));
+		rfilter->configure();
+		MIPMap *mip = new MIPMap(bitmap, Bitmap::ERGB, Bitmap::EFloat, rfilter, ReconstructionFilter::ERepeat, ReconstructionFilter::EClamp,
+			EEWA, 10.0f, fs::pathstr(), 0, std::numeric_limits<Float>::infinity(), Spectrum::EIlluminant);
+		std::vector<float> out;
+		out.push_back((float) mip->getLevels());
+		for (int l = 0; l < mip->getLevels(); ++l) {
+			const MIPMap::Array2DType &a = mip->getArray(l);
+			out.push_back((float) a.getSize().x); out.push_back((float) a.getSize().y);
+			for (int y = 0; y < a.getSize().y; ++y)
+				for (int x = 0; x < a.getSize().x; ++x) {
+					Spectrum v(a(x, y));
+					Float r, g, b; v.toLinearRGB(r, g, b);
+					out.push_back(r); out.push_back(g); out.push_back(b);
+				}
+		}
+		writeFloats(argv[3], out);
+		cout << "mipmap: " << mip->getLevels() << " levels from " << bitmap->getWidth() << "x" << bitmap->getHeight() << endl;
+		delete mip;
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -306,10 +342,11 @@ public:
 	}
 
 	int run(int argc, char **argv) {
-		if (argc < 2) { cout << "raydump trace|light|all|bsdf|emitter ..." << endl; return 1; }
+		if (argc < 2) { cout << "raydump trace|light|all|mipmap|bsdf|emitter ..." << endl; return 1; }
 		if (!strcmp(argv[1], "trace")) return trace(argc, argv);
 		if (!strcmp(argv[1], "light")) return light(argc, argv);
 		if (!strcmp(argv[1], "all")) return all(argc, argv);
+		if (!strcmp(argv[1], "mipmap")) return mipmap(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

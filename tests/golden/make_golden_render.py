@@ -164,6 +164,42 @@ def analytic_lights_cases(td):
     li_case(td, "analytic_lights", S.analytic_lights_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=59))
 
 
+def envmap_cases(td):
+    """`envmap` (src/emitters/envmap.cpp): the MIP pyramid the reference builds from scenes.sky_image() (oracle/raydump.cpp
+    `mipmap`), pointwise Scene::sampleEmitterDirect / pdfEmitterDirect, and per-sample renders through `path` and `direct` (the
+    camera sees the map directly: the EWA-filtered lookups of sensor rays, mipmap.h:630-716)."""
+    img = S.sky_image()
+    S.write_pfm(os.path.join(td, "sky.pfm"), img)
+    mp = os.path.join(td, "mip.bin")
+    r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "mipmap", os.path.join(td, "sky.pfm"), mp], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0 or not os.path.exists(mp):
+        raise RuntimeError(r.stdout[-3000:])
+    a = np.fromfile(mp, np.float32)
+    levels, off, pyr = int(a[0]), 1, {}
+    for l in range(levels):
+        w, h = int(a[off]), int(a[off + 1]); off += 2
+        pyr["level%d" % l] = a[off:off + w * h * 3].reshape(h, w, 3).astype(np.float16)      # the reference stores half precision
+        assert (pyr["level%d" % l].astype(np.float32) == a[off:off + w * h * 3].reshape(h, w, 3)).all()
+        off += w * h * 3
+    np.savez_compressed(os.path.join(GOLD, "envmap_pyramid.npz"), **pyr)
+    pyramid = [pyr["level%d" % l].astype(np.float32) for l in range(levels)]
+    sd = S.envmap_scene(pyramid=pyramid)
+    xml = sd.to_xml(td, "env")
+    rng = np.random.default_rng(21)
+    n = 2048
+    inp = np.zeros((n, 8), np.float32)
+    inp[:, 0:3] = rng.uniform([-2, 0, -1.5], [2, 1.5, 1.5], (n, 3))
+    nrm = rand_dirs(rng, n, 0.5)
+    nrm[: n // 4] = 0
+    inp[:, 3:6] = nrm
+    inp[:, 6:8] = rng.random((n, 2), dtype=np.float32)
+    out = run_util("emitter", xml, inp, 12)
+    np.savez_compressed(os.path.join(GOLD, "emitter_envmap.npz"), inp=inp, out=out)
+    print("emitter_envmap:", inp.shape, "nonzero frac", (out[:, 0:3].sum(1) > 0).mean(), "emitters", np.unique(out[:, 8]))
+    li_case(td, "envmap", S.envmap_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=67, pyramid=pyramid))
+    li_case(td, "envmap_direct", S.envmap_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=71, pyramid=pyramid, kind="direct"))
+
+
 def all_case(td):
     """Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-792; oracle/raydump.cpp `all`): the kd-tree shapes plus the special
     shapes of Scene::initializeBidirectional — here the aperture disk of the thinlens sensor and the bounding sphere of the
@@ -213,6 +249,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "envmap":           # round 2
+        with tempfile.TemporaryDirectory() as td:
+            envmap_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "analytic_lights":  # round 2
         with tempfile.TemporaryDirectory() as td:
             analytic_lights_cases(td)
@@ -254,3 +294,4 @@ if __name__ == "__main__":
         roughplastic_cases(td)
         all_case(td)
         analytic_lights_cases(td)
+        envmap_cases(td)

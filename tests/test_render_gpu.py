@@ -11,6 +11,12 @@ import oracle as O
 pytestmark = pytest.mark.gpu
 
 
+def _pyramid(golden):
+    """The MIP pyramid the reference builds from scenes.sky_image() (tests/golden/envmap_pyramid.npz, raydump `mipmap`)."""
+    g = golden("envmap_pyramid.npz")
+    return [g["level%d" % l].astype(np.float32) for l in range(len(g.files))]
+
+
 def _close(a, b, rtol, atol):
     return np.abs(a - b) <= atol + rtol * np.abs(b)
 
@@ -59,7 +65,7 @@ def test_roughplastic_pointwise_matches_reference_plugin(pkg, ctx, golden):
     _bsdf_pointwise(pkg, ctx, golden("bsdf_roughplastic.npz"), pkg.scenes.ROUGH_PLASTICS)
 
 
-@pytest.mark.parametrize("which", ["emitter", "emitter_analytic"])
+@pytest.mark.parametrize("which", ["emitter", "emitter_analytic", "emitter_envmap"])
 def test_emitter_sampling_matches_reference(pkg, ctx, golden, which):
     """mtsb_eval_emitter vs Scene::sampleEmitterDirect (no visibility) + pdfEmitterDirect over a point light, a constant
     environment and a mesh area light — tests/golden/emitter.npz; and over area lights on analytic shapes: a sphere seen
@@ -68,7 +74,9 @@ def test_emitter_sampling_matches_reference(pkg, ctx, golden, which):
     S = pkg.scenes
     g = golden(which + ".npz")
     inp, ref = g["inp"], g["out"]
-    sc = (S.materials_scene() if which == "emitter" else S.analytic_lights_scene()).upload(ctx)
+    # emitter_envmap.npz: EnvironmentMap::sampleDirect / pdfDirect (envmap.cpp:525-606) on a rotated, scaled map beside a mesh light
+    sd = S.materials_scene() if which == "emitter" else (S.analytic_lights_scene() if which == "emitter_analytic" else S.envmap_scene(pyramid=_pyramid(golden)))
+    sc = sd.upload(ctx)
     try:
         out = sc.eval_emitter(inp[:, 0:3], inp[:, 3:6], inp[:, 6:8])
         same_zero = (out[:, 0:3].sum(axis=1) == 0) == (ref[:, 0:3].sum(axis=1) == 0)
@@ -111,7 +119,8 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
-                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights"])
+                                  "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights",
+                                  "envmap", "envmap_direct"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -137,6 +146,11 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     elif name == "analytic":
         # analytic sphere / disk shapes (src/shapes/sphere.cpp, disk.cpp) through the path tracer
         sd = S.analytic_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
+    elif name in ("envmap", "envmap_direct"):
+        # `envmap` emitter: importance sampling, bilinear lookups for scattered rays, EWA-filtered lookups (ray differentials scaled
+        # by 1 / sqrt(spp)) where the camera sees the map directly — through `path` and through `direct`
+        sd = S.envmap_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramid=_pyramid(golden),
+                            kind="direct" if name == "envmap_direct" else "path")
     elif name == "analytic_lights":
         # area lights on analytic spheres (cone / uniform-sphere sampling, sphere.cpp:286-385) and a disk (disk.cpp:247-259)
         sd = S.analytic_lights_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
