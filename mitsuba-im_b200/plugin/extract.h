@@ -14,6 +14,9 @@
 #include <mitsuba/render/sampler.h>
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/plugin.h>
+#include <mitsuba/core/fstream.h>
+#include <mitsuba/core/bitmap.h>
+#include <mitsuba/render/mipmap.h>
 #include "microfacet.h"          /* src/bsdfs/microfacet.h: MicrofacetDistribution(props) reads alpha / distribution / sampleVisible */
 #include "rtrans.h"              /* src/bsdfs/rtrans.h: RoughTransmittance, header-only, as roughplastic.cpp includes it */
 #include "ior.h"                 /* src/bsdfs/ior.h: lookupIOR(), header-only, as the BSDF plugins include it */

@@ -58,6 +58,47 @@ static void describeMedium(const Medium *medium, mtsb_medium_desc &d) {
 	else SLog(EError, "gpupath: phase function \"%s\" is outside the GPU subset (isotropic, hg)", pcls.c_str());
 }
 
+/// The `envmap` emitter keeps its MIP map private, so the plugin loads the image again and builds the pyramid exactly as the
+/// emitter's constructor does (src/emitters/envmap.cpp:152-178), with the reference's own Bitmap / MIPMap classes: RGB,
+/// half-precision storage, 2-lobed Lanczos downsampling, repeat / clamp boundaries.
+static void uploadEnvmap(mtsb_scene *out, int id, const Emitter *e) {
+	typedef TSpectrum<half, SPECTRUM_SAMPLES> SpectrumHalf;
+	typedef TMIPMap<Spectrum, SpectrumHalf> MIPMap;
+	const Properties &props = e->getProperties();
+	if (!props.hasProperty("filename")) SLog(EError, "gpupath: envmap without a file name (raw bitmap data) is outside the GPU subset");
+	fs::pathstr filename = Thread::getThread()->getFileResolver()->resolve(fs::pathstr(props.getString("filename")));
+	ref<FileStream> stream = new FileStream(filename, FileStream::EReadOnly);
+	ref<Bitmap> bitmap = new Bitmap(Bitmap::EAuto, stream);
+	const Float gamma = props.getFloat("gamma", 0);
+	if (gamma != 0) bitmap->setGamma(gamma);
+	Properties rfilterProps("lanczos");
+	rfilterProps.setInteger("lobes", 2);
+	ref<ReconstructionFilter> rfilter = static_cast<ReconstructionFilter *>(PluginManager::getInstance()->createObject(
+		MTS_CLASS(ReconstructionFilter), rfilterProps));
+	rfilter->configure();
+	MIPMap *mip = new MIPMap(bitmap, Bitmap::ERGB, Bitmap::EFloat, rfilter, ReconstructionFilter::ERepeat, ReconstructionFilter::EClamp,
+		EEWA, 10.0f, fs::pathstr(), 0, std::numeric_limits<Float>::infinity(), Spectrum::EIlluminant);
+	const int levels = mip->getLevels();
+	std::vector<int32_t> sizes(2 * levels);
+	std::vector<std::vector<float> > data(levels);
+	std::vector<const float *> ptrs(levels);
+	for (int l = 0; l < levels; ++l) {
+		const MIPMap::Array2DType &a = mip->getArray(l);
+		sizes[2 * l] = a.getSize().x; sizes[2 * l + 1] = a.getSize().y;
+		data[l].resize((size_t) a.getSize().x * a.getSize().y * 3);
+		float *dst = data[l].data();
+		for (int y = 0; y < a.getSize().y; ++y)
+			for (int x = 0; x < a.getSize().x; ++x, dst += 3) toRGB(Spectrum(a(x, y)), dst);
+		ptrs[l] = data[l].data();
+	}
+	mtsb_envmap_desc ed; memset(&ed, 0, sizeof(ed));
+	ed.levels = levels; ed.sizes = sizes.data(); ed.data = ptrs.data();
+	ed.scale = (float) props.getFloat("scale", 1.0f);
+	matrixToArray(e->getWorldTransform()->eval(0).getMatrix(), ed.to_world);
+	MTSB_CALL(mtsb_scene_set_envmap(out, id, &ed));
+	delete mip;
+}
+
 /// Uploads shapes / BSDFs / emitters in Scene order and commits (BVH build on the device).
 static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 	mtsb_scene *out = NULL;
@@ -82,12 +123,15 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		} else if (cls == "ConstantBackgroundEmitter") {            // src/emitters/constant.cpp:44-52
 			d.type = MTSB_EMITTER_CONSTANT;
 			toRGB(props.getSpectrum("radiance", Spectrum::getD65()), d.radiance);
+		} else if (cls == "EnvironmentMap") {                       // src/emitters/envmap.cpp:98-185
+			d.type = MTSB_EMITTER_ENVMAP;
 		} else {
-			SLog(EError, "gpupath: emitter \"%s\" is outside the GPU subset (area, point, constant)", cls.c_str());
+			SLog(EError, "gpupath: emitter \"%s\" is outside the GPU subset (area, point, constant, envmap)", cls.c_str());
 		}
 		int id = mtsb_scene_add_emitter(out, &d);
 		if (id < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
 		emitterIds[e] = id;
+		if (d.type == MTSB_EMITTER_ENVMAP) uploadEnvmap(out, id, e);
 	}
 	const std::vector<const Medium *> media = collectMedia(scene);
 	for (size_t i = 0; i < media.size(); ++i) {

@@ -151,6 +151,20 @@ def test_roughplastic_through_the_loader(tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_envmap_through_the_loader(pkg, tmp_path):
+    """`envmap` instantiated by the stock XML loader from a PFM file: plugin/extract_scene.h rebuilds the MIP
+    pyramid with the reference's own Bitmap / MIPMap classes; the camera sees the map directly (EWA lookups of the sensor rays'
+    differentials) — per-pixel match with the stock `path` under the shared sampler, classic scheduler."""
+    sd = pkg.scenes.envmap_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=73)
+    xml = sd.to_xml(str(tmp_path), "env")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
 def test_volpath_simple_with_media_through_the_loader(pkg, tmp_path):
     """§8 f4 through the drop-in: overlay/plugins/volpath_simple.so replaces the stock SimpleVolumetricPathTracer for an
     unmodified scene file with homogeneous media (isotropic + HG), `null` and dielectric medium boundaries and a sensor
