@@ -209,6 +209,24 @@ typedef struct mtsb_envmap_desc {
 	float scale;
 	float to_world[16];
 } mtsb_envmap_desc;
+/* `bitmap` texture (src/textures/bitmap.cpp over Texture2D, src/librender/texture.cpp:112-121) as the MIP pyramid the reference
+ * builds (bitmap.cpp:283-305: RGB float texels, 2-lobed Lanczos downsampling under the texture's wrap modes).  wrap_u / wrap_v:
+ * 0 repeat, 1 clamp, 2 mirror, 3 zero, 4 one; filter_type: 0 nearest, 1 bilinear, 2 trilinear, 3 ewa (max_anisotropy, 20 by
+ * default; 1 for the other filters).  Sensor rays carry differentials: the first hit of a path computes uv partials
+ * (Intersection::computePartials, src/librender/intersection.cpp:5-76) and takes the filtered lookup, later hits the
+ * full-resolution one — as `path` / `direct` / `volpath*` do in the reference.  mtsb_scene_set_bsdf_texture binds a texture to
+ * the `reflectance` of an MTSB_BSDF_DIFFUSE (the only textured slot of the subset); textured BSDFs go on triangle meshes and
+ * rectangles. */
+typedef struct mtsb_texture_desc {
+	int32_t levels;
+	const int32_t *sizes;
+	const float *const *data;
+	int32_t wrap_u, wrap_v, filter_type;
+	float max_anisotropy;
+	float uv_scale[2], uv_offset[2];
+} mtsb_texture_desc;
+MTSB_API int  mtsb_scene_add_texture(mtsb_scene *scene, const mtsb_texture_desc *desc);
+MTSB_API int  mtsb_scene_set_bsdf_texture(mtsb_scene *scene, int bsdf, int texture);
 MTSB_API int  mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc *desc);
 MTSB_API int  mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc);    /* returns id >= 0 */
 /* TriMesh (include/mitsuba/render/trimesh.h): positions 3V, normals 3V or NULL, texcoords 2V or NULL,

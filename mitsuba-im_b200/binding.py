@@ -65,6 +65,16 @@ class EnvmapDesc(C.Structure):
                 ("scale", C.c_float), ("to_world", C.c_float * 16)]
 
 
+class TextureDesc(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("sizes", C.POINTER(C.c_int32)), ("data", C.POINTER(C.POINTER(C.c_float))),
+                ("wrap_u", C.c_int32), ("wrap_v", C.c_int32), ("filter_type", C.c_int32), ("max_anisotropy", C.c_float),
+                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2)]
+
+
+WRAP_MODES = dict(repeat=0, clamp=1, mirror=2, zero=3, one=4)
+FILTER_TYPES = dict(nearest=0, bilinear=1, trilinear=2, ewa=3)
+
+
 class Camera(C.Structure):
     _fields_ = [("sample_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
                 ("near_clip", C.c_float), ("far_clip", C.c_float), ("inv_resolution", C.c_float * 2),
@@ -108,6 +118,7 @@ def lib():
         "mtsb_scene_create": (i32, [vp, C.POINTER(vp)]), "mtsb_scene_destroy": (None, [vp]),
         "mtsb_scene_add_bsdf": (i32, [vp, C.POINTER(BsdfDesc)]), "mtsb_scene_add_emitter": (i32, [vp, C.POINTER(EmitterDesc)]),
         "mtsb_scene_set_bsdf_table": (i32, [vp, i32, vp, sz]), "mtsb_scene_set_envmap": (i32, [vp, i32, C.POINTER(EnvmapDesc)]),
+        "mtsb_scene_add_texture": (i32, [vp, C.POINTER(TextureDesc)]), "mtsb_scene_set_bsdf_texture": (i32, [vp, i32, i32]),
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
@@ -227,6 +238,22 @@ class Scene:
         """The rough-transmittance slice of a roughplastic BSDF (hostmath.rough_transmittance_slices)."""
         t = np.ascontiguousarray(table, dtype=np.float32)
         _check(lib().mtsb_scene_set_bsdf_table(self.h, int(bsdf), _ptr(t), t.shape[0]))
+
+    def add_texture(self, pyramid, wrap_u="repeat", wrap_v="repeat", filter_type="ewa", max_anisotropy=20.0, uv_scale=(1, 1), uv_offset=(0, 0)):
+        """A `bitmap` texture given by its MIP pyramid (list of [h, w, 3] float arrays, level 0 first); returns its id."""
+        levels = [np.ascontiguousarray(a, dtype=np.float32) for a in pyramid]
+        d = TextureDesc()
+        d.levels = len(levels)
+        sizes = (C.c_int32 * (2 * len(levels)))(*[v for a in levels for v in (a.shape[1], a.shape[0])])
+        ptrs = (C.POINTER(C.c_float) * len(levels))(*[a.ctypes.data_as(C.POINTER(C.c_float)) for a in levels])
+        d.sizes, d.data = sizes, ptrs
+        d.wrap_u, d.wrap_v, d.filter_type, d.max_anisotropy = WRAP_MODES[wrap_u], WRAP_MODES[wrap_v], FILTER_TYPES[filter_type], float(max_anisotropy)
+        d.uv_scale[:] = [float(uv_scale[0]), float(uv_scale[1])]
+        d.uv_offset[:] = [float(uv_offset[0]), float(uv_offset[1])]
+        return _check(lib().mtsb_scene_add_texture(self.h, C.byref(d)))
+
+    def set_bsdf_texture(self, bsdf, texture):
+        _check(lib().mtsb_scene_set_bsdf_texture(self.h, int(bsdf), int(texture)))
 
     def set_envmap(self, emitter, pyramid, scale=1.0, to_world=None):
         """The MIP pyramid of an EMITTER_ENVMAP emitter: list of [h, w, 3] float arrays, level 0 first (mtsb_scene_set_envmap)."""

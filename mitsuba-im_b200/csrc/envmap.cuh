@@ -24,6 +24,11 @@ struct EnvmapDev {
 	float normalization, scale, pixelSizeX, pixelSizeY;
 	float toWorld[9], toLocal[9];                  // linear parts of m_worldTransform and of its inverse
 	float lut[MTSB_MIPMAP_LUT_SIZE];               // mipmap.h:297-303
+	// the same record serves `bitmap` textures (src/textures/bitmap.cpp); an envmap is repeat / clamp, EWA, anisotropy 10
+	int bcu, bcv;                                  // ReconstructionFilter::EBoundaryCondition: 0 repeat, 1 clamp, 2 mirror, 3 zero, 4 one
+	int filterType;                                // EMIPFilterType: 0 nearest, 1 bilinear, 2 trilinear, 3 EWA
+	float maxAnisotropy;
+	float uvScaleX, uvScaleY, uvOffsetX, uvOffsetY;   // Texture2D (src/librender/texture.cpp:112-121)
 };
 
 // an ENVMAP emitter record carries the device address of its EnvmapDev in pos.x / pos.y (scene.cu)
@@ -38,11 +43,22 @@ __device__ __forceinline__ V3 mat3_mul(const float *m, const V3 &v) {
 }
 __device__ __forceinline__ float safe_acos(float x) { return acosf(fminf(1.0f, fmaxf(-1.0f, x))); }
 
-// MIPMap::evalTexel (mipmap.h:504-564) with bcu = ERepeat, bcv = EClamp
+// MIPMap::evalTexel (mipmap.h:504-564)
+__device__ __forceinline__ bool env_wrap(int bc, int &x, int size, float &constant) {
+	if (x >= 0 && x < size) return true;
+	switch (bc) {
+		case 0: { const int r = x % size; x = r < 0 ? r + size : r; return true; }
+		case 1: x = min(max(x, 0), size - 1); return true;
+		case 2: { int r = x % (2 * size); if (r < 0) r += 2 * size; x = r >= size ? 2 * size - r - 1 : r; return true; }
+		case 3: constant = 0.0f; return false;
+		default: constant = 1.0f; return false;
+	}
+}
 __device__ inline V3 env_texel(const EnvmapDev &E, int level, int x, int y) {
 	const int w = E.w[level], h = E.h[level];
-	if (x < 0 || x >= w) { int r = x % w; x = r < 0 ? r + w : r; }
-	if (y < 0 || y >= h) y = min(max(y, 0), h - 1);
+	float c = 0.0f;
+	if (!env_wrap(E.bcu, x, w, c)) return v3(c);
+	if (!env_wrap(E.bcv, y, h, c)) return v3(c);
 	const float *p = E.data + ((size_t) E.offset[level] + (size_t) y * w + x) * 3;
 	return v3(p[0], p[1], p[2]);
 }
@@ -89,20 +105,22 @@ __device__ inline V3 env_ewa(const EnvmapDev &E, int level, float uvx, float uvy
 	if (denominator == 0) return env_bilinear(E, level, uvx, uvy);
 	return result / denominator;
 }
-// MIPMap::eval with the EWA filter, maxAnisotropy = 10 (mipmap.h:630-716; envmap.cpp:143-144)
+// MIPMap::eval (mipmap.h:630-716); an envmap: EWA with maxAnisotropy = 10 (envmap.cpp:143-144)
 __device__ inline V3 env_filtered(const EnvmapDev &E, float uvx, float uvy, float d0x, float d0y, float d1x, float d1y) {
+	if (E.filterType == 0) return env_box(E, 0, uvx, uvy);
+	if (E.filterType == 1) return env_bilinear(E, 0, uvx, uvy);
 	const float du0 = d0x * E.w[0], dv0 = d0y * E.h[0], du1 = d1x * E.w[0], dv1 = d1y * E.h[0];
 	float A = dv0 * dv0 + dv1 * dv1, B = -2.0f * (du0 * dv0 + du1 * dv1), C = du0 * du0 + du1 * du1, F = A * C - B * B * 0.25f;
 	const float root = hypotf(A - C, B), Aprime = 0.5f * (A + C - root), Cprime = 0.5f * (A + C + root);
 	float majorRadius = Aprime != 0 ? sqrtf(F / Aprime) : 0, minorRadius = Cprime != 0 ? sqrtf(F / Cprime) : 0;
-	if (!(minorRadius > 0) || !(majorRadius > 0) || F < 0) {
+	if (E.filterType == 2 || !(minorRadius > 0) || !(majorRadius > 0) || F < 0) {
 		const float level = log2f(fmaxf(majorRadius, MTS_EPSILON));
 		const int ilevel = (int) floorf(level);
 		if (ilevel < 0) return env_bilinear(E, 0, uvx, uvy);
 		const float a = level - ilevel;
 		return env_bilinear(E, ilevel, uvx, uvy) * (1.0f - a) + env_bilinear(E, ilevel + 1, uvx, uvy) * a;
 	}
-	const float maxAnisotropy = 10.0f;
+	const float maxAnisotropy = E.maxAnisotropy;
 	if (minorRadius * maxAnisotropy < majorRadius) {
 		minorRadius = majorRadius / maxAnisotropy;
 		const float theta = 0.5f * atanf(B / (A - C));
@@ -133,6 +151,14 @@ __device__ inline V3 envmap_eval(const EnvmapDev &E, const V3 &d, bool hasDiffer
 		value = env_filtered(E, uvx, uvy, t1 * (dvdx.z * v.x - dvdx.x * v.z), t2 * dvdx.y, t1 * (dvdy.z * v.x - dvdy.x * v.z), t2 * dvdy.y);
 	}
 	return value * E.scale;
+}
+
+// Texture2D::eval(its, filter = true) over BitmapTexture::eval (texture.cpp:112-121, bitmap.cpp:434-502): the filtered lookup
+// where the intersection carries uv partials, the full-resolution one (bilinear, or box for `nearest`) otherwise
+__device__ inline V3 texture_eval(const EnvmapDev &T, float u, float v, bool hasPartials, float dudx, float dvdx, float dudy, float dvdy) {
+	const float uvx = u * T.uvScaleX + T.uvOffsetX, uvy = v * T.uvScaleY + T.uvOffsetY;
+	if (hasPartials) return env_filtered(T, uvx, uvy, dudx * T.uvScaleX, dvdx * T.uvScaleY, dudy * T.uvScaleX, dvdy * T.uvScaleY);
+	return T.filterType != 0 ? env_bilinear(T, 0, uvx, uvy) : env_box(T, 0, uvx, uvy);
 }
 
 // sampleReuse of envmap.cpp:663-668 (std::lower_bound over size + 1 entries)

@@ -61,7 +61,7 @@ direct_head_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed,
 			if (emitterId >= 0 && !integ.hideEmitters) Li += area_emitter_eval(S, emitterId, sf.ns, -d);      // :169-170
 			const V3 wi = to_local(sf, -d);
 			if (!(integ.strictNormals && dot(d, sf.ng) * wi.z >= 0)) {                                          // :178-191
-				const BsdfRec bsdf = S.bsdfs[bsdfId];
+				const BsdfRec bsdf = load_bsdf(S, bsdfId, sf, hitSlot, o, true, ps.prev[slot], ps.L + slot);
 				const uint32_t btype = bsdf_type(bsdf);
 				const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);
 				// ---- emitter sampling (:211-244)

@@ -356,7 +356,7 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	g.pixPadded = g.tilesX * ((g.h + 3) / 4) * 32;
 	g.sppBegin = spp_begin; g.sppStride = sample_stride; g.sppPhase = sample_phase; g.seed = r->seed;
 	g.samples = nullptr;
-	g.diffScale = r->scene->envmapEmitter >= 0 ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
+	g.diffScale = (r->scene->envmapEmitter >= 0 || !r->scene->texRecords.empty()) ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	const unsigned long long total = (unsigned long long) g.pixPadded * spp_count;
 	// chunks hold whole sample planes when possible so that a warp covers an 8x4 pixel tile of one sample index
 	size_t chunk = std::min<unsigned long long>(total, max_paths(r));
@@ -515,7 +515,7 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	if (pos_out) MTSB_CHECK(dP.alloc(n * 2));
 	GenParams g; memset(&g, 0, sizeof(g));
 	g.count = (uint32_t) n; g.samples = dS.ptr; g.seed = r->seed; g.pixPadded = 1; g.tilesX = 1; g.sppStride = 1;
-	g.diffScale = r->scene->envmapEmitter >= 0 ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
+	g.diffScale = (r->scene->envmapEmitter >= 0 || !r->scene->texRecords.empty()) ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	MTSB_CHECK(run_chunk(r, g, dO.ptr, pos_out ? dP.ptr : nullptr));
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	if (pos_out) MTSB_CUDA(cudaMemcpyAsync(pos_out, dP.ptr, n * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));

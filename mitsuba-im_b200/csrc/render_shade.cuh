@@ -102,7 +102,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 		// :155-164
 		if (((int) depth >= integ.maxDepth && integ.maxDepth > 0) || (integ.strictNormals && dot(d, sf.ng) * wi.z >= 0)) alive = false;
 		if (alive) {
-			const BsdfRec bsdf = S.bsdfs[bsdfId];
+			const BsdfRec bsdf = load_bsdf<LEAN>(S, bsdfId, sf, hitSlot, o, first, prev, ps.L + slot);
 			const uint32_t btype = bsdf_type(bsdf);
 			const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);   // DirectSamplingRecord(its), records.inl:160-164
 			// ---- emitter sampling (:171-199)

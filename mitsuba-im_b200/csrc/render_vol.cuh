@@ -221,7 +221,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 			const V3 wi = to_local(sf, -d);
 			if (integ.strictNormals && -dot(sf.ng, d) * wi.z < 0) out.alive = false;          // :192-195 (no depth test here: recursiveType below ends the path)
 			if (out.alive) {
-				const BsdfRec bsdf = S.bsdfs[sh.bsdf];
+				const BsdfRec bsdf = load_bsdf(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
 				const uint32_t btype = bsdf_type(bsdf);
 				// ---- direct illumination (:201-227): no MIS, one attenuated emitter sample
 				if ((vf & VF_REST) && (btype & B_SMOOTH)) {
@@ -437,7 +437,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 				const V3 wi = to_local(sf, -d);
 				if (out.alive && integ.strictNormals && -dot(sf.ng, d) * wi.z < 0) out.alive = false;
 				if (out.alive) {
-					const BsdfRec bsdf = S.bsdfs[sh.bsdf];
+					const BsdfRec bsdf = load_bsdf(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
 					const uint32_t btype = bsdf_type(bsdf);
 					const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);
 					// ---- emitter sampling with MIS (:212-247)

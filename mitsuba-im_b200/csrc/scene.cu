@@ -170,6 +170,52 @@ int mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc *desc) {
 	return (int) scene->emitters.size() - 1;
 }
 
+// levels of a MIP pyramid -> record + texel store (sizes, offsets, size ratios of mipmap.h:243, 265-267, the EWA weight table)
+static int fill_pyramid(EnvmapDev &E, int levels, const int32_t *sizes, const float *const *data, std::vector<float> &store, const char *who) {
+	if (levels < 1 || levels > MTSB_ENVMAP_MAX_LEVELS) MTSB_FAIL(MTSB_EINVAL, "%s: %d levels", who, levels);
+	const size_t base = store.size() / 3;
+	E.levels = levels;
+	for (int l = 0; l < levels; ++l) {
+		const int w = sizes[2 * l], h = sizes[2 * l + 1];
+		if (w < 1 || h < 1 || w > 0xFFFF || h > 0xFFFF || !data[l]) MTSB_FAIL(MTSB_EINVAL, "%s: level %d is %dx%d", who, l, w, h);
+		E.w[l] = w; E.h[l] = h; E.offset[l] = (unsigned) (store.size() / 3 - base);
+		E.ratioX[l] = (float) w / (float) sizes[0]; E.ratioY[l] = (float) h / (float) sizes[1];
+		store.insert(store.end(), data[l], data[l] + (size_t) w * h * 3);
+	}
+	for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) {                           // mipmap.h:297-303 (math::fastexp via double)
+		const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1);
+		E.lut[i] = (float) exp((double) (-2.0f * r2)) - (float) exp((double) -2.0f);
+	}
+	E.uvScaleX = E.uvScaleY = 1.0f;
+	return 0;
+}
+
+int mtsb_scene_add_texture(mtsb_scene *scene, const mtsb_texture_desc *desc) {
+	if (!scene || !desc || !desc->sizes || !desc->data) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_texture: NULL argument");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_texture: scene already committed");
+	if (desc->wrap_u < 0 || desc->wrap_u > 4 || desc->wrap_v < 0 || desc->wrap_v > 4 || desc->filter_type < 0 || desc->filter_type > 3)
+		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_texture: wrap mode / filter type out of range");
+	EnvmapDev E; memset(&E, 0, sizeof(E));
+	scene->texDataOffset.push_back(scene->texData.size());
+	MTSB_CHECK(fill_pyramid(E, desc->levels, desc->sizes, desc->data, scene->texData, "mtsb_scene_add_texture"));
+	E.bcu = desc->wrap_u; E.bcv = desc->wrap_v; E.filterType = desc->filter_type;
+	E.maxAnisotropy = desc->filter_type == 3 ? desc->max_anisotropy : 1.0f;                 // bitmap.cpp:234-237
+	E.uvScaleX = desc->uv_scale[0]; E.uvScaleY = desc->uv_scale[1]; E.uvOffsetX = desc->uv_offset[0]; E.uvOffsetY = desc->uv_offset[1];
+	scene->texRecords.push_back(std::vector<unsigned char>((const unsigned char *) &E, (const unsigned char *) &E + sizeof(E)));
+	return (int) scene->texRecords.size() - 1;
+}
+
+int mtsb_scene_set_bsdf_texture(mtsb_scene *scene, int bsdf, int texture) {
+	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: NULL scene");
+	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: scene already committed");
+	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size() || (scene->bsdfs[bsdf].type & 0xff) != MTSB_BSDF_DIFFUSE)
+		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_set_bsdf_texture: only the reflectance of a diffuse BSDF takes a texture (bsdf %d)", bsdf);
+	if (texture < 0 || texture >= (int) scene->texRecords.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: texture %d unknown", texture);
+	scene->bsdfTexture.resize(scene->bsdfs.size(), -1);
+	scene->bsdfTexture[bsdf] = texture;
+	return 0;
+}
+
 // EnvironmentMap::configure (src/emitters/envmap.cpp:276-333) restated: marginal / conditional CDFs over luminance x sin(theta)
 int mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc *desc) {
 	if (!scene || !desc || !desc->sizes || !desc->data) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: NULL argument");
@@ -177,17 +223,10 @@ int mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc
 	if (emitter < 0 || emitter >= (int) scene->emitters.size() || scene->emitters[emitter].type != MTSB_EMITTER_ENVMAP)
 		MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: emitter %d is not an MTSB_EMITTER_ENVMAP", emitter);
 	if (scene->envmapEmitter >= 0 && scene->envmapEmitter != emitter) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_set_envmap: one environment map per scene");
-	if (desc->levels < 1 || desc->levels > MTSB_ENVMAP_MAX_LEVELS) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: %d levels", desc->levels);
 	EnvmapDev E; memset(&E, 0, sizeof(E));
-	E.levels = desc->levels;
 	scene->envData.clear();
-	for (int l = 0; l < desc->levels; ++l) {
-		const int w = desc->sizes[2 * l], h = desc->sizes[2 * l + 1];
-		if (w < 1 || h < 1 || w > 0xFFFF || h > 0xFFFF || !desc->data[l]) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_envmap: level %d is %dx%d", l, w, h);
-		E.w[l] = w; E.h[l] = h; E.offset[l] = (unsigned) (scene->envData.size() / 3);
-		E.ratioX[l] = (float) w / (float) desc->sizes[0]; E.ratioY[l] = (float) h / (float) desc->sizes[1];     // mipmap.h:243, 265-267
-		scene->envData.insert(scene->envData.end(), desc->data[l], desc->data[l] + (size_t) w * h * 3);
-	}
+	MTSB_CHECK(fill_pyramid(E, desc->levels, desc->sizes, desc->data, scene->envData, "mtsb_scene_set_envmap"));
+	E.bcu = 0; E.bcv = 1; E.filterType = 3; E.maxAnisotropy = 10.0f;                       // envmap.cpp:143-144, 175-176
 	const int W = E.w[0], H = E.h[0];
 	const float *img = scene->envData.data();
 	scene->envCdfCols.assign((size_t) (W + 1) * H, 0.0f); scene->envCdfRows.assign(H + 1, 0.0f); scene->envRowWeights.assign(H, 0.0f);
@@ -221,10 +260,6 @@ int mtsb_scene_set_envmap(mtsb_scene *scene, int emitter, const mtsb_envmap_desc
 	float inv[12];
 	invert_affine(desc->to_world, inv);
 	for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { E.toWorld[r * 3 + c] = desc->to_world[r * 4 + c]; E.toLocal[r * 3 + c] = inv[r * 4 + c]; }
-	for (int i = 0; i < MTSB_MIPMAP_LUT_SIZE; ++i) {                           // mipmap.h:297-303 (math::fastexp via double)
-		const float r2 = (float) i / (float) (MTSB_MIPMAP_LUT_SIZE - 1);
-		E.lut[i] = (float) exp((double) (-2.0f * r2)) - (float) exp((double) -2.0f);
-	}
 	scene->envRecord.assign((const unsigned char *) &E, (const unsigned char *) &E + sizeof(E));
 	scene->envmapEmitter = emitter;
 	return 0;
@@ -467,6 +502,27 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 
 	MTSB_CHECK(scene->dShapes.upload(scene->shapes, st));
 	MTSB_CHECK(scene->dRects.upload(scene->rects, st));
+	// bitmap textures: texels and records to the device; a textured diffuse record carries the record's address in p[13..14], p[12] = 1
+	if (!scene->texRecords.empty()) {
+		MTSB_CHECK(scene->dTexData.upload(scene->texData, st));
+		std::vector<unsigned char> recs;
+		for (size_t t = 0; t < scene->texRecords.size(); ++t) {
+			EnvmapDev *E = (EnvmapDev *) scene->texRecords[t].data();
+			E->data = scene->dTexData.ptr + scene->texDataOffset[t];
+			recs.insert(recs.end(), scene->texRecords[t].begin(), scene->texRecords[t].end());
+		}
+		MTSB_CHECK(scene->dTexRecords.upload(recs, st));
+		scene->bsdfTexture.resize(scene->bsdfs.size(), -1);
+		for (size_t i = 0; i < scene->bsdfs.size(); ++i) {
+			if (scene->bsdfTexture[i] < 0) continue;
+			const unsigned char *dev = scene->dTexRecords.ptr + (size_t) scene->bsdfTexture[i] * sizeof(EnvmapDev);
+			memcpy(&scene->bsdfs[i].p[13], &dev, sizeof(dev));
+			scene->bsdfs[i].p[12] = 1.0f;
+		}
+		for (const ShapeRec &sh : scene->shapes)
+			if (scene->bsdfTexture[sh.bsdf] >= 0 && sh.type != SHAPE_MESH && sh.type != SHAPE_RECT)
+				MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_commit: textured BSDFs go on triangle meshes and rectangles");
+	}
 	// lookup tables first: a roughplastic record carries the device address of its table in p[13..14]
 	if (!scene->bsdfTables.empty()) MTSB_CHECK(scene->dBsdfTables.upload(scene->bsdfTables, st));
 	for (size_t i = 0; i < scene->bsdfs.size(); ++i) {
@@ -563,7 +619,7 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));
-	scene->lean = !(ctx->shadeLean == 0) && scene->envmapEmitter < 0;
+	scene->lean = !(ctx->shadeLean == 0) && scene->envmapEmitter < 0 && scene->texRecords.empty();
 	for (const BsdfRec &b : scene->bsdfs) {
 		const int t = b.type & 0xff;
 		const bool ok = t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_NULL || t == MTSB_BSDF_DIELECTRIC ||

@@ -30,6 +30,11 @@ struct mtsb_scene {
 	mtsb::DevBuf<float> dEnvData, dEnvCdfRows, dEnvCdfCols, dEnvRowWeights;
 	mtsb::DevBuf<unsigned char> dEnvmap;           // one EnvmapDev
 	std::vector<unsigned char> envRecord;          // host copy of the EnvmapDev (pointers patched at commit)
+	// `bitmap` textures: one EnvmapDev-shaped record each (envmap.cuh), all texels in one buffer
+	std::vector<std::vector<unsigned char> > texRecords; std::vector<size_t> texDataOffset;
+	std::vector<float> texData;
+	std::vector<int> bsdfTexture;                  // per BSDF: texture bound to its reflectance or -1
+	mtsb::DevBuf<float> dTexData; mtsb::DevBuf<unsigned char> dTexRecords;
 	std::vector<mtsb::EmitterRec> emitters;
 	std::vector<mtsb::MediumRec> media;
 	std::vector<float> emitterWeights;

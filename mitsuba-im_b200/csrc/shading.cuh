@@ -117,3 +117,4 @@ __device__ inline V3 fresnel_conductor_exact(float cosThetaI, V3 eta, V3 k) {   
 #include "microfacet.cuh"
 #include "bsdf.cuh"
 #include "emitter.cuh"
+#include "texture.cuh"

@@ -53,16 +53,86 @@ struct RoughTransmittanceAccess : public RoughTransmittance {
 	size_t thetaSamples() const { return m_thetaSamples; }
 };
 
-static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float> *table = NULL) {
+/// A `bitmap` texture as the device takes it: the MIP pyramid the texture's own constructor builds (src/textures/bitmap.cpp:248-305),
+/// rebuilt here with the reference's Bitmap / MIPMap classes from the texture's file, plus the Texture2D parameters.
+struct TextureData {
+	bool present;
+	std::vector<int32_t> sizes; std::vector<std::vector<float> > levels;
+	int wrapU, wrapV, filterType; float maxAnisotropy, uvScale[2], uvOffset[2];
+	TextureData() : present(false) { }
+};
+
+static int parseWrapMode(const std::string &m) {
+	if (m == "repeat") return 0; if (m == "clamp") return 1; if (m == "mirror") return 2;
+	if (m == "zero" || m == "black") return 3; if (m == "one" || m == "white") return 4;
+	SLog(EError, "gpupath: unknown texture wrap mode \"%s\"", m.c_str());
+	return 0;
+}
+
+static void describeBitmapTexture(const Texture *tex, TextureData &td) {
+	typedef TMIPMap<Color3, Color3> MIPMap3;
+	static const ReconstructionFilter::EBoundaryCondition bc[5] = { ReconstructionFilter::ERepeat, ReconstructionFilter::EClamp,
+		ReconstructionFilter::EMirror, ReconstructionFilter::EZero, ReconstructionFilter::EOne };
+	const Properties &props = tex->getProperties();
+	if (!props.hasProperty("filename") || !props.getString("channel", "").empty())
+		SLog(EError, "gpupath: bitmap textures from raw data or a single channel are outside the GPU subset");
+	if (props.getString("coordinates", "uv") != "uv") SLog(EError, "gpupath: only UV texture coordinates are supported");
+	const std::string wrap = props.getString("wrapMode", "repeat"), filter = to_lower_copy(props.getString("filterType", "ewa"));
+	td.wrapU = parseWrapMode(props.getString("wrapModeU", wrap)); td.wrapV = parseWrapMode(props.getString("wrapModeV", wrap));
+	td.filterType = filter == "ewa" ? 3 : (filter == "trilinear" ? 2 : (filter == "bilinear" ? 1 : (filter == "nearest" ? 0 : -1)));
+	if (td.filterType < 0) SLog(EError, "gpupath: unknown texture filter type \"%s\"", filter.c_str());
+	td.maxAnisotropy = td.filterType == 3 ? (float) props.getFloat("maxAnisotropy", 20) : 1.0f;
+	const Float uvscale = props.getFloat("uvscale", 1.0f);
+	td.uvScale[0] = (float) props.getFloat("uscale", uvscale); td.uvScale[1] = (float) props.getFloat("vscale", uvscale);
+	td.uvOffset[0] = (float) props.getFloat("uoffset", 0.0f); td.uvOffset[1] = (float) props.getFloat("voffset", 0.0f);
+	fs::pathstr filename = Thread::getThread()->getFileResolver()->resolve(fs::pathstr(props.getString("filename")));
+	ref<FileStream> stream = new FileStream(filename, FileStream::EReadOnly);
+	ref<Bitmap> bitmap = new Bitmap(Bitmap::EAuto, stream);
+	const Float gamma = props.getFloat("gamma", 0);
+	if (gamma != 0) bitmap->setGamma(gamma);
+	if (bitmap->getPixelFormat() != Bitmap::ERGB && bitmap->getPixelFormat() != Bitmap::ERGBA)
+		SLog(EError, "gpupath: only RGB bitmap textures are inside the GPU subset");
+	Properties rfilterProps("lanczos");
+	rfilterProps.setInteger("lobes", 2);
+	ref<ReconstructionFilter> rfilter = static_cast<ReconstructionFilter *>(PluginManager::getInstance()->createObject(
+		MTS_CLASS(ReconstructionFilter), rfilterProps));
+	rfilter->configure();
+	ref<MIPMap3> mip = new MIPMap3(bitmap, Bitmap::ERGB, Bitmap::EFloat, rfilter, bc[td.wrapU], bc[td.wrapV],
+		(EMIPFilterType) td.filterType, td.maxAnisotropy, fs::pathstr(), 0);
+	const int levels = mip->getLevels();
+	td.sizes.resize(2 * levels); td.levels.resize(levels);
+	for (int l = 0; l < levels; ++l) {
+		const MIPMap3::Array2DType &a = mip->getArray(l);
+		td.sizes[2 * l] = a.getSize().x; td.sizes[2 * l + 1] = a.getSize().y;
+		td.levels[l].resize((size_t) a.getSize().x * a.getSize().y * 3);
+		float *dst = td.levels[l].data();
+		for (int y = 0; y < a.getSize().y; ++y)
+			for (int x = 0; x < a.getSize().x; ++x, dst += 3) { const Color3 v = a(x, y); dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2]; }
+	}
+	td.present = true;
+}
+
+static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float> *table = NULL, TextureData *texture = NULL) {
 	memset(&d, 0, sizeof(d));
 	const std::string cls = bsdf->getClass()->getName();
 	const Properties &props = bsdf->getProperties();
-	if (bsdf->usesRayDifferentials())
+	if (bsdf->usesRayDifferentials() && cls != "SmoothDiffuse" && cls != "TwoSidedBRDF")
 		SLog(EError, "gpupath: BSDF \"%s\" uses textures that need ray differentials — outside the GPU subset", cls.c_str());
 	Intersection its = dummyIntersection();
 	if (cls == "SmoothDiffuse") {                                   // src/bsdfs/diffuse.cpp:80-100
 		d.type = MTSB_BSDF_DIFFUSE;
 		toRGB(bsdf->getDiffuseReflectance(its), d.p);
+		if (bsdf->usesRayDifferentials()) {
+			// a textured reflectance.  SmoothDiffuse keeps it in `private: ref<Texture> m_reflectance` (diffuse.cpp:188), its only data
+			// member, behind no accessor: read through a layout mirror, checked by RTTI (as for twosided below)
+			struct Mirror { char base[sizeof(BSDF)]; const Texture *reflectance; };
+			const Texture *tex = reinterpret_cast<const Mirror *>(static_cast<const BSDF *>(bsdf))->reflectance;
+			if (!tex || !tex->getClass()->derivesFrom(MTS_CLASS(Texture)) || tex->getClass()->getName() != "BitmapTexture")
+				SLog(EError, "gpupath: the reflectance texture of this diffuse BSDF is outside the GPU subset (bitmap; a texture brighter than 1 gets wrapped in a scaling texture): %s",
+					bsdf->toString().substr(0, 300).c_str());
+			if (!texture) SLog(EError, "gpupath: a textured BSDF inside an adapter is outside the GPU subset");
+			describeBitmapTexture(tex, *texture);
+		}
 	} else if (cls == "SmoothDielectric") {                         // src/bsdfs/dielectric.cpp:150-165
 		d.type = MTSB_BSDF_DIELECTRIC;
 		d.p[0] = (float) bsdf->getEta();
@@ -173,7 +243,7 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float>
 		if (!n0 || !n1 || !n0->getClass()->derivesFrom(MTS_CLASS(BSDF)) || !n1->getClass()->derivesFrom(MTS_CLASS(BSDF)))
 			SLog(EError, "gpupath: cannot read the nested BRDFs of %s", desc.substr(0, 200).c_str());
 		mtsb_bsdf_desc d1;
-		if (!describeBSDF(n0, d, table) || !describeBSDF(n1, d1))
+		if (!describeBSDF(n0, d, table, texture) || !describeBSDF(n1, d1))
 			SLog(EError, "gpupath: twosided around a BRDF outside the GPU subset: %s", desc.c_str());
 		if (memcmp(&d, &d1, sizeof(d)) != 0)
 			SLog(EError, "gpupath: twosided with two DIFFERENT nested BRDFs is outside the GPU subset: %s", desc.c_str());

@@ -151,12 +151,24 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		else {
 			mtsb_bsdf_desc bd;
 			std::vector<float> table;
-			if (!describeBSDF(bsdf, bd, &table))
+			TextureData tex;
+			if (!describeBSDF(bsdf, bd, &table, &tex))
 				SLog(EError, "gpupath: BSDF \"%s\" is outside the GPU subset (diffuse, dielectric, plastic, roughplastic, conductor, roughconductor, roughdielectric, null, twosided)",
 					bsdf->getClass()->getName().c_str());
 			bid = mtsb_scene_add_bsdf(out, &bd);
 			if (bid < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
 			if (!table.empty()) MTSB_CALL(mtsb_scene_set_bsdf_table(out, bid, table.data(), table.size()));
+			if (tex.present) {
+				std::vector<const float *> ptrs(tex.levels.size());
+				for (size_t l = 0; l < tex.levels.size(); ++l) ptrs[l] = tex.levels[l].data();
+				mtsb_texture_desc td; memset(&td, 0, sizeof(td));
+				td.levels = (int32_t) tex.levels.size(); td.sizes = tex.sizes.data(); td.data = ptrs.data();
+				td.wrap_u = tex.wrapU; td.wrap_v = tex.wrapV; td.filter_type = tex.filterType; td.max_anisotropy = tex.maxAnisotropy;
+				td.uv_scale[0] = tex.uvScale[0]; td.uv_scale[1] = tex.uvScale[1]; td.uv_offset[0] = tex.uvOffset[0]; td.uv_offset[1] = tex.uvOffset[1];
+				const int tid = mtsb_scene_add_texture(out, &td);
+				if (tid < 0) SLog(EError, "libmtsb200: %s", mtsb_last_error());
+				MTSB_CALL(mtsb_scene_set_bsdf_texture(out, bid, tid));
+			}
 			bsdfIds[bsdf] = bid;
 		}
 		int eid = -1;

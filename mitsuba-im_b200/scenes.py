@@ -403,6 +403,14 @@ class SceneDesc:
             bid = sc.add_bsdf(tid, params)
             if bd.get("_table") is not None:
                 sc.set_bsdf_table(bid, bd["_table"])
+            if bd.get("texture") is not None:
+                t = bd["texture"]
+                if t.get("pyramid") is None:
+                    raise ValueError("bitmap texture: pass the MIP pyramid (texture=dict(image=..., pyramid=[...]))")
+                tid_ = sc.add_texture(t["pyramid"], wrap_u=t.get("wrap_u", t.get("wrap", "repeat")), wrap_v=t.get("wrap_v", t.get("wrap", "repeat")),
+                                      filter_type=t.get("filter", "ewa"), max_anisotropy=t.get("max_anisotropy", 20.0),
+                                      uv_scale=t.get("uv_scale", (1, 1)), uv_offset=t.get("uv_offset", (0, 0)))
+                sc.set_bsdf_texture(bid, tid_)
             eid = -1
             if s["emitter"] is not None:
                 eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
@@ -460,7 +468,17 @@ class SceneDesc:
         if t == "passthrough":          # index-matched medium boundary (src/bsdfs/null.cpp)
             return '<bsdf type="null"/>'
         inner = ""
-        if t == "diffuse":
+        if t == "diffuse" and b.get("texture") is not None:
+            # `bitmap` texture on the reflectance (src/textures/bitmap.cpp); to_xml() has written the image and set its file name
+            x = b["texture"]
+            inner = ('<bsdf type="diffuse"><texture type="bitmap" name="reflectance"><string name="filename" value="%s"/>'
+                     '<string name="wrapModeU" value="%s"/><string name="wrapModeV" value="%s"/><string name="filterType" value="%s"/>'
+                     '<float name="maxAnisotropy" value="%r"/><float name="uscale" value="%r"/><float name="vscale" value="%r"/>'
+                     '<float name="uoffset" value="%r"/><float name="voffset" value="%r"/><boolean name="cache" value="false"/></texture></bsdf>') % (
+                x["filename"], x.get("wrap_u", x.get("wrap", "repeat")), x.get("wrap_v", x.get("wrap", "repeat")), x.get("filter", "ewa"),
+                float(x.get("max_anisotropy", 20.0)), float(x.get("uv_scale", (1, 1))[0]), float(x.get("uv_scale", (1, 1))[1]),
+                float(x.get("uv_offset", (0, 0))[0]), float(x.get("uv_offset", (0, 0))[1]))
+        elif t == "diffuse":
             inner = '<bsdf type="diffuse">%s</bsdf>' % rgb("reflectance", b.get("reflectance", (0.5, 0.5, 0.5)))
         elif t == "dielectric":
             inner = '<bsdf type="dielectric"><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/></bsdf>' % (
@@ -548,6 +566,9 @@ class SceneDesc:
             else:
                 out.append('<emitter type="constant"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in e["radiance"]))
         for i, s in enumerate(self.shapes):
+            if s["bsdf"] is not None and s["bsdf"].get("texture") is not None:
+                s["bsdf"]["texture"]["filename"] = "%s_tex%d.pfm" % (name, i)
+                write_pfm(os.path.join(directory, s["bsdf"]["texture"]["filename"]), s["bsdf"]["texture"]["image"])
             em = ""
             if s["emitter"] is not None:
                 em = '<emitter type="area"><rgb name="radiance" value="%s"/></emitter>' % ", ".join(repr(float(x)) for x in s["emitter"])
@@ -778,6 +799,44 @@ def analytic_lights_scene(width=48, height=32, spp=4, max_depth=6, sampler="inde
     sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
     sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
     sd.set_integrator("path", max_depth=max_depth, rr_depth=3)
+    return sd
+
+
+def texture_image(size=64, seed=9):
+    """A colour texture with fine detail (checker x stripes + noise, values in (0, 0.9]): minification makes the MIP levels matter."""
+    y, x = np.meshgrid(np.arange(size), np.arange(size), indexing="ij")
+    chk = ((x // 4 + y // 4) % 2).astype(np.float32)
+    img = np.stack([0.15 + 0.7 * chk, 0.2 + 0.6 * ((x // 2) % 2), 0.25 + 0.5 * ((y // 8) % 2)], axis=-1).astype(np.float32)
+    rng = np.random.default_rng(seed)
+    return np.clip(img * (1.0 + 0.1 * rng.standard_normal((size, size, 1))), 0.02, 0.9).astype(np.float32)
+
+
+def textured_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent", seed=0, pyramids=None, kind="path"):
+    """`bitmap` textures on the reflectance of diffuse BSDFs: a floor mesh with texture coordinates that repeat the
+    texture 6 x 6 times (EWA, seen at a grazing angle: anisotropic footprints), a wall `rectangle` (trilinear, clamp, uv scale and
+    offset) and a displaced sphere with spherical coordinates (bilinear, mirror); pyramids = the three MIP pyramids."""
+    img = texture_image()
+    pyramids = pyramids or [None, None, None]
+    sd = SceneDesc()
+    sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
+    sd.add_constant_env((0.3, 0.35, 0.5))
+    g = 4.0
+    gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
+    gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    gUV = np.array([[0, 0], [6, 0], [6, 6], [0, 6]], np.float32)
+    sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), UV=gUV,
+                bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[0], wrap="repeat", filter="ewa")))
+    sd.add_rectangle(translate(0, 1.5, 2.5) @ rotate((0, 1, 0), 180) @ scale(2.5, 1.5, 1.0),
+                     bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[1], wrap="clamp", filter="trilinear", uv_scale=(3, 2), uv_offset=(-0.4, 0.1))))
+    c = np.array((0.3, 0.7, 0.2))
+    V, N, F = displaced_sphere(3, seed=33, radius=0.7, center=tuple(c))
+    dn = (V - c) / np.linalg.norm(V - c, axis=1, keepdims=True)
+    UV = np.stack([np.arctan2(dn[:, 2], dn[:, 0]) / (2 * math.pi) + 0.5, np.arccos(np.clip(dn[:, 1], -1, 1)) / math.pi], axis=1) * 3.0
+    sd.add_mesh(V, N, F, UV=UV, bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[2], wrap="mirror", filter="bilinear")))
+    V, N, F = displaced_sphere(2, seed=34, radius=0.4, center=(-1.3, 0.4, -0.4))
+    sd.add_mesh(V, N, F, bsdf=dict(type="dielectric"))
+    sd.set_sensor(look_at((0.3, 1.3, -4.5), (0, 0.7, 0), (0, 1, 0)), 50.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_integrator(kind, max_depth=max_depth, rr_depth=3)
     return sd
 
 

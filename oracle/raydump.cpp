@@ -277,6 +277,37 @@ public:
 		return 0;
 	}
 
+	/// The MIP pyramid a `bitmap` texture builds from an RGB image (src/textures/bitmap.cpp:283-305: float texels, 2-lobed Lanczos
+	/// downsampling under the texture's own wrap modes); same output layout as `mipmap`
+	int mipmap3(int argc, char **argv) {
+		if (argc < 6) { cout << "mipmap3 <image> <out> <wrapU> <wrapV>  (0 repeat, 1 clamp, 2 mirror, 3 zero, 4 one)" << endl; return 1; }
+		typedef TMIPMap<Color3, Color3> MIPMap3;
+		static const ReconstructionFilter::EBoundaryCondition bc[5] = { ReconstructionFilter::ERepeat, ReconstructionFilter::EClamp,
+			ReconstructionFilter::EMirror, ReconstructionFilter::EZero, ReconstructionFilter::EOne };
+		ref<FileStream> fs = new FileStream(fs::pathstr(argv[2]), FileStream::EReadOnly);
+		ref<Bitmap> bitmap = new Bitmap(Bitmap::EAuto, fs);
+		Properties rfilterProps("lanczos");
+		rfilterProps.setInteger("lobes", 2);
+		ref<ReconstructionFilter> rfilter = static_cast<ReconstructionFilter *>(PluginManager::getInstance()->createObject(
+			MTS_CLASS(ReconstructionFilter), rfilterProps));
+		rfilter->configure();
+		ref<MIPMap3> mip = new MIPMap3(bitmap, Bitmap::ERGB, Bitmap::EFloat, rfilter, bc[atoi(argv[4])], bc[atoi(argv[5])], EEWA, 20.0f, fs::pathstr(), 0);
+		std::vector<float> out;
+		out.push_back((float) mip->getLevels());
+		for (int l = 0; l < mip->getLevels(); ++l) {
+			const MIPMap3::Array2DType &a = mip->getArray(l);
+			out.push_back((float) a.getSize().x); out.push_back((float) a.getSize().y);
+			for (int y = 0; y < a.getSize().y; ++y)
+				for (int x = 0; x < a.getSize().x; ++x) {
+					const Color3 v = a(x, y);
+					out.push_back(v[0]); out.push_back(v[1]); out.push_back(v[2]);
+				}
+		}
+		writeFloats(argv[3], out);
+		cout << "mipmap3: " << mip->getLevels() << " levels from " << bitmap->getWidth() << "x" << bitmap->getHeight() << endl;
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -347,6 +378,7 @@ public:
 		if (!strcmp(argv[1], "light")) return light(argc, argv);
 		if (!strcmp(argv[1], "all")) return all(argc, argv);
 		if (!strcmp(argv[1], "mipmap")) return mipmap(argc, argv);
+		if (!strcmp(argv[1], "mipmap3")) return mipmap3(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

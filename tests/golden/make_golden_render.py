@@ -200,6 +200,31 @@ def envmap_cases(td):
     li_case(td, "envmap_direct", S.envmap_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=71, pyramid=pyramid, kind="direct"))
 
 
+def texture_cases(td):
+    """`bitmap` textures (src/textures/bitmap.cpp): the MIP pyramids the reference builds from scenes.texture_image() under the three
+    wrap modes of scenes.textured_scene (oracle/raydump.cpp `mipmap3`), and per-sample renders through `path` and `direct`."""
+    img = S.texture_image()
+    S.write_pfm(os.path.join(td, "tex.pfm"), img)
+    B = pkg.binding
+    pyramids, store = [], {}
+    for k, wrap in enumerate(("repeat", "clamp", "mirror")):
+        mp = os.path.join(td, "mip3_%d.bin" % k)
+        w = str(B.WRAP_MODES[wrap])
+        r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "mipmap3", os.path.join(td, "tex.pfm"), mp, w, w], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0 or not os.path.exists(mp):
+            raise RuntimeError(r.stdout[-3000:])
+        a = np.fromfile(mp, np.float32)
+        levels, off, pyr = int(a[0]), 1, []
+        for l in range(levels):
+            w_, h_ = int(a[off]), int(a[off + 1]); off += 2
+            pyr.append(a[off:off + w_ * h_ * 3].reshape(h_, w_, 3).copy()); off += w_ * h_ * 3
+            store["%s_level%d" % (wrap, l)] = pyr[-1]
+        pyramids.append(pyr)
+    np.savez_compressed(os.path.join(GOLD, "texture_pyramids.npz"), **store)
+    li_case(td, "textured", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=79, pyramids=pyramids))
+    li_case(td, "textured_direct", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=83, pyramids=pyramids, kind="direct"))
+
+
 def all_case(td):
     """Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-792; oracle/raydump.cpp `all`): the kd-tree shapes plus the special
     shapes of Scene::initializeBidirectional — here the aperture disk of the thinlens sensor and the bounding sphere of the
@@ -249,6 +274,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "texture":          # round 2
+        with tempfile.TemporaryDirectory() as td:
+            texture_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "envmap":           # round 2
         with tempfile.TemporaryDirectory() as td:
             envmap_cases(td)
@@ -295,3 +324,4 @@ if __name__ == "__main__":
         all_case(td)
         analytic_lights_cases(td)
         envmap_cases(td)
+        texture_cases(td)

@@ -151,6 +151,21 @@ def test_roughplastic_through_the_loader(tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_bitmap_textures_through_the_loader(pkg, tmp_path):
+    """`bitmap` textures on diffuse reflectances, instantiated by the stock XML loader from a PFM file: the plugin
+    reads the texture out of the BSDF (plugin/extract.h) and rebuilds its MIP pyramid with the reference's own classes — EWA on a
+    repeating floor, trilinear + clamp + uv scale / offset on a rectangle, bilinear + mirror on a sphere; per-pixel match with the
+    stock `path` under the shared sampler."""
+    sd = pkg.scenes.textured_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=89)
+    xml = sd.to_xml(str(tmp_path), "tex")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
 def test_envmap_through_the_loader(pkg, tmp_path):
     """`envmap` instantiated by the stock XML loader from a PFM file: plugin/extract_scene.h rebuilds the MIP
     pyramid with the reference's own Bitmap / MIPMap classes; the camera sees the map directly (EWA lookups of the sensor rays'
