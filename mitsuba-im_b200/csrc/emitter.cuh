@@ -54,7 +54,10 @@ __device__ inline bool sphere_intersect(const V3 &center, float radius, const V3
 	return true;
 }
 
-// Shape::samplePosition for the shape an area light is attached to
+// Shape::samplePosition for the shape an area light is attached to.
+// LEAN (here and below): the scene has no environment map and no area light on an analytic sphere / disk (scene.cu), so the
+// kernels of the benchmark configurations are compiled without those branches — as for the BSDFs (bsdf.cuh)
+template <bool LEAN = false>
 __device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeIdx, float sx, float sy, V3 &p, V3 &n, float &pdf) {
 	const ShapeRec sh = S.shapes[shapeIdx];
 	if (sh.type == SHAPE_RECT) {
@@ -65,7 +68,7 @@ __device__ inline void shape_sample_position(const SceneDev &S, uint32_t shapeId
 		n = r.n; pdf = r.invSurfaceArea;
 		return;
 	}
-	if (sh.type == SHAPE_DISK) {
+	if (!LEAN && sh.type == SHAPE_DISK) {
 		const RectRec &r = S.rects[sh.rect];
 		float x, y; square_to_disk_concentric(sx, sy, x, y);
 		const float *m = r.toWorld;
@@ -157,18 +160,19 @@ __device__ inline float sphere_pdf_direct(const RectRec &r, const V3 &ref, const
 }
 
 // Emitter::sampleDirect for emitter `e`
+template <bool LEAN = false>
 __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
 	const EmitterRec &em = S.emitters[e];
 	out.emitter = (int) e; out.pdf = 0; out.n = v3(0.0f); out.d = v3(0.0f); out.dist = 0; out.measure = M_SOLID_ANGLE; out.p = ref;
 	if (em.type == MTSB_EMITTER_AREA) {
 		V3 d; float pdf;
 		const ShapeRec &esh = S.shapes[em.shape];
-		if (esh.type == SHAPE_SPHERE) {                       // the sphere overrides Shape::sampleDirect
+		if (!LEAN && esh.type == SHAPE_SPHERE) {              // the sphere overrides Shape::sampleDirect
 			sphere_sample_direct(S.rects[esh.rect], ref, sx, sy, out);
 			d = out.d; pdf = out.pdf;
 		} else {
 			V3 p;
-			shape_sample_position(S, em.shape, sx, sy, p, out.n, pdf);
+			shape_sample_position<LEAN>(S, em.shape, sx, sy, p, out.n, pdf);
 			out.p = p;
 			d = p - ref;
 			const float distSquared = dot(d, d);
@@ -187,7 +191,7 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 		const float invDist = 1.0f / out.dist;
 		out.d = d * invDist; out.pdf = 1; out.measure = M_DISCRETE; out.p = em.pos;
 		return em.radiance * (invDist * invDist);
-	} else if (em.type == MTSB_EMITTER_ENVMAP) {                 // EnvironmentMap::sampleDirect (envmap.cpp:525-553)
+	} else if (!LEAN && em.type == MTSB_EMITTER_ENVMAP) {        // EnvironmentMap::sampleDirect (envmap.cpp:525-553)
 		const EnvmapDev &E = *envmap_of(em);
 		V3 value, dl; float pdf;
 		envmap_sample_direction(E, sx, sy, dl, value, pdf);
@@ -222,13 +226,14 @@ __device__ inline V3 emitter_sample_direct(const SceneDev &S, uint32_t e, const 
 
 // Emitter::pdfDirect for a direction that hit emitter `e` (d, dist, n of the hit; measure = solid angle).  `ref` (dRec.ref) is
 // read by sphere emitters only.
+template <bool LEAN = false>
 __device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const V3 &refN, const V3 &d, float dist, const V3 &n, int measure,
 		const V3 &ref = V3()) {
 	const EmitterRec &em = S.emitters[e];
 	if (em.type == MTSB_EMITTER_AREA) {
 		if (dot(d, refN) >= 0 && dot(d, n) < 0) {
 			const ShapeRec &esh = S.shapes[em.shape];
-			if (esh.type == SHAPE_SPHERE) {
+			if (!LEAN && esh.type == SHAPE_SPHERE) {
 				const float pdfSA = sphere_pdf_direct(S.rects[esh.rect], ref, d, dist, n);
 				if (measure == M_SOLID_ANGLE) return pdfSA;
 				if (measure == M_AREA) {
@@ -244,7 +249,7 @@ __device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const 
 		return 0.0f;
 	} else if (em.type == MTSB_EMITTER_POINT) {
 		return measure == M_DISCRETE ? 1.0f : 0.0f;
-	} else if (em.type == MTSB_EMITTER_ENVMAP) {                 // EnvironmentMap::pdfDirect (envmap.cpp:555-565)
+	} else if (!LEAN && em.type == MTSB_EMITTER_ENVMAP) {        // EnvironmentMap::pdfDirect (envmap.cpp:555-565)
 		const EnvmapDev &E = *envmap_of(em);
 		const float pdfSA = envmap_pdf_direction(E, mat3_mul(E.toLocal, d));
 		if (measure == M_SOLID_ANGLE) return pdfSA;
@@ -262,10 +267,11 @@ __device__ inline float emitter_pdf_direct(const SceneDev &S, uint32_t e, const 
 __device__ inline float emitter_pdf_discrete(const SceneDev &S, uint32_t e) { return S.emitters[e].samplingWeight * S.emitterNorm; }
 
 // Scene::sampleEmitterDirect(dRec, sample, testVisibility = false)
+template <bool LEAN = false>
 __device__ inline V3 scene_sample_emitter_direct(const SceneDev &S, const V3 &ref, const V3 &refN, float sx, float sy, DirectSample &out) {
 	float emPdf;
 	const uint32_t index = cdf_sample_reuse(S.emitterCdf, S.emitterCount, sx, emPdf);
-	V3 value = emitter_sample_direct(S, index, ref, refN, sx, sy, out);
+	V3 value = emitter_sample_direct<LEAN>(S, index, ref, refN, sx, sy, out);
 	if (out.pdf != 0) { out.pdf *= emPdf; return value / emPdf; }
 	return v3(0.0f);
 }

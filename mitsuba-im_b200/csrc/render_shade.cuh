@@ -51,7 +51,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 				value = area_emitter_eval(S, emitterId, sf.ns, -d);
 				hitEmitter = true;
 				if (!(flags & PF_DELTA))
-					lumPdf = emitter_pdf_direct(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, emitterId);
+					lumPdf = emitter_pdf_direct<LEAN>(S, emitterId, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, emitterId);
 			}
 		} else if (S.envEmitter >= 0) {
 			if (integ.hideEmitters && !(flags & PF_SCATTERED)) alive = false;
@@ -64,7 +64,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 					hitEmitter = true;
 					if (!(flags & PF_DELTA)) {
 						const V3 n = normalize(env.sphereCenter - (o + d * farT));
-						lumPdf = emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
+						lumPdf = emitter_pdf_direct<LEAN>(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
 					}
 				}
 			}
@@ -113,7 +113,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 			if (smooth || integ.type == MTSB_INTEGRATOR_DIRECT) next2D(rs, sx, sy);
 			if (smooth) {
 				DirectSample ds;
-				const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
+				const V3 value = scene_sample_emitter_direct<LEAN>(S, sf.p, refN, sx, sy, ds);
 				if (!is_zero(value)) {
 					const V3 wo = to_local(sf, ds.d);
 					const V3 bsdfVal = bsdf_eval<LEAN>(bsdf, wi, wo);
