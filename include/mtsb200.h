@@ -346,6 +346,15 @@ MTSB_API int  mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, c
 MTSB_API void mtsb_render_destroy(mtsb_render *r);
 MTSB_API int  mtsb_render_set_camera(mtsb_render *r, const mtsb_camera *camera);
 MTSB_API int  mtsb_render_clear(mtsb_render *r);
+/* Switches the render from the independent sampler to the `sobol` sampler (src/samplers/sobol.cpp:84-251, scramble = 0): sample
+ * index s of pixel (x, y) is the s-th point of the Sobol' sequence that falls into that pixel (sobol::look_up,
+ * src/samplers/sobolseq.h:97-131, over the film size rounded up to a power of two), its first two dimensions place the sample
+ * inside the pixel, every later draw of the path takes the next dimension.  tables = the reference's direction numbers as
+ * 32-bit words: Matrices::matrices32 [1024 x 52], then rows m = 1..16 of vdc_sobol_matrices and of vdc_sobol_matrices_inv
+ * ([52] uint64 each, low word first) — 56576 words; the plugin reads them out of the reference's sobol plugin.  Integrators
+ * that request sample arrays (`direct` with emitterSamples / bsdfSamples other than 1) are refused with this sampler. */
+#define MTSB_SOBOL_TABLE_WORDS (1024 * 52 + 2 * 16 * 52 * 2)
+MTSB_API int  mtsb_render_set_sobol(mtsb_render *r, const uint32_t *tables, size_t words);
 /* Sensor::getMedium(): the medium the camera sits in (-1 = none, the default); volpath_simple starts its paths there. */
 MTSB_API int  mtsb_render_set_camera_medium(mtsb_render *r, int medium);
 /* Gives the render a CUDA stream of its own (default: the context stream).  Renders are independent — own path state,

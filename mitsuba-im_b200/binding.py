@@ -123,7 +123,7 @@ def lib():
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
         "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
-        "mtsb_render_set_camera_medium": (i32, [vp, i32]),
+        "mtsb_render_set_camera_medium": (i32, [vp, i32]), "mtsb_render_set_sobol": (i32, [vp, vp, sz]),
         "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
         "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
@@ -469,6 +469,11 @@ class Render:
 
     def set_camera(self, camera):
         _check(lib().mtsb_render_set_camera(self.h, C.byref(camera)))
+
+    def set_sobol(self, tables):
+        """Switches to the `sobol` sampler; tables = the reference's direction numbers as uint32 words (mtsb_render_set_sobol)."""
+        t = np.ascontiguousarray(tables, dtype=np.uint32)
+        _check(lib().mtsb_render_set_sobol(self.h, _ptr(t), t.shape[0]))
 
     def set_camera_medium(self, medium):
         _check(lib().mtsb_render_set_camera_medium(self.h, int(medium)))

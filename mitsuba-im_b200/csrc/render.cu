@@ -54,6 +54,8 @@ struct GenParams {
 	uint32_t tilesX, pixPadded;
 	uint32_t sppBegin, sppStride, sppPhase, seed;
 	const uint32_t *samples;   // explicit {px,py,sampleIndex,0} list (mtsb_render_samples) or NULL
+	const uint32_t *sobol;     // Sobol' sampler: direction numbers + enumeration tables (mtsb_render_set_sobol) or NULL
+	uint32_t sobolLogRes;      // m_logResolution: log2 of the film size rounded up to a power of two (sobol.cpp:147-158)
 	float diffScale;           // > 0: the scene looks ray differentials up (an `envmap` seen by sensor rays): 1 / sqrt(spp), integrator.cpp:145-146
 };
 
@@ -92,8 +94,33 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	__syncthreads();
 	if (!valid) return;
 	const uint32_t pos = blockBase + warpCount[warp] + __popc(vm & ((1u << lane) - 1u));
-	SamplerState rs; rs.px = px; rs.py = py; rs.sample = sidx; rs.dim = 0; rs.seed = g.seed;
-	float u1, u2; next2D(rs, u1, u2);
+	SamplerState rs; rs.px = px; rs.py = py; rs.sample = sidx; rs.dim = 0; rs.seed = g.seed; rs.sobol = g.sobol;
+	float u1, u2;
+	uint32_t rngY = py, rngZ = sidx;
+	if (g.sobol) {
+		// SobolSampler::generate / setSampleIndex (sobol.cpp:172-215): the sidx-th point of the sequence that falls into this pixel
+		// (sobol::look_up, sobolseq.h:97-131), whose first two dimensions give the position inside the pixel (:240-243)
+		const uint32_t m = g.sobolLogRes;
+		unsigned long long index = sidx;
+		if (m > 1) {
+			const uint32_t *vdc = g.sobol + 1024 * 52 + (m - 1) * 104, *inv = g.sobol + 1024 * 52 + 16 * 104 + (m - 1) * 104;
+			index = (unsigned long long) sidx << (2 * m);
+			unsigned long long delta = 0;
+			uint32_t frame = sidx;
+			for (uint32_t c = 0; frame; frame >>= 1, ++c)
+				if (frame & 1) delta ^= (unsigned long long) vdc[2 * c] | ((unsigned long long) vdc[2 * c + 1] << 32);
+			unsigned long long b = (((unsigned long long) px << m) | py) ^ delta;
+			for (uint32_t c = 0; b; b >>= 1, ++c)
+				if (b & 1) index ^= (unsigned long long) inv[2 * c] | ((unsigned long long) inv[2 * c + 1] << 32);
+		}
+		rngY = (uint32_t) (index >> 32); rngZ = (uint32_t) index;
+		rs.py = rngY; rs.sample = rngZ;
+		u1 = next1D(rs); u2 = next1D(rs);
+		if (index != (unsigned long long) sidx) {
+			const float res = (float) (1u << m);
+			u1 = u1 * res - (float) px; u2 = u2 * res - (float) py;
+		}
+	} else next2D(rs, u1, u2);
 	const float sx = (float) px + u1, sy = (float) py + u2;            // samplePos (integrator.cpp:172)
 	const V3 nearP = xform_projective_point(cam.s2c, v3(sx * cam.invResX, sy * cam.invResY, 0.0f));
 	V3 d, o;
@@ -136,7 +163,7 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	ps.thr[j] = make_float4(1, 1, 1, 1);
 	ps.prev[j] = prev0;
 	ps.misc[j] = make_float4(sx, sy, 0.0f, 0.0f);
-	ps.rng[j] = make_uint4(px, py, sidx, PATH_PACK(rs.dim, 0u, 1u));              // flags = 0, depth = 1; L is started by the first shade
+	ps.rng[j] = make_uint4(px, rngY, rngZ, PATH_PACK(rs.dim, 0u, 1u));              // flags = 0, depth = 1; L is started by the first shade
 	queue[pos] = j;
 }
 

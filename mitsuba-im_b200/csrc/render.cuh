@@ -51,7 +51,10 @@ struct FilmDev {
 	int cropW, cropH;
 };
 
-struct IntegratorDev { int type, maxDepth, rrDepth, strictNormals, hideEmitters, emitterSamples, bsdfSamples, cameraMedium; };
+struct IntegratorDev {
+	int type, maxDepth, rrDepth, strictNormals, hideEmitters, emitterSamples, bsdfSamples, cameraMedium;
+	const uint32_t *sobol;         // Sobol' direction numbers when the render uses that sampler (mtsb_render_set_sobol), else NULL
+};
 
 } // namespace mtsb
 
@@ -61,6 +64,8 @@ struct mtsb_render {
 	mtsb::FilmDev film;
 	mtsb::IntegratorDev integ;
 	uint32_t seed = 0;
+	mtsb::DevBuf<uint32_t> dSobol; // matrices32 [1024 x 52], then vdc_sobol_matrices / _inv rows for m = 1..16 as (lo, hi) words
+	int sobolLogRes = 0;
 	int cameraMedium = -1;         // Sensor::getMedium() (volpath_simple starts its paths in it)
 	cudaStream_t stream = nullptr; // the context stream, or a stream of its own (mtsb_render_private_stream)
 	bool ownStream = false;

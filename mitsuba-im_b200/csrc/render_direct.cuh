@@ -43,7 +43,7 @@ direct_head_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed,
 		const uint32_t slot = QUEUE_SLOT(ps.queueA[i]);
 		const float4 r1 = ps.rayD[slot], r0 = ps.rayO[slot], h = ps.hit[slot];
 		const uint4 rg = ps.rng[slot];
-		SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed;
+		SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
 		const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 		const uint32_t hitSlot = __float_as_uint(h.w);
 		V3 Li = v3(0.0f);

@@ -263,7 +263,7 @@ int mtsb_render_create(mtsb_scene *scene, const mtsb_camera *camera, const mtsb_
 	ig.type = integrator->type; ig.maxDepth = integrator->max_depth; ig.rrDepth = integrator->rr_depth;
 	ig.strictNormals = integrator->strict_normals; ig.hideEmitters = integrator->hide_emitters;
 	ig.emitterSamples = integrator->emitter_samples; ig.bsdfSamples = integrator->bsdf_samples;
-	ig.cameraMedium = -1;
+	ig.cameraMedium = -1; ig.sobol = nullptr;
 	if (ig.type == MTSB_INTEGRATOR_DIRECT) { ig.maxDepth = 2; ig.rrDepth = 1 << 30; }   // direct(1,1) == one-bounce path
 	if (ig.maxDepth == 0) { delete r; MTSB_FAIL(MTSB_EINVAL, "mtsb_render_create: maxDepth must be -1 or > 0"); }
 	r->seed = (uint32_t) seed;
@@ -321,6 +321,23 @@ int mtsb_render_private_stream(mtsb_render *r) {
 	return 0;
 }
 
+int mtsb_render_set_sobol(mtsb_render *r, const uint32_t *tables, size_t words) {
+	if (!r || !tables) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_sobol: NULL argument");
+	if (words != MTSB_SOBOL_TABLE_WORDS) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_sobol: %zu table words (%d expected)", words, (int) MTSB_SOBOL_TABLE_WORDS);
+	if (fan_mode(r)) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_set_sobol: sample arrays (direct with emitterSamples / bsdfSamples != 1) are not available with the sobol sampler");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	MTSB_CHECK(r->dSobol.upload(tables, words, r->stream));
+	MTSB_CUDA(cudaStreamSynchronize(r->stream));
+	// setFilmResolution(film->getCropSize(), bucketed) (sobol.cpp:147-158): math::roundToPowerOfTwo + log2i
+	uint32_t res = 1, lg = 0;
+	while (res < (uint32_t) std::max(r->film.cropW, r->film.cropH)) { res <<= 1; ++lg; }
+	if (lg > 16) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_sobol: film larger than 65536 pixels a side");
+	r->sobolLogRes = (int) lg;
+	r->integ.sobol = r->dSobol.ptr;
+	destroy_bounce_graph(r);                     // the integrator block is a kernel argument of the graph's nodes
+	return 0;
+}
+
 int mtsb_render_set_camera_medium(mtsb_render *r, int medium) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: NULL argument");
 	if (medium < -1 || medium >= (int) r->scene->media.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: medium %d unknown", medium);
@@ -356,6 +373,7 @@ int mtsb_render_pass(mtsb_render *r, uint32_t spp_begin, uint32_t spp_count, uin
 	g.pixPadded = g.tilesX * ((g.h + 3) / 4) * 32;
 	g.sppBegin = spp_begin; g.sppStride = sample_stride; g.sppPhase = sample_phase; g.seed = r->seed;
 	g.samples = nullptr;
+	g.sobol = r->integ.sobol; g.sobolLogRes = (uint32_t) r->sobolLogRes;
 	g.diffScale = (r->scene->envmapEmitter >= 0 || !r->scene->texRecords.empty()) ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	const unsigned long long total = (unsigned long long) g.pixPadded * spp_count;
 	// chunks hold whole sample planes when possible so that a warp covers an 8x4 pixel tile of one sample index
@@ -515,6 +533,7 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	if (pos_out) MTSB_CHECK(dP.alloc(n * 2));
 	GenParams g; memset(&g, 0, sizeof(g));
 	g.count = (uint32_t) n; g.samples = dS.ptr; g.seed = r->seed; g.pixPadded = 1; g.tilesX = 1; g.sppStride = 1;
+	g.sobol = r->integ.sobol; g.sobolLogRes = (uint32_t) r->sobolLogRes;
 	g.diffScale = (r->scene->envmapEmitter >= 0 || !r->scene->texRecords.empty()) ? 1.0f / sqrtf((float) std::max(1u, spp_total)) : 0.0f;
 	MTSB_CHECK(run_chunk(r, g, dO.ptr, pos_out ? dP.ptr : nullptr));
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st));

@@ -148,7 +148,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 	float4 thr4 = ps.thr[slot];
 	const float4 prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);
 	float eta = thr4.w;
@@ -308,7 +308,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 	float4 thr4 = ps.thr[slot];
 	const float4 prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);
 	float eta = thr4.w;

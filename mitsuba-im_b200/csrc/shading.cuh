@@ -26,7 +26,17 @@ enum { M_SOLID_ANGLE = 1, M_LENGTH = 2, M_AREA = 3, M_DISCRETE = 4 };
 // Philox4x32-10, counter {px, py, sampleIndex, dim/4}, key {seed, 0x6d747362}: the stream oracle/ctrsampler.cpp feeds
 // the reference.  Replaces IndependentSampler::next1D/next2D (src/samplers/independent.cpp:51-106); the float
 // conversion is Random::nextFloat's 23-bit mantissa trick (src/libcore/random.cpp:626-635).
-struct SamplerState { uint32_t px, py, sample, dim, seed; };
+// `sobol` != NULL selects the Sobol' sampler (src/samplers/sobol.cpp over sobolseq.h): the 1024 x 52 direction numbers; the path's
+// 64-bit sequence index then travels in (py, sample) = (high, low) and `dim` is the Sobol' dimension.
+struct SamplerState { uint32_t px, py, sample, dim, seed; const uint32_t *sobol; };
+
+// sobol::sampleSingle (sobolseq.h:43-59), scramble = 0
+__device__ inline float sobol_sample(const uint32_t *matrices, unsigned long long index, uint32_t dimension) {
+	uint32_t result = 0;
+	for (uint32_t i = min(dimension, 1023u) * 52u; index; index >>= 1, ++i)
+		if (index & 1) result ^= __ldg(matrices + i);
+	return fminf(result * (1.0f / 4294967296.0f), 0.999999940395355225f);
+}
 
 __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]) {
 	#pragma unroll
@@ -40,6 +50,7 @@ __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 }
 
 __device__ inline float next1D(SamplerState &s) {
+	if (s.sobol) return sobol_sample(s.sobol, ((unsigned long long) s.py << 32) | s.sample, s.dim++);      // SobolSampler::next1D (sobol.cpp:218-228)
 	uint32_t w[4];
 	philox4x32_10(s.px, s.py, s.sample, s.dim >> 2, s.seed, 0x6d747362u, w);
 	const uint32_t word = (s.dim & 3) == 0 ? w[0] : ((s.dim & 3) == 1 ? w[1] : ((s.dim & 3) == 2 ? w[2] : w[3]));
@@ -47,6 +58,13 @@ __device__ inline float next1D(SamplerState &s) {
 	return __uint_as_float((word >> 9) | 0x3f800000u) - 1.0f;
 }
 __device__ inline void next2D(SamplerState &s, float &a, float &b) {
+	if (s.sobol) {
+		// SobolSampler::next2D (:230-251).  Dimensions [m_arrayStartDim, m_arrayEndDim) = [5, 5 + requests) are reserved for sample
+		// arrays, and the test `m_dimension + 1 >= m_arrayStartDim && m_dimension < m_arrayEndDim` moves a pair that would start at
+		// dimension 4 to 5 even when nothing is reserved.  (The pixel-relative first pair is generate_kernel's business.)
+		if (s.dim == 4) s.dim = 5;
+		a = next1D(s); b = next1D(s); return;
+	}
 	if ((s.dim & 3) < 3) {   // both words come from the same Philox block
 		uint32_t w[4];
 		philox4x32_10(s.px, s.py, s.sample, s.dim >> 2, s.seed, 0x6d747362u, w);

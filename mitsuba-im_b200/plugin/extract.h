@@ -19,6 +19,7 @@
 #include <mitsuba/render/mipmap.h>
 #include "microfacet.h"          /* src/bsdfs/microfacet.h: MicrofacetDistribution(props) reads alpha / distribution / sampleVisible */
 #include "rtrans.h"              /* src/bsdfs/rtrans.h: RoughTransmittance, header-only, as roughplastic.cpp includes it */
+#include "sobolseq.h"            /* src/samplers/sobolseq.h: sobol::Matrices (the tables are linked in from sobolseq.cpp) */
 #include "ior.h"                 /* src/bsdfs/ior.h: lookupIOR(), header-only, as the BSDF plugins include it */
 #include "../../include/mtsb200.h"
 #include <map>
@@ -52,6 +53,23 @@ struct RoughTransmittanceAccess : public RoughTransmittance {
 	const Float *trans() const { return m_trans; }
 	size_t thetaSamples() const { return m_thetaSamples; }
 };
+
+/// Switches a render to the `sobol` sampler when the scene uses it (src/samplers/sobol.cpp); other samplers keep the independent
+/// stream (or the shared counter stream of oracle/ctrsampler.cpp).  Low-discrepancy samplers the device does not have are refused.
+static void configureDeviceSampler(mtsb_render *r, const Sampler *sampler) {
+	const std::string cls = sampler->getClass()->getName();
+	if (cls == "SobolSampler") {
+		if (sampler->getProperties().getSize("scramble", 0) != 0) SLog(EError, "gpupath: the sobol sampler with a scramble value is outside the GPU subset");
+		std::vector<uint32_t> t;
+		t.reserve(MTSB_SOBOL_TABLE_WORDS);
+		for (uint32_t i = 0; i < sobol::Matrices::num_dimensions * sobol::Matrices::size; ++i) t.push_back(sobol::Matrices::matrices32[i]);
+		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { const uint64_t v = sobol::Matrices::vdc_sobol_matrices[m][c]; t.push_back((uint32_t) v); t.push_back((uint32_t) (v >> 32)); }
+		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { const uint64_t v = sobol::Matrices::vdc_sobol_matrices_inv[m][c]; t.push_back((uint32_t) v); t.push_back((uint32_t) (v >> 32)); }
+		MTSB_CALL(mtsb_render_set_sobol(r, t.data(), t.size()));
+	} else if (cls == "LowDiscrepancySampler" || cls == "HaltonSampler" || cls == "HammersleySampler" || cls == "StratifiedSampler") {
+		SLog(EError, "gpupath: sampler \"%s\" is outside the GPU subset (independent, sobol)", cls.c_str());
+	}
+}
 
 /// A `bitmap` texture as the device takes it: the MIP pyramid the texture's own constructor builds (src/textures/bitmap.cpp:248-305),
 /// rebuilt here with the reference's Bitmap / MIPMap classes from the texture's file, plus the Texture2D parameters.

@@ -147,6 +147,7 @@ public:
 		for (int g = 0; g < m_gpus; ++g) {
 			MTSB_CALL(mtsb_render_create(device(g, scene).scene, &cam, &fd, &id, seedFor(sampler), &renders[g]));
 			MTSB_CALL(mtsb_render_set_camera_medium(renders[g], mediumIndex(collectMedia(scene), sensor->getMedium())));
+			configureDeviceSampler(renders[g], sampler);
 		}
 		const size_t pixels = (size_t) film->getCropSize().x * film->getCropSize().y;
 		const uint32_t pass = m_sppPerPass > 0 ? (uint32_t) m_sppPerPass : (uint32_t) std::max<size_t>(1, ((size_t) 1 << 23) / std::max<size_t>(pixels, 1));

@@ -63,6 +63,7 @@ mtsb_render *GPUResponsiveIntegrator::renderFor(int gpu, const Scene &scene, con
 	mtsb_render *r = NULL;
 	MTSB_CALL(mtsb_render_create(dev.scene, &cam, &fd, &id, p->seedFor(&sampler), &r));
 	MTSB_CALL(mtsb_render_set_camera_medium(r, mediumIndex(collectMedia(&scene), sensor.getMedium())));
+	configureDeviceSampler(r, &sampler);
 	MTSB_CALL(mtsb_render_private_stream(r));
 	MTSB_CALL(mtsb_render_reserve(r, maxPass(target)));
 	LockGuard lock(p->m_mutex);

@@ -16,6 +16,8 @@ from . import binding as B
 EPSILON = 1e-4
 # the renderer's data/microfacet directory (rough-transmittance tables read by `roughplastic`, src/bsdfs/rtrans.h:95-97)
 MICROFACET_DIR = os.environ.get("MTSB_MICROFACET_DIR")
+# the direction numbers of the `sobol` sampler as uint32 words (include/mtsb200.h: mtsb_render_set_sobol); set by the host
+SOBOL_TABLES = None
 SHADOW_EPSILON = 1e-3
 
 
@@ -456,6 +458,10 @@ class SceneDesc:
         rd = B.Render(scene, self.camera(), self.film(channels=channels), self.integrator_desc(), seed=self.sampler["seed"] if seed is None else seed)
         if self.camera_medium is not None:
             rd.set_camera_medium(self.camera_medium)
+        if self.sampler["kind"] == "sobol":
+            if SOBOL_TABLES is None:
+                raise ValueError("sobol sampler: set scenes.SOBOL_TABLES (the reference's direction numbers, binding.Render.set_sobol)")
+            rd.set_sobol(SOBOL_TABLES)
         return rd
 
     # -- reference back end ----------------------------------------------------------------------
@@ -544,7 +550,9 @@ class SceneDesc:
             else:
                 out.append('<sensor type="perspective"><float name="fov" value="%r"/><string name="fovAxis" value="%s"/>' % (s["fov"], s["fov_axis"]))
             out.append('<transform name="toWorld">%s</transform>' % _mat_xml(s["to_world"]))
-            if sm["kind"] == "ctr":
+            if sm["kind"] == "sobol":
+                out.append('<sampler type="sobol"><integer name="sampleCount" value="%d"/></sampler>' % sm["spp"])
+            elif sm["kind"] == "ctr":
                 out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/></sampler>' % (sm["spp"], sm["seed"]))
             else:
                 out.append('<sampler type="independent"><integer name="sampleCount" value="%d"/></sampler>' % sm["spp"])

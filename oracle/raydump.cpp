@@ -35,6 +35,7 @@
 #include <mitsuba/core/fstream.h>
 #include <mitsuba/core/bitmap.h>
 #include <mitsuba/render/mipmap.h>
+#include "sobolseq.h"            /* src/samplers/sobolseq.h: the Sobol direction numbers (raydump sobol) */
 #include <thread>
 #include <vector>
 #include <chrono>
@@ -308,6 +309,21 @@ public:
 		return 0;
 	}
 
+	/// The tables of the `sobol` sampler (src/samplers/sobolseq.h:30-36) as raw uint32 words: 1024 x 52 matrices32, then the 52-column
+	/// rows of vdc_sobol_matrices and vdc_sobol_matrices_inv for m = 1..16 as (lo, hi) pairs
+	int sobolTables(int argc, char **argv) {
+		if (argc < 3) { cout << "sobol <out>" << endl; return 1; }
+		std::vector<uint32_t> out;
+		for (uint32_t i = 0; i < sobol::Matrices::num_dimensions * sobol::Matrices::size; ++i) out.push_back(sobol::Matrices::matrices32[i]);
+		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { uint64_t v = sobol::Matrices::vdc_sobol_matrices[m][c]; out.push_back((uint32_t) v); out.push_back((uint32_t) (v >> 32)); }
+		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { uint64_t v = sobol::Matrices::vdc_sobol_matrices_inv[m][c]; out.push_back((uint32_t) v); out.push_back((uint32_t) (v >> 32)); }
+		FILE *f = fopen(argv[2], "wb");
+		if (!f) return 1;
+		fwrite(out.data(), 4, out.size(), f); fclose(f);
+		cout << "sobol: " << out.size() << " words" << endl;
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -379,6 +395,7 @@ public:
 		if (!strcmp(argv[1], "all")) return all(argc, argv);
 		if (!strcmp(argv[1], "mipmap")) return mipmap(argc, argv);
 		if (!strcmp(argv[1], "mipmap3")) return mipmap3(argc, argv);
+		if (!strcmp(argv[1], "sobol")) return sobolTables(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

@@ -225,6 +225,13 @@ def texture_cases(td):
     li_case(td, "textured_direct", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=83, pyramids=pyramids, kind="direct"))
 
 
+def sobol_cases(td):
+    """The `sobol` sampler (src/samplers/sobol.cpp): the reference's own plugin drives `path` on the materials scene (48 x 32 -> the
+    enumeration works on a 64 x 64 grid) and on the Cornell box at a non-power-of-two size; deterministic, no shared sampler needed."""
+    li_case(td, "sobol_materials", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="sobol", seed=0))
+    li_case(td, "sobol_cornell", S.cornell_box(40, 24, spp=8, max_depth=5, sampler="sobol", seed=0))
+
+
 def all_case(td):
     """Scene::rayIntersectAll x2 (src/librender/scene.cpp:716-792; oracle/raydump.cpp `all`): the kd-tree shapes plus the special
     shapes of Scene::initializeBidirectional — here the aperture disk of the thinlens sensor and the bounding sphere of the
@@ -274,6 +281,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "sobol":            # round 2
+        with tempfile.TemporaryDirectory() as td:
+            sobol_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "texture":          # round 2
         with tempfile.TemporaryDirectory() as td:
             texture_cases(td)
@@ -325,3 +336,4 @@ if __name__ == "__main__":
         analytic_lights_cases(td)
         envmap_cases(td)
         texture_cases(td)
+        sobol_cases(td)

@@ -151,6 +151,20 @@ def test_roughplastic_through_the_loader(tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_sobol_sampler_through_the_loader(pkg, tmp_path):
+    """`sobol` sampler: the plugin sees the scene's SobolSampler and hands the reference's direction numbers to the
+    device (plugin/extract.h: configureDeviceSampler); deterministic on both sides, so the stock `path` render and the GPU render of
+    the same file agree pixel by pixel — classic scheduler, and the responsive one (which enumerates the same samples)."""
+    sd = pkg.scenes.materials_scene(64, 48, spp=8, max_depth=6, sampler="sobol", seed=0)
+    xml = sd.to_xml(str(tmp_path), "sobol")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
+    assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
 def test_bitmap_textures_through_the_loader(pkg, tmp_path):
     """`bitmap` textures on diffuse reflectances, instantiated by the stock XML loader from a PFM file: the plugin
     reads the texture out of the BSDF (plugin/extract.h) and rebuilds its MIP pyramid with the reference's own classes — EWA on a

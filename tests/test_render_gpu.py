@@ -27,6 +27,15 @@ def _tex_pyramids(golden):
     return out
 
 
+def _sobol_tables(tmp_path):
+    """The reference's Sobol' direction numbers, dumped by oracle/raydump.cpp `sobol` (test infrastructure)."""
+    import subprocess
+    out = str(tmp_path / "sobol.bin")
+    r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "sobol", out], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0 and os.path.exists(out), r.stdout[-2000:]
+    return np.fromfile(out, np.uint32)
+
+
 def _close(a, b, rtol, atol):
     return np.abs(a - b) <= atol + rtol * np.abs(b)
 
@@ -233,6 +242,36 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     dev = film[b:film.shape[0] - b, b:film.shape[1] - b, 0:3] / wgt[..., None]
     assert np.allclose(dev[nominal], img[nominal], rtol=1e-4, atol=1e-5)
     assert stats["paths"] == img.shape[0] * img.shape[1] * spp * 2
+
+
+@pytest.mark.parametrize("name", ["sobol_materials", "sobol_cornell"])
+def test_sobol_sampler_matches_reference_per_sample(pkg, ctx, golden, tmp_path, name):
+    """The `sobol` sampler (src/samplers/sobol.cpp:172-251 over sobolseq.h): pixel-wise enumeration of the sequence (look_up on the
+    film size rounded up to a power of two), the first two dimensions as the position inside the pixel, one dimension per later
+    draw — against images the reference's own sobol plugin rendered through `path` (make_golden_render.sobol_cases)."""
+    S = pkg.scenes
+    S.SOBOL_TABLES = _sobol_tables(tmp_path)
+    g = golden("li_%s.npz" % name)
+    ref = g["image"]
+    spp = int(g["spp"])
+    sd = (S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="sobol", seed=0) if name == "sobol_materials"
+          else S.cornell_box(40, 24, spp=spp, max_depth=5, sampler="sobol", seed=0))
+    for tail in (TAIL_OFF, TAIL_ALL):
+        L, film, stats = _li_image(pkg, ctx, sd, tail=tail)
+        # Sobol' points are dyadic: one pixel in 64 owns a sample exactly on its corner, which the box filter (radius 0.5 + 1e-5,
+        # src/rfilters/box.cpp:33-40) also splats into the three pixels that share the corner.  The reference image is a developed
+        # film, so the comparison is film against film (ImageBlock::put on both sides) ...
+        b = sd.film().border
+        wgt = film[b:film.shape[0] - b, b:film.shape[1] - b, 4]
+        dev = film[b:film.shape[0] - b, b:film.shape[1] - b, 0:3] / wgt[..., None]
+        ok = _close(dev, ref, 2e-3, 2e-4).all(axis=2)
+        print(name, "tail", tail, "pixels within tolerance: %.4f" % ok.mean(), "pixels with a neighbour's corner sample: %.4f" % (~np.isclose(wgt, np.median(wgt), rtol=1e-6)).mean())
+        assert ok.mean() >= 0.97, "only %.4f of the pixels agree" % ok.mean()
+        assert abs(dev.mean() - ref.mean()) <= 0.01 * ref.mean()
+        # ... and the per-sample radiances average to the film wherever a pixel holds only its own samples
+        img = L[..., 0:3].mean(axis=2)
+        nominal = np.isclose(wgt, np.median(wgt), rtol=1e-6)
+        assert nominal.mean() > 0.9 and np.allclose(dev[nominal], img[nominal], rtol=1e-4, atol=1e-5)
 
 
 def _imageblock_put(shape, border, radius, table, pos, values):
