@@ -24,7 +24,7 @@ __device__ __forceinline__ void shade_path(const SceneDev &S, const PathState &p
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
 	float4 thr4 = ps.thr[slot], prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = LEAN ? nullptr : integ.sobol;      // a render with the sobol sampler runs the full kernel
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);          // Li: what THIS bounce adds
 	float eta = thr4.w;

@@ -142,6 +142,7 @@ __device__ __forceinline__ uint32_t vol_max_interactions(const IntegratorDev &in
 }
 
 // One iteration of the while loop of SimpleVolumetricPathTracer::Li for the path in `slot`.
+template <bool PLAIN = false>
 __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, VolOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
@@ -186,7 +187,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 			float sx, sy; next2D(rs, sx, sy);
 			if (S.emitterCount > 0) {
 				DirectSample ds;
-				const V3 value = scene_sample_emitter_direct(S, ms.p, v3(0.0f), sx, sy, ds);
+				const V3 value = scene_sample_emitter_direct<PLAIN>(S, ms.p, v3(0.0f), sx, sy, ds);
 				if (ds.pdf != 0 && !is_zero(value)) {
 					const V3 c = thr * value * phase_eval(m, -d, ds.d);
 					const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
@@ -208,8 +209,8 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 		if (!valid) {
 			if ((vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)) && S.envEmitter >= 0) {
 				V3 rx = v3(0.0f), ry = v3(0.0f);           // only the sensor ray carries differentials (generate_kernel: prev / L)
-				if (first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
-				V3 value = thr * env_radiance(S, d, first, rx, ry);
+				if (!PLAIN && first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
+				V3 value = thr * env_radiance<PLAIN>(S, d, first, rx, ry);
 				// rRec.medium->evalTransmittance(ray): the ray's own [mint, maxt] = an infinite segment
 				if (medium >= 0) value *= medium_transmittance(S.media[medium], INFINITY);
 				Li += value;
@@ -221,7 +222,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 			const V3 wi = to_local(sf, -d);
 			if (integ.strictNormals && -dot(sf.ng, d) * wi.z < 0) out.alive = false;          // :192-195 (no depth test here: recursiveType below ends the path)
 			if (out.alive) {
-				const BsdfRec bsdf = load_bsdf(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
+				const BsdfRec bsdf = load_bsdf<PLAIN>(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
 				const uint32_t btype = bsdf_type(bsdf);
 				// ---- direct illumination (:201-227): no MIS, one attenuated emitter sample
 				if ((vf & VF_REST) && (btype & B_SMOOTH)) {
@@ -229,7 +230,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 					float sx, sy; next2D(rs, sx, sy);
 					if (S.emitterCount > 0) {
 						DirectSample ds;
-						const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
+						const V3 value = scene_sample_emitter_direct<PLAIN>(S, sf.p, refN, sx, sy, ds);
 						if (ds.pdf != 0 && !is_zero(value)) {
 							const V3 wo = to_local(sf, ds.d);
 							const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
@@ -302,6 +303,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 // function therefore begins with the TAIL of the previous iteration — the emitter found at (or behind) the first hit, then
 // the Russian roulette that closes that iteration — as shade_path does for `path`.  Behind an index-matched first hit the walk
 // goes on in connect_vol_kernel (a VQ_LOOK queue entry).
+template <bool PLAIN = false>
 __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, VolOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
@@ -348,7 +350,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 					if (isEmitter) {                                  // dRec.setQuery(ray, its); value = transmittance * Le
 						const V3 value = T0 * area_emitter_eval(S, sh.emitter, sf.ns, -d);
 						if (!is_zero(value)) {
-							const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, sh.emitter, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, sh.emitter);
+							const float emitterPdf = delta ? 0.0f : emitter_pdf_direct<PLAIN>(S, sh.emitter, refN, d, h.x, sf.ns, M_SOLID_ANGLE, o) * emitter_pdf_discrete(S, sh.emitter);
 							Li += thr * value * mi_weight(samplePdf, emitterPdf);
 						}
 					}
@@ -361,10 +363,10 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 				const EmitterRec &env = S.emitters[S.envEmitter];
 				float nearT, farT;                                  // fillDirectSamplingRecord (constant.cpp:238-256)
 				if (sphere_intersect(env.sphereCenter, env.sphereRadius, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
-					const V3 value = T0 * env_radiance(S, d);
+					const V3 value = T0 * env_radiance<PLAIN>(S, d);
 					if (!is_zero(value)) {
 						const V3 n = normalize(env.sphereCenter - (o + d * farT));
-						const float emitterPdf = delta ? 0.0f : emitter_pdf_direct(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
+						const float emitterPdf = delta ? 0.0f : emitter_pdf_direct<PLAIN>(S, S.envEmitter, refN, d, farT, n, M_SOLID_ANGLE) * emitter_pdf_discrete(S, S.envEmitter);
 						Li += thr * value * mi_weight(samplePdf, emitterPdf);
 					}
 				}
@@ -398,7 +400,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 					float sx, sy; next2D(rs, sx, sy);
 					if (S.emitterCount > 0) {
 						DirectSample ds;
-						const V3 value = scene_sample_emitter_direct(S, ms.p, v3(0.0f), sx, sy, ds);
+						const V3 value = scene_sample_emitter_direct<PLAIN>(S, ms.p, v3(0.0f), sx, sy, ds);
 						if (ds.pdf != 0 && !is_zero(value)) {
 							const float phaseVal = phase_eval(m, -d, ds.d);
 							if (phaseVal != 0) {
@@ -424,8 +426,8 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 			if (!valid) {
 				if ((vf & VF_EMITTED) && (!integ.hideEmitters || (vf & VF_SCATTERED)) && S.envEmitter >= 0) {
 					V3 rx = v3(0.0f), ry = v3(0.0f);           // only the sensor ray carries differentials (generate_kernel: prev / L)
-					if (first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
-					V3 value = thr * env_radiance(S, d, first, rx, ry);
+					if (!PLAIN && first && S.emitters[S.envEmitter].type == MTSB_EMITTER_ENVMAP) { const float4 l = ps.L[slot]; rx = v3(prev.x, prev.y, prev.z); ry = v3(l.x, l.y, l.z); }
+					V3 value = thr * env_radiance<PLAIN>(S, d, first, rx, ry);
 					if (medium >= 0) value *= medium_transmittance(S.media[medium], INFINITY);
 					Li += value;
 				}
@@ -437,7 +439,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 				const V3 wi = to_local(sf, -d);
 				if (out.alive && integ.strictNormals && -dot(sf.ng, d) * wi.z < 0) out.alive = false;
 				if (out.alive) {
-					const BsdfRec bsdf = load_bsdf(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
+					const BsdfRec bsdf = load_bsdf<PLAIN>(S, sh.bsdf, sf, hitSlot, o, first, prev, ps.L + slot);
 					const uint32_t btype = bsdf_type(bsdf);
 					const V3 refN = (btype & (B_TRANSMISSION | B_BACK)) == 0 ? sf.ns : v3(0.0f);
 					// ---- emitter sampling with MIS (:212-247)
@@ -445,7 +447,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 						float sx, sy; next2D(rs, sx, sy);
 						if (S.emitterCount > 0) {
 							DirectSample ds;
-							const V3 value = scene_sample_emitter_direct(S, sf.p, refN, sx, sy, ds);
+							const V3 value = scene_sample_emitter_direct<PLAIN>(S, sf.p, refN, sx, sy, ds);
 							if (ds.pdf != 0 && !is_zero(value)) {
 								const V3 wo = to_local(sf, ds.d);
 								const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
@@ -515,8 +517,8 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 #ifndef MTSB_VOLSHADE_MIN_BLOCKS
 #define MTSB_VOLSHADE_MIN_BLOCKS 1
 #endif
-// MIS = 0: volpath_simple (volshade_path), 1: volpath (volmis_path)
-template <int MIS = 0>
+// MIS = 0: volpath_simple (volshade_path), 1: volpath (volmis_path); PLAIN: scene->plain (no envmap / textures / analytic lights)
+template <int MIS = 0, bool PLAIN = false>
 __global__ void __launch_bounds__(RENDER_BLOCK, MTSB_VOLSHADE_MIN_BLOCKS)
 volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
@@ -528,8 +530,8 @@ volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 		const uint32_t slot = QUEUE_SLOT(queueIn[i]);
 		if (__float_as_uint(ps.hit[slot].w) == SUSPENDED_SLOT) { queueOut[warp_append(countOut)] = slot | QUEUE_RESUME; continue; }
 		VolOut vo;
-		if (MIS) volmis_path(S, ps, integ, seed, slot, vo);
-		else volshade_path(S, ps, integ, seed, slot, vo);
+		if (MIS) volmis_path<PLAIN>(S, ps, integ, seed, slot, vo);
+		else volshade_path<PLAIN>(S, ps, integ, seed, slot, vo);
 		if (vo.alive) queueOut[warp_append(countOut)] = slot;
 		for (int k = 0; k < 2; ++k)
 			if (k < vo.nReq) {

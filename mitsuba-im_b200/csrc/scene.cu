@@ -619,9 +619,10 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	MTSB_CHECK(scene->dEmitters.upload(scene->emitters, st));
 	D.emitters = scene->dEmitters.ptr;
 	MTSB_CUDA(cudaStreamSynchronize(st));
-	scene->lean = !(ctx->shadeLean == 0) && scene->envmapEmitter < 0 && scene->texRecords.empty();
+	scene->plain = scene->envmapEmitter < 0 && scene->texRecords.empty();
 	for (const ShapeRec &sh : scene->shapes)
-		if (sh.emitter >= 0 && (sh.type == SHAPE_SPHERE || sh.type == SHAPE_DISK)) scene->lean = false;      // emitter.cuh: LEAN
+		if (sh.emitter >= 0 && (sh.type == SHAPE_SPHERE || sh.type == SHAPE_DISK)) scene->plain = false;     // emitter.cuh: LEAN
+	scene->lean = !(ctx->shadeLean == 0) && scene->plain;
 	for (const BsdfRec &b : scene->bsdfs) {
 		const int t = b.type & 0xff;
 		const bool ok = t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_NULL || t == MTSB_BSDF_DIELECTRIC ||
