@@ -2,7 +2,8 @@
 // (GenericKDTree::buildInternal, include/mitsuba/render/gkdtree.h:958-1263) and of the TriAccel records
 // (ShapeKDTree::build, src/librender/skdtree.cpp:68-110; TriAccel::load, include/mitsuba/render/triaccel.h:61-94).
 //
-// Pipeline (all on the context stream, no host round trips except the per-level queue size):
+// Pipeline (all on the context stream; the PLOC rounds and the collapse levels read their counts from the device, the host
+// looks at them once per batch of rounds / levels):
 //   prim_bounds   : AABB + centroid of every primitive (triangle or analytic rectangle), scene AABB reduction
 //   morton + sort : 63-bit Morton codes of centroids, cub::DeviceRadixSort
 //   binary tree   : LBVH (Karras 2012) or PLOC (Meister & Bittner 2018) over the sorted primitives
@@ -198,9 +199,13 @@ __device__ __forceinline__ float box_area(float4 l, float4 h) {
 	return 2.0f * (dx * dy + dy * dz + dz * dx);
 }
 
-__global__ void ploc_nearest_kernel(int m, const int *cluster, const float4 *blo, const float4 *bhi, int *nearest) {
-	int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= m) return;
+// The merge rounds are driven from the device: every kernel reads the live cluster count m from mPtr and is launched over
+// an upper bound `mBound` the host knew a few rounds ago, so a round needs no host round trip (the host reads m back once
+// per PLOC_BATCH rounds to shrink the grids); below PLOC_TAIL clusters one CTA finishes the tree by itself (ploc_tail_kernel).
+#define PLOC_BATCH 4
+#define PLOC_TAIL 1024
+
+__device__ __forceinline__ int ploc_nearest(int i, int m, const int *cluster, const float4 *blo, const float4 *bhi) {
 	float4 l = blo[cluster[i]], h = bhi[cluster[i]];
 	float best = INFINITY; int bestJ = -1;
 	int j0 = max(0, i - PLOC_RADIUS), j1 = min(m - 1, i + PLOC_RADIUS);
@@ -212,14 +217,12 @@ __global__ void ploc_nearest_kernel(int m, const int *cluster, const float4 *blo
 		float a = box_area(ml, mh);
 		if (a < best || (a == best && j < bestJ)) { best = a; bestJ = j; }
 	}
-	nearest[i] = bestJ;
+	return bestJ;
 }
 
-// merge mutual pairs (lower index of the pair creates the node); writes cluster id or -1 into out
-__global__ void ploc_merge_kernel(int m, const int *cluster, const int *nearest, float4 *blo, float4 *bhi,
-		int2 *children, int *parent, int *nodeCounter, int *out, int *validFlag) {
-	int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= m) return;
+// merge mutual pairs (lower index of the pair creates the node); returns the cluster id that stays at position i or -1
+__device__ __forceinline__ int ploc_merge(int i, const int *cluster, const int *nearest, float4 *blo, float4 *bhi,
+		int2 *children, int *parent, int *nodeCounter) {
 	int j = nearest[i];
 	int res = cluster[i];
 	if (j >= 0 && nearest[j] == i) {
@@ -237,14 +240,67 @@ __global__ void ploc_merge_kernel(int m, const int *cluster, const int *nearest,
 			res = -1;
 		}
 	}
+	return res;
+}
+
+__global__ void ploc_nearest_kernel(const int *mPtr, const int *cluster, const float4 *blo, const float4 *bhi, int *nearest) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int m = *mPtr;
+	if (i >= m) return;
+	nearest[i] = ploc_nearest(i, m, cluster, blo, bhi);
+}
+
+// positions m .. mBound-1 are dead: their flag is cleared so the scan over mBound items counts the live ones only
+__global__ void ploc_merge_kernel(const int *mPtr, int mBound, const int *cluster, const int *nearest, float4 *blo, float4 *bhi,
+		int2 *children, int *parent, int *nodeCounter, int *out, int *validFlag) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= mBound) return;
+	if (i >= *mPtr) { validFlag[i] = 0; return; }
+	int res = ploc_merge(i, cluster, nearest, blo, bhi, children, parent, nodeCounter);
 	out[i] = res;
 	validFlag[i] = res >= 0 ? 1 : 0;
 }
 
-__global__ void ploc_compact_kernel(int m, const int *in, const int *validFlag, const int *scan, int *outCluster) {
+// the last position also publishes the next round's cluster count (mNext is the other slot of the ping-pong pair, no
+// kernel of this round reads it)
+__global__ void ploc_compact_kernel(const int *mPtr, int mBound, const int *in, const int *validFlag, const int *scan, int *outCluster, int *mNext) {
 	int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= m) return;
-	if (validFlag[i]) outCluster[scan[i]] = in[i];
+	if (i >= mBound) return;
+	if (i == mBound - 1) *mNext = scan[i] + validFlag[i];
+	if (i < *mPtr && validFlag[i]) outCluster[scan[i]] = in[i];
+}
+
+// one CTA runs every remaining round over <= PLOC_TAIL clusters: same nearest / merge rules, the compaction is a block scan
+__global__ void __launch_bounds__(PLOC_TAIL) ploc_tail_kernel(const int *mPtr, const int *cluster, float4 *blo, float4 *bhi,
+		int2 *children, int *parent, int *nodeCounter) {
+	__shared__ int cl[2][PLOC_TAIL];
+	__shared__ int nearest[PLOC_TAIL];
+	__shared__ int warpOffset[PLOC_TAIL / 32];
+	__shared__ int total;
+	const int i = threadIdx.x, lane = i & 31, warp = i >> 5;
+	int m = min(*mPtr, PLOC_TAIL);
+	if (i < m) cl[0][i] = cluster[i];
+	int cur = 0;
+	__syncthreads();
+	while (m > 1) {
+		if (i < m) nearest[i] = ploc_nearest(i, m, cl[cur], blo, bhi);
+		__syncthreads();
+		const int res = i < m ? ploc_merge(i, cl[cur], nearest, blo, bhi, children, parent, nodeCounter) : -1;
+		const unsigned keep = __ballot_sync(0xffffffffu, res >= 0);
+		if (lane == 0) warpOffset[warp] = __popc(keep);
+		__syncthreads();
+		if (warp == 0) {
+			const int c = warpOffset[lane];
+			int incl = c;
+			for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+			warpOffset[lane] = incl - c;
+			if (lane == 31) total = incl;
+		}
+		__syncthreads();
+		if (res >= 0) cl[cur ^ 1][warpOffset[warp] + __popc(keep & ((1u << lane) - 1u))] = res;
+		m = total; cur ^= 1;
+		__syncthreads();      // also orders this round's blo / bhi / cl writes before the next round's reads
+	}
 }
 
 __global__ void ploc_init_kernel(int n, const uint32_t *sortedPrim, const float4 *primLo, const float4 *primHi,
@@ -328,12 +384,16 @@ __device__ __forceinline__ int enumerate_leaf(int n, int node, const int2 *child
 	return cnt;
 }
 
-__global__ void collapse_kernel(int n, int rootIsLeaf, const CollapseItem *inQ, uint32_t inCount, CollapseItem *outQ, uint32_t *outCount,
+// The queue length of a level is read from the device (inCountPtr); the host launches a level over the bound 8^level
+// (a wide node has at most 8 children) and looks at the counts once per batch of levels only.
+__global__ void collapse_kernel(int n, int rootIsLeaf, const CollapseItem *inQ, const uint32_t *inCountPtr, CollapseItem *outQ, uint32_t *outCount,
 		const int2 *children, const float4 *blo, const float4 *bhi, const uint32_t *sortedPrim,
 		uint4 *nodes, uint32_t *nodeCounter, uint32_t *slotCounter, uint32_t *slotPrim, float *sahAccum, uint32_t *leafCounter,
-		const uint8_t *dpSplit) {
+		const uint8_t *dpSplit, uint32_t *depthCounter, uint32_t level) {
 	uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t inCount = *inCountPtr;
 	if (w >= inCount) return;
+	if (w == 0) *depthCounter = level + 1;        // levels run in stream order: the last non-empty one leaves the depth
 	const CollapseItem item = inQ[w];
 
 	int kids[8]; int nk = 0;
@@ -622,19 +682,22 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 		ploc_init_kernel<<<div_up(n, 256), 256, 0, st>>>(n, sortedPrim.ptr, primLo.ptr, primHi.ptr, blo.ptr, bhi.ptr, clA.ptr);
 		int nodeCounter = n - 1;
 		MTSB_CUDA(cudaMemcpyAsync(counter.ptr, &nodeCounter, sizeof(int), cudaMemcpyHostToDevice, st));
-		int m = n; int *cur = clA.ptr, *nxt = clB.ptr;
-		while (m > 1) {
-			ploc_nearest_kernel<<<div_up(m, 128), 128, 0, st>>>(m, cur, blo.ptr, bhi.ptr, nearest.ptr);
-			ploc_merge_kernel<<<div_up(m, 256), 256, 0, st>>>(m, cur, nearest.ptr, blo.ptr, bhi.ptr, children.ptr, parent.ptr, counter.ptr, merged.ptr, valid.ptr);
-			MTSB_CUDA(cub::DeviceScan::ExclusiveSum(tmp.ptr, tmpBytes, valid.ptr, scan.ptr, m, st));
-			ploc_compact_kernel<<<div_up(m, 256), 256, 0, st>>>(m, merged.ptr, valid.ptr, scan.ptr, nxt);
-			int lastScan = 0, lastValid = 0;
-			MTSB_CUDA(cudaMemcpyAsync(&lastScan, scan.ptr + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
-			MTSB_CUDA(cudaMemcpyAsync(&lastValid, valid.ptr + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+		DevBuf<int> mDev; MTSB_CHECK(mDev.alloc(2));          // ping-pong pair: round r reads slot r & 1, publishes into the other
+		int m = n, round = 0; int *cur = clA.ptr, *nxt = clB.ptr;
+		MTSB_CUDA(cudaMemcpyAsync(mDev.ptr, &m, sizeof(int), cudaMemcpyHostToDevice, st));
+		while (m > PLOC_TAIL) {
+			for (int b = 0; b < PLOC_BATCH; ++b, ++round) {
+				const int *mIn = mDev.ptr + (round & 1); int *mOut = mDev.ptr + ((round + 1) & 1);
+				ploc_nearest_kernel<<<div_up(m, 128), 128, 0, st>>>(mIn, cur, blo.ptr, bhi.ptr, nearest.ptr);
+				ploc_merge_kernel<<<div_up(m, 256), 256, 0, st>>>(mIn, m, cur, nearest.ptr, blo.ptr, bhi.ptr, children.ptr, parent.ptr, counter.ptr, merged.ptr, valid.ptr);
+				MTSB_CUDA(cub::DeviceScan::ExclusiveSum(tmp.ptr, tmpBytes, valid.ptr, scan.ptr, m, st));
+				ploc_compact_kernel<<<div_up(m, 256), 256, 0, st>>>(mIn, m, merged.ptr, valid.ptr, scan.ptr, nxt, mOut);
+				std::swap(cur, nxt);
+			}
+			MTSB_CUDA(cudaMemcpyAsync(&m, mDev.ptr + (round & 1), sizeof(int), cudaMemcpyDeviceToHost, st));
 			MTSB_CUDA(cudaStreamSynchronize(st));
-			m = lastScan + lastValid;
-			std::swap(cur, nxt);
 		}
+		if (m > 1) ploc_tail_kernel<<<1, PLOC_TAIL, 0, st>>>(mDev.ptr + (round & 1), cur, blo.ptr, bhi.ptr, children.ptr, parent.ptr, counter.ptr);
 		root = 0;    // last id handed out is 0
 	} else {
 		lbvh_kernel<<<div_up(n - 1, 256), 256, 0, st>>>(n, sortedKeys.ptr, children.ptr, parent.ptr);
@@ -649,8 +712,8 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 	DevBuf<uint4> nodesTmp; MTSB_CHECK(nodesTmp.alloc(maxNodes * 5));
 	DevBuf<uint32_t> slotPrim; MTSB_CHECK(slotPrim.alloc(n));
 	DevBuf<CollapseItem> qA, qB; MTSB_CHECK(qA.alloc(maxNodes)); MTSB_CHECK(qB.alloc(maxNodes));
-	DevBuf<uint32_t> counters; MTSB_CHECK(counters.alloc(8));   // 0 nodeCounter, 1 slotCounter, 2 outCount, 3 sah(float), 4 leaves
-	uint32_t initCounters[8] = { 1, 0, 0, 0, 0, 0, 0, 0 };
+	DevBuf<uint32_t> counters; MTSB_CHECK(counters.alloc(8));   // 0 nodeCounter, 1 slotCounter, 2 | 5 queue lengths (ping-pong), 3 sah(float), 4 leaves, 6 depth
+	uint32_t initCounters[8] = { 1, 0, 1, 0, 0, 0, 0, 0 };
 	MTSB_CUDA(cudaMemcpyAsync(counters.ptr, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, st));
 	// cost-driven collapse (default; MTSB_COLLAPSE_DP=0 falls back to the greedy largest-area collapse).  c_prim / c_node
 	// = 0.7 measured best on configs 1-3 (0.4 ... 1.5 within 1 %): a triangle round costs fewer instructions than a node
@@ -671,20 +734,28 @@ int build_bvh(mtsb_ctx *ctx, SceneDev &S, uint32_t primCount, int builder, BvhRe
 	CollapseItem rootItem = { root, 0 };
 	MTSB_CUDA(cudaMemcpyAsync(qA.ptr, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
 	int rootIsLeaf = n <= LEAF_MAX ? 1 : 0;
-	uint32_t inCount = 1; int depth = 0;
+	uint32_t live = 1; int level = 0; size_t bound = 1;
+	int firstBatch = 4; while (firstBatch < 12 && ((size_t) 1 << (3 * (firstBatch - 3))) < (size_t) n) ++firstBatch;   // a balanced tree's depth + 3
 	CollapseItem *qi = qA.ptr, *qo = qB.ptr;
-	while (inCount) {
-		MTSB_CUDA(cudaMemsetAsync(counters.ptr + 2, 0, sizeof(uint32_t), st));
-		collapse_kernel<<<div_up(inCount, 64), 64, 0, st>>>(n, rootIsLeaf, qi, inCount, qo, counters.ptr + 2, children.ptr, blo.ptr, bhi.ptr,
-			sortedPrim.ptr, nodesTmp.ptr, counters.ptr + 0, counters.ptr + 1, slotPrim.ptr, (float *) (counters.ptr + 3), counters.ptr + 4, dpSplitPtr);
-		MTSB_CUDA(cudaMemcpyAsync(&inCount, counters.ptr + 2, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	const int slot[2] = { 2, 5 };
+	while (live) {
+		for (int b = level == 0 ? firstBatch : 8; b > 0; --b, ++level) {
+			uint32_t *inCount = counters.ptr + slot[level & 1], *outCount = counters.ptr + slot[(level + 1) & 1];
+			MTSB_CUDA(cudaMemsetAsync(outCount, 0, sizeof(uint32_t), st));
+			collapse_kernel<<<div_up(bound, 64), 64, 0, st>>>(n, rootIsLeaf, qi, inCount, qo, outCount, children.ptr, blo.ptr, bhi.ptr,
+				sortedPrim.ptr, nodesTmp.ptr, counters.ptr + 0, counters.ptr + 1, slotPrim.ptr, (float *) (counters.ptr + 3), counters.ptr + 4, dpSplitPtr,
+				counters.ptr + 6, (uint32_t) level);
+			std::swap(qi, qo);
+			bound = std::min(bound * 8, maxNodes);
+		}
+		MTSB_CUDA(cudaMemcpyAsync(&live, counters.ptr + slot[level & 1], sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		MTSB_CUDA(cudaStreamSynchronize(st));
-		std::swap(qi, qo); ++depth;
-		if (depth > 256) MTSB_FAIL(MTSB_EINVAL, "build_bvh: wide tree is more than 256 levels deep, the traversal stack holds 64 (degenerate geometry: many coincident primitives? the LBVH builder copes with them)");
+		if (level > 256) MTSB_FAIL(MTSB_EINVAL, "build_bvh: wide tree is more than 256 levels deep, the traversal stack holds 64 (degenerate geometry: many coincident primitives? the LBVH builder copes with them)");
 	}
 	uint32_t fin[8];
 	MTSB_CUDA(cudaMemcpy(fin, counters.ptr, sizeof(fin), cudaMemcpyDeviceToHost));
 	const uint32_t nodeCount = fin[0], slotCount = fin[1];
+	const int depth = (int) fin[6];
 	if (slotCount != primCount) MTSB_FAIL(MTSB_EINVAL, "build_bvh: %u primitives but %u leaf slots", primCount, slotCount);
 
 	// the traversal stack holds one entry per level (MTSB_STACK_SHARED + MTSB_STACK_LOCAL); a deeper tree (thousands of
