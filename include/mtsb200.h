@@ -234,6 +234,30 @@ MTSB_API int  mtsb_scene_add_emitter(mtsb_scene *scene, const mtsb_emitter_desc 
 MTSB_API int  mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *normals,
                                   const float *texcoords, const uint32_t *triangles,
                                   size_t vertex_count, size_t triangle_count, int bsdf, int emitter);
+/* A binary PLY file decoded ON THE DEVICE (replaces, for the on-disk geometry path, the host-side parse of
+ * src/shapes/ply.cpp:146-290 + TriMesh::configure/computeNormals, src/librender/trimesh.cpp:363-387,608-681): `file` is the
+ * whole file image (header and body) in host memory, `bytes` its size; the call parses the text header, copies the image to
+ * the device and returns; the vertex / face records are decoded by kernels at mtsb_scene_commit straight into the scene's
+ * arrays.  to_world / to_world_inv: row-major 4x4 `toWorld` and its inverse (Transform holds both), NULL = identity.
+ * flags: MTSB_PLY_FACE_NORMALS (`faceNormals`: drop / do not compute vertex normals), MTSB_PLY_FLIP_NORMALS (`flipNormals`).
+ * Reads what the reference binds: float32 x y z, nx ny nz, u|s|texture_u, v|t|texture_v of `vertex`, the
+ * vertex_indices / vertex_index list of `face` (uchar|uint count, int|uint index); other scalar properties are skipped;
+ * a file without normals gets the angle-weighted vertex normals of computeNormals.  MTSB_EUNSUPPORTED (use the host
+ * parser + mtsb_scene_add_mesh): ascii / big-endian files, files mixing triangles and quads, other list properties.
+ * Vertex colours are not kept (the device subset has no `vertexcolors` texture).  The shape cannot carry an area emitter.
+ * vertex_count / triangle_count (may be NULL) receive the sizes.  Returns the shape index. */
+#define MTSB_PLY_FACE_NORMALS 1u
+#define MTSB_PLY_FLIP_NORMALS 2u
+MTSB_API int  mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const float to_world[16],
+                                 const float to_world_inv[16], uint32_t flags, int bsdf,
+                                 uint32_t *vertex_count, uint32_t *triangle_count);
+/* Header of a binary PLY file image only: the vertex and triangle counts mtsb_scene_add_ply would produce, or the error it
+ * would return (no device work, no scene) — lets a caller that already holds the host-parsed mesh check the two agree. */
+MTSB_API int  mtsb_ply_probe(const void *file, size_t bytes, uint32_t *vertex_count, uint32_t *triangle_count);
+/* The decoded arrays of a mesh shape, copied back to the host after commit (checks, and callers that need the geometry
+ * the device decoded): positions 3V, normals 3V, texcoords 2V, triangles 3T; any pointer may be NULL. */
+MTSB_API int  mtsb_scene_read_mesh(const mtsb_scene *scene, int shape, float *positions, float *normals, float *texcoords,
+                                   uint32_t *triangles);
 /* Analytic rectangle (src/shapes/rectangle.cpp): object-to-world 4x4 row-major, flipNormals. */
 MTSB_API int  mtsb_scene_add_rectangle(mtsb_scene *scene, const float object_to_world[16],
                                        int flip_normals, int bsdf, int emitter);
@@ -272,7 +296,8 @@ MTSB_API size_t mtsb_scene_shape_count(const mtsb_scene *scene);
 /* shape_offsets[i] = global primitive index of shape i's first primitive; n+1 entries. */
 MTSB_API int  mtsb_scene_shape_offsets(const mtsb_scene *scene, uint32_t *offsets_out);
 /* Build statistics: out[0]=build ms (device), out[1]=wide nodes, out[2]=bytes of nodes, out[3]=bytes of
- * triangle records, out[4]=SAH cost of the wide tree, out[5]=leaf count, out[6]=max depth. */
+ * triangle records, out[4]=SAH cost of the wide tree, out[5]=leaf count, out[6]=max depth, out[7]=device ms of the PLY
+ * decode kernels (mtsb_scene_add_ply), 0 without any. */
 MTSB_API int  mtsb_scene_build_stats(const mtsb_scene *scene, double out[8]);
 
 /* ---------------------------------------------------------------- ray queries -------------------- */

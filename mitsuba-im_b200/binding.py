@@ -19,7 +19,9 @@ LIB_PATH = os.path.join(_HERE, "lib", "libmtsb200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "mtsb200.h")
 
 MTSB_NO_HIT = 0xFFFFFFFF
+PLY_FACE_NORMALS, PLY_FLIP_NORMALS = 1, 2
 NOALLOC_MAX_RAYS = 65536
+EINVAL, ENODEVICE, ECUDA, EUNSUPPORTED, ENOMEM = -1, -2, -3, -4, -5
 SPECIAL_PRIM = 0xF0000000
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_PLASTIC, BSDF_ROUGHCONDUCTOR, BSDF_NULL, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4, 5, 6
 BSDF_PASSTHROUGH = 7
@@ -120,6 +122,9 @@ def lib():
         "mtsb_scene_set_bsdf_table": (i32, [vp, i32, vp, sz]), "mtsb_scene_set_envmap": (i32, [vp, i32, C.POINTER(EnvmapDesc)]),
         "mtsb_scene_add_texture": (i32, [vp, C.POINTER(TextureDesc)]), "mtsb_scene_set_bsdf_texture": (i32, [vp, i32, i32]),
         "mtsb_scene_add_mesh": (i32, [vp, vp, vp, vp, vp, sz, sz, i32, i32]),
+        "mtsb_scene_add_ply": (i32, [vp, vp, sz, vp, vp, u32, i32, C.POINTER(u32), C.POINTER(u32)]),
+        "mtsb_scene_read_mesh": (i32, [vp, i32, vp, vp, vp, vp]),
+        "mtsb_ply_probe": (i32, [vp, sz, C.POINTER(u32), C.POINTER(u32)]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
         "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
@@ -163,6 +168,14 @@ def _check(rc):
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def ply_probe(image):
+    """(vertices, triangles) the device decoder would produce for a binary PLY file image; raises what add_ply would."""
+    buf = np.frombuffer(image, dtype=np.uint8)
+    nv, nt = C.c_uint32(0), C.c_uint32(0)
+    _check(lib().mtsb_ply_probe(_ptr(buf), buf.size, C.byref(nv), C.byref(nt)))
+    return nv.value, nt.value
 
 
 def device_count():
@@ -283,6 +296,29 @@ class Scene:
         UV = None if texcoords is None else np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1, 2)
         return _check(lib().mtsb_scene_add_mesh(self.h, _ptr(P), _ptr(N), _ptr(UV), _ptr(T), P.shape[0], T.shape[0], bsdf, emitter))
 
+    def add_ply(self, image, to_world=None, face_normals=False, flip_normals=False, bsdf=0):
+        """A binary PLY file image (bytes / numpy uint8 array) decoded on the device at commit; returns the shape index and
+        remembers (vertices, triangles) for read_mesh."""
+        buf = np.frombuffer(image, dtype=np.uint8) if not isinstance(image, np.ndarray) else np.ascontiguousarray(image, dtype=np.uint8)
+        M = Mi = None
+        if to_world is not None:
+            M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
+            Mi = np.ascontiguousarray(np.linalg.inv(M.astype(np.float64)), dtype=np.float32)
+        nv, nt = C.c_uint32(0), C.c_uint32(0)
+        flags = (PLY_FACE_NORMALS if face_normals else 0) | (PLY_FLIP_NORMALS if flip_normals else 0)
+        shape = _check(lib().mtsb_scene_add_ply(self.h, _ptr(buf), buf.size, _ptr(M), _ptr(Mi), flags, bsdf, C.byref(nv), C.byref(nt)))
+        if not hasattr(self, "_mesh_sizes"):
+            self._mesh_sizes = {}
+        self._mesh_sizes[shape] = (nv.value, nt.value)
+        return shape
+
+    def read_mesh(self, shape, sizes=None):
+        """(positions, normals, texcoords, triangles) of a mesh shape as the device holds them (after commit)."""
+        nv, nt = sizes if sizes is not None else self._mesh_sizes[shape]
+        P, N, UV, T = np.empty((nv, 3), np.float32), np.empty((nv, 3), np.float32), np.empty((nv, 2), np.float32), np.empty((nt, 3), np.uint32)
+        _check(lib().mtsb_scene_read_mesh(self.h, shape, _ptr(P), _ptr(N), _ptr(UV), _ptr(T)))
+        return P, N, UV, T
+
     def add_rectangle(self, to_world, flip_normals=False, bsdf=0, emitter=-1):
         M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
         return _check(lib().mtsb_scene_add_rectangle(self.h, _ptr(M), int(flip_normals), bsdf, emitter))
@@ -343,7 +379,7 @@ class Scene:
         out = np.zeros(8, np.float64)
         _check(lib().mtsb_scene_build_stats(self.h, _ptr(out)))
         return dict(build_ms=out[0], nodes=int(out[1]), node_bytes=int(out[2]), tri_bytes=int(out[3]),
-                    sah_cost=out[4], leaves=int(out[5]), depth=int(out[6]))
+                    sah_cost=out[4], leaves=int(out[5]), depth=int(out[6]), ply_decode_ms=out[7])
 
     # --- ray queries -------------------------------------------------------------------------
     @staticmethod

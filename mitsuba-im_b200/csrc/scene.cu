@@ -128,6 +128,7 @@ void mtsb_scene_destroy(mtsb_scene *scene) {
 	cudaSetDevice(scene->ctx->device);
 	mtsb_release_pipe(scene);
 	mtsb::l2_claim(scene, 0);
+	for (mtsb::PlyMesh *M : scene->plyMeshes) mtsb::ply_release(M);
 	delete scene;
 }
 
@@ -286,10 +287,14 @@ int mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
 	sh.type = SHAPE_MESH;
 	sh.primOffset = scene->primCount; sh.primCount = (uint32_t) triangle_count;
-	sh.vtxBase = (uint32_t) (scene->positions.size() / 3);
-	sh.triBase = (uint32_t) (scene->indices.size() / 3);
+	if (scene->vtxTotal + vertex_count > 0xffffffffull) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_mesh: more than 2^32 vertices");
+	sh.vtxBase = (uint32_t) scene->vtxTotal;
+	sh.triBase = (uint32_t) scene->triTotal;
 	sh.flags = (normals ? SHAPE_HAS_NORMALS : 0) | (texcoords ? SHAPE_HAS_UV : 0);
 	sh.bsdf = bsdf; sh.emitter = emitter; sh.interior = -1; sh.exterior = -1;
+	scene->meshHost.resize(scene->shapes.size() + 1, std::make_pair((size_t) -1, (size_t) -1));
+	scene->meshHost.back() = std::make_pair(scene->positions.size() / 3, scene->indices.size() / 3);
+	scene->vtxTotal += vertex_count; scene->triTotal += triangle_count;
 	scene->positions.insert(scene->positions.end(), positions, positions + vertex_count * 3);
 	if (normals) scene->normals.insert(scene->normals.end(), normals, normals + vertex_count * 3);
 	else scene->normals.resize(scene->normals.size() + vertex_count * 3, 0.0f);
@@ -301,6 +306,57 @@ int mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *
 	scene->shapeOffsets.push_back(scene->primCount);
 	if (emitter >= 0) scene->emitters[emitter].shape = (uint32_t) scene->shapes.size() - 1;
 	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const float to_world[16], const float to_world_inv[16],
+		uint32_t flags, int bsdf, uint32_t *vertex_count, uint32_t *triangle_count) {
+	if (!scene || !file) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, -1, "mtsb_scene_add_ply"));
+	if (flags & ~(MTSB_PLY_FACE_NORMALS | MTSB_PLY_FLIP_NORMALS)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: unknown flags %#x", flags);
+	uint32_t nv = 0, nt = 0; bool hasUV = false, hasNormals = false; PlyMesh *M = nullptr;
+	MTSB_CHECK(ply_stage(scene, file, bytes, to_world, to_world_inv, flags, bsdf, &nv, &nt, &hasUV, &hasNormals, &M));
+	if ((uint64_t) scene->primCount + nt > 0x7fffffffull || scene->vtxTotal + nv > 0xffffffffull) {
+		ply_release(M); MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: more than 2^31 primitives");
+	}
+	ShapeRec sh; memset(&sh, 0, sizeof(sh));
+	sh.type = SHAPE_MESH;
+	sh.primOffset = scene->primCount; sh.primCount = nt;
+	sh.vtxBase = (uint32_t) scene->vtxTotal; sh.triBase = (uint32_t) scene->triTotal;
+	// a file without normals gets computed ones unless faceNormals is set (TriMesh::computeNormals)
+	sh.flags = ((flags & MTSB_PLY_FACE_NORMALS) ? 0 : SHAPE_HAS_NORMALS) | (hasUV ? SHAPE_HAS_UV : 0);
+	sh.bsdf = bsdf; sh.emitter = -1; sh.interior = -1; sh.exterior = -1;
+	scene->vtxTotal += nv; scene->triTotal += nt;
+	scene->shapes.push_back(sh);
+	scene->meshHost.resize(scene->shapes.size(), std::make_pair((size_t) -1, (size_t) -1));
+	scene->primCount += nt;
+	scene->shapeOffsets.push_back(scene->primCount);
+	ply_place(M, (int) scene->shapes.size() - 1, sh.vtxBase, sh.triBase);
+	scene->plyMeshes.push_back(M);
+	if (vertex_count) *vertex_count = nv;
+	if (triangle_count) *triangle_count = nt;
+	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_ply_probe(const void *file, size_t bytes, uint32_t *vertex_count, uint32_t *triangle_count) {
+	if (!file) MTSB_FAIL(MTSB_EINVAL, "mtsb_ply_probe: NULL argument");
+	return ply_probe(file, bytes, vertex_count, triangle_count);
+}
+
+int mtsb_scene_read_mesh(const mtsb_scene *scene, int shape, float *positions, float *normals, float *texcoords, uint32_t *triangles) {
+	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_read_mesh: scene not committed");
+	if (shape < 0 || shape >= (int) scene->shapes.size() || scene->shapes[shape].type != SHAPE_MESH) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_read_mesh: shape %d is not a triangle mesh", shape);
+	const ShapeRec &sh = scene->shapes[shape];
+	// the vertex range of a mesh ends where the next mesh's begins
+	size_t vEnd = scene->vtxTotal;
+	for (size_t s = (size_t) shape + 1; s < scene->shapes.size(); ++s) if (scene->shapes[s].type == SHAPE_MESH) { vEnd = scene->shapes[s].vtxBase; break; }
+	const size_t V = vEnd - sh.vtxBase, T = sh.primCount;
+	MTSB_CUDA(cudaSetDevice(scene->ctx->device));
+	MTSB_CUDA(cudaStreamSynchronize(scene->ctx->stream));
+	if (positions) MTSB_CUDA(cudaMemcpy(positions, scene->dPositions.ptr + (size_t) sh.vtxBase * 3, V * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	if (normals) MTSB_CUDA(cudaMemcpy(normals, scene->dNormals.ptr + (size_t) sh.vtxBase * 3, V * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+	if (texcoords) MTSB_CUDA(cudaMemcpy(texcoords, scene->dTexcoords.ptr + (size_t) sh.vtxBase * 2, V * 2 * sizeof(float), cudaMemcpyDeviceToHost));
+	if (triangles) MTSB_CUDA(cudaMemcpy(triangles, scene->dIndices.ptr + (size_t) sh.triBase * 3, T * 3 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+	return 0;
 }
 
 int mtsb_scene_add_rectangle(mtsb_scene *scene, const float m[16], int flip_normals, int bsdf, int emitter) {
@@ -462,10 +518,11 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 		size_t base = triAreaCdf.size();
 		triAreaCdf.push_back(0.0f);
 		for (uint32_t t = 0; t < sh.primCount; ++t) {
-			const uint32_t *ix = &scene->indices[(size_t) (sh.triBase + t) * 3];
-			const float *p0 = &scene->positions[(size_t) (sh.vtxBase + ix[0]) * 3];
-			const float *p1 = &scene->positions[(size_t) (sh.vtxBase + ix[1]) * 3];
-			const float *p2 = &scene->positions[(size_t) (sh.vtxBase + ix[2]) * 3];
+			const size_t hv = scene->meshHost[s].first, ht = scene->meshHost[s].second;      // emitter meshes are host-staged
+			const uint32_t *ix = &scene->indices[(ht + t) * 3];
+			const float *p0 = &scene->positions[(hv + ix[0]) * 3];
+			const float *p1 = &scene->positions[(hv + ix[1]) * 3];
+			const float *p2 = &scene->positions[(hv + ix[2]) * 3];
 			V3 a = v3(p1[0]-p0[0], p1[1]-p0[1], p1[2]-p0[2]), b = v3(p2[0]-p0[0], p2[1]-p0[1], p2[2]-p0[2]);
 			V3 c = cross(a, b);
 			float area = 0.5f * sqrtf(dot(c, c));
@@ -532,10 +589,34 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 		memcpy(&scene->bsdfs[i].p[13], &dev, sizeof(dev));
 	}
 	MTSB_CHECK(scene->dBsdfs.upload(scene->bsdfs, st));
-	MTSB_CHECK(scene->dPositions.upload(scene->positions, st));
-	MTSB_CHECK(scene->dNormals.upload(scene->normals, st));
-	MTSB_CHECK(scene->dTexcoords.upload(scene->texcoords, st));
-	MTSB_CHECK(scene->dIndices.upload(scene->indices, st));
+	if (scene->plyMeshes.empty()) {
+		MTSB_CHECK(scene->dPositions.upload(scene->positions, st));
+		MTSB_CHECK(scene->dNormals.upload(scene->normals, st));
+		MTSB_CHECK(scene->dTexcoords.upload(scene->texcoords, st));
+		MTSB_CHECK(scene->dIndices.upload(scene->indices, st));
+	} else {
+		// host-staged meshes are copied to their place, PLY images are decoded into theirs by kernels (ply.cu)
+		MTSB_CHECK(scene->dPositions.alloc(scene->vtxTotal * 3)); MTSB_CHECK(scene->dNormals.alloc(scene->vtxTotal * 3));
+		MTSB_CHECK(scene->dTexcoords.alloc(scene->vtxTotal * 2)); MTSB_CHECK(scene->dIndices.alloc(scene->triTotal * 3));
+		scene->meshHost.resize(scene->shapes.size(), std::make_pair((size_t) -1, (size_t) -1));
+		for (size_t s = 0; s < scene->shapes.size(); ++s) {
+			const ShapeRec &sh = scene->shapes[s];
+			if (sh.type != SHAPE_MESH || scene->meshHost[s].first == (size_t) -1) continue;
+			const size_t hv = scene->meshHost[s].first, ht = scene->meshHost[s].second;
+			size_t hvEnd = scene->positions.size() / 3;
+			for (size_t k = s + 1; k < scene->shapes.size(); ++k) if (scene->meshHost[k].first != (size_t) -1) { hvEnd = scene->meshHost[k].first; break; }
+			const size_t V = hvEnd - hv, T = sh.primCount;
+			MTSB_CUDA(cudaMemcpyAsync(scene->dPositions.ptr + (size_t) sh.vtxBase * 3, &scene->positions[hv * 3], V * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+			MTSB_CUDA(cudaMemcpyAsync(scene->dNormals.ptr + (size_t) sh.vtxBase * 3, &scene->normals[hv * 3], V * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+			MTSB_CUDA(cudaMemcpyAsync(scene->dTexcoords.ptr + (size_t) sh.vtxBase * 2, &scene->texcoords[hv * 2], V * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+			MTSB_CUDA(cudaMemcpyAsync(scene->dIndices.ptr + (size_t) sh.triBase * 3, &scene->indices[ht * 3], T * 3 * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+		}
+		DevBuf<uint32_t> plyScratch; MTSB_CHECK(plyScratch.alloc(2));
+		for (PlyMesh *M : scene->plyMeshes)
+			MTSB_CHECK(ply_decode(scene, M, scene->dPositions.ptr, scene->dNormals.ptr, scene->dTexcoords.ptr, scene->dIndices.ptr, plyScratch.ptr));
+		for (PlyMesh *M : scene->plyMeshes) ply_release(M);
+		scene->plyMeshes.clear();
+	}
 	MTSB_CHECK(scene->dEmitterCdf.upload(emitterCdf, st));
 	MTSB_CHECK(scene->dTriAreaCdf.upload(triAreaCdf, st));
 	MTSB_CHECK(scene->dTriAreaCdfOffset.upload(triAreaCdfOffset, st));
@@ -653,7 +734,7 @@ int mtsb_scene_build_stats(const mtsb_scene *scene, double out[8]) {
 	if (!scene || !scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_build_stats: scene not committed");
 	out[0] = scene->bvh.buildMs; out[1] = scene->bvh.nodeCount; out[2] = (double) scene->bvh.nodeBytes;
 	out[3] = (double) scene->bvh.triBytes; out[4] = scene->bvh.sahCost; out[5] = scene->bvh.leafCount;
-	out[6] = scene->bvh.depth; out[7] = 0;
+	out[6] = scene->bvh.depth; out[7] = scene->plyDecodeMs;
 	return 0;
 }
 

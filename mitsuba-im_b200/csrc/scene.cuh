@@ -5,7 +5,7 @@
 #include <mutex>
 #include <algorithm>
 
-namespace mtsb { struct TracePipe; }
+namespace mtsb { struct TracePipe; struct PlyMesh; }
 
 struct mtsb_scene {
 	mtsb_ctx *ctx = nullptr;
@@ -43,6 +43,12 @@ struct mtsb_scene {
 	std::vector<uint32_t> indices;
 	std::vector<uint32_t> shapeOffsets;   // n+1 prefix sums of primitive counts
 	uint32_t primCount = 0;
+	// vertex / triangle totals over host-staged AND device-decoded meshes (a shape's vtxBase / triBase index the final device
+	// arrays); per shape, where its host-staged arrays start in positions / indices ((size_t) -1: not host-staged)
+	size_t vtxTotal = 0, triTotal = 0;
+	std::vector<std::pair<size_t, size_t> > meshHost;
+	float plyDecodeMs = 0;                         // device time of the decode kernels at commit (CUDA events), mtsb_scene_build_stats out[7]
+	std::vector<mtsb::PlyMesh *> plyMeshes;        // binary PLY images waiting on the device for commit (ply.cu)
 
 	// device copies
 	mtsb::DevBuf<mtsb::ShapeRec> dShapes;
@@ -66,6 +72,16 @@ struct mtsb_scene {
 	mtsb::TracePipe *pipe = nullptr;
 	size_t l2Bytes = 0;                   // persisting-L2 claim of this scene (l2_claim below), 0 = none
 };
+
+// ply.cu
+namespace mtsb {
+int ply_stage(mtsb_scene *scene, const void *file, size_t bytes, const float *toWorld, const float *toWorldInv, uint32_t flags, int bsdf,
+	uint32_t *vertexCountOut, uint32_t *triangleCountOut, bool *hasUVOut, bool *hasNormalsOut, PlyMesh **out);
+void ply_release(PlyMesh *M);
+int ply_probe(const void *file, size_t bytes, uint32_t *nv, uint32_t *nt);
+void ply_place(PlyMesh *M, int shape, uint32_t vtxBase, uint32_t triBase);
+int ply_decode(mtsb_scene *scene, PlyMesh *M, float *positions, float *normals, float *texcoords, uint32_t *indices, uint32_t *scratch);
+}
 
 namespace mtsb {
 

@@ -15,6 +15,7 @@
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/plugin.h>
 #include <mitsuba/core/fstream.h>
+#include <mitsuba/core/mmap.h>
 #include <mitsuba/core/bitmap.h>
 #include <mitsuba/render/mipmap.h>
 #include "microfacet.h"          /* src/bsdfs/microfacet.h: MicrofacetDistribution(props) reads alpha / distribution / sampleVisible */

@@ -100,6 +100,34 @@ static void uploadEnvmap(mtsb_scene *out, int id, const Emitter *e) {
 }
 
 /// Uploads shapes / BSDFs / emitters in Scene order and commits (BVH build on the device).
+/// A mesh that came out of the `ply` plugin is decoded again, on the device, from its file (mtsb_scene_add_ply) instead of
+/// being copied out of the TriMesh's host arrays — when the file is one the device decoder takes and its header agrees with
+/// the mesh the reference's loader produced.  Returns the shape index or -1 (caller falls back to mtsb_scene_add_mesh).
+static int addPlyFromFile(mtsb_scene *out, const TriMesh *mesh, int bid) {
+	if (mesh->getClass()->getName() != "PLYLoader") return -1;
+	const Properties &props = mesh->getProperties();
+	if (props.hasProperty("maxSmoothAngle") || !props.hasProperty("filename")) return -1;     // rebuildTopology changes the arrays
+	if (const char *e = getenv("MTSB_PLY_ON_DEVICE")) if (atoi(e) == 0) return -1;
+	try {
+		const fs::pathstr resolved = Thread::getThread()->getFileResolver()->resolve(fs::pathstr(props.getString("filename")));     // ply.cpp:76-77
+		const fs::path path = fs::decode_pathstr(resolved);
+		if (!fs::exists(path)) return -1;
+		ref<MemoryMappedFile> file = new MemoryMappedFile(resolved, true);
+		uint32_t nv = 0, nt = 0;
+		if (mtsb_ply_probe(file->getData(), file->getSize(), &nv, &nt) != 0) return -1;
+		if (nv != mesh->getVertexCount() || nt != mesh->getTriangleCount()) return -1;
+		const Transform toWorld = props.getTransform("toWorld", Transform());
+		float m[16], inv[16];
+		matrixToArray(toWorld.getMatrix(), m); matrixToArray(toWorld.getInverseMatrix(), inv);
+		const uint32_t flags = (props.getBoolean("faceNormals", false) ? MTSB_PLY_FACE_NORMALS : 0u) | (props.getBoolean("flipNormals", false) ? MTSB_PLY_FLIP_NORMALS : 0u);
+		const int rc = mtsb_scene_add_ply(out, file->getData(), file->getSize(), m, inv, flags, bid, NULL, NULL);
+		if (rc >= 0) SLog(EInfo, "gpupath: \"%s\" decoded on the device (%u triangles)", path.filename().string().c_str(), nt);
+		return rc;
+	} catch (const std::exception &) {
+		return -1;
+	}
+}
+
 static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 	mtsb_scene *out = NULL;
 	MTSB_CALL(mtsb_scene_create(ctx, &out));
@@ -180,10 +208,12 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		int rc;
 		if (shape->getClass()->derivesFrom(MTS_CLASS(TriMesh))) {
 			const TriMesh *mesh = static_cast<const TriMesh *>(shape);
+			rc = eid < 0 ? addPlyFromFile(out, mesh, bid) : -1;
 			// Point / Normal are 3 packed floats, Point2 2 floats, Triangle 3 uint32 (include/mitsuba/core/triangle.h)
-			rc = mtsb_scene_add_mesh(out, (const float *) mesh->getVertexPositions(), (const float *) mesh->getVertexNormals(),
-				(const float *) mesh->getVertexTexcoords(), (const uint32_t *) mesh->getTriangles(),
-				mesh->getVertexCount(), mesh->getTriangleCount(), bid, eid);
+			if (rc < 0)
+				rc = mtsb_scene_add_mesh(out, (const float *) mesh->getVertexPositions(), (const float *) mesh->getVertexNormals(),
+					(const float *) mesh->getVertexTexcoords(), (const uint32_t *) mesh->getTriangles(),
+					mesh->getVertexCount(), mesh->getTriangleCount(), bid, eid);
 		} else if (shape->getClass()->getName() == "Rectangle") {   // src/shapes/rectangle.cpp:79-84
 			const Properties &props = shape->getProperties();
 			float m[16]; matrixToArray(props.getTransform("toWorld", Transform()).getMatrix(), m);

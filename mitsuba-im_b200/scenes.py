@@ -85,8 +85,8 @@ def displaced_sphere(subdiv, seed=1, radius=1.0, center=(0, 0, 0), amplitude=0.0
     return V.astype(np.float32), N.astype(np.float32), F.astype(np.uint32)
 
 
-def write_ply(path, V, N, F, UV=None):
-    """Binary little-endian PLY with per-vertex normals (so TriMesh::computeNormals keeps them as-is) and optional
+def ply_image(V, N, F, UV=None):
+    """Binary little-endian PLY file image with per-vertex normals (so TriMesh::computeNormals keeps them as-is) and optional
     texture coordinates (properties u, v)."""
     V = np.asarray(V, np.float32)
     F = np.asarray(F, np.int32)
@@ -96,16 +96,18 @@ def write_ply(path, V, N, F, UV=None):
     if UV is not None:
         hdr += "property float u\nproperty float v\n"
     hdr += "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % F.shape[0]
+    vd = V if N is None else np.concatenate([V, np.asarray(N, np.float32)], axis=1)
+    if UV is not None:
+        vd = np.concatenate([vd, np.asarray(UV, np.float32)], axis=1)
+    fd = np.empty(F.shape[0], dtype=[("n", "u1"), ("i", "<i4", 3)])
+    fd["n"] = 3
+    fd["i"] = F
+    return hdr.encode("ascii") + np.ascontiguousarray(vd, "<f4").tobytes() + fd.tobytes()
+
+
+def write_ply(path, V, N, F, UV=None):
     with open(path, "wb") as f:
-        f.write(hdr.encode("ascii"))
-        vd = V if N is None else np.concatenate([V, np.asarray(N, np.float32)], axis=1)
-        if UV is not None:
-            vd = np.concatenate([vd, np.asarray(UV, np.float32)], axis=1)
-        f.write(np.ascontiguousarray(vd, "<f4").tobytes())
-        fd = np.empty(F.shape[0], dtype=[("n", "u1"), ("i", "<i4", 3)])
-        fd["n"] = 3
-        fd["i"] = F
-        f.write(fd.tobytes())
+        f.write(ply_image(V, N, F, UV))
 
 
 # ------------------------------------------------------------------------------------------------ transforms
@@ -378,7 +380,9 @@ class SceneDesc:
                                                                         dict(beckmann=0, ggx=1)[dist], 1.0 if b.get("sample_visible", True) else 0.0]
         raise ValueError("BSDF outside the GPU subset: %s" % t)
 
-    def upload(self, ctx, builder=B.BUILDER_LBVH):
+    def upload(self, ctx, builder=B.BUILDER_LBVH, ply_images=None):
+        """ply_images: {shape index: binary PLY file image} — those mesh shapes are decoded on the device (Scene.add_ply) instead of
+        being passed as arrays."""
         """Creates and commits a binding.Scene.  Emitter order = Mitsuba's: Scene::addChild registers a shape's area
         emitter when the shape is added, free emitters in XML order — free emitters are emitted first in to_xml()."""
         sc = B.Scene(ctx)
@@ -416,7 +420,11 @@ class SceneDesc:
             eid = -1
             if s["emitter"] is not None:
                 eid = sc.add_emitter(B.EMITTER_AREA, radiance=s["emitter"])
-            if s["type"] == "mesh":
+            if s["type"] == "mesh" and ply_images is not None and k in ply_images:
+                if eid >= 0:
+                    raise ValueError("a device-decoded PLY mesh cannot carry an area emitter")
+                sc.add_ply(ply_images[k], bsdf=bid)
+            elif s["type"] == "mesh":
                 sc.add_mesh(s["V"], s["F"], normals=s["N"], texcoords=s.get("UV"), bsdf=bid, emitter=eid)
             elif s["type"] == "sphere":
                 sc.add_sphere(translate(*s["center"]), s["radius"], flip_normals=s["flip_normals"], bsdf=bid, emitter=eid)

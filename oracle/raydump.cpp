@@ -324,6 +324,51 @@ public:
 		return 0;
 	}
 
+	/// The triangle meshes of a scene as the reference's loaders (ply.cpp, TriMesh::configure / computeNormals) leave them:
+	/// per mesh shape the words {V, T, hasNormals, hasUV}, 3V position floats, 3V normal floats (if any), 2V uv floats (if any),
+	/// 3T index words.  Prints the wall time of loadScene + initialize (the host parse the device decoder replaces).
+	int mesh(int argc, char **argv) {
+		if (argc < 4) { cout << "mesh <scene> <out>" << endl; return 1; }
+		auto t0 = std::chrono::steady_clock::now();
+		load(argv[2]);
+		double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+		FILE *f = fopen(argv[3], "wb");
+		if (!f) return 1;
+		size_t meshes = 0;
+		for (const Shape *s : m_shapes) {
+			if (!s->getClass()->derivesFrom(MTS_CLASS(TriMesh))) continue;
+			const TriMesh *m = static_cast<const TriMesh *>(s);
+			uint32_t hdr[4] = { (uint32_t) m->getVertexCount(), (uint32_t) m->getTriangleCount(), m->hasVertexNormals() ? 1u : 0u, m->hasVertexTexcoords() ? 1u : 0u };
+			fwrite(hdr, 4, 4, f);
+			fwrite(m->getVertexPositions(), sizeof(Point), hdr[0], f);
+			if (hdr[2]) fwrite(m->getVertexNormals(), sizeof(Normal), hdr[0], f);
+			if (hdr[3]) fwrite(m->getVertexTexcoords(), sizeof(Point2), hdr[0], f);
+			fwrite(m->getTriangles(), sizeof(Triangle), hdr[1], f);
+			++meshes;
+		}
+		fclose(f);
+		cout << "mesh: " << meshes << " meshes, load " << secs << " s" << endl;
+		return 0;
+	}
+
+	/// Wall time of the reference's PLY loader alone (PLYLoader constructor + TriMesh::configure), no kd-tree: the host parse
+	/// the device decoder replaces, timed for bench reports
+	int plyload(int argc, char **argv) {
+		if (argc < 3) { cout << "plyload <file.ply>..." << endl; return 1; }
+		double total = 0; size_t tris = 0;
+		for (int i = 2; i < argc; ++i) {
+			auto t0 = std::chrono::steady_clock::now();
+			Properties props("ply");
+			props.setString("filename", argv[i]);
+			ref<TriMesh> mesh = static_cast<TriMesh *>(PluginManager::getInstance()->createObject(MTS_CLASS(TriMesh), props));
+			mesh->configure();
+			total += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+			tris += mesh->getTriangleCount();
+		}
+		cout << "plyload: " << tris << " triangles in " << total << " s" << endl;
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -396,6 +441,8 @@ public:
 		if (!strcmp(argv[1], "mipmap")) return mipmap(argc, argv);
 		if (!strcmp(argv[1], "mipmap3")) return mipmap3(argc, argv);
 		if (!strcmp(argv[1], "sobol")) return sobolTables(argc, argv);
+		if (!strcmp(argv[1], "mesh")) return mesh(argc, argv);
+		if (!strcmp(argv[1], "plyload")) return plyload(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
 		cout << "unknown mode" << endl;

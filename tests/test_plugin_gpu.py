@@ -19,7 +19,7 @@ XML = os.path.join(ROOT, "tests", "golden", "cbox_config1.xml")
 XML_GLOSSY = os.path.join(ROOT, "tests", "golden", "cbox_glossy.xml")
 
 
-def run_mitsuba(out, classic, overlay, defines, threads=4, xml=XML):
+def run_mitsuba(out, classic, overlay, defines, threads=4, xml=XML, env=None):
     cmd = [os.path.join(O.REF_DIR, "mitsuba"), "-p", str(threads)]
     if classic:
         cmd.append("-C")
@@ -28,7 +28,8 @@ def run_mitsuba(out, classic, overlay, defines, threads=4, xml=XML):
     for k, v in defines.items():
         cmd += ["-D", "%s=%s" % (k, v)]
     cmd += ["-o", out, xml]
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, errors="replace", timeout=900)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, errors="replace", timeout=900,
+                       env=None if env is None else dict(os.environ, **env))
     assert r.returncode == 0 and os.path.exists(out), r.stdout[-3000:]
     return O.read_pfm(out), r.stdout
 
@@ -189,6 +190,24 @@ def test_envmap_through_the_loader(pkg, tmp_path):
     ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
     gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
     assert "gpupath:" in log, "the overlay plugin did not run"
+    ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
+    assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
+    assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
+
+
+def test_ply_meshes_are_decoded_on_the_device(pkg, tmp_path):
+    """SURVEY 8 f3 through the loader: a mesh that came out of the `ply` plugin is decoded again from its file by
+    mtsb_scene_add_ply (plugin/extract_scene.h addPlyFromFile) — same image as with the host arrays (MTSB_PLY_ON_DEVICE=0)
+    and as the stock `path`."""
+    sd = pkg.scenes.materials_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=5)
+    xml = sd.to_xml(str(tmp_path), "mats")
+    ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
+    gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
+    host, log_host = run_mitsuba(str(tmp_path / "host.pfm"), True, True, {}, xml=xml, env={"MTSB_PLY_ON_DEVICE": "0"})
+    assert "decoded on the device" in log and "decoded on the device" not in log_host
+    # same positions and indices bit for bit, normals to the last bit of their re-normalisation
+    close = (np.abs(gpu - host) <= 1e-5 + 1e-4 * np.abs(host)).all(axis=2)
+    assert close.mean() >= 0.995, close.mean()
     ok = (np.abs(gpu - ref) <= 2e-4 + 2e-3 * np.abs(ref)).all(axis=2)
     assert ok.mean() >= 0.96, "%.4f of the pixels match the reference's own render" % ok.mean()
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
