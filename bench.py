@@ -385,7 +385,7 @@ def main():
             detail[name + "_mrays"] = m / (a.elapsed_time(b) / 5) / 1e3
         if not args.no_path:
             import bench_render
-            detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5, "vol") + (() if args.no_plugin or world > 1 else ("plugin",)), cpu=not args.no_cpu_baseline and world == 1)
+            detail["path"] = bench_render.run(pkg, ctx, stream, configs=(1, 3, 5, "vol", "ply") + (() if args.no_plugin or world > 1 else ("plugin",)), cpu=not args.no_cpu_baseline and world == 1)
 
     # --- config 4: 3840x2160, 1024 spp split by sample index over the ranks (strong scaling), one NCCL film reduce ---
     c4s = None

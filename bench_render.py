@@ -255,6 +255,58 @@ def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
     return out
 
 
+def ply_load_bench(pkg, ctx, sd, cpu=True):
+    """SURVEY 8 f3, the on-disk geometry path: the scene's emitter-less meshes as binary PLY file images
+      device     image -> mtsb_scene_add_ply (H2D of the image) -> decode kernels at commit (device ms from CUDA events)
+      arrays     the same meshes as host arrays through mtsb_scene_add_mesh
+      reference  the unmodified `ply` plugin + TriMesh::configure on one host thread (oracle/raydump.cpp `plyload`), no kd-tree
+    Decoded positions / indices must equal the arrays the images were written from bit for bit."""
+    import subprocess
+    import tempfile
+    B, S = pkg.binding, pkg.scenes
+    images = {k: S.ply_image(s["V"], s["N"], s["F"]) for k, s in enumerate(sd.shapes) if s["type"] == "mesh" and s["emitter"] is None}
+    body = sum(len(v) for v in images.values())
+    nv = sum(sd.shapes[k]["V"].shape[0] for k in images)
+    nt = sum(sd.shapes[k]["F"].shape[0] for k in images)
+    out = {"triangles": nt, "vertices": nv, "file_bytes": body}
+    for rep in range(2):                      # the second round is the one reported (first: allocator and module warm-up)
+        for name, kw in (("arrays", {}), ("device", dict(ply_images=images))):
+            t0 = time.perf_counter()
+            sc = sd.upload(ctx, B.BUILDER_PLOC, **kw)
+            ctx.sync()
+            dt = time.perf_counter() - t0
+            st = sc.build_stats()
+            out[name] = {"upload_and_commit_s": dt, "bvh_build_ms": st["build_ms"], "ply_decode_ms": st["ply_decode_ms"]}
+            if name == "device" and rep == 1:
+                ok = True
+                for k in images:
+                    P, N, UV, T = sc.read_mesh(k)
+                    ok = ok and bool((P.view(np.uint32) == np.asarray(sd.shapes[k]["V"], np.float32).view(np.uint32)).all() and (T == sd.shapes[k]["F"]).all()
+                                     and np.abs(N - sd.shapes[k]["N"]).max() <= 2e-7)
+                out["decoded_equals_source_arrays"] = ok
+            sc.close()
+    # algorithmic bytes of the decode: the file body read once, 32 B per vertex and 12 B per triangle written
+    alg = body + 32 * nv + 12 * nt
+    out["device"]["decode_algorithmic_bytes"] = alg
+    out["device"]["decode_GBps"] = alg / (out["device"]["ply_decode_ms"] * 1e-3) / 1e9
+    if cpu:
+        import oracle as O                   # the CPU-baseline leg only: times the reference's own loader
+    if cpu and os.path.exists(os.path.join(O.REF_DIR, "mtsutil")):
+        with tempfile.TemporaryDirectory() as td:
+            files = []
+            for k, img in images.items():
+                fn = os.path.join(td, "m%d.ply" % k)
+                with open(fn, "wb") as f:
+                    f.write(img)
+                files.append(fn)
+            r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "plyload"] + files, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            line = [l for l in r.stdout.splitlines() if l.startswith("plyload:")]
+            if line:
+                out["reference"] = {"ply_load_s": float(line[0].split(" in ")[1].split()[0]), "threads": 1, "kind": "reference",
+                                    "what": "PLYLoader + TriMesh::configure of the unmodified reference on the same files, no kd-tree"}
+    return out
+
+
 def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=None, spp4=1024, spp3=256, builder=None):
     S = pkg.scenes
     out = {}
@@ -270,7 +322,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
             out["volpath_cpu_reference"] = cpu_reference(pkg, S.fog_scene(1024, 768, spp=8, max_depth=8, haze=True), os.cpu_count() or 1,
                                                          what="fog scene (volpath_simple) at %d spp (of 64)")
     sd = None
-    if {3, 4, 5, "plugin"} & set(configs):
+    if {3, 4, 5, "plugin", "ply"} & set(configs):
         t0 = time.perf_counter()
         sd = S.sphere_field(subdiv=6, nx=16, ny=8, width=1920, height=1080, spp=256, max_depth=8, rfilter="gaussian")
         gen_s = time.perf_counter() - t0
@@ -291,6 +343,8 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
                 out["config3_cpu_reference"] = c
                 out["config5_cpu_reference"] = {"fps": c["samples_per_s"] / (1280 * 720), "kind": "reference (derived)", "cores": c["cores"],
                                                 "sample": "1280x720 x 1 spp frames at the rate of config3_cpu_reference; kd-tree build (%s ms) excluded" % c["kd_build_ms"]}
+    if "ply" in configs and rank == 0:
+        out["ply_load_config3_meshes"] = ply_load_bench(pkg, ctx, sd, cpu=cpu)
     if "plugin" in configs and rank == 0:
         import torch
         out["plugin"] = plugin_bench(pkg, sd, gpus=(1, 2) if torch.cuda.device_count() >= 2 else (1,))
@@ -305,7 +359,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", nargs="*", default=["1", "3", "5"], help="1 3 4 5, vol and/or plugin")
+    ap.add_argument("--config", nargs="*", default=["1", "3", "5"], help="1 3 4 5, vol, ply and/or plugin")
     ap.add_argument("--spp4", type=int, default=1024)
     ap.add_argument("--builder", default=None, choices=["lbvh", "ploc"])
     ap.add_argument("--spp3", type=int, default=256, help="samples per pixel of config 3 (BASELINE: 256; smaller only for ncu runs)")

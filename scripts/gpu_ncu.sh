@@ -12,5 +12,5 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
 $R3 > gpurun_out/ncu_plain_c3.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_c3.csv $R3 > gpurun_out/ncu_c3_1.log 2>&1
 $R3 > gpurun_out/ncu_plain_c3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'extend_kernel|shade_kernel|connect_kernel|splat_kernel|generate_kernel' -s 1 -c 12 -o gpurun_out/prof_render -f $R3 > gpurun_out/ncu_render2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'extend_kernel|shade_kernel|connect_kernel|splat_kernel|generate_kernel' -s 1 -c 8 -o gpurun_out/prof_render -f $R3 > gpurun_out/ncu_render2.log 2>&1
 ls -la gpurun_out | tail -5
