@@ -357,6 +357,12 @@ def main():
         detail["closest_mrays_%s" % ("lbvh" if other == B.BUILDER_LBVH else "ploc")] = n / (a.elapsed_time(b) / 3) / 1e3
         detail["build_other"] = sc2.build_stats()
         sc2.close()
+        # the build once more: 3 of 12 recorded runs read 0.7-0.8 s for the build above (14 ms everywhere else; the phases add up to
+        # 14 ms under a per-phase trace, profiles/r02r_build_trace.log) — a host-side stall inside the event window, right after
+        # the clock sampler's nvidia-smi subprocess is torn down.  Both readings are reported.
+        sc3 = sd.upload(ctx, other)
+        detail["build_other"]["build_ms_again"] = sc3.build_stats()["build_ms"]
+        sc3.close()
         sc.trace_device("closest", rays_d.data_ptr(), n, hits_d.data_ptr())      # hits_d back to the headline tree's answers
         torch.cuda.synchronize()
         res = 4096 if n >= (1 << 24) else int(np.sqrt(n))
