@@ -285,11 +285,27 @@ def ply_load_bench(pkg, ctx, sd, cpu=True):
                                      and np.abs(N - sd.shapes[k]["N"]).max() <= 2e-7)
                 out["decoded_equals_source_arrays"] = ok
             sc.close()
+    # the same meshes as `serialized` files (one deflate stream each): inflated on the host by zlib, decoded by the same kernels
+    ser = {k: S.serialized_image([dict(V=sd.shapes[k]["V"], F=sd.shapes[k]["F"], N=sd.shapes[k]["N"])], level=1) for k in images}
+    for rep in range(2):
+        t0 = time.perf_counter()
+        sc = B.Scene(ctx)
+        bs = sc.add_bsdf(B.BSDF_DIFFUSE, (0.5, 0.5, 0.5))
+        for k in ser:
+            sc.add_serialized(ser[k], bsdf=bs)
+        t1 = time.perf_counter()
+        sc.commit(B.BUILDER_PLOC)
+        ctx.sync()
+        st = sc.build_stats()
+        out["serialized_device"] = {"file_bytes": sum(len(v) for v in ser.values()), "inflate_and_upload_s": t1 - t0, "commit_s": time.perf_counter() - t1,
+                                    "bvh_build_ms": st["build_ms"], "decode_ms": st["ply_decode_ms"]}
+        sc.close()
     # algorithmic bytes of the decode: the file body read once, 32 B per vertex and 12 B per triangle written
     alg = body + 32 * nv + 12 * nt
     out["device"]["decode_algorithmic_bytes"] = alg
     out["device"]["decode_GBps"] = alg / (out["device"]["ply_decode_ms"] * 1e-3) / 1e9
     if cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import oracle as O                   # the CPU-baseline leg only: times the reference's own loader
     if cpu and os.path.exists(os.path.join(O.REF_DIR, "mtsutil")):
         with tempfile.TemporaryDirectory() as td:
@@ -304,6 +320,16 @@ def ply_load_bench(pkg, ctx, sd, cpu=True):
             if line:
                 out["reference"] = {"ply_load_s": float(line[0].split(" in ")[1].split()[0]), "threads": 1, "kind": "reference",
                                     "what": "PLYLoader + TriMesh::configure of the unmodified reference on the same files, no kd-tree"}
+            files = []
+            for k, img in ser.items():
+                fn = os.path.join(td, "m%d.serialized" % k)
+                with open(fn, "wb") as f:
+                    f.write(img)
+                files.append(fn)
+            r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "plyload"] + files, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            line = [l for l in r.stdout.splitlines() if l.startswith("plyload:")]
+            if line:
+                out["reference"]["serialized_load_s"] = float(line[0].split(" in ")[1].split()[0])
     return out
 
 

@@ -251,6 +251,16 @@ MTSB_API int  mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, con
 MTSB_API int  mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const float to_world[16],
                                  const float to_world_inv[16], uint32_t flags, int bsdf,
                                  uint32_t *vertex_count, uint32_t *triangle_count);
+/* A `serialized` mesh file (TriMesh::loadCompressed, src/librender/trimesh.cpp:176-296, and the `serialized` shape plugin,
+ * src/shapes/serialized.cpp:148-210): `file` is the whole file image, shape_index the mesh inside it (`shapeIndex`, offset
+ * dictionary of format versions 3 and 4).  The deflate stream is inflated on the host (zlib, sequential by nature); the
+ * payload — one array per attribute, float or double — is converted, sent through to_world (a mirroring transform swaps the
+ * winding, stored normals are re-normalised only behind a transform, as the plugin does), triangulated and given computed
+ * normals by the same kernels as mtsb_scene_add_ply at commit.  flags as for mtsb_scene_add_ply.  Vertex colours are skipped. */
+MTSB_API int  mtsb_scene_add_serialized(mtsb_scene *scene, const void *file, size_t bytes, int shape_index,
+                                        const float to_world[16], const float to_world_inv[16], uint32_t flags, int bsdf,
+                                        uint32_t *vertex_count, uint32_t *triangle_count);
+MTSB_API int  mtsb_serialized_probe(const void *file, size_t bytes, int shape_index, uint32_t *vertex_count, uint32_t *triangle_count);
 /* Header of a binary PLY file image only: the vertex and triangle counts mtsb_scene_add_ply would produce, or the error it
  * would return (no device work, no scene) — lets a caller that already holds the host-parsed mesh check the two agree. */
 MTSB_API int  mtsb_ply_probe(const void *file, size_t bytes, uint32_t *vertex_count, uint32_t *triangle_count);

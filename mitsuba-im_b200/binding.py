@@ -125,6 +125,8 @@ def lib():
         "mtsb_scene_add_ply": (i32, [vp, vp, sz, vp, vp, u32, i32, C.POINTER(u32), C.POINTER(u32)]),
         "mtsb_scene_read_mesh": (i32, [vp, i32, vp, vp, vp, vp]),
         "mtsb_ply_probe": (i32, [vp, sz, C.POINTER(u32), C.POINTER(u32)]),
+        "mtsb_scene_add_serialized": (i32, [vp, vp, sz, i32, vp, vp, u32, i32, C.POINTER(u32), C.POINTER(u32)]),
+        "mtsb_serialized_probe": (i32, [vp, sz, i32, C.POINTER(u32), C.POINTER(u32)]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
         "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
@@ -175,6 +177,13 @@ def ply_probe(image):
     buf = np.frombuffer(image, dtype=np.uint8)
     nv, nt = C.c_uint32(0), C.c_uint32(0)
     _check(lib().mtsb_ply_probe(_ptr(buf), buf.size, C.byref(nv), C.byref(nt)))
+    return nv.value, nt.value
+
+
+def serialized_probe(image, shape_index=0):
+    buf = np.frombuffer(image, dtype=np.uint8)
+    nv, nt = C.c_uint32(0), C.c_uint32(0)
+    _check(lib().mtsb_serialized_probe(_ptr(buf), buf.size, int(shape_index), C.byref(nv), C.byref(nt)))
     return nv.value, nt.value
 
 
@@ -307,6 +316,21 @@ class Scene:
         nv, nt = C.c_uint32(0), C.c_uint32(0)
         flags = (PLY_FACE_NORMALS if face_normals else 0) | (PLY_FLIP_NORMALS if flip_normals else 0)
         shape = _check(lib().mtsb_scene_add_ply(self.h, _ptr(buf), buf.size, _ptr(M), _ptr(Mi), flags, bsdf, C.byref(nv), C.byref(nt)))
+        if not hasattr(self, "_mesh_sizes"):
+            self._mesh_sizes = {}
+        self._mesh_sizes[shape] = (nv.value, nt.value)
+        return shape
+
+    def add_serialized(self, image, shape_index=0, to_world=None, face_normals=False, flip_normals=False, bsdf=0):
+        """A `serialized` mesh file image: inflated on the host, decoded on the device at commit (mtsb_scene_add_serialized)."""
+        buf = np.frombuffer(image, dtype=np.uint8) if not isinstance(image, np.ndarray) else np.ascontiguousarray(image, dtype=np.uint8)
+        M = Mi = None
+        if to_world is not None:
+            M = np.ascontiguousarray(to_world, dtype=np.float32).reshape(4, 4)
+            Mi = np.ascontiguousarray(np.linalg.inv(M.astype(np.float64)), dtype=np.float32)
+        nv, nt = C.c_uint32(0), C.c_uint32(0)
+        flags = (PLY_FACE_NORMALS if face_normals else 0) | (PLY_FLIP_NORMALS if flip_normals else 0)
+        shape = _check(lib().mtsb_scene_add_serialized(self.h, _ptr(buf), buf.size, int(shape_index), _ptr(M), _ptr(Mi), flags, bsdf, C.byref(nv), C.byref(nt)))
         if not hasattr(self, "_mesh_sizes"):
             self._mesh_sizes = {}
         self._mesh_sizes[shape] = (nv.value, nt.value)

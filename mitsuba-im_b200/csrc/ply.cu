@@ -1,4 +1,4 @@
-// ply.cu — binary PLY files decoded on the device (the on-disk geometry path).
+// ply.cu — mesh files decoded on the device: binary PLY and `serialized` (the on-disk geometry path).
 //
 // What the reference does on one host thread (src/shapes/ply.cpp:146-290 driving src/shapes/ply/ply_parser.cpp: one
 // std::function call per scalar, per vertex and per face, then TriMesh::configure -> computeNormals,
@@ -24,6 +24,7 @@
 #include <string>
 #include <cstring>
 #include <cstdlib>
+#include <zlib.h>
 
 namespace mtsb {
 
@@ -32,9 +33,15 @@ struct PlyLayout {
 	uint32_t vertexStride, faceStride;
 	int offPos[3], offNrm[3], offUV[2];   // byte offsets inside a vertex record, -1 = absent
 	uint32_t faceListOffset;              // offset of the list inside a face record
-	uint32_t faceCountBytes;              // 1 (uchar) or 4 (uint)
+	uint32_t faceCountBytes;              // 1 (uchar) or 4 (uint); 0 = no count field (`serialized`: bare index triples)
 	uint32_t vertsPerFace;                // 3 or 4
 	size_t vertexBegin, faceBegin;        // byte offsets of the two elements in the file
+	// PLY interleaves a vertex's properties in one record (the three bases equal vertexBegin, the strides vertexStride); the
+	// `serialized` payload stores one array per attribute
+	size_t posBase, nrmBase, uvBase;
+	uint32_t posStride, nrmStride, uvStride;
+	int f64;                              // attributes are doubles (`serialized` with EDoublePrecision), converted like readHelper does
+	int normalizeStored;                  // ply.cpp:210 always normalises a stored normal, serialized.cpp:191-194 only behind a toWorld
 };
 
 __device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteOffset) {
@@ -44,6 +51,10 @@ __device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteO
 	return __funnelshift_r(lo, words[w + 1], sh);
 }
 __device__ __forceinline__ float load_f32(const uint32_t *words, size_t byteOffset) { return __uint_as_float(load_u32(words, byteOffset)); }
+__device__ __forceinline__ float load_real(const uint32_t *words, size_t byteOffset, int f64) {
+	if (!f64) return load_f32(words, byteOffset);
+	return (float) __hiloint2double((int) load_u32(words, byteOffset + 4), (int) load_u32(words, byteOffset));     // (Float) temp[i]
+}
 
 struct PlyXform { float m[16], inv[16]; int identity; };
 
@@ -51,9 +62,10 @@ __global__ void ply_vertex_kernel(const uint32_t *words, size_t base, PlyLayout 
 		float *positions, float *normals, float *texcoords) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= L.vertexCount) return;
-	const size_t rec = base + L.vertexBegin + (size_t) i * L.vertexStride;
+	const size_t recP = base + L.posBase + (size_t) i * L.posStride, recN = base + L.nrmBase + (size_t) i * L.nrmStride,
+		recT = base + L.uvBase + (size_t) i * L.uvStride;
 	float p[3];
-	for (int a = 0; a < 3; ++a) p[a] = L.offPos[a] >= 0 ? load_f32(words, rec + L.offPos[a]) : 0.0f;
+	for (int a = 0; a < 3; ++a) p[a] = L.offPos[a] >= 0 ? load_real(words, recP + L.offPos[a], L.f64) : 0.0f;
 	if (!X.identity) {
 		// the reference's expression order, no contraction
 		float q[4];
@@ -65,21 +77,21 @@ __global__ void ply_vertex_kernel(const uint32_t *words, size_t base, PlyLayout 
 	positions[(size_t) i * 3] = p[0]; positions[(size_t) i * 3 + 1] = p[1]; positions[(size_t) i * 3 + 2] = p[2];
 	if (L.offNrm[0] >= 0 && !zeroNormals) {
 		float n[3];
-		for (int a = 0; a < 3; ++a) n[a] = L.offNrm[a] >= 0 ? load_f32(words, rec + L.offNrm[a]) : 0.0f;
+		for (int a = 0; a < 3; ++a) n[a] = L.offNrm[a] >= 0 ? load_real(words, recN + L.offNrm[a], L.f64) : 0.0f;
 		if (!X.identity) {
 			float t[3];
 			for (int c = 0; c < 3; ++c)
 				t[c] = __fadd_rn(__fadd_rn(__fmul_rn(X.inv[c], n[0]), __fmul_rn(X.inv[4 + c], n[1])), __fmul_rn(X.inv[8 + c], n[2]));
 			n[0] = t[0]; n[1] = t[1]; n[2] = t[2];
 		}
-		float inv = 1.0f / sqrtf(n[0]*n[0] + n[1]*n[1] + n[2]*n[2]);     // normalize(): v / length
+		float inv = L.normalizeStored ? 1.0f / sqrtf(n[0]*n[0] + n[1]*n[1] + n[2]*n[2]) : 1.0f;     // normalize(): v / length
 		if (flipNormals) inv = -inv;                                      // computeNormals: m_normals[i] *= -1
 		normals[(size_t) i * 3] = n[0] * inv; normals[(size_t) i * 3 + 1] = n[1] * inv; normals[(size_t) i * 3 + 2] = n[2] * inv;
 	} else {
 		normals[(size_t) i * 3] = 0; normals[(size_t) i * 3 + 1] = 0; normals[(size_t) i * 3 + 2] = 0;
 	}
-	texcoords[(size_t) i * 2]     = L.offUV[0] >= 0 ? load_f32(words, rec + L.offUV[0]) : 0.0f;
-	texcoords[(size_t) i * 2 + 1] = L.offUV[1] >= 0 ? load_f32(words, rec + L.offUV[1]) : 0.0f;
+	texcoords[(size_t) i * 2]     = L.offUV[0] >= 0 ? load_real(words, recT + L.offUV[0], L.f64) : 0.0f;
+	texcoords[(size_t) i * 2 + 1] = L.offUV[1] >= 0 ? load_real(words, recT + L.offUV[1], L.f64) : 0.0f;
 }
 
 __device__ __forceinline__ float unit_angle(const float *u, const float *v) {      // include/mitsuba/core/util.h:321-326
@@ -117,9 +129,11 @@ __global__ void ply_face_kernel(const uint32_t *words, size_t base, PlyLayout L,
 	const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
 	if (f >= L.faceCount) return;
 	const size_t rec = base + L.faceBegin + (size_t) f * L.faceStride + L.faceListOffset;
-	uint32_t count = load_u32(words, rec);
-	if (L.faceCountBytes == 1) count &= 0xffu;
-	if (count != L.vertsPerFace) { atomicOr(error, 1u); return; }
+	if (L.faceCountBytes) {
+		uint32_t count = load_u32(words, rec);
+		if (L.faceCountBytes == 1) count &= 0xffu;
+		if (count != L.vertsPerFace) { atomicOr(error, 1u); return; }
+	}
 	uint32_t v[4] = { 0, 0, 0, 0 };
 	bool ok = true;
 	for (uint32_t k = 0; k < L.vertsPerFace; ++k) {
@@ -175,8 +189,10 @@ static std::vector<std::string> split_ws(const std::string &line) {
 
 struct PlyMesh {
 	PlyLayout L; PlyXform X;
-	DevBuf<uint32_t> raw; size_t base = 0;       // file image on the device, its first byte at byte `base` of raw
+	DevBuf<uint32_t> raw; size_t base = 0;       // file image (PLY) / inflated payload (serialized) on the device, its first byte at byte `base` of raw
 	int shape = -1; bool hasNormals = false, faceNormals = false, flipNormals = false;
+	bool mirrored = false;                       // serialized.cpp:197-202: a toWorld with a negative determinant swaps the winding
+	const char *kind = "PLY";
 	uint32_t vtxBase = 0, triBase = 0;
 };
 
@@ -269,6 +285,34 @@ static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, b
 	else if (faceBytes == (fixed + 16) * L.faceCount) L.vertsPerFace = 4;
 	else MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_ply: %u faces in %zu bytes: neither all triangles nor all quads (or a truncated file); mixed files go through the host parser", L.faceCount, faceBytes);
 	L.faceStride = (uint32_t) (fixed + 4 * L.vertsPerFace);
+	L.posBase = L.nrmBase = L.uvBase = L.vertexBegin;
+	L.posStride = L.nrmStride = L.uvStride = L.vertexStride;
+	L.f64 = 0; L.normalizeStored = 1;
+	return 0;
+}
+
+static int set_transform(PlyMesh *M, const float *toWorld, const float *toWorldInv, const char *who) {
+	memset(&M->X, 0, sizeof(M->X));
+	M->X.identity = 1;
+	for (int i = 0; i < 16; ++i) { M->X.m[i] = M->X.inv[i] = (i % 5 == 0) ? 1.0f : 0.0f; }
+	if (toWorld) {
+		if (!toWorldInv) MTSB_FAIL(MTSB_EINVAL, "%s: to_world needs its inverse beside it (Transform holds both)", who);
+		for (int i = 0; i < 16; ++i) { M->X.m[i] = toWorld[i]; M->X.inv[i] = toWorldInv[i]; if (toWorld[i] != ((i % 5 == 0) ? 1.0f : 0.0f)) M->X.identity = 0; }
+	}
+	return 0;
+}
+
+// the image goes to the device with its position block on a 16-byte boundary; 8 bytes of slack behind it for load_u32
+static int upload_image(mtsb_scene *scene, PlyMesh *M, const void *image, size_t bytes, const char *who) {
+	mtsb_ctx *ctx = scene->ctx;
+	cudaSetDevice(ctx->device);
+	M->base = (16 - (M->L.posBase & 15)) & 15;
+	const size_t words = (M->base + bytes + 8 + 3) / 4;
+	MTSB_CHECK(M->raw.alloc(words));
+	cudaError_t e = cudaMemsetAsync(M->raw.ptr + (words - 3), 0, 12, ctx->stream);
+	if (e == cudaSuccess) e = cudaMemcpyAsync((unsigned char *) M->raw.ptr + M->base, image, bytes, cudaMemcpyHostToDevice, ctx->stream);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);          // the caller's buffer may go away after the call
+	if (e != cudaSuccess) MTSB_FAIL(MTSB_ECUDA, "%s: upload: %s", who, cudaGetErrorString(e));
 	return 0;
 }
 
@@ -277,27 +321,127 @@ int ply_stage(mtsb_scene *scene, const void *file, size_t bytes, const float *to
 	PlyMesh *M = new PlyMesh();
 	bool hasUV = false;
 	int rc = parse_header((const unsigned char *) file, bytes, M->L, M->hasNormals, hasUV);
-	if (rc) { delete M; return rc; }
-	memset(&M->X, 0, sizeof(M->X));
-	M->X.identity = 1;
-	for (int i = 0; i < 16; ++i) { M->X.m[i] = M->X.inv[i] = (i % 5 == 0) ? 1.0f : 0.0f; }
-	if (toWorld) {
-		if (!toWorldInv) { delete M; MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: to_world needs its inverse beside it (Transform holds both)"); }
-		for (int i = 0; i < 16; ++i) { M->X.m[i] = toWorld[i]; M->X.inv[i] = toWorldInv[i]; if (toWorld[i] != ((i % 5 == 0) ? 1.0f : 0.0f)) M->X.identity = 0; }
-	}
+	if (!rc) rc = set_transform(M, toWorld, toWorldInv, "mtsb_scene_add_ply");
 	M->faceNormals = (flags & MTSB_PLY_FACE_NORMALS) != 0; M->flipNormals = (flags & MTSB_PLY_FLIP_NORMALS) != 0;
-	// the file image goes to the device with its vertex block on a 16-byte boundary; 8 bytes of slack behind it for load_u32
-	mtsb_ctx *ctx = scene->ctx;
-	cudaSetDevice(ctx->device);
-	M->base = (16 - (M->L.vertexBegin & 15)) & 15;
-	const size_t words = (M->base + bytes + 8 + 3) / 4;
-	rc = M->raw.alloc(words);
+	if (!rc) rc = upload_image(scene, M, file, bytes, "mtsb_scene_add_ply");
 	if (rc) { delete M; return rc; }
-	cudaError_t e = cudaMemsetAsync(M->raw.ptr + (words - 3), 0, 12, ctx->stream);
-	if (e == cudaSuccess) e = cudaMemcpyAsync((unsigned char *) M->raw.ptr + M->base, file, bytes, cudaMemcpyHostToDevice, ctx->stream);
-	if (e != cudaSuccess) { delete M; MTSB_FAIL(MTSB_ECUDA, "mtsb_scene_add_ply: upload: %s", cudaGetErrorString(e)); }
 	(void) bsdf;
 	*vertexCountOut = M->L.vertexCount; *triangleCountOut = M->L.faceCount * (M->L.vertsPerFace - 2);
+	*hasUVOut = hasUV; *hasNormalsOut = M->hasNormals && !M->faceNormals;
+	*out = M;
+	return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// `serialized` (TriMesh::loadCompressed, src/librender/trimesh.cpp:176-253, readOffset :274-296; shapes/serialized.cpp:148-210)
+// A deflate stream is sequential: it is inflated here on the host (zlib, as the reference's ZStream does) straight into one
+// buffer; the payload — one array per attribute, float or double — goes to the device in one copy and the kernels above
+// convert, transform and triangulate it.
+// ---------------------------------------------------------------------------------------------------------------------------
+static inline uint32_t rd_u32(const unsigned char *p) { uint32_t v; memcpy(&v, p, 4); return v; }
+static inline uint64_t rd_u64(const unsigned char *p) { uint64_t v; memcpy(&v, p, 8); return v; }
+static inline uint16_t rd_u16(const unsigned char *p) { uint16_t v; memcpy(&v, p, 2); return v; }
+
+static int ser_open(const unsigned char *f, size_t bytes, int index, size_t &dataBegin, int &version) {
+	if (bytes < 8) MTSB_FAIL(MTSB_EINVAL, "serialized: file too short");
+	if (rd_u16(f) != 0x041C) MTSB_FAIL(MTSB_EINVAL, "serialized: encountered an invalid file format");
+	version = rd_u16(f + 2);
+	if (version != 3 && version != 4) MTSB_FAIL(MTSB_EINVAL, "serialized: encountered an incompatible file version (%d)", version);
+	size_t offset = 0;
+	if (index != 0) {
+		const uint32_t count = rd_u32(f + bytes - 4);
+		if (index < 0 || (uint32_t) index >= count) MTSB_FAIL(MTSB_EINVAL, "serialized: shape index is out of range (requested %d out of 0..%u)", index, count - 1);
+		const size_t entry = version == 4 ? 8 : 4;
+		if ((size_t) count * entry + 4 > bytes) MTSB_FAIL(MTSB_EINVAL, "serialized: offset dictionary larger than the file");
+		const size_t pos = version == 4 ? bytes - 8 * (size_t) (count - index) - 4 : bytes - 4 * (size_t) (count - index + 1);
+		offset = version == 4 ? (size_t) rd_u64(f + pos) : (size_t) rd_u32(f + pos);
+		if (offset + 4 > bytes) MTSB_FAIL(MTSB_EINVAL, "serialized: mesh offset beyond the end of the file");
+	}
+	dataBegin = offset + 4;
+	return 0;
+}
+
+// inflates the mesh's header (flags, name, counts), then — unless probing — the whole payload into `out`
+static int ser_inflate(const unsigned char *src, size_t srcBytes, int version, PlyLayout &L, bool &hasNormals, bool &hasUV,
+		std::vector<unsigned char> *out) {
+	z_stream z; memset(&z, 0, sizeof(z));
+	if (inflateInit2(&z, 15) != Z_OK) MTSB_FAIL(MTSB_EINVAL, "serialized: could not initialize zlib");
+	z.next_in = (Bytef *) src; z.avail_in = (uInt) std::min<size_t>(srcBytes, 0x40000000u);
+	size_t consumed = z.avail_in;
+	std::vector<unsigned char> head(4096);
+	z.next_out = head.data(); z.avail_out = (uInt) head.size();
+	int rc = inflate(&z, Z_SYNC_FLUSH);
+	if (rc != Z_OK && rc != Z_STREAM_END) { inflateEnd(&z); MTSB_FAIL(MTSB_EINVAL, "serialized: inflate(): stream error %d", rc); }
+	const size_t got = head.size() - z.avail_out;
+	size_t p = 4;
+	if (version == 4) { while (p < got && head[p] != 0) ++p; ++p; }
+	if (p + 16 > got) { inflateEnd(&z); MTSB_FAIL(MTSB_EINVAL, "serialized: mesh header truncated (or a name longer than 4 KB)"); }
+	const uint32_t flags = rd_u32(head.data());
+	const uint64_t V = rd_u64(head.data() + p), T = rd_u64(head.data() + p + 8);
+	p += 16;
+	if (V == 0 || T == 0 || V > 0xffffffffull || T > 0x7fffffffull) { inflateEnd(&z); MTSB_FAIL(MTSB_EINVAL, "serialized: %llu vertices, %llu triangles", (unsigned long long) V, (unsigned long long) T); }
+	memset(&L, 0, sizeof(L));
+	L.f64 = (flags & 0x2000u) ? 1 : 0;                                    // EDoublePrecision
+	const uint32_t fsz = L.f64 ? 8 : 4;
+	L.vertexCount = (uint32_t) V; L.faceCount = (uint32_t) T; L.vertsPerFace = 3; L.faceCountBytes = 0; L.faceListOffset = 0; L.faceStride = 12;
+	for (int a = 0; a < 3; ++a) { L.offPos[a] = (int) (a * fsz); L.offNrm[a] = -1; }
+	L.offUV[0] = L.offUV[1] = -1;
+	size_t next = p;
+	L.posBase = next; L.posStride = 3 * fsz; next += (size_t) V * 3 * fsz;
+	L.nrmBase = L.uvBase = L.posBase; L.nrmStride = L.uvStride = 0;
+	hasNormals = (flags & 0x0001u) != 0; hasUV = (flags & 0x0002u) != 0;
+	if (hasNormals) { L.nrmBase = next; L.nrmStride = 3 * fsz; for (int a = 0; a < 3; ++a) L.offNrm[a] = (int) (a * fsz); next += (size_t) V * 3 * fsz; }
+	if (hasUV) { L.uvBase = next; L.uvStride = 2 * fsz; L.offUV[0] = 0; L.offUV[1] = (int) fsz; next += (size_t) V * 2 * fsz; }
+	if (flags & 0x0008u) next += (size_t) V * 3 * fsz;                    // EHasColors: stepped over
+	L.faceBegin = next; L.vertexBegin = L.posBase; L.vertexStride = L.posStride;
+	const size_t total = next + (size_t) T * 12;
+	if (!out) { inflateEnd(&z); return 0; }
+	out->resize(total);
+	memcpy(out->data(), head.data(), std::min(got, total));
+	size_t have = std::min(got, total);
+	while (have < total && rc != Z_STREAM_END) {
+		if (z.avail_in == 0 && consumed < srcBytes) { z.avail_in = (uInt) std::min<size_t>(srcBytes - consumed, 0x40000000u); consumed += z.avail_in; }
+		z.next_out = out->data() + have; z.avail_out = (uInt) std::min<size_t>(total - have, 0x40000000u);
+		const size_t before = z.avail_out;
+		rc = inflate(&z, Z_NO_FLUSH);
+		have += before - z.avail_out;
+		if (rc != Z_OK && rc != Z_STREAM_END) break;
+		if (before == z.avail_out && z.avail_in == 0 && consumed >= srcBytes) break;
+	}
+	inflateEnd(&z);
+	if (have < total) MTSB_FAIL(MTSB_EINVAL, "serialized: the stream ends after %zu of %zu payload bytes (zlib %d)", have, total, rc);
+	return 0;
+}
+
+int ser_probe(const void *file, size_t bytes, int index, uint32_t *nv, uint32_t *nt) {
+	size_t begin = 0; int version = 0; PlyLayout L; bool hn, hu;
+	MTSB_CHECK(ser_open((const unsigned char *) file, bytes, index, begin, version));
+	MTSB_CHECK(ser_inflate((const unsigned char *) file + begin, bytes - begin, version, L, hn, hu, nullptr));
+	if (nv) *nv = L.vertexCount;
+	if (nt) *nt = L.faceCount;
+	return 0;
+}
+
+int ser_stage(mtsb_scene *scene, const void *file, size_t bytes, int index, const float *toWorld, const float *toWorldInv, uint32_t flags,
+		uint32_t *vertexCountOut, uint32_t *triangleCountOut, bool *hasUVOut, bool *hasNormalsOut, PlyMesh **out) {
+	size_t begin = 0; int version = 0;
+	MTSB_CHECK(ser_open((const unsigned char *) file, bytes, index, begin, version));
+	PlyMesh *M = new PlyMesh();
+	M->kind = "serialized";
+	bool hasUV = false;
+	std::vector<unsigned char> payload;
+	int rc = ser_inflate((const unsigned char *) file + begin, bytes - begin, version, M->L, M->hasNormals, hasUV, &payload);
+	if (!rc) rc = set_transform(M, toWorld, toWorldInv, "mtsb_scene_add_serialized");
+	if (!rc) {
+		const float *m = M->X.m;
+		const float det = m[0] * (m[5] * m[10] - m[6] * m[9]) - m[1] * (m[4] * m[10] - m[6] * m[8]) + m[2] * (m[4] * m[9] - m[5] * m[8]);
+		M->mirrored = det < 0;
+		M->L.normalizeStored = M->X.identity ? 0 : 1;
+		M->faceNormals = (flags & MTSB_PLY_FACE_NORMALS) != 0; M->flipNormals = (flags & MTSB_PLY_FLIP_NORMALS) != 0;
+		rc = upload_image(scene, M, payload.data(), payload.size(), "mtsb_scene_add_serialized");
+	}
+	if (rc) { delete M; return rc; }
+	*vertexCountOut = M->L.vertexCount; *triangleCountOut = M->L.faceCount;
 	*hasUVOut = hasUV; *hasNormalsOut = M->hasNormals && !M->faceNormals;
 	*out = M;
 	return 0;
@@ -326,7 +470,7 @@ int ply_decode(mtsb_scene *scene, PlyMesh *M, float *positions, float *normals, 
 	MTSB_CUDA(cudaEventCreate(&ev0)); MTSB_CUDA(cudaEventCreate(&ev1));
 	MTSB_CUDA(cudaEventRecord(ev0, st));
 	ply_vertex_kernel<<<(L.vertexCount + 255) / 256, 256, 0, st>>>(M->raw.ptr, M->base, L, M->X, M->flipNormals ? 1 : 0, (M->faceNormals || compute) ? 1 : 0, P, N, T);
-	ply_face_kernel<<<(L.faceCount + 255) / 256, 256, 0, st>>>(M->raw.ptr, M->base, L, (M->faceNormals && M->flipNormals) ? 1 : 0, compute ? 1 : 0, P, N, I, scratch);
+	ply_face_kernel<<<(L.faceCount + 255) / 256, 256, 0, st>>>(M->raw.ptr, M->base, L, ((M->faceNormals && M->flipNormals) != M->mirrored) ? 1 : 0, compute ? 1 : 0, P, N, I, scratch);
 	if (compute) ply_normalize_kernel<<<(L.vertexCount + 255) / 256, 256, 0, st>>>(L.vertexCount, M->flipNormals ? 1 : 0, N, scratch + 1);
 	MTSB_CUDA(cudaEventRecord(ev1, st));
 	MTSB_CUDA(cudaGetLastError());
@@ -335,8 +479,8 @@ int ply_decode(mtsb_scene *scene, PlyMesh *M, float *positions, float *normals, 
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	float ms = 0; cudaEventElapsedTime(&ms, ev0, ev1); scene->plyDecodeMs += ms;
 	cudaEventDestroy(ev0); cudaEventDestroy(ev1);
-	if (err[0] & 1u) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_commit: PLY shape %d mixes triangles and quads (or holds a face that is neither): load it with the host parser", M->shape);
-	if (err[0] & 2u) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: PLY shape %d: a face references a vertex >= %u", M->shape, L.vertexCount);
+	if (err[0] & 1u) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_commit: %s shape %d mixes triangles and quads (or holds a face that is neither): load it with the host parser", M->kind, M->shape);
+	if (err[0] & 2u) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: %s shape %d: a face references a vertex >= %u", M->kind, M->shape, L.vertexCount);
 	M->raw.release();
 	return 0;
 }

@@ -308,15 +308,10 @@ int mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, const float *
 	return (int) scene->shapes.size() - 1;
 }
 
-int mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const float to_world[16], const float to_world_inv[16],
-		uint32_t flags, int bsdf, uint32_t *vertex_count, uint32_t *triangle_count) {
-	if (!scene || !file) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: NULL argument");
-	MTSB_CHECK(check_refs(scene, bsdf, -1, "mtsb_scene_add_ply"));
-	if (flags & ~(MTSB_PLY_FACE_NORMALS | MTSB_PLY_FLIP_NORMALS)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: unknown flags %#x", flags);
-	uint32_t nv = 0, nt = 0; bool hasUV = false, hasNormals = false; PlyMesh *M = nullptr;
-	MTSB_CHECK(ply_stage(scene, file, bytes, to_world, to_world_inv, flags, bsdf, &nv, &nt, &hasUV, &hasNormals, &M));
+static int add_decoded_mesh(mtsb_scene *scene, PlyMesh *M, uint32_t nv, uint32_t nt, bool hasUV, uint32_t flags, int bsdf,
+		uint32_t *vertex_count, uint32_t *triangle_count, const char *who) {
 	if ((uint64_t) scene->primCount + nt > 0x7fffffffull || scene->vtxTotal + nv > 0xffffffffull) {
-		ply_release(M); MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: more than 2^31 primitives");
+		ply_release(M); MTSB_FAIL(MTSB_EINVAL, "%s: more than 2^31 primitives", who);
 	}
 	ShapeRec sh; memset(&sh, 0, sizeof(sh));
 	sh.type = SHAPE_MESH;
@@ -335,6 +330,31 @@ int mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const 
 	if (vertex_count) *vertex_count = nv;
 	if (triangle_count) *triangle_count = nt;
 	return (int) scene->shapes.size() - 1;
+}
+
+int mtsb_scene_add_ply(mtsb_scene *scene, const void *file, size_t bytes, const float to_world[16], const float to_world_inv[16],
+		uint32_t flags, int bsdf, uint32_t *vertex_count, uint32_t *triangle_count) {
+	if (!scene || !file) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, -1, "mtsb_scene_add_ply"));
+	if (flags & ~(MTSB_PLY_FACE_NORMALS | MTSB_PLY_FLIP_NORMALS)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: unknown flags %#x", flags);
+	uint32_t nv = 0, nt = 0; bool hasUV = false, hasNormals = false; PlyMesh *M = nullptr;
+	MTSB_CHECK(ply_stage(scene, file, bytes, to_world, to_world_inv, flags, bsdf, &nv, &nt, &hasUV, &hasNormals, &M));
+	return add_decoded_mesh(scene, M, nv, nt, hasUV, flags, bsdf, vertex_count, triangle_count, "mtsb_scene_add_ply");
+}
+
+int mtsb_scene_add_serialized(mtsb_scene *scene, const void *file, size_t bytes, int shape_index, const float to_world[16],
+		const float to_world_inv[16], uint32_t flags, int bsdf, uint32_t *vertex_count, uint32_t *triangle_count) {
+	if (!scene || !file) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_serialized: NULL argument");
+	MTSB_CHECK(check_refs(scene, bsdf, -1, "mtsb_scene_add_serialized"));
+	if (flags & ~(MTSB_PLY_FACE_NORMALS | MTSB_PLY_FLIP_NORMALS)) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_serialized: unknown flags %#x", flags);
+	uint32_t nv = 0, nt = 0; bool hasUV = false, hasNormals = false; PlyMesh *M = nullptr;
+	MTSB_CHECK(ser_stage(scene, file, bytes, shape_index, to_world, to_world_inv, flags, &nv, &nt, &hasUV, &hasNormals, &M));
+	return add_decoded_mesh(scene, M, nv, nt, hasUV, flags, bsdf, vertex_count, triangle_count, "mtsb_scene_add_serialized");
+}
+
+int mtsb_serialized_probe(const void *file, size_t bytes, int shape_index, uint32_t *vertex_count, uint32_t *triangle_count) {
+	if (!file) MTSB_FAIL(MTSB_EINVAL, "mtsb_serialized_probe: NULL argument");
+	return ser_probe(file, bytes, shape_index, vertex_count, triangle_count);
 }
 
 int mtsb_ply_probe(const void *file, size_t bytes, uint32_t *vertex_count, uint32_t *triangle_count) {

@@ -79,6 +79,9 @@ int ply_stage(mtsb_scene *scene, const void *file, size_t bytes, const float *to
 	uint32_t *vertexCountOut, uint32_t *triangleCountOut, bool *hasUVOut, bool *hasNormalsOut, PlyMesh **out);
 void ply_release(PlyMesh *M);
 int ply_probe(const void *file, size_t bytes, uint32_t *nv, uint32_t *nt);
+int ser_probe(const void *file, size_t bytes, int index, uint32_t *nv, uint32_t *nt);
+int ser_stage(mtsb_scene *scene, const void *file, size_t bytes, int index, const float *toWorld, const float *toWorldInv, uint32_t flags,
+	uint32_t *vertexCountOut, uint32_t *triangleCountOut, bool *hasUVOut, bool *hasNormalsOut, PlyMesh **out);
 void ply_place(PlyMesh *M, int shape, uint32_t vtxBase, uint32_t triBase);
 int ply_decode(mtsb_scene *scene, PlyMesh *M, float *positions, float *normals, float *texcoords, uint32_t *indices, uint32_t *scratch);
 }

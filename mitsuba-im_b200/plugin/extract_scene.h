@@ -100,11 +100,14 @@ static void uploadEnvmap(mtsb_scene *out, int id, const Emitter *e) {
 }
 
 /// Uploads shapes / BSDFs / emitters in Scene order and commits (BVH build on the device).
-/// A mesh that came out of the `ply` plugin is decoded again, on the device, from its file (mtsb_scene_add_ply) instead of
-/// being copied out of the TriMesh's host arrays — when the file is one the device decoder takes and its header agrees with
-/// the mesh the reference's loader produced.  Returns the shape index or -1 (caller falls back to mtsb_scene_add_mesh).
-static int addPlyFromFile(mtsb_scene *out, const TriMesh *mesh, int bid) {
-	if (mesh->getClass()->getName() != "PLYLoader") return -1;
+/// A mesh that came out of the `ply` or `serialized` plugin is decoded again, on the device, from its file (mtsb_scene_add_ply /
+/// mtsb_scene_add_serialized) instead of being copied out of the TriMesh's host arrays — when the file is one the device
+/// decoder takes and its header agrees with the mesh the reference's loader produced.  Returns the shape index or -1 (caller
+/// falls back to mtsb_scene_add_mesh).
+static int addMeshFromFile(mtsb_scene *out, const TriMesh *mesh, int bid) {
+	const std::string cls = mesh->getClass()->getName();
+	const bool ply = cls == "PLYLoader", ser = cls == "SerializedMesh";
+	if (!ply && !ser) return -1;
 	const Properties &props = mesh->getProperties();
 	if (props.hasProperty("maxSmoothAngle") || !props.hasProperty("filename")) return -1;     // rebuildTopology changes the arrays
 	if (const char *e = getenv("MTSB_PLY_ON_DEVICE")) if (atoi(e) == 0) return -1;
@@ -113,14 +116,18 @@ static int addPlyFromFile(mtsb_scene *out, const TriMesh *mesh, int bid) {
 		const fs::path path = fs::decode_pathstr(resolved);
 		if (!fs::exists(path)) return -1;
 		ref<MemoryMappedFile> file = new MemoryMappedFile(resolved, true);
+		const int shapeIndex = ser ? props.getInteger("shapeIndex", 0) : 0;
 		uint32_t nv = 0, nt = 0;
-		if (mtsb_ply_probe(file->getData(), file->getSize(), &nv, &nt) != 0) return -1;
+		const int probe = ply ? mtsb_ply_probe(file->getData(), file->getSize(), &nv, &nt)
+		                      : mtsb_serialized_probe(file->getData(), file->getSize(), shapeIndex, &nv, &nt);
+		if (probe != 0) return -1;
 		if (nv != mesh->getVertexCount() || nt != mesh->getTriangleCount()) return -1;
 		const Transform toWorld = props.getTransform("toWorld", Transform());
 		float m[16], inv[16];
 		matrixToArray(toWorld.getMatrix(), m); matrixToArray(toWorld.getInverseMatrix(), inv);
 		const uint32_t flags = (props.getBoolean("faceNormals", false) ? MTSB_PLY_FACE_NORMALS : 0u) | (props.getBoolean("flipNormals", false) ? MTSB_PLY_FLIP_NORMALS : 0u);
-		const int rc = mtsb_scene_add_ply(out, file->getData(), file->getSize(), m, inv, flags, bid, NULL, NULL);
+		const int rc = ply ? mtsb_scene_add_ply(out, file->getData(), file->getSize(), m, inv, flags, bid, NULL, NULL)
+		                   : mtsb_scene_add_serialized(out, file->getData(), file->getSize(), shapeIndex, m, inv, flags, bid, NULL, NULL);
 		if (rc >= 0) SLog(EInfo, "gpupath: \"%s\" decoded on the device (%u triangles)", path.filename().string().c_str(), nt);
 		return rc;
 	} catch (const std::exception &) {
@@ -208,7 +215,7 @@ static mtsb_scene *uploadScene(mtsb_ctx *ctx, const Scene *scene, int builder) {
 		int rc;
 		if (shape->getClass()->derivesFrom(MTS_CLASS(TriMesh))) {
 			const TriMesh *mesh = static_cast<const TriMesh *>(shape);
-			rc = eid < 0 ? addPlyFromFile(out, mesh, bid) : -1;
+			rc = eid < 0 ? addMeshFromFile(out, mesh, bid) : -1;
 			// Point / Normal are 3 packed floats, Point2 2 floats, Triangle 3 uint32 (include/mitsuba/core/triangle.h)
 			if (rc < 0)
 				rc = mtsb_scene_add_mesh(out, (const float *) mesh->getVertexPositions(), (const float *) mesh->getVertexNormals(),

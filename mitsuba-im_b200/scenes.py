@@ -105,6 +105,30 @@ def ply_image(V, N, F, UV=None):
     return hdr.encode("ascii") + np.ascontiguousarray(vd, "<f4").tobytes() + fd.tobytes()
 
 
+def serialized_image(meshes, version=4, double=False, level=6):
+    """A `serialized` file image (TriMesh::serialize layout, src/librender/trimesh.cpp): meshes = list of dicts with V, F and
+    optionally N, UV, C (colours), name; one deflate stream per mesh behind a 4-byte header, offset dictionary at the end."""
+    import struct
+    import zlib
+    ft = "<f8" if double else "<f4"
+    blobs, offsets, pos = [], [], 0
+    for m in meshes:
+        V, F = np.asarray(m["V"]), np.asarray(m["F"])
+        flags = (0x2000 if double else 0x1000) | (1 if m.get("N") is not None else 0) | (2 if m.get("UV") is not None else 0) | (8 if m.get("C") is not None else 0)
+        payload = struct.pack("<I", flags)
+        if version == 4:
+            payload += m.get("name", "mesh").encode("utf-8") + b"\0"
+        payload += struct.pack("<QQ", V.shape[0], F.shape[0]) + np.ascontiguousarray(V, ft).tobytes()
+        for k in ("N", "UV", "C"):
+            if m.get(k) is not None:
+                payload += np.ascontiguousarray(m[k], ft).tobytes()
+        payload += np.ascontiguousarray(F, "<u4").tobytes()
+        blob = struct.pack("<HH", 0x041C, version) + zlib.compress(payload, level)
+        offsets.append(pos); pos += len(blob); blobs.append(blob)
+    tail = b"".join(struct.pack("<Q" if version == 4 else "<I", o) for o in offsets) + struct.pack("<I", len(offsets))
+    return b"".join(blobs) + tail
+
+
 def write_ply(path, V, N, F, UV=None):
     with open(path, "wb") as f:
         f.write(ply_image(V, N, F, UV))
@@ -532,8 +556,10 @@ class SceneDesc:
             inner = '<bsdf type="twosided">%s</bsdf>' % inner
         return inner
 
-    def to_xml(self, directory, name="scene", film_format="pfm"):
-        """Writes <directory>/<name>.xml (+ one PLY per mesh) and returns the XML path."""
+    def to_xml(self, directory, name="scene", film_format="pfm", mesh_format="ply"):
+        """Writes <directory>/<name>.xml (+ one PLY per mesh, or with mesh_format="serialized" ONE `serialized` file holding every mesh,
+        addressed by shapeIndex) and returns the XML path."""
+        ser_meshes = []
         os.makedirs(directory, exist_ok=True)
         out = ['<?xml version="1.0" encoding="utf-8"?>', '<scene version="0.5.0">']
         ig = self.integrator
@@ -592,7 +618,12 @@ class SceneDesc:
             for side in ("interior", "exterior"):
                 if s.get(side) is not None:
                     bs += '<ref name="%s" id="medium%d"/>' % (side, s[side])
-            if s["type"] == "mesh":
+            if s["type"] == "mesh" and mesh_format == "serialized":
+                face = "" if s["N"] is not None else '<boolean name="faceNormals" value="true"/>'
+                out.append('<shape type="serialized"><string name="filename" value="%s.serialized"/><integer name="shapeIndex" value="%d"/>%s%s%s</shape>' % (
+                    name, len(ser_meshes), face, bs, em))
+                ser_meshes.append(dict(V=s["V"], F=s["F"], N=s["N"], UV=s.get("UV"), name="mesh%d" % i))
+            elif s["type"] == "mesh":
                 fn = "%s_mesh%d.ply" % (name, i)
                 write_ply(os.path.join(directory, fn), s["V"], s["N"], s["F"], s.get("UV"))
                 face = "" if s["N"] is not None else '<boolean name="faceNormals" value="true"/>'
@@ -608,6 +639,9 @@ class SceneDesc:
                 flip = '<boolean name="flipNormals" value="true"/>' if s["flip_normals"] else ""
                 out.append('<shape type="rectangle"><transform name="toWorld">%s</transform>%s%s%s</shape>' % (_mat_xml(s["to_world"]), flip, bs, em))
         out.append('</scene>')
+        if ser_meshes:
+            with open(os.path.join(directory, name + ".serialized"), "wb") as f:
+                f.write(serialized_image(ser_meshes))
         path = os.path.join(directory, name + ".xml")
         with open(path, "w") as f:
             f.write("\n".join(out))

@@ -358,7 +358,8 @@ public:
 		double total = 0; size_t tris = 0;
 		for (int i = 2; i < argc; ++i) {
 			auto t0 = std::chrono::steady_clock::now();
-			Properties props("ply");
+			std::string fn(argv[i]);
+			Properties props(fn.size() > 11 && fn.substr(fn.size() - 11) == ".serialized" ? "serialized" : "ply");
 			props.setString("filename", argv[i]);
 			ref<TriMesh> mesh = static_cast<TriMesh *>(PluginManager::getInstance()->createObject(MTS_CLASS(TriMesh), props));
 			mesh->configure();

@@ -1,5 +1,5 @@
-"""Golden meshes for the device PLY decoder: every file image of tests/ply_cases.py loaded by the UNMODIFIED reference
-(`ply` plugin + TriMesh::configure through oracle/raydump.cpp `mesh`) -> tests/golden/ply_meshes.npz.
+"""Golden meshes for the device mesh-file decoders: every file image of tests/ply_cases.py loaded by the UNMODIFIED reference
+(`ply` / `serialized` plugins + TriMesh::configure through oracle/raydump.cpp `mesh`) -> tests/golden/ply_meshes.npz.
 
 Run here:  python tests/golden/make_golden_ply.py
 """
@@ -18,12 +18,12 @@ import oracle as O  # noqa: E402
 import ply_cases  # noqa: E402
 
 
-def reference_mesh(image, extra, td, name):
-    with open(os.path.join(td, name + ".ply"), "wb") as f:
+def reference_mesh(image, extra, td, name, kind="ply"):
+    with open(os.path.join(td, name + "." + kind), "wb") as f:
         f.write(image)
     xml = os.path.join(td, name + ".xml")
     with open(xml, "w") as f:
-        f.write(ply_cases.scene_xml(name + ".ply", extra))
+        f.write(ply_cases.scene_xml(name + "." + kind, extra, kind))
     out = os.path.join(td, name + ".bin")
     r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "mesh", xml, out], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0 or not os.path.exists(out):
@@ -36,8 +36,11 @@ def reference_mesh(image, extra, td, name):
 def main():
     data = {}
     with tempfile.TemporaryDirectory() as td:
-        for name, c in ply_cases.cases().items():
-            P, N, UV, T = reference_mesh(c["image"], c["xml"], td, name)
+        import __graft_entry__ as g
+        scenes = g.load_package().scenes
+        todo = [(n, c, "ply") for n, c in ply_cases.cases().items()] + [(n, c, "serialized") for n, c in ply_cases.ser_cases(scenes).items()]
+        for name, c, kind in todo:
+            P, N, UV, T = reference_mesh(c["image"], c["xml"], td, name, kind)
             data[name + "_P"], data[name + "_T"] = P, T
             if N is not None:
                 data[name + "_N"] = N

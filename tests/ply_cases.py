@@ -96,9 +96,35 @@ def cases():
     return out
 
 
-def scene_xml(filename, extra):
-    return ('<?xml version="1.0" encoding="utf-8"?>\n<scene version="0.5.0">\n<shape type="ply"><string name="filename" value="%s"/>%s'
-            '<bsdf type="diffuse"/></shape>\n<emitter type="point"><point name="position" x="0" y="0" z="5"/></emitter>\n</scene>\n' % (filename, extra))
+def ser_cases(scenes):
+    """`serialized` file images: name -> dict(image, xml, kwargs of Scene.add_serialized)"""
+    out = {}
+    V, N, UV, Q = _grid(12, 7)
+    F = tris_of(Q)
+    V2, N2, UV2, Q2 = _grid(9, 8)
+    F2 = tris_of(Q2)
+    rgb = np.random.default_rng(4).random((len(V), 3)).astype(np.float32)
+    meshes = [dict(V=V, F=F, N=N, UV=UV, name="first"), dict(V=V2 * 0.5, F=F2, name="second, no normals"), dict(V=V, F=F, N=N, C=rgb, name="third")]
+    # 1. version 4, single precision, stored normals and uv, no transform: every array bit-exact (normals are NOT re-normalised)
+    out["ser_v4_n_uv"] = dict(image=scenes.serialized_image(meshes, 4), xml="", kwargs={})
+    # 2. version 4, double precision, second mesh of the file, no normals (computed), through toWorld
+    out["ser_v4_double_computed_xform"] = dict(image=scenes.serialized_image(meshes, 4, double=True), xml='<integer name="shapeIndex" value="1"/>' + TO_WORLD,
+                                               kwargs=dict(shape_index=1, to_world=to_world_matrix()))
+    # 3. version 3, third mesh (colours skipped), mirrored: the winding is swapped, normals go through the inverse transpose
+    mirror = np.diag([-1.0, 1.0, 1.0, 1.0])
+    out["ser_v3_mirror_xform"] = dict(image=scenes.serialized_image(meshes, 3), xml='<integer name="shapeIndex" value="2"/><transform name="toWorld"><scale x="-1"/></transform>',
+                                      kwargs=dict(shape_index=2, to_world=mirror))
+    # 4. faceNormals + flipNormals on the first mesh
+    out["ser_v4_facenormals_flip"] = dict(image=out["ser_v4_n_uv"]["image"], xml='<boolean name="faceNormals" value="true"/><boolean name="flipNormals" value="true"/>',
+                                          kwargs=dict(face_normals=True, flip_normals=True))
+    # 5. flipNormals on stored normals, double precision file
+    out["ser_v4_double_flip"] = dict(image=out["ser_v4_double_computed_xform"]["image"], xml='<boolean name="flipNormals" value="true"/>', kwargs=dict(flip_normals=True))
+    return out
+
+
+def scene_xml(filename, extra, kind="ply"):
+    return ('<?xml version="1.0" encoding="utf-8"?>\n<scene version="0.5.0">\n<shape type="%s"><string name="filename" value="%s"/>%s'
+            '<bsdf type="diffuse"/></shape>\n<emitter type="point"><point name="position" x="0" y="0" z="5"/></emitter>\n</scene>\n' % (kind, filename, extra))
 
 
 def read_mesh_dump(path):

@@ -195,12 +195,13 @@ def test_envmap_through_the_loader(pkg, tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
-def test_ply_meshes_are_decoded_on_the_device(pkg, tmp_path):
-    """SURVEY 8 f3 through the loader: a mesh that came out of the `ply` plugin is decoded again from its file by
-    mtsb_scene_add_ply (plugin/extract_scene.h addPlyFromFile) — same image as with the host arrays (MTSB_PLY_ON_DEVICE=0)
-    and as the stock `path`."""
+@pytest.mark.parametrize("mesh_format", ["ply", "serialized"])
+def test_mesh_files_are_decoded_on_the_device(pkg, tmp_path, mesh_format):
+    """SURVEY 8 f3 through the loader: a mesh that came out of the `ply` / `serialized` plugin is decoded again from its file by
+    mtsb_scene_add_ply / _add_serialized (plugin/extract_scene.h addMeshFromFile) — same image as with the host arrays
+    (MTSB_PLY_ON_DEVICE=0) and as the stock `path`.  The serialized variant keeps every mesh in one file (shapeIndex)."""
     sd = pkg.scenes.materials_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=5)
-    xml = sd.to_xml(str(tmp_path), "mats")
+    xml = sd.to_xml(str(tmp_path), "mats", mesh_format=mesh_format)
     ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
     gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)
     host, log_host = run_mitsuba(str(tmp_path / "host.pfm"), True, True, {}, xml=xml, env={"MTSB_PLY_ON_DEVICE": "0"})

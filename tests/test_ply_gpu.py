@@ -1,5 +1,5 @@
-"""GPU parity tests of the device PLY decoder (mtsb_scene_add_ply, csrc/ply.cu) against what the unmodified reference's
-`ply` plugin + TriMesh::configure produce for the same file images: committed golden meshes (tests/golden/ply_meshes.npz,
+"""GPU parity tests of the device mesh-file decoders (mtsb_scene_add_ply / _add_serialized, csrc/ply.cu) against what the unmodified
+reference's `ply` / `serialized` plugins + TriMesh::configure produce for the same file images: committed golden meshes (tests/golden/ply_meshes.npz,
 made by tests/golden/make_golden_ply.py) and, where oracle/_ref is present, the live reference.
 
 Bar: triangle indices, texture coordinates and untransformed positions bit-exact; transformed positions and stored normals
@@ -18,13 +18,14 @@ import ply_cases
 pytestmark = pytest.mark.gpu
 
 
-def _decode(pkg, ctx, case, extra_first=None):
+def _decode(pkg, ctx, case, extra_first=None, kind="ply"):
     B = pkg.binding
     sc = B.Scene(ctx)
     bs = sc.add_bsdf(B.BSDF_DIFFUSE, (0.5, 0.5, 0.5))
     if extra_first is not None:
         sc.add_mesh(extra_first[0], extra_first[1], bsdf=bs)
-    shape = sc.add_ply(case["image"], bsdf=bs, **case["kwargs"])
+    add = sc.add_ply if kind == "ply" else sc.add_serialized
+    shape = add(case["image"], bsdf=bs, **case["kwargs"])
     sc.commit(B.BUILDER_LBVH)
     return sc, shape
 
@@ -49,23 +50,35 @@ def _golden_ref(gold, name):
     return g("_P"), g("_N"), g("_UV"), g("_T")
 
 
-@pytest.mark.parametrize("name", sorted(ply_cases.cases().keys()))
+def _all_cases(pkg):
+    out = {n: (c, "ply") for n, c in ply_cases.cases().items()}
+    out.update({n: (c, "serialized") for n, c in ply_cases.ser_cases(pkg.scenes).items()})
+    return out
+
+
+CASE_NAMES = sorted(ply_cases.cases().keys()) + ["ser_v3_mirror_xform", "ser_v4_double_computed_xform", "ser_v4_double_flip", "ser_v4_facenormals_flip", "ser_v4_n_uv"]
+
+
+@pytest.mark.parametrize("name", CASE_NAMES)
 def test_device_ply_decode_matches_reference_loader(pkg, ctx, golden, name):
-    case = ply_cases.cases()[name]
+    case, kind = _all_cases(pkg)[name]
     gold = golden("ply_meshes.npz")
-    sc, shape = _decode(pkg, ctx, case)
+    sc, shape = _decode(pkg, ctx, case, kind=kind)
     got = sc.read_mesh(shape)
     ref = _golden_ref(gold, name)
     _check_against(got, ref, name, computed="computed" in name, xform="xform" in name)
+    if name in ("ser_v4_n_uv", "ser_v4_double_flip"):
+        # the `serialized` plugin leaves stored normals alone without a toWorld (serialized.cpp:184-195): bit-exact, flipped or not
+        assert (got[1].view(np.uint32) == ref[1].view(np.uint32)).all()
     if ref[1] is None:      # faceNormals: the shape record says "no vertex normals"
         surf = sc.ray_intersect_surface(np.array([[0, 0, 5, 0, 0, 0, -1, np.inf]], np.float32))
         assert np.isfinite(surf["t"][0]) and np.abs(surf["ns"][0] - surf["ng"][0]).max() < 1e-6
     if os.path.exists(os.path.join(O.REF_DIR, "mtsutil")):        # live reference (travels to the GPU box)
         with tempfile.TemporaryDirectory() as td:
-            with open(os.path.join(td, "m.ply"), "wb") as f:
+            with open(os.path.join(td, "m." + kind), "wb") as f:
                 f.write(case["image"])
             with open(os.path.join(td, "m.xml"), "w") as f:
-                f.write(ply_cases.scene_xml("m.ply", case["xml"]))
+                f.write(ply_cases.scene_xml("m." + kind, case["xml"], kind))
             r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "mesh", os.path.join(td, "m.xml"), os.path.join(td, "m.bin")],
                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
             assert r.returncode == 0, r.stdout[-2000:]
@@ -136,6 +149,21 @@ def test_ply_decoder_refuses_what_it_cannot_decode(pkg, ctx):
     bad = hdr + verts + bytes([3]) + np.array([0, 1, 2], "<i4").tobytes() + bytes([3]) + np.array([0, 2, 7], "<i4").tobytes()
     with pytest.raises(B.MtsbError, match="references a vertex"):
         attempt(bad)
+    # `serialized`: wrong magic, shape index out of range, a stream cut short
+    ser = ply_cases.ser_cases(pkg.scenes)["ser_v4_n_uv"]["image"]
+
+    def attempt_ser(image, index=0):
+        sc = B.Scene(ctx)
+        bs = sc.add_bsdf(B.BSDF_DIFFUSE, (0.5, 0.5, 0.5))
+        sc.add_serialized(image, shape_index=index, bsdf=bs)
+
+    assert B.serialized_probe(ser, 1) == (100, 162) and B.ply_probe(img) == (169, 288)
+    with pytest.raises(B.MtsbError, match="invalid file format"):
+        attempt_ser(b"\x00\x00" + ser[2:])
+    with pytest.raises(B.MtsbError, match="out of range"):
+        attempt_ser(ser, 3)
+    with pytest.raises(B.MtsbError, match="stream"):
+        attempt_ser(ser[:2000])
     neg = hdr + verts + bytes([3]) + np.array([0, 1, 2], "<i4").tobytes() + bytes([3]) + np.array([0, 2, -1], "<i4").tobytes()
     with pytest.raises(B.MtsbError, match="references a vertex"):
         attempt(neg)
