@@ -367,6 +367,9 @@ MTSB_API void  mtsb_host_free(void *p);
 MTSB_API int  mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *bsdf_in, size_t n, float *bsdf_out);
 /* Same, with the extra draw that EUsesSampler plugins take from bRec.sampler inside sample() (roughdielectric's
  * lobe selection, src/bsdfs/roughdielectric.cpp:562): s3 = n floats, NULL = 0.5 for every row. */
+/* Test support: the draws the render's sampler (independent or ldsampler) hands to samples first .. first+n-1 of pixel (px, py):
+ * per sample `draws` next2D calls, then `draws` next1D calls; out[n][draws][3] = (2D.x, 2D.y, 1D). */
+MTSB_API int  mtsb_render_sampler_dump(mtsb_render *r, uint32_t px, uint32_t py, uint32_t first, uint32_t n, uint32_t draws, float *out);
 MTSB_API int  mtsb_eval_bsdf_s3(mtsb_scene *scene, int bsdf, const float *bsdf_in, const float *s3, size_t n, float *bsdf_out);
 MTSB_API int  mtsb_eval_emitter(mtsb_scene *scene, const float *em_in, size_t n, float *em_out);
 
@@ -390,6 +393,13 @@ MTSB_API int  mtsb_render_clear(mtsb_render *r);
  * that request sample arrays (`direct` with emitterSamples / bsdfSamples other than 1) are refused with this sampler. */
 #define MTSB_SOBOL_TABLE_WORDS (1024 * 52 + 2 * 16 * 52 * 2)
 MTSB_API int  mtsb_render_set_sobol(mtsb_render *r, const uint32_t *tables, size_t words);
+/* Switches the render to the `ldsampler` (src/samplers/ldsampler.cpp:78-239): for the first `dimension` 1D and 2D draws of a
+ * sample the pixel's sample_count (rounded up to a power of two) points are a randomly scrambled van der Corput sequence / (0,2)
+ * sequence (radicalInverse2Single, sample02Single, include/mitsuba/core/qmc.h) in shuffled order; later draws are independent.
+ * The reference scrambles and shuffles from a sequential Random per pixel in scheduler order and documents that two of its own
+ * runs differ; here both are keyed by a counter-based generator on (pixel, dimension, seed): the same point-set construction,
+ * another realisation — parity is statistical.  sample_count = the render's total samples per pixel. */
+MTSB_API int  mtsb_render_set_ldsampler(mtsb_render *r, int dimension, size_t sample_count);
 /* Sensor::getMedium(): the medium the camera sits in (-1 = none, the default); volpath_simple starts its paths there. */
 MTSB_API int  mtsb_render_set_camera_medium(mtsb_render *r, int medium);
 /* Gives the render a CUDA stream of its own (default: the context stream).  Renders are independent — own path state,

@@ -130,7 +130,7 @@ def lib():
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
         "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
-        "mtsb_render_set_camera_medium": (i32, [vp, i32]), "mtsb_render_set_sobol": (i32, [vp, vp, sz]),
+        "mtsb_render_set_camera_medium": (i32, [vp, i32]), "mtsb_render_set_ldsampler": (i32, [vp, i32, sz]), "mtsb_render_sampler_dump": (i32, [vp, u32, u32, u32, u32, u32, vp]), "mtsb_render_set_sobol": (i32, [vp, vp, sz]),
         "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
         "mtsb_scene_shape_offsets": (i32, [vp, vp]), "mtsb_scene_build_stats": (i32, [vp, vp]),
@@ -534,6 +534,16 @@ class Render:
         """Switches to the `sobol` sampler; tables = the reference's direction numbers as uint32 words (mtsb_render_set_sobol)."""
         t = np.ascontiguousarray(tables, dtype=np.uint32)
         _check(lib().mtsb_render_set_sobol(self.h, _ptr(t), t.shape[0]))
+
+    def set_ldsampler(self, dimension, sample_count):
+        """Switches to the `ldsampler` ((0,2)-sequence point sets per pixel, mtsb_render_set_ldsampler)."""
+        _check(lib().mtsb_render_set_ldsampler(self.h, int(dimension), int(sample_count)))
+
+    def sampler_dump(self, px, py, first, n, draws):
+        """[n, draws, 3] = (next2D.x, next2D.y, next1D) the sampler hands to samples first..first+n-1 of a pixel (test support)."""
+        out = np.zeros((n, draws, 3), np.float32)
+        _check(lib().mtsb_render_sampler_dump(self.h, px, py, first, n, draws, _ptr(out)))
+        return out
 
     def set_camera_medium(self, medium):
         _check(lib().mtsb_render_set_camera_medium(self.h, int(medium)))

@@ -97,7 +97,7 @@ generate_kernel(GenParams g, CameraDev cam, PathState ps, uint32_t *queue) {
 	SamplerState rs; rs.px = px; rs.py = py; rs.sample = sidx; rs.dim = 0; rs.seed = g.seed; rs.sobol = g.sobol;
 	float u1, u2;
 	uint32_t rngY = py, rngZ = sidx;
-	if (g.sobol) {
+	if (g.sobol && !ld_tag(g.sobol)) {
 		// SobolSampler::generate / setSampleIndex (sobol.cpp:172-215): the sidx-th point of the sequence that falls into this pixel
 		// (sobol::look_up, sobolseq.h:97-131), whose first two dimensions give the position inside the pixel (:240-243)
 		const uint32_t m = g.sobolLogRes;

@@ -338,6 +338,21 @@ int mtsb_render_set_sobol(mtsb_render *r, const uint32_t *tables, size_t words) 
 	return 0;
 }
 
+static inline uint32_t ld_tag_host(const uint32_t *p) { const uintptr_t v = (uintptr_t) p; return v < 0x10000u ? (uint32_t) v : 0u; }
+
+int mtsb_render_set_ldsampler(mtsb_render *r, int dimension, size_t sample_count) {
+	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_ldsampler: NULL argument");
+	if (dimension < 1 || dimension > 15) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_set_ldsampler: dimension %d (1..15: the counters ride in the path state)", dimension);
+	if (sample_count == 0 || sample_count > ((size_t) 1 << 24)) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_ldsampler: sample count %zu", sample_count);
+	if (fan_mode(r)) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_set_ldsampler: sample arrays (direct with emitterSamples / bsdfSamples != 1) are not available with the ldsampler");
+	uint32_t lg = 0;
+	while (((size_t) 1 << lg) < sample_count) ++lg;          // math::roundToPowerOfTwo (ldsampler.cpp:83-87)
+	r->dSobol.release();
+	r->integ.sobol = (const uint32_t *) (uintptr_t) ((uint32_t) dimension | (lg << 8));      // shading.cuh ld_tag
+	destroy_bounce_graph(r);
+	return 0;
+}
+
 int mtsb_render_set_camera_medium(mtsb_render *r, int medium) {
 	if (!r) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: NULL argument");
 	if (medium < -1 || medium >= (int) r->scene->media.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_set_camera_medium: medium %d unknown", medium);
@@ -538,6 +553,20 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	MTSB_CHECK(run_chunk(r, g, dO.ptr, pos_out ? dP.ptr : nullptr));
 	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, n * 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	if (pos_out) MTSB_CUDA(cudaMemcpyAsync(pos_out, dP.ptr, n * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	return 0;
+}
+
+int mtsb_render_sampler_dump(mtsb_render *r, uint32_t px, uint32_t py, uint32_t first, uint32_t n, uint32_t draws, float *out) {
+	if (!r || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_sampler_dump: NULL argument");
+	if (n == 0 || draws == 0) return 0;
+	if (ld_tag_host(r->integ.sobol) == 0 && r->integ.sobol) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_render_sampler_dump: the sobol sampler's sequence index is per path (use mtsb_render_samples_ex)");
+	MTSB_CUDA(cudaSetDevice(r->scene->ctx->device));
+	cudaStream_t st = r->stream;
+	DevBuf<float> dO; MTSB_CHECK(dO.alloc((size_t) n * draws * 3));
+	sampler_dump_kernel<<<blocks_for(n, 128), 128, 0, st>>>(r->integ, r->seed, px, py, first, n, draws, dO.ptr);
+	MTSB_CUDA(cudaGetLastError());
+	MTSB_CUDA(cudaMemcpyAsync(out, dO.ptr, (size_t) n * draws * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	return 0;
 }

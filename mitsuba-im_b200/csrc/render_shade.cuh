@@ -305,6 +305,17 @@ __global__ void preview_stack_kernel(StackIn in, size_t pixels, float4 *out) {
 }
 
 // ---- pointwise plugin math for parity tests (mtsb_eval_bsdf / mtsb_eval_emitter) ----
+// The sampler's draws for `n` consecutive samples of one pixel: `draws` next2D calls, then `draws` next1D calls per sample,
+// written as [n][draws][3] (pointwise checks of the samplers: stratification of the ldsampler's point sets, Sobol' dimensions)
+__global__ void sampler_dump_kernel(IntegratorDev integ, uint32_t seed, uint32_t px, uint32_t py, uint32_t first, uint32_t n, uint32_t draws, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	SamplerState rs; rs.px = px; rs.py = py; rs.sample = first + i; rs.dim = 0; rs.seed = seed; rs.sobol = integ.sobol;
+	float *o = out + (size_t) i * draws * 3;
+	for (uint32_t k = 0; k < draws; ++k) next2D(rs, o[k * 3], o[k * 3 + 1]);
+	for (uint32_t k = 0; k < draws; ++k) o[k * 3 + 2] = next1D(rs);
+}
+
 __global__ void eval_bsdf_kernel(SceneDev S, int bsdfId, const float *in, const float *s3, size_t n, float *out) {
 	const size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
 	if (i >= n) return;

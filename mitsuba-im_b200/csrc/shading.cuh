@@ -49,8 +49,64 @@ __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 	out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+// ---- `ldsampler` (src/samplers/ldsampler.cpp): per pixel and per dimension a scrambled (0,2)-sequence / van der Corput point set
+// of sampleCount points in shuffled order, for the first `dimension` 1D and 2D draws of a sample; later draws are independent.
+// The reference scrambles and shuffles with its sequential Random, per pixel in scheduler order (its own documentation: two runs
+// differ), so the realisation cannot be shared; the point sets are the same construction (radicalInverse2Single / sample02Single,
+// include/mitsuba/core/qmc.h:43-59,82-87,164-168) keyed by Philox on (pixel, dimension).  A `sobol` field holding a small
+// integer instead of an address selects it: dimension | log2(sampleCount) << 8 (mtsb_render_set_ldsampler).  The 16-bit `dim`
+// of the path state is split into the 1D counter (4 bits), the 2D counter (4 bits) and the count of independent draws (8 bits).
+__device__ __forceinline__ uint32_t ld_tag(const uint32_t *p) { const unsigned long long v = (unsigned long long) p; return v < 0x10000ull ? (uint32_t) v : 0u; }
+// Kensler's hashed permutation ("Correlated Multi-Jittered Sampling", 2013) of [0, mask] for a power-of-two length: every step is a
+// bijection on the low bits, so no cycle walking is needed
+__device__ __forceinline__ uint32_t ld_permute(uint32_t i, uint32_t w, uint32_t p) {
+	i ^= p; i *= 0xe170893du; i ^= p >> 16; i ^= (i & w) >> 4; i ^= p >> 8; i *= 0x0929eb3fu; i ^= p >> 23; i ^= (i & w) >> 1;
+	i *= 1u | p >> 27; i *= 0x6935fa69u; i ^= (i & w) >> 11; i *= 0x74dcb303u; i ^= (i & w) >> 2; i *= 0x9e501cc3u; i ^= (i & w) >> 2;
+	i *= 0xc860a3dfu; i &= w; i ^= i >> 5;
+	return (i + p) & w;
+}
+__device__ __forceinline__ float ld_radical_inverse2(uint32_t n, uint32_t scramble) {      // qmc.h:43-59
+	n = (__brev(n) >> 8) ^ (scramble & 0x00ffffffu);
+	return (float) n / 16777216.0f;
+}
+__device__ __forceinline__ float ld_sobol2(uint32_t n, uint32_t scramble) {                // qmc.h:82-87
+	for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+		if (n & 1) scramble ^= v;
+	return fminf((float) scramble / 4294967296.0f, 0.999999940395355225f);                  // the division rounds to 1.0f for the top 128 values
+}
+__device__ inline float ld_independent(SamplerState &s) {
+	const uint32_t c = (s.dim >> 8) & 0xffu;
+	s.dim = (s.dim & 0xffu) | (((c + 1u) & 0xffu) << 8);
+	uint32_t w[4];
+	philox4x32_10(s.px, s.py, s.sample, 0x80000000u | (c >> 2), s.seed, 0x6d747362u, w);
+	const uint32_t word = (c & 3) == 0 ? w[0] : ((c & 3) == 1 ? w[1] : ((c & 3) == 2 ? w[2] : w[3]));
+	return __uint_as_float((word >> 9) | 0x3f800000u) - 1.0f;
+}
+__device__ inline float ld_next1D(SamplerState &s, uint32_t tag) {                           // ldsampler.cpp:225-231
+	const uint32_t d = s.dim & 0xfu;
+	if (d >= (tag & 0xffu)) return ld_independent(s);
+	s.dim += 1u;
+	uint32_t w[4];
+	philox4x32_10(s.px, s.py, d, 0x6c643144u, s.seed, 0x6d747362u, w);
+	const uint32_t mask = (1u << (tag >> 8)) - 1u;
+	return ld_radical_inverse2(ld_permute(s.sample & mask, mask, w[2]), w[0]);
+}
+__device__ inline void ld_next2D(SamplerState &s, uint32_t tag, float &a, float &b) {        // ldsampler.cpp:233-239
+	const uint32_t d = (s.dim >> 4) & 0xfu;
+	if (d >= (tag & 0xffu)) { a = ld_independent(s); b = ld_independent(s); return; }
+	s.dim += 16u;
+	uint32_t w[4];
+	philox4x32_10(s.px, s.py, 16u + d, 0x6c643244u, s.seed, 0x6d747362u, w);
+	const uint32_t mask = (1u << (tag >> 8)) - 1u, i = ld_permute(s.sample & mask, mask, w[2]);
+	a = ld_radical_inverse2(i, w[0]); b = ld_sobol2(i, w[1]);                                // sample02Single
+}
+
 __device__ inline float next1D(SamplerState &s) {
-	if (s.sobol) return sobol_sample(s.sobol, ((unsigned long long) s.py << 32) | s.sample, s.dim++);      // SobolSampler::next1D (sobol.cpp:218-228)
+	if (s.sobol) {
+		const uint32_t tag = ld_tag(s.sobol);
+		if (tag) return ld_next1D(s, tag);
+		return sobol_sample(s.sobol, ((unsigned long long) s.py << 32) | s.sample, s.dim++);      // SobolSampler::next1D (sobol.cpp:218-228)
+	}
 	uint32_t w[4];
 	philox4x32_10(s.px, s.py, s.sample, s.dim >> 2, s.seed, 0x6d747362u, w);
 	const uint32_t word = (s.dim & 3) == 0 ? w[0] : ((s.dim & 3) == 1 ? w[1] : ((s.dim & 3) == 2 ? w[2] : w[3]));
@@ -59,6 +115,8 @@ __device__ inline float next1D(SamplerState &s) {
 }
 __device__ inline void next2D(SamplerState &s, float &a, float &b) {
 	if (s.sobol) {
+		const uint32_t tag = ld_tag(s.sobol);
+		if (tag) { ld_next2D(s, tag, a, b); return; }
 		// SobolSampler::next2D (:230-251).  Dimensions [m_arrayStartDim, m_arrayEndDim) = [5, 5 + requests) are reserved for sample
 		// arrays, and the test `m_dimension + 1 >= m_arrayStartDim && m_dimension < m_arrayEndDim` moves a pair that would start at
 		// dimension 4 to 5 even when nothing is reserved.  (The pixel-relative first pair is generate_kernel's business.)

@@ -494,6 +494,8 @@ class SceneDesc:
             if SOBOL_TABLES is None:
                 raise ValueError("sobol sampler: set scenes.SOBOL_TABLES (the reference's direction numbers, binding.Render.set_sobol)")
             rd.set_sobol(SOBOL_TABLES)
+        elif self.sampler["kind"] == "ldsampler":
+            rd.set_ldsampler(self.sampler.get("dimension", 4), self.sampler["spp"])
         return rd
 
     # -- reference back end ----------------------------------------------------------------------
@@ -586,6 +588,8 @@ class SceneDesc:
             out.append('<transform name="toWorld">%s</transform>' % _mat_xml(s["to_world"]))
             if sm["kind"] == "sobol":
                 out.append('<sampler type="sobol"><integer name="sampleCount" value="%d"/></sampler>' % sm["spp"])
+            elif sm["kind"] == "ldsampler":
+                out.append('<sampler type="ldsampler"><integer name="sampleCount" value="%d"/><integer name="dimension" value="%d"/></sampler>' % (sm["spp"], sm.get("dimension", 4)))
             elif sm["kind"] == "ctr":
                 out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/></sampler>' % (sm["spp"], sm["seed"]))
             else:

@@ -37,6 +37,7 @@
 #include <mitsuba/render/mipmap.h>
 #include "sobolseq.h"            /* src/samplers/sobolseq.h: the Sobol direction numbers (raydump sobol) */
 #include <thread>
+#include <mitsuba/core/qmc.h>
 #include <vector>
 #include <chrono>
 #include <cstdio>
@@ -370,6 +371,20 @@ public:
 		return 0;
 	}
 
+	/// radicalInverse2Single / sobol2Single (include/mitsuba/core/qmc.h) on (n, scramble0, scramble1) triples of uint32 words
+	int qmc(int argc, char **argv) {
+		if (argc < 4) { cout << "qmc <in> <out>" << endl; return 1; }
+		std::vector<float> in = readFloats(argv[2]);
+		std::vector<float> out;
+		for (size_t i = 0; i + 2 < in.size(); i += 3) {
+			uint32_t w[3]; memcpy(w, &in[i], 12);
+			out.push_back(radicalInverse2Single(w[0], w[1]));
+			out.push_back(sobol2Single(w[0], w[2]));
+		}
+		writeFloats(argv[3], out);
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -443,6 +458,7 @@ public:
 		if (!strcmp(argv[1], "mipmap3")) return mipmap3(argc, argv);
 		if (!strcmp(argv[1], "sobol")) return sobolTables(argc, argv);
 		if (!strcmp(argv[1], "mesh")) return mesh(argc, argv);
+		if (!strcmp(argv[1], "qmc")) return qmc(argc, argv);
 		if (!strcmp(argv[1], "plyload")) return plyload(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);

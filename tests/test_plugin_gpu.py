@@ -214,6 +214,27 @@ def test_mesh_files_are_decoded_on_the_device(pkg, tmp_path, mesh_format):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
+def test_ldsampler_through_the_loader(pkg, tmp_path, golden):
+    """`ldsampler` instantiated by the stock XML loader: plugin/extract.h hands its `dimension` and sample count to
+    mtsb_render_set_ldsampler.  No shared sample stream exists for this sampler (tests/test_ldsampler_gpu.py), so the image is held
+    to the reference's own ldsampler renders statistically: error against the converged image, and the image mean."""
+    g = golden("li_ldsampler_cornell.npz")
+    hi = g["ref_hi"]
+
+    def err(img):
+        e = np.sort(((img - hi) ** 2 / (hi ** 2 + 1e-3)).mean(axis=2).ravel())
+        return float(e[: int(e.size * 0.98)].mean())
+    sd = pkg.scenes.cornell_box(64, 64, spp=16, max_depth=5, sampler="ldsampler", rfilter="box")
+    xml = sd.to_xml(str(tmp_path), "cbox_ld")
+    for classic in (True, False):
+        gpu, log = run_mitsuba(str(tmp_path / ("gpu%d.pfm" % classic)), classic, True, {}, xml=xml)
+        assert "gpupath:" in log, "the overlay plugin did not run"
+        ref_ld = float(np.mean([err(i) for i in g["ref_ld"]])); ref_ind = float(np.mean([err(i) for i in g["ref_ind"]]))
+        assert 0.6 * ref_ld <= err(gpu[..., :3]) <= 1.25 * ref_ld, (err(gpu[..., :3]), ref_ld)
+        assert err(gpu[..., :3]) < 0.9 * ref_ind
+        assert abs(gpu[..., :3].mean() - hi.mean()) <= 0.015 * hi.mean()
+
+
 def test_volpath_simple_with_media_through_the_loader(pkg, tmp_path):
     """§8 f4 through the drop-in: overlay/plugins/volpath_simple.so replaces the stock SimpleVolumetricPathTracer for an
     unmodified scene file with homogeneous media (isotropic + HG), `null` and dielectric medium boundaries and a sensor

@@ -90,3 +90,16 @@ def test_rough_transmittance_slices_of_roughplastic(pkg):
         tid, params = S.SceneDesc._bsdf_params(m)
         assert (tid & 0xff) == B.BSDF_ROUGHPLASTIC and len(params) == 13 and np.isfinite(params).all()
         assert m["_table"].shape == (100,) and 'type="roughplastic"' in S.SceneDesc._bsdf_xml(m)
+
+
+def test_ld_restatement_matches_the_reference_qmc_functions(golden):
+    """tests/ld_restate.py radical_inverse2 / sobol2 against radicalInverse2Single / sobol2Single of the reference
+    (tests/golden/qmc.npz, oracle/raydump.cpp `qmc`), bit for bit; and the hashed permutation is one."""
+    import ld_restate as L
+    g = golden("qmc.npz")
+    assert (L.radical_inverse2(g["n"], g["s0"]).view(np.uint32) == g["radical_inverse"].view(np.uint32)).all()
+    assert (L.sobol2(g["n"], g["s1"]).view(np.uint32) == g["sobol2"].view(np.uint32)).all()
+    for log2n in (0, 1, 4, 6, 10):
+        n = 1 << log2n
+        for p in (0, 1, 0x12345678, 0xffffffff):
+            assert sorted(L.permute(np.arange(n), n - 1, p).tolist()) == list(range(n))
