@@ -396,7 +396,9 @@ static int ser_inflate(const unsigned char *src, size_t srcBytes, int version, P
 	L.faceBegin = next; L.vertexBegin = L.posBase; L.vertexStride = L.posStride;
 	const size_t total = next + (size_t) T * 12;
 	if (!out) { inflateEnd(&z); return 0; }
-	out->resize(total);
+	// deflate expands by at most 1032 : 1 — counts that promise more than the stream can hold are refused before allocating
+	if (total > srcBytes * 1100 + 4096) { inflateEnd(&z); MTSB_FAIL(MTSB_EINVAL, "serialized: header promises %zu payload bytes, the stream has %zu", total, srcBytes); }
+	try { out->resize(total); } catch (const std::exception &) { inflateEnd(&z); MTSB_FAIL(MTSB_ENOMEM, "serialized: %zu bytes of host memory for the payload", total); }
 	memcpy(out->data(), head.data(), std::min(got, total));
 	size_t have = std::min(got, total);
 	while (have < total && rc != Z_STREAM_END) {
