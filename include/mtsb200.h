@@ -367,6 +367,14 @@ MTSB_API void  mtsb_host_free(void *p);
 MTSB_API int  mtsb_eval_bsdf(mtsb_scene *scene, int bsdf, const float *bsdf_in, size_t n, float *bsdf_out);
 /* Same, with the extra draw that EUsesSampler plugins take from bRec.sampler inside sample() (roughdielectric's
  * lobe selection, src/bsdfs/roughdielectric.cpp:562): s3 = n floats, NULL = 0.5 for every row. */
+/* Scene::evalTransmittance (src/librender/scene.cpp:650-713) for a batch of segments: the transmittance between p1 and p2
+ * through the scene's participating media, walking through index-matched (`null` BSDF) boundaries with the light-record
+ * overload and switching media at each of them; 0 behind an occluder or on a "medium inconsistency".  flags bit 0 / bit 1 =
+ * p1OnSurface / p2OnSurface (Epsilon at the start, the shadow-ray shortening at the end), medium = the medium at p1 (-1 =
+ * none), max_interactions = the caller's `interactions` bound (-1 = none).  out_rgb: 3 floats per segment.  The same kernel
+ * (connect_vol_kernel, csrc/render_vol.cuh) serves the volumetric integrators' connection queue. */
+typedef struct mtsb_segment { float p1[3]; uint32_t flags; float p2[3]; int32_t medium; } mtsb_segment;
+MTSB_API int  mtsb_eval_transmittance(mtsb_scene *scene, const mtsb_segment *segments, size_t n, int max_interactions, float *out_rgb);
 /* Test support: the draws the render's sampler (independent or ldsampler) hands to samples first .. first+n-1 of pixel (px, py):
  * per sample `draws` next2D calls, then `draws` next1D calls; out[n][draws][3] = (2D.x, 2D.y, 1D). */
 MTSB_API int  mtsb_render_sampler_dump(mtsb_render *r, uint32_t px, uint32_t py, uint32_t first, uint32_t n, uint32_t draws, float *out);

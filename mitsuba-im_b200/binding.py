@@ -36,6 +36,7 @@ hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]
 surface_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4"), ("shape", "<u4"),
                           ("prim_local", "<u4"), ("p", "<f4", 3), ("ng", "<f4", 3), ("ns", "<f4", 3),
                           ("s", "<f4", 3), ("tt", "<f4", 3), ("uv", "<f4", 2)])
+segment_dtype = np.dtype([("p1", "<f4", 3), ("flags", "<u4"), ("p2", "<f4", 3), ("medium", "<i4")])
 light_dtype = np.dtype([("t", "<f4"), ("shape", "<u4"), ("n", "<f4", 3), ("uv", "<f4", 2), ("pad", "<u4")])
 assert light_dtype.itemsize == 32
 assert ray_dtype.itemsize == 32 and hit_dtype.itemsize == 16 and surface_dtype.itemsize == 92
@@ -129,7 +130,7 @@ def lib():
         "mtsb_serialized_probe": (i32, [vp, sz, i32, C.POINTER(u32), C.POINTER(u32)]),
         "mtsb_scene_add_rectangle": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_add_disk": (i32, [vp, vp, i32, i32, i32]), "mtsb_scene_expand_bounds": (i32, [vp, vp, vp]),
         "mtsb_scene_add_sphere": (i32, [vp, vp, C.c_float, i32, i32, i32]),
-        "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
+        "mtsb_eval_transmittance": (i32, [vp, vp, sz, i32, vp]), "mtsb_scene_add_medium": (i32, [vp, vp]), "mtsb_scene_set_shape_media": (i32, [vp, i32, i32, i32]),
         "mtsb_render_set_camera_medium": (i32, [vp, i32]), "mtsb_render_set_ldsampler": (i32, [vp, i32, sz]), "mtsb_render_sampler_dump": (i32, [vp, u32, u32, u32, u32, u32, vp]), "mtsb_render_set_sobol": (i32, [vp, vp, sz]),
         "mtsb_scene_commit": (i32, [vp, i32]), "mtsb_scene_aabb": (i32, [vp, vp, vp]),
         "mtsb_scene_primitive_count": (sz, [vp]), "mtsb_scene_shape_count": (sz, [vp]),
@@ -432,6 +433,17 @@ class Scene:
         r = self._rays(rays)
         out = np.empty(r.shape[0], surface_dtype)
         _check(lib().mtsb_trace_surface(self.h, _ptr(r), r.shape[0], _ptr(out), 0))
+        return out
+
+    def eval_transmittance(self, p1, p2, medium, p1_on_surface=False, p2_on_surface=False, max_interactions=-1):
+        """Scene::evalTransmittance for a batch of segments (mtsb_eval_transmittance); returns [n, 3]."""
+        p1 = np.asarray(p1, np.float32).reshape(-1, 3)
+        seg = np.zeros(p1.shape[0], segment_dtype)
+        seg["p1"] = p1; seg["p2"] = np.asarray(p2, np.float32).reshape(-1, 3)
+        seg["medium"] = medium
+        seg["flags"] = np.asarray(p1_on_surface, np.uint32) * 1 + np.asarray(p2_on_surface, np.uint32) * 2
+        out = np.zeros((p1.shape[0], 3), np.float32)
+        _check(lib().mtsb_eval_transmittance(self.h, _ptr(seg), seg.shape[0], int(max_interactions), _ptr(out)))
         return out
 
     def ray_intersect_light(self, rays):

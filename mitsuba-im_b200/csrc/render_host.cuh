@@ -557,6 +557,48 @@ int mtsb_render_samples_ex(mtsb_render *r, const uint32_t *samples, size_t n, ui
 	return 0;
 }
 
+// ---- Scene::evalTransmittance for a batch of segments: the connection walk of the volumetric integrators on its own
+__global__ void transmittance_setup_kernel(const mtsb_segment *segs, uint32_t n, int maxInteractions, PathState ps) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i == 0) { ps.counters[CTR_SHADOW] = n; ps.work[1] = 0ull; }
+	if (i >= n) return;
+	const mtsb_segment s = segs[i];
+	const uint32_t maxi = maxInteractions < 0 ? 0xffffu : (uint32_t) min(maxInteractions, 0xfffe);
+	const uint32_t bits = VQ_PACK(s.flags & 3u, s.medium, maxi);
+	ps.shO[i] = make_float4(s.p1[0], s.p1[1], s.p1[2], __uint_as_float(bits));
+	ps.shD[i] = make_float4(s.p2[0], s.p2[1], s.p2[2], 0.0f);
+	ps.shL[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(i));
+	ps.L[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+int mtsb_eval_transmittance(mtsb_scene *scene, const mtsb_segment *segments, size_t n, int max_interactions, float *out_rgb) {
+	if (!scene || !scene->committed || !segments || !out_rgb) MTSB_FAIL(MTSB_EINVAL, "mtsb_eval_transmittance: NULL argument or scene not committed");
+	if (n == 0) return 0;
+	if (n > 0x7fffffffull) MTSB_FAIL(MTSB_EINVAL, "mtsb_eval_transmittance: at most 2^31 segments a call");
+	for (size_t i = 0; i < n; ++i)
+		if (segments[i].medium < -1 || segments[i].medium >= (int) scene->media.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_eval_transmittance: segment %zu names medium %d", i, segments[i].medium);
+	mtsb_ctx *ctx = scene->ctx;
+	MTSB_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t st = ctx->stream;
+	DevBuf<mtsb_segment> dS; DevBuf<float4> q; DevBuf<uint32_t> counters; DevBuf<unsigned long long> work;
+	MTSB_CHECK(dS.upload(segments, n, st)); MTSB_CHECK(q.alloc(4 * n)); MTSB_CHECK(counters.alloc(CTR_WORDS)); MTSB_CHECK(work.alloc(8));
+	MTSB_CUDA(cudaMemsetAsync(counters.ptr, 0, CTR_WORDS * sizeof(uint32_t), st));
+	MTSB_CUDA(cudaMemsetAsync(work.ptr, 0, 8 * sizeof(unsigned long long), st));
+	PathState ps; memset(&ps, 0, sizeof(ps));
+	ps.shO = q.ptr; ps.shD = q.ptr + n; ps.shL = q.ptr + 2 * n; ps.L = q.ptr + 3 * n;
+	ps.counters = counters.ptr; ps.work = work.ptr; ps.stats = work.ptr + 4;      // stats[2] = shadow rays lands in work[6]
+	transmittance_setup_kernel<<<blocks_for(n, 256), 256, 0, st>>>(dS.ptr, (uint32_t) n, max_interactions, ps);
+	l2_phase(scene, false);
+	const unsigned grid = (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS;
+	MTSB_CHECK(launch_trav(scene, scene->curved ? connect_vol_kernel<true> : connect_vol_kernel<false>, grid, st, scene->dev, ps));
+	MTSB_CUDA(cudaGetLastError());
+	std::vector<float4> host(n);
+	MTSB_CUDA(cudaMemcpyAsync(host.data(), ps.L, n * sizeof(float4), cudaMemcpyDeviceToHost, st));
+	MTSB_CUDA(cudaStreamSynchronize(st));
+	for (size_t i = 0; i < n; ++i) { out_rgb[3 * i] = host[i].x; out_rgb[3 * i + 1] = host[i].y; out_rgb[3 * i + 2] = host[i].z; }
+	return 0;
+}
+
 int mtsb_render_sampler_dump(mtsb_render *r, uint32_t px, uint32_t py, uint32_t first, uint32_t n, uint32_t draws, float *out) {
 	if (!r || !out) MTSB_FAIL(MTSB_EINVAL, "mtsb_render_sampler_dump: NULL argument");
 	if (n == 0 || draws == 0) return 0;

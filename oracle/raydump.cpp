@@ -385,6 +385,29 @@ public:
 		return 0;
 	}
 
+	/// Scene::evalTransmittance on segments {p1[3], flags (bit 0 p1OnSurface, bit 1 p2OnSurface), p2[3], medium index or -1} (8 floats
+	/// each, the two integers as float values); media in the order of Scene::getMedia().  Output: 3 floats per segment.
+	int transmittance(int argc, char **argv) {
+		if (argc < 5) { cout << "transmittance <scene> <in> <out> [maxInteractions]" << endl; return 1; }
+		load(argv[2]);
+		std::vector<float> in = readFloats(argv[3]);
+		const int maxInteractions = argc > 5 ? atoi(argv[5]) : -1;
+		const ref_vector<Medium> &media = m_scene->getMedia();
+		std::vector<float> out;
+		for (size_t i = 0; i + 7 < in.size(); i += 8) {
+			const int flags = (int) in[i+3], mi = (int) in[i+7];
+			const Medium *medium = mi >= 0 && mi < (int) media.size() ? media[mi].get() : NULL;
+			int interactions = maxInteractions;
+			Spectrum T = m_scene->evalTransmittance(Point(in[i], in[i+1], in[i+2]), (flags & 1) != 0, Point(in[i+4], in[i+5], in[i+6]), (flags & 2) != 0,
+				0.0f, medium, interactions, NULL);
+			Float r, g, b; T.toLinearRGB(r, g, b);
+			out.push_back(r); out.push_back(g); out.push_back(b);
+		}
+		writeFloats(argv[4], out);
+		cout << "transmittance: " << out.size() / 3 << " segments, " << media.size() << " media" << endl;
+		return 0;
+	}
+
 	int bsdf(int argc, char **argv) {
 		if (argc < 5) { cout << "bsdf <scene> <in> <out>" << endl; return 1; }
 		load(argv[2]);
@@ -459,6 +482,7 @@ public:
 		if (!strcmp(argv[1], "sobol")) return sobolTables(argc, argv);
 		if (!strcmp(argv[1], "mesh")) return mesh(argc, argv);
 		if (!strcmp(argv[1], "qmc")) return qmc(argc, argv);
+		if (!strcmp(argv[1], "transmittance")) return transmittance(argc, argv);
 		if (!strcmp(argv[1], "plyload")) return plyload(argc, argv);
 		if (!strcmp(argv[1], "bsdf")) return bsdf(argc, argv);
 		if (!strcmp(argv[1], "emitter")) return emitter(argc, argv);
