@@ -42,6 +42,7 @@ struct PlyLayout {
 	uint32_t posStride, nrmStride, uvStride;
 	int f64;                              // attributes are doubles (`serialized` with EDoublePrecision), converted like readHelper does
 	int normalizeStored;                  // ply.cpp:210 always normalises a stored normal, serialized.cpp:191-194 only behind a toWorld
+	int bigEndian;                        // `format binary_big_endian`: every multi-byte field is byte-swapped after the load
 };
 
 __device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteOffset) {
@@ -50,9 +51,13 @@ __device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteO
 	if (sh == 0) return lo;
 	return __funnelshift_r(lo, words[w + 1], sh);
 }
+__device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteOffset, int bigEndian) {
+	const uint32_t v = load_u32(words, byteOffset);
+	return bigEndian ? __byte_perm(v, 0, 0x0123) : v;
+}
 __device__ __forceinline__ float load_f32(const uint32_t *words, size_t byteOffset) { return __uint_as_float(load_u32(words, byteOffset)); }
-__device__ __forceinline__ float load_real(const uint32_t *words, size_t byteOffset, int f64) {
-	if (!f64) return load_f32(words, byteOffset);
+__device__ __forceinline__ float load_real(const uint32_t *words, size_t byteOffset, int f64, int bigEndian = 0) {
+	if (!f64) return __uint_as_float(load_u32(words, byteOffset, bigEndian));
 	return (float) __hiloint2double((int) load_u32(words, byteOffset + 4), (int) load_u32(words, byteOffset));     // (Float) temp[i]
 }
 
@@ -65,7 +70,7 @@ __global__ void ply_vertex_kernel(const uint32_t *words, size_t base, PlyLayout 
 	const size_t recP = base + L.posBase + (size_t) i * L.posStride, recN = base + L.nrmBase + (size_t) i * L.nrmStride,
 		recT = base + L.uvBase + (size_t) i * L.uvStride;
 	float p[3];
-	for (int a = 0; a < 3; ++a) p[a] = L.offPos[a] >= 0 ? load_real(words, recP + L.offPos[a], L.f64) : 0.0f;
+	for (int a = 0; a < 3; ++a) p[a] = L.offPos[a] >= 0 ? load_real(words, recP + L.offPos[a], L.f64, L.bigEndian) : 0.0f;
 	if (!X.identity) {
 		// the reference's expression order, no contraction
 		float q[4];
@@ -77,7 +82,7 @@ __global__ void ply_vertex_kernel(const uint32_t *words, size_t base, PlyLayout 
 	positions[(size_t) i * 3] = p[0]; positions[(size_t) i * 3 + 1] = p[1]; positions[(size_t) i * 3 + 2] = p[2];
 	if (L.offNrm[0] >= 0 && !zeroNormals) {
 		float n[3];
-		for (int a = 0; a < 3; ++a) n[a] = L.offNrm[a] >= 0 ? load_real(words, recN + L.offNrm[a], L.f64) : 0.0f;
+		for (int a = 0; a < 3; ++a) n[a] = L.offNrm[a] >= 0 ? load_real(words, recN + L.offNrm[a], L.f64, L.bigEndian) : 0.0f;
 		if (!X.identity) {
 			float t[3];
 			for (int c = 0; c < 3; ++c)
@@ -90,8 +95,8 @@ __global__ void ply_vertex_kernel(const uint32_t *words, size_t base, PlyLayout 
 	} else {
 		normals[(size_t) i * 3] = 0; normals[(size_t) i * 3 + 1] = 0; normals[(size_t) i * 3 + 2] = 0;
 	}
-	texcoords[(size_t) i * 2]     = L.offUV[0] >= 0 ? load_real(words, recT + L.offUV[0], L.f64) : 0.0f;
-	texcoords[(size_t) i * 2 + 1] = L.offUV[1] >= 0 ? load_real(words, recT + L.offUV[1], L.f64) : 0.0f;
+	texcoords[(size_t) i * 2]     = L.offUV[0] >= 0 ? load_real(words, recT + L.offUV[0], L.f64, L.bigEndian) : 0.0f;
+	texcoords[(size_t) i * 2 + 1] = L.offUV[1] >= 0 ? load_real(words, recT + L.offUV[1], L.f64, L.bigEndian) : 0.0f;
 }
 
 __device__ __forceinline__ float unit_angle(const float *u, const float *v) {      // include/mitsuba/core/util.h:321-326
@@ -130,14 +135,15 @@ __global__ void ply_face_kernel(const uint32_t *words, size_t base, PlyLayout L,
 	if (f >= L.faceCount) return;
 	const size_t rec = base + L.faceBegin + (size_t) f * L.faceStride + L.faceListOffset;
 	if (L.faceCountBytes) {
-		uint32_t count = load_u32(words, rec);
+		uint32_t count = load_u32(words, rec);                 // a one-byte count is the first byte in memory either way
 		if (L.faceCountBytes == 1) count &= 0xffu;
+		else if (L.bigEndian) count = __byte_perm(count, 0, 0x0123);
 		if (count != L.vertsPerFace) { atomicOr(error, 1u); return; }
 	}
 	uint32_t v[4] = { 0, 0, 0, 0 };
 	bool ok = true;
 	for (uint32_t k = 0; k < L.vertsPerFace; ++k) {
-		v[k] = load_u32(words, rec + L.faceCountBytes + 4 * k);
+		v[k] = load_u32(words, rec + L.faceCountBytes + 4 * k, L.bigEndian);
 		ok = ok && v[k] < L.vertexCount;          // Assert((size_t) element < m_vertexCount), ply.cpp:266,272 (a negative int32 fails it too)
 	}
 	if (!ok) { atomicOr(error, 2u); return; }
@@ -202,7 +208,7 @@ static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, b
 	L.offUV[0] = L.offUV[1] = -1;
 	size_t pos = 0; int lineNo = 0;
 	enum { NONE, VERTEX, FACE, OTHER } cur = NONE;
-	bool sawFormat = false, sawVertex = false, sawFace = false, faceList = false, done = false;
+	bool bigEndian = false, sawFormat = false, sawVertex = false, sawFace = false, faceList = false, done = false;
 	size_t otherBytesAfterFace = 0, otherCount = 0, otherStride = 0; bool otherBeforeVertex = false;
 	size_t bytesBeforeVertex = 0, bytesBetween = 0;
 	auto closeOther = [&]() {
@@ -219,9 +225,9 @@ static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, b
 		if (lineNo == 1) { if (w.size() != 1 || w[0] != "ply") MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: not a PLY file (no 'ply' magic)"); continue; }
 		if (w.empty() || w[0] == "comment" || w[0] == "obj_info") continue;
 		if (w[0] == "format") {
-			if (w.size() < 3 || w[1] != "binary_little_endian")
-				MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_ply: format '%s' (the device decoder reads binary_little_endian; ascii and big-endian files go through the host parser)", w.size() > 1 ? w[1].c_str() : "");
-			sawFormat = true;
+			if (w.size() < 3 || (w[1] != "binary_little_endian" && w[1] != "binary_big_endian"))
+				MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_ply: format '%s' (the device decoder reads binary_little_endian and binary_big_endian; ascii files go through the host parser)", w.size() > 1 ? w[1].c_str() : "");
+			sawFormat = true; bigEndian = w[1] == "binary_big_endian";
 		} else if (w[0] == "element") {
 			if (w.size() != 3) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: header line %d: malformed element", lineNo);
 			closeOther();
@@ -287,7 +293,7 @@ static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, b
 	L.faceStride = (uint32_t) (fixed + 4 * L.vertsPerFace);
 	L.posBase = L.nrmBase = L.uvBase = L.vertexBegin;
 	L.posStride = L.nrmStride = L.uvStride = L.vertexStride;
-	L.f64 = 0; L.normalizeStored = 1;
+	L.f64 = 0; L.normalizeStored = 1; L.bigEndian = bigEndian ? 1 : 0;
 	return 0;
 }
 

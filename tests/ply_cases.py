@@ -17,8 +17,11 @@ def _grid(n, seed):
     return V, N, UV, Q
 
 
-def _image(header_lines, vertex_fields, vertex_data, face_dtype, face_data, tail=b""):
-    hdr = "ply\nformat binary_little_endian 1.0\n" + "".join(l + "\n" for l in header_lines) + "end_header\n"
+def _image(header_lines, vertex_fields, vertex_data, face_dtype, face_data, tail=b"", big_endian=False):
+    hdr = "ply\nformat %s 1.0\n" % ("binary_big_endian" if big_endian else "binary_little_endian") + "".join(l + "\n" for l in header_lines) + "end_header\n"
+    if big_endian:
+        vertex_fields = [(n, t.replace("<", ">")) for n, t in vertex_fields]
+        face_dtype = [tuple(x.replace("<", ">") if isinstance(x, str) and i == 1 else x for i, x in enumerate(f)) for f in face_dtype]
     vd = np.empty(len(vertex_data[0]), dtype=vertex_fields)
     for (name, _), col in zip(vertex_fields, vertex_data):
         vd[name] = col
@@ -62,6 +65,13 @@ def cases():
          "element face %d" % len(F), "property list uchar int vertex_indices"],
         [(k, f32) for k in ("x", "y", "z", "nx", "ny", "nz", "u", "v")], [V[:, 0], V[:, 1], V[:, 2], N[:, 0], N[:, 1], N[:, 2], UV[:, 0], UV[:, 1]],
         [("n", "u1"), ("i", "<i4", 3)], [np.full(len(F), 3), F]), xml="", kwargs={})
+    # 1b. the same file in binary_big_endian, with a uint count
+    out["tri_n_uv_big_endian"] = dict(image=_image(
+        ["element vertex %d" % len(V), "property float x", "property float y", "property float z",
+         "property float nx", "property float ny", "property float nz", "property float u", "property float v",
+         "element face %d" % len(F), "property list uint int vertex_indices"],
+        [(k, f32) for k in ("x", "y", "z", "nx", "ny", "nz", "u", "v")], [V[:, 0], V[:, 1], V[:, 2], N[:, 0], N[:, 1], N[:, 2], UV[:, 0], UV[:, 1]],
+        [("n", "<u4"), ("i", "<i4", 3)], [np.full(len(F), 3), F], big_endian=True), xml="", kwargs={})
     # 2. no normals in the file: TriMesh::computeNormals makes angle-weighted ones; through toWorld
     out["tri_computed_normals_xform"] = dict(image=_image(
         ["element vertex %d" % len(V), "property float32 x", "property float32 y", "property float32 z",
