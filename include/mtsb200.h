@@ -215,8 +215,9 @@ typedef struct mtsb_envmap_desc {
  * default; 1 for the other filters).  Sensor rays carry differentials: the first hit of a path computes uv partials
  * (Intersection::computePartials, src/librender/intersection.cpp:5-76) and takes the filtered lookup, later hits the
  * full-resolution one — as `path` / `direct` / `volpath*` do in the reference.  mtsb_scene_set_bsdf_texture binds a texture to
- * the `reflectance` of an MTSB_BSDF_DIFFUSE (the only textured slot of the subset); textured BSDFs go on triangle meshes and
- * rectangles. */
+ * the `reflectance` of an MTSB_BSDF_DIFFUSE or to the `diffuseReflectance` of an MTSB_BSDF_PLASTIC (whose p[1..3] then only
+ * matter for p[9]: the reference weighs the lobes by the texture's average, plastic.cpp:202-205); textured BSDFs go on triangle
+ * meshes and rectangles. */
 typedef struct mtsb_texture_desc {
 	int32_t levels;
 	const int32_t *sizes;

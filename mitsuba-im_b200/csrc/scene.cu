@@ -209,8 +209,9 @@ int mtsb_scene_add_texture(mtsb_scene *scene, const mtsb_texture_desc *desc) {
 int mtsb_scene_set_bsdf_texture(mtsb_scene *scene, int bsdf, int texture) {
 	if (!scene) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: NULL scene");
 	if (scene->committed) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: scene already committed");
-	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size() || (scene->bsdfs[bsdf].type & 0xff) != MTSB_BSDF_DIFFUSE)
-		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_set_bsdf_texture: only the reflectance of a diffuse BSDF takes a texture (bsdf %d)", bsdf);
+	if (bsdf < 0 || bsdf >= (int) scene->bsdfs.size() ||
+	    ((scene->bsdfs[bsdf].type & 0xff) != MTSB_BSDF_DIFFUSE && (scene->bsdfs[bsdf].type & 0xff) != MTSB_BSDF_PLASTIC))
+		MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_set_bsdf_texture: only the reflectance of a diffuse BSDF and the diffuseReflectance of a plastic BSDF take a texture (bsdf %d)", bsdf);
 	if (texture < 0 || texture >= (int) scene->texRecords.size()) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_set_bsdf_texture: texture %d unknown", texture);
 	scene->bsdfTexture.resize(scene->bsdfs.size(), -1);
 	scene->bsdfTexture[bsdf] = texture;

@@ -8,7 +8,8 @@
 
 namespace mtsb {
 
-__device__ __forceinline__ bool bsdf_textured(const BsdfRec &b) { return (b.type & 0xff) == MTSB_BSDF_DIFFUSE && b.p[12] != 0.0f; }
+// the diffuse reflectance of `diffuse` (p[0..2]) or of `plastic` (p[1..3]) comes from a texture: p[12] = 1, p[13..14] = its record
+__device__ __forceinline__ bool bsdf_textured(const BsdfRec &b) { const int t = b.type & 0xff; return (t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_PLASTIC) && b.p[12] != 0.0f; }
 
 // its.dpdu / its.dpdv for a hit on a triangle mesh or a rectangle
 __device__ inline void surface_tangents(const SceneDev &S, uint32_t slot, const ShapeRec &sh, uint32_t prim, V3 &dpdu, V3 &dpdv) {
@@ -63,7 +64,7 @@ __device__ inline void compute_partials(const V3 &n, const V3 &p, const V3 &o, c
 	if (solve_linear_2x2(A, By, x)) { dudy = x[0]; dvdy = x[1]; } else { dudy = 1; dvdy = 0; }      // (":74 dudy = 0; dudy = 1;" as written)
 }
 
-// Replaces the reflectance of a textured diffuse record by the texture's value at this hit.  hasDifferentials: the ray is a
+// Replaces the diffuse reflectance of a textured `diffuse` / `plastic` record by the texture's value at this hit.  hasDifferentials: the ray is a
 // sensor ray (rx, ry = its differential directions); kept out of line, like the environment lookup.
 static __device__ __noinline__ void resolve_bsdf_texture(const SceneDev *S, BsdfRec *b, const Surf *sf, uint32_t slot, bool hasDifferentials,
 		float ox, float oy, float oz, float rxx, float rxy, float rxz, float ryx, float ryy, float ryz) {
@@ -76,7 +77,8 @@ static __device__ __noinline__ void resolve_bsdf_texture(const SceneDev *S, Bsdf
 		compute_partials(sf->ng, sf->p, v3(ox, oy, oz), v3(rxx, rxy, rxz), v3(ryx, ryy, ryz), dpdu, dpdv, dudx, dvdx, dudy, dvdy);
 	}
 	const V3 c = texture_eval(T, sf->u, sf->v, hasDifferentials, dudx, dvdx, dudy, dvdy);
-	b->p[0] = c.x; b->p[1] = c.y; b->p[2] = c.z;
+	const int off = (b->type & 0xff) == MTSB_BSDF_PLASTIC ? 1 : 0;
+	b->p[off] = c.x; b->p[off + 1] = c.y; b->p[off + 2] = c.z;
 }
 
 // the BSDF record of a hit, textures resolved; `first`: the path's sensor ray, whose differentials generate_kernel left in prev / L

@@ -140,7 +140,7 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float>
 	memset(&d, 0, sizeof(d));
 	const std::string cls = bsdf->getClass()->getName();
 	const Properties &props = bsdf->getProperties();
-	if (bsdf->usesRayDifferentials() && cls != "SmoothDiffuse" && cls != "TwoSidedBRDF")
+	if (bsdf->usesRayDifferentials() && cls != "SmoothDiffuse" && cls != "SmoothPlastic" && cls != "TwoSidedBRDF")
 		SLog(EError, "gpupath: BSDF \"%s\" uses textures that need ray differentials — outside the GPU subset", cls.c_str());
 	Intersection its = dummyIntersection();
 	if (cls == "SmoothDiffuse") {                                   // src/bsdfs/diffuse.cpp:80-100
@@ -166,10 +166,31 @@ static bool describeBSDF(const BSDF *bsdf, mtsb_bsdf_desc &d, std::vector<float>
 		d.type = MTSB_BSDF_PLASTIC;
 		const Float intIOR = lookupIOR(props, "intIOR", "polypropylene"), extIOR = lookupIOR(props, "extIOR", "air");
 		const Float eta = intIOR / extIOR;
-		const Spectrum diff = props.getSpectrum("diffuseReflectance", Spectrum(0.5f));
+		Spectrum diff = props.getSpectrum("diffuseReflectance", Spectrum(0.5f));
 		const Spectrum spec = props.getSpectrum("specularReflectance", Spectrum(1.0f));
+		const Texture *texturedDiffuse = NULL;
+		{
+			// textures arrive through addChild, not through the properties: SmoothPlastic keeps them in private members behind no
+			// accessor (plastic.cpp:475-480) — read through a layout mirror, checked against the eta computed above and by RTTI
+			struct Mirror { char base[sizeof(BSDF)]; Float fdrInt, fdrExt, eta, invEta2; const Texture *diffuse; const Texture *specular; Float ssw; bool nonlinear; };
+			const Mirror *m = reinterpret_cast<const Mirror *>(static_cast<const BSDF *>(bsdf));
+			if (m->eta != eta || !m->diffuse || !m->specular || !m->diffuse->getClass()->derivesFrom(MTS_CLASS(Texture)) || !m->specular->getClass()->derivesFrom(MTS_CLASS(Texture)))
+				SLog(EError, "gpupath: SmoothPlastic does not have the layout of src/bsdfs/plastic.cpp:475-480");
+			if (!m->specular->isConstant()) SLog(EError, "gpupath: a textured specularReflectance is outside the GPU subset");
+			if (!m->diffuse->isConstant()) {
+				if (m->diffuse->getClass()->getName() != "BitmapTexture")
+					SLog(EError, "gpupath: the diffuseReflectance texture of this plastic BSDF is outside the GPU subset (bitmap; a texture brighter than 1 gets wrapped in a scaling texture): %s",
+						bsdf->toString().substr(0, 300).c_str());
+				if (!texture) SLog(EError, "gpupath: a textured BSDF inside an adapter is outside the GPU subset");
+				describeBitmapTexture(m->diffuse, *texture);
+				diff = m->diffuse->getAverage();                       // plastic.cpp:202-205 weighs the lobes by the texture's average
+				texturedDiffuse = m->diffuse;
+			}
+		}
 		d.p[0] = (float) eta;
 		toRGB(diff, d.p + 1); toRGB(spec, d.p + 4);
+		// the record's own colour is replaced at every hit; the value at the dummy intersection keeps selfCheckBSDF meaningful
+		if (texturedDiffuse) toRGB(texturedDiffuse->eval(its), d.p + 1);
 		d.p[7] = (float) fresnelDiffuseReflectance(1 / eta, false);
 		d.p[8] = (float) fresnelDiffuseReflectance(eta, false);
 		const Float dAvg = diff.getLuminance(), sAvg = spec.getLuminance();

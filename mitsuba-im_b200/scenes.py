@@ -359,6 +359,9 @@ class SceneDesc:
             fdr_int = fresnel_diffuse_reflectance(1.0 / eta)
             fdr_ext = fresnel_diffuse_reflectance(eta)
             dr = list(b.get("diffuse_reflectance", (0.5, 0.5, 0.5)))
+            if b.get("texture") is not None and b["texture"].get("pyramid") is not None:
+                # plastic.cpp:202-205 weighs the lobes by Texture::getAverage(): the mean of the texture's full-resolution level
+                dr = [float(x) for x in np.asarray(b["texture"]["pyramid"][0], np.float64).reshape(-1, 3).mean(axis=0)]
             sr = list(b.get("specular_reflectance", (1, 1, 1)))
             lum = lambda c: 0.212671 * c[0] + 0.715160 * c[1] + 0.072169 * c[2]   # Spectrum::getLuminance (RGB build)
             d_avg, s_avg = lum(dr), lum(sr)
@@ -508,16 +511,22 @@ class SceneDesc:
         if t == "passthrough":          # index-matched medium boundary (src/bsdfs/null.cpp)
             return '<bsdf type="null"/>'
         inner = ""
-        if t == "diffuse" and b.get("texture") is not None:
-            # `bitmap` texture on the reflectance (src/textures/bitmap.cpp); to_xml() has written the image and set its file name
-            x = b["texture"]
-            inner = ('<bsdf type="diffuse"><texture type="bitmap" name="reflectance"><string name="filename" value="%s"/>'
-                     '<string name="wrapModeU" value="%s"/><string name="wrapModeV" value="%s"/><string name="filterType" value="%s"/>'
-                     '<float name="maxAnisotropy" value="%r"/><float name="uscale" value="%r"/><float name="vscale" value="%r"/>'
-                     '<float name="uoffset" value="%r"/><float name="voffset" value="%r"/><boolean name="cache" value="false"/></texture></bsdf>') % (
-                x["filename"], x.get("wrap_u", x.get("wrap", "repeat")), x.get("wrap_v", x.get("wrap", "repeat")), x.get("filter", "ewa"),
+
+        def tex_xml(name, x):
+            # `bitmap` texture (src/textures/bitmap.cpp); to_xml() has written the image and set its file name
+            return ('<texture type="bitmap" name="%s"><string name="filename" value="%s"/>'
+                    '<string name="wrapModeU" value="%s"/><string name="wrapModeV" value="%s"/><string name="filterType" value="%s"/>'
+                    '<float name="maxAnisotropy" value="%r"/><float name="uscale" value="%r"/><float name="vscale" value="%r"/>'
+                    '<float name="uoffset" value="%r"/><float name="voffset" value="%r"/><boolean name="cache" value="false"/></texture>') % (
+                name, x["filename"], x.get("wrap_u", x.get("wrap", "repeat")), x.get("wrap_v", x.get("wrap", "repeat")), x.get("filter", "ewa"),
                 float(x.get("max_anisotropy", 20.0)), float(x.get("uv_scale", (1, 1))[0]), float(x.get("uv_scale", (1, 1))[1]),
                 float(x.get("uv_offset", (0, 0))[0]), float(x.get("uv_offset", (0, 0))[1]))
+        if t == "diffuse" and b.get("texture") is not None:
+            inner = '<bsdf type="diffuse">%s</bsdf>' % tex_xml("reflectance", b["texture"])
+        elif t == "plastic" and b.get("texture") is not None:
+            inner = '<bsdf type="plastic"><float name="intIOR" value="%r"/><float name="extIOR" value="%r"/>%s%s<boolean name="nonlinear" value="%s"/></bsdf>' % (
+                b.get("int_ior", 1.49), b.get("ext_ior", 1.000277), tex_xml("diffuseReflectance", b["texture"]),
+                rgb("specularReflectance", b.get("specular_reflectance", (1, 1, 1))), "true" if b.get("nonlinear") else "false")
         elif t == "diffuse":
             inner = '<bsdf type="diffuse">%s</bsdf>' % rgb("reflectance", b.get("reflectance", (0.5, 0.5, 0.5)))
         elif t == "dielectric":
@@ -865,10 +874,12 @@ def texture_image(size=64, seed=9):
     return np.clip(img * (1.0 + 0.1 * rng.standard_normal((size, size, 1))), 0.02, 0.9).astype(np.float32)
 
 
-def textured_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent", seed=0, pyramids=None, kind="path"):
+def textured_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent", seed=0, pyramids=None, kind="path", plastic=False):
     """`bitmap` textures on the reflectance of diffuse BSDFs: a floor mesh with texture coordinates that repeat the
     texture 6 x 6 times (EWA, seen at a grazing angle: anisotropic footprints), a wall `rectangle` (trilinear, clamp, uv scale and
-    offset) and a displaced sphere with spherical coordinates (bilinear, mirror); pyramids = the three MIP pyramids."""
+    offset) and a displaced sphere with spherical coordinates (bilinear, mirror); pyramids = the three MIP pyramids.
+    plastic=True: the wall and the sphere carry the texture on the diffuseReflectance of a `plastic` BSDF instead (the sphere's
+    with nonlinear colour shifts)."""
     img = texture_image()
     pyramids = pyramids or [None, None, None]
     sd = SceneDesc()
@@ -880,13 +891,14 @@ def textured_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent
     gUV = np.array([[0, 0], [6, 0], [6, 6], [0, 6]], np.float32)
     sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), UV=gUV,
                 bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[0], wrap="repeat", filter="ewa")))
+    mat = "plastic" if plastic else "diffuse"
     sd.add_rectangle(translate(0, 1.5, 2.5) @ rotate((0, 1, 0), 180) @ scale(2.5, 1.5, 1.0),
-                     bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[1], wrap="clamp", filter="trilinear", uv_scale=(3, 2), uv_offset=(-0.4, 0.1))))
+                     bsdf=dict(type=mat, texture=dict(image=img, pyramid=pyramids[1], wrap="clamp", filter="trilinear", uv_scale=(3, 2), uv_offset=(-0.4, 0.1))))
     c = np.array((0.3, 0.7, 0.2))
     V, N, F = displaced_sphere(3, seed=33, radius=0.7, center=tuple(c))
     dn = (V - c) / np.linalg.norm(V - c, axis=1, keepdims=True)
     UV = np.stack([np.arctan2(dn[:, 2], dn[:, 0]) / (2 * math.pi) + 0.5, np.arccos(np.clip(dn[:, 1], -1, 1)) / math.pi], axis=1) * 3.0
-    sd.add_mesh(V, N, F, UV=UV, bsdf=dict(type="diffuse", texture=dict(image=img, pyramid=pyramids[2], wrap="mirror", filter="bilinear")))
+    sd.add_mesh(V, N, F, UV=UV, bsdf=dict(type=mat, nonlinear=plastic, int_ior=1.7, texture=dict(image=img, pyramid=pyramids[2], wrap="mirror", filter="bilinear")))
     V, N, F = displaced_sphere(2, seed=34, radius=0.4, center=(-1.3, 0.4, -0.4))
     sd.add_mesh(V, N, F, bsdf=dict(type="dielectric"))
     sd.set_sensor(look_at((0.3, 1.3, -4.5), (0, 0.7, 0), (0, 1, 0)), 50.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)

@@ -223,6 +223,7 @@ def texture_cases(td):
     np.savez_compressed(os.path.join(GOLD, "texture_pyramids.npz"), **store)
     li_case(td, "textured", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=79, pyramids=pyramids))
     li_case(td, "textured_direct", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=83, pyramids=pyramids, kind="direct"))
+    li_case(td, "textured_plastic", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=89, pyramids=pyramids, plastic=True))
 
 
 def sobol_cases(td):

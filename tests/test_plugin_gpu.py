@@ -166,12 +166,13 @@ def test_sobol_sampler_through_the_loader(pkg, tmp_path):
     assert abs(gpu.mean() - ref.mean()) <= 0.01 * ref.mean()
 
 
-def test_bitmap_textures_through_the_loader(pkg, tmp_path):
-    """`bitmap` textures on diffuse reflectances, instantiated by the stock XML loader from a PFM file: the plugin
-    reads the texture out of the BSDF (plugin/extract.h) and rebuilds its MIP pyramid with the reference's own classes — EWA on a
-    repeating floor, trilinear + clamp + uv scale / offset on a rectangle, bilinear + mirror on a sphere; per-pixel match with the
-    stock `path` under the shared sampler."""
-    sd = pkg.scenes.textured_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=89)
+@pytest.mark.parametrize("plastic", [False, True], ids=["diffuse", "plastic"])
+def test_bitmap_textures_through_the_loader(pkg, tmp_path, plastic):
+    """`bitmap` textures on diffuse reflectances (and on the diffuseReflectance of `plastic`), instantiated by the
+    stock XML loader from a PFM file: the plugin reads the texture out of the BSDF (plugin/extract.h) and rebuilds its MIP pyramid
+    with the reference's own classes — EWA on a repeating floor, trilinear + clamp + uv scale / offset on a rectangle, bilinear +
+    mirror on a sphere; per-pixel match with the stock `path` under the shared sampler."""
+    sd = pkg.scenes.textured_scene(64, 48, spp=8, max_depth=5, sampler="ctr", seed=89, plastic=plastic)
     xml = sd.to_xml(str(tmp_path), "tex")
     ref, _ = run_mitsuba(str(tmp_path / "ref.pfm"), True, False, {}, xml=xml)
     gpu, log = run_mitsuba(str(tmp_path / "gpu.pfm"), True, True, {}, xml=xml)

@@ -139,7 +139,7 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
                                   "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights",
-                                  "envmap", "envmap_direct", "textured", "textured_direct"])
+                                  "envmap", "envmap_direct", "textured", "textured_direct", "textured_plastic"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -170,11 +170,11 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
         # by 1 / sqrt(spp)) where the camera sees the map directly — through `path` and through `direct`
         sd = S.envmap_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramid=_pyramid(golden),
                             kind="direct" if name == "envmap_direct" else "path")
-    elif name in ("textured", "textured_direct"):
+    elif name in ("textured", "textured_direct", "textured_plastic"):
         # `bitmap` textures on diffuse reflectances: uv partials from the sensor ray's differentials at the first hit
         # (intersection.cpp:5-76) and EWA / trilinear lookups there, full-resolution lookups at later hits; repeat / clamp / mirror
         sd = S.textured_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramids=_tex_pyramids(golden),
-                              kind="direct" if name == "textured_direct" else "path")
+                              kind="direct" if name == "textured_direct" else "path", plastic=name == "textured_plastic")
     elif name == "analytic_lights":
         # area lights on analytic spheres (cone / uniform-sphere sampling, sphere.cpp:286-385) and a disk (disk.cpp:247-259)
         sd = S.analytic_lights_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
