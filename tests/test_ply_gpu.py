@@ -167,3 +167,28 @@ def test_ply_decoder_refuses_what_it_cannot_decode(pkg, ctx):
     neg = hdr + verts + bytes([3]) + np.array([0, 1, 2], "<i4").tobytes() + bytes([3]) + np.array([0, 2, -1], "<i4").tobytes()
     with pytest.raises(B.MtsbError, match="references a vertex"):
         attempt(neg)
+
+
+def test_ply_decode_at_config2_size(pkg, ctx):
+    """BASELINE config 2's mesh (1 310 720 triangles) as a binary PLY image: the decoded positions and indices equal the arrays the
+    image was written from bit for bit, stored normals to the last bit of their re-normalisation, and the scene built from the
+    image answers 2 M chord rays exactly like the scene built from the arrays (same arrays -> same BVH -> same hits)."""
+    import bench
+    S, B = pkg.scenes, pkg.binding
+    sd = bench.build_mesh(S)
+    m = sd.shapes[0]
+    image = S.ply_image(m["V"], m["N"], m["F"])
+    assert B.ply_probe(image) == (m["V"].shape[0], m["F"].shape[0])
+    sc_ply = sd.upload(ctx, B.BUILDER_LBVH, ply_images={0: image})
+    sc_arr = sd.upload(ctx, B.BUILDER_LBVH)
+    P, N, UV, T = sc_ply.read_mesh(0)
+    assert (P.view(np.uint32) == np.asarray(m["V"], np.float32).view(np.uint32)).all()
+    assert (T == np.asarray(m["F"], np.uint32)).all()
+    assert np.abs(N - m["N"]).max() <= 2e-7
+    assert sc_ply.build_stats()["ply_decode_ms"] > 0 and sc_arr.build_stats()["ply_decode_ms"] == 0
+    rays = S.chord_rays(1 << 21, radius=1.1, seed=5)
+    a, b = sc_ply.ray_intersect(rays), sc_arr.ray_intersect(rays)
+    assert np.isfinite(b["t"]).mean() > 0.5
+    for k in ("t", "u", "v", "prim"):
+        assert (a[k].view(np.uint32) == b[k].view(np.uint32)).all(), k
+    sc_ply.close(); sc_arr.close()
