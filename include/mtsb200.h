@@ -408,7 +408,8 @@ MTSB_API int  mtsb_render_set_sobol(mtsb_render *r, const uint32_t *tables, size
  * sequence (radicalInverse2Single, sample02Single, include/mitsuba/core/qmc.h) in shuffled order; later draws are independent.
  * The reference scrambles and shuffles from a sequential Random per pixel in scheduler order and documents that two of its own
  * runs differ; here both are keyed by a counter-based generator on (pixel, dimension, seed): the same point-set construction,
- * another realisation — parity is statistical.  sample_count = the render's total samples per pixel. */
+ * another realisation (per-sample parity through the reference's integrators with the oracle's twin sampler,
+ * statistical parity against the stock plugin).  sample_count = the render's total samples per pixel. */
 MTSB_API int  mtsb_render_set_ldsampler(mtsb_render *r, int dimension, size_t sample_count);
 /* Sensor::getMedium(): the medium the camera sits in (-1 = none, the default); volpath_simple starts its paths there. */
 MTSB_API int  mtsb_render_set_camera_medium(mtsb_render *r, int medium);

@@ -497,7 +497,8 @@ class SceneDesc:
             if SOBOL_TABLES is None:
                 raise ValueError("sobol sampler: set scenes.SOBOL_TABLES (the reference's direction numbers, binding.Render.set_sobol)")
             rd.set_sobol(SOBOL_TABLES)
-        elif self.sampler["kind"] == "ldsampler":
+        elif self.sampler["kind"] in ("ldsampler", "ldctr"):
+            # "ldctr": the oracle's counter sampler in its low-discrepancy mode (oracle/ctrsampler.cpp) — the same numbers, draw for draw
             rd.set_ldsampler(self.sampler.get("dimension", 4), self.sampler["spp"])
         return rd
 
@@ -599,6 +600,9 @@ class SceneDesc:
                 out.append('<sampler type="sobol"><integer name="sampleCount" value="%d"/></sampler>' % sm["spp"])
             elif sm["kind"] == "ldsampler":
                 out.append('<sampler type="ldsampler"><integer name="sampleCount" value="%d"/><integer name="dimension" value="%d"/></sampler>' % (sm["spp"], sm.get("dimension", 4)))
+            elif sm["kind"] == "ldctr":
+                out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/><integer name="ldDimension" value="%d"/></sampler>' % (
+                    sm["spp"], sm["seed"], sm.get("dimension", 4)))
             elif sm["kind"] == "ctr":
                 out.append('<sampler type="ctr"><integer name="sampleCount" value="%d"/><integer name="seed" value="%d"/></sampler>' % (sm["spp"], sm["seed"]))
             else:

@@ -226,6 +226,20 @@ def texture_cases(td):
     li_case(td, "textured_plastic", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=89, pyramids=pyramids, plastic=True))
 
 
+def ldctr_cases(td):
+    """The low-discrepancy twin of the counter sampler (oracle/ctrsampler.cpp, ldDimension > 0): the reference's `path` / `direct`
+    consume the CUDA path's ldsampler numbers draw for draw — pins WHICH draws are 1D and which are 2D, which the shared
+    independent stream cannot tell apart."""
+    sd = S.cornell_box(32, 32, spp=8, max_depth=5, sampler="ldctr", seed=97)
+    li_case(td, "ldctr_cornell", sd)
+    sd = S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ldctr", seed=101)
+    li_case(td, "ldctr_materials", sd)
+    sd = S.materials_scene(48, 32, spp=4, max_depth=6, sampler="ldctr", seed=103)
+    sd.sampler["dimension"] = 2
+    sd.set_integrator("direct")
+    li_case(td, "ldctr_direct", sd)
+
+
 def sobol_cases(td):
     """The `sobol` sampler (src/samplers/sobol.cpp): the reference's own plugin drives `path` on the materials scene (48 x 32 -> the
     enumeration works on a 64 x 64 grid) and on the Cornell box at a non-power-of-two size; deterministic, no shared sampler needed."""
@@ -282,6 +296,10 @@ def fog_cases(td):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "ldctr":            # round 2
+        with tempfile.TemporaryDirectory() as td:
+            ldctr_cases(td)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "sobol":            # round 2
         with tempfile.TemporaryDirectory() as td:
             sobol_cases(td)

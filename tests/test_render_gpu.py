@@ -139,7 +139,8 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
                                   "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights",
-                                  "envmap", "envmap_direct", "textured", "textured_direct", "textured_plastic"])
+                                  "envmap", "envmap_direct", "textured", "textured_direct", "textured_plastic",
+                                  "ldctr_cornell", "ldctr_materials", "ldctr_direct"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
     the same random numbers (ctr sampler, box filter, classic block renderer) — once with every bounce run by the wavefront
@@ -150,6 +151,17 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     spp, seed = int(g["spp"]), int(g["seed"])
     if name == "cornell":
         sd = S.cornell_box(32, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed)
+    elif name.startswith("ldctr_"):
+        # the ldsampler's numbers (csrc/shading.cuh ld_next1D / ld_next2D) against the reference integrators fed the same numbers
+        # by the counter sampler's low-discrepancy twin (oracle/ctrsampler.cpp): the 1D and 2D counters advance separately, so
+        # this pins which draws are 1D and which are 2D; parameters of make_golden_render.ldctr_cases
+        if name == "ldctr_cornell":
+            sd = S.cornell_box(32, 32, spp=spp, max_depth=5, sampler="ldctr", seed=seed)
+        else:
+            sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ldctr", seed=seed)
+            if name == "ldctr_direct":
+                sd.sampler["dimension"] = 2
+                sd.set_integrator("direct")
     elif name == "materials":
         sd = S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed)
     elif name == "direct":
