@@ -238,6 +238,9 @@ def ldctr_cases(td):
     sd.sampler["dimension"] = 2
     sd.set_integrator("direct")
     li_case(td, "ldctr_direct", sd)
+    # the volumetric integrators draw 1D numbers for distances and lobes, 2D numbers for phase functions and emitters
+    li_case(td, "fog_ldctr", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ldctr", seed=107, haze=True))
+    li_case(td, "fogmis_ldctr", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ldctr", seed=109, haze=True, kind="volpath"))
 
 
 def sobol_cases(td):

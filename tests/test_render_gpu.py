@@ -224,7 +224,7 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
 
 
-@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze"])
+@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr"])
 def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
     (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
@@ -236,8 +236,13 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     spp, seed = int(g["spp"]), int(g["seed"])
     # fogmis*: VolumetricPathTracer::Li (volpath.cpp:84-425), the variant with multiple importance sampling
     kind = "volpath" if name.startswith("fogmis") else "volpath_simple"
-    sd = S.fog_scene(48, 32, spp=spp, max_depth={"": 6, "_short": 3, "_haze": -1}[name.replace("fogmis", "").replace("fog", "")], sampler="ctr", seed=seed,
-                     haze=name.endswith("_haze"), kind=kind)
+    if name.endswith("_ldctr"):
+        # the ldsampler's numbers through the reference's volumetric integrators (the counter sampler's low-discrepancy twin):
+        # distances and lobe choices are 1D draws, phase functions and emitter samples 2D draws, counted separately
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ldctr", seed=seed, haze=True, kind=kind)
+    else:
+        sd = S.fog_scene(48, 32, spp=spp, max_depth={"": 6, "_short": 3, "_haze": -1}[name.replace("fogmis", "").replace("fog", "")], sampler="ctr", seed=seed,
+                         haze=name.endswith("_haze"), kind=kind)
     L, film, stats = _li_image(pkg, ctx, sd)
     img = L[..., 0:3].mean(axis=2)
     ok = _close(img, ref, 2e-3, 2e-4).all(axis=2)
