@@ -67,6 +67,9 @@ static void configureDeviceSampler(mtsb_render *r, const Sampler *sampler) {
 		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { const uint64_t v = sobol::Matrices::vdc_sobol_matrices[m][c]; t.push_back((uint32_t) v); t.push_back((uint32_t) (v >> 32)); }
 		for (int m = 0; m < 16; ++m) for (int c = 0; c < 52; ++c) { const uint64_t v = sobol::Matrices::vdc_sobol_matrices_inv[m][c]; t.push_back((uint32_t) v); t.push_back((uint32_t) (v >> 32)); }
 		MTSB_CALL(mtsb_render_set_sobol(r, t.data(), t.size()));
+	} else if (cls == "CounterSampler" && sampler->getProperties().getInteger("ldDimension", 0) > 0) {
+		// the oracle's counter sampler in its low-discrepancy mode (oracle/ctrsampler.cpp): the device's ldsampler numbers
+		MTSB_CALL(mtsb_render_set_ldsampler(r, sampler->getProperties().getInteger("ldDimension", 0), sampler->getSampleCount()));
 	} else if (cls == "LowDiscrepancySampler") {
 		// ldsampler.cpp:78-87: `dimension` (default 4); getSampleCount() is already rounded up to a power of two
 		const int dimension = sampler->getProperties().getInteger("dimension", 4);

@@ -227,6 +227,13 @@ def test_ldsampler_through_the_loader(pkg, tmp_path, golden):
         return float(e[: int(e.size * 0.98)].mean())
     sd = pkg.scenes.cornell_box(64, 64, spp=16, max_depth=5, sampler="ldsampler", rfilter="box")
     xml = sd.to_xml(str(tmp_path), "cbox_ld")
+    # and per pixel: the stock `path` fed the device's numbers by the counter sampler's low-discrepancy twin (oracle/ctrsampler.cpp)
+    sd2 = pkg.scenes.cornell_box(64, 64, spp=16, max_depth=5, sampler="ldctr", seed=7, rfilter="box")
+    xml2 = sd2.to_xml(str(tmp_path), "cbox_ldctr")
+    ref2, _ = run_mitsuba(str(tmp_path / "ref_ldctr.pfm"), True, False, {}, xml=xml2)
+    gpu2, _ = run_mitsuba(str(tmp_path / "gpu_ldctr.pfm"), True, True, {}, xml=xml2)
+    ok = (np.abs(gpu2 - ref2) <= 2e-4 + 2e-3 * np.abs(ref2)).all(axis=2)
+    assert ok.mean() >= 0.97, "%.4f of the pixels match the reference's own render" % ok.mean()
     for classic in (True, False):
         gpu, log = run_mitsuba(str(tmp_path / ("gpu%d.pfm" % classic)), classic, True, {}, xml=xml)
         assert "gpupath:" in log, "the overlay plugin did not run"
