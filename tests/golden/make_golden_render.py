@@ -248,6 +248,10 @@ def sobol_cases(td):
     enumeration works on a 64 x 64 grid) and on the Cornell box at a non-power-of-two size; deterministic, no shared sampler needed."""
     li_case(td, "sobol_materials", S.materials_scene(48, 32, spp=4, max_depth=6, sampler="sobol", seed=0))
     li_case(td, "sobol_cornell", S.cornell_box(40, 24, spp=8, max_depth=5, sampler="sobol", seed=0))
+    # through the volumetric integrators: distance / lobe draws interleave 1D and 2D requests, which moves the places where the
+    # reserved-dimension quirk of next2D bites
+    li_case(td, "sobol_fog", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="sobol", seed=0, haze=True))
+    li_case(td, "sobol_fogmis", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="sobol", seed=0, haze=True, kind="volpath"))
 
 
 def all_case(td):

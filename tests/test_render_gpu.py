@@ -261,7 +261,7 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     assert stats["paths"] == img.shape[0] * img.shape[1] * spp * 2
 
 
-@pytest.mark.parametrize("name", ["sobol_materials", "sobol_cornell"])
+@pytest.mark.parametrize("name", ["sobol_materials", "sobol_cornell", "sobol_fog", "sobol_fogmis"])
 def test_sobol_sampler_matches_reference_per_sample(pkg, ctx, golden, tmp_path, name):
     """The `sobol` sampler (src/samplers/sobol.cpp:172-251 over sobolseq.h): pixel-wise enumeration of the sequence (look_up on the
     film size rounded up to a power of two), the first two dimensions as the position inside the pixel, one dimension per later
@@ -271,9 +271,12 @@ def test_sobol_sampler_matches_reference_per_sample(pkg, ctx, golden, tmp_path, 
     g = golden("li_%s.npz" % name)
     ref = g["image"]
     spp = int(g["spp"])
-    sd = (S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="sobol", seed=0) if name == "sobol_materials"
-          else S.cornell_box(40, 24, spp=spp, max_depth=5, sampler="sobol", seed=0))
-    for tail in (TAIL_OFF, TAIL_ALL):
+    if name in ("sobol_fog", "sobol_fogmis"):       # volpath_simple / volpath over the haze variant of the fog scene
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="sobol", seed=0, haze=True, kind="volpath" if name == "sobol_fogmis" else "volpath_simple")
+    else:
+        sd = (S.materials_scene(48, 32, spp=spp, max_depth=6, sampler="sobol", seed=0) if name == "sobol_materials"
+              else S.cornell_box(40, 24, spp=spp, max_depth=5, sampler="sobol", seed=0))
+    for tail in (TAIL_OFF, TAIL_ALL) if "fog" not in name else (TAIL_OFF,):      # the volumetric integrators have no tail kernel
         L, film, stats = _li_image(pkg, ctx, sd, tail=tail)
         # Sobol' points are dyadic: one pixel in 64 owns a sample exactly on its corner, which the box filter (radius 0.5 + 1e-5,
         # src/rfilters/box.cpp:33-40) also splats into the three pixels that share the corner.  The reference image is a developed
