@@ -932,7 +932,7 @@ def envmap_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent",
     return sd
 
 
-def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False):
+def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False, sphere_light=False):
     """Participating media: a ball of isotropic fog behind an index-matched boundary (no BSDF: `null`), a
     glass ball filled with a forward-scattering (HG, g = 0.6) coloured medium, a diffuse ball, on a mesh floor under a mesh
     area light, a point light and a constant environment; camera outside the media.  haze=True wraps all of it in a large
@@ -963,6 +963,10 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
     sd.add_mesh(gV, gN, np.array([[0, 2, 1], [0, 3, 2]], np.uint32), bsdf=dict(type="diffuse", reflectance=(0.5, 0.5, 0.5)))
     lV, lN, lF = displaced_sphere(1, seed=99, radius=0.4, center=(0.5, 2.6, 0.3), amplitude=0.0)
     sd.add_mesh(lV, lN, lF, bsdf=None, emitter=(25, 22, 18))
+    if sphere_light:
+        # an area light on an analytic sphere: the scene is no longer "plain", the volumetric kernels run with their emitter /
+        # texture / environment-map branches compiled in (render_vol.cuh: PLAIN = false)
+        sd.add_sphere((-1.8, 1.6, 1.0), 0.25, bsdf=None, emitter=(12, 14, 18))
     sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
     sd.set_integrator(kind, max_depth=max_depth, rr_depth=3)
     return sd

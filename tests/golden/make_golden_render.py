@@ -300,6 +300,9 @@ def fog_cases(td):
     li_case(td, "fogmis", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=37, kind="volpath"))
     li_case(td, "fogmis_short", S.fog_scene(48, 32, spp=4, max_depth=3, sampler="ctr", seed=41, kind="volpath"))
     li_case(td, "fogmis_haze", S.fog_scene(48, 32, spp=4, max_depth=-1, sampler="ctr", seed=43, haze=True, kind="volpath"))
+    # an area light on an analytic sphere inside the haze: the kernels compiled WITH the analytic-light / texture / envmap branches
+    li_case(td, "fog_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, haze=True, sphere_light=True))
+    li_case(td, "fogmis_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=53, haze=True, sphere_light=True, kind="volpath"))
 
 
 if __name__ == "__main__":

@@ -224,7 +224,7 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
 
 
-@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr"])
+@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere"])
 def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
     (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
@@ -236,7 +236,11 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     spp, seed = int(g["spp"]), int(g["seed"])
     # fogmis*: VolumetricPathTracer::Li (volpath.cpp:84-425), the variant with multiple importance sampling
     kind = "volpath" if name.startswith("fogmis") else "volpath_simple"
-    if name.endswith("_ldctr"):
+    if name.endswith("_sphere"):
+        # an analytic sphere light in the haze: volshade_kernel<*, PLAIN = false> (the variants with the analytic-light, texture and
+        # environment-map code compiled in), which the other fog scenes never launch
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, sphere_light=True, kind=kind)
+    elif name.endswith("_ldctr"):
         # the ldsampler's numbers through the reference's volumetric integrators (the counter sampler's low-discrepancy twin):
         # distances and lobe choices are 1D draws, phase functions and emitter samples 2D draws, counted separately
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ldctr", seed=seed, haze=True, kind=kind)
