@@ -932,7 +932,7 @@ def envmap_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent",
     return sd
 
 
-def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False, sphere_light=False):
+def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False, sphere_light=False, envmap=False, envmap_pyramid=None):
     """Participating media: a ball of isotropic fog behind an index-matched boundary (no BSDF: `null`), a
     glass ball filled with a forward-scattering (HG, g = 0.6) coloured medium, a diffuse ball, on a mesh floor under a mesh
     area light, a point light and a constant environment; camera outside the media.  haze=True wraps all of it in a large
@@ -940,7 +940,10 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
     boundaries separate two media, and rays leave the haze through its boundary to reach the environment."""
     sd = SceneDesc()
     sd.add_point_light((-3.0, 4.0, -2.0), (20, 18, 15))
-    sd.add_constant_env((0.3, 0.35, 0.5))
+    if envmap:      # the synthetic sky of envmap_scene instead of the constant environment (seen through the media)
+        sd.add_envmap(sky_image(), scale=1.3, to_world=rotate((0, 1, 0), 35) @ rotate((1, 0, 0), 20), pyramid=envmap_pyramid)
+    else:
+        sd.add_constant_env((0.3, 0.35, 0.5))
     fog = sd.add_medium((0.2, 0.2, 0.2), (1.6, 1.8, 2.2))
     milk = sd.add_medium((0.05, 0.4, 0.8), (3.0, 2.5, 1.5), phase="hg", g=0.6)
     V, N, F = displaced_sphere(2, seed=41, radius=0.6, center=(-1.0, 0.65, 0.1), amplitude=0.0)

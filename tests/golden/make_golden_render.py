@@ -303,6 +303,11 @@ def fog_cases(td):
     # an area light on an analytic sphere inside the haze: the kernels compiled WITH the analytic-light / texture / envmap branches
     li_case(td, "fog_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, haze=True, sphere_light=True))
     li_case(td, "fogmis_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=53, haze=True, sphere_light=True, kind="volpath"))
+    # the environment map behind the media (pyramid: tests/golden/envmap_pyramid.npz, as envmap_cases dumps it)
+    g = np.load(os.path.join(GOLD, "envmap_pyramid.npz"))
+    pyramid = [g["level%d" % l].astype(np.float32) for l in range(len(g.files))]
+    li_case(td, "fog_envmap", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=59, haze=True, envmap=True, envmap_pyramid=pyramid))
+    li_case(td, "fogmis_envmap", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=61, haze=True, envmap=True, envmap_pyramid=pyramid, kind="volpath"))
 
 
 if __name__ == "__main__":

@@ -224,7 +224,7 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
 
 
-@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere"])
+@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere", "fog_envmap", "fogmis_envmap"])
 def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
     (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
@@ -240,6 +240,9 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
         # an analytic sphere light in the haze: volshade_kernel<*, PLAIN = false> (the variants with the analytic-light, texture and
         # environment-map code compiled in), which the other fog scenes never launch
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, sphere_light=True, kind=kind)
+    elif name.endswith("_envmap"):
+        # the environment map seen and sampled through the media (importance sampling, EWA lookups where the camera sees it)
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, envmap=True, envmap_pyramid=_pyramid(golden), kind=kind)
     elif name.endswith("_ldctr"):
         # the ldsampler's numbers through the reference's volumetric integrators (the counter sampler's low-discrepancy twin):
         # distances and lobe choices are 1D draws, phase functions and emitter samples 2D draws, counted separately
