@@ -224,6 +224,17 @@ def texture_cases(td):
     li_case(td, "textured", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=79, pyramids=pyramids))
     li_case(td, "textured_direct", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=83, pyramids=pyramids, kind="direct"))
     li_case(td, "textured_plastic", S.textured_scene(48, 32, spp=4, max_depth=5, sampler="ctr", seed=89, pyramids=pyramids, plastic=True))
+    li_case(td, "textured_thinlens", textured_thinlens(pyramids))
+
+
+def textured_thinlens(pyramids, spp=4, seed=113):
+    """The textured scene through a `thinlens` sensor: ThinLensCamera::sampleRayDifferential (thinlens.cpp:324-372) aims the two
+    offset rays through the SAME aperture point, which is what the uv partials of the first hit are computed from."""
+    sd = S.textured_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramids=pyramids)
+    s = sd.sensor
+    sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=spp, seed=seed, sampler="ctr",
+                  aperture_radius=0.08, focus_distance=4.6)
+    return sd
 
 
 def ldctr_cases(td):

@@ -139,7 +139,7 @@ def _li_image(pkg, ctx, sd, tail=-1, positions=False):
 @pytest.mark.parametrize("tail", [TAIL_OFF, TAIL_ALL], ids=["wavefront", "tailkernel"])
 @pytest.mark.parametrize("name", ["cornell", "materials", "materials_deep", "direct", "thinlens", "strict",
                                   "direct_4_2", "direct_1_3", "direct_3_1", "direct_2_0", "analytic", "roughplastic", "analytic_lights",
-                                  "envmap", "envmap_direct", "textured", "textured_direct", "textured_plastic",
+                                  "envmap", "envmap_direct", "textured", "textured_direct", "textured_plastic", "textured_thinlens",
                                   "ldctr_cornell", "ldctr_materials", "ldctr_direct"])
 def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     """Per-pixel mean of Li over the pixel's samples vs the reference's own `path` plugin rendering the same scene with
@@ -182,6 +182,13 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
         # by 1 / sqrt(spp)) where the camera sees the map directly — through `path` and through `direct`
         sd = S.envmap_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramid=_pyramid(golden),
                             kind="direct" if name == "envmap_direct" else "path")
+    elif name == "textured_thinlens":
+        # ray differentials of the thinlens sensor (thinlens.cpp:324-372) feeding the texture lookups of the first hit;
+        # parameters of make_golden_render.textured_thinlens
+        sd = S.textured_scene(48, 32, spp=spp, max_depth=5, sampler="ctr", seed=seed, pyramids=_tex_pyramids(golden))
+        s = sd.sensor
+        sd.set_sensor(s["to_world"], s["fov"], s["width"], s["height"], rfilter="box", spp=spp, seed=seed, sampler="ctr",
+                      aperture_radius=0.08, focus_distance=4.6)
     elif name in ("textured", "textured_direct", "textured_plastic"):
         # `bitmap` textures on diffuse reflectances: uv partials from the sensor ray's differentials at the first hit
         # (intersection.cpp:5-76) and EWA / trilinear lookups there, full-resolution lookups at later hits; repeat / clamp / mirror
