@@ -255,6 +255,57 @@ def plugin_bench(pkg, sd3=None, threads=None, gpus=(1,)):
     return out
 
 
+def transmittance_bench(pkg, ctx, cpu=True, n=1 << 22):
+    """SURVEY 8 f1: batched Scene::evalTransmittance (mtsb_eval_transmittance) on random segments of the fog scene (haze variant:
+    three media, index-matched boundaries) — host buffers in, host buffers out, H2D / D2H inside the timed call; the reference's own
+    Scene::evalTransmittance on one host thread (oracle/raydump.cpp `transmittance`) on a 2^18-segment sample of the same batch."""
+    import subprocess
+    import tempfile
+    B, S = pkg.binding, pkg.scenes
+    sd = S.fog_scene(48, 32, spp=4, haze=True)
+    sc = sd.upload(ctx, B.BUILDER_PLOC)
+    rng = np.random.default_rng(23)
+    lo, hi = np.array([-2.2, 0.05, -1.6]), np.array([2.2, 2.2, 1.6])
+    p1 = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    p2 = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    d_fog = np.linalg.norm(p1 - np.array([-1.0, 0.65, 0.1], np.float32), axis=1)
+    d_milk = np.linalg.norm(p1 - np.array([0.4, 0.55, -0.2], np.float32), axis=1)
+    medium = np.where(d_fog < 0.6, 0, np.where(d_milk < 0.5, 1, 2)).astype(np.int32)        # fog ball, glass ball of milk, haze
+    seg = np.zeros(n, B.segment_dtype)
+    seg["p1"], seg["p2"], seg["medium"] = p1, p2, medium
+    T = np.zeros((n, 3), np.float32)
+    sc.eval_transmittance_segments(seg, out=T)                                             # warm-up
+    best = 1e9
+    for _ in range(3):
+        t0 = time.perf_counter()
+        sc.eval_transmittance_segments(seg, out=T)
+        best = min(best, time.perf_counter() - t0)
+    out = {"segments": n, "seconds": best, "segments_per_s": n / best, "blocked_fraction": float((T.max(axis=1) == 0).mean()),
+           "api": "mtsb_eval_transmittance(host buffers): H2D of the segments, the walk, D2H of the answers"}
+    sc.close()
+    if cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle as O
+        m = 1 << 18
+        if O.have_reference():
+            with tempfile.TemporaryDirectory() as td:
+                xml = sd.to_xml(td, "fog")
+                inp = np.zeros((m, 8), np.float32)
+                inp[:, 0:3] = p1[:m]; inp[:, 4:7] = p2[:m]; inp[:, 7] = medium[:m]
+                ip, op = os.path.join(td, "in.bin"), os.path.join(td, "out.bin")
+                inp.tofile(ip)
+                r = subprocess.run([os.path.join(O.REF_DIR, "mtsutil"), "raydump", "transmittance", xml, ip, op], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                line = [l for l in r.stdout.splitlines() if l.startswith("transmittance_seconds:")]
+                if line and os.path.exists(op):
+                    secs = float(line[0].split()[1])
+                    ref = np.fromfile(op, np.float32).reshape(-1, 3)
+                    both = (ref.max(axis=1) > 0) & (T[:m].max(axis=1) > 0)
+                    out["reference"] = {"segments": m, "seconds": secs, "segments_per_s": m / secs, "threads": 1, "kind": "reference",
+                                        "blocked_agree": float(((ref.max(axis=1) == 0) == (T[:m].max(axis=1) == 0)).mean()),
+                                        "max_abs_diff": float(np.abs(ref[both] - T[:m][both]).max())}
+    return out
+
+
 def ply_load_bench(pkg, ctx, sd, cpu=True):
     """SURVEY 8 f3, the on-disk geometry path: the scene's emitter-less meshes as binary PLY file images
       device     image -> mtsb_scene_add_ply (H2D of the image) -> decode kernels at commit (device ms from CUDA events)
@@ -347,6 +398,7 @@ def run(pkg, ctx, stream, configs=(1, 3, 4, 5), cpu=True, rank=0, world=1, comm=
         if cpu:
             out["volpath_cpu_reference"] = cpu_reference(pkg, S.fog_scene(1024, 768, spp=8, max_depth=8, haze=True), os.cpu_count() or 1,
                                                          what="fog scene (volpath_simple) at %d spp (of 64)")
+        out["eval_transmittance_fog"] = transmittance_bench(pkg, ctx, cpu=cpu)
     sd = None
     if {3, 4, 5, "plugin", "ply"} & set(configs):
         t0 = time.perf_counter()

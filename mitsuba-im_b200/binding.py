@@ -442,7 +442,13 @@ class Scene:
         seg["p1"] = p1; seg["p2"] = np.asarray(p2, np.float32).reshape(-1, 3)
         seg["medium"] = medium
         seg["flags"] = np.asarray(p1_on_surface, np.uint32) * 1 + np.asarray(p2_on_surface, np.uint32) * 2
-        out = np.zeros((p1.shape[0], 3), np.float32)
+        return self.eval_transmittance_segments(seg, max_interactions=max_interactions)
+
+    def eval_transmittance_segments(self, segments, out=None, max_interactions=-1):
+        """mtsb_eval_transmittance on a prepared segment_dtype array (what a C caller hands over)."""
+        seg = np.ascontiguousarray(segments, dtype=segment_dtype)
+        if out is None:
+            out = np.zeros((seg.shape[0], 3), np.float32)
         _check(lib().mtsb_eval_transmittance(self.h, _ptr(seg), seg.shape[0], int(max_interactions), _ptr(out)))
         return out
 
