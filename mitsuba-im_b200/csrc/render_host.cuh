@@ -592,7 +592,8 @@ int mtsb_eval_transmittance(mtsb_scene *scene, const mtsb_segment *segments, siz
 	const unsigned grid = (unsigned) ctx->smCount * MTSB_TAIL_MIN_BLOCKS;
 	MTSB_CHECK(launch_trav(scene, scene->curved ? connect_vol_kernel<true> : connect_vol_kernel<false>, grid, st, scene->dev, ps));
 	MTSB_CUDA(cudaGetLastError());
-	std::vector<float4> host(n);
+	std::vector<float4> host;
+	try { host.resize(n); } catch (const std::exception &) { MTSB_FAIL(MTSB_ENOMEM, "mtsb_eval_transmittance: %zu bytes of host memory", n * sizeof(float4)); }
 	MTSB_CUDA(cudaMemcpyAsync(host.data(), ps.L, n * sizeof(float4), cudaMemcpyDeviceToHost, st));
 	MTSB_CUDA(cudaStreamSynchronize(st));
 	for (size_t i = 0; i < n; ++i) { out_rgb[3 * i] = host[i].x; out_rgb[3 * i + 1] = host[i].y; out_rgb[3 * i + 2] = host[i].z; }
