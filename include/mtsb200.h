@@ -244,8 +244,8 @@ MTSB_API int  mtsb_scene_add_mesh(mtsb_scene *scene, const float *positions, con
  * Reads what the reference binds: float32 x y z, nx ny nz, u|s|texture_u, v|t|texture_v of `vertex`, the
  * vertex_indices / vertex_index list of `face` (uchar|uint count, int|uint index); other scalar properties are skipped;
  * a file without normals gets the angle-weighted vertex normals of computeNormals.  MTSB_EUNSUPPORTED (use the host
- * parser + mtsb_scene_add_mesh): ascii files, files mixing triangles and quads, other list properties (binary_big_endian
- * files are byte-swapped on the device).
+ * parser + mtsb_scene_add_mesh): ascii files, other list properties (binary_big_endian files are byte-swapped on the
+ * device; for a file that mixes triangles and quads the host makes one pass over the count fields to index the records).
  * Vertex colours are not kept (the device subset has no `vertexcolors` texture).  The shape cannot carry an area emitter.
  * vertex_count / triangle_count (may be NULL) receive the sizes.  Returns the shape index. */
 #define MTSB_PLY_FACE_NORMALS 1u

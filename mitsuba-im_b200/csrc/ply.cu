@@ -16,10 +16,10 @@
 // each byte of the file once: the kernels are HBM-streaming, algorithmic bytes = file body + 32 B per vertex + 12 B per
 // triangle written.
 //
-// A face list is variable-length in the format, which makes the position of face i depend on every face before it.  The
-// decoder therefore takes the two layouts that make up practically every file — all triangles or all quads, told apart by
-// the size of the face element — and refuses a mixed file with MTSB_EUNSUPPORTED (load it with the host parser and
-// mtsb_scene_add_mesh); every count byte is still verified on the device.
+// A face list is variable-length in the format, which makes the position of face i depend on every face before it.  The two
+// layouts that make up practically every file — all triangles or all quads, told apart by the size of the face element — need
+// no index at all (every count byte is still verified on the device); for a file that mixes the two the host makes ONE pass
+// over the count fields and hands the kernel a {record offset, first triangle} pair per face.
 #include "scene.cuh"
 #include <string>
 #include <cstring>
@@ -43,6 +43,11 @@ struct PlyLayout {
 	int f64;                              // attributes are doubles (`serialized` with EDoublePrecision), converted like readHelper does
 	int normalizeStored;                  // ply.cpp:210 always normalises a stored normal, serialized.cpp:191-194 only behind a toWorld
 	int bigEndian;                        // `format binary_big_endian`: every multi-byte field is byte-swapped after the load
+	// a file that mixes triangles and quads: per face {byte offset of its record inside the face element, index of its first
+	// triangle}, found by ONE sequential pass of the host over the count bytes (records are self-delimiting only in order);
+	// NULL for the uniform layouts, where both follow from the face's number
+	const uint2 *faceIndex;
+	uint32_t triangleCount;
 };
 
 __device__ __forceinline__ uint32_t load_u32(const uint32_t *words, size_t byteOffset) {
@@ -133,22 +138,25 @@ __global__ void ply_face_kernel(const uint32_t *words, size_t base, PlyLayout L,
 		const float *positions, float *normals, uint32_t *indices, uint32_t *error) {
 	const uint32_t f = blockIdx.x * blockDim.x + threadIdx.x;
 	if (f >= L.faceCount) return;
-	const size_t rec = base + L.faceBegin + (size_t) f * L.faceStride + L.faceListOffset;
+	size_t rec = base + L.faceBegin + (size_t) f * L.faceStride + L.faceListOffset;
+	uint32_t vertsPerFace = L.vertsPerFace, firstTri = f * (L.vertsPerFace - 2);
+	if (L.faceIndex) { const uint2 fi = L.faceIndex[f]; rec = base + L.faceBegin + fi.x + L.faceListOffset; firstTri = fi.y; }
 	if (L.faceCountBytes) {
 		uint32_t count = load_u32(words, rec);                 // a one-byte count is the first byte in memory either way
 		if (L.faceCountBytes == 1) count &= 0xffu;
 		else if (L.bigEndian) count = __byte_perm(count, 0, 0x0123);
-		if (count != L.vertsPerFace) { atomicOr(error, 1u); return; }
+		if (L.faceIndex) { if (count != 3 && count != 4) { atomicOr(error, 1u); return; } vertsPerFace = count; }
+		else if (count != L.vertsPerFace) { atomicOr(error, 1u); return; }
 	}
 	uint32_t v[4] = { 0, 0, 0, 0 };
 	bool ok = true;
-	for (uint32_t k = 0; k < L.vertsPerFace; ++k) {
+	for (uint32_t k = 0; k < vertsPerFace; ++k) {
 		v[k] = load_u32(words, rec + L.faceCountBytes + 4 * k, L.bigEndian);
 		ok = ok && v[k] < L.vertexCount;          // Assert((size_t) element < m_vertexCount), ply.cpp:266,272 (a negative int32 fails it too)
 	}
 	if (!ok) { atomicOr(error, 2u); return; }
-	const uint32_t trisPerFace = L.vertsPerFace - 2;
-	uint32_t *out = indices + (size_t) f * trisPerFace * 3;
+	const uint32_t trisPerFace = vertsPerFace - 2;
+	uint32_t *out = indices + (size_t) firstTri * 3;
 	uint32_t t0[3] = { v[0], v[1], v[2] }, t1[3] = { v[3], v[0], v[2] };
 	if (swapWinding) { uint32_t s = t0[0]; t0[0] = t0[1]; t0[1] = s; s = t1[0]; t1[0] = t1[1]; t1[1] = s; }   // faceNormals + flipNormals (trimesh.cpp:616-622)
 	out[0] = t0[0]; out[1] = t0[1]; out[2] = t0[2];
@@ -199,10 +207,11 @@ struct PlyMesh {
 	int shape = -1; bool hasNormals = false, faceNormals = false, flipNormals = false;
 	bool mirrored = false;                       // serialized.cpp:197-202: a toWorld with a negative determinant swaps the winding
 	const char *kind = "PLY";
+	DevBuf<uint2> faceIndex;                     // mixed triangle / quad files only
 	uint32_t vtxBase = 0, triBase = 0;
 };
 
-static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, bool &hasNormals, bool &hasUV) {
+static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, bool &hasNormals, bool &hasUV, std::vector<uint2> *faceIndexOut = nullptr) {
 	memset(&L, 0, sizeof(L));
 	for (int a = 0; a < 3; ++a) { L.offPos[a] = -1; L.offNrm[a] = -1; }
 	L.offUV[0] = L.offUV[1] = -1;
@@ -287,10 +296,31 @@ static int parse_header(const unsigned char *file, size_t bytes, PlyLayout &L, b
 	if (L.faceBegin + otherBytesAfterFace > bytes) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: file is shorter than its header says");
 	const size_t faceBytes = bytes - L.faceBegin - otherBytesAfterFace;
 	const size_t fixed = (size_t) L.faceStride + L.faceCountBytes;
+	L.faceIndex = nullptr;
 	if (faceBytes == (fixed + 12) * L.faceCount) L.vertsPerFace = 3;
 	else if (faceBytes == (fixed + 16) * L.faceCount) L.vertsPerFace = 4;
-	else MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_ply: %u faces in %zu bytes: neither all triangles nor all quads (or a truncated file); mixed files go through the host parser", L.faceCount, faceBytes);
-	L.faceStride = (uint32_t) (fixed + 4 * L.vertsPerFace);
+	else {
+		// neither all triangles nor all quads: one pass over the count fields finds where every record starts
+		if (faceBytes > 0xffffffffull) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_add_ply: a mixed triangle / quad face element larger than 4 GB");
+		const unsigned char *fb = file + L.faceBegin;
+		size_t off = 0; uint64_t tri = 0;
+		if (faceIndexOut) faceIndexOut->resize(L.faceCount);
+		for (uint32_t f = 0; f < L.faceCount; ++f) {
+			if (off + fixed > faceBytes) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: %u faces in %zu bytes: the face element ends inside face %u (a truncated file?)", L.faceCount, faceBytes, f);
+			const unsigned char *c = fb + off + L.faceListOffset;
+			uint32_t count = c[0];
+			if (L.faceCountBytes == 4) count = bigEndian ? ((uint32_t) c[0] << 24 | (uint32_t) c[1] << 16 | (uint32_t) c[2] << 8 | c[3]) : ((uint32_t) c[3] << 24 | (uint32_t) c[2] << 16 | (uint32_t) c[1] << 8 | c[0]);
+			if (count != 3 && count != 4)      // ply.cpp:251-262
+				MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: %u faces in %zu bytes: neither all triangles nor all quads, and face %u has %u vertices (only triangle and quad-based PLY meshes are supported; a truncated file?)", L.faceCount, faceBytes, f, count);
+			if (faceIndexOut) (*faceIndexOut)[f] = make_uint2((uint32_t) off, (uint32_t) tri);
+			off += fixed + 4 * (size_t) count; tri += count - 2;
+		}
+		if (off != faceBytes) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: neither all triangles nor all quads, and the faces take %zu bytes of a %zu-byte face element (a truncated file?)", off, faceBytes);
+		if (tri > 0x7fffffffull) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_add_ply: too many triangles");
+		L.vertsPerFace = 0; L.triangleCount = (uint32_t) tri;
+	}
+	if (L.vertsPerFace) { L.faceStride = (uint32_t) (fixed + 4 * L.vertsPerFace); L.triangleCount = L.faceCount * (L.vertsPerFace - 2); }
+	else L.faceStride = 0;
 	L.posBase = L.nrmBase = L.uvBase = L.vertexBegin;
 	L.posStride = L.nrmStride = L.uvStride = L.vertexStride;
 	L.f64 = 0; L.normalizeStored = 1; L.bigEndian = bigEndian ? 1 : 0;
@@ -326,13 +356,19 @@ int ply_stage(mtsb_scene *scene, const void *file, size_t bytes, const float *to
 		uint32_t *vertexCountOut, uint32_t *triangleCountOut, bool *hasUVOut, bool *hasNormalsOut, PlyMesh **out) {
 	PlyMesh *M = new PlyMesh();
 	bool hasUV = false;
-	int rc = parse_header((const unsigned char *) file, bytes, M->L, M->hasNormals, hasUV);
+	std::vector<uint2> faceIndex;
+	int rc = parse_header((const unsigned char *) file, bytes, M->L, M->hasNormals, hasUV, &faceIndex);
 	if (!rc) rc = set_transform(M, toWorld, toWorldInv, "mtsb_scene_add_ply");
 	M->faceNormals = (flags & MTSB_PLY_FACE_NORMALS) != 0; M->flipNormals = (flags & MTSB_PLY_FLIP_NORMALS) != 0;
-	if (!rc) rc = upload_image(scene, M, file, bytes, "mtsb_scene_add_ply");
+	if (!rc && M->L.vertsPerFace == 0) {
+		cudaSetDevice(scene->ctx->device);
+		rc = M->faceIndex.upload(faceIndex.data(), faceIndex.size(), scene->ctx->stream);
+		M->L.faceIndex = M->faceIndex.ptr;
+	}
+	if (!rc) rc = upload_image(scene, M, file, bytes, "mtsb_scene_add_ply");      // synchronizes: faceIndex may go out of scope
 	if (rc) { delete M; return rc; }
 	(void) bsdf;
-	*vertexCountOut = M->L.vertexCount; *triangleCountOut = M->L.faceCount * (M->L.vertsPerFace - 2);
+	*vertexCountOut = M->L.vertexCount; *triangleCountOut = M->L.triangleCount;
 	*hasUVOut = hasUV; *hasNormalsOut = M->hasNormals && !M->faceNormals;
 	*out = M;
 	return 0;
@@ -389,7 +425,7 @@ static int ser_inflate(const unsigned char *src, size_t srcBytes, int version, P
 	memset(&L, 0, sizeof(L));
 	L.f64 = (flags & 0x2000u) ? 1 : 0;                                    // EDoublePrecision
 	const uint32_t fsz = L.f64 ? 8 : 4;
-	L.vertexCount = (uint32_t) V; L.faceCount = (uint32_t) T; L.vertsPerFace = 3; L.faceCountBytes = 0; L.faceListOffset = 0; L.faceStride = 12;
+	L.vertexCount = (uint32_t) V; L.faceCount = (uint32_t) T; L.triangleCount = (uint32_t) T; L.faceIndex = nullptr; L.vertsPerFace = 3; L.faceCountBytes = 0; L.faceListOffset = 0; L.faceStride = 12;
 	for (int a = 0; a < 3; ++a) { L.offPos[a] = (int) (a * fsz); L.offNrm[a] = -1; }
 	L.offUV[0] = L.offUV[1] = -1;
 	size_t next = p;
@@ -459,7 +495,7 @@ int ply_probe(const void *file, size_t bytes, uint32_t *nv, uint32_t *nt) {
 	PlyLayout L; bool hn = false, hu = false;
 	MTSB_CHECK(parse_header((const unsigned char *) file, bytes, L, hn, hu));
 	if (nv) *nv = L.vertexCount;
-	if (nt) *nt = L.faceCount * (L.vertsPerFace - 2);
+	if (nt) *nt = L.triangleCount;
 	return 0;
 }
 
@@ -489,7 +525,7 @@ int ply_decode(mtsb_scene *scene, PlyMesh *M, float *positions, float *normals, 
 	cudaEventDestroy(ev0); cudaEventDestroy(ev1);
 	if (err[0] & 1u) MTSB_FAIL(MTSB_EUNSUPPORTED, "mtsb_scene_commit: %s shape %d mixes triangles and quads (or holds a face that is neither): load it with the host parser", M->kind, M->shape);
 	if (err[0] & 2u) MTSB_FAIL(MTSB_EINVAL, "mtsb_scene_commit: %s shape %d: a face references a vertex >= %u", M->kind, M->shape, L.vertexCount);
-	M->raw.release();
+	M->raw.release(); M->faceIndex.release();
 	return 0;
 }
 

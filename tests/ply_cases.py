@@ -103,6 +103,18 @@ def cases():
          "element face %d" % len(F6), "property list uchar int vertex_indices"],
         [(k, f32) for k in ("x", "y", "z")], [V6[:, 0], V6[:, 1], V6[:, 2]],
         [("n", "u1"), ("i", "<i4", 3)], [np.full(len(F6), 3), F6]), xml='<boolean name="flipNormals" value="true"/>', kwargs=dict(flip_normals=True))
+    # 7. triangles and quads mixed in one face element: variable-length records, indexed by one host pass over the count bytes
+    nq = len(Q) // 2
+    recs = []
+    for k, q in enumerate(Q):
+        if k < nq or k % 3 == 0:
+            recs.append(bytes([4]) + np.asarray(q, "<i4").tobytes())
+        else:
+            recs.append(bytes([3]) + np.asarray(q[[0, 1, 2]], "<i4").tobytes() + bytes([3]) + np.asarray(q[[0, 2, 3]], "<i4").tobytes())
+    nfaces = sum(1 if r[0] == 4 else 2 for r in recs)
+    hdr = ("ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+           "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % (len(V), nfaces)).encode("ascii")
+    out["mixed_tri_quad_computed"] = dict(image=hdr + np.ascontiguousarray(V, "<f4").tobytes() + b"".join(recs), xml="", kwargs={})
     return out
 
 
