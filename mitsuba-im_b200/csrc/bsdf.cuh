@@ -284,8 +284,7 @@ __device__ inline V3 bsdf_sample_1(const BsdfRec &b, const V3 &wi, float sx, flo
 			out.pdf = MTS_INV_PI * out.wo.z;
 			return v3(b.p[0], b.p[1], b.p[2]);
 		}
-		case MTSB_BSDF_PASSTHROUGH: {                              // null.cpp:55-78
-			if (LEAN) __builtin_unreachable();
+		case MTSB_BSDF_PASSTHROUGH: {                              // null.cpp:55-78 (part of the LEAN set: the volumetric kernels meet it)
 			out.wo = v3(-wi.x, -wi.y, -wi.z); out.type = B_NULL; out.pdf = 1.0f;
 			return v3(1.0f);
 		}

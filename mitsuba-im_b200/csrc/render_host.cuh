@@ -68,6 +68,15 @@ static int launch_trav(mtsb_scene *scene, void (*kernel)(KArgs...), unsigned gri
 
 struct LoopShape { unsigned traceGrid, shadeGrid, tailGrid; };
 
+// which instantiation of the volumetric shade kernel a render runs (render_vol.cuh): MIS = `volpath`, PLAIN / LEAN by the scene
+typedef void (*VolShadeKernel)(SceneDev, PathState, IntegratorDev, uint32_t);
+static VolShadeKernel volshade_kernel_for(const mtsb_render *r, bool mis) {
+	const mtsb_scene *scene = r->scene;
+	const bool lean = scene->volLean && !r->integ.sobol;
+	if (mis) return lean ? volshade_kernel<1, true, true> : (scene->plain ? volshade_kernel<1, true, false> : volshade_kernel<1, false, false>);
+	return lean ? volshade_kernel<0, true, true> : (scene->plain ? volshade_kernel<0, true, false> : volshade_kernel<0, false, false>);
+}
+
 static void destroy_bounce_graph(mtsb_render *r) {
 	if (r->bounceExec) cudaGraphExecDestroy(r->bounceExec);
 	if (r->bounceGraph) cudaGraphDestroy(r->bounceGraph);
@@ -114,7 +123,7 @@ static int build_bounce_graph(mtsb_render *r, const LoopShape &sh, uint32_t tail
 	void *aShade[] = { &S, &ps, &integ, &seed };
 	MTSB_CUDA(add_kernel(body, &n1, nullptr, scene->curved ? (void *) extend_kernel<true> : (void *) extend_kernel<false>, sh.traceGrid, MTSB_TRACE_BLOCK, aExtend, scene));
 	if (vol_mode(r)) {
-		MTSB_CUDA(add_kernel(body, &n2, n1, volmis_mode(r) ? (scene->plain ? (void *) volshade_kernel<1, true> : (void *) volshade_kernel<1, false>) : (scene->plain ? (void *) volshade_kernel<0, true> : (void *) volshade_kernel<0, false>), sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
+		MTSB_CUDA(add_kernel(body, &n2, n1, (void *) volshade_kernel_for(r, volmis_mode(r)), sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
 		MTSB_CUDA(add_kernel(body, &n3, n2, scene->curved ? (void *) connect_vol_kernel<true> : (void *) connect_vol_kernel<false>, sh.tailGrid, MTSB_TRACE_BLOCK, aTrace, scene));
 	} else {
 		MTSB_CUDA(add_kernel(body, &n2, n1, (scene->lean && !r->integ.sobol) ? (void *) shade_kernel<true> : (void *) shade_kernel<false>, sh.shadeGrid, RENDER_BLOCK, aShade, nullptr));
@@ -197,8 +206,7 @@ static int run_chunk(mtsb_render *r, const GenParams &g, float *samplesOut, floa
 		for (uint32_t bounce = 0; bounce < ctl.maxBounces; ++bounce) {
 			MTSB_CHECK(launch_trav(scene, scene->curved ? extend_kernel<true> : extend_kernel<false>, sh.traceGrid, st, S, ps, 0u));
 			if (vol_mode(r)) {
-				if (volmis_mode(r)) { if (scene->plain) volshade_kernel<1, true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed); else volshade_kernel<1, false><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed); }
-				else { if (scene->plain) volshade_kernel<0, true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed); else volshade_kernel<0, false><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed); }
+				volshade_kernel_for(r, volmis_mode(r))<<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);
 				MTSB_CHECK(launch_trav(scene, scene->curved ? connect_vol_kernel<true> : connect_vol_kernel<false>, sh.tailGrid, st, S, ps));
 			} else {
 				if (scene->lean && !r->integ.sobol) shade_kernel<true><<<sh.shadeGrid, RENDER_BLOCK, 0, st>>>(S, ps, r->integ, r->seed);

@@ -142,14 +142,14 @@ __device__ __forceinline__ uint32_t vol_max_interactions(const IntegratorDev &in
 }
 
 // One iteration of the while loop of SimpleVolumetricPathTracer::Li for the path in `slot`.
-template <bool PLAIN = false>
+template <bool PLAIN = false, bool LEAN = false>
 __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, VolOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
 	float4 thr4 = ps.thr[slot];
 	const float4 prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = LEAN ? nullptr : integ.sobol;
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);
 	float eta = thr4.w;
@@ -233,7 +233,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 						const V3 value = scene_sample_emitter_direct<PLAIN>(S, sf.p, refN, sx, sy, ds);
 						if (ds.pdf != 0 && !is_zero(value)) {
 							const V3 wo = to_local(sf, ds.d);
-							const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
+							const V3 bsdfVal = bsdf_eval<LEAN>(bsdf, wi, wo);
 							if (!is_zero(bsdfVal) && (!integ.strictNormals || dot(sf.ng, ds.d) * wo.z > 0)) {
 								const int med = (sh.interior >= 0 || sh.exterior >= 0) ? target_medium(sh, sf.ng, ds.d) : medium;   // scene.cpp:919-920
 								const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
@@ -247,7 +247,7 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 				float sx, sy; next2D(rs, sx, sy);
 				const float sz = bsdf_uses_sampler(bsdf) ? next1D(rs) : 0.0f;
 				BsdfSample bs;
-				const V3 bsdfVal = bsdf_sample(bsdf, wi, sx, sy, sz, bs);
+				const V3 bsdfVal = bsdf_sample<LEAN>(bsdf, wi, sx, sy, sz, bs);
 				if (is_zero(bsdfVal)) out.alive = false;
 				else {
 					uint32_t recursive = 0;
@@ -303,14 +303,14 @@ __device__ __forceinline__ void volshade_path(const SceneDev &S, const PathState
 // function therefore begins with the TAIL of the previous iteration — the emitter found at (or behind) the first hit, then
 // the Russian roulette that closes that iteration — as shade_path does for `path`.  Behind an index-matched first hit the walk
 // goes on in connect_vol_kernel (a VQ_LOOK queue entry).
-template <bool PLAIN = false>
+template <bool PLAIN = false, bool LEAN = false>
 __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &ps, const IntegratorDev &integ, uint32_t seed,
 		uint32_t slot, VolOut &out) {
 	const float4 r0 = ps.rayO[slot], r1 = ps.rayD[slot], h = ps.hit[slot];
 	float4 thr4 = ps.thr[slot];
 	const float4 prev = ps.prev[slot];
 	const uint4 rg = ps.rng[slot];
-	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = integ.sobol;
+	SamplerState rs; rs.px = rg.x; rs.py = rg.y; rs.sample = rg.z; rs.dim = PATH_DIM(rg.w); rs.seed = seed; rs.sobol = LEAN ? nullptr : integ.sobol;
 	const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r1.x, r1.y, r1.z);
 	V3 thr = v3(thr4.x, thr4.y, thr4.z), Li = v3(0.0f);
 	float eta = thr4.w;
@@ -450,10 +450,10 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 							const V3 value = scene_sample_emitter_direct<PLAIN>(S, sf.p, refN, sx, sy, ds);
 							if (ds.pdf != 0 && !is_zero(value)) {
 								const V3 wo = to_local(sf, ds.d);
-								const V3 bsdfVal = bsdf_eval(bsdf, wi, wo);
+								const V3 bsdfVal = bsdf_eval<LEAN>(bsdf, wi, wo);
 								if (!is_zero(bsdfVal) && (!integ.strictNormals || dot(sf.ng, ds.d) * wo.z > 0)) {
 									const bool onSurface = S.emitters[ds.emitter].type != MTSB_EMITTER_POINT;
-									const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf(bsdf, wi, wo) : 0.0f;
+									const float bp = (onSurface && ds.measure == M_SOLID_ANGLE) ? bsdf_pdf<LEAN>(bsdf, wi, wo) : 0.0f;
 									const int med = transition ? target_medium(sh, sf.ng, ds.d) : medium;
 									vol_request(out, sf.p, ds.p, VQ_PACK(VQ_P1_SURFACE | (onSurface ? VQ_P2_SURFACE : 0u), med, vol_max_interactions(integ, depth)),
 										thr * value * bsdfVal * mi_weight(ds.pdf, bp), slot);
@@ -465,7 +465,7 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 					float sx, sy; next2D(rs, sx, sy);
 					const float sz = bsdf_uses_sampler(bsdf) ? next1D(rs) : 0.0f;
 					BsdfSample bs;
-					const V3 bsdfWeight = bsdf_sample(bsdf, wi, sx, sy, sz, bs);
+					const V3 bsdfWeight = bsdf_sample<LEAN>(bsdf, wi, sx, sy, sz, bs);
 					if (is_zero(bsdfWeight)) out.alive = false;
 					else {
 						const V3 wo = to_world(sf, bs.wo);
@@ -518,7 +518,10 @@ __device__ __forceinline__ void volmis_path(const SceneDev &S, const PathState &
 #define MTSB_VOLSHADE_MIN_BLOCKS 1
 #endif
 // MIS = 0: volpath_simple (volshade_path), 1: volpath (volmis_path); PLAIN: scene->plain (no envmap / textures / analytic lights)
-template <int MIS = 0, bool PLAIN = false>
+// LEAN (implies PLAIN): every BSDF is diffuse / null / dielectric / GGX roughconductor with visible-normal sampling / the index-matched
+// `null` boundary, and the sampler is the independent one — the other BSDFs' and samplers' code is left out of the kernel, which is
+// bound by instruction fetch (profiles/r02v_ncu_full_vol.json: stall_no_instruction 8.5-9.2 cycles per issue)
+template <int MIS = 0, bool PLAIN = false, bool LEAN = false>
 __global__ void __launch_bounds__(RENDER_BLOCK, MTSB_VOLSHADE_MIN_BLOCKS)
 volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 	const uint32_t parity = ps.counters[CTR_PARITY] & 1u;
@@ -530,8 +533,8 @@ volshade_kernel(SceneDev S, PathState ps, IntegratorDev integ, uint32_t seed) {
 		const uint32_t slot = QUEUE_SLOT(queueIn[i]);
 		if (__float_as_uint(ps.hit[slot].w) == SUSPENDED_SLOT) { queueOut[warp_append(countOut)] = slot | QUEUE_RESUME; continue; }
 		VolOut vo;
-		if (MIS) volmis_path<PLAIN>(S, ps, integ, seed, slot, vo);
-		else volshade_path<PLAIN>(S, ps, integ, seed, slot, vo);
+		if (MIS) volmis_path<PLAIN, LEAN>(S, ps, integ, seed, slot, vo);
+		else volshade_path<PLAIN, LEAN>(S, ps, integ, seed, slot, vo);
 		if (vo.alive) queueOut[warp_append(countOut)] = slot;
 		for (int k = 0; k < 2; ++k)
 			if (k < vo.nReq) {

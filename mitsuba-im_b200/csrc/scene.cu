@@ -725,11 +725,13 @@ int mtsb_scene_commit(mtsb_scene *scene, int builder) {
 	for (const ShapeRec &sh : scene->shapes)
 		if (sh.emitter >= 0 && (sh.type == SHAPE_SPHERE || sh.type == SHAPE_DISK)) scene->plain = false;     // emitter.cuh: LEAN
 	scene->lean = !(ctx->shadeLean == 0) && scene->plain;
+	scene->volLean = scene->lean;
 	for (const BsdfRec &b : scene->bsdfs) {
 		const int t = b.type & 0xff;
 		const bool ok = t == MTSB_BSDF_DIFFUSE || t == MTSB_BSDF_NULL || t == MTSB_BSDF_DIELECTRIC ||
 			(t == MTSB_BSDF_ROUGHCONDUCTOR && b.p[11] == 1.0f && b.p[12] != 0.0f);
 		if (!ok) scene->lean = false;
+		if (!ok && t != MTSB_BSDF_PASSTHROUGH) scene->volLean = false;
 	}
 	mtsb::l2_claim(scene, scene->bvh.accel.bytes());
 	scene->committed = true;

@@ -11,6 +11,7 @@ struct mtsb_scene {
 	mtsb_ctx *ctx = nullptr;
 	bool committed = false;
 	bool lean = false;                    // every BSDF is diffuse / null / dielectric / GGX roughconductor with visible-normal sampling (bsdf.cuh: LEAN)
+	bool volLean = false;                 // LEAN for the volumetric kernels: the same set plus the index-matched `null` boundary (render_vol.cuh)
 	bool plain = true;                    // no environment map, no textures, no area light on an analytic sphere / disk: kernels compiled without those branches
 	bool curved = false;                  // holds analytic disks / spheres: traversal kernels with their leaf test (trace.cuh)
 
