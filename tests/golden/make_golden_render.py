@@ -314,6 +314,11 @@ def fog_cases(td):
     # an area light on an analytic sphere inside the haze: the kernels compiled WITH the analytic-light / texture / envmap branches
     li_case(td, "fog_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=47, haze=True, sphere_light=True))
     li_case(td, "fogmis_sphere", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=53, haze=True, sphere_light=True, kind="volpath"))
+    # strictNormals + hideEmitters in the volumetric integrators (volpath_simple.cpp:176-197,223,266; volpath.cpp likewise)
+    for name, kind, seed in (("fog_strict", "volpath_simple", 67), ("fogmis_strict", "volpath", 71)):
+        sd = S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=seed, haze=True, kind=kind)
+        sd.set_integrator(kind, max_depth=6, rr_depth=3, strict_normals=True, hide_emitters=True)
+        li_case(td, name, sd)
     # the environment map behind the media (pyramid: tests/golden/envmap_pyramid.npz, as envmap_cases dumps it)
     g = np.load(os.path.join(GOLD, "envmap_pyramid.npz"))
     pyramid = [g["level%d" % l].astype(np.float32) for l in range(len(g.files))]

@@ -231,7 +231,8 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
     assert stats["closest_rays"] >= stats["paths"] and stats["depth_sum"] >= stats["paths"]
 
 
-@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere", "fog_envmap", "fogmis_envmap"])
+@pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere", "fog_envmap", "fogmis_envmap",
+                                  "fog_strict", "fogmis_strict"])
 def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
     (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
@@ -247,6 +248,10 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
         # an analytic sphere light in the haze: volshade_kernel<*, PLAIN = false> (the variants with the analytic-light, texture and
         # environment-map code compiled in), which the other fog scenes never launch
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, sphere_light=True, kind=kind)
+    elif name.endswith("_strict"):
+        # strictNormals + hideEmitters (volpath_simple.cpp:176-197,223,266); parameters of make_golden_render.fog_cases
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, kind=kind)
+        sd.set_integrator(kind, max_depth=6, rr_depth=3, strict_normals=True, hide_emitters=True)
     elif name.endswith("_envmap"):
         # the environment map seen and sampled through the media (importance sampling, EWA lookups where the camera sees it)
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, envmap=True, envmap_pyramid=_pyramid(golden), kind=kind)
