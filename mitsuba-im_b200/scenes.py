@@ -932,7 +932,8 @@ def envmap_scene(width=48, height=32, spp=4, max_depth=5, sampler="independent",
     return sd
 
 
-def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False, sphere_light=False, envmap=False, envmap_pyramid=None):
+def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", seed=0, kind="volpath_simple", haze=False, sphere_light=False, envmap=False, envmap_pyramid=None,
+              ball_bsdf=None, aperture_radius=0.0):
     """Participating media: a ball of isotropic fog behind an index-matched boundary (no BSDF: `null`), a
     glass ball filled with a forward-scattering (HG, g = 0.6) coloured medium, a diffuse ball, on a mesh floor under a mesh
     area light, a point light and a constant environment; camera outside the media.  haze=True wraps all of it in a large
@@ -959,7 +960,7 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
         sd.set_media(c, interior=hz)
         sd.set_camera_medium(hz)
     V, N, F = displaced_sphere(2, seed=43, radius=0.4, center=(1.5, 0.45, 0.5), amplitude=0.03)
-    sd.add_mesh(V, N, F, bsdf=dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
+    sd.add_mesh(V, N, F, bsdf=ball_bsdf if ball_bsdf is not None else dict(type="diffuse", reflectance=(0.6, 0.3, 0.2)))
     g = 4.0
     gV = np.array([[-g, 0, -g], [g, 0, -g], [g, 0, g], [-g, 0, g]], np.float32)
     gN = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
@@ -970,7 +971,8 @@ def fog_scene(width=48, height=32, spp=4, max_depth=6, sampler="independent", se
         # an area light on an analytic sphere: the scene is no longer "plain", the volumetric kernels run with their emitter /
         # texture / environment-map branches compiled in (render_vol.cuh: PLAIN = false)
         sd.add_sphere((-1.8, 1.6, 1.0), 0.25, bsdf=None, emitter=(12, 14, 18))
-    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed)
+    sd.set_sensor(look_at((0.3, 3.0, -4.5), (0, 0.4, 0), (0, 1, 0)), 40.0, width, height, rfilter="box", spp=spp, sampler=sampler, seed=seed,
+                  aperture_radius=aperture_radius, focus_distance=5.2)
     sd.set_integrator(kind, max_depth=max_depth, rr_depth=3)
     return sd
 

@@ -319,6 +319,10 @@ def fog_cases(td):
         sd = S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=seed, haze=True, kind=kind)
         sd.set_integrator(kind, max_depth=6, rr_depth=3, strict_normals=True, hide_emitters=True)
         li_case(td, name, sd)
+    # a plastic ball (the kernels outside the LEAN set, independent sampler) seen through a thinlens sensor inside the haze
+    PLASTIC = dict(type="plastic", diffuse_reflectance=(0.6, 0.3, 0.2), nonlinear=True)
+    li_case(td, "fog_plastic_thinlens", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=73, haze=True, ball_bsdf=PLASTIC, aperture_radius=0.1))
+    li_case(td, "fogmis_plastic_thinlens", S.fog_scene(48, 32, spp=4, max_depth=6, sampler="ctr", seed=79, haze=True, ball_bsdf=PLASTIC, aperture_radius=0.1, kind="volpath"))
     # the environment map behind the media (pyramid: tests/golden/envmap_pyramid.npz, as envmap_cases dumps it)
     g = np.load(os.path.join(GOLD, "envmap_pyramid.npz"))
     pyramid = [g["level%d" % l].astype(np.float32) for l in range(len(g.files))]

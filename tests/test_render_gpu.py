@@ -232,7 +232,7 @@ def test_li_matches_reference_per_sample(pkg, ctx, golden, name, tail):
 
 
 @pytest.mark.parametrize("name", ["fog", "fog_short", "fog_haze", "fogmis", "fogmis_short", "fogmis_haze", "fog_ldctr", "fogmis_ldctr", "fog_sphere", "fogmis_sphere", "fog_envmap", "fogmis_envmap",
-                                  "fog_strict", "fogmis_strict"])
+                                  "fog_strict", "fogmis_strict", "fog_plastic_thinlens", "fogmis_plastic_thinlens"])
 def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
     """SimpleVolumetricPathTracer::Li (src/integrators/path/volpath_simple.cpp:88-300) with homogeneous media
     (src/medium/homogeneous.cpp), isotropic / HG phase functions and Scene::evalTransmittance through index-matched
@@ -248,6 +248,10 @@ def test_volpath_simple_matches_reference_per_sample(pkg, ctx, golden, name):
         # an analytic sphere light in the haze: volshade_kernel<*, PLAIN = false> (the variants with the analytic-light, texture and
         # environment-map code compiled in), which the other fog scenes never launch
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, sphere_light=True, kind=kind)
+    elif name.endswith("_plastic_thinlens"):
+        # a plastic ball: volshade_kernel<*, PLAIN, LEAN = false> under the independent sampler; thinlens sensor inside the haze
+        sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, kind=kind, aperture_radius=0.1,
+                         ball_bsdf=dict(type="plastic", diffuse_reflectance=(0.6, 0.3, 0.2), nonlinear=True))
     elif name.endswith("_strict"):
         # strictNormals + hideEmitters (volpath_simple.cpp:176-197,223,266); parameters of make_golden_render.fog_cases
         sd = S.fog_scene(48, 32, spp=spp, max_depth=6, sampler="ctr", seed=seed, haze=True, kind=kind)
